@@ -1,0 +1,3 @@
+from .data import Data  # noqa: F401
+from .synth import synthetic_batch  # noqa: F401
+from .seeding import fill_deterministic  # noqa: F401
