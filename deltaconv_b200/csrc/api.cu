@@ -1,0 +1,36 @@
+// Library-wide plumbing of the C ABI: error reporting and device facts.
+#include "common.cuh"
+#include <stdarg.h>
+#include <stdio.h>
+
+static thread_local char g_err[512] = "";
+
+void dc_set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int dc_check_launch(const char* what) {
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) return DC_OK;
+    dc_set_error("%s: %s", what, cudaGetErrorString(e));
+    return (int)e;
+}
+
+int dc_sm_count() {
+    static thread_local int cached_dev = -1, cached = 148;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+    if (dev != cached_dev) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0) cached = n;
+        cached_dev = dev;
+    }
+    return cached;
+}
+
+extern "C" const char* dc_last_error(void) { return g_err; }
+extern "C" int dc_abi_version(void) { return 1; }
+extern "C" int dc_device_sm_count(void) { return dc_sm_count(); }

@@ -1,0 +1,233 @@
+// K2/K3 — tangent frames and the fused WLS grad/div operator build, emitting fixed-k ELL.
+//
+// Reference path replaced (relative to /root/reference): deltaconv/geometry/grad_div_mls.py
+//   :10-47 estimate_basis, :50-69 build_tangent_basis, :197-277 build_grad_div and its helpers —
+//   ~70 ATen launches, [E,*] temporaries, two COO->CSR sorts become:
+//     edge_mean_kernel  (pass A: per-point mean edge length)            -> ws.m[N]
+//     cloud_mean_kernel (per-cloud mean of m, zero the cloud maxima)    -> ws.abar[B], ws.S[B]
+//     fit_kernel<REDUCE> (pass B1: fit, row norms, per-cloud max)        -> ws.S[B]   (only if normalized)
+//     fit_kernel<WRITE>  (pass B2: fit again, scale, frame mapping)      -> G[N,k,2], D[N,k,2]
+// One thread owns one point; its k slots live in shared memory slot-major (stride T+1, conflict
+// free), which also turns the idx tile load and the G/D tile stores into fully coalesced
+// streams.  The 6x6 normal equations are assembled and Cholesky-solved in registers.
+#include "common.cuh"
+#include "geom_core.cuh"
+
+namespace {
+
+__global__ void tangent_basis_kernel(const float* __restrict__ normal, int N, float* __restrict__ xb, float* __restrict__ yb) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    V3 n = v3_load(normal + 3 * (size_t)i), ex, ey;
+    tangent_basis(n, ex, ey);
+    xb[3 * (size_t)i] = ex.x; xb[3 * (size_t)i + 1] = ex.y; xb[3 * (size_t)i + 2] = ex.z;
+    yb[3 * (size_t)i] = ey.x; yb[3 * (size_t)i + 1] = ey.y; yb[3 * (size_t)i + 2] = ey.z;
+}
+
+__global__ void estimate_basis_kernel(const float* __restrict__ pos, const int* __restrict__ idx, int N, int k,
+                                      const float* __restrict__ orient, float* __restrict__ normal,
+                                      float* __restrict__ xb, float* __restrict__ yb) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    V3 p = v3_load(pos + 3 * (size_t)i);
+    double cov[6] = {0, 0, 0, 0, 0, 0};
+    const int* row = idx + (size_t)i * k;
+    for (int e = 0; e < k; ++e) {
+        int j = __ldg(row + e);
+        if (j < 0 || j >= N) j = 0;
+        V3 d = v3_load(pos + 3 * (size_t)j) - p;
+        cov[0] += (double)d.x * d.x; cov[1] += (double)d.x * d.y; cov[2] += (double)d.x * d.z;
+        cov[3] += (double)d.y * d.y; cov[4] += (double)d.y * d.z; cov[5] += (double)d.z * d.z;
+    }
+    V3 n, ex, ey;
+    frame_from_scatter(cov, orient ? orient + 3 * (size_t)i : nullptr, n, ex, ey);
+    size_t o = 3 * (size_t)i;
+    normal[o] = n.x; normal[o + 1] = n.y; normal[o + 2] = n.z;
+    xb[o] = ex.x; xb[o + 1] = ex.y; xb[o + 2] = ex.z;
+    yb[o] = ey.x; yb[o + 1] = ey.y; yb[o + 2] = ey.z;
+}
+
+// ---- pass A: m_i = mean_e ||p_j - p_i||  (grad_div_mls.py:233, :112 inner mean) --------------
+// 8 lanes per point keep the idx reads coalesced and the gathers parallel.
+__global__ void edge_mean_kernel(const float* __restrict__ pos, const int* __restrict__ idx, int N, int k,
+                                 float* __restrict__ m) {
+    const int sub = threadIdx.x & 7;
+    const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 3;
+    float acc = 0.f;
+    if (i < N) {
+        V3 p = v3_load(pos + 3 * (size_t)i);
+        for (int e = sub; e < k; e += 8) {
+            int j = __ldg(idx + (size_t)i * k + e);
+            if (j < 0 || j >= N) j = 0;
+            V3 d = v3_load(pos + 3 * (size_t)j) - p;
+            acc += sqrtf(dot(d, d));
+        }
+    }
+    acc += __shfl_xor_sync(FULL, acc, 4);
+    acc += __shfl_xor_sync(FULL, acc, 2);
+    acc += __shfl_xor_sync(FULL, acc, 1);
+    if (i < N && sub == 0) m[i] = acc / (float)k;
+}
+
+// ---- per-cloud mean of m (scatter_mean, grad_div_mls.py:112); fixed-order tree => deterministic
+__global__ void cloud_mean_kernel(const float* __restrict__ m, const int* __restrict__ cloud_ptr, int B,
+                                  float* __restrict__ abar, unsigned* __restrict__ S) {
+    __shared__ double part[256];
+    const int c = blockIdx.x;
+    const int s = cloud_ptr[c], e = cloud_ptr[c + 1];
+    double acc = 0.0;
+    for (int i = s + threadIdx.x; i < e; i += blockDim.x) acc += (double)m[i];
+    part[threadIdx.x] = acc;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if (threadIdx.x < o) part[threadIdx.x] += part[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        int cnt = e - s;
+        abar[c] = (float)(part[0] / (double)(cnt > 0 ? cnt : 1));
+        S[c] = 0u;
+    }
+}
+
+// ---- pass B ---------------------------------------------------------------------------------
+template <int T, bool WRITE>
+__global__ void __launch_bounds__(T)
+fit_kernel(const float* __restrict__ pos, const float* __restrict__ normal, const float* __restrict__ xb,
+           const float* __restrict__ yb, const int* __restrict__ idx, const int* __restrict__ cloud_ptr, int B,
+           int N, int k, float kernel_width, FitParams fp, int normalized, const float* __restrict__ abar,
+           unsigned* __restrict__ S, float* __restrict__ G, float* __restrict__ D,
+           float* __restrict__ dbg_coords, float* __restrict__ dbg_weights, float* __restrict__ dbg_mapping) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    constexpr int STRIDE = T + 1;
+    float4* s_dat = reinterpret_cast<float4*>(smem_raw);                        // [k][STRIDE]
+    int* s_idx = reinterpret_cast<int*>(smem_raw + (size_t)k * STRIDE * sizeof(float4));   // [k][STRIDE]
+
+    const int base = blockIdx.x * T;
+    const int npts = min(T, N - base);
+    const int tile = npts * k;
+    // coalesced idx tile load, transposed into slot-major shared memory
+    const int* gidx = idx + (size_t)base * k;
+    for (int l = threadIdx.x; l < tile; l += T) {
+        int p = l / k, e = l - p * k;
+        s_idx[e * STRIDE + p] = __ldg(gidx + l);
+    }
+    __syncthreads();
+
+    const int i = base + threadIdx.x;
+    if (threadIdx.x < npts) {
+        SlotView sv;
+        sv.idx = s_idx + threadIdx.x;
+        sv.dat = s_dat + threadIdx.x;
+        sv.stride = STRIDE;
+        const V3 p = v3_load(pos + 3 * (size_t)i), n = v3_load(normal + 3 * (size_t)i);
+        const V3 ex = v3_load(xb + 3 * (size_t)i), ey = v3_load(yb + 3 * (size_t)i);
+        const int c = cloud_of(cloud_ptr, B, i);
+        const float sc = kernel_width * __ldg(abar + c);
+        const float wsum = fit_pass1(pos, N, i, k, p, n, ex, ey, sc * sc, sv);
+        float z1[6], z2[6], coef[6];
+        fit_pass2(N, k, wsum, fp, sv, z1, z2, coef);
+        if (!WRITE) {
+            float s_i = fit_row_norm(k, sv, z1, z2);
+            // s_i >= 0, so its bit pattern orders like the value: integer max is exact and
+            // order-independent (deterministic), replacing scatter_max (grad_div_mls.py:259)
+            atomicMax(S + c, __float_as_uint(s_i));
+        } else {
+            const float Sc = normalized ? __uint_as_float(S[c]) : 0.f;
+            fit_pass3(xb, yb, N, k, n, ex, ey, Sc, sv, z1, z2, coef,
+                      dbg_coords ? dbg_coords + (size_t)i * k * 2 : nullptr,
+                      dbg_weights ? dbg_weights + (size_t)i * k : nullptr,
+                      dbg_mapping ? dbg_mapping + (size_t)i * k * 4 : nullptr);
+        }
+    }
+    if (!WRITE) return;
+    __syncthreads();
+    // coalesced G / D tile stores (float2 per slot)
+    float2* gG = reinterpret_cast<float2*>(G) + (size_t)base * k;
+    float2* gD = reinterpret_cast<float2*>(D) + (size_t)base * k;
+    for (int l = threadIdx.x; l < tile; l += T) {
+        int p = l / k, e = l - p * k;
+        float4 v = s_dat[e * STRIDE + p];
+        gG[l] = make_float2(v.x, v.y);
+        gD[l] = make_float2(v.z, v.w);
+    }
+}
+
+size_t fit_smem_bytes(int T, int k) { return (size_t)k * (T + 1) * (sizeof(float4) + sizeof(int)); }
+
+template <int T>
+int launch_fit(bool write, const float* pos, const float* normal, const float* xb, const float* yb, const int* idx,
+               const int* cloud_ptr, int B, int N, int k, float kernel_width, FitParams fp, int normalized,
+               const float* abar, unsigned* S, float* G, float* D, float* dc, float* dw, float* dm, cudaStream_t st) {
+    size_t smem = fit_smem_bytes(T, k);
+    int grid = dc_ceil_div(N, T);
+    if (write) {
+        DC_CUDA(cudaFuncSetAttribute(fit_kernel<T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        fit_kernel<T, true><<<grid, T, smem, st>>>(pos, normal, xb, yb, idx, cloud_ptr, B, N, k, kernel_width, fp,
+                                                    normalized, abar, S, G, D, dc, dw, dm);
+    } else {
+        DC_CUDA(cudaFuncSetAttribute(fit_kernel<T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        fit_kernel<T, false><<<grid, T, smem, st>>>(pos, normal, xb, yb, idx, cloud_ptr, B, N, k, kernel_width, fp,
+                                                     normalized, abar, S, G, D, dc, dw, dm);
+    }
+    return dc_check_launch("dc_build_grad_div/fit");
+}
+
+}  // namespace
+
+extern "C" int dc_tangent_basis(const float* normal, int N, float* xb, float* yb, void* stream) {
+    if (N <= 0) return DC_OK;
+    tangent_basis_kernel<<<dc_ceil_div(N, 256), 256, 0, (cudaStream_t)stream>>>(normal, N, xb, yb);
+    return dc_check_launch("dc_tangent_basis");
+}
+
+extern "C" int dc_estimate_basis(const float* pos, const int32_t* idx, int N, int k, const float* orient_or_null,
+                                 float* normal, float* xb, float* yb, void* stream) {
+    DC_REQUIRE(k >= 1, "dc_estimate_basis: k must be >= 1");
+    if (N <= 0) return DC_OK;
+    estimate_basis_kernel<<<dc_ceil_div(N, 128), 128, 0, (cudaStream_t)stream>>>(pos, idx, N, k, orient_or_null, normal, xb, yb);
+    return dc_check_launch("dc_estimate_basis");
+}
+
+extern "C" size_t dc_build_ws_bytes(int N, int B) {
+    // m[N] floats, abar[B] floats, S[B] uints; each region 256-byte aligned
+    size_t a = ((size_t)N * 4 + 255) / 256 * 256, b = ((size_t)B * 4 + 255) / 256 * 256;
+    return a + 2 * b;
+}
+
+extern "C" int dc_build_grad_div(const float* pos, const float* normal, const float* xb, const float* yb,
+                                 const int32_t* idx, const int32_t* cloud_ptr, int B, int N, int k,
+                                 float kernel_width, float lam, float lam_shape, int use_shape, int normalized,
+                                 float* G, float* D, float* dbg_coords, float* dbg_weights, float* dbg_mapping,
+                                 void* ws, size_t ws_bytes, void* stream) {
+    DC_REQUIRE(k >= 1 && k <= 256, "dc_build_grad_div: k must be in [1,256] (got %d)", k);
+    DC_REQUIRE(B >= 1, "dc_build_grad_div: B must be >= 1");
+    DC_REQUIRE(ws_bytes >= dc_build_ws_bytes(N, B), "dc_build_grad_div: workspace too small (%zu < %zu)", ws_bytes,
+               dc_build_ws_bytes(N, B));
+    if (N <= 0) return DC_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    size_t a = ((size_t)N * 4 + 255) / 256 * 256, b = ((size_t)B * 4 + 255) / 256 * 256;
+    float* m = (float*)ws;
+    float* abar = (float*)((char*)ws + a);
+    unsigned* S = (unsigned*)((char*)ws + a + b);
+    FitParams fp;
+    fp.lam = lam; fp.lam_shape = lam_shape; fp.use_shape = use_shape;
+
+    edge_mean_kernel<<<dc_ceil_div((long long)N * 8, 256), 256, 0, st>>>(pos, idx, N, k, m);
+    cloud_mean_kernel<<<B, 256, 0, st>>>(m, cloud_ptr, B, abar, S);
+    int rc = dc_check_launch("dc_build_grad_div/mean");
+    if (rc) return rc;
+    // threads per CTA: as many as keep two CTAs resident per SM (<= ~110 KB of shared memory each)
+    const size_t budget = 110 * 1024;
+    for (int pass = normalized ? 0 : 1; pass < 2; ++pass) {
+        bool write = pass == 1;
+        if (fit_smem_bytes(128, k) <= budget)
+            rc = launch_fit<128>(write, pos, normal, xb, yb, idx, cloud_ptr, B, N, k, kernel_width, fp, normalized, abar, S, G, D, dbg_coords, dbg_weights, dbg_mapping, st);
+        else if (fit_smem_bytes(64, k) <= budget)
+            rc = launch_fit<64>(write, pos, normal, xb, yb, idx, cloud_ptr, B, N, k, kernel_width, fp, normalized, abar, S, G, D, dbg_coords, dbg_weights, dbg_mapping, st);
+        else
+            rc = launch_fit<32>(write, pos, normal, xb, yb, idx, cloud_ptr, B, N, k, kernel_width, fp, normalized, abar, S, G, D, dbg_coords, dbg_weights, dbg_mapping, st);
+        if (rc) return rc;
+    }
+    return DC_OK;
+}

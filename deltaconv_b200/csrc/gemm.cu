@@ -1,0 +1,209 @@
+// K9 (first cut) — fp32 SIMT GEMM for the per-point channel mixing: torch.nn.Linear inside
+// MLP / VectorMLP (/root/reference/deltaconv/nn/mlp.py:9,15) and the heads
+// (deltanet_classification.py:33-36, deltanet_segmentation.py:40-51), forward and both backward
+// products, exact fp32 (FFMA) so that the logits parity bound of 1e-4 holds with margin.
+// The tensor-core (tcgen05) kernel for the large layers lives in gemm_tc.cu and is selected by
+// dc_linear_* when the shape allows; this kernel remains the generic path (any M, N, K, strides).
+//
+//   C[i,j] = sum_p A(i,p) * B(p,j) (+ bias[j]),   A(i,p) = A[i*sa_i + p*sa_p],  B(p,j) = B[p*sb_p + j*sb_j]
+#include "common.cuh"
+
+namespace {
+
+constexpr int BM = 128, BN = 64, BK = 16, GT = 256;
+
+struct GemmArgs {
+    const float* A; long long sa_i, sa_p;
+    const float* B; long long sb_p, sb_j;
+    float* C; long long ldc;
+    const float* bias;
+    int M, N, K;
+    int k_per_split;        // reduction elements per grid.z slice
+    float* partial;         // [splits][M][N] when splits > 1
+};
+
+template <bool A_PC, bool B_JC>
+__global__ void __launch_bounds__(GT) sgemm_kernel(GemmArgs g) {
+    __shared__ __align__(16) float As[BK][BM + 4];
+    __shared__ __align__(16) float Bs[BK][BN + 4];
+    const int t = threadIdx.x, tx = t & 15, ty = t >> 4;
+    const int i0 = blockIdx.y * BM, j0 = blockIdx.x * BN;
+    const int k_begin = blockIdx.z * g.k_per_split;
+    const int k_end = min(g.K, k_begin + g.k_per_split);
+    float acc[8][4];
+#pragma unroll
+    for (int r = 0; r < 8; ++r)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) acc[r][c] = 0.f;
+
+    for (int k0 = k_begin; k0 < k_end; k0 += BK) {
+#pragma unroll
+        for (int q = 0; q < (BM * BK) / GT; ++q) {
+            int e = t + GT * q;
+            int p, i;
+            if (A_PC) { p = e % BK; i = e / BK; } else { i = e % BM; p = e / BM; }
+            float v = 0.f;
+            if (i0 + i < g.M && k0 + p < k_end) v = __ldg(g.A + (long long)(i0 + i) * g.sa_i + (long long)(k0 + p) * g.sa_p);
+            As[p][i] = v;
+        }
+#pragma unroll
+        for (int q = 0; q < (BK * BN) / GT; ++q) {
+            int e = t + GT * q;
+            int p, j;
+            if (B_JC) { j = e % BN; p = e / BN; } else { p = e % BK; j = e / BK; }
+            float v = 0.f;
+            if (j0 + j < g.N && k0 + p < k_end) v = __ldg(g.B + (long long)(k0 + p) * g.sb_p + (long long)(j0 + j) * g.sb_j);
+            Bs[p][j] = v;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int p = 0; p < BK; ++p) {
+            float4 a0 = *reinterpret_cast<const float4*>(&As[p][ty * 8]);
+            float4 a1 = *reinterpret_cast<const float4*>(&As[p][ty * 8 + 4]);
+            float4 b = *reinterpret_cast<const float4*>(&Bs[p][tx * 4]);
+            const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+            const float bb[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+            for (int r = 0; r < 8; ++r)
+#pragma unroll
+                for (int c = 0; c < 4; ++c) acc[r][c] = fmaf(a[r], bb[c], acc[r][c]);
+        }
+        __syncthreads();
+    }
+    float* out = g.partial ? g.partial + (size_t)blockIdx.z * g.M * g.N : g.C;
+    const long long ldo = g.partial ? g.N : g.ldc;
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+        int i = i0 + ty * 8 + r;
+        if (i >= g.M) continue;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            int j = j0 + tx * 4 + c;
+            if (j >= g.N) continue;
+            float v = acc[r][c];
+            if (!g.partial && g.bias) v += __ldg(g.bias + j);
+            out[(long long)i * ldo + j] = v;
+        }
+    }
+}
+
+__global__ void splitk_reduce_kernel(const float* __restrict__ partial, int splits, long long MN, int N, float* __restrict__ C,
+                                     long long ldc, const float* __restrict__ bias) {
+    long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (t >= MN) return;
+    float s = 0.f;
+    for (int z = 0; z < splits; ++z) s += partial[(size_t)z * MN + t];     // fixed order: deterministic
+    long long i = t / N; int j = (int)(t - i * N);
+    if (bias) s += __ldg(bias + j);
+    C[i * ldc + j] = s;
+}
+
+int choose_splits(int M, int N, int K) {
+    long long tiles = (long long)dc_ceil_div(M, BM) * dc_ceil_div(N, BN);
+    long long target = 2LL * dc_sm_count();
+    if (tiles >= target || K <= 4 * BK) return 1;
+    long long s = (target + tiles - 1) / tiles;
+    long long maxs = K / (4 * BK);
+    if (s > maxs) s = maxs;
+    if (s > 128) s = 128;
+    return (int)(s < 1 ? 1 : s);
+}
+
+int run_gemm(GemmArgs g, bool a_pc, bool b_jc, void* ws, size_t ws_bytes, cudaStream_t st) {
+    if (g.M <= 0 || g.N <= 0) return DC_OK;
+    int splits = choose_splits(g.M, g.N, g.K);
+    while (splits > 1 && (size_t)splits * g.M * g.N * sizeof(float) > ws_bytes) --splits;
+    int kps = dc_ceil_div(dc_ceil_div(g.K, splits), BK) * BK;
+    if (kps < BK) kps = BK;
+    splits = g.K > 0 ? dc_ceil_div(g.K, kps) : 1;
+    g.k_per_split = kps;
+    g.partial = splits > 1 ? (float*)ws : nullptr;
+    dim3 grid(dc_ceil_div(g.N, BN), dc_ceil_div(g.M, BM), splits);
+    DC_REQUIRE(grid.y <= 65535u, "gemm: M too large for this launch shape");
+    if (a_pc && b_jc) sgemm_kernel<true, true><<<grid, GT, 0, st>>>(g);
+    else if (a_pc && !b_jc) sgemm_kernel<true, false><<<grid, GT, 0, st>>>(g);
+    else if (!a_pc && b_jc) sgemm_kernel<false, true><<<grid, GT, 0, st>>>(g);
+    else sgemm_kernel<false, false><<<grid, GT, 0, st>>>(g);
+    if (splits > 1) {
+        long long MN = (long long)g.M * g.N;
+        splitk_reduce_kernel<<<dc_ceil_div(MN, 256), 256, 0, st>>>(g.partial, splits, MN, g.N, g.C, g.ldc, g.bias);
+    }
+    return dc_check_launch("gemm");
+}
+
+// W [Cout, 2K] = [W1 | W2]  ->  W' [2Cout, 2K] = [[W1, -W2], [W2, W1]]
+// so that VectorMLP's Linear on I_J(v) (deltaconv.py:68, operators.py:19-21) becomes one plain
+// GEMM on the [N, 2K] view of the interleaved vector field: [v_x | v_y] W'^T = [out_x | out_y].
+__global__ void expand_vec_weight_kernel(const float* __restrict__ W, int Cout, int K, float* __restrict__ We) {
+    long long total = (long long)Cout * K;
+    long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (t >= total) return;
+    int o = (int)(t / K), p = (int)(t - (long long)o * K);
+    float w1 = W[(size_t)o * 2 * K + p], w2 = W[(size_t)o * 2 * K + K + p];
+    We[(size_t)o * 2 * K + p] = w1;
+    We[(size_t)o * 2 * K + K + p] = -w2;
+    We[(size_t)(Cout + o) * 2 * K + p] = w2;
+    We[(size_t)(Cout + o) * 2 * K + K + p] = w1;
+}
+
+__global__ void fold_vec_weight_grad_kernel(const float* __restrict__ dWe, int Cout, int K, float* __restrict__ dW) {
+    long long total = (long long)Cout * K;
+    long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (t >= total) return;
+    int o = (int)(t / K), p = (int)(t - (long long)o * K);
+    dW[(size_t)o * 2 * K + p] = dWe[(size_t)o * 2 * K + p] + dWe[(size_t)(Cout + o) * 2 * K + K + p];
+    dW[(size_t)o * 2 * K + K + p] = dWe[(size_t)(Cout + o) * 2 * K + p] - dWe[(size_t)o * 2 * K + K + p];
+}
+
+}  // namespace
+
+// split-K workspace for a product with output M x N and reduction length K (0 when no split is used)
+extern "C" size_t dc_gemm_ws_bytes(int64_t M, int64_t N, int64_t K) {
+    int s = choose_splits((int)M, (int)N, (int)K);
+    return s > 1 ? (size_t)s * (size_t)M * (size_t)N * sizeof(float) : 0;
+}
+
+// Y[M,Nout] = X[M,K] W[Nout,K]^T (+ bias)              — torch.nn.Linear forward
+extern "C" int dc_linear_fwd(const float* X, int64_t ldx, const float* W, int64_t ldw, const float* bias_or_null,
+                             int64_t M, int K, int Nout, float* Y, int64_t ldy, void* ws, size_t ws_bytes, void* stream) {
+    DC_REQUIRE(M < 2147483647LL, "dc_linear_fwd: M must fit in int32");
+    GemmArgs g = {};
+    g.A = X; g.sa_i = ldx; g.sa_p = 1;
+    g.B = W; g.sb_p = 1; g.sb_j = ldw;
+    g.C = Y; g.ldc = ldy; g.bias = bias_or_null; g.M = (int)M; g.N = Nout; g.K = K;
+    return run_gemm(g, true, false, ws, ws_bytes, (cudaStream_t)stream);
+}
+
+// dX[M,K] = dY[M,Nout] W[Nout,K]                       — Linear backward w.r.t. the input
+extern "C" int dc_linear_bwd_input(const float* dY, int64_t ld_dy, const float* W, int64_t ldw, int64_t M, int K, int Nout,
+                                   float* dX, int64_t ld_dx, void* ws, size_t ws_bytes, void* stream) {
+    DC_REQUIRE(M < 2147483647LL, "dc_linear_bwd_input: M must fit in int32");
+    GemmArgs g = {};
+    g.A = dY; g.sa_i = ld_dy; g.sa_p = 1;
+    g.B = W; g.sb_p = ldw; g.sb_j = 1;
+    g.C = dX; g.ldc = ld_dx; g.M = (int)M; g.N = K; g.K = Nout;
+    return run_gemm(g, true, true, ws, ws_bytes, (cudaStream_t)stream);
+}
+
+// dW[Nout,K] = dY[M,Nout]^T X[M,K]                     — Linear backward w.r.t. the weight
+extern "C" int dc_linear_bwd_weight(const float* dY, int64_t ld_dy, const float* X, int64_t ldx, int64_t M, int K, int Nout,
+                                    float* dW, int64_t ld_dw, void* ws, size_t ws_bytes, void* stream) {
+    DC_REQUIRE(M < 2147483647LL, "dc_linear_bwd_weight: M must fit in int32");
+    GemmArgs g = {};
+    g.A = dY; g.sa_i = 1; g.sa_p = ld_dy;
+    g.B = X; g.sb_p = ldx; g.sb_j = 1;
+    g.C = dW; g.ldc = ld_dw; g.M = Nout; g.N = K; g.K = (int)M;
+    return run_gemm(g, false, true, ws, ws_bytes, (cudaStream_t)stream);
+}
+
+extern "C" int dc_expand_vec_weight(const float* W, int Cout, int K, float* W_expanded, void* stream) {
+    if (Cout <= 0 || K <= 0) return DC_OK;
+    expand_vec_weight_kernel<<<dc_ceil_div((long long)Cout * K, 256), 256, 0, (cudaStream_t)stream>>>(W, Cout, K, W_expanded);
+    return dc_check_launch("dc_expand_vec_weight");
+}
+
+extern "C" int dc_fold_vec_weight_grad(const float* dW_expanded, int Cout, int K, float* dW, void* stream) {
+    if (Cout <= 0 || K <= 0) return DC_OK;
+    fold_vec_weight_grad_kernel<<<dc_ceil_div((long long)Cout * K, 256), 256, 0, (cudaStream_t)stream>>>(dW_expanded, Cout, K, dW);
+    return dc_check_launch("dc_fold_vec_weight_grad");
+}

@@ -1,0 +1,610 @@
+// K7/K8/K10 and the BatchNorm pieces — everything in DeltaConv / MLP / VectorMLP that is not an
+// SpMM or a GEMM.  Reference code replaced (relative to /root/reference):
+//   deltaconv/nn/deltaconv.py:50-54   torch_scatter.scatter(reduce='max') over the kNN graph
+//   deltaconv/nn/nonlin.py:11-35      BatchNorm1d wrapper (+ mlp.py:7-11 LeakyReLU)
+//   deltaconv/nn/nonlin.py:63-82      VectorNonLin
+//   deltaconv/models/deltanet_classification.py:46-47, deltanet_segmentation.py:61  global pools
+//
+// BatchNorm in training mode needs a column reduction over all rows between the GEMM and the
+// activation.  It is done as: per-CTA fp64 partial sums (one CTA per row chunk, fixed grid) ->
+// one finalize kernel that adds the partials in a fixed order.  No atomics, bit-reproducible.
+#include "common.cuh"
+
+namespace {
+
+constexpr int RED_T = 256;       // threads per CTA in the column reductions
+constexpr int RED_MAX_CHUNKS = 1184;   // 8 x 148
+
+// ------------------------------------------------------------------------------------------
+// generic column reduction: every element (r, c) contributes NV values; partial[chunk][v][c]
+// ------------------------------------------------------------------------------------------
+struct ColLayout {
+    int col_lanes;     // threads along the columns
+    int row_lanes;     // threads along the rows (col_lanes * row_lanes == RED_T)
+    int col_blocks;    // grid.y : ceil(C / col_lanes)
+    int chunks;        // grid.x
+    long long rows_per_chunk;
+};
+
+ColLayout col_layout(long long M, int C) {
+    ColLayout L;
+    int cl = 1;
+    while (cl < C && cl < 64) cl <<= 1;
+    L.col_lanes = cl;
+    L.row_lanes = RED_T / cl;
+    L.col_blocks = (C + cl - 1) / cl;
+    long long want = (long long)dc_sm_count() * 8 / L.col_blocks;
+    if (want < 1) want = 1;
+    long long by_rows = (M + L.row_lanes * 4 - 1) / (L.row_lanes * 4);   // at least 4 rows per thread
+    if (by_rows < 1) by_rows = 1;
+    long long chunks = want < by_rows ? want : by_rows;
+    if (chunks > RED_MAX_CHUNKS) chunks = RED_MAX_CHUNKS;
+    L.chunks = (int)chunks;
+    L.rows_per_chunk = (M + chunks - 1) / chunks;
+    return L;
+}
+
+template <int NV, class F>
+__global__ void __launch_bounds__(RED_T) col_reduce_kernel(F f, long long M, int C, int col_lanes, long long rows_per_chunk,
+                                                           double* __restrict__ partial) {
+    __shared__ double sh[NV][RED_T];
+    const int cl = threadIdx.x % col_lanes, rl = threadIdx.x / col_lanes, row_lanes = RED_T / col_lanes;
+    const int c = blockIdx.y * col_lanes + cl;
+    const long long r0 = blockIdx.x * rows_per_chunk;
+    const long long r1 = min(M, r0 + rows_per_chunk);
+    double acc[NV];
+#pragma unroll
+    for (int v = 0; v < NV; ++v) acc[v] = 0.0;
+    if (c < C) {
+        for (long long r = r0 + rl; r < r1; r += row_lanes) {
+            float vals[NV];
+            f(r, c, vals);
+#pragma unroll
+            for (int v = 0; v < NV; ++v) acc[v] += (double)vals[v];
+        }
+    }
+#pragma unroll
+    for (int v = 0; v < NV; ++v) sh[v][threadIdx.x] = acc[v];
+    __syncthreads();
+    if (rl == 0 && c < C) {
+#pragma unroll
+        for (int v = 0; v < NV; ++v) {
+            double s = 0.0;
+            for (int q = 0; q < row_lanes; ++q) s += sh[v][q * col_lanes + cl];
+            partial[((size_t)blockIdx.x * NV + v) * C + c] = s;
+        }
+    }
+}
+
+struct SumVal {        // plain column sums of a [M,C] matrix
+    const float* x; long long ld;
+    __device__ void operator()(long long r, int c, float (&o)[1]) const { o[0] = __ldg(x + r * ld + c); }
+};
+__global__ void sum1_finalize_kernel(const double* __restrict__ partial, int chunks, int C, float* __restrict__ s0) {
+    int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    double a = 0.0;
+    for (int q = 0; q < chunks; ++q) a += partial[(size_t)q * C + c];
+    s0[c] = (float)a;
+}
+
+// ---- BatchNorm statistics ------------------------------------------------------------------
+struct PlainVal {      // x and x^2 of a [M,C] matrix
+    const float* x; long long ld;
+    __device__ void operator()(long long r, int c, float (&o)[2]) const { float v = __ldg(x + r * ld + c); o[0] = v; o[1] = v * v; }
+};
+struct NormVal {       // |v| and |v|^2 of a [2M,C] vector field (nonlin.py:68)
+    const float* x; long long ld;
+    __device__ void operator()(long long r, int c, float (&o)[2]) const {
+        float a = __ldg(x + (2 * r) * ld + c), b = __ldg(x + (2 * r + 1) * ld + c);
+        float n2 = a * a + b * b;
+        o[0] = sqrtf(n2); o[1] = n2;
+    }
+};
+
+// mean / biased variance -> (mean, invstd); running stats updated like torch.nn.BatchNorm1d
+// (momentum, unbiased variance).  One thread per column, partials added in chunk order.
+__global__ void bn_finalize_kernel(const double* __restrict__ partial, int chunks, long long M, int C, float eps,
+                                   float momentum, float* __restrict__ mean, float* __restrict__ invstd,
+                                   float* __restrict__ running_mean, float* __restrict__ running_var) {
+    int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    double s = 0.0, s2 = 0.0;
+    for (int q = 0; q < chunks; ++q) { s += partial[((size_t)q * 2) * C + c]; s2 += partial[((size_t)q * 2 + 1) * C + c]; }
+    double mu = s / (double)M;
+    double var = s2 / (double)M - mu * mu;
+    if (var < 0.0) var = 0.0;
+    mean[c] = (float)mu;
+    invstd[c] = (float)(1.0 / sqrt(var + (double)eps));
+    if (running_mean) {
+        double unbiased = M > 1 ? var * (double)M / (double)(M - 1) : var;
+        running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * (float)mu;
+        running_var[c] = (1.f - momentum) * running_var[c] + momentum * (float)unbiased;
+    }
+}
+
+// ---- fused BN + LeakyReLU (+ residual addend), forward -------------------------------------
+// out = act(gamma * (y - mean) * invstd + beta) + addend        act(t) = t > 0 ? t : slope * t
+__global__ void bn_act_fwd_kernel(const float* __restrict__ y, long long ldy, long long M, int C,
+                                  const float* __restrict__ mean, const float* __restrict__ invstd,
+                                  const float* __restrict__ gamma, const float* __restrict__ beta, float slope,
+                                  const float* __restrict__ addend, long long ld_add, float* __restrict__ out, long long ldo) {
+    const long long total = M * (long long)C;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+        long long r = t / C; int c = (int)(t - r * C);
+        float g = gamma ? __ldg(gamma + c) : 1.f, b = beta ? __ldg(beta + c) : 0.f;
+        float z = g * ((__ldg(y + r * ldy + c) - __ldg(mean + c)) * __ldg(invstd + c)) + b;
+        z = z > 0.f ? z : slope * z;
+        if (addend) z += __ldg(addend + r * ld_add + c);
+        out[r * ldo + c] = z;
+    }
+}
+
+// backward, reduction part: dz = dOut * act'(bn); sums of dz and dz * xhat per column
+struct BnBwdVal {
+    const float* y; long long ldy; const float* dout; long long ldd;
+    const float* mean; const float* invstd; const float* gamma; const float* beta; float slope;
+    __device__ void operator()(long long r, int c, float (&o)[2]) const {
+        float xh = (__ldg(y + r * ldy + c) - __ldg(mean + c)) * __ldg(invstd + c);
+        float g = gamma ? __ldg(gamma + c) : 1.f, b = beta ? __ldg(beta + c) : 0.f;
+        float z = g * xh + b;
+        float dz = __ldg(dout + r * ldd + c) * (z > 0.f ? 1.f : slope);
+        o[0] = dz; o[1] = dz * xh;
+    }
+};
+
+__global__ void sum2_finalize_kernel(const double* __restrict__ partial, int chunks, int C, float* __restrict__ s0, float* __restrict__ s1) {
+    int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    double a = 0.0, b = 0.0;
+    for (int q = 0; q < chunks; ++q) { a += partial[((size_t)q * 2) * C + c]; b += partial[((size_t)q * 2 + 1) * C + c]; }
+    s0[c] = (float)a; s1[c] = (float)b;
+}
+
+// backward, elementwise part: dy = gamma * invstd * (dz - sum_dz/M - xhat * sum_dz_xhat/M)   (training)
+//                              dy = gamma * invstd * dz                                     (eval)
+__global__ void bn_act_bwd_kernel(const float* __restrict__ y, long long ldy, const float* __restrict__ dout, long long ldd,
+                                  long long M, int C, const float* __restrict__ mean, const float* __restrict__ invstd,
+                                  const float* __restrict__ gamma, const float* __restrict__ beta, float slope,
+                                  const float* __restrict__ sum_dz, const float* __restrict__ sum_dz_xh, int training,
+                                  float* __restrict__ dy, long long ld_dy) {
+    const long long total = M * (long long)C;
+    const float invM = 1.f / (float)M;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+        long long r = t / C; int c = (int)(t - r * C);
+        float is = __ldg(invstd + c);
+        float xh = (__ldg(y + r * ldy + c) - __ldg(mean + c)) * is;
+        float g = gamma ? __ldg(gamma + c) : 1.f, b = beta ? __ldg(beta + c) : 0.f;
+        float z = g * xh + b;
+        float dz = __ldg(dout + r * ldd + c) * (z > 0.f ? 1.f : slope);
+        float v = training ? dz - __ldg(sum_dz + c) * invM - xh * (__ldg(sum_dz_xh + c) * invM) : dz;
+        dy[r * ld_dy + c] = g * is * v;
+    }
+}
+
+// ---- VectorNonLin (nonlin.py:63-82) -----------------------------------------------------------
+// n = |v|;  s = relu(gamma (n - mean) invstd + beta)  [batchnorm]   or  relu(n + bias)  [no BN]
+// out = v * s / max(n, 1e-8)
+__device__ __forceinline__ float vnl_shift(float n, int c, const float* mean, const float* invstd, const float* gamma,
+                                           const float* beta, const float* bias) {
+    if (mean) {
+        float g = gamma ? __ldg(gamma + c) : 1.f, b = beta ? __ldg(beta + c) : 0.f;
+        return g * ((n - __ldg(mean + c)) * __ldg(invstd + c)) + b;
+    }
+    return n + __ldg(bias + c);
+}
+
+__global__ void vecnonlin_fwd_kernel(const float* __restrict__ v, long long ldv, long long M, int C,
+                                     const float* __restrict__ mean, const float* __restrict__ invstd,
+                                     const float* __restrict__ gamma, const float* __restrict__ beta,
+                                     const float* __restrict__ bias, float* __restrict__ out, long long ldo) {
+    const long long total = M * (long long)C;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+        long long r = t / C; int c = (int)(t - r * C);
+        float a = __ldg(v + (2 * r) * ldv + c), b = __ldg(v + (2 * r + 1) * ldv + c);
+        float n = sqrtf(a * a + b * b);
+        float s = fmaxf(vnl_shift(n, c, mean, invstd, gamma, beta, bias), 0.f) / fmaxf(n, 1e-8f);
+        out[(2 * r) * ldo + c] = a * s;
+        out[(2 * r + 1) * ldo + c] = b * s;
+    }
+}
+
+// Backward.  With q = relu(shift(n)), h = q / max(n, eps):  out = v h.
+//   d out / d v = h I + v (dh/dn) (v^T / n),  dh/dn = q'/max(n,eps) - q [n > eps] / n^2
+// dq (the gradient reaching the BN output through q) = (dout . v) / max(n, eps); its BN backward
+// needs the column sums of dq*relu' and dq*relu'*xhat over all points (training mode).
+struct VnlBwdVal {
+    const float* v; long long ldv; const float* dout; long long ldd;
+    const float* mean; const float* invstd; const float* gamma; const float* beta;
+    __device__ void operator()(long long r, int c, float (&o)[2]) const {
+        float a = __ldg(v + (2 * r) * ldv + c), b = __ldg(v + (2 * r + 1) * ldv + c);
+        float n = sqrtf(a * a + b * b);
+        float xh = (n - __ldg(mean + c)) * __ldg(invstd + c);
+        float g = gamma ? __ldg(gamma + c) : 1.f, be = beta ? __ldg(beta + c) : 0.f;
+        float z = g * xh + be;
+        float dq = (__ldg(dout + (2 * r) * ldd + c) * a + __ldg(dout + (2 * r + 1) * ldd + c) * b) / fmaxf(n, 1e-8f);
+        float dz = z > 0.f ? dq : 0.f;
+        o[0] = dz; o[1] = dz * xh;
+    }
+};
+
+__global__ void vecnonlin_bwd_kernel(const float* __restrict__ v, long long ldv, const float* __restrict__ dout, long long ldd,
+                                     long long M, int C, const float* __restrict__ mean, const float* __restrict__ invstd,
+                                     const float* __restrict__ gamma, const float* __restrict__ beta, const float* __restrict__ bias,
+                                     const float* __restrict__ sum_dz, const float* __restrict__ sum_dz_xh, int training,
+                                     float* __restrict__ dv, long long ld_dv, float* __restrict__ dbias_rows) {
+    const long long total = M * (long long)C;
+    const float invM = 1.f / (float)M;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+        long long r = t / C; int c = (int)(t - r * C);
+        float a = __ldg(v + (2 * r) * ldv + c), b = __ldg(v + (2 * r + 1) * ldv + c);
+        float da = __ldg(dout + (2 * r) * ldd + c), db = __ldg(dout + (2 * r + 1) * ldd + c);
+        float n = sqrtf(a * a + b * b), nc = fmaxf(n, 1e-8f);
+        float z, dn_from_q;        // dn_from_q: gradient w.r.t. n through q = relu(shift(n))
+        float dq = (da * a + db * b) / nc;
+        if (mean) {
+            float is = __ldg(invstd + c);
+            float xh = (n - __ldg(mean + c)) * is;
+            float g = gamma ? __ldg(gamma + c) : 1.f, be = beta ? __ldg(beta + c) : 0.f;
+            z = g * xh + be;
+            float dz = z > 0.f ? dq : 0.f;
+            float core = training ? dz - __ldg(sum_dz + c) * invM - xh * (__ldg(sum_dz_xh + c) * invM) : dz;
+            dn_from_q = g * is * core;
+        } else {
+            z = n + __ldg(bias + c);
+            dn_from_q = z > 0.f ? dq : 0.f;
+            if (dbias_rows) dbias_rows[r * C + c] = dn_from_q;
+        }
+        float q = fmaxf(z, 0.f);
+        float h = q / nc;
+        // through the 1/max(n,eps) factor: -q/n^2 * (dout . v) when n > eps
+        float dn_from_h = n > 1e-8f ? -(da * a + db * b) * q / (nc * nc) : 0.f;
+        float dn = dn_from_q + dn_from_h;
+        float inv_n = n > 0.f ? 1.f / n : 0.f;     // d n / d v = v / n   (0 at the origin)
+        dv[(2 * r) * ld_dv + c] = da * h + dn * a * inv_n;
+        dv[(2 * r + 1) * ld_dv + c] = db * h + dn * b * inv_n;
+    }
+}
+
+// ---- kNN max aggregation (deltaconv.py:54) ----------------------------------------------------
+// out[i,c] = max_e y[idx[i,e], c]; arg[i,c] = lowest slot attaining it (parity rule)
+__global__ void gathermax_fwd_kernel(const int* __restrict__ idx, int N, int k, int C, const float* __restrict__ y, long long ldy,
+                                     float* __restrict__ out, long long ldo, unsigned char* __restrict__ arg) {
+    // one warp per point, lanes over channels (coalesced row gathers)
+    const long long warp = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (warp >= N) return;
+    const int i = (int)warp;
+    for (int c0 = 0; c0 < C; c0 += 32 * 4) {
+        float best[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+        int slot[4] = {0, 0, 0, 0};
+        for (int e = 0; e < k; ++e) {
+            int j = __ldg(idx + (size_t)i * k + e);
+            if ((unsigned)j >= (unsigned)N) continue;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                int c = c0 + u * 32 + lane;
+                if (c < C) {
+                    float val = __ldg(y + (size_t)j * ldy + c);
+                    if (val > best[u]) { best[u] = val; slot[u] = e; }
+                }
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            int c = c0 + u * 32 + lane;
+            if (c < C) {
+                out[(size_t)i * ldo + c] = best[u] == -INFINITY ? 0.f : best[u];    // empty group -> 0 (torch_scatter)
+                arg[(size_t)i * C + c] = (unsigned char)slot[u];
+            }
+        }
+    }
+}
+
+// dY[j,c] = sum over incoming edges (i,e) with arg[i,c] == e of dOut[i,c]
+__global__ void gathermax_bwd_kernel(const int* __restrict__ in_ptr, const int* __restrict__ in_edge, int N, int k, int C,
+                                     const unsigned char* __restrict__ arg, const float* __restrict__ dout, long long ldd,
+                                     float* __restrict__ dy, long long ld_dy) {
+    const long long warp = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (warp >= N) return;
+    const int j = (int)warp;
+    const int b = __ldg(in_ptr + j), e_ = __ldg(in_ptr + j + 1);
+    for (int c0 = 0; c0 < C; c0 += 32 * 4) {
+        float acc[4] = {0.f, 0.f, 0.f, 0.f};
+        for (int t = b; t < e_; ++t) {
+            int edge = __ldg(in_edge + t);
+            int i = edge / k, e = edge - i * k;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                int c = c0 + u * 32 + lane;
+                if (c < C && arg[(size_t)i * C + c] == (unsigned char)e) acc[u] += __ldg(dout + (size_t)i * ldd + c);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            int c = c0 + u * 32 + lane;
+            if (c < C) dy[(size_t)j * ld_dy + c] = acc[u];
+        }
+    }
+}
+
+// ---- centralized first layer helpers (deltaconv.py:50-52) -----------------------------------
+// edge features x_j - x_i for every slot: [N*k, C]
+__global__ void edge_diff_kernel(const int* __restrict__ idx, int N, int k, int C, const float* __restrict__ x, long long ldx,
+                                 float* __restrict__ out) {
+    const long long total = (long long)N * k * C;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+        long long edge = t / C; int c = (int)(t - edge * C);
+        int i = (int)(edge / k);
+        int j = __ldg(idx + edge);
+        if ((unsigned)j >= (unsigned)N) j = i;
+        out[t] = __ldg(x + (size_t)j * ldx + c) - __ldg(x + (size_t)i * ldx + c);
+    }
+}
+
+// transpose of the above: dX[p] = sum_{in-edges (i,e)->p} dE[i,e] - sum_e dE[p,e]
+__global__ void edge_diff_bwd_kernel(const int* __restrict__ in_ptr, const int* __restrict__ in_edge, int N, int k, int C,
+                                     const float* __restrict__ dE, float* __restrict__ dx, long long ld_dx) {
+    const long long total = (long long)N * C;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+        int p = (int)(t / C), c = (int)(t - (long long)p * C);
+        float acc = 0.f;
+        for (int q = __ldg(in_ptr + p); q < __ldg(in_ptr + p + 1); ++q) acc += __ldg(dE + (size_t)__ldg(in_edge + q) * C + c);
+        for (int e = 0; e < k; ++e) acc -= __ldg(dE + ((size_t)p * k + e) * C + c);
+        dx[(size_t)p * ld_dx + c] = acc;
+    }
+}
+
+// max over the k consecutive rows of each point: in [N*k, C] -> out [N, C], arg slot
+__global__ void segmax_fwd_kernel(const float* __restrict__ in, int N, int k, int C, const int* __restrict__ idx,
+                                  float* __restrict__ out, long long ldo, unsigned char* __restrict__ arg) {
+    const long long total = (long long)N * C;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+        int i = (int)(t / C), c = (int)(t - (long long)i * C);
+        float best = -INFINITY; int slot = 0;
+        for (int e = 0; e < k; ++e) {
+            if (idx && (unsigned)__ldg(idx + (size_t)i * k + e) >= (unsigned)N) continue;
+            float v = __ldg(in + ((size_t)i * k + e) * C + c);
+            if (v > best) { best = v; slot = e; }
+        }
+        out[(size_t)i * ldo + c] = best == -INFINITY ? 0.f : best;
+        arg[t] = (unsigned char)slot;
+    }
+}
+
+__global__ void segmax_bwd_kernel(const float* __restrict__ dout, long long ldd, int N, int k, int C,
+                                  const unsigned char* __restrict__ arg, float* __restrict__ din) {
+    const long long total = (long long)N * k * C;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+        long long edge = t / C; int c = (int)(t - edge * C);
+        int i = (int)(edge / k), e = (int)(edge - (long long)i * k);
+        din[t] = arg[(size_t)i * C + c] == (unsigned char)e ? __ldg(dout + (size_t)i * ldd + c) : 0.f;
+    }
+}
+
+// ---- global pools (one CTA per (cloud, 32-channel block); rows of a cloud are contiguous) ------
+// out_max[b,c] = max_i x[i,c] (arg kept), out_mean[b,c] = mean_i x[i,c]
+__global__ void __launch_bounds__(256) pool_fwd_kernel(const float* __restrict__ x, long long ldx, const int* __restrict__ cloud_ptr,
+                                                       int C, float* __restrict__ out_max, long long ld_max,
+                                                       float* __restrict__ out_mean, long long ld_mean, int* __restrict__ arg) {
+    __shared__ float smax[8][32];
+    __shared__ int sarg[8][32];
+    __shared__ float ssum[8][32];
+    const int b = blockIdx.x, lane = threadIdx.x & 31, rl = threadIdx.x >> 5;
+    const int c = blockIdx.y * 32 + lane;
+    const int s = __ldg(cloud_ptr + b), e = __ldg(cloud_ptr + b + 1);
+    float best = -INFINITY, sum = 0.f; int bi = s;
+    if (c < C) {
+        for (int i = s + rl; i < e; i += 8) {
+            float v = __ldg(x + (size_t)i * ldx + c);
+            sum += v;
+            if (v > best) { best = v; bi = i; }
+        }
+    }
+    smax[rl][lane] = best; sarg[rl][lane] = bi; ssum[rl][lane] = sum;
+    __syncthreads();
+    if (rl == 0 && c < C) {
+        for (int q = 1; q < 8; ++q) {
+            float v = smax[q][lane]; int a = sarg[q][lane];
+            if (v > best || (v == best && a < bi)) { best = v; bi = a; }
+            sum += ssum[q][lane];
+        }
+        int cnt = e - s;
+        if (out_max) { out_max[(size_t)b * ld_max + c] = cnt > 0 ? best : 0.f; arg[(size_t)b * C + c] = bi; }
+        if (out_mean) out_mean[(size_t)b * ld_mean + c] = sum / (float)(cnt > 0 ? cnt : 1);
+    }
+}
+
+__global__ void pool_bwd_kernel(const int* __restrict__ cloud_ptr, int B, int N, int C, const int* __restrict__ arg,
+                                const float* __restrict__ d_max, long long ld_dmax, const float* __restrict__ d_mean, long long ld_dmean,
+                                float* __restrict__ dx, long long ld_dx) {
+    const long long total = (long long)N * C;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+        int i = (int)(t / C), c = (int)(t - (long long)i * C);
+        int b = cloud_of(cloud_ptr, B, i);
+        float g = 0.f;
+        if (d_max && __ldg(arg + (size_t)b * C + c) == i) g += __ldg(d_max + (size_t)b * ld_dmax + c);
+        if (d_mean) g += __ldg(d_mean + (size_t)b * ld_dmean + c) / (float)(__ldg(cloud_ptr + b + 1) - __ldg(cloud_ptr + b));
+        dx[(size_t)i * ld_dx + c] = g;
+    }
+}
+
+// out[i, :] = src[cloud(i), :]  (x_max[batch], deltanet_segmentation.py:61,64) and its transpose
+__global__ void bcast_rows_kernel(const float* __restrict__ src, long long lds, const int* __restrict__ cloud_ptr, int B, int N, int C,
+                                  float* __restrict__ out, long long ldo) {
+    const long long total = (long long)N * C;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+        int i = (int)(t / C), c = (int)(t - (long long)i * C);
+        out[(size_t)i * ldo + c] = __ldg(src + (size_t)cloud_of(cloud_ptr, B, i) * lds + c);
+    }
+}
+
+int elementwise_grid(long long total) {
+    long long g = (total + 255) / 256;
+    long long cap = (long long)dc_sm_count() * 16;
+    return (int)(g < cap ? (g < 1 ? 1 : g) : cap);
+}
+
+}  // namespace
+
+// ================================ C ABI ===========================================================
+
+extern "C" size_t dc_colreduce_ws_bytes(int C) { return (size_t)RED_MAX_CHUNKS * 2 * (size_t)C * sizeof(double); }
+
+// mode 0: statistics of x [M,C]; mode 1: statistics of the norms of a vector field x [2M,C]
+extern "C" int dc_bn_stats(const float* x, int64_t ldx, int64_t M, int C, int mode, float eps, float momentum,
+                           float* mean, float* invstd, float* running_mean_or_null, float* running_var_or_null,
+                           void* ws, size_t ws_bytes, void* stream) {
+    DC_REQUIRE(M >= 1 && C >= 1, "dc_bn_stats: empty input");
+    DC_REQUIRE(ws_bytes >= dc_colreduce_ws_bytes(C), "dc_bn_stats: workspace too small");
+    cudaStream_t st = (cudaStream_t)stream;
+    ColLayout L = col_layout(M, C);
+    dim3 grid(L.chunks, L.col_blocks);
+    double* partial = (double*)ws;
+    if (mode == 0) { PlainVal f = {x, ldx}; col_reduce_kernel<2><<<grid, RED_T, 0, st>>>(f, M, C, L.col_lanes, L.rows_per_chunk, partial); }
+    else { NormVal f = {x, ldx}; col_reduce_kernel<2><<<grid, RED_T, 0, st>>>(f, M, C, L.col_lanes, L.rows_per_chunk, partial); }
+    bn_finalize_kernel<<<dc_ceil_div(C, 128), 128, 0, st>>>(partial, L.chunks, M, C, eps, momentum, mean, invstd,
+                                                            running_mean_or_null, running_var_or_null);
+    return dc_check_launch("dc_bn_stats");
+}
+
+// out[c] = sum_r x[r,c]  (bias gradients)
+extern "C" int dc_col_sum(const float* x, int64_t ldx, int64_t M, int C, float* out, void* ws, size_t ws_bytes, void* stream) {
+    DC_REQUIRE(M >= 1 && C >= 1, "dc_col_sum: empty input");
+    DC_REQUIRE(ws_bytes >= dc_colreduce_ws_bytes(C), "dc_col_sum: workspace too small");
+    cudaStream_t st = (cudaStream_t)stream;
+    ColLayout L = col_layout(M, C);
+    dim3 grid(L.chunks, L.col_blocks);
+    SumVal f = {x, ldx};
+    col_reduce_kernel<1><<<grid, RED_T, 0, st>>>(f, M, C, L.col_lanes, L.rows_per_chunk, (double*)ws);
+    sum1_finalize_kernel<<<dc_ceil_div(C, 128), 128, 0, st>>>((double*)ws, L.chunks, C, out);
+    return dc_check_launch("dc_col_sum");
+}
+
+extern "C" int dc_bn_act_fwd(const float* y, int64_t ldy, int64_t M, int C, const float* mean, const float* invstd,
+                             const float* gamma_or_null, const float* beta_or_null, float slope,
+                             const float* addend_or_null, int64_t ld_add, float* out, int64_t ldo, void* stream) {
+    if (M <= 0 || C <= 0) return DC_OK;
+    bn_act_fwd_kernel<<<elementwise_grid(M * C), 256, 0, (cudaStream_t)stream>>>(y, ldy, M, C, mean, invstd, gamma_or_null,
+                                                                                 beta_or_null, slope, addend_or_null, ld_add, out, ldo);
+    return dc_check_launch("dc_bn_act_fwd");
+}
+
+// d_gamma = sum dz*xhat, d_beta = sum dz (written to the two [C] outputs), dy as documented above
+extern "C" int dc_bn_act_bwd(const float* y, int64_t ldy, const float* dout, int64_t ldd, int64_t M, int C,
+                             const float* mean, const float* invstd, const float* gamma_or_null, const float* beta_or_null,
+                             float slope, int training, float* d_gamma, float* d_beta, float* dy, int64_t ld_dy,
+                             void* ws, size_t ws_bytes, void* stream) {
+    DC_REQUIRE(M >= 1 && C >= 1, "dc_bn_act_bwd: empty input");
+    DC_REQUIRE(ws_bytes >= dc_colreduce_ws_bytes(C), "dc_bn_act_bwd: workspace too small");
+    cudaStream_t st = (cudaStream_t)stream;
+    ColLayout L = col_layout(M, C);
+    dim3 grid(L.chunks, L.col_blocks);
+    double* partial = (double*)ws;
+    BnBwdVal f = {y, ldy, dout, ldd, mean, invstd, gamma_or_null, beta_or_null, slope};
+    col_reduce_kernel<2><<<grid, RED_T, 0, st>>>(f, M, C, L.col_lanes, L.rows_per_chunk, partial);
+    sum2_finalize_kernel<<<dc_ceil_div(C, 128), 128, 0, st>>>(partial, L.chunks, C, d_beta, d_gamma);
+    bn_act_bwd_kernel<<<elementwise_grid(M * C), 256, 0, st>>>(y, ldy, dout, ldd, M, C, mean, invstd, gamma_or_null, beta_or_null,
+                                                               slope, d_beta, d_gamma, training, dy, ld_dy);
+    return dc_check_launch("dc_bn_act_bwd");
+}
+
+extern "C" int dc_vecnonlin_fwd(const float* v, int64_t ldv, int64_t M, int C, const float* mean_or_null,
+                                const float* invstd_or_null, const float* gamma_or_null, const float* beta_or_null,
+                                const float* bias_or_null, float* out, int64_t ldo, void* stream) {
+    DC_REQUIRE(mean_or_null != nullptr || bias_or_null != nullptr, "dc_vecnonlin_fwd: need BN statistics or a bias");
+    if (M <= 0 || C <= 0) return DC_OK;
+    vecnonlin_fwd_kernel<<<elementwise_grid(M * C), 256, 0, (cudaStream_t)stream>>>(v, ldv, M, C, mean_or_null, invstd_or_null,
+                                                                                    gamma_or_null, beta_or_null, bias_or_null, out, ldo);
+    return dc_check_launch("dc_vecnonlin_fwd");
+}
+
+// With BN: d_gamma/d_beta [C] are produced. Without BN: dbias_rows [M,C] receives the per-row bias
+// gradient (the caller sums it over rows), d_gamma/d_beta are ignored.
+extern "C" int dc_vecnonlin_bwd(const float* v, int64_t ldv, const float* dout, int64_t ldd, int64_t M, int C,
+                                const float* mean_or_null, const float* invstd_or_null, const float* gamma_or_null,
+                                const float* beta_or_null, const float* bias_or_null, int training,
+                                float* d_gamma, float* d_beta, float* dbias_rows_or_null, float* dv, int64_t ld_dv,
+                                void* ws, size_t ws_bytes, void* stream) {
+    DC_REQUIRE(M >= 1 && C >= 1, "dc_vecnonlin_bwd: empty input");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (mean_or_null) {
+        DC_REQUIRE(ws_bytes >= dc_colreduce_ws_bytes(C), "dc_vecnonlin_bwd: workspace too small");
+        ColLayout L = col_layout(M, C);
+        dim3 grid(L.chunks, L.col_blocks);
+        double* partial = (double*)ws;
+        VnlBwdVal f = {v, ldv, dout, ldd, mean_or_null, invstd_or_null, gamma_or_null, beta_or_null};
+        col_reduce_kernel<2><<<grid, RED_T, 0, st>>>(f, M, C, L.col_lanes, L.rows_per_chunk, partial);
+        sum2_finalize_kernel<<<dc_ceil_div(C, 128), 128, 0, st>>>(partial, L.chunks, C, d_beta, d_gamma);
+    }
+    vecnonlin_bwd_kernel<<<elementwise_grid(M * C), 256, 0, st>>>(v, ldv, dout, ldd, M, C, mean_or_null, invstd_or_null, gamma_or_null,
+                                                                  beta_or_null, bias_or_null, d_beta, d_gamma, training, dv, ld_dv,
+                                                                  dbias_rows_or_null);
+    return dc_check_launch("dc_vecnonlin_bwd");
+}
+
+extern "C" int dc_gathermax_fwd(const int32_t* idx, int N, int k, int C, const float* y, int64_t ldy, float* out, int64_t ldo,
+                                uint8_t* arg, void* stream) {
+    DC_REQUIRE(k <= 255, "dc_gathermax_fwd: k must be <= 255 (arg slots are stored as u8)");
+    if (N <= 0 || C <= 0) return DC_OK;
+    gathermax_fwd_kernel<<<dc_ceil_div((long long)N * 32, 256), 256, 0, (cudaStream_t)stream>>>(idx, N, k, C, y, ldy, out, ldo, arg);
+    return dc_check_launch("dc_gathermax_fwd");
+}
+
+extern "C" int dc_gathermax_bwd(const int32_t* in_ptr, const int32_t* in_edge, int N, int k, int C, const uint8_t* arg,
+                                const float* dout, int64_t ldd, float* dy, int64_t ld_dy, void* stream) {
+    if (N <= 0 || C <= 0) return DC_OK;
+    gathermax_bwd_kernel<<<dc_ceil_div((long long)N * 32, 256), 256, 0, (cudaStream_t)stream>>>(in_ptr, in_edge, N, k, C, arg, dout, ldd, dy, ld_dy);
+    return dc_check_launch("dc_gathermax_bwd");
+}
+
+extern "C" int dc_edge_diff_fwd(const int32_t* idx, int N, int k, int C, const float* x, int64_t ldx, float* out, void* stream) {
+    if (N <= 0 || C <= 0) return DC_OK;
+    edge_diff_kernel<<<elementwise_grid((long long)N * k * C), 256, 0, (cudaStream_t)stream>>>(idx, N, k, C, x, ldx, out);
+    return dc_check_launch("dc_edge_diff_fwd");
+}
+
+extern "C" int dc_edge_diff_bwd(const int32_t* in_ptr, const int32_t* in_edge, int N, int k, int C, const float* d_edge,
+                                float* dx, int64_t ld_dx, void* stream) {
+    if (N <= 0 || C <= 0) return DC_OK;
+    edge_diff_bwd_kernel<<<elementwise_grid((long long)N * C), 256, 0, (cudaStream_t)stream>>>(in_ptr, in_edge, N, k, C, d_edge, dx, ld_dx);
+    return dc_check_launch("dc_edge_diff_bwd");
+}
+
+extern "C" int dc_segmax_fwd(const float* in, int N, int k, int C, const int32_t* idx_or_null, float* out, int64_t ldo,
+                             uint8_t* arg, void* stream) {
+    DC_REQUIRE(k <= 255, "dc_segmax_fwd: k must be <= 255");
+    if (N <= 0 || C <= 0) return DC_OK;
+    segmax_fwd_kernel<<<elementwise_grid((long long)N * C), 256, 0, (cudaStream_t)stream>>>(in, N, k, C, idx_or_null, out, ldo, arg);
+    return dc_check_launch("dc_segmax_fwd");
+}
+
+extern "C" int dc_segmax_bwd(const float* dout, int64_t ldd, int N, int k, int C, const uint8_t* arg, float* din, void* stream) {
+    if (N <= 0 || C <= 0) return DC_OK;
+    segmax_bwd_kernel<<<elementwise_grid((long long)N * k * C), 256, 0, (cudaStream_t)stream>>>(dout, ldd, N, k, C, arg, din);
+    return dc_check_launch("dc_segmax_bwd");
+}
+
+extern "C" int dc_pool_fwd(const float* x, int64_t ldx, const int32_t* cloud_ptr, int B, int C, float* out_max_or_null,
+                           int64_t ld_max, float* out_mean_or_null, int64_t ld_mean, int32_t* arg, void* stream) {
+    if (B <= 0 || C <= 0) return DC_OK;
+    dim3 grid(B, dc_ceil_div(C, 32));
+    pool_fwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, ldx, cloud_ptr, C, out_max_or_null, ld_max, out_mean_or_null, ld_mean, arg);
+    return dc_check_launch("dc_pool_fwd");
+}
+
+extern "C" int dc_pool_bwd(const int32_t* cloud_ptr, int B, int N, int C, const int32_t* arg, const float* d_max_or_null,
+                           int64_t ld_dmax, const float* d_mean_or_null, int64_t ld_dmean, float* dx, int64_t ld_dx, void* stream) {
+    if (N <= 0 || C <= 0) return DC_OK;
+    pool_bwd_kernel<<<elementwise_grid((long long)N * C), 256, 0, (cudaStream_t)stream>>>(cloud_ptr, B, N, C, arg, d_max_or_null, ld_dmax,
+                                                                                           d_mean_or_null, ld_dmean, dx, ld_dx);
+    return dc_check_launch("dc_pool_bwd");
+}
+
+extern "C" int dc_bcast_rows(const float* src, int64_t lds, const int32_t* cloud_ptr, int B, int N, int C, float* out, int64_t ldo,
+                             void* stream) {
+    if (N <= 0 || C <= 0) return DC_OK;
+    bcast_rows_kernel<<<elementwise_grid((long long)N * C), 256, 0, (cudaStream_t)stream>>>(src, lds, cloud_ptr, B, N, C, out, ldo);
+    return dc_check_launch("dc_bcast_rows");
+}

@@ -1,0 +1,61 @@
+"""Operator construction entry points with the reference's signatures
+(deltaconv/geometry/grad_div_mls.py), backed by the CUDA library.
+
+`estimate_basis`, `build_tangent_basis` and `build_grad_div` are the public entry points the
+models use.  The reference's intermediate helpers (`coords_projected`, `gaussian_weights`,
+`fit_vector_mapping`) are exposed from the same fused kernel through its debug outputs.
+"""
+import torch
+
+from .. import ops
+
+__all__ = ['estimate_basis', 'build_tangent_basis', 'build_grad_div', 'operator_parts']
+
+
+def estimate_basis(pos, edge_index, k=None, orientation=None):
+    """(normal, x_basis, y_basis) from the local 3 x k neighbourhood (grad_div_mls.py:10-47).
+    `k` is accepted for signature parity; the graph itself carries it."""
+    graph = ops.graph_of(edge_index, pos.size(0))
+    if k is not None and int(k) != graph.k:
+        raise ValueError(f"k={int(k)} does not match the graph's k={graph.k}")
+    return ops.estimate_frames(pos, graph, orientation)
+
+
+def build_tangent_basis(normal):
+    """(x_basis, y_basis) orthonormal to `normal` (grad_div_mls.py:50-69)."""
+    return ops.tangent_basis(normal)
+
+
+def _prepare(pos, edge_index, batch):
+    graph = ops.graph_of(edge_index, pos.size(0))
+    if batch is None:
+        cp, B = ops.cloud_ptr_of(None, pos.size(0), pos.device)
+    elif graph.cloud_ptr is not None and getattr(batch, '_dc_cloud', None) is not None and batch._dc_cloud[0] is graph.cloud_ptr:
+        cp, B = graph.cloud_ptr, graph.B
+    else:
+        cp, B = ops.cloud_ptr_of(batch, pos.size(0), pos.device)
+    return graph, cp, B
+
+
+def build_grad_div(pos, normal, x_basis, y_basis, edge_index, batch=None, kernel_width=1, regularizer=0.001,
+                   normalized=True, shape_regularizer=None):
+    """(grad, div): the 2N x N gradient and N x 2N divergence of the weighted-least-squares fit
+    (grad_div_mls.py:197-277) as `EllOperator`s sharing one fixed-k ELL storage."""
+    graph, cp, B = _prepare(pos, edge_index, batch)
+    with torch.no_grad():
+        G, D = ops.build_operators(pos, normal, x_basis, y_basis, graph, cp, B, kernel_width, regularizer,
+                                   normalized, shape_regularizer)
+    return ops.EllOperator('grad', graph, G, D), ops.EllOperator('div', graph, G, D)
+
+
+def operator_parts(pos, normal, x_basis, y_basis, edge_index, batch=None, kernel_width=1, regularizer=0.001,
+                   normalized=True, shape_regularizer=None):
+    """dict(coords [E,2], weights [E], mapping [E,2,2]): what the reference's `coords_projected`
+    (:72-97), `gaussian_weights` (:100-116) and `fit_vector_mapping` (:155-194) return for the same
+    inputs, read out of the fused build kernel."""
+    graph, cp, B = _prepare(pos, edge_index, batch)
+    with torch.no_grad():
+        _, _, (coords, weights, mapping) = ops.build_operators(pos, normal, x_basis, y_basis, graph, cp, B, kernel_width,
+                                                               regularizer, normalized, shape_regularizer, debug=True)
+    E = graph.N * graph.k
+    return dict(coords=coords.view(E, 2), weights=weights.view(E), mapping=mapping.view(E, 2, 2))

@@ -1,0 +1,45 @@
+"""DeltaNet backbone (reference: deltaconv/models/deltanet_base.py:8-87)."""
+import torch
+
+from ..geometry.graph import knn_graph
+from ..geometry.grad_div_mls import build_grad_div, build_tangent_basis, estimate_basis
+from ..nn import DeltaConv
+
+
+class DeltaNetBase(torch.nn.Module):
+    def __init__(self, in_channels, conv_channels, mlp_depth, num_neighbors, grad_regularizer, grad_kernel_width,
+                 centralize_first=True):
+        super().__init__()
+        self.k = num_neighbors
+        self.grad_regularizer = grad_regularizer
+        self.grad_kernel_width = grad_kernel_width
+        conv_channels = [in_channels] + list(conv_channels)
+        self.convs = torch.nn.ModuleList()
+        for i in range(len(conv_channels) - 1):
+            last_layer = i == (len(conv_channels) - 2)
+            self.convs.append(DeltaConv(conv_channels[i], conv_channels[i + 1], depth=mlp_depth,
+                                        centralized=(centralize_first and i == 0), vector=not last_layer))
+
+    def forward(self, data):
+        pos, batch = data.pos, data.batch
+        clouds = getattr(data, '_num_clouds', None)      # optional hint that avoids one device sync
+
+        # operator construction (deltanet_base.py:52-69): kNN graph -> frames -> grad/div
+        edge_index = knn_graph(pos, self.k, batch, loop=True, flow='target_to_source', num_clouds=clouds)
+        if hasattr(data, 'norm') and data.norm is not None:
+            normal = data.norm
+            x_basis, y_basis = build_tangent_basis(normal)
+        else:
+            edge_index_normal = knn_graph(pos, 10, batch, loop=True, flow='target_to_source', num_clouds=clouds)
+            normal, x_basis, y_basis = estimate_basis(pos, edge_index_normal, orientation=pos)
+        grad, div = build_grad_div(pos, normal, x_basis, y_basis, edge_index, batch,
+                                   kernel_width=self.grad_kernel_width, regularizer=self.grad_regularizer)
+
+        # convolutions (deltanet_base.py:76-87)
+        x = data.x if hasattr(data, 'x') and data.x is not None else pos
+        v = grad @ x
+        out = []
+        for conv in self.convs:
+            x, v = conv(x, v, grad, div, edge_index)
+            out.append(x)
+        return out

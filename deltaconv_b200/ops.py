@@ -1,0 +1,741 @@
+"""Host side of the CUDA operators: graph/operator containers and `torch.autograd.Function`
+wrappers around the C ABI (include/deltaconv_b200.h).  PyTorch supplies device memory, the
+current stream and the autograd tape; all arithmetic happens in the library.
+
+Every function here requires contiguous fp32 CUDA tensors and raises otherwise — there is no
+CPU or eager-PyTorch fallback.
+"""
+import torch
+
+from . import _lib
+from ._lib import call, ptr, query, rows_ld
+
+_F32, _I32, _I64 = torch.float32, torch.int32, torch.int64
+
+_workspaces = {}
+
+
+def workspace(nbytes, device):
+    """Cached scratch buffer (one per device, grows on demand).  All kernels that use it are
+    enqueued on the current stream, so successive users are ordered."""
+    key = (device.type, device.index)
+    buf = _workspaces.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(max(int(nbytes), 1 << 20), dtype=torch.uint8, device=device)
+        _workspaces[key] = buf
+    return buf
+
+
+def _f32(t, name='tensor'):
+    if not (torch.is_tensor(t) and t.is_cuda and t.dtype == _F32):
+        raise _lib.DeltaConvLibraryError(
+            f"{name}: expected an fp32 CUDA tensor, got {getattr(t, 'dtype', type(t))} on "
+            f"{getattr(t, 'device', '?')} (deltaconv_b200 has no CPU path)")
+    return t
+
+
+def _mat(t, name='tensor'):
+    """2-D fp32 CUDA tensor with unit column stride -> (tensor, ld)."""
+    _f32(t, name)
+    if t.dim() != 2:
+        raise _lib.DeltaConvLibraryError(f"{name}: expected a 2-D tensor, got shape {tuple(t.shape)}")
+    return rows_ld(t)
+
+
+# ------------------------------------------------------------------------------------------------
+# clouds and graphs
+# ------------------------------------------------------------------------------------------------
+
+def cloud_ptr_of(batch, num_points, device, num_clouds=None):
+    """(cloud_ptr int32 [B+1], B) for a sorted PyG batch vector; cached on the tensor object.
+    `batch=None` means one cloud.  Without `num_clouds` the count is read back from the device
+    (one sync, as the reference's scatter calls do)."""
+    if batch is None:
+        return torch.tensor([0, num_points], dtype=_I32, device=device), 1
+    cached = getattr(batch, '_dc_cloud', None)
+    if cached is not None and cached[2] == num_points:
+        return cached[0], cached[1]
+    if not batch.is_cuda or batch.dtype != _I64:
+        raise _lib.DeltaConvLibraryError("batch must be an int64 CUDA tensor")
+    batch = batch.contiguous()
+    B = int(num_clouds) if num_clouds is not None else (int(batch[-1].item()) + 1 if num_points else 1)
+    cp = torch.empty(B + 1, dtype=_I32, device=device)
+    call('dc_cloud_ptr', ptr(batch), num_points, B, ptr(cp))
+    try:
+        batch._dc_cloud = (cp, B, num_points)
+    except Exception:
+        pass
+    return cp, B
+
+
+class EllGraph:
+    """Fixed-k neighbourhood graph in ELL form plus, lazily, its incoming-edge CSR."""
+
+    def __init__(self, idx, cloud_ptr=None, num_clouds=None):
+        self.idx = idx
+        self.N, self.k = idx.shape
+        self.cloud_ptr, self.B = cloud_ptr, num_clouds
+        self._transpose = None
+        self._edge_index = None
+
+    def transpose(self):
+        if self._transpose is None:
+            dev = self.idx.device
+            in_ptr = torch.empty(self.N + 1, dtype=_I32, device=dev)
+            in_edge = torch.empty(max(self.N * self.k, 1), dtype=_I32, device=dev)
+            nbytes = query('dc_ell_transpose_ws_bytes', self.N)
+            ws = workspace(nbytes, dev)
+            call('dc_ell_transpose', ptr(self.idx), self.N, self.k, ptr(in_ptr), ptr(in_edge), ptr(ws), nbytes)
+            self._transpose = (in_ptr, in_edge)
+        return self._transpose
+
+    def edge_index(self):
+        if self._edge_index is None:
+            ei = torch.empty(2, self.N * self.k, dtype=_I64, device=self.idx.device)
+            call('dc_edge_index_from_ell', ptr(self.idx), self.N, self.k, ptr(ei))
+            ei._dc_graph = self
+            self._edge_index = ei
+        return self._edge_index
+
+
+def knn(pos, k, batch=None, num_clouds=None, want_edge_index=True):
+    """ELL kNN graph of `pos` [N,3] per cloud (self included, ascending (d2, index))."""
+    pos = _f32(pos, 'pos').contiguous()
+    if pos.dim() != 2 or pos.size(1) != 3:
+        raise _lib.DeltaConvLibraryError(f"knn: expected pos of shape [N,3], got {tuple(pos.shape)}")
+    N = pos.size(0)
+    cp, B = cloud_ptr_of(batch, N, pos.device, num_clouds)
+    idx = torch.empty(N, k, dtype=_I32, device=pos.device)
+    ei = torch.empty(2, N * k, dtype=_I64, device=pos.device) if want_edge_index else None
+    call('dc_knn', ptr(pos), ptr(cp), B, N, k, ptr(idx), ptr(ei), None)
+    graph = EllGraph(idx, cp, B)
+    if ei is not None:
+        ei._dc_graph = graph
+        graph._edge_index = ei
+    return graph
+
+
+def graph_of(edge_index, num_points):
+    """EllGraph behind a [2,E] int64 edge_index: the one `knn_graph` attached, else a conversion
+    under the reference's own assumption (rows grouped by centre, same k everywhere —
+    grad_div_mls.py:24-25,224)."""
+    if isinstance(edge_index, EllGraph):
+        return edge_index
+    g = getattr(edge_index, '_dc_graph', None)
+    if g is not None and g.N == num_points:
+        return g
+    if isinstance(edge_index, (tuple, list)):
+        edge_index = torch.stack(list(edge_index))
+    if not (edge_index.is_cuda and edge_index.dtype == _I64 and edge_index.dim() == 2 and edge_index.size(0) == 2):
+        raise _lib.DeltaConvLibraryError("edge_index must be a [2,E] int64 CUDA tensor")
+    E = edge_index.size(1)
+    if num_points == 0 or E % num_points:
+        raise _lib.DeltaConvLibraryError(f"edge_index with {E} edges is not a fixed-k graph on {num_points} points")
+    k = E // num_points
+    ei = edge_index.contiguous()
+    idx = torch.empty(num_points, k, dtype=_I32, device=ei.device)
+    call('dc_ell_from_edge_index', ptr(ei), num_points, k, ptr(idx))
+    g = EllGraph(idx)
+    try:
+        edge_index._dc_graph = g
+    except Exception:
+        pass
+    return g
+
+
+# ------------------------------------------------------------------------------------------------
+# frames and operator build
+# ------------------------------------------------------------------------------------------------
+
+def tangent_basis(normal):
+    normal = _f32(normal, 'normal').contiguous()
+    xb, yb = torch.empty_like(normal), torch.empty_like(normal)
+    call('dc_tangent_basis', ptr(normal), normal.size(0), ptr(xb), ptr(yb))
+    return xb, yb
+
+
+def estimate_frames(pos, graph, orientation=None):
+    pos = _f32(pos, 'pos').contiguous()
+    if orientation is not None:
+        orientation = _f32(orientation, 'orientation').contiguous()
+    n, xb, yb = (torch.empty_like(pos) for _ in range(3))
+    call('dc_estimate_basis', ptr(pos), ptr(graph.idx), graph.N, graph.k, ptr(orientation), ptr(n), ptr(xb), ptr(yb))
+    return n, xb, yb
+
+
+def build_operators(pos, normal, xb, yb, graph, cloud_ptr, B, kernel_width=1.0, lam=1e-3, normalized=True,
+                    lam_shape=None, debug=False):
+    pos, normal, xb, yb = (_f32(t, n).contiguous() for t, n in ((pos, 'pos'), (normal, 'normal'), (xb, 'x_basis'), (yb, 'y_basis')))
+    N, k = graph.N, graph.k
+    dev = pos.device
+    G = torch.empty(N, k, 2, dtype=_F32, device=dev)
+    D = torch.empty(N, k, 2, dtype=_F32, device=dev)
+    dbg = [None, None, None]
+    if debug:
+        dbg = [torch.empty(N, k, 2, dtype=_F32, device=dev), torch.empty(N, k, dtype=_F32, device=dev),
+               torch.empty(N, k, 2, 2, dtype=_F32, device=dev)]
+    nbytes = query('dc_build_ws_bytes', N, B)
+    ws = workspace(nbytes, dev)
+    call('dc_build_grad_div', ptr(pos), ptr(normal), ptr(xb), ptr(yb), ptr(graph.idx), ptr(cloud_ptr), B, N, k,
+         float(kernel_width), float(lam), float(lam_shape if lam_shape is not None else 0.0),
+         int(lam_shape is not None), int(bool(normalized)), ptr(G), ptr(D), ptr(dbg[0]), ptr(dbg[1]), ptr(dbg[2]),
+         ptr(ws), nbytes)
+    return (G, D, dbg) if debug else (G, D)
+
+
+# ------------------------------------------------------------------------------------------------
+# operator application
+# ------------------------------------------------------------------------------------------------
+
+class _GradApply(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, op):
+        x, ldx = _mat(x, 'x')
+        g = op.graph
+        if x.size(0) != g.N:
+            raise _lib.DeltaConvLibraryError(f"grad @ x: x has {x.size(0)} rows, operator has {g.N} columns")
+        out = torch.empty(2 * g.N, x.size(1), dtype=_F32, device=x.device)
+        call('dc_grad_fwd', ptr(g.idx), ptr(op.G), g.N, g.k, x.size(1), ptr(x), ldx, ptr(out), out.size(1))
+        ctx.op = op
+        return out
+
+    @staticmethod
+    def backward(ctx, dv):
+        op, g = ctx.op, ctx.op.graph
+        dv, ld = _mat(dv, 'grad_output')
+        in_ptr, in_edge = g.transpose()
+        dx = torch.empty(g.N, dv.size(1), dtype=_F32, device=dv.device)
+        call('dc_grad_bwd', ptr(in_ptr), ptr(in_edge), ptr(op.G), g.N, g.k, dv.size(1), ptr(dv), ld, ptr(dx), dx.size(1))
+        return dx, None
+
+
+class _DivApply(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, v, op):
+        v, ldv = _mat(v, 'v')
+        g = op.graph
+        if v.size(0) != 2 * g.N:
+            raise _lib.DeltaConvLibraryError(f"div @ v: v has {v.size(0)} rows, operator has {2 * g.N} columns")
+        C = v.size(1)
+        out = torch.empty(g.N, C, dtype=_F32, device=v.device)
+        call('dc_divcurlnorm_fwd', ptr(g.idx), ptr(op.D), g.N, g.k, C, ptr(v), ldv, ptr(out), C, None, 0, None, 0)
+        ctx.op = op
+        return out
+
+    @staticmethod
+    def backward(ctx, dd):
+        op, g = ctx.op, ctx.op.graph
+        dd, ld = _mat(dd, 'grad_output')
+        in_ptr, in_edge = g.transpose()
+        C = dd.size(1)
+        dv = torch.empty(2 * g.N, C, dtype=_F32, device=dd.device)
+        call('dc_divcurlnorm_bwd', ptr(in_ptr), ptr(in_edge), ptr(op.D), g.N, g.k, C, ptr(dd), ld, None, 0, None, 0,
+             None, 0, ptr(dv), C)
+        return dv, None
+
+
+class EllOperator:
+    """What `build_grad_div` returns in place of a torch_sparse.SparseTensor: supports `.size(i)`,
+    `.sizes()` and `@ dense` (differentiable w.r.t. the dense operand), like the reference's
+    operators are used (deltanet_base.py:78, deltaconv.py:57,66, operators.py:23-46)."""
+
+    def __init__(self, kind, graph, G, D):
+        self.kind, self.graph, self.G, self.D = kind, graph, G, D
+
+    def size(self, dim):
+        N = self.graph.N
+        return (2 * N, N)[dim] if self.kind == 'grad' else (N, 2 * N)[dim]
+
+    def sizes(self):
+        return [self.size(0), self.size(1)]
+
+    def __matmul__(self, dense):
+        return _GradApply.apply(dense, self) if self.kind == 'grad' else _DivApply.apply(dense, self)
+
+    matmul = __matmul__
+
+    def coo(self):
+        """(row, col, value) sorted by (row, col) — the reference's SparseTensor storage order
+        (grad_div_mls.py:253-255,263,273-275).  For parity tests and interoperability."""
+        g = self.graph
+        N, k = g.N, g.k
+        idx = g.idx.long()
+        i = torch.arange(N, device=idx.device)[:, None].expand(N, k)
+        valid = (idx != N).reshape(-1).repeat_interleave(2)
+        if self.kind == 'grad':
+            row = torch.stack([2 * i, 2 * i + 1], -1).reshape(-1)
+            col = torch.stack([idx, idx], -1).reshape(-1)
+            val, ncol = self.G.reshape(-1), N
+        else:
+            row = torch.stack([i, i], -1).reshape(-1)
+            col = torch.stack([2 * idx, 2 * idx + 1], -1).reshape(-1)
+            val, ncol = self.D.reshape(-1), 2 * N
+        row, col, val = row[valid], col[valid], val[valid]
+        perm = torch.argsort(row * ncol + col, stable=True)
+        return row[perm], col[perm], val[perm]
+
+    def to_dense(self):
+        row, col, val = self.coo()
+        out = torch.zeros(self.size(0), self.size(1), dtype=_F32, device=val.device)
+        out.index_put_((row, col), val, accumulate=True)
+        return out
+
+    def __repr__(self):
+        return f'EllOperator({self.kind}, N={self.graph.N}, k={self.graph.k})'
+
+
+class _ScalarCat(torch.autograd.Function):
+    """[x | div v | curl v | |v|] (deltaconv.py:57) in one pass over v, plus a compact [div|curl]
+    copy for the Hodge Laplacian of the vector stream."""
+
+    @staticmethod
+    def forward(ctx, x, v, op):
+        x, _ = _mat(x, 'x')
+        v, ldv = _mat(v, 'v')
+        g = op.graph
+        C = x.size(1)
+        if v.size(0) != 2 * g.N or v.size(1) != C or x.size(0) != g.N:
+            raise _lib.DeltaConvLibraryError(f"DeltaConv: x {tuple(x.shape)} / v {tuple(v.shape)} do not match N={g.N}")
+        cat = torch.empty(g.N, 4 * C, dtype=_F32, device=x.device)
+        cat[:, :C].copy_(x)
+        call('dc_divcurlnorm_fwd', ptr(g.idx), ptr(op.D), g.N, g.k, C, ptr(v), ldv,
+             cat.data_ptr() + 4 * C, 4 * C, cat.data_ptr() + 8 * C, 4 * C, cat.data_ptr() + 12 * C, 4 * C)
+        dc = cat[:, C:3 * C].contiguous()
+        ctx.op, ctx.C = op, C
+        ctx.save_for_backward(v)
+        return cat, dc
+
+    @staticmethod
+    def backward(ctx, dcat, ddc):
+        op, g, C = ctx.op, ctx.op.graph, ctx.C
+        (v,) = ctx.saved_tensors
+        v, ldv = _mat(v)
+        dcat, ld = _mat(dcat.contiguous(), 'grad_output')
+        if ddc is not None:
+            t = dcat[:, C:3 * C] + ddc
+            d_div, d_curl, ldt = t.data_ptr(), t.data_ptr() + 4 * C, 2 * C
+        else:
+            d_div, d_curl, ldt = dcat.data_ptr() + 4 * C, dcat.data_ptr() + 8 * C, ld
+        in_ptr, in_edge = g.transpose()
+        dv = torch.empty(2 * g.N, C, dtype=_F32, device=dcat.device)
+        call('dc_divcurlnorm_bwd', ptr(in_ptr), ptr(in_edge), ptr(op.D), g.N, g.k, C, d_div, ldt, d_curl, ldt,
+             dcat.data_ptr() + 12 * C, ld, ptr(v), ldv, ptr(dv), C)
+        return dcat[:, :C], dv, None
+
+
+class _VectorCat(torch.autograd.Function):
+    """[v | hodge_laplacian(v) | grad x'] (deltaconv.py:66, operators.py:35-46) from the div/curl
+    already computed for the scalar stream."""
+
+    @staticmethod
+    def forward(ctx, v, dc, x_new, op):
+        v, _ = _mat(v, 'v')
+        dc, ld_dc = _mat(dc, 'div_curl')
+        x_new, ldx = _mat(x_new, 'x')
+        g = op.graph
+        Cin, Cout = v.size(1), x_new.size(1)
+        W = 2 * Cin + Cout
+        cat = torch.empty(2 * g.N, W, dtype=_F32, device=v.device)
+        cat[:, :Cin].copy_(v)
+        call('dc_hodge_fwd', ptr(g.idx), ptr(op.G), g.N, g.k, Cin, ptr(dc), ld_dc, dc.data_ptr() + 4 * Cin, ld_dc,
+             cat.data_ptr() + 4 * Cin, W)
+        call('dc_grad_fwd', ptr(g.idx), ptr(op.G), g.N, g.k, Cout, ptr(x_new), ldx, cat.data_ptr() + 8 * Cin, W)
+        ctx.op, ctx.Cin, ctx.Cout = op, Cin, Cout
+        return cat
+
+    @staticmethod
+    def backward(ctx, dcat):
+        op, g, Cin, Cout = ctx.op, ctx.op.graph, ctx.Cin, ctx.Cout
+        dcat, ld = _mat(dcat.contiguous(), 'grad_output')
+        in_ptr, in_edge = g.transpose()
+        ddc = torch.empty(g.N, 2 * Cin, dtype=_F32, device=dcat.device)
+        call('dc_hodge_bwd', ptr(in_ptr), ptr(in_edge), ptr(op.G), g.N, g.k, Cin, dcat.data_ptr() + 4 * Cin, ld,
+             ptr(ddc), 2 * Cin, ddc.data_ptr() + 4 * Cin, 2 * Cin)
+        dx = torch.empty(g.N, Cout, dtype=_F32, device=dcat.device)
+        call('dc_grad_bwd', ptr(in_ptr), ptr(in_edge), ptr(op.G), g.N, g.k, Cout, dcat.data_ptr() + 8 * Cin, ld, ptr(dx), Cout)
+        return dcat[:, :Cin], ddc, dx, None
+
+
+def scalar_cat(x, v, div_op):
+    return _ScalarCat.apply(x, v, div_op)
+
+
+def vector_cat(v, div_curl, x_new, grad_op):
+    return _VectorCat.apply(v, div_curl, x_new, grad_op)
+
+
+def curl_of(v, div_op):
+    """curl(v, div) = -div @ J(v)  (operators.py:23-27) without materialising J(v)."""
+    return _CurlApply.apply(v, div_op)
+
+
+class _CurlApply(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, v, op):
+        v, ldv = _mat(v, 'v')
+        g = op.graph
+        C = v.size(1)
+        out = torch.empty(g.N, C, dtype=_F32, device=v.device)
+        call('dc_divcurlnorm_fwd', ptr(g.idx), ptr(op.D), g.N, g.k, C, ptr(v), ldv, None, 0, ptr(out), C, None, 0)
+        ctx.op = op
+        return out
+
+    @staticmethod
+    def backward(ctx, dcurl):
+        op, g = ctx.op, ctx.op.graph
+        dcurl, ld = _mat(dcurl, 'grad_output')
+        in_ptr, in_edge = g.transpose()
+        C = dcurl.size(1)
+        dv = torch.empty(2 * g.N, C, dtype=_F32, device=dcurl.device)
+        call('dc_divcurlnorm_bwd', ptr(in_ptr), ptr(in_edge), ptr(op.D), g.N, g.k, C, None, 0, ptr(dcurl), ld, None, 0,
+             None, 0, ptr(dv), C)
+        return dv, None
+
+
+# ------------------------------------------------------------------------------------------------
+# Linear
+# ------------------------------------------------------------------------------------------------
+
+def _gemm_ws(M, N, K, device):
+    nbytes = query('dc_gemm_ws_bytes', M, N, K)
+    return workspace(nbytes, device), nbytes
+
+
+class _Linear(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias):
+        x, ldx = _mat(x, 'input')
+        weight, ldw = _mat(weight, 'weight')
+        if x.size(1) != weight.size(1):
+            raise _lib.DeltaConvLibraryError(f"Linear: input has {x.size(1)} features, weight expects {weight.size(1)}")
+        M, K, Nout = x.size(0), x.size(1), weight.size(0)
+        y = torch.empty(M, Nout, dtype=_F32, device=x.device)
+        if M:
+            ws, nb = _gemm_ws(M, Nout, K, x.device)
+            call('dc_linear_fwd', ptr(x), ldx, ptr(weight), ldw, ptr(_f32(bias, 'bias').contiguous()) if bias is not None else None,
+                 M, K, Nout, ptr(y), Nout, ptr(ws), nb)
+        ctx.save_for_backward(x, weight)
+        ctx.has_bias = bias is not None
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, weight = ctx.saved_tensors
+        x, ldx = _mat(x)
+        weight, ldw = _mat(weight)
+        dy, ld = _mat(dy, 'grad_output')
+        M, K, Nout = x.size(0), x.size(1), weight.size(0)
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty(M, K, dtype=_F32, device=dy.device)
+            ws, nb = _gemm_ws(M, K, Nout, dy.device)
+            call('dc_linear_bwd_input', ptr(dy), ld, ptr(weight), ldw, M, K, Nout, ptr(dx), K, ptr(ws), nb)
+        if ctx.needs_input_grad[1]:
+            dw = torch.empty(Nout, K, dtype=_F32, device=dy.device)
+            ws, nb = _gemm_ws(Nout, K, M, dy.device)
+            call('dc_linear_bwd_weight', ptr(dy), ld, ptr(x), ldx, M, K, Nout, ptr(dw), K, ptr(ws), nb)
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            db = torch.empty(Nout, dtype=_F32, device=dy.device)
+            nb = query('dc_colreduce_ws_bytes', Nout)
+            ws = workspace(nb, dy.device)
+            call('dc_col_sum', ptr(dy), ld, M, Nout, ptr(db), ptr(ws), nb)
+        return dx, dw, db
+
+
+def linear(x, weight, bias=None):
+    return _Linear.apply(x, weight, bias)
+
+
+class _ExpandVecWeight(torch.autograd.Function):
+    """[W1 | W2] -> [[W1, -W2], [W2, W1]] — folds I_J (operators.py:19-21) into the weights."""
+
+    @staticmethod
+    def forward(ctx, weight):
+        weight = _f32(weight, 'weight').contiguous()
+        Cout, K2 = weight.shape
+        out = torch.empty(2 * Cout, K2, dtype=_F32, device=weight.device)
+        call('dc_expand_vec_weight', ptr(weight), Cout, K2 // 2, ptr(out))
+        return out
+
+    @staticmethod
+    def backward(ctx, dwe):
+        dwe = dwe.contiguous()
+        Cout, K2 = dwe.size(0) // 2, dwe.size(1)
+        dw = torch.empty(Cout, K2, dtype=_F32, device=dwe.device)
+        call('dc_fold_vec_weight_grad', ptr(dwe), Cout, K2 // 2, ptr(dw))
+        return dw
+
+
+def vector_linear_with_rotation(v_cat, weight):
+    """Linear(I_J(v_cat)) (deltaconv.py:68) as one GEMM on the [N, 2K] view of the interleaved
+    field with the expanded weight; v_cat [2N,K], weight [Cout,2K] -> [2N,Cout]."""
+    rows, K = v_cat.shape
+    if weight.size(1) != 2 * K:
+        raise _lib.DeltaConvLibraryError(f"vector Linear: weight expects {weight.size(1)} inputs, I_J(v) has {2 * K}")
+    we = _ExpandVecWeight.apply(weight)
+    out = _Linear.apply(v_cat.contiguous().view(rows // 2, 2 * K), we, None)
+    return out.view(rows, weight.size(0))
+
+
+# ------------------------------------------------------------------------------------------------
+# BatchNorm + activation, VectorNonLin
+# ------------------------------------------------------------------------------------------------
+
+def _bn_moments(bn, x, ldx, M, C, mode):
+    """(mean, invstd) to normalise with: batch statistics in training mode (running stats are
+    updated in place like torch.nn.BatchNorm1d), running statistics in eval mode."""
+    dev = x.device
+    use_batch = bn.training or not bn.track_running_stats or bn.running_mean is None
+    if use_batch:
+        mean = torch.empty(C, dtype=_F32, device=dev)
+        invstd = torch.empty(C, dtype=_F32, device=dev)
+        update = bn.training and bn.track_running_stats and bn.running_mean is not None
+        momentum = 0.0
+        if update:
+            bn.num_batches_tracked += 1
+            momentum = bn.momentum if bn.momentum is not None else 1.0 / float(bn.num_batches_tracked)
+        nb = query('dc_colreduce_ws_bytes', C)
+        ws = workspace(nb, dev)
+        call('dc_bn_stats', x.data_ptr(), ldx, M, C, mode, float(bn.eps), float(momentum), ptr(mean), ptr(invstd),
+             ptr(bn.running_mean) if update else None, ptr(bn.running_var) if update else None, ptr(ws), nb)
+        return mean, invstd, True
+    mean = bn.running_mean.contiguous()
+    invstd = torch.rsqrt(bn.running_var + bn.eps)
+    return mean, invstd, False
+
+
+class _BNAct(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, y, gamma, beta, addend, bn, slope):
+        y, ldy = _mat(y, 'input')
+        M, C = y.shape
+        if M == 0:
+            raise _lib.DeltaConvLibraryError("BatchNorm1d: empty batch")
+        mean, invstd, batch_stats = _bn_moments(bn, y, ldy, M, C, 0)
+        out = torch.empty(M, C, dtype=_F32, device=y.device)
+        add_p, ld_add = (None, 0)
+        if addend is not None:
+            addend, ld_add = _mat(addend, 'addend')
+            add_p = ptr(addend)
+        call('dc_bn_act_fwd', ptr(y), ldy, M, C, ptr(mean), ptr(invstd), ptr(gamma), ptr(beta), float(slope),
+             add_p, ld_add, ptr(out), C)
+        ctx.save_for_backward(y, mean, invstd, gamma, beta)
+        ctx.slope, ctx.batch_stats, ctx.has_add = slope, batch_stats, addend is not None
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        y, mean, invstd, gamma, beta = ctx.saved_tensors
+        y, ldy = _mat(y)
+        dout, ldd = _mat(dout, 'grad_output')
+        M, C = y.shape
+        dgamma = torch.empty(C, dtype=_F32, device=y.device)
+        dbeta = torch.empty(C, dtype=_F32, device=y.device)
+        dy = torch.empty(M, C, dtype=_F32, device=y.device)
+        nb = query('dc_colreduce_ws_bytes', C)
+        ws = workspace(nb, y.device)
+        call('dc_bn_act_bwd', ptr(y), ldy, ptr(dout), ldd, M, C, ptr(mean), ptr(invstd), ptr(gamma), ptr(beta),
+             float(ctx.slope), int(ctx.batch_stats), ptr(dgamma), ptr(dbeta), ptr(dy), C, ptr(ws), nb)
+        return (dy, dgamma if gamma is not None else None, dbeta if beta is not None else None,
+                dout if ctx.has_add else None, None, None)
+
+
+def bn_act(y, bn, slope=1.0, addend=None):
+    """act(BatchNorm1d(y)) + addend with act = LeakyReLU(slope) (slope 1 = identity)."""
+    return _BNAct.apply(y, bn.weight, bn.bias, addend, bn, float(slope))
+
+
+class _VecNonLin(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, v, gamma, beta, bias, bn):
+        v, ldv = _mat(v, 'input')
+        rows, C = v.shape
+        if rows % 2:
+            raise _lib.DeltaConvLibraryError("VectorNonLin: vector fields have an even number of rows")
+        M = rows // 2
+        out = torch.empty(rows, C, dtype=_F32, device=v.device)
+        if bn is not None:
+            mean, invstd, batch_stats = _bn_moments(bn, v, ldv, M, C, 1)
+            call('dc_vecnonlin_fwd', ptr(v), ldv, M, C, ptr(mean), ptr(invstd), ptr(gamma), ptr(beta), None, ptr(out), C)
+        else:
+            mean = invstd = None
+            batch_stats = False
+            call('dc_vecnonlin_fwd', ptr(v), ldv, M, C, None, None, None, None, ptr(bias), ptr(out), C)
+        ctx.save_for_backward(v, mean, invstd, gamma, beta, bias)
+        ctx.batch_stats, ctx.with_bn = batch_stats, bn is not None
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        v, mean, invstd, gamma, beta, bias = ctx.saved_tensors
+        v, ldv = _mat(v)
+        dout, ldd = _mat(dout, 'grad_output')
+        rows, C = v.shape
+        M = rows // 2
+        dv = torch.empty(rows, C, dtype=_F32, device=v.device)
+        nb = query('dc_colreduce_ws_bytes', C)
+        ws = workspace(nb, v.device)
+        if ctx.with_bn:
+            dgamma = torch.empty(C, dtype=_F32, device=v.device)
+            dbeta = torch.empty(C, dtype=_F32, device=v.device)
+            call('dc_vecnonlin_bwd', ptr(v), ldv, ptr(dout), ldd, M, C, ptr(mean), ptr(invstd), ptr(gamma), ptr(beta), None,
+                 int(ctx.batch_stats), ptr(dgamma), ptr(dbeta), None, ptr(dv), C, ptr(ws), nb)
+            return dv, dgamma if gamma is not None else None, dbeta if beta is not None else None, None, None
+        rows_grad = torch.empty(M, C, dtype=_F32, device=v.device)
+        call('dc_vecnonlin_bwd', ptr(v), ldv, ptr(dout), ldd, M, C, None, None, None, None, ptr(bias), 0,
+             None, None, ptr(rows_grad), ptr(dv), C, ptr(ws), nb)
+        dbias = torch.empty(C, dtype=_F32, device=v.device)
+        call('dc_col_sum', ptr(rows_grad), C, M, C, ptr(dbias), ptr(ws), nb)
+        return dv, None, None, dbias, None
+
+
+def vec_nonlin(v, bias, bn):
+    if bn is not None:
+        return _VecNonLin.apply(v, bn.weight, bn.bias, None, bn)
+    return _VecNonLin.apply(v, None, None, bias, None)
+
+
+# ------------------------------------------------------------------------------------------------
+# neighbourhood max, pools
+# ------------------------------------------------------------------------------------------------
+
+class _GatherMax(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, y, graph):
+        y, ldy = _mat(y, 'input')
+        N, k, C = graph.N, graph.k, y.size(1)
+        out = torch.empty(N, C, dtype=_F32, device=y.device)
+        arg = torch.empty(N, C, dtype=torch.uint8, device=y.device)
+        call('dc_gathermax_fwd', ptr(graph.idx), N, k, C, ptr(y), ldy, ptr(out), C, ptr(arg))
+        ctx.graph = graph
+        ctx.save_for_backward(arg)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        g = ctx.graph
+        (arg,) = ctx.saved_tensors
+        dout, ldd = _mat(dout, 'grad_output')
+        in_ptr, in_edge = g.transpose()
+        C = dout.size(1)
+        dy = torch.empty(g.N, C, dtype=_F32, device=dout.device)
+        call('dc_gathermax_bwd', ptr(in_ptr), ptr(in_edge), g.N, g.k, C, ptr(arg), ptr(dout), ldd, ptr(dy), C)
+        return dy, None
+
+
+def gather_max(y, graph):
+    return _GatherMax.apply(y, graph)
+
+
+class _EdgeDiff(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, graph):
+        x, ldx = _mat(x, 'x')
+        N, k, C = graph.N, graph.k, x.size(1)
+        out = torch.empty(N * k, C, dtype=_F32, device=x.device)
+        call('dc_edge_diff_fwd', ptr(graph.idx), N, k, C, ptr(x), ldx, ptr(out))
+        ctx.graph = graph
+        return out
+
+    @staticmethod
+    def backward(ctx, de):
+        g = ctx.graph
+        de = de.contiguous()
+        in_ptr, in_edge = g.transpose()
+        C = de.size(1)
+        dx = torch.empty(g.N, C, dtype=_F32, device=de.device)
+        call('dc_edge_diff_bwd', ptr(in_ptr), ptr(in_edge), g.N, g.k, C, ptr(de), ptr(dx), C)
+        return dx, None
+
+
+class _SegMax(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, t, graph):
+        t = _f32(t, 'input').contiguous()
+        N, k, C = graph.N, graph.k, t.size(1)
+        out = torch.empty(N, C, dtype=_F32, device=t.device)
+        arg = torch.empty(N, C, dtype=torch.uint8, device=t.device)
+        call('dc_segmax_fwd', ptr(t), N, k, C, ptr(graph.idx), ptr(out), C, ptr(arg))
+        ctx.graph = graph
+        ctx.save_for_backward(arg)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        g = ctx.graph
+        (arg,) = ctx.saved_tensors
+        dout, ldd = _mat(dout, 'grad_output')
+        C = dout.size(1)
+        din = torch.empty(g.N * g.k, C, dtype=_F32, device=dout.device)
+        call('dc_segmax_bwd', ptr(dout), ldd, g.N, g.k, C, ptr(arg), ptr(din))
+        return din, None
+
+
+def edge_diff(x, graph):
+    return _EdgeDiff.apply(x, graph)
+
+
+def segment_max(t, graph):
+    return _SegMax.apply(t, graph)
+
+
+class _Pool(torch.autograd.Function):
+    """mode 'max' | 'mean' | 'maxmean' ([max | mean] side by side, deltanet_classification.py:46-49)."""
+
+    @staticmethod
+    def forward(ctx, x, cloud_ptr, B, mode):
+        x, ldx = _mat(x, 'x')
+        N, C = x.shape
+        want_max, want_mean = mode in ('max', 'maxmean'), mode in ('mean', 'maxmean')
+        width = C * (2 if mode == 'maxmean' else 1)
+        out = torch.empty(B, width, dtype=_F32, device=x.device)
+        arg = torch.empty(B, C, dtype=_I32, device=x.device) if want_max else None
+        mean_p = (out.data_ptr() + (4 * C if mode == 'maxmean' else 0)) if want_mean else None
+        call('dc_pool_fwd', ptr(x), ldx, ptr(cloud_ptr), B, C, ptr(out) if want_max else None, width, mean_p, width, ptr(arg))
+        ctx.mode, ctx.N, ctx.C, ctx.B = mode, N, C, B
+        ctx.save_for_backward(cloud_ptr, arg)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        cloud_ptr, arg = ctx.saved_tensors
+        dout, ld = _mat(dout, 'grad_output')
+        N, C, B, mode = ctx.N, ctx.C, ctx.B, ctx.mode
+        dx = torch.empty(N, C, dtype=_F32, device=dout.device)
+        dmax = dout.data_ptr() if mode in ('max', 'maxmean') else None
+        dmean = (dout.data_ptr() + (4 * C if mode == 'maxmean' else 0)) if mode in ('mean', 'maxmean') else None
+        call('dc_pool_bwd', ptr(cloud_ptr), B, N, C, ptr(arg), dmax, ld, dmean, ld, ptr(dx), C)
+        return dx, None, None, None
+
+
+def pool(x, batch, mode, size=None):
+    cp, B = cloud_ptr_of(batch, x.size(0), x.device, size)
+    return _Pool.apply(x, cp, B, mode)
+
+
+class _BcastRows(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, src, cloud_ptr, B, N):
+        src, lds = _mat(src, 'src')
+        C = src.size(1)
+        out = torch.empty(N, C, dtype=_F32, device=src.device)
+        call('dc_bcast_rows', ptr(src), lds, ptr(cloud_ptr), B, N, C, ptr(out), C)
+        ctx.B, ctx.N = B, N
+        ctx.save_for_backward(cloud_ptr)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        (cloud_ptr,) = ctx.saved_tensors
+        dout, ld = _mat(dout, 'grad_output')
+        C = dout.size(1)
+        # per-cloud column sums = mean-pool backward's transpose: reuse the pool kernel (mean * count)
+        dsrc = torch.empty(ctx.B, C, dtype=_F32, device=dout.device)
+        call('dc_pool_fwd', ptr(dout), ld, ptr(cloud_ptr), ctx.B, C, None, 0, ptr(dsrc), C, None)
+        counts = (cloud_ptr[1:] - cloud_ptr[:-1]).to(_F32)
+        return dsrc * counts[:, None], None, None, None
+
+
+def broadcast_rows(src, batch, num_points):
+    cp, B = cloud_ptr_of(batch, num_points, src.device, src.size(0))
+    return _BcastRows.apply(src, cp, B, num_points)

@@ -1,0 +1,172 @@
+/* deltaconv_b200 — C ABI of the B200-native (sm_100a) DeltaConv hot path.
+ *
+ * Conventions (all entry points):
+ *   - plain C, no torch types; every pointer is a DEVICE pointer to a contiguous row-major array
+ *     unless a leading dimension ("ld", in elements) is given, in which case rows are ld apart;
+ *   - float = fp32, indices int32 (ELL) or int64 (edge_index, batch, as PyTorch-Geometric holds them);
+ *   - `stream` is a cudaStream_t passed as void*; all work is enqueued on it, nothing synchronises;
+ *   - the library allocates nothing: the caller supplies outputs and workspaces (sizes from dc_*_ws_bytes);
+ *   - return value: 0 ok, <0 invalid argument, >0 a cudaError_t; dc_last_error() holds the message
+ *     (thread-local).
+ *
+ * Layouts:
+ *   idx [N,k] int32   neighbour of point i in slot e (slot 0 = i itself, ascending distance);
+ *                     the value N is the padding sentinel of the reference (grad_div_mls.py:226-227)
+ *   G, D [N,k,2] f32  grad[2i+a, idx[i,e]] = G[i,e,a];  div[i, 2*idx[i,e]+a] = D[i,e,a]
+ *   vector fields [2N,C]: rows (2i, 2i+1) are the (x, y) components of point i (operators.py:7,12-16)
+ *   in_ptr [N+1], in_edge [nnz] int32: incoming edges of every point (edge id = i*k+e), ascending.
+ *
+ * Each declaration cites the reference interface it replaces (paths relative to the reference
+ * repository root, rubenwiersma/deltaconv @186fec3).
+ */
+#ifndef DELTACONV_B200_H
+#define DELTACONV_B200_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* dc_last_error(void);
+int dc_abi_version(void);
+int dc_device_sm_count(void);
+
+/* ---- graph ------------------------------------------------------------------------------- */
+
+/* cloud_ptr[B+1] from the sorted PyG batch vector (deltanet_base.py:44 `data.batch`). */
+int dc_cloud_ptr(const int64_t* batch, int N, int B, int32_t* cloud_ptr, void* stream);
+
+/* knn_graph(pos, k, batch, loop=True, flow='target_to_source') — deltanet_base.py:52,63 (torch_cluster).
+ * Neighbours ascending by (d2, index), d2 = (dx*dx+dy*dy)+dz*dz in fp32 without contraction.
+ * edge_index_or_null: [2, N*k] int64 in PyG layout; d2_or_null: [N,k]. k <= 128. */
+int dc_knn(const float* pos, const int32_t* cloud_ptr, int B, int N, int k, int32_t* idx,
+           int64_t* edge_index_or_null, float* d2_or_null, void* stream);
+
+/* [2,N*k] int64 edge_index (rows grouped by centre, fixed k — grad_div_mls.py:24-25,224) <-> ELL idx. */
+int dc_ell_from_edge_index(const int64_t* edge_index, int N, int k, int32_t* idx, void* stream);
+int dc_edge_index_from_ell(const int32_t* idx, int N, int k, int64_t* edge_index, void* stream);
+
+/* Incoming-edge CSR of the graph: the structure torch_sparse caches as CSC for the backward SpMM. */
+size_t dc_ell_transpose_ws_bytes(int N);
+int dc_ell_transpose(const int32_t* idx, int N, int k, int32_t* in_ptr, int32_t* in_edge,
+                     void* ws, size_t ws_bytes, void* stream);
+
+/* ---- tangent frames ------------------------------------------------------------------------ */
+
+/* build_tangent_basis(normal) — grad_div_mls.py:50-69. */
+int dc_tangent_basis(const float* normal, int N, float* xb, float* yb, void* stream);
+
+/* estimate_basis(pos, edge_index, k, orientation) — grad_div_mls.py:10-47 (batched 3xk SVD). */
+int dc_estimate_basis(const float* pos, const int32_t* idx, int N, int k, const float* orient_or_null,
+                      float* normal, float* xb, float* yb, void* stream);
+
+/* ---- operator build ------------------------------------------------------------------------ */
+
+/* build_grad_div(pos, normal, x_basis, y_basis, edge_index, batch, kernel_width, regularizer,
+ * normalized, shape_regularizer) — grad_div_mls.py:197-277 with coords_projected (:72-97),
+ * gaussian_weights (:100-116), weighted_least_squares (:119-152), fit_vector_mapping (:155-194).
+ * Optional debug outputs expose those helpers' results: coords [N,k,2], weights [N,k], mapping [N,k,2,2]. */
+size_t dc_build_ws_bytes(int N, int B);
+int dc_build_grad_div(const float* pos, const float* normal, const float* xb, const float* yb,
+                      const int32_t* idx, const int32_t* cloud_ptr, int B, int N, int k,
+                      float kernel_width, float lam, float lam_shape, int use_shape, int normalized,
+                      float* G, float* D, float* dbg_coords, float* dbg_weights, float* dbg_mapping,
+                      void* ws, size_t ws_bytes, void* stream);
+
+/* ---- operator application (SparseTensor @ dense and operators.py) --------------------------- */
+
+/* grad @ x — deltanet_base.py:78, deltaconv.py:66:  out[2i+a,:] = sum_e G[i,e,a] x[idx[i,e],:] */
+int dc_grad_fwd(const int32_t* idx, const float* G, int N, int k, int C, const float* x, int64_t ldx,
+                float* out, int64_t ldo, void* stream);
+/* its transpose (autograd of the above w.r.t. x): dX[j,:] = sum_{(i,e)->j} G[i,e,:] . dV[2i:2i+2,:] */
+int dc_grad_bwd(const int32_t* in_ptr, const int32_t* in_edge, const float* G, int N, int k, int C,
+                const float* dV, int64_t ld_dv, float* dX, int64_t ld_dx, void* stream);
+
+/* [div @ v | curl(v, div) | norm(v)] in one pass — deltaconv.py:57, operators.py:4-7,23-27. */
+int dc_divcurlnorm_fwd(const int32_t* idx, const float* D, int N, int k, int C, const float* v, int64_t ldv,
+                       float* div_or_null, int64_t ld_div, float* curl_or_null, int64_t ld_curl,
+                       float* norm_or_null, int64_t ld_norm, void* stream);
+int dc_divcurlnorm_bwd(const int32_t* in_ptr, const int32_t* in_edge, const float* D, int N, int k, int C,
+                       const float* d_div_or_null, int64_t ld_ddiv, const float* d_curl_or_null, int64_t ld_dcurl,
+                       const float* d_norm_or_null, int64_t ld_dnorm, const float* v, int64_t ldv,
+                       float* dV, int64_t ld_dv, void* stream);
+
+/* hodge_laplacian(v, grad, div) given div v and curl v — operators.py:35-46:
+ * out = -(grad(div_v) + J grad(curl_v)), rows interleaved like every vector field. */
+int dc_hodge_fwd(const int32_t* idx, const float* G, int N, int k, int C, const float* div_v, int64_t ld_a,
+                 const float* curl_v, int64_t ld_b, float* out, int64_t ldo, void* stream);
+int dc_hodge_bwd(const int32_t* in_ptr, const int32_t* in_edge, const float* G, int N, int k, int C,
+                 const float* d_out, int64_t ld_do, float* d_div, int64_t ld_da, float* d_curl, int64_t ld_db,
+                 void* stream);
+
+/* ---- scalar stream: kNN max aggregation ------------------------------------------------------ */
+
+/* scatter(s_mlp_max(x)[edge_index[1]], edge_index[0], reduce='max') — deltaconv.py:54 (torch_scatter).
+ * arg [N,C] u8 = lowest slot attaining the maximum (the element that receives the gradient). */
+int dc_gathermax_fwd(const int32_t* idx, int N, int k, int C, const float* y, int64_t ldy, float* out, int64_t ldo,
+                     uint8_t* arg, void* stream);
+int dc_gathermax_bwd(const int32_t* in_ptr, const int32_t* in_edge, int N, int k, int C, const uint8_t* arg,
+                     const float* dout, int64_t ldd, float* dy, int64_t ld_dy, void* stream);
+
+/* centralized first layer, deltaconv.py:50-52: edge features x[col]-x[row] ([N*k,C], dense) and the
+ * max over the k rows of every point after the edge MLP. */
+int dc_edge_diff_fwd(const int32_t* idx, int N, int k, int C, const float* x, int64_t ldx, float* out, void* stream);
+int dc_edge_diff_bwd(const int32_t* in_ptr, const int32_t* in_edge, int N, int k, int C, const float* d_edge,
+                     float* dx, int64_t ld_dx, void* stream);
+int dc_segmax_fwd(const float* in, int N, int k, int C, const int32_t* idx_or_null, float* out, int64_t ldo,
+                  uint8_t* arg, void* stream);
+int dc_segmax_bwd(const float* dout, int64_t ldd, int N, int k, int C, const uint8_t* arg, float* din, void* stream);
+
+/* ---- BatchNorm1d wrapper + LeakyReLU (nonlin.py:11-35, mlp.py:7-11) -------------------------- */
+
+size_t dc_colreduce_ws_bytes(int C);
+/* mode 0: batch statistics of x [M,C]; mode 1: of the norms of a vector field x [2M,C] (nonlin.py:68,77).
+ * Writes mean/invstd (biased variance, eps) and updates running stats like torch.nn.BatchNorm1d. */
+int dc_bn_stats(const float* x, int64_t ldx, int64_t M, int C, int mode, float eps, float momentum,
+                float* mean, float* invstd, float* running_mean_or_null, float* running_var_or_null,
+                void* ws, size_t ws_bytes, void* stream);
+/* out = leaky_relu(gamma*(y-mean)*invstd+beta, slope) + addend   (addend: `x_max +`, deltaconv.py:59) */
+int dc_bn_act_fwd(const float* y, int64_t ldy, int64_t M, int C, const float* mean, const float* invstd,
+                  const float* gamma_or_null, const float* beta_or_null, float slope,
+                  const float* addend_or_null, int64_t ld_add, float* out, int64_t ldo, void* stream);
+int dc_bn_act_bwd(const float* y, int64_t ldy, const float* dout, int64_t ldd, int64_t M, int C,
+                  const float* mean, const float* invstd, const float* gamma_or_null, const float* beta_or_null,
+                  float slope, int training, float* d_gamma, float* d_beta, float* dy, int64_t ld_dy,
+                  void* ws, size_t ws_bytes, void* stream);
+int dc_col_sum(const float* x, int64_t ldx, int64_t M, int C, float* out, void* ws, size_t ws_bytes, void* stream);
+
+/* ---- VectorNonLin (nonlin.py:38-86) ------------------------------------------------------------ */
+int dc_vecnonlin_fwd(const float* v, int64_t ldv, int64_t M, int C, const float* mean_or_null,
+                     const float* invstd_or_null, const float* gamma_or_null, const float* beta_or_null,
+                     const float* bias_or_null, float* out, int64_t ldo, void* stream);
+int dc_vecnonlin_bwd(const float* v, int64_t ldv, const float* dout, int64_t ldd, int64_t M, int C,
+                     const float* mean_or_null, const float* invstd_or_null, const float* gamma_or_null,
+                     const float* beta_or_null, const float* bias_or_null, int training,
+                     float* d_gamma, float* d_beta, float* dbias_rows_or_null, float* dv, int64_t ld_dv,
+                     void* ws, size_t ws_bytes, void* stream);
+
+/* ---- global pools (deltanet_classification.py:46-47, deltanet_segmentation.py:61; PyG scatter) --- */
+int dc_pool_fwd(const float* x, int64_t ldx, const int32_t* cloud_ptr, int B, int C, float* out_max_or_null,
+                int64_t ld_max, float* out_mean_or_null, int64_t ld_mean, int32_t* arg, void* stream);
+int dc_pool_bwd(const int32_t* cloud_ptr, int B, int N, int C, const int32_t* arg, const float* d_max_or_null,
+                int64_t ld_dmax, const float* d_mean_or_null, int64_t ld_dmean, float* dx, int64_t ld_dx, void* stream);
+/* out[i,:] = src[cloud(i),:] — `global_max_pool(x, batch)[batch]`, deltanet_segmentation.py:61,64 */
+int dc_bcast_rows(const float* src, int64_t lds, const int32_t* cloud_ptr, int B, int N, int C, float* out, int64_t ldo,
+                  void* stream);
+
+/* ---- Linear (mlp.py:9,15; heads) ---------------------------------------------------------------- */
+size_t dc_gemm_ws_bytes(int64_t M, int64_t N, int64_t K);
+int dc_linear_fwd(const float* X, int64_t ldx, const float* W, int64_t ldw, const float* bias_or_null,
+                  int64_t M, int K, int Nout, float* Y, int64_t ldy, void* ws, size_t ws_bytes, void* stream);
+int dc_linear_bwd_input(const float* dY, int64_t ld_dy, const float* W, int64_t ldw, int64_t M, int K, int Nout,
+                        float* dX, int64_t ld_dx, void* ws, size_t ws_bytes, void* stream);
+int dc_linear_bwd_weight(const float* dY, int64_t ld_dy, const float* X, int64_t ldx, int64_t M, int K, int Nout,
+                         float* dW, int64_t ld_dw, void* ws, size_t ws_bytes, void* stream);
+/* I_J folded into the weights (operators.py:19-21, deltaconv.py:68): W [Cout,2K] -> [[W1,-W2],[W2,W1]] */
+int dc_expand_vec_weight(const float* W, int Cout, int K, float* W_expanded, void* stream);
+int dc_fold_vec_weight_grad(const float* dW_expanded, int Cout, int K, float* dW, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DELTACONV_B200_H */

@@ -1,0 +1,336 @@
+"""GPU parity: Linear / BatchNorm / VectorNonLin / aggregation kernels, DeltaConv layers and whole
+networks (forward AND backward) against torch fp64, the oracle and the golden fixtures produced
+by the unmodified reference.  Run with `-m gpu`."""
+import copy
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+from helpers import load, t, rel_err, LOGIT_REL, GRAD_REL
+from oracle import geometry as og
+from oracle import network as on
+
+pytestmark = pytest.mark.gpu
+DEV = 'cuda'
+
+
+def dc():
+    import deltaconv_b200
+    return deltaconv_b200
+
+
+def no_dropout(m):
+    for mod in m.modules():
+        if isinstance(mod, torch.nn.Dropout):
+            mod.p = 0.0
+    return m
+
+
+# ----------------------------------------------------------------------------------------------
+# kernels against torch fp64
+# ----------------------------------------------------------------------------------------------
+
+@pytest.mark.parametrize('M,K,N,bias', [(1, 1, 1, False), (37, 3, 64, False), (1000, 12, 1, True), (4096, 256, 64, False),
+                                        (333, 517, 129, True), (32, 2048, 512, False), (20000, 24, 16, False)])
+def test_linear_forward_backward(M, K, N, bias):
+    x0, w0 = torch.randn(M, K), torch.randn(N, K) / K ** 0.5
+    b0 = torch.randn(N) if bias else None
+    g0 = torch.randn(M, N)
+    x, w = x0.to(DEV).requires_grad_(True), w0.to(DEV).requires_grad_(True)
+    b = b0.to(DEV).requires_grad_(True) if bias else None
+    y = dc().ops.linear(x, w, b)
+    (y * g0.to(DEV)).sum().backward()
+    xr, wr = x0.double().requires_grad_(True), w0.double().requires_grad_(True)
+    br = b0.double().requires_grad_(True) if bias else None
+    yr = F.linear(xr, wr, br)
+    (yr * g0.double()).sum().backward()
+    assert rel_err(y.detach().cpu(), yr.detach()) < 2e-6
+    assert rel_err(x.grad.cpu(), xr.grad) < 2e-6
+    assert rel_err(w.grad.cpu(), wr.grad) < 5e-6
+    if bias:
+        assert rel_err(b.grad.cpu(), br.grad) < 2e-6
+
+
+@pytest.mark.parametrize('M,C,slope,train', [(1000, 64, 0.2, True), (257, 5, 1.0, True), (4096, 130, 0.2, False),
+                                             (50000, 16, 0.0, True), (2, 1, 0.2, True)])
+def test_batchnorm_activation(M, C, slope, train):
+    nn = dc().nn
+    mod = nn.BatchNorm1d(C).to(DEV)
+    ref = torch.nn.BatchNorm1d(C).double()
+    with torch.no_grad():
+        for p_, q_ in ((mod.bn.weight, ref.weight), (mod.bn.bias, ref.bias), (mod.bn.running_mean, ref.running_mean),
+                       (mod.bn.running_var, ref.running_var)):
+            val = torch.randn(C) * 0.3 + (1.0 if p_ is mod.bn.weight or p_ is mod.bn.running_var else 0.0)
+            if p_ is mod.bn.running_var:
+                val = val.abs() + 0.1
+            p_.copy_(val)
+            q_.copy_(val.double())
+    mod.train(train)
+    ref.train(train)
+    x0 = torch.randn(M, C) * 2 + 3          # mean >> 0: exercises the variance accumulation
+    add0, g0 = torch.randn(M, C), torch.randn(M, C)
+    x = x0.to(DEV).requires_grad_(True)
+    add = add0.to(DEV).requires_grad_(True)
+    out = mod(x, slope, add)
+    (out * g0.to(DEV)).sum().backward()
+    xr, addr = x0.double().requires_grad_(True), add0.double().requires_grad_(True)
+    outr = F.leaky_relu(ref(xr), slope) + addr
+    (outr * g0.double()).sum().backward()
+    assert rel_err(out.detach().cpu(), outr.detach()) < 5e-6
+    assert rel_err(x.grad.cpu(), xr.grad) < 1e-4
+    assert rel_err(add.grad.cpu(), addr.grad) < 1e-6
+    assert rel_err(mod.bn.weight.grad.cpu(), ref.weight.grad) < 1e-4
+    assert rel_err(mod.bn.bias.grad.cpu(), ref.bias.grad) < 1e-4
+    assert rel_err(mod.bn.running_mean.cpu(), ref.running_mean) < 1e-5
+    assert rel_err(mod.bn.running_var.cpu(), ref.running_var) < 1e-5
+    assert int(mod.bn.num_batches_tracked) == int(ref.num_batches_tracked)
+
+
+@pytest.mark.parametrize('M,C,with_bn,train', [(777, 32, True, True), (100, 7, False, True), (2048, 64, True, False)])
+def test_vector_nonlin(M, C, with_bn, train):
+    nn = dc().nn
+    mod = nn.VectorNonLin(C, batchnorm=nn.BatchNorm1d(C) if with_bn else None).to(DEV)
+    ref = on.VectorNonLin(C, batchnorm=on.BatchNorm1d(C) if with_bn else None).double()
+    with torch.no_grad():
+        mod.bias.copy_(torch.randn(C) * 0.5 - 0.3)
+        if with_bn:
+            mod.batchnorm.bn.weight.copy_(torch.randn(C) * 0.3 + 1)
+            mod.batchnorm.bn.bias.copy_(torch.randn(C) * 0.3)
+    ref.load_state_dict({k_: v_.double() if v_.is_floating_point() else v_ for k_, v_ in mod.state_dict().items()})
+    mod.train(train)
+    ref.train(train)
+    v0 = torch.randn(2 * M, C)
+    v0[:4] = 0                               # zero vectors: the 1e-8 clamp path
+    g0 = torch.randn(2 * M, C)
+    v = v0.to(DEV).requires_grad_(True)
+    out = mod(v)
+    (out * g0.to(DEV)).sum().backward()
+    vr = v0.double().requires_grad_(True)
+    outr = ref(vr)
+    (outr * g0.double()).sum().backward()
+    assert rel_err(out.detach().cpu(), outr.detach()) < 5e-6
+    assert rel_err(v.grad.cpu(), vr.grad) < 1e-4
+    if with_bn:
+        assert rel_err(mod.batchnorm.bn.weight.grad.cpu(), ref.batchnorm.bn.weight.grad) < 1e-4
+        assert rel_err(mod.batchnorm.bn.bias.grad.cpu(), ref.batchnorm.bn.bias.grad) < 1e-4
+        assert mod.bias.grad is None                       # unused when BN is on
+    else:
+        assert rel_err(mod.bias.grad.cpu(), ref.bias.grad) < 1e-4
+
+
+def test_gather_max_pool_broadcast_edge_ops():
+    d = dc().utils.synthetic_batch(3, 0, config=8, sizes=[90, 130, 64])
+    idx = og.knn_ell(d.pos, 9, d.batch)
+    g = dc().ops.knn(d.pos.to(DEV), 9, d.batch.to(DEV))
+    N, C = d.pos.size(0), 70
+    y0, g0 = torch.randn(N, C), torch.randn(N, C)
+    y = y0.to(DEV).requires_grad_(True)
+    out = dc().ops.gather_max(y, g)
+    (out * g0.to(DEV)).sum().backward()
+    yr = y0.double().requires_grad_(True)
+    outr = yr[idx].max(dim=1).values
+    (outr * g0.double()).sum().backward()
+    assert torch.equal(out.detach().cpu().double(), outr.detach()) and rel_err(y.grad.cpu(), yr.grad) < 1e-6
+    # edge differences + segment max (centralized first layer, deltaconv.py:50-52)
+    x = y0[:, :5].contiguous().to(DEV).requires_grad_(True)
+    e = dc().ops.edge_diff(x, g)
+    m = dc().ops.segment_max(e * 1.0, g)
+    (m * g0[:, :5].to(DEV)).sum().backward()
+    xr = y0[:, :5].double().requires_grad_(True)
+    er = (xr[idx] - xr[:, None]).reshape(N * 9, 5)
+    mr = er.reshape(N, 9, 5).max(dim=1).values
+    (mr * g0[:, :5].double()).sum().backward()
+    assert torch.equal(e.detach().cpu().double(), er.detach().float().double()) or rel_err(e.detach().cpu(), er.detach()) < 1e-6
+    assert rel_err(m.detach().cpu(), mr.detach()) < 1e-6 and rel_err(x.grad.cpu(), xr.grad) < 1e-5
+    # pools
+    batch = d.batch.to(DEV)
+    for mode in ('max', 'mean', 'maxmean'):
+        z = y0.to(DEV).requires_grad_(True)
+        p = dc().ops.pool(z, batch, mode)
+        gp = torch.randn(p.shape)
+        (p * gp.to(DEV)).sum().backward()
+        zr = y0.double().requires_grad_(True)
+        mx, mn = on._pool(zr, d.batch, 3, 'max'), on._pool(zr, d.batch, 3, 'mean')
+        pr = {'max': mx, 'mean': mn, 'maxmean': torch.cat([mx, mn], 1)}[mode]
+        (pr * gp.double()).sum().backward()
+        assert rel_err(p.detach().cpu(), pr.detach()) < 1e-6 and rel_err(z.grad.cpu(), zr.grad) < 1e-6
+    assert torch.equal(dc().geometry.global_max_pool(y0.to(DEV), batch).cpu(), on._pool(y0, d.batch, 3, 'max'))
+    # broadcast of per-cloud rows
+    s0 = torch.randn(3, 11)
+    s = s0.to(DEV).requires_grad_(True)
+    bc = dc().ops.broadcast_rows(s, batch, N)
+    gb = torch.randn(N, 11)
+    (bc * gb.to(DEV)).sum().backward()
+    assert torch.equal(bc.detach().cpu(), s0[d.batch])
+    assert rel_err(s.grad.cpu(), torch.zeros(3, 11).index_add(0, d.batch, gb)) < 1e-5
+
+
+# ----------------------------------------------------------------------------------------------
+# layers and networks against the reference's own outputs (golden) and the oracle
+# ----------------------------------------------------------------------------------------------
+
+def test_deltaconv_layers_vs_reference_golden():
+    g, z = load('layers_deltaconv')
+    D = dc()
+    pos, normal, batch, k = t(g.pos).to(DEV), t(g.normal).to(DEV), t(g.batch).to(DEV), int(g.k)
+    ei = D.geometry.knn_graph(pos, k, batch, loop=True, flow='target_to_source')
+    xb, yb = D.geometry.build_tangent_basis(normal)
+    grad, div = D.geometry.build_grad_div(pos, normal, xb, yb, ei, batch)
+    conv0 = D.utils.fill_deterministic(D.nn.DeltaConv(3, 16, depth=1, centralized=True, vector=True), 3).to(DEV)
+    conv1 = D.utils.fill_deterministic(D.nn.DeltaConv(16, 8, depth=2, centralized=False, vector=True), 4).to(DEV)
+    assert repr(conv0) == 'DeltaConv(3, 16)'
+    x_in = pos.clone().requires_grad_(True)
+    x1, v1 = conv0(x_in, grad @ x_in, grad, div, ei)
+    x2, v2 = conv1(x1, v1, grad, div, ei)
+    ((x2 * t(g.wx).to(DEV)).sum() + (v2 * t(g.wv).to(DEV)).sum()).backward()
+    for ours, key in ((x1, 'x1'), (v1, 'v1'), (x2, 'x2'), (v2, 'v2')):
+        assert rel_err(ours.detach().cpu(), t(z[f'ref64_{key}'])) < LOGIT_REL, key
+    assert rel_err(x_in.grad.cpu(), t(z['ref64_dx_in'])) < GRAD_REL
+    for cname, conv in (('conv0', conv0), ('conv1', conv1)):
+        for pname, p in conv.named_parameters():
+            key = f'ref64_grad.{cname}.{pname}'
+            if key in z.files:
+                assert rel_err(p.grad.cpu(), t(z[key])) < GRAD_REL, key
+            else:
+                assert p.grad is None, key
+        for bname, b in conv.named_buffers():
+            if 'running' in bname:
+                assert rel_err(b.cpu(), t(z[f'ref64_buf.{cname}.{bname}'])) < 1e-4, bname
+    # vector=False returns the input v object untouched (deltaconv.py:64-70, test_deltaconv.py:37-40)
+    conv2 = D.nn.DeltaConv(16, 8, vector=False).to(DEV)
+    _, v_same = conv2(x1.detach(), v1.detach(), grad, div, ei)
+    assert v_same.data_ptr() == v1.data_ptr()
+
+
+def _models(kind, k):
+    D = dc()
+    if kind == 'model_cls':
+        return D.models.DeltaNetClassification(3, 7, conv_channels=[16, 16, 32], num_neighbors=k)
+    if kind == 'model_cls_nonormal':
+        return D.models.DeltaNetClassification(3, 5, conv_channels=[8, 16], num_neighbors=k)
+    return D.models.DeltaNetSegmentation(3, 6, conv_channels=[8, 16, 16], mlp_depth=2, embedding_size=64,
+                                         categorical_vector=True, num_neighbors=k)
+
+
+@pytest.mark.parametrize('kind', ['model_cls', 'model_cls_nonormal', 'model_seg'])
+def test_models_vs_reference_golden(kind):
+    g, z = load(kind)
+    D = dc()
+    model = no_dropout(D.utils.fill_deterministic(_models(kind, int(g.k)), 2)).to(DEV)
+    data = D.utils.Data(pos=t(g.pos), batch=t(g.batch), y=t(g.y))
+    data.norm = t(g.normal) if 'normal' in z.files else None
+    if 'category' in z.files:
+        data.category = t(g.category)
+    data = data.to(DEV)
+    model.eval()
+    with torch.no_grad():
+        assert rel_err(model(data).cpu(), t(g.ref64_logits_eval)) < LOGIT_REL
+    model.train()
+    logits = model(data)
+    loss = F.cross_entropy(logits, data.y)
+    loss.backward()
+    assert rel_err(logits.detach().cpu(), t(g.ref64_logits_train)) < LOGIT_REL
+    assert abs(loss.item() - float(g.ref64_loss)) < LOGIT_REL * max(1.0, abs(float(g.ref64_loss)))
+    names = dict(model.named_parameters())
+    for key in z.files:
+        if key.startswith('ref64_gnorm.'):
+            p = names[key[len('ref64_gnorm.'):]]
+            ref = float(z[key])
+            assert p.grad is not None, key
+            assert abs(p.grad.norm().item() - ref) <= GRAD_REL * max(ref, 1e-6), key
+    for name, p in names.items():
+        if f'ref64_gnorm.{name}' not in z.files:
+            assert p.grad is None, name            # VectorNonLin.bias under BN
+
+
+def test_full_width_classifier_vs_oracle():
+    """The shipped architecture (convs [64,64,128,256], 2,045,928 parameters) on a 4 x 256 batch:
+    logits and loss against the fp64 oracle with identical weights, training-mode BN."""
+    D = dc()
+    data = D.utils.synthetic_batch(4, 256, config=2)
+    model = no_dropout(D.utils.fill_deterministic(D.models.DeltaNetClassification(3, 40), 1))
+    oracle = no_dropout(on.DeltaNetClassification(3, 40)).double()
+    oracle.load_state_dict({k_: (v_.double() if v_.is_floating_point() else v_) for k_, v_ in model.state_dict().items()})
+    model = model.to(DEV)
+    model.train()
+    oracle.train()
+    logits = model(data.to(DEV))
+    ref = oracle(data.double())
+    assert rel_err(logits.detach().cpu(), ref.detach()) < LOGIT_REL
+    on.smoothed_cross_entropy(ref, data.y).backward()
+    on.smoothed_cross_entropy(logits, data.y.to(DEV)).backward()
+    ref_grads = dict(oracle.named_parameters())
+    for name, p in model.named_parameters():
+        if ref_grads[name].grad is None:
+            assert p.grad is None, name
+            continue
+        assert rel_err(p.grad.cpu(), ref_grads[name].grad) < 5 * GRAD_REL, name
+    # state dicts stay interchangeable with the reference layout
+    assert set(model.state_dict()) == set(oracle.state_dict())
+
+
+# ----------------------------------------------------------------------------------------------
+# the reference's own property tests, run against the CUDA modules
+# ----------------------------------------------------------------------------------------------
+
+def test_vector_mlp_equivariance():
+    """MLP(T v) = T MLP(v) for per-point rotations/reflections T (reference: test/nn/test_mlp.py:42-78)."""
+    D = dc()
+    N, C = 500, 16
+    mlp = D.nn.VectorMLP([C, 32, 8]).to(DEV).eval()
+    v = torch.randn(2 * N, C, device=DEV)
+    ang = torch.rand(N, device=DEV) * 2 * torch.pi
+    refl = torch.where(torch.rand(N, device=DEV) < 0.5, -1.0, 1.0)
+    T = torch.stack([torch.cos(ang), -torch.sin(ang) * refl, torch.sin(ang), torch.cos(ang) * refl], 1).view(N, 2, 2)
+
+    def apply(Tm, field):
+        return torch.einsum('nab,nbc->nac', Tm, field.view(N, 2, -1)).reshape(2 * N, -1)
+    assert torch.allclose(mlp(apply(T, v)), apply(T, mlp(v)), atol=1e-5)
+
+
+def test_scalar_vector_mlp_conventions():
+    D = dc()
+    m = D.nn.ScalarVectorMLP([4, 8]).to(DEV)
+    x, v = torch.randn(50, 4, device=DEV), torch.randn(100, 4, device=DEV)
+    xo, vo = m((x, v))
+    assert xo.shape == (50, 8) and vo.shape == (100, 8)
+    with pytest.raises(AssertionError):
+        m(x)
+    m2 = D.nn.ScalarVectorMLP([4, 8], vector_stream=False).to(DEV)
+    assert m2(x).shape == (50, 8)
+    assert D.nn.ScalarVectorIdentity()((x, v))[0] is x
+    assert repr(D.nn.BatchNorm1d(8)) == 'BatchNorm1d(8)'
+    assert repr(D.nn.VectorNonLin(8, batchnorm=D.nn.BatchNorm1d(8))) == 'VectorNonLin(batchnorm=BatchNorm1d(8))'
+
+
+def test_coordinate_independence_of_weight_gradients():
+    """Same weight gradients with randomly rotated tangent frames (reference: test/nn/test_deltaconv.py:42-74)."""
+    D = dc()
+    torch.manual_seed(1)
+    N = 1000
+    x = torch.rand(N, 3, device=DEV)
+    ei = D.geometry.knn_graph(x, 20, loop=True, flow='target_to_source')
+    normal, xb, yb = D.geometry.estimate_basis(x, ei)
+    grad, div = D.geometry.build_grad_div(x, normal, xb, yb, ei, regularizer=1e-3)
+    xb_rot = D.geometry.rotate_around(xb, normal, torch.rand(N, device=DEV) * 2 * torch.pi)
+    yb_rot = torch.linalg.cross(normal, xb_rot, dim=-1)
+    grad_r, div_r = D.geometry.build_grad_div(x, normal, xb_rot, yb_rot, ei, regularizer=1e-3)
+    target = torch.rand(N, 1, device=DEV)
+    conv = D.nn.DeltaConv(3, 1, depth=1, centralized=False).to(DEV)
+    grads = []
+    for gr, dv in ((grad, div), (grad_r, div_r)):
+        conv.zero_grad()
+        conv2 = copy.deepcopy(conv)          # identical running stats for both passes
+        out, _ = conv2(x, gr @ x, gr, dv, ei)
+        F.l1_loss(out, target).backward()
+        grads.append(torch.cat([p.grad.flatten() for p in conv2.parameters() if p.grad is not None]))
+    assert torch.allclose(grads[0], grads[1], atol=1e-4)
+
+
+def test_cpu_tensors_fail_loudly():
+    D = dc()
+    with pytest.raises(D._lib.DeltaConvLibraryError):
+        D.geometry.build_tangent_basis(torch.randn(10, 3))
+    with pytest.raises(D._lib.DeltaConvLibraryError):
+        D.nn.Linear(4, 4)(torch.randn(3, 4))
