@@ -18,6 +18,8 @@ _P, _I, _L, _F, _Z = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_flo
 _SIGNATURES = {
     'dc_abi_version': [],
     'dc_device_sm_count': [],
+    'dc_launch_count': [],
+    'dc_reset_launch_count': [],
     'dc_cloud_ptr': [_P, _I, _I, _P, _P],
     'dc_knn': [_P, _P, _I, _I, _I, _P, _P, _P, _P],
     'dc_ell_from_edge_index': [_P, _I, _I, _P, _P],
@@ -57,7 +59,8 @@ _SIGNATURES = {
     'dc_expand_vec_weight': [_P, _I, _I, _P, _P],
     'dc_fold_vec_weight_grad': [_P, _I, _I, _P, _P],
 }
-_RESTYPES = {'dc_ell_transpose_ws_bytes': _Z, 'dc_build_ws_bytes': _Z, 'dc_colreduce_ws_bytes': _Z,
+_RESTYPES = {'dc_launch_count': ctypes.c_longlong, 'dc_reset_launch_count': None,
+             'dc_ell_transpose_ws_bytes': _Z, 'dc_build_ws_bytes': _Z, 'dc_colreduce_ws_bytes': _Z,
              'dc_gemm_ws_bytes': _Z}
 
 _lib = None
@@ -109,10 +112,18 @@ def check(t, dtype, name):
     return t
 
 
+PROFILER = None      # optional object with .begin(name, args) -> token and .end(token); see bench.py
+
+
 def call(name, *args):
     """Call an int-returning entry point on the current stream (appended as the last argument)."""
     lib = load()
-    rc = getattr(lib, name)(*args, stream_ptr())
+    if PROFILER is not None:
+        token = PROFILER.begin(name, args)
+        rc = getattr(lib, name)(*args, stream_ptr())
+        PROFILER.end(token)
+    else:
+        rc = getattr(lib, name)(*args, stream_ptr())
     if rc != 0:
         msg = lib.dc_last_error().decode(errors='replace')
         raise DeltaConvLibraryError(f"{name} failed (code {rc}): {msg}")

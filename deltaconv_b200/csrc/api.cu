@@ -2,6 +2,7 @@
 #include "common.cuh"
 #include <stdarg.h>
 #include <stdio.h>
+#include <atomic>
 
 static thread_local char g_err[512] = "";
 
@@ -12,7 +13,12 @@ void dc_set_error(const char* fmt, ...) {
     va_end(ap);
 }
 
-int dc_check_launch(const char* what) {
+static std::atomic<long long> g_launches{0};
+
+int dc_check_launch(const char* what) { return dc_check_launch_n(what, 1); }
+
+int dc_check_launch_n(const char* what, int n) {
+    g_launches += n;
     cudaError_t e = cudaGetLastError();
     if (e == cudaSuccess) return DC_OK;
     dc_set_error("%s: %s", what, cudaGetErrorString(e));
@@ -33,4 +39,7 @@ int dc_sm_count() {
 
 extern "C" const char* dc_last_error(void) { return g_err; }
 extern "C" int dc_abi_version(void) { return 1; }
+// kernels launched by this library since the last reset (bench.py reports it as gpu_launches)
+extern "C" long long dc_launch_count(void) { return g_launches.load(); }
+extern "C" void dc_reset_launch_count(void) { g_launches = 0; }
 extern "C" int dc_device_sm_count(void) { return dc_sm_count(); }

@@ -215,7 +215,7 @@ extern "C" int dc_build_grad_div(const float* pos, const float* normal, const fl
 
     edge_mean_kernel<<<dc_ceil_div((long long)N * 8, 256), 256, 0, st>>>(pos, idx, N, k, m);
     cloud_mean_kernel<<<B, 256, 0, st>>>(m, cloud_ptr, B, abar, S);
-    int rc = dc_check_launch("dc_build_grad_div/mean");
+    int rc = dc_check_launch_n("dc_build_grad_div/mean", 2);
     if (rc) return rc;
     // threads per CTA: as many as keep two CTAs resident per SM (<= ~110 KB of shared memory each)
     const size_t budget = 110 * 1024;

@@ -16,6 +16,8 @@
 void dc_set_error(const char* fmt, ...);
 // returns 0 or the pending cudaError_t (and records its string)
 int dc_check_launch(const char* what);
+// same, and adds n to the library's launch counter (dc_launch_count)
+int dc_check_launch_n(const char* what, int n);
 
 #define DC_REQUIRE(cond, ...)            \
     do {                                 \

@@ -128,7 +128,7 @@ int run_gemm(GemmArgs g, bool a_pc, bool b_jc, void* ws, size_t ws_bytes, cudaSt
         long long MN = (long long)g.M * g.N;
         splitk_reduce_kernel<<<dc_ceil_div(MN, 256), 256, 0, st>>>(g.partial, splits, MN, g.N, g.C, g.ldc, g.bias);
     }
-    return dc_check_launch("gemm");
+    return dc_check_launch_n("gemm", splits > 1 ? 2 : 1);
 }
 
 // W [Cout, 2K] = [W1 | W2]  ->  W' [2Cout, 2K] = [[W1, -W2], [W2, W1]]

@@ -6,6 +6,7 @@
 
 void dc_set_error(const char*, ...) {}
 int dc_check_launch(const char*) { return 0; }
+int dc_check_launch_n(const char*, int) { return 0; }
 int dc_sm_count() { return 0; }
 
 extern "C" void hc_knn_dist2(const float* q, const float* p, int n, float* out) {

@@ -466,7 +466,7 @@ extern "C" int dc_bn_stats(const float* x, int64_t ldx, int64_t M, int C, int mo
     else { NormVal f = {x, ldx}; col_reduce_kernel<2><<<grid, RED_T, 0, st>>>(f, M, C, L.col_lanes, L.rows_per_chunk, partial); }
     bn_finalize_kernel<<<dc_ceil_div(C, 128), 128, 0, st>>>(partial, L.chunks, M, C, eps, momentum, mean, invstd,
                                                             running_mean_or_null, running_var_or_null);
-    return dc_check_launch("dc_bn_stats");
+    return dc_check_launch_n("dc_bn_stats", 2);
 }
 
 // out[c] = sum_r x[r,c]  (bias gradients)
@@ -479,7 +479,7 @@ extern "C" int dc_col_sum(const float* x, int64_t ldx, int64_t M, int C, float* 
     SumVal f = {x, ldx};
     col_reduce_kernel<1><<<grid, RED_T, 0, st>>>(f, M, C, L.col_lanes, L.rows_per_chunk, (double*)ws);
     sum1_finalize_kernel<<<dc_ceil_div(C, 128), 128, 0, st>>>((double*)ws, L.chunks, C, out);
-    return dc_check_launch("dc_col_sum");
+    return dc_check_launch_n("dc_col_sum", 2);
 }
 
 extern "C" int dc_bn_act_fwd(const float* y, int64_t ldy, int64_t M, int C, const float* mean, const float* invstd,
@@ -507,7 +507,7 @@ extern "C" int dc_bn_act_bwd(const float* y, int64_t ldy, const float* dout, int
     sum2_finalize_kernel<<<dc_ceil_div(C, 128), 128, 0, st>>>(partial, L.chunks, C, d_beta, d_gamma);
     bn_act_bwd_kernel<<<elementwise_grid(M * C), 256, 0, st>>>(y, ldy, dout, ldd, M, C, mean, invstd, gamma_or_null, beta_or_null,
                                                                slope, d_beta, d_gamma, training, dy, ld_dy);
-    return dc_check_launch("dc_bn_act_bwd");
+    return dc_check_launch_n("dc_bn_act_bwd", 3);
 }
 
 extern "C" int dc_vecnonlin_fwd(const float* v, int64_t ldv, int64_t M, int C, const float* mean_or_null,
@@ -541,7 +541,7 @@ extern "C" int dc_vecnonlin_bwd(const float* v, int64_t ldv, const float* dout, 
     vecnonlin_bwd_kernel<<<elementwise_grid(M * C), 256, 0, st>>>(v, ldv, dout, ldd, M, C, mean_or_null, invstd_or_null, gamma_or_null,
                                                                   beta_or_null, bias_or_null, d_beta, d_gamma, training, dv, ld_dv,
                                                                   dbias_rows_or_null);
-    return dc_check_launch("dc_vecnonlin_bwd");
+    return dc_check_launch_n("dc_vecnonlin_bwd", mean_or_null ? 3 : 1);
 }
 
 extern "C" int dc_gathermax_fwd(const int32_t* idx, int N, int k, int C, const float* y, int64_t ldy, float* out, int64_t ldo,

@@ -277,7 +277,7 @@ extern "C" int dc_ell_transpose(const int32_t* idx, int N, int k, int32_t* in_pt
     scan_kernel<<<1, SCAN_T, 0, st>>>(cnt, N, in_ptr);
     fill_in_kernel<<<dc_ceil_div(E, 256), 256, 0, st>>>(idx, E, N, in_ptr, cursor, in_edge);
     sort_rows_kernel<<<dc_ceil_div(N, 128), 128, 0, st>>>(in_ptr, N, in_edge);
-    return dc_check_launch("dc_ell_transpose");
+    return dc_check_launch_n("dc_ell_transpose", 4);
 }
 
 extern "C" int dc_grad_fwd(const int32_t* idx, const float* G, int N, int k, int C, const float* x, int64_t ldx,

@@ -30,6 +30,9 @@ extern "C" {
 const char* dc_last_error(void);
 int dc_abi_version(void);
 int dc_device_sm_count(void);
+/* kernels launched by the library since the last reset */
+long long dc_launch_count(void);
+void dc_reset_launch_count(void);
 
 /* ---- graph ------------------------------------------------------------------------------- */
 

@@ -150,7 +150,7 @@ def model_case(name, kind):
         data = synthetic_batch(len(sizes), 0, config=cfg, sizes=sizes, num_classes=7)
         build = lambda: ref.models.DeltaNetClassification(3, 7, conv_channels=[16, 16, 32], num_neighbors=k)   # noqa: E731
     elif kind == 'cls_nonormal':
-        sizes, k, cfg = [120, 100], 12, 22
+        sizes, k, cfg = [120, 100, 90, 110], 12, 22      # >= 4 clouds: the head's BatchNorm runs over B rows
         data = synthetic_batch(len(sizes), 0, config=cfg, sizes=sizes, num_classes=5, normals=False)
         build = lambda: ref.models.DeltaNetClassification(3, 5, conv_channels=[8, 16], num_neighbors=k)       # noqa: E731
     else:

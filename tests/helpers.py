@@ -44,3 +44,15 @@ def check_frames(normal, xb, yb, tol=1e-5):
     assert (normal * yb).sum(1).abs().max() < tol
     assert (xb * yb).sum(1).abs().max() < tol
     assert (torch.linalg.cross(xb, yb, dim=-1) - normal).abs().max() < 10 * tol
+
+
+def report(name, value):
+    """Append a measured error to gpurun_out/parity_report.txt (margins, not just pass/fail)."""
+    out = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), 'gpurun_out')
+    try:
+        os.makedirs(out, exist_ok=True)
+        with open(os.path.join(out, 'parity_report.txt'), 'a') as f:
+            f.write(f'{name}\t{value:.3e}\n')
+    except OSError:
+        pass
+    return value

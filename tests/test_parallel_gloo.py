@@ -1,0 +1,66 @@
+"""CPU, world_size 2, gloo: cloud sharding and the flat-gradient all-reduce give the same
+parameter update as one process on the whole batch."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from deltaconv_b200.parallel import FlatGradients, shard_range
+
+
+def test_shard_range_partitions_everything():
+    for n in (0, 1, 7, 32, 33):
+        for w in (1, 2, 3, 8):
+            ranges = [shard_range(n, r, w) for r in range(w)]
+            assert ranges[0][0] == 0 and ranges[-1][1] == n
+            assert all(a[1] == b[0] for a, b in zip(ranges, ranges[1:]))
+            sizes = [e - b for b, e in ranges]
+            assert max(sizes) - min(sizes) <= 1
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(('127.0.0.1', 0))
+        return s.getsockname()[1]
+
+
+def _model():
+    torch.manual_seed(3)
+    m = torch.nn.Sequential(torch.nn.Linear(6, 5), torch.nn.Tanh(), torch.nn.Linear(5, 2))
+    m.extra = torch.nn.Parameter(torch.zeros(4))      # never used: grad slot must stay zero on every rank
+    return m
+
+
+def _worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR='127.0.0.1', MASTER_PORT=str(port))
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    torch.manual_seed(0)
+    x, y = torch.randn(8, 6), torch.randn(8, 2)
+    model = _model()
+    flat = FlatGradients(model.parameters())
+    b, e = shard_range(8, rank, world)
+    flat.zero()
+    loss = ((model(x[b:e]) - y[b:e]) ** 2).sum() / 8 * world      # local mean scaled so the rank-average is the global mean
+    loss.backward()
+    flat.all_reduce()
+    if rank == 0:
+        torch.save(flat.flat.clone(), out)
+    dist.destroy_process_group()
+
+
+@pytest.mark.timeout(120)
+def test_flat_gradient_allreduce_matches_single_process(tmp_path):
+    out = str(tmp_path / 'flat.pt')
+    mp.spawn(_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    got = torch.load(out)
+    torch.manual_seed(0)
+    x, y = torch.randn(8, 6), torch.randn(8, 2)
+    model = _model()
+    flat = FlatGradients(model.parameters())
+    (((model(x) - y) ** 2).sum() / 8).backward()
+    assert torch.allclose(got, flat.flat, atol=1e-6)
+    assert (model.extra.grad == 0).all() and (got[:4] == 0).all()      # `extra` is registered first
+    assert model[0].weight.grad.data_ptr() == flat.flat.data_ptr() + 16      # grads are views of the flat buffer
