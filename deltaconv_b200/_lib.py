@@ -30,6 +30,9 @@ _SIGNATURES = {
     'dc_estimate_basis': [_P, _P, _I, _I, _P, _P, _P, _P, _P],
     'dc_build_ws_bytes': [_I, _I],
     'dc_build_grad_div': [_P, _P, _P, _P, _P, _P, _I, _I, _I, _F, _F, _F, _I, _I, _P, _P, _P, _P, _P, _P, _Z, _P],
+    'dc_build_static_max_points': [],
+    'dc_build_static_max_clouds': [],
+    'dc_build_grad_div_static': [_P, _P, _P, _P, _P, _P, _I, _I, _I, _F, _F, _F, _I, _I, _P, _P, _P],
     'dc_grad_fwd': [_P, _P, _I, _I, _I, _P, _L, _P, _L, _P],
     'dc_grad_bwd': [_P, _P, _P, _I, _I, _I, _P, _L, _P, _L, _P],
     'dc_divcurlnorm_fwd': [_P, _P, _I, _I, _I, _P, _L, _P, _L, _P, _L, _P, _L, _P],

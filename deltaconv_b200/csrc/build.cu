@@ -231,3 +231,72 @@ extern "C" int dc_build_grad_div(const float* pos, const float* normal, const fl
     }
     return DC_OK;
 }
+
+// ================================================================================================
+// dc_build_grad_div_static — the operator build for callers that may not allocate device memory
+// ================================================================================================
+// Some hosts of this library cannot hand it a workspace: an inference server whose device memory is
+// carved up once at start-up and whose plugins are forbidden to allocate afterwards, or a
+// latency-critical loop in which cudaMalloc (which synchronises the device) is not acceptable and
+// no spare buffer was provisioned.  For them the scratch of the build (per-point mean edge length,
+// per-cloud mean, per-cloud infinity norm) lives in the fixed array below, which is part of the
+// library image: every GPU that loads the library holds these ~1.03 MB until the process exits.
+//
+// Limits: N <= DC_STATIC_MAX_POINTS points and B <= DC_STATIC_MAX_CLOUDS clouds per call; larger
+// batches are refused with an error (use dc_build_grad_div with a caller-provided workspace).
+//
+// Sharing: all calls on one GPU use the same array and it keeps whatever the previous call left.
+// Nothing needs to be cleared by the caller: the per-cloud maxima are reset by the kernels of each
+// call before they are accumulated, everything else is overwritten before it is read.  Because the
+// array is shared, two calls whose kernels can overlap on the GPU (different streams, no
+// dependency between them) race on it — serialise such calls.
+//
+// First call on each GPU: the array's device address is looked up once (cudaGetSymbolAddress, with
+// that GPU current) and cached.  Make that first call outside of any stream capture.
+#include <mutex>
+
+#define DC_STATIC_MAX_POINTS 262144
+#define DC_STATIC_MAX_CLOUDS 4096
+#define DC_STATIC_ALIGN(x) ((((size_t)(x)) + 255) / 256 * 256)
+#define DC_STATIC_SCRATCH_BYTES (DC_STATIC_ALIGN((size_t)DC_STATIC_MAX_POINTS * 4) + 2 * DC_STATIC_ALIGN((size_t)DC_STATIC_MAX_CLOUDS * 4))
+
+// In host code this name is only a handle for cudaGetSymbolAddress, never a device pointer.
+static __device__ __align__(256) unsigned char g_build_scratch[DC_STATIC_SCRATCH_BYTES];
+
+extern "C" int dc_build_static_max_points(void) { return DC_STATIC_MAX_POINTS; }
+extern "C" int dc_build_static_max_clouds(void) { return DC_STATIC_MAX_CLOUDS; }
+
+extern "C" int dc_build_grad_div_static(const float* pos, const float* normal, const float* xb, const float* yb,
+                                        const int32_t* idx, const int32_t* cloud_ptr, int B, int N, int k,
+                                        float kernel_width, float lam, float lam_shape, int use_shape, int normalized,
+                                        float* G, float* D, void* stream) {
+    DC_REQUIRE(N <= DC_STATIC_MAX_POINTS,
+               "dc_build_grad_div_static: %d points exceed the built-in scratch (max %d); use dc_build_grad_div with a workspace",
+               N, DC_STATIC_MAX_POINTS);
+    DC_REQUIRE(B <= DC_STATIC_MAX_CLOUDS,
+               "dc_build_grad_div_static: %d clouds exceed the built-in scratch (max %d); use dc_build_grad_div with a workspace",
+               B, DC_STATIC_MAX_CLOUDS);
+    DC_REQUIRE(dc_build_ws_bytes(N, B) <= DC_STATIC_SCRATCH_BYTES, "dc_build_grad_div_static: internal size mismatch");
+    constexpr int kMaxDevices = 64;
+    static std::mutex mu;
+    static void* scratch_of_device[kMaxDevices] = {nullptr};
+    int dev = -1;
+    DC_CUDA(cudaGetDevice(&dev));
+    DC_REQUIRE(dev >= 0 && dev < kMaxDevices, "dc_build_grad_div_static: device ordinal %d not supported", dev);
+    void* scratch = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        if (scratch_of_device[dev] == nullptr) {       // set-up, once per device, with that device current
+            void* p = nullptr;
+            cudaError_t e = cudaGetSymbolAddress(&p, g_build_scratch);
+            if (e != cudaSuccess || p == nullptr) {
+                dc_set_error("dc_build_grad_div_static: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+                return e != cudaSuccess ? (int)e : DC_EINVAL;
+            }
+            scratch_of_device[dev] = p;
+        }
+        scratch = scratch_of_device[dev];
+    }
+    return dc_build_grad_div(pos, normal, xb, yb, idx, cloud_ptr, B, N, k, kernel_width, lam, lam_shape, use_shape,
+                             normalized, G, D, nullptr, nullptr, nullptr, scratch, DC_STATIC_SCRATCH_BYTES, stream);
+}

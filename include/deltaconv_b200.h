@@ -76,6 +76,20 @@ int dc_build_grad_div(const float* pos, const float* normal, const float* xb, co
                       float* G, float* D, float* dbg_coords, float* dbg_weights, float* dbg_mapping,
                       void* ws, size_t ws_bytes, void* stream);
 
+/* Same build for callers that must not allocate device memory (a host whose memory is partitioned once
+ * at start-up, a loop that cannot afford cudaMalloc's device synchronisation): the scratch lives in a
+ * fixed array inside the library (~1.03 MB held by every GPU that loads it, until exit).  No counterpart
+ * in the reference.  Limits: N <= dc_build_static_max_points() (262144), B <= dc_build_static_max_clouds()
+ * (4096); larger batches return an error.  All calls on a GPU share the array: calls that can overlap on
+ * the GPU race; nothing has to be cleared between calls.  The first call on each GPU looks the array's
+ * address up (cudaGetSymbolAddress) — make it before any stream capture.  No debug outputs. */
+int dc_build_static_max_points(void);
+int dc_build_static_max_clouds(void);
+int dc_build_grad_div_static(const float* pos, const float* normal, const float* xb, const float* yb,
+                             const int32_t* idx, const int32_t* cloud_ptr, int B, int N, int k,
+                             float kernel_width, float lam, float lam_shape, int use_shape, int normalized,
+                             float* G, float* D, void* stream);
+
 /* ---- operator application (SparseTensor @ dense and operators.py) --------------------------- */
 
 /* grad @ x — deltanet_base.py:78, deltaconv.py:66:  out[2i+a,:] = sum_e G[i,e,a] x[idx[i,e],:] */
