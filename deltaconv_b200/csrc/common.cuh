@@ -38,6 +38,13 @@ int dc_check_launch_n(const char* what, int n);
 
 static inline int dc_ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
 
+// tensor-core GEMM (gemm_tc.cu): returns 0 when it ran, 1 when the shape/layout is not eligible (caller falls
+// back to the fp32 SIMT kernel), <0 on error; *launches = kernels launched
+int dc_tc_gemm(const float* A, long long lda, int a_mn, const float* B, long long ldb, int b_mn, const float* bias,
+               long long M, int N, long long K, float* C, long long ldc, void* ws, size_t ws_bytes, cudaStream_t st,
+               int* launches);
+size_t dc_tc_ws_bytes(long long M, long long N, long long K);
+
 // cached SM count of the current device (148 on B200)
 int dc_sm_count();
 

@@ -160,13 +160,20 @@ __global__ void fold_vec_weight_grad_kernel(const float* __restrict__ dWe, int C
 // split-K workspace for a product with output M x N and reduction length K (0 when no split is used)
 extern "C" size_t dc_gemm_ws_bytes(int64_t M, int64_t N, int64_t K) {
     int s = choose_splits((int)M, (int)N, (int)K);
-    return s > 1 ? (size_t)s * (size_t)M * (size_t)N * sizeof(float) : 0;
+    size_t simt = s > 1 ? (size_t)s * (size_t)M * (size_t)N * sizeof(float) : 0;
+    size_t tc = dc_tc_ws_bytes(M, N, K);
+    return simt > tc ? simt : tc;
 }
 
 // Y[M,Nout] = X[M,K] W[Nout,K]^T (+ bias)              — torch.nn.Linear forward
 extern "C" int dc_linear_fwd(const float* X, int64_t ldx, const float* W, int64_t ldw, const float* bias_or_null,
                              int64_t M, int K, int Nout, float* Y, int64_t ldy, void* ws, size_t ws_bytes, void* stream) {
     DC_REQUIRE(M < 2147483647LL, "dc_linear_fwd: M must fit in int32");
+    {
+        int n = 0;
+        int rc = dc_tc_gemm(X, ldx, 0, W, ldw, 0, bias_or_null, M, Nout, K, Y, ldy, ws, ws_bytes, (cudaStream_t)stream, &n);
+        if (rc <= 0) return rc < 0 ? rc : dc_check_launch_n("dc_linear_fwd/tc", n);
+    }
     GemmArgs g = {};
     g.A = X; g.sa_i = ldx; g.sa_p = 1;
     g.B = W; g.sb_p = 1; g.sb_j = ldw;
@@ -178,6 +185,11 @@ extern "C" int dc_linear_fwd(const float* X, int64_t ldx, const float* W, int64_
 extern "C" int dc_linear_bwd_input(const float* dY, int64_t ld_dy, const float* W, int64_t ldw, int64_t M, int K, int Nout,
                                    float* dX, int64_t ld_dx, void* ws, size_t ws_bytes, void* stream) {
     DC_REQUIRE(M < 2147483647LL, "dc_linear_bwd_input: M must fit in int32");
+    {   // A = dY (reduction over Nout, contiguous); B = W stored [Nout, K] i.e. reduction rows, output index contiguous
+        int n = 0;
+        int rc = dc_tc_gemm(dY, ld_dy, 0, W, ldw, 1, nullptr, M, K, Nout, dX, ld_dx, ws, ws_bytes, (cudaStream_t)stream, &n);
+        if (rc <= 0) return rc < 0 ? rc : dc_check_launch_n("dc_linear_bwd_input/tc", n);
+    }
     GemmArgs g = {};
     g.A = dY; g.sa_i = ld_dy; g.sa_p = 1;
     g.B = W; g.sb_p = ldw; g.sb_j = 1;
@@ -189,6 +201,11 @@ extern "C" int dc_linear_bwd_input(const float* dY, int64_t ld_dy, const float* 
 extern "C" int dc_linear_bwd_weight(const float* dY, int64_t ld_dy, const float* X, int64_t ldx, int64_t M, int K, int Nout,
                                     float* dW, int64_t ld_dw, void* ws, size_t ws_bytes, void* stream) {
     DC_REQUIRE(M < 2147483647LL, "dc_linear_bwd_weight: M must fit in int32");
+    {   // reduction over the M rows: both operands have their output index contiguous (MN-major)
+        int n = 0;
+        int rc = dc_tc_gemm(dY, ld_dy, 1, X, ldx, 1, nullptr, Nout, K, M, dW, ld_dw, ws, ws_bytes, (cudaStream_t)stream, &n);
+        if (rc <= 0) return rc < 0 ? rc : dc_check_launch_n("dc_linear_bwd_weight/tc", n);
+    }
     GemmArgs g = {};
     g.A = dY; g.sa_i = 1; g.sa_p = ld_dy;
     g.B = X; g.sb_p = ldx; g.sb_j = 1;

@@ -1,0 +1,424 @@
+// K9 — tensor-core GEMM for the per-point channel mixing on sm_100a: tcgen05.mma (kind::tf32) issued
+// by one thread, operands staged in shared memory by TMA (128-byte swizzle), accumulators in TMEM.
+//
+//   C[m, n] = sum_k A(m, k) * B(n, k)        fp32 in HBM on both sides, fp32 accumulation
+//
+// Accuracy.  The reference computes its Linears in fp32 and the parity bound on logits is 1e-4, so
+// the default mode is a 3xTF32 split: x = hi + lo with hi = x & 0xffffe000 (exactly representable in
+// TF32) and lo = x - hi, and  A B ~= A_hi B_hi + A_lo B_hi + A_hi B_lo  (the dropped lo*lo term is
+// 2^-22 relative).  Four "converter" warps split every landed stage in shared memory (hi in place, lo
+// into a second buffer) before the MMA warp consumes it.  SPLIT3 = false gives plain TF32 (1 MMA).
+//
+// Operand layouts.  "K-major": the reduction index is contiguous in HBM (X[M,K], W[N,K]); the smem
+// tile is rows x 128 B.  "MN-major": the M/N index is contiguous (dY[M,Nout] and X[M,K] reduced over
+// rows for the weight gradient; W[Nout,K] for the input gradient); the tile is fetched as 32-wide
+// column chunks, each chunk 32 reduction rows x 128 B.  Both are canonical UMMA SWIZZLE_128B layouts,
+// so no transposed copy of any activation is ever made.
+//
+// Roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer,
+// warps 2..5 = converters, then epilogue (TMEM -> registers -> HBM; warp w owns TMEM lanes 32*(w%4)..).
+#include "common.cuh"
+#include <cuda.h>
+
+namespace {
+
+constexpr int TC_BM = 128;          // UMMA_M (cta_group::1)
+constexpr int TC_BK = 32;           // fp32 elements per k-block = one 128-byte swizzle span
+constexpr int TC_THREADS = 192;
+constexpr int TC_MAX_STAGES = 4;
+
+struct TcArgs {
+    float* C; long long ldc;
+    const float* bias;
+    int M, N, K;
+    int kb_per_split;       // k-blocks per grid.z slice
+    float* partial;         // [splits][M][N] when split-K
+    int stages;
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done;
+    long long t0 = 0;
+    do {
+        asm volatile(
+            "{\n\t"
+            ".reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t"
+            "}" : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+        if (!done) {                       // watchdog: a protocol bug must fault, not hang the GPU
+            if (t0 == 0) t0 = clock64();
+            else if (clock64() - t0 > 4000000000LL) __trap();
+        }
+    } while (!done);
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// UMMA shared-memory descriptor, SWIZZLE_128B (cute::UMMA::SmemDescriptor: start>>4 [0,14), LBO>>4 [16,30),
+// SBO>>4 [32,46), version=1 [46,48), layout_type=2 [61,64))
+// layout_type: 2 = SWIZZLE_128B (16-byte chunks XOR row%8; K-major tiles),
+//              1 = SWIZZLE_128B_BASE32B (32-byte chunks XOR row%4) — the only layout UMMA accepts for MN-major tf32
+//                  operands (cutlass sm100_common.inl:92); TMA writes it with CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B.
+__device__ __forceinline__ uint64_t umma_desc(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout_type) {
+    return (uint64_t)((addr >> 4) & 0x3FFF) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16) |
+           ((uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32) | (1ull << 46) | ((uint64_t)layout_type << 61);
+}
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_c, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+        "}" ::"r"(tmem_c), "l"(da), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+
+template <int BN, bool A_MN, bool B_MN, bool SPLIT3>
+__global__ void __launch_bounds__(TC_THREADS) tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                             const __grid_constant__ CUtensorMap tmB, TcArgs g) {
+    constexpr uint32_t A_BYTES = TC_BM * 128, B_BYTES = BN * 128;
+    constexpr uint32_t STAGE_BYTES = (A_BYTES + B_BYTES) * (SPLIT3 ? 2 : 1);
+    constexpr uint32_t CHUNK_BYTES = TC_BK * 128;                 // one 32-wide MN chunk of an MN-major tile
+    constexpr uint32_t TMEM_COLS = BN <= 32 ? 32 : BN <= 64 ? 64 : BN <= 128 ? 128 : 256;
+    // instruction descriptor (cute::UMMA::InstrDescriptor): c=F32, a=b=TF32, majors, N>>3, M>>4
+    constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
+                               ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
+
+    extern __shared__ unsigned char smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;          // SWIZZLE_128B atoms are 1024-byte aligned
+    unsigned char* base_ptr = smem_raw + (base - smem_u32(smem_raw));
+    const int stages = g.stages;
+    // barriers and the TMEM base live after the stage buffers
+    const uint32_t bar_base = base + stages * STAGE_BYTES;
+    auto full_bar = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar = [&](int s) { return bar_base + 8u * (TC_MAX_STAGES + s); };
+    auto conv_bar = [&](int s) { return bar_base + 8u * (2 * TC_MAX_STAGES + s); };
+    const uint32_t accum_bar = bar_base + 8u * (3 * TC_MAX_STAGES);
+    const uint32_t tmem_slot = accum_bar + 8u;
+    volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(base_ptr + (tmem_slot - base));
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n0 = blockIdx.x * BN, m0 = blockIdx.y * TC_BM;
+    const int total_kb = (g.K + TC_BK - 1) / TC_BK;
+    const int kb_begin = blockIdx.z * g.kb_per_split;
+    const int nkb = min(total_kb, kb_begin + g.kb_per_split) - kb_begin;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < stages; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); mbar_init(conv_bar(s), 4); }
+        mbar_init(accum_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot_ptr;
+
+    auto stage_a = [&](int s) { return base + s * STAGE_BYTES; };
+    auto stage_a_lo = [&](int s) { return base + s * STAGE_BYTES + A_BYTES; };
+    auto stage_b = [&](int s) { return base + s * STAGE_BYTES + (SPLIT3 ? 2 : 1) * A_BYTES; };
+    auto stage_b_lo = [&](int s) { return base + s * STAGE_BYTES + 2 * A_BYTES + B_BYTES; };
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
+            asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
+            for (int it = 0; it < nkb; ++it) {
+                const int s = it % stages;
+                const uint32_t ph = (it / stages) & 1;
+                mbar_wait(empty_bar(s), ph ^ 1u);
+                mbar_expect_tx(full_bar(s), A_BYTES + B_BYTES);
+                const int k0 = (kb_begin + it) * TC_BK;
+                if (!A_MN) tma_load_2d(stage_a(s), &tmA, full_bar(s), k0, m0);
+                else
+#pragma unroll
+                    for (int c = 0; c < TC_BM / 32; ++c) tma_load_2d(stage_a(s) + c * CHUNK_BYTES, &tmA, full_bar(s), m0 + 32 * c, k0);
+                if (!B_MN) tma_load_2d(stage_b(s), &tmB, full_bar(s), k0, n0);
+                else
+#pragma unroll
+                    for (int c = 0; c < BN / 32; ++c) tma_load_2d(stage_b(s) + c * CHUNK_BYTES, &tmB, full_bar(s), n0 + 32 * c, k0);
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        for (int it = 0; it < nkb; ++it) {
+            const int s = it % stages;
+            const uint32_t ph = (it / stages) & 1;
+            mbar_wait(SPLIT3 ? conv_bar(s) : full_bar(s), ph);
+            tc_fence_after();
+            if (lane == 0) {
+#pragma unroll
+                for (int kk = 0; kk < TC_BK / 8; ++kk) {          // UMMA_K = 8 for tf32
+                    // K-major: +32 B inside the swizzle span; MN-major: next 8-row group (+1024 B)
+                    const uint32_t a_off = A_MN ? kk * 1024u : kk * 32u, b_off = B_MN ? kk * 1024u : kk * 32u;
+                    // K-major: 8-row groups 1024 B apart.  MN-major: 32-wide chunks CHUNK_BYTES apart (LBO),
+                    // 4-row groups of the 32-byte-atom swizzle 512 B apart (SBO).
+                    const uint32_t a_lbo = A_MN ? CHUNK_BYTES : 16u, b_lbo = B_MN ? CHUNK_BYTES : 16u;
+                    const uint32_t a_sbo = A_MN ? 512u : 1024u, b_sbo = B_MN ? 512u : 1024u;
+                    const uint32_t a_lt = A_MN ? 1u : 2u, b_lt = B_MN ? 1u : 2u;
+                    const uint64_t da = umma_desc(stage_a(s) + a_off, a_lbo, a_sbo, a_lt);
+                    const uint64_t db = umma_desc(stage_b(s) + b_off, b_lbo, b_sbo, b_lt);
+                    umma_tf32(tmem_base, da, db, IDESC, (it > 0 || kk > 0) ? 1u : 0u);
+                    if (SPLIT3) {
+                        const uint64_t da_lo = umma_desc(stage_a_lo(s) + a_off, a_lbo, a_sbo, a_lt);
+                        const uint64_t db_lo = umma_desc(stage_b_lo(s) + b_off, b_lbo, b_sbo, b_lt);
+                        umma_tf32(tmem_base, da_lo, db, IDESC, 1u);
+                        umma_tf32(tmem_base, da, db_lo, IDESC, 1u);
+                    }
+                }
+                umma_commit(empty_bar(s));                        // frees the stage when the MMAs have read it
+                if (it == nkb - 1) umma_commit(accum_bar);        // accumulator complete
+            }
+            __syncwarp();
+        }
+    } else {
+        // ===================== converters, then epilogue =====================
+        const int t = threadIdx.x - 64;                           // 0..127
+        if (SPLIT3) {
+            for (int it = 0; it < nkb; ++it) {
+                const int s = it % stages;
+                const uint32_t ph = (it / stages) & 1;
+                mbar_wait(full_bar(s), ph);
+                float4* a_hi = reinterpret_cast<float4*>(base_ptr + (stage_a(s) - base));
+                float4* a_lo = reinterpret_cast<float4*>(base_ptr + (stage_a_lo(s) - base));
+                float4* b_hi = reinterpret_cast<float4*>(base_ptr + (stage_b(s) - base));
+                float4* b_lo = reinterpret_cast<float4*>(base_ptr + (stage_b_lo(s) - base));
+                auto split = [](float4* hi, float4* lo, int i) {
+                    float4 x = hi[i], h, l;
+                    h.x = __uint_as_float(__float_as_uint(x.x) & 0xffffe000u); l.x = x.x - h.x;
+                    h.y = __uint_as_float(__float_as_uint(x.y) & 0xffffe000u); l.y = x.y - h.y;
+                    h.z = __uint_as_float(__float_as_uint(x.z) & 0xffffe000u); l.z = x.z - h.z;
+                    h.w = __uint_as_float(__float_as_uint(x.w) & 0xffffe000u); l.w = x.w - h.w;
+                    hi[i] = h; lo[i] = l;
+                };
+#pragma unroll
+                for (int i = 0; i < (int)(A_BYTES / 16) / 128; ++i) split(a_hi, a_lo, t + 128 * i);
+#pragma unroll
+                for (int i = 0; i < (int)(B_BYTES / 16) / 128; ++i) split(b_hi, b_lo, t + 128 * i);
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // generic writes -> visible to the MMA (async proxy)
+                __syncwarp();
+                if (lane == 0) mbar_arrive(conv_bar(s));
+            }
+        }
+        mbar_wait(accum_bar, 0);
+        tc_fence_after();
+        const int q = warp & 3;                                   // TMEM lane quarter this warp may read
+        const int row = m0 + q * 32 + lane;
+        float* out = g.partial ? g.partial + (size_t)blockIdx.z * g.M * g.N : g.C;
+        const long long ldo = g.partial ? g.N : g.ldc;
+        const bool vec_ok = (ldo % 4 == 0) && ((reinterpret_cast<uintptr_t>(out) & 15u) == 0);
+#pragma unroll 1
+        for (int c0 = 0; c0 < BN; c0 += 16) {
+            if (n0 + c0 >= g.N) break;                            // warp-uniform
+            uint32_t r[16];
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0;
+            asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+                         : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                           "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+                         : "r"(taddr));
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            if (row < g.M) {
+                float* dst = out + (long long)row * ldo + n0 + c0;
+#pragma unroll
+                for (int v = 0; v < 4; ++v) {
+                    const int col = n0 + c0 + 4 * v;
+                    float4 o = make_float4(__uint_as_float(r[4 * v]), __uint_as_float(r[4 * v + 1]), __uint_as_float(r[4 * v + 2]), __uint_as_float(r[4 * v + 3]));
+                    if (!g.partial && g.bias) {
+                        if (col < g.N) o.x += __ldg(g.bias + col);
+                        if (col + 1 < g.N) o.y += __ldg(g.bias + col + 1);
+                        if (col + 2 < g.N) o.z += __ldg(g.bias + col + 2);
+                        if (col + 3 < g.N) o.w += __ldg(g.bias + col + 3);
+                    }
+                    if (vec_ok && col + 3 < g.N) *reinterpret_cast<float4*>(dst + 4 * v) = o;
+                    else {
+                        if (col < g.N) dst[4 * v] = o.x;
+                        if (col + 1 < g.N) dst[4 * v + 1] = o.y;
+                        if (col + 2 < g.N) dst[4 * v + 2] = o.z;
+                        if (col + 3 < g.N) dst[4 * v + 3] = o.w;
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
+}
+
+__global__ void tc_splitk_reduce_kernel(const float* __restrict__ partial, int splits, long long MN, int N, float* __restrict__ C,
+                                        long long ldc, const float* __restrict__ bias) {
+    long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (t >= MN) return;
+    float s = 0.f;
+    for (int z = 0; z < splits; ++z) s += partial[(size_t)z * MN + t];          // fixed order: deterministic
+    long long i = t / N; int j = (int)(t - i * N);
+    if (bias) s += __ldg(bias + j);
+    C[i * ldc + j] = s;
+}
+
+// ---- host side ------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+            fn = (EncodeTiledFn)p;
+    }
+    return fn;
+}
+
+// 2-D fp32 tensor map: inner (contiguous) extent x outer extent with row pitch ld elements; 128-byte swizzle;
+// out-of-bounds elements read as zero (that is what pads ragged M / N / K edges).
+bool make_map(CUtensorMap* map, const float* ptr, long long inner, long long outer, long long ld, int box_outer, bool mn_major) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) return false;
+    cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
+    cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
+    cuuint32_t box[2] = {32u, (cuuint32_t)box_outer};
+    cuuint32_t estr[2] = {1u, 1u};
+    return fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+              mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+size_t tc_smem_bytes(int BN, bool split3, int stages) {
+    return (size_t)stages * (TC_BM + BN) * 128 * (split3 ? 2 : 1) + 1024 /*alignment*/ + 8 * (3 * TC_MAX_STAGES + 2) + 16;
+}
+
+template <int BN, bool A_MN, bool B_MN, bool SPLIT3>
+int launch_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, TcArgs g, dim3 grid, cudaStream_t st) {
+    // as many stages as fit while keeping two CTAs per SM when the tile is small
+    const size_t per_stage = (size_t)(TC_BM + BN) * 128 * (SPLIT3 ? 2 : 1);
+    int stages = per_stage <= 49152 ? 2 : (int)((200 * 1024) / per_stage);
+    if (stages > TC_MAX_STAGES) stages = TC_MAX_STAGES;
+    if (stages < 2) stages = 2;
+    g.stages = stages;
+    const size_t smem = tc_smem_bytes(BN, SPLIT3, stages);
+    DC_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<BN, A_MN, B_MN, SPLIT3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    tc_gemm_kernel<BN, A_MN, B_MN, SPLIT3><<<grid, TC_THREADS, smem, st>>>(tmA, tmB, g);
+    return DC_OK;
+}
+
+template <bool A_MN, bool B_MN>
+int dispatch_tc(int BN, bool split3, const CUtensorMap& a, const CUtensorMap& b, const TcArgs& g, dim3 grid, cudaStream_t st) {
+    if (split3) {
+        if (BN == 64) return launch_tc<64, A_MN, B_MN, true>(a, b, g, grid, st);
+        if (BN == 128) return launch_tc<128, A_MN, B_MN, true>(a, b, g, grid, st);
+        return launch_tc<256, A_MN, B_MN, true>(a, b, g, grid, st);
+    }
+    if (BN == 64) return launch_tc<64, A_MN, B_MN, false>(a, b, g, grid, st);
+    if (BN == 128) return launch_tc<128, A_MN, B_MN, false>(a, b, g, grid, st);
+    return launch_tc<256, A_MN, B_MN, false>(a, b, g, grid, st);
+}
+
+}  // namespace
+
+// Precision mode of the tensor-core path: 0 = off (fp32 SIMT everywhere), 1 = TF32, 3 = 3xTF32 (default).
+static int g_tc_mode = 3;
+extern "C" int dc_set_gemm_mode(int mode) {
+    DC_REQUIRE(mode == 0 || mode == 1 || mode == 3, "dc_set_gemm_mode: mode must be 0 (fp32 SIMT), 1 (TF32) or 3 (3xTF32)");
+    g_tc_mode = mode;
+    return DC_OK;
+}
+extern "C" int dc_get_gemm_mode(void) { return g_tc_mode; }
+
+// Generic tensor-core product  C[M,N] = op(A) op(B)^T (+bias).  a_mn / b_mn select the operand layout:
+//   a_mn = 0: A is [M, K] with K contiguous (lda = row pitch);  a_mn = 1: A is stored [K, M] with M contiguous.
+//   b_mn = 0: B is [N, K] with K contiguous;                    b_mn = 1: B is stored [K, N] with N contiguous.
+// Returns 1 (not an error) when the shape is not eligible, so the caller can use the SIMT kernel.
+int dc_tc_gemm(const float* A, long long lda, int a_mn, const float* B, long long ldb, int b_mn, const float* bias,
+               long long M, int N, long long K, float* C, long long ldc, void* ws, size_t ws_bytes, cudaStream_t st,
+               int* launches) {
+    *launches = 0;
+    if (g_tc_mode == 0 || M < 64 || N < 16 || K < 8) return 1;
+    if (lda % 4 || ldb % 4 || (reinterpret_cast<uintptr_t>(A) & 15u) || (reinterpret_cast<uintptr_t>(B) & 15u)) return 1;
+    if (M >= 2147483647LL || K >= 2147483647LL) return 1;
+    const int BN = N <= 64 ? 64 : N <= 128 ? 128 : 256;
+    CUtensorMap tmA, tmB;
+    bool ok = a_mn ? make_map(&tmA, A, M, K, lda, TC_BK, true) : make_map(&tmA, A, K, M, lda, TC_BM, false);
+    ok = ok && (b_mn ? make_map(&tmB, B, N, K, ldb, TC_BK, true) : make_map(&tmB, B, K, N, ldb, BN, false));
+    if (!ok) return 1;
+    const int total_kb = (int)((K + TC_BK - 1) / TC_BK);
+    const long long tiles = ((M + TC_BM - 1) / TC_BM) * ((N + BN - 1) / BN);
+    int splits = 1;
+    const long long target = 2LL * dc_sm_count();
+    if (tiles < target && total_kb >= 8) {
+        long long s = (target + tiles - 1) / tiles;
+        if (s > total_kb / 4) s = total_kb / 4;
+        while (s > 1 && (size_t)s * M * N * sizeof(float) > ws_bytes) --s;
+        splits = (int)(s < 1 ? 1 : s);
+    }
+    TcArgs g = {};
+    g.C = C; g.ldc = ldc; g.bias = bias; g.M = (int)M; g.N = N; g.K = (int)K;
+    g.kb_per_split = (total_kb + splits - 1) / splits;
+    splits = (total_kb + g.kb_per_split - 1) / g.kb_per_split;
+    g.partial = splits > 1 ? (float*)ws : nullptr;
+    dim3 grid((unsigned)((N + BN - 1) / BN), (unsigned)((M + TC_BM - 1) / TC_BM), (unsigned)splits);
+    if (grid.y > 65535u) return 1;
+    const bool split3 = g_tc_mode == 3;
+    int rc;
+    if (!a_mn && !b_mn) rc = dispatch_tc<false, false>(BN, split3, tmA, tmB, g, grid, st);
+    else if (!a_mn && b_mn) rc = dispatch_tc<false, true>(BN, split3, tmA, tmB, g, grid, st);
+    else if (a_mn && b_mn) rc = dispatch_tc<true, true>(BN, split3, tmA, tmB, g, grid, st);
+    else return 1;
+    if (rc) return rc < 0 ? rc : -rc;
+    *launches = 1;
+    if (splits > 1) {
+        const long long MN = M * N;
+        tc_splitk_reduce_kernel<<<dc_ceil_div(MN, 256), 256, 0, st>>>(g.partial, splits, MN, N, C, ldc, bias);
+        *launches = 2;
+    }
+    return DC_OK;
+}
+
+// workspace for the split-K partials of a product with output M x N and reduction K
+size_t dc_tc_ws_bytes(long long M, long long N, long long K) {
+    const int BN = N <= 64 ? 64 : N <= 128 ? 128 : 256;
+    const long long total_kb = (K + TC_BK - 1) / TC_BK;
+    const long long tiles = ((M + TC_BM - 1) / TC_BM) * ((N + BN - 1) / BN);
+    const long long target = 2LL * dc_sm_count();
+    if (tiles >= target || total_kb < 8) return 0;
+    long long s = (target + tiles - 1) / tiles;
+    if (s > total_kb / 4) s = total_kb / 4;
+    return s > 1 ? (size_t)s * M * N * sizeof(float) : 0;
+}
+
+// Raw access to the tensor-core product for tests and experiments (no SIMT fallback: returns 1 when the
+// shape is not eligible).  Layout flags as in dc_tc_gemm above.
+extern "C" int dc_gemm_tc_raw(const float* A, int64_t lda, int a_mn, const float* B, int64_t ldb, int b_mn,
+                              const float* bias_or_null, int64_t M, int N, int64_t K, float* C, int64_t ldc,
+                              void* ws, size_t ws_bytes, void* stream) {
+    int n = 0;
+    int rc = dc_tc_gemm(A, lda, a_mn, B, ldb, b_mn, bias_or_null, M, N, K, C, ldc, ws, ws_bytes, (cudaStream_t)stream, &n);
+    if (rc == 1) { dc_set_error("dc_gemm_tc_raw: shape/layout not eligible for the tensor-core kernel"); return 1; }
+    if (rc) return rc;
+    return dc_check_launch_n("dc_gemm_tc_raw", n);
+}

@@ -33,7 +33,7 @@ ColLayout col_layout(long long M, int C) {
     L.col_lanes = cl;
     L.row_lanes = RED_T / cl;
     L.col_blocks = (C + cl - 1) / cl;
-    long long want = (long long)dc_sm_count() * 8 / L.col_blocks;
+    long long want = (long long)dc_sm_count() * 4 / L.col_blocks;
     if (want < 1) want = 1;
     long long by_rows = (M + L.row_lanes * 4 - 1) / (L.row_lanes * 4);   // at least 4 rows per thread
     if (by_rows < 1) by_rows = 1;
@@ -76,16 +76,45 @@ __global__ void __launch_bounds__(RED_T) col_reduce_kernel(F f, long long M, int
     }
 }
 
+
+// Sum partial[q][v][c] over the chunks q for one column c and value v.  A CTA of 256 threads
+// owns 32 columns: lane = column, the 8 warps stride over the chunks (coalesced 256-byte rows),
+// then the 8 per-warp sums are added in a fixed order -> deterministic.
+constexpr int FIN_T = 256;
+template <int NV>
+__device__ __forceinline__ bool finalize_sums(const double* __restrict__ partial, int chunks, int C, double (&out)[NV]) {
+    __shared__ double sh[NV][8][33];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int c = blockIdx.x * 32 + lane;
+    double acc[NV];
+#pragma unroll
+    for (int v = 0; v < NV; ++v) acc[v] = 0.0;
+    if (c < C)
+        for (int q = w; q < chunks; q += 8)
+#pragma unroll
+            for (int v = 0; v < NV; ++v) acc[v] += partial[((size_t)q * NV + v) * C + c];
+#pragma unroll
+    for (int v = 0; v < NV; ++v) sh[v][w][lane] = acc[v];
+    __syncthreads();
+    if (w != 0 || c >= C) return false;
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+        double s = 0.0;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) s += sh[v][q][lane];
+        out[v] = s;
+    }
+    return true;
+}
+
 struct SumVal {        // plain column sums of a [M,C] matrix
     const float* x; long long ld;
     __device__ void operator()(long long r, int c, float (&o)[1]) const { o[0] = __ldg(x + r * ld + c); }
 };
 __global__ void sum1_finalize_kernel(const double* __restrict__ partial, int chunks, int C, float* __restrict__ s0) {
-    int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= C) return;
-    double a = 0.0;
-    for (int q = 0; q < chunks; ++q) a += partial[(size_t)q * C + c];
-    s0[c] = (float)a;
+    double r[1];
+    if (!finalize_sums<1>(partial, chunks, C, r)) return;
+    s0[blockIdx.x * 32 + (threadIdx.x & 31)] = (float)r[0];
 }
 
 // ---- BatchNorm statistics ------------------------------------------------------------------
@@ -107,10 +136,10 @@ struct NormVal {       // |v| and |v|^2 of a [2M,C] vector field (nonlin.py:68)
 __global__ void bn_finalize_kernel(const double* __restrict__ partial, int chunks, long long M, int C, float eps,
                                    float momentum, float* __restrict__ mean, float* __restrict__ invstd,
                                    float* __restrict__ running_mean, float* __restrict__ running_var) {
-    int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= C) return;
-    double s = 0.0, s2 = 0.0;
-    for (int q = 0; q < chunks; ++q) { s += partial[((size_t)q * 2) * C + c]; s2 += partial[((size_t)q * 2 + 1) * C + c]; }
+    double r[2];
+    if (!finalize_sums<2>(partial, chunks, C, r)) return;
+    const int c = blockIdx.x * 32 + (threadIdx.x & 31);
+    double s = r[0], s2 = r[1];
     double mu = s / (double)M;
     double var = s2 / (double)M - mu * mu;
     if (var < 0.0) var = 0.0;
@@ -154,11 +183,10 @@ struct BnBwdVal {
 };
 
 __global__ void sum2_finalize_kernel(const double* __restrict__ partial, int chunks, int C, float* __restrict__ s0, float* __restrict__ s1) {
-    int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= C) return;
-    double a = 0.0, b = 0.0;
-    for (int q = 0; q < chunks; ++q) { a += partial[((size_t)q * 2) * C + c]; b += partial[((size_t)q * 2 + 1) * C + c]; }
-    s0[c] = (float)a; s1[c] = (float)b;
+    double r[2];
+    if (!finalize_sums<2>(partial, chunks, C, r)) return;
+    const int c = blockIdx.x * 32 + (threadIdx.x & 31);
+    s0[c] = (float)r[0]; s1[c] = (float)r[1];
 }
 
 // backward, elementwise part: dy = gamma * invstd * (dz - sum_dz/M - xhat * sum_dz_xhat/M)   (training)
@@ -464,7 +492,7 @@ extern "C" int dc_bn_stats(const float* x, int64_t ldx, int64_t M, int C, int mo
     double* partial = (double*)ws;
     if (mode == 0) { PlainVal f = {x, ldx}; col_reduce_kernel<2><<<grid, RED_T, 0, st>>>(f, M, C, L.col_lanes, L.rows_per_chunk, partial); }
     else { NormVal f = {x, ldx}; col_reduce_kernel<2><<<grid, RED_T, 0, st>>>(f, M, C, L.col_lanes, L.rows_per_chunk, partial); }
-    bn_finalize_kernel<<<dc_ceil_div(C, 128), 128, 0, st>>>(partial, L.chunks, M, C, eps, momentum, mean, invstd,
+    bn_finalize_kernel<<<dc_ceil_div(C, 32), FIN_T, 0, st>>>(partial, L.chunks, M, C, eps, momentum, mean, invstd,
                                                             running_mean_or_null, running_var_or_null);
     return dc_check_launch_n("dc_bn_stats", 2);
 }
@@ -478,7 +506,7 @@ extern "C" int dc_col_sum(const float* x, int64_t ldx, int64_t M, int C, float* 
     dim3 grid(L.chunks, L.col_blocks);
     SumVal f = {x, ldx};
     col_reduce_kernel<1><<<grid, RED_T, 0, st>>>(f, M, C, L.col_lanes, L.rows_per_chunk, (double*)ws);
-    sum1_finalize_kernel<<<dc_ceil_div(C, 128), 128, 0, st>>>((double*)ws, L.chunks, C, out);
+    sum1_finalize_kernel<<<dc_ceil_div(C, 32), FIN_T, 0, st>>>((double*)ws, L.chunks, C, out);
     return dc_check_launch_n("dc_col_sum", 2);
 }
 
@@ -504,7 +532,7 @@ extern "C" int dc_bn_act_bwd(const float* y, int64_t ldy, const float* dout, int
     double* partial = (double*)ws;
     BnBwdVal f = {y, ldy, dout, ldd, mean, invstd, gamma_or_null, beta_or_null, slope};
     col_reduce_kernel<2><<<grid, RED_T, 0, st>>>(f, M, C, L.col_lanes, L.rows_per_chunk, partial);
-    sum2_finalize_kernel<<<dc_ceil_div(C, 128), 128, 0, st>>>(partial, L.chunks, C, d_beta, d_gamma);
+    sum2_finalize_kernel<<<dc_ceil_div(C, 32), FIN_T, 0, st>>>(partial, L.chunks, C, d_beta, d_gamma);
     bn_act_bwd_kernel<<<elementwise_grid(M * C), 256, 0, st>>>(y, ldy, dout, ldd, M, C, mean, invstd, gamma_or_null, beta_or_null,
                                                                slope, d_beta, d_gamma, training, dy, ld_dy);
     return dc_check_launch_n("dc_bn_act_bwd", 3);
@@ -536,7 +564,7 @@ extern "C" int dc_vecnonlin_bwd(const float* v, int64_t ldv, const float* dout, 
         double* partial = (double*)ws;
         VnlBwdVal f = {v, ldv, dout, ldd, mean_or_null, invstd_or_null, gamma_or_null, beta_or_null};
         col_reduce_kernel<2><<<grid, RED_T, 0, st>>>(f, M, C, L.col_lanes, L.rows_per_chunk, partial);
-        sum2_finalize_kernel<<<dc_ceil_div(C, 128), 128, 0, st>>>(partial, L.chunks, C, d_beta, d_gamma);
+        sum2_finalize_kernel<<<dc_ceil_div(C, 32), FIN_T, 0, st>>>(partial, L.chunks, C, d_beta, d_gamma);
     }
     vecnonlin_bwd_kernel<<<elementwise_grid(M * C), 256, 0, st>>>(v, ldv, dout, ldd, M, C, mean_or_null, invstd_or_null, gamma_or_null,
                                                                   beta_or_null, bias_or_null, d_beta, d_gamma, training, dv, ld_dv,

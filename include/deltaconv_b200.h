@@ -172,7 +172,18 @@ int dc_bcast_rows(const float* src, int64_t lds, const int32_t* cloud_ptr, int B
                   void* stream);
 
 /* ---- Linear (mlp.py:9,15; heads) ---------------------------------------------------------------- */
+/* Precision of the tensor-core (tcgen05) path behind dc_linear_*: 3 = 3xTF32 split, fp32-grade accuracy (default);
+ * 1 = plain TF32 (~1e-3 relative); 0 = tensor cores off, exact fp32 FFMA kernel.  Shapes the tensor-core
+ * kernel does not take (row pitch not a multiple of 4 floats, M < 64, N < 16, K < 8) always use the FFMA kernel. */
+int dc_set_gemm_mode(int mode);
+int dc_get_gemm_mode(void);
 size_t dc_gemm_ws_bytes(int64_t M, int64_t N, int64_t K);
+/* The tensor-core product itself, C[M,N] = op(A) op(B)^T: a_mn/b_mn = 0 when the reduction index is contiguous
+ * ([M,K] / [N,K] storage), 1 when the M / N index is contiguous ([K,M] / [K,N] storage).  Returns 1 if the shape is
+ * not eligible.  Used by dc_linear_fwd (0,0), dc_linear_bwd_input (0,1) and dc_linear_bwd_weight (1,1). */
+int dc_gemm_tc_raw(const float* A, int64_t lda, int a_mn, const float* B, int64_t ldb, int b_mn,
+                   const float* bias_or_null, int64_t M, int N, int64_t K, float* C, int64_t ldc,
+                   void* ws, size_t ws_bytes, void* stream);
 int dc_linear_fwd(const float* X, int64_t ldx, const float* W, int64_t ldw, const float* bias_or_null,
                   int64_t M, int K, int Nout, float* Y, int64_t ldy, void* ws, size_t ws_bytes, void* stream);
 int dc_linear_bwd_input(const float* dY, int64_t ld_dy, const float* W, int64_t ldw, int64_t M, int K, int Nout,

@@ -45,11 +45,36 @@ def test_linear_forward_backward(M, K, N, bias):
     br = b0.double().requires_grad_(True) if bias else None
     yr = F.linear(xr, wr, br)
     (yr * g0.double()).sum().backward()
-    assert rel_err(y.detach().cpu(), yr.detach()) < 2e-6
-    assert rel_err(x.grad.cpu(), xr.grad) < 2e-6
-    assert rel_err(w.grad.cpu(), wr.grad) < 5e-6
+    assert rel_err(y.detach().cpu(), yr.detach()) < 1e-5
+    assert rel_err(x.grad.cpu(), xr.grad) < 1e-5
+    assert rel_err(w.grad.cpu(), wr.grad) < 1e-5
     if bias:
         assert rel_err(b.grad.cpu(), br.grad) < 2e-6
+
+
+@pytest.mark.parametrize('mode,tol', [(3, 1e-5), (1, 3e-3), (0, 2e-6)])
+@pytest.mark.parametrize('M,K,N', [(4096, 256, 64), (1000, 512, 1024), (32768, 140, 64), (8192, 64, 256), (777, 36, 40),
+                                   (130, 1024, 16), (65536, 24, 128)])
+def test_tensor_core_linear_modes(M, K, N, mode, tol):
+    """dc_linear_* through the tcgen05 kernel: 3xTF32 (default, fp32-grade), plain TF32, and tensor cores off."""
+    from deltaconv_b200 import _lib
+    lib = _lib.load()
+    x0, w0, g0 = torch.randn(M, K), torch.randn(N, K) / K ** 0.5, torch.randn(M, N)
+    prev = lib.dc_get_gemm_mode()
+    try:
+        assert lib.dc_set_gemm_mode(mode) == 0
+        x, w = x0.to(DEV).requires_grad_(True), w0.to(DEV).requires_grad_(True)
+        y = dc().ops.linear(x, w)
+        (y * g0.to(DEV)).sum().backward()
+        torch.cuda.synchronize()
+    finally:
+        lib.dc_set_gemm_mode(prev)
+    xr, wr = x0.double().requires_grad_(True), w0.double().requires_grad_(True)
+    yr = F.linear(xr, wr)
+    (yr * g0.double()).sum().backward()
+    e = [report(f'tc_linear.mode{mode}.{M}x{K}x{N}.{n_}', rel_err(a.cpu(), b))
+         for n_, a, b in (('y', y.detach(), yr.detach()), ('dx', x.grad, xr.grad), ('dw', w.grad, wr.grad))]
+    assert max(e) < tol, e
 
 
 @pytest.mark.parametrize('M,C,slope,train', [(1000, 64, 0.2, True), (257, 5, 1.0, True), (4096, 130, 0.2, False),
