@@ -111,7 +111,7 @@ WORK = {
     'dc_edge_diff_fwd': (_w_ediff, 'centralized'), 'dc_segmax_fwd': (_w_segmax, 'centralized'),
     'dc_segmax_bwd': (_w_segmax_t, 'centralized'),
 }
-KERNEL_OF = {'gemm': 'sgemm_kernel (dc_linear_fwd / _bwd_input / _bwd_weight)', 'spmm': 'spmm_kernel (grad/div/curl/hodge and transposes)',
+KERNEL_OF = {'gemm': 'tc_gemm_kernel / sgemm_kernel (dc_linear_fwd / _bwd_input / _bwd_weight)', 'spmm': 'spmm_kernel (grad/div/curl/hodge and transposes)',
              'batchnorm': 'col_reduce/bn_act kernels', 'knn': 'knn_kernel', 'build_grad_div': 'fit_kernel (+ edge/cloud means)',
              'gathermax': 'gathermax kernels', 'vecnonlin': 'vecnonlin kernels', 'centralized': 'edge_diff/segmax kernels'}
 
@@ -128,7 +128,7 @@ class EntryPointProfiler:
         s.record()
         work = WORK.get(name)
         wb, wf = work[0](args) if work else (0, 0)
-        return (name, work[1] if work else 'other', wb, wf, s, e)
+        return (name, work[1] if work else 'other', wb, wf, s, e, tuple(a for a in args if isinstance(a, int) and 0 < a < (1 << 31)))
 
     def end(self, token):
         token[5].record()
@@ -137,13 +137,28 @@ class EntryPointProfiler:
     def families(self):
         torch.cuda.synchronize()
         fam = {}
-        for name, family, wb, wf, s, e in self.records:
+        for name, family, wb, wf, s, e, _dims in self.records:
             f = fam.setdefault(family, dict(ms=0.0, bytes=0, flops=0, launches=0))
             f['ms'] += s.elapsed_time(e)
             f['bytes'] += wb
             f['flops'] += wf
             f['launches'] += 1
         return fam
+
+
+    def detail(self, steps, top=40):
+        torch.cuda.synchronize()
+        calls = {}
+        for name, family, wb, wf, s, e, dims in self.records:
+            c = calls.setdefault((name, dims), [0, 0.0, wb, wf])
+            c[0] += 1
+            c[1] += s.elapsed_time(e)
+        lines = []
+        for (name, dims), (n, ms, wb, wf) in sorted(calls.items(), key=lambda kv: -kv[1][1])[:top]:
+            sec = ms / n / 1000
+            lines.append(f"{ms / steps:8.4f} ms/step  x{n // steps:<3d} {name:24s} {str(dims):44s} "
+                         f"{wb / sec / 1e9:8.1f} GB/s {wf / sec / 1e12:7.2f} TF/s")
+        return '\n'.join(lines)
 
 
 def smoothed_loss(logits, target):
@@ -266,12 +281,21 @@ def run_cuda_arm(args):
     for _ in range(max(args.warmup, 3)):
         step(resident)
 
+    graphed = None
+    if not args.no_graph:
+        static = host.to(dev)
+        static._num_clouds = CLOUDS
+        graphed = D.utils.GraphedTrainStep(model, opt, smoothed_loss, static, flat=flat)
+        for _ in range(3):
+            graphed()
+
     # (1) device-resident throughput
     sampler = ClockSampler(local) if rank == 0 else None
     wall0 = time.time()
     lib.dc_reset_launch_count()
-    total_ms = timed(lambda: step(resident), args.steps)
+    eager_ms = timed(lambda: step(resident), args.steps)
     launches = int(lib.dc_launch_count())
+    total_ms = timed(graphed, args.steps) if graphed else eager_ms
     wall1 = time.time()
     clocks = sampler.summary(wall0, wall1) if sampler else None
 
@@ -280,9 +304,14 @@ def run_cuda_arm(args):
         data = host.to(dev, non_blocking=True)
         data._num_clouds = CLOUDS
         return step(data).item()
+    def e2e_graph_step():
+        graphed.load(host)
+        return graphed().item()
+    e2e_fn = e2e_graph_step if graphed else e2e_step
     for _ in range(2):
-        e2e_step()
-    e2e_ms = timed(e2e_step, args.steps)
+        e2e_fn()
+    e2e_ms = timed(e2e_fn, args.steps)
+    e2e_eager_ms = timed(e2e_step, args.steps) if graphed else e2e_ms
 
     # (3) per-entry-point device time (CUDA events on the launching stream), same steps
     prof = EntryPointProfiler()
@@ -297,6 +326,8 @@ def run_cuda_arm(args):
     _lib.PROFILER = None
     fam = prof.families()
     prof_total_ms = w0.elapsed_time(w1)
+    if args.detail and rank == 0:
+        open(args.detail, 'w').write(prof.detail(args.steps) + '\n')
 
     if rank != 0:
         if world > 1:
@@ -345,7 +376,10 @@ def run_cuda_arm(args):
                 ms_per_step=round(ms_per_step, 4), higher_is_better=True, scaling='weak', vs_baseline=None, dtype='f32',
                 data='synthetic',
                 config=dict(workload=WORKLOAD, clouds_per_gpu=CLOUDS, points=POINTS, k=K_NN, parallelism=f'dp{world} (shard by cloud, flat-gradient all-reduce)',
-                            l2='256 MiB buffer rewritten between steps (inside the timed region)', gemm='fp32 SIMT (FFMA)'),
+                            l2='256 MiB buffer rewritten between steps (inside the timed region)',
+                            gemm='tcgen05 kind::tf32, 3xTF32 split (fp32-grade accuracy), fp32 accumulate; FFMA kernel for ineligible shapes',
+                            launch='CUDA-graph replay of the whole step' if graphed else 'eager (one Python launch per kernel)',
+                            eager_ms_per_step=round(eager_ms / args.steps, 4), e2e_eager_ms_per_step=round(e2e_eager_ms / args.steps, 4)),
                 e2e=dict(value=round(e2e_value, 2), unit='clouds/s', h2d_bytes_per_step=host.nbytes(), d2h_bytes_per_step=4,
                          ms_per_step=round(e2e_ms / args.steps, 4)),
                 gpu_launches=launches, roofline=roof, cpu_baseline=cpu, clocks=clocks,
@@ -364,6 +398,8 @@ def main():
     ap.add_argument('--warmup', type=int, default=5)
     ap.add_argument('--impl', default='cuda', choices=['cuda', 'reference'])
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-graph', action='store_true', help='time eager launches instead of CUDA-graph replays')
+    ap.add_argument('--detail', default=None, help='write the per-call device-time table to this file')
     args = ap.parse_args()
     if args.impl == 'reference':
         run_reference_arm(args)

@@ -1,0 +1,69 @@
+"""Whole training step captured in CUDA graphs.
+
+At 1K-point clouds one step is a few hundred short kernels: launched one by one from Python the
+host takes longer than the GPU.  Shapes are static once (clouds, points, k) are fixed, so the step
+is captured once and replayed; new batches are copied into the static input tensors.
+
+The reference's loop (experiments/train_modelnet.py:98-108) maps onto it as
+    step.load(batch)        # data = data.to(device)
+    loss = step()           # zero_grad / forward / loss / backward / (all-reduce) / optimizer.step
+"""
+import torch
+import torch.distributed as dist
+
+from ..parallel import FlatGradients
+
+
+class GraphedTrainStep:
+    """forward + loss + backward (+ gradient all-reduce) + optimizer step as CUDA graph replays.
+
+    `example` is a device-resident `Data` batch whose tensors become the static inputs; every later
+    batch must have the same shapes and the same cloud layout (same points per cloud), because the
+    per-cloud offsets are baked into the captured kernels' arguments."""
+
+    def __init__(self, model, optimizer, loss_fn, example, flat=None, warmup=3):
+        self.model, self.optimizer, self.loss_fn = model, optimizer, loss_fn
+        self.static = example
+        self.flat = flat if flat is not None else FlatGradients(model.parameters())
+        self.distributed = dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(warmup):
+                self._forward_backward()
+                self.flat.all_reduce()
+                self.optimizer.step()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        self.graph_fb = torch.cuda.CUDAGraph()
+        self.graph_opt = None
+        if self.distributed:
+            # the collective stays outside the graphs: fwd+bwd graph -> NCCL all-reduce -> optimizer graph
+            with torch.cuda.graph(self.graph_fb):
+                self.loss = self._forward_backward()
+            self.graph_opt = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.graph_opt, pool=self.graph_fb.pool()):
+                self.optimizer.step()
+        else:
+            with torch.cuda.graph(self.graph_fb):
+                self.loss = self._forward_backward()
+                self.optimizer.step()
+
+    def _forward_backward(self):
+        self.flat.zero()
+        loss = self.loss_fn(self.model(self.static), self.static.y)
+        loss.backward()
+        return loss.detach()
+
+    def load(self, batch):
+        """Copy a (pinned-host or device) batch with the captured shapes into the static inputs."""
+        for name, dst in self.static.__dict__.items():
+            if torch.is_tensor(dst):
+                dst.copy_(getattr(batch, name), non_blocking=True)
+
+    def __call__(self):
+        self.graph_fb.replay()
+        if self.graph_opt is not None:
+            self.flat.all_reduce()
+            self.graph_opt.replay()
+        return self.loss

@@ -368,3 +368,34 @@ def test_cpu_tensors_fail_loudly():
         D.geometry.build_tangent_basis(torch.randn(10, 3))
     with pytest.raises(D._lib.DeltaConvLibraryError):
         D.nn.Linear(4, 4)(torch.randn(3, 4))
+
+
+def test_graphed_train_step_matches_eager():
+    """CUDA-graph replay of the step = the eager step (same kernels, same order): identical weights."""
+    D = dc()
+    from deltaconv_b200.parallel import FlatGradients
+    from deltaconv_b200.utils.losses import calc_loss
+    data = D.utils.synthetic_batch(4, 256, config=2, num_classes=10).to(DEV)
+    data._num_clouds = 4
+    nets = []
+    for _ in range(2):
+        torch.manual_seed(0)
+        nets.append(no_dropout(D.utils.fill_deterministic(D.models.DeltaNetClassification(3, 10, conv_channels=[16, 32]), 5)).to(DEV).train())
+    eager, graphed_net = nets
+    flat = FlatGradients(eager.parameters())
+    opt = torch.optim.SGD(eager.parameters(), lr=0.05, momentum=0.9, weight_decay=1e-4)
+    opt2 = torch.optim.SGD(graphed_net.parameters(), lr=0.05, momentum=0.9, weight_decay=1e-4)
+    step = D.utils.GraphedTrainStep(graphed_net, opt2, calc_loss, data, warmup=2)
+    losses_e, losses_g = [], []
+    for _ in range(2 + 3):                       # the graphed net already took 2 warm-up steps at construction
+        flat.zero()
+        loss = calc_loss(eager(data), data.y)
+        loss.backward()
+        opt.step()
+        losses_e.append(loss.item())
+    for _ in range(3):
+        step.load(data)
+        losses_g.append(step().item())
+    assert losses_g == pytest.approx(losses_e[2:], rel=1e-5)
+    for (n1, p1), (n2, p2) in zip(eager.named_parameters(), graphed_net.named_parameters()):
+        assert torch.allclose(p1, p2, rtol=1e-5, atol=1e-6), n1
