@@ -1,0 +1,113 @@
+// Deterministic column reductions shared by the BatchNorm-type kernels (nnops.cu, central.cu):
+// per-CTA fp64 partial sums over a row chunk (fixed grid), then a finalize step that adds the
+// partials in a fixed order.  No atomics anywhere, so results are bit-reproducible.
+#pragma once
+#include "common.cuh"
+
+namespace {
+
+constexpr int RED_T = 256;       // threads per CTA in the column reductions
+constexpr int RED_MAX_CHUNKS = 1184;   // 8 x 148
+
+// ------------------------------------------------------------------------------------------
+// generic column reduction: every element (r, c) contributes NV values; partial[chunk][v][c]
+// ------------------------------------------------------------------------------------------
+struct ColLayout {
+    int col_lanes;     // threads along the columns
+    int row_lanes;     // threads along the rows (col_lanes * row_lanes == RED_T)
+    int col_blocks;    // grid.y : ceil(C / col_lanes)
+    int chunks;        // grid.x
+    long long rows_per_chunk;
+};
+
+ColLayout col_layout(long long M, int C) {
+    ColLayout L;
+    int cl = 1;
+    while (cl < C && cl < 64) cl <<= 1;
+    L.col_lanes = cl;
+    L.row_lanes = RED_T / cl;
+    L.col_blocks = (C + cl - 1) / cl;
+    long long want = (long long)dc_sm_count() * 4 / L.col_blocks;
+    if (want < 1) want = 1;
+    long long by_rows = (M + L.row_lanes * 4 - 1) / (L.row_lanes * 4);   // at least 4 rows per thread
+    if (by_rows < 1) by_rows = 1;
+    long long chunks = want < by_rows ? want : by_rows;
+    if (chunks > RED_MAX_CHUNKS) chunks = RED_MAX_CHUNKS;
+    L.chunks = (int)chunks;
+    L.rows_per_chunk = (M + chunks - 1) / chunks;
+    return L;
+}
+
+template <int NV, class F>
+__global__ void __launch_bounds__(RED_T) col_reduce_kernel(F f, long long M, int C, int col_lanes, long long rows_per_chunk,
+                                                           double* __restrict__ partial) {
+    __shared__ double sh[NV][RED_T];
+    const int cl = threadIdx.x % col_lanes, rl = threadIdx.x / col_lanes, row_lanes = RED_T / col_lanes;
+    const int c = blockIdx.y * col_lanes + cl;
+    const long long r0 = blockIdx.x * rows_per_chunk;
+    const long long r1 = min(M, r0 + rows_per_chunk);
+    double acc[NV];
+#pragma unroll
+    for (int v = 0; v < NV; ++v) acc[v] = 0.0;
+    if (c < C) {
+        long long r = r0 + rl;
+        // four independent rows in flight per thread (the loads do not depend on the accumulators)
+        for (; r + 3LL * row_lanes < r1; r += 4LL * row_lanes) {
+            float v0[NV], v1[NV], v2[NV], v3[NV];
+            f(r, c, v0); f(r + row_lanes, c, v1); f(r + 2LL * row_lanes, c, v2); f(r + 3LL * row_lanes, c, v3);
+#pragma unroll
+            for (int v = 0; v < NV; ++v) acc[v] += ((double)v0[v] + (double)v1[v]) + ((double)v2[v] + (double)v3[v]);
+        }
+        for (; r < r1; r += row_lanes) {
+            float vals[NV];
+            f(r, c, vals);
+#pragma unroll
+            for (int v = 0; v < NV; ++v) acc[v] += (double)vals[v];
+        }
+    }
+#pragma unroll
+    for (int v = 0; v < NV; ++v) sh[v][threadIdx.x] = acc[v];
+    __syncthreads();
+    if (rl == 0 && c < C) {
+#pragma unroll
+        for (int v = 0; v < NV; ++v) {
+            double s = 0.0;
+            for (int q = 0; q < row_lanes; ++q) s += sh[v][q * col_lanes + cl];
+            partial[((size_t)blockIdx.x * NV + v) * C + c] = s;
+        }
+    }
+}
+
+
+// Sum partial[q][v][c] over the chunks q for one column c and value v.  A CTA of 256 threads
+// owns 32 columns: lane = column, the 8 warps stride over the chunks (coalesced 256-byte rows),
+// then the 8 per-warp sums are added in a fixed order -> deterministic.
+constexpr int FIN_T = 256;
+template <int NV>
+__device__ __forceinline__ bool finalize_sums(const double* __restrict__ partial, int chunks, int C, double (&out)[NV]) {
+    __shared__ double sh[NV][8][33];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int c = blockIdx.x * 32 + lane;
+    double acc[NV];
+#pragma unroll
+    for (int v = 0; v < NV; ++v) acc[v] = 0.0;
+    if (c < C)
+        for (int q = w; q < chunks; q += 8)
+#pragma unroll
+            for (int v = 0; v < NV; ++v) acc[v] += partial[((size_t)q * NV + v) * C + c];
+#pragma unroll
+    for (int v = 0; v < NV; ++v) sh[v][w][lane] = acc[v];
+    __syncthreads();
+    if (w != 0 || c >= C) return false;
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+        double s = 0.0;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) s += sh[v][q][lane];
+        out[v] = s;
+    }
+    return true;
+}
+
+
+}  // namespace

@@ -9,103 +9,9 @@
 // activation.  It is done as: per-CTA fp64 partial sums (one CTA per row chunk, fixed grid) ->
 // one finalize kernel that adds the partials in a fixed order.  No atomics, bit-reproducible.
 #include "common.cuh"
+#include "colreduce.cuh"
 
 namespace {
-
-constexpr int RED_T = 256;       // threads per CTA in the column reductions
-constexpr int RED_MAX_CHUNKS = 1184;   // 8 x 148
-
-// ------------------------------------------------------------------------------------------
-// generic column reduction: every element (r, c) contributes NV values; partial[chunk][v][c]
-// ------------------------------------------------------------------------------------------
-struct ColLayout {
-    int col_lanes;     // threads along the columns
-    int row_lanes;     // threads along the rows (col_lanes * row_lanes == RED_T)
-    int col_blocks;    // grid.y : ceil(C / col_lanes)
-    int chunks;        // grid.x
-    long long rows_per_chunk;
-};
-
-ColLayout col_layout(long long M, int C) {
-    ColLayout L;
-    int cl = 1;
-    while (cl < C && cl < 64) cl <<= 1;
-    L.col_lanes = cl;
-    L.row_lanes = RED_T / cl;
-    L.col_blocks = (C + cl - 1) / cl;
-    long long want = (long long)dc_sm_count() * 4 / L.col_blocks;
-    if (want < 1) want = 1;
-    long long by_rows = (M + L.row_lanes * 4 - 1) / (L.row_lanes * 4);   // at least 4 rows per thread
-    if (by_rows < 1) by_rows = 1;
-    long long chunks = want < by_rows ? want : by_rows;
-    if (chunks > RED_MAX_CHUNKS) chunks = RED_MAX_CHUNKS;
-    L.chunks = (int)chunks;
-    L.rows_per_chunk = (M + chunks - 1) / chunks;
-    return L;
-}
-
-template <int NV, class F>
-__global__ void __launch_bounds__(RED_T) col_reduce_kernel(F f, long long M, int C, int col_lanes, long long rows_per_chunk,
-                                                           double* __restrict__ partial) {
-    __shared__ double sh[NV][RED_T];
-    const int cl = threadIdx.x % col_lanes, rl = threadIdx.x / col_lanes, row_lanes = RED_T / col_lanes;
-    const int c = blockIdx.y * col_lanes + cl;
-    const long long r0 = blockIdx.x * rows_per_chunk;
-    const long long r1 = min(M, r0 + rows_per_chunk);
-    double acc[NV];
-#pragma unroll
-    for (int v = 0; v < NV; ++v) acc[v] = 0.0;
-    if (c < C) {
-        for (long long r = r0 + rl; r < r1; r += row_lanes) {
-            float vals[NV];
-            f(r, c, vals);
-#pragma unroll
-            for (int v = 0; v < NV; ++v) acc[v] += (double)vals[v];
-        }
-    }
-#pragma unroll
-    for (int v = 0; v < NV; ++v) sh[v][threadIdx.x] = acc[v];
-    __syncthreads();
-    if (rl == 0 && c < C) {
-#pragma unroll
-        for (int v = 0; v < NV; ++v) {
-            double s = 0.0;
-            for (int q = 0; q < row_lanes; ++q) s += sh[v][q * col_lanes + cl];
-            partial[((size_t)blockIdx.x * NV + v) * C + c] = s;
-        }
-    }
-}
-
-
-// Sum partial[q][v][c] over the chunks q for one column c and value v.  A CTA of 256 threads
-// owns 32 columns: lane = column, the 8 warps stride over the chunks (coalesced 256-byte rows),
-// then the 8 per-warp sums are added in a fixed order -> deterministic.
-constexpr int FIN_T = 256;
-template <int NV>
-__device__ __forceinline__ bool finalize_sums(const double* __restrict__ partial, int chunks, int C, double (&out)[NV]) {
-    __shared__ double sh[NV][8][33];
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    const int c = blockIdx.x * 32 + lane;
-    double acc[NV];
-#pragma unroll
-    for (int v = 0; v < NV; ++v) acc[v] = 0.0;
-    if (c < C)
-        for (int q = w; q < chunks; q += 8)
-#pragma unroll
-            for (int v = 0; v < NV; ++v) acc[v] += partial[((size_t)q * NV + v) * C + c];
-#pragma unroll
-    for (int v = 0; v < NV; ++v) sh[v][w][lane] = acc[v];
-    __syncthreads();
-    if (w != 0 || c >= C) return false;
-#pragma unroll
-    for (int v = 0; v < NV; ++v) {
-        double s = 0.0;
-#pragma unroll
-        for (int q = 0; q < 8; ++q) s += sh[v][q][lane];
-        out[v] = s;
-    }
-    return true;
-}
 
 struct SumVal {        // plain column sums of a [M,C] matrix
     const float* x; long long ld;
@@ -169,6 +75,32 @@ __global__ void bn_act_fwd_kernel(const float* __restrict__ y, long long ldy, lo
     }
 }
 
+// float4 variant (C % 4 == 0, every leading dimension % 4 == 0, 16-byte aligned bases)
+__global__ void bn_act_fwd_vec4_kernel(const float* __restrict__ y, long long ldy, long long M, int C4,
+                                       const float* __restrict__ mean, const float* __restrict__ invstd,
+                                       const float* __restrict__ gamma, const float* __restrict__ beta, float slope,
+                                       const float* __restrict__ addend, long long ld_add, float* __restrict__ out, long long ldo) {
+    const long long total = M * (long long)C4;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+        const long long r = t / C4;
+        const int c = (int)(t - r * C4) * 4;
+        const float4 v = ld_stream4(reinterpret_cast<const float4*>(y + r * ldy + c));
+        const float4 mu = __ldg(reinterpret_cast<const float4*>(mean + c)), is = __ldg(reinterpret_cast<const float4*>(invstd + c));
+        const float4 g = gamma ? __ldg(reinterpret_cast<const float4*>(gamma + c)) : make_float4(1.f, 1.f, 1.f, 1.f);
+        const float4 b = beta ? __ldg(reinterpret_cast<const float4*>(beta + c)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        float4 z;
+        z.x = g.x * ((v.x - mu.x) * is.x) + b.x; z.y = g.y * ((v.y - mu.y) * is.y) + b.y;
+        z.z = g.z * ((v.z - mu.z) * is.z) + b.z; z.w = g.w * ((v.w - mu.w) * is.w) + b.w;
+        z.x = z.x > 0.f ? z.x : slope * z.x; z.y = z.y > 0.f ? z.y : slope * z.y;
+        z.z = z.z > 0.f ? z.z : slope * z.z; z.w = z.w > 0.f ? z.w : slope * z.w;
+        if (addend) {
+            const float4 a = ld_stream4(reinterpret_cast<const float4*>(addend + r * ld_add + c));
+            z.x += a.x; z.y += a.y; z.z += a.z; z.w += a.w;
+        }
+        *reinterpret_cast<float4*>(out + r * ldo + c) = z;
+    }
+}
+
 // backward, reduction part: dz = dOut * act'(bn); sums of dz and dz * xhat per column
 struct BnBwdVal {
     const float* y; long long ldy; const float* dout; long long ldd;
@@ -207,6 +139,36 @@ __global__ void bn_act_bwd_kernel(const float* __restrict__ y, long long ldy, co
         float dz = __ldg(dout + r * ldd + c) * (z > 0.f ? 1.f : slope);
         float v = training ? dz - __ldg(sum_dz + c) * invM - xh * (__ldg(sum_dz_xh + c) * invM) : dz;
         dy[r * ld_dy + c] = g * is * v;
+    }
+}
+
+__global__ void bn_act_bwd_vec4_kernel(const float* __restrict__ y, long long ldy, const float* __restrict__ dout, long long ldd,
+                                       long long M, int C4, const float* __restrict__ mean, const float* __restrict__ invstd,
+                                       const float* __restrict__ gamma, const float* __restrict__ beta, float slope,
+                                       const float* __restrict__ sum_dz, const float* __restrict__ sum_dz_xh, int training,
+                                       float* __restrict__ dy, long long ld_dy) {
+    const long long total = M * (long long)C4;
+    const float invM = 1.f / (float)M;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+        const long long r = t / C4;
+        const int c = (int)(t - r * C4) * 4;
+        const float4 yv = ld_stream4(reinterpret_cast<const float4*>(y + r * ldy + c));
+        const float4 dv = ld_stream4(reinterpret_cast<const float4*>(dout + r * ldd + c));
+        const float4 mu = __ldg(reinterpret_cast<const float4*>(mean + c)), is = __ldg(reinterpret_cast<const float4*>(invstd + c));
+        const float4 g = gamma ? __ldg(reinterpret_cast<const float4*>(gamma + c)) : make_float4(1.f, 1.f, 1.f, 1.f);
+        const float4 b = beta ? __ldg(reinterpret_cast<const float4*>(beta + c)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        const float4 s1 = __ldg(reinterpret_cast<const float4*>(sum_dz + c)), s2 = __ldg(reinterpret_cast<const float4*>(sum_dz_xh + c));
+        auto one = [&](float yy, float dd, float m, float i_, float gg, float bb, float a1, float a2) {
+            float xh = (yy - m) * i_;
+            float z = gg * xh + bb;
+            float dz = dd * (z > 0.f ? 1.f : slope);
+            float v = training ? dz - a1 * invM - xh * (a2 * invM) : dz;
+            return gg * i_ * v;
+        };
+        float4 o;
+        o.x = one(yv.x, dv.x, mu.x, is.x, g.x, b.x, s1.x, s2.x); o.y = one(yv.y, dv.y, mu.y, is.y, g.y, b.y, s1.y, s2.y);
+        o.z = one(yv.z, dv.z, mu.z, is.z, g.z, b.z, s1.z, s2.z); o.w = one(yv.w, dv.w, mu.w, is.w, g.w, b.w, s1.w, s2.w);
+        *reinterpret_cast<float4*>(dy + r * ld_dy + c) = o;
     }
 }
 
@@ -357,6 +319,76 @@ __global__ void gathermax_bwd_kernel(const int* __restrict__ in_ptr, const int* 
     }
 }
 
+// float4 variants: a group of LPP lanes owns one point and 4*LPP consecutive channels (like spmm_kernel)
+__global__ void __launch_bounds__(256) gathermax_fwd_vec4_kernel(const int* __restrict__ idx, int N, int k, int C, const float* __restrict__ y,
+                                                                 long long ldy, float* __restrict__ out, long long ldo,
+                                                                 unsigned char* __restrict__ arg, int lpp_log2) {
+    const int lpp = 1 << lpp_log2, lane = threadIdx.x & 31, sub = lane & (lpp - 1);
+    const long long row_ll = ((long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * (32 >> lpp_log2) + (lane >> lpp_log2);
+    const bool row_ok = row_ll < N;
+    const int i = row_ok ? (int)row_ll : 0;
+    const int ch = (blockIdx.y * lpp + sub) * 4;
+    const bool ch_ok = ch < C;
+    float4 best = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+    uchar4 slot = make_uchar4(0, 0, 0, 0);
+    for (int e0 = 0; e0 < k; e0 += lpp) {
+        int my_j = -1;
+        if (row_ok && e0 + sub < k) { my_j = __ldg(idx + (size_t)i * k + e0 + sub); if ((unsigned)my_j >= (unsigned)N) my_j = -1; }
+        const int cnt = min(lpp, k - e0);
+#pragma unroll 4
+        for (int q = 0; q < cnt; ++q) {
+            const int j = __shfl_sync(FULL, my_j, q, lpp);
+            if (!row_ok || !ch_ok || j < 0) continue;
+            const float4 v = __ldg(reinterpret_cast<const float4*>(y + (size_t)j * ldy + ch));
+            const unsigned char e = (unsigned char)(e0 + q);
+            if (v.x > best.x) { best.x = v.x; slot.x = e; }
+            if (v.y > best.y) { best.y = v.y; slot.y = e; }
+            if (v.z > best.z) { best.z = v.z; slot.z = e; }
+            if (v.w > best.w) { best.w = v.w; slot.w = e; }
+        }
+    }
+    if (!row_ok || !ch_ok) return;
+    best.x = best.x == -INFINITY ? 0.f : best.x; best.y = best.y == -INFINITY ? 0.f : best.y;
+    best.z = best.z == -INFINITY ? 0.f : best.z; best.w = best.w == -INFINITY ? 0.f : best.w;
+    *reinterpret_cast<float4*>(out + (size_t)i * ldo + ch) = best;
+    *reinterpret_cast<uchar4*>(arg + (size_t)i * C + ch) = slot;
+}
+
+__global__ void __launch_bounds__(256) gathermax_bwd_vec4_kernel(const int* __restrict__ in_ptr, const int* __restrict__ in_edge, int N, int k,
+                                                                 int C, const unsigned char* __restrict__ arg, const float* __restrict__ dout,
+                                                                 long long ldd, float* __restrict__ dy, long long ld_dy, int lpp_log2) {
+    const int lpp = 1 << lpp_log2, lane = threadIdx.x & 31, sub = lane & (lpp - 1);
+    const long long row_ll = ((long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * (32 >> lpp_log2) + (lane >> lpp_log2);
+    const bool row_ok = row_ll < N;
+    const int j = row_ok ? (int)row_ll : 0;
+    const int ch = (blockIdx.y * lpp + sub) * 4;
+    const bool ch_ok = ch < C;
+    const int t_begin = row_ok ? __ldg(in_ptr + j) : 0, len = row_ok ? __ldg(in_ptr + j + 1) - t_begin : 0;
+    int max_len = len;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) max_len = max(max_len, __shfl_xor_sync(FULL, max_len, o));
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int t0 = 0; t0 < max_len; t0 += lpp) {
+        int my_edge = -1;
+        if (t0 + sub < len) my_edge = __ldg(in_edge + t_begin + t0 + sub);
+        const int cnt = min(lpp, max_len - t0);
+#pragma unroll 4
+        for (int q = 0; q < cnt; ++q) {
+            const int edge = __shfl_sync(FULL, my_edge, q, lpp);
+            if (!ch_ok || edge < 0) continue;
+            const int i = edge / k;
+            const unsigned char e = (unsigned char)(edge - i * k);
+            const uchar4 a = *reinterpret_cast<const uchar4*>(arg + (size_t)i * C + ch);
+            const float4 d = __ldg(reinterpret_cast<const float4*>(dout + (size_t)i * ldd + ch));
+            if (a.x == e) acc.x += d.x;
+            if (a.y == e) acc.y += d.y;
+            if (a.z == e) acc.z += d.z;
+            if (a.w == e) acc.w += d.w;
+        }
+    }
+    if (row_ok && ch_ok) *reinterpret_cast<float4*>(dy + (size_t)j * ld_dy + ch) = acc;
+}
+
 // ---- centralized first layer helpers (deltaconv.py:50-52) -----------------------------------
 // edge features x_j - x_i for every slot: [N*k, C]
 __global__ void edge_diff_kernel(const int* __restrict__ idx, int N, int k, int C, const float* __restrict__ x, long long ldx,
@@ -444,6 +476,21 @@ __global__ void __launch_bounds__(256) pool_fwd_kernel(const float* __restrict__
     }
 }
 
+// one CTA column per cloud: no per-element cloud search, the 1/count is computed once per thread
+__global__ void __launch_bounds__(256) pool_bwd_cloud_kernel(const int* __restrict__ cloud_ptr, int C, const int* __restrict__ arg,
+                                                             const float* __restrict__ d_max, long long ld_dmax, const float* __restrict__ d_mean,
+                                                             long long ld_dmean, float* __restrict__ dx, long long ld_dx) {
+    const int b = blockIdx.y, lane = threadIdx.x & 31, rl = threadIdx.x >> 5;
+    const int s = __ldg(cloud_ptr + b), e = __ldg(cloud_ptr + b + 1);
+    const float inv = 1.f / (float)max(e - s, 1);
+    for (int c = lane; c < C; c += 32) {
+        const float gm = d_max ? __ldg(d_max + (size_t)b * ld_dmax + c) : 0.f;
+        const int am = d_max ? __ldg(arg + (size_t)b * C + c) : -1;
+        const float ga = d_mean ? __ldg(d_mean + (size_t)b * ld_dmean + c) * inv : 0.f;
+        for (int i = s + blockIdx.x * 8 + rl; i < e; i += gridDim.x * 8) dx[(size_t)i * ld_dx + c] = (i == am ? gm : 0.f) + ga;
+    }
+}
+
 __global__ void pool_bwd_kernel(const int* __restrict__ cloud_ptr, int B, int N, int C, const int* __restrict__ arg,
                                 const float* __restrict__ d_max, long long ld_dmax, const float* __restrict__ d_mean, long long ld_dmean,
                                 float* __restrict__ dx, long long ld_dx) {
@@ -466,6 +513,14 @@ __global__ void bcast_rows_kernel(const float* __restrict__ src, long long lds, 
         int i = (int)(t / C), c = (int)(t - (long long)i * C);
         out[(size_t)i * ldo + c] = __ldg(src + (size_t)cloud_of(cloud_ptr, B, i) * lds + c);
     }
+}
+
+template <class... P>
+bool all_aligned16(P... ptrs) {
+    const void* a[] = {(const void*)ptrs...};
+    for (const void* p : a)
+        if (p != nullptr && (reinterpret_cast<uintptr_t>(p) & 15u)) return false;
+    return true;
 }
 
 int elementwise_grid(long long total) {
@@ -514,8 +569,12 @@ extern "C" int dc_bn_act_fwd(const float* y, int64_t ldy, int64_t M, int C, cons
                              const float* gamma_or_null, const float* beta_or_null, float slope,
                              const float* addend_or_null, int64_t ld_add, float* out, int64_t ldo, void* stream) {
     if (M <= 0 || C <= 0) return DC_OK;
-    bn_act_fwd_kernel<<<elementwise_grid(M * C), 256, 0, (cudaStream_t)stream>>>(y, ldy, M, C, mean, invstd, gamma_or_null,
-                                                                                 beta_or_null, slope, addend_or_null, ld_add, out, ldo);
+    if (C % 4 == 0 && ldy % 4 == 0 && ldo % 4 == 0 && ld_add % 4 == 0 && all_aligned16(y, out, addend_or_null, mean, invstd, gamma_or_null, beta_or_null))
+        bn_act_fwd_vec4_kernel<<<elementwise_grid(M * C / 4), 256, 0, (cudaStream_t)stream>>>(y, ldy, M, C / 4, mean, invstd, gamma_or_null,
+                                                                                          beta_or_null, slope, addend_or_null, ld_add, out, ldo);
+    else
+        bn_act_fwd_kernel<<<elementwise_grid(M * C), 256, 0, (cudaStream_t)stream>>>(y, ldy, M, C, mean, invstd, gamma_or_null,
+                                                                                     beta_or_null, slope, addend_or_null, ld_add, out, ldo);
     return dc_check_launch("dc_bn_act_fwd");
 }
 
@@ -533,8 +592,13 @@ extern "C" int dc_bn_act_bwd(const float* y, int64_t ldy, const float* dout, int
     BnBwdVal f = {y, ldy, dout, ldd, mean, invstd, gamma_or_null, beta_or_null, slope};
     col_reduce_kernel<2><<<grid, RED_T, 0, st>>>(f, M, C, L.col_lanes, L.rows_per_chunk, partial);
     sum2_finalize_kernel<<<dc_ceil_div(C, 32), FIN_T, 0, st>>>(partial, L.chunks, C, d_beta, d_gamma);
-    bn_act_bwd_kernel<<<elementwise_grid(M * C), 256, 0, st>>>(y, ldy, dout, ldd, M, C, mean, invstd, gamma_or_null, beta_or_null,
-                                                               slope, d_beta, d_gamma, training, dy, ld_dy);
+    if (C % 4 == 0 && ldy % 4 == 0 && ldd % 4 == 0 && ld_dy % 4 == 0 && all_aligned16(y, dout, dy, mean, invstd, gamma_or_null, beta_or_null) &&
+        all_aligned16(d_beta, d_gamma))
+        bn_act_bwd_vec4_kernel<<<elementwise_grid(M * C / 4), 256, 0, st>>>(y, ldy, dout, ldd, M, C / 4, mean, invstd, gamma_or_null, beta_or_null,
+                                                                        slope, d_beta, d_gamma, training, dy, ld_dy);
+    else
+        bn_act_bwd_kernel<<<elementwise_grid(M * C), 256, 0, st>>>(y, ldy, dout, ldd, M, C, mean, invstd, gamma_or_null, beta_or_null,
+                                                                   slope, d_beta, d_gamma, training, dy, ld_dy);
     return dc_check_launch_n("dc_bn_act_bwd", 3);
 }
 
@@ -576,14 +640,26 @@ extern "C" int dc_gathermax_fwd(const int32_t* idx, int N, int k, int C, const f
                                 uint8_t* arg, void* stream) {
     DC_REQUIRE(k <= 255, "dc_gathermax_fwd: k must be <= 255 (arg slots are stored as u8)");
     if (N <= 0 || C <= 0) return DC_OK;
-    gathermax_fwd_kernel<<<dc_ceil_div((long long)N * 32, 256), 256, 0, (cudaStream_t)stream>>>(idx, N, k, C, y, ldy, out, ldo, arg);
+    if (C % 4 == 0 && ldy % 4 == 0 && ldo % 4 == 0 && all_aligned16(y, out) && (reinterpret_cast<uintptr_t>(arg) & 3u) == 0) {
+        int lpp_log2 = 0;
+        while ((1 << lpp_log2) < C / 4 && lpp_log2 < 5) ++lpp_log2;
+        dim3 grid(dc_ceil_div(N, 8 * (32 >> lpp_log2)), dc_ceil_div(C / 4, 1 << lpp_log2));
+        gathermax_fwd_vec4_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(idx, N, k, C, y, ldy, out, ldo, arg, lpp_log2);
+    } else
+        gathermax_fwd_kernel<<<dc_ceil_div((long long)N * 32, 256), 256, 0, (cudaStream_t)stream>>>(idx, N, k, C, y, ldy, out, ldo, arg);
     return dc_check_launch("dc_gathermax_fwd");
 }
 
 extern "C" int dc_gathermax_bwd(const int32_t* in_ptr, const int32_t* in_edge, int N, int k, int C, const uint8_t* arg,
                                 const float* dout, int64_t ldd, float* dy, int64_t ld_dy, void* stream) {
     if (N <= 0 || C <= 0) return DC_OK;
-    gathermax_bwd_kernel<<<dc_ceil_div((long long)N * 32, 256), 256, 0, (cudaStream_t)stream>>>(in_ptr, in_edge, N, k, C, arg, dout, ldd, dy, ld_dy);
+    if (C % 4 == 0 && ldd % 4 == 0 && ld_dy % 4 == 0 && all_aligned16(dout, dy) && (reinterpret_cast<uintptr_t>(arg) & 3u) == 0) {
+        int lpp_log2 = 0;
+        while ((1 << lpp_log2) < C / 4 && lpp_log2 < 5) ++lpp_log2;
+        dim3 grid(dc_ceil_div(N, 8 * (32 >> lpp_log2)), dc_ceil_div(C / 4, 1 << lpp_log2));
+        gathermax_bwd_vec4_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(in_ptr, in_edge, N, k, C, arg, dout, ldd, dy, ld_dy, lpp_log2);
+    } else
+        gathermax_bwd_kernel<<<dc_ceil_div((long long)N * 32, 256), 256, 0, (cudaStream_t)stream>>>(in_ptr, in_edge, N, k, C, arg, dout, ldd, dy, ld_dy);
     return dc_check_launch("dc_gathermax_bwd");
 }
 
@@ -625,8 +701,14 @@ extern "C" int dc_pool_fwd(const float* x, int64_t ldx, const int32_t* cloud_ptr
 extern "C" int dc_pool_bwd(const int32_t* cloud_ptr, int B, int N, int C, const int32_t* arg, const float* d_max_or_null,
                            int64_t ld_dmax, const float* d_mean_or_null, int64_t ld_dmean, float* dx, int64_t ld_dx, void* stream) {
     if (N <= 0 || C <= 0) return DC_OK;
-    pool_bwd_kernel<<<elementwise_grid((long long)N * C), 256, 0, (cudaStream_t)stream>>>(cloud_ptr, B, N, C, arg, d_max_or_null, ld_dmax,
-                                                                                           d_mean_or_null, ld_dmean, dx, ld_dx);
+    {
+        int per_cloud = dc_ceil_div((long long)dc_sm_count() * 4, B);
+        int by_rows = dc_ceil_div(dc_ceil_div(N, B), 8 * 4);
+        if (per_cloud > by_rows) per_cloud = by_rows;
+        if (per_cloud < 1) per_cloud = 1;
+        dim3 grid(per_cloud, B);
+        pool_bwd_cloud_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(cloud_ptr, C, arg, d_max_or_null, ld_dmax, d_mean_or_null, ld_dmean, dx, ld_dx);
+    }
     return dc_check_launch("dc_pool_bwd");
 }
 

@@ -9,7 +9,7 @@
 import torch
 
 from .. import ops
-from .mlp import MLP, VectorMLP
+from .mlp import MLP, VectorMLP, _slope_of
 
 __all__ = ['DeltaConv']
 
@@ -34,7 +34,14 @@ class DeltaConv(torch.nn.Module):
 
         # scalar stream (deltaconv.py:50-59)
         if self.centralized:
-            x_max = ops.segment_max(self.s_mlp_max(ops.edge_diff(x, graph)), graph)
+            block = self.s_mlp_max[0]
+            slope = _slope_of(block[2])
+            if (len(self.s_mlp_max) == 1 and slope is not None and block[0].bias is None
+                    and ops.centralized_max_supported(x.size(1), graph.k)):
+                # edge MLP + BatchNorm over the E edge rows + max, without any per-edge tensor
+                x_max = ops.centralized_max(x, block[0].weight, block[1].bn, graph, slope)
+            else:
+                x_max = ops.segment_max(self.s_mlp_max(ops.edge_diff(x, graph)), graph)
         else:
             x_max = ops.gather_max(self.s_mlp_max(x), graph)
         x_cat, div_curl = ops.scalar_cat(x, v, div)

@@ -679,6 +679,74 @@ def segment_max(t, graph):
     return _SegMax.apply(t, graph)
 
 
+class _CentralizedMax(torch.autograd.Function):
+    """max over each point's k edges of act(BatchNorm(Linear(x_j - x_i))) — the centralized scalar aggregation of
+    the first DeltaConv layer (deltaconv.py:50-52) — without materialising any per-edge tensor."""
+
+    @staticmethod
+    def forward(ctx, x, weight, gamma, beta, bn, graph, slope):
+        x, ldx = _mat(x, 'x')
+        weight = _f32(weight, 'weight').contiguous()
+        N, k, Cin, Cout = graph.N, graph.k, x.size(1), weight.size(0)
+        dev = x.device
+        nbytes = query('dc_central_ws_bytes', N, k, Cin, Cout)
+        ws = workspace(nbytes, dev)
+        use_batch = bn.training or not bn.track_running_stats or bn.running_mean is None
+        moments = None
+        if use_batch:
+            moments = torch.empty(20, dtype=torch.float64, device=dev)
+            mean = torch.empty(Cout, dtype=_F32, device=dev)
+            invstd = torch.empty(Cout, dtype=_F32, device=dev)
+            update = bn.training and bn.track_running_stats and bn.running_mean is not None
+            momentum = 0.0
+            if update:
+                bn.num_batches_tracked += 1
+                momentum = bn.momentum if bn.momentum is not None else 1.0 / float(bn.num_batches_tracked)
+            call('dc_central_stats', ptr(graph.idx), N, k, Cin, Cout, ptr(x), ldx, ptr(weight), float(bn.eps), float(momentum),
+                 ptr(moments), ptr(mean), ptr(invstd), ptr(bn.running_mean) if update else None,
+                 ptr(bn.running_var) if update else None, ptr(ws), nbytes)
+        else:
+            mean = bn.running_mean.contiguous()
+            invstd = torch.rsqrt(bn.running_var + bn.eps)
+        out = torch.empty(N, Cout, dtype=_F32, device=dev)
+        arg = torch.empty(N, Cout, dtype=torch.uint8, device=dev)
+        call('dc_central_fwd', ptr(graph.idx), N, k, Cin, Cout, ptr(x), ldx, ptr(weight), ptr(gamma), ptr(beta), ptr(mean), ptr(invstd),
+             float(slope), ptr(out), Cout, ptr(arg))
+        ctx.graph, ctx.slope, ctx.use_batch = graph, slope, use_batch
+        ctx.save_for_backward(x, weight, gamma, beta, mean, invstd, moments, arg)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        x, weight, gamma, beta, mean, invstd, moments, arg = ctx.saved_tensors
+        g = ctx.graph
+        x, ldx = _mat(x)
+        dout, ldd = _mat(dout, 'grad_output')
+        N, k, Cin, Cout = g.N, g.k, x.size(1), weight.size(0)
+        dev = x.device
+        nbytes = query('dc_central_ws_bytes', N, k, Cin, Cout)
+        ws = workspace(nbytes, dev)
+        dW = torch.empty(Cout, Cin, dtype=_F32, device=dev)
+        dgamma = torch.empty(Cout, dtype=_F32, device=dev)
+        dbeta = torch.empty(Cout, dtype=_F32, device=dev)
+        dx, in_ptr, in_edge = None, None, None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty(N, Cin, dtype=_F32, device=dev)
+            in_ptr, in_edge = g.transpose()
+        call('dc_central_bwd', ptr(g.idx), ptr(in_ptr), ptr(in_edge), N, k, Cin, Cout, ptr(x), ldx, ptr(weight), ptr(gamma), ptr(beta),
+             ptr(mean), ptr(invstd), ptr(moments), float(ctx.slope), int(ctx.use_batch), ptr(arg), ptr(dout), ldd,
+             ptr(dW), ptr(dgamma), ptr(dbeta), ptr(dx), Cin, ptr(ws), nbytes)
+        return (dx, dW, dgamma if gamma is not None else None, dbeta if beta is not None else None, None, None, None)
+
+
+def centralized_max_supported(in_channels, k):
+    return in_channels <= query('dc_central_max_cin') and k <= 64
+
+
+def centralized_max(x, weight, bn, graph, slope):
+    return _CentralizedMax.apply(x, weight, bn.weight, bn.bias, bn, graph, float(slope))
+
+
 class _Pool(torch.autograd.Function):
     """mode 'max' | 'mean' | 'maxmean' ([max | mean] side by side, deltanet_classification.py:46-49)."""
 

@@ -134,6 +134,24 @@ int dc_segmax_fwd(const float* in, int N, int k, int C, const int32_t* idx_or_nu
                   uint8_t* arg, void* stream);
 int dc_segmax_bwd(const float* dout, int64_t ldd, int N, int k, int C, const uint8_t* arg, float* din, void* stream);
 
+/* Fused form of the same three lines for Cin <= dc_central_max_cin() (4), k <= 64 and a depth-1 edge MLP:
+ * scatter_max(LeakyReLU(BatchNorm(Linear(x[col]-x[row]))), row) without any [E,*] temporary.  dc_central_stats gives the
+ * batch statistics over the E = N*k edge rows from the moments of the edge offsets (training mode; in eval mode pass the
+ * running statistics to dc_central_fwd directly); moments = 20 doubles kept for dc_central_bwd. */
+int dc_central_max_cin(void);
+size_t dc_central_ws_bytes(int N, int k, int Cin, int Cout);
+int dc_central_stats(const int32_t* idx, int N, int k, int Cin, int Cout, const float* x, int64_t ldx, const float* W,
+                     float eps, float momentum, double* moments, float* mean, float* invstd,
+                     float* running_mean_or_null, float* running_var_or_null, void* ws, size_t ws_bytes, void* stream);
+int dc_central_fwd(const int32_t* idx, int N, int k, int Cin, int Cout, const float* x, int64_t ldx, const float* W,
+                   const float* gamma_or_null, const float* beta_or_null, const float* mean, const float* invstd, float slope,
+                   float* out, int64_t ldo, uint8_t* arg, void* stream);
+int dc_central_bwd(const int32_t* idx, const int32_t* in_ptr_or_null, const int32_t* in_edge_or_null, int N, int k, int Cin, int Cout,
+                   const float* x, int64_t ldx, const float* W, const float* gamma_or_null, const float* beta_or_null,
+                   const float* mean, const float* invstd, const double* moments, float slope, int training,
+                   const uint8_t* arg, const float* dout, int64_t ldd, float* dW, float* dgamma, float* dbeta,
+                   float* dx_or_null, int64_t ld_dx, void* ws, size_t ws_bytes, void* stream);
+
 /* ---- BatchNorm1d wrapper + LeakyReLU (nonlin.py:11-35, mlp.py:7-11) -------------------------- */
 
 size_t dc_colreduce_ws_bytes(int C);
