@@ -197,6 +197,7 @@ def run_reference_arm(args):
     rank = int(os.environ.get('RANK', '0'))
     if rank != 0:
         return
+    torch.set_num_threads(os.cpu_count() or 1)          # torchrun pins OMP_NUM_THREADS=1; use all host cores
     cores = torch.get_num_threads()
     clouds = 4
     probe = cpu_port_steps(1, 0, 2)[0] / 2                                   # size the sample: seconds per cloud
@@ -236,6 +237,7 @@ def run_cuda_arm(args):
     torch.cuda.set_device(local)
     dev = torch.device('cuda', local)
     if world > 1:
+        os.environ['NCCL_DEBUG'] = os.environ.get('DC_NCCL_DEBUG', 'WARN')     # stdout must carry exactly one JSON line
         dist.init_process_group('nccl', device_id=dev)
     lib = _lib.load()
 
@@ -366,6 +368,7 @@ def run_cuda_arm(args):
 
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
+        torch.set_num_threads(os.cpu_count() or 1)
         cores = torch.get_num_threads()
         t = cpu_port_steps(2, 1, 4)
         v = 4 / (sum(t) / len(t))
