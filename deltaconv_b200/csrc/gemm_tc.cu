@@ -15,8 +15,9 @@
 // column chunks, each chunk 32 reduction rows x 128 B.  Both are canonical UMMA SWIZZLE_128B layouts,
 // so no transposed copy of any activation is ever made.
 //
-// Roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer,
-// warps 2..5 = converters, then epilogue (TMEM -> registers -> HBM; warp w owns TMEM lanes 32*(w%4)..).
+// Roles (320 threads, persistent CTA per SM): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer,
+// warps 2..5 = converters, warps 6..9 = epilogue (TMEM -> registers -> HBM; warp w owns TMEM lanes 32*(w%4)..);
+// two TMEM accumulators so the epilogue of one tile overlaps the main loop of the next.
 #include "common.cuh"
 #include <cuda.h>
 
@@ -24,7 +25,7 @@ namespace {
 
 constexpr int TC_BM = 128;          // UMMA_M (cta_group::1)
 constexpr int TC_BK = 32;           // fp32 elements per k-block = one 128-byte swizzle span
-constexpr int TC_THREADS = 192;
+constexpr int TC_THREADS = 320;       // TMA, MMA, 4 converter warps, 4 epilogue warps
 constexpr int TC_MAX_STAGES = 4;
 
 struct TcArgs {
@@ -33,7 +34,6 @@ struct TcArgs {
     int M, N, K;
     int kb_per_split;       // k-blocks per grid.z slice
     float* partial;         // [splits][M][N] when split-K
-    int stages;
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -91,39 +91,41 @@ __device__ __forceinline__ void umma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
 
-template <int BN, bool A_MN, bool B_MN, bool SPLIT3>
-__global__ void __launch_bounds__(TC_THREADS) tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA,
-                                                             const __grid_constant__ CUtensorMap tmB, TcArgs g) {
+// Persistent kernel: every CTA walks the tile list (n fastest, so CTAs that run together share the A rows in L2)
+// with five roles that only meet at mbarriers.  Two TMEM accumulators let the epilogue of tile t overlap the
+// main loop of tile t+1.
+template <int BN, bool A_MN, bool B_MN, bool SPLIT3, int STAGES>
+__global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                                const __grid_constant__ CUtensorMap tmB, TcArgs g) {
     constexpr uint32_t A_BYTES = TC_BM * 128, B_BYTES = BN * 128;
     constexpr uint32_t STAGE_BYTES = (A_BYTES + B_BYTES) * (SPLIT3 ? 2 : 1);
     constexpr uint32_t CHUNK_BYTES = TC_BK * 128;                 // one 32-wide MN chunk of an MN-major tile
-    constexpr uint32_t TMEM_COLS = BN <= 32 ? 32 : BN <= 64 ? 64 : BN <= 128 ? 128 : 256;
+    constexpr uint32_t TMEM_COLS = 2 * BN <= 32 ? 32 : 2 * BN <= 64 ? 64 : 2 * BN <= 128 ? 128 : 2 * BN <= 256 ? 256 : 512;
     // instruction descriptor (cute::UMMA::InstrDescriptor): c=F32, a=b=TF32, majors, N>>3, M>>4
     constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
                                ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
 
     extern __shared__ unsigned char smem_raw[];
-    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;          // SWIZZLE_128B atoms are 1024-byte aligned
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;          // swizzle atoms are 1024-byte aligned
     unsigned char* base_ptr = smem_raw + (base - smem_u32(smem_raw));
-    const int stages = g.stages;
-    // barriers and the TMEM base live after the stage buffers
-    const uint32_t bar_base = base + stages * STAGE_BYTES;
+    const uint32_t bar_base = base + STAGES * STAGE_BYTES;
     auto full_bar = [&](int s) { return bar_base + 8u * s; };
     auto empty_bar = [&](int s) { return bar_base + 8u * (TC_MAX_STAGES + s); };
     auto conv_bar = [&](int s) { return bar_base + 8u * (2 * TC_MAX_STAGES + s); };
-    const uint32_t accum_bar = bar_base + 8u * (3 * TC_MAX_STAGES);
-    const uint32_t tmem_slot = accum_bar + 8u;
+    auto acc_full_bar = [&](int a) { return bar_base + 8u * (3 * TC_MAX_STAGES + a); };
+    auto acc_empty_bar = [&](int a) { return bar_base + 8u * (3 * TC_MAX_STAGES + 2 + a); };
+    const uint32_t tmem_slot = bar_base + 8u * (3 * TC_MAX_STAGES + 4);
     volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(base_ptr + (tmem_slot - base));
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int n0 = blockIdx.x * BN, m0 = blockIdx.y * TC_BM;
+    const int tiles_n = (g.N + BN - 1) / BN, tiles_m = (g.M + TC_BM - 1) / TC_BM;
     const int total_kb = (g.K + TC_BK - 1) / TC_BK;
-    const int kb_begin = blockIdx.z * g.kb_per_split;
-    const int nkb = min(total_kb, kb_begin + g.kb_per_split) - kb_begin;
+    const int splits = (total_kb + g.kb_per_split - 1) / g.kb_per_split;
+    const long long num_tiles = (long long)tiles_n * tiles_m * splits;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < stages; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); mbar_init(conv_bar(s), 4); }
-        mbar_init(accum_bar, 1);
+        for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); mbar_init(conv_bar(s), 4); }
+        for (int a = 0; a < 2; ++a) { mbar_init(acc_full_bar(a), 1); mbar_init(acc_empty_bar(a), 4); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
@@ -139,127 +141,167 @@ __global__ void __launch_bounds__(TC_THREADS) tc_gemm_kernel(const __grid_consta
     auto stage_a_lo = [&](int s) { return base + s * STAGE_BYTES + A_BYTES; };
     auto stage_b = [&](int s) { return base + s * STAGE_BYTES + (SPLIT3 ? 2 : 1) * A_BYTES; };
     auto stage_b_lo = [&](int s) { return base + s * STAGE_BYTES + 2 * A_BYTES + B_BYTES; };
+    // tile id -> (m0, n0, first k-block, number of k-blocks)
+    auto decode = [&](long long tile, int& m0, int& n0, int& kb_begin, int& nkb) {
+        const int nt = (int)(tile % tiles_n);
+        const long long r = tile / tiles_n;
+        const int mt = (int)(r % tiles_m), z = (int)(r / tiles_m);
+        m0 = mt * TC_BM; n0 = nt * BN;
+        kb_begin = z * g.kb_per_split;
+        nkb = min(total_kb, kb_begin + g.kb_per_split) - kb_begin;
+    };
 
     if (warp == 0) {
         // ===================== TMA producer =====================
         if (lane == 0) {
             asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
             asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
-            for (int it = 0; it < nkb; ++it) {
-                const int s = it % stages;
-                const uint32_t ph = (it / stages) & 1;
-                mbar_wait(empty_bar(s), ph ^ 1u);
-                mbar_expect_tx(full_bar(s), A_BYTES + B_BYTES);
-                const int k0 = (kb_begin + it) * TC_BK;
-                if (!A_MN) tma_load_2d(stage_a(s), &tmA, full_bar(s), k0, m0);
-                else
+            uint32_t it = 0;
+            for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                int m0, n0, kb_begin, nkb;
+                decode(tile, m0, n0, kb_begin, nkb);
+                for (int kb = 0; kb < nkb; ++kb, ++it) {
+                    const int s = it % STAGES;
+                    const uint32_t ph = (it / STAGES) & 1;
+                    mbar_wait(empty_bar(s), ph ^ 1u);
+                    mbar_expect_tx(full_bar(s), A_BYTES + B_BYTES);
+                    const int k0 = (kb_begin + kb) * TC_BK;
+                    if (!A_MN) tma_load_2d(stage_a(s), &tmA, full_bar(s), k0, m0);
+                    else
 #pragma unroll
-                    for (int c = 0; c < TC_BM / 32; ++c) tma_load_2d(stage_a(s) + c * CHUNK_BYTES, &tmA, full_bar(s), m0 + 32 * c, k0);
-                if (!B_MN) tma_load_2d(stage_b(s), &tmB, full_bar(s), k0, n0);
-                else
+                        for (int c = 0; c < TC_BM / 32; ++c) tma_load_2d(stage_a(s) + c * CHUNK_BYTES, &tmA, full_bar(s), m0 + 32 * c, k0);
+                    if (!B_MN) tma_load_2d(stage_b(s), &tmB, full_bar(s), k0, n0);
+                    else
 #pragma unroll
-                    for (int c = 0; c < BN / 32; ++c) tma_load_2d(stage_b(s) + c * CHUNK_BYTES, &tmB, full_bar(s), n0 + 32 * c, k0);
+                        for (int c = 0; c < BN / 32; ++c) tma_load_2d(stage_b(s) + c * CHUNK_BYTES, &tmB, full_bar(s), n0 + 32 * c, k0);
+                }
             }
         }
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
-        for (int it = 0; it < nkb; ++it) {
-            const int s = it % stages;
-            const uint32_t ph = (it / stages) & 1;
-            mbar_wait(SPLIT3 ? conv_bar(s) : full_bar(s), ph);
+        uint32_t it = 0, tcount = 0;
+        for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tcount) {
+            int m0, n0, kb_begin, nkb;
+            decode(tile, m0, n0, kb_begin, nkb);
+            const uint32_t acc = tcount & 1, acc_ph = (tcount >> 1) & 1;
+            mbar_wait(acc_empty_bar(acc), acc_ph ^ 1u);            // the epilogue has drained this accumulator
             tc_fence_after();
-            if (lane == 0) {
+            const uint32_t tmem_acc = tmem_base + acc * BN;
+            for (int kb = 0; kb < nkb; ++kb, ++it) {
+                const int s = it % STAGES;
+                const uint32_t ph = (it / STAGES) & 1;
+                mbar_wait(SPLIT3 ? conv_bar(s) : full_bar(s), ph);
+                tc_fence_after();
+                if (lane == 0) {
 #pragma unroll
-                for (int kk = 0; kk < TC_BK / 8; ++kk) {          // UMMA_K = 8 for tf32
-                    // K-major: +32 B inside the swizzle span; MN-major: next 8-row group (+1024 B)
-                    const uint32_t a_off = A_MN ? kk * 1024u : kk * 32u, b_off = B_MN ? kk * 1024u : kk * 32u;
-                    // K-major: 8-row groups 1024 B apart.  MN-major: 32-wide chunks CHUNK_BYTES apart (LBO),
-                    // 4-row groups of the 32-byte-atom swizzle 512 B apart (SBO).
-                    const uint32_t a_lbo = A_MN ? CHUNK_BYTES : 16u, b_lbo = B_MN ? CHUNK_BYTES : 16u;
-                    const uint32_t a_sbo = A_MN ? 512u : 1024u, b_sbo = B_MN ? 512u : 1024u;
-                    const uint32_t a_lt = A_MN ? 1u : 2u, b_lt = B_MN ? 1u : 2u;
-                    const uint64_t da = umma_desc(stage_a(s) + a_off, a_lbo, a_sbo, a_lt);
-                    const uint64_t db = umma_desc(stage_b(s) + b_off, b_lbo, b_sbo, b_lt);
-                    umma_tf32(tmem_base, da, db, IDESC, (it > 0 || kk > 0) ? 1u : 0u);
-                    if (SPLIT3) {
-                        const uint64_t da_lo = umma_desc(stage_a_lo(s) + a_off, a_lbo, a_sbo, a_lt);
-                        const uint64_t db_lo = umma_desc(stage_b_lo(s) + b_off, b_lbo, b_sbo, b_lt);
-                        umma_tf32(tmem_base, da_lo, db, IDESC, 1u);
-                        umma_tf32(tmem_base, da, db_lo, IDESC, 1u);
+                    for (int kk = 0; kk < TC_BK / 8; ++kk) {          // UMMA_K = 8 for tf32
+                        // K-major: +32 B inside the swizzle span; MN-major: next 8-row group (+1024 B)
+                        const uint32_t a_off = A_MN ? kk * 1024u : kk * 32u, b_off = B_MN ? kk * 1024u : kk * 32u;
+                        // K-major: 8-row groups 1024 B apart.  MN-major: 32-wide chunks CHUNK_BYTES apart (LBO),
+                        // 4-row groups of the 32-byte-atom swizzle 512 B apart (SBO).
+                        const uint32_t a_lbo = A_MN ? CHUNK_BYTES : 16u, b_lbo = B_MN ? CHUNK_BYTES : 16u;
+                        const uint32_t a_sbo = A_MN ? 512u : 1024u, b_sbo = B_MN ? 512u : 1024u;
+                        const uint32_t a_lt = A_MN ? 1u : 2u, b_lt = B_MN ? 1u : 2u;
+                        const uint64_t da = umma_desc(stage_a(s) + a_off, a_lbo, a_sbo, a_lt);
+                        const uint64_t db = umma_desc(stage_b(s) + b_off, b_lbo, b_sbo, b_lt);
+                        umma_tf32(tmem_acc, da, db, IDESC, (kb > 0 || kk > 0) ? 1u : 0u);
+                        if (SPLIT3) {
+                            const uint64_t da_lo = umma_desc(stage_a_lo(s) + a_off, a_lbo, a_sbo, a_lt);
+                            const uint64_t db_lo = umma_desc(stage_b_lo(s) + b_off, b_lbo, b_sbo, b_lt);
+                            umma_tf32(tmem_acc, da_lo, db, IDESC, 1u);
+                            umma_tf32(tmem_acc, da, db_lo, IDESC, 1u);
+                        }
                     }
+                    umma_commit(empty_bar(s));                        // frees the stage when the MMAs have read it
+                    if (kb == nkb - 1) umma_commit(acc_full_bar(acc)); // accumulator complete
                 }
-                umma_commit(empty_bar(s));                        // frees the stage when the MMAs have read it
-                if (it == nkb - 1) umma_commit(accum_bar);        // accumulator complete
+                __syncwarp();
             }
-            __syncwarp();
+        }
+    } else if (warp < 6) {
+        // ===================== converters (3xTF32 split of every landed stage) =====================
+        if (SPLIT3) {
+            const int t = threadIdx.x - 64;                           // 0..127
+            uint32_t it = 0;
+            for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                int m0, n0, kb_begin, nkb;
+                decode(tile, m0, n0, kb_begin, nkb);
+                for (int kb = 0; kb < nkb; ++kb, ++it) {
+                    const int s = it % STAGES;
+                    const uint32_t ph = (it / STAGES) & 1;
+                    mbar_wait(full_bar(s), ph);
+                    float4* a_hi = reinterpret_cast<float4*>(base_ptr + (stage_a(s) - base));
+                    float4* a_lo = reinterpret_cast<float4*>(base_ptr + (stage_a_lo(s) - base));
+                    float4* b_hi = reinterpret_cast<float4*>(base_ptr + (stage_b(s) - base));
+                    float4* b_lo = reinterpret_cast<float4*>(base_ptr + (stage_b_lo(s) - base));
+                    auto split = [](float4* hi, float4* lo, int i) {
+                        float4 x = hi[i], h, l;
+                        h.x = __uint_as_float(__float_as_uint(x.x) & 0xffffe000u); l.x = x.x - h.x;
+                        h.y = __uint_as_float(__float_as_uint(x.y) & 0xffffe000u); l.y = x.y - h.y;
+                        h.z = __uint_as_float(__float_as_uint(x.z) & 0xffffe000u); l.z = x.z - h.z;
+                        h.w = __uint_as_float(__float_as_uint(x.w) & 0xffffe000u); l.w = x.w - h.w;
+                        hi[i] = h; lo[i] = l;
+                    };
+#pragma unroll
+                    for (int i = 0; i < (int)(A_BYTES / 16) / 128; ++i) split(a_hi, a_lo, t + 128 * i);
+#pragma unroll
+                    for (int i = 0; i < (int)(B_BYTES / 16) / 128; ++i) split(b_hi, b_lo, t + 128 * i);
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // generic writes -> visible to the MMA (async proxy)
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(conv_bar(s));
+                }
+            }
         }
     } else {
-        // ===================== converters, then epilogue =====================
-        const int t = threadIdx.x - 64;                           // 0..127
-        if (SPLIT3) {
-            for (int it = 0; it < nkb; ++it) {
-                const int s = it % stages;
-                const uint32_t ph = (it / stages) & 1;
-                mbar_wait(full_bar(s), ph);
-                float4* a_hi = reinterpret_cast<float4*>(base_ptr + (stage_a(s) - base));
-                float4* a_lo = reinterpret_cast<float4*>(base_ptr + (stage_a_lo(s) - base));
-                float4* b_hi = reinterpret_cast<float4*>(base_ptr + (stage_b(s) - base));
-                float4* b_lo = reinterpret_cast<float4*>(base_ptr + (stage_b_lo(s) - base));
-                auto split = [](float4* hi, float4* lo, int i) {
-                    float4 x = hi[i], h, l;
-                    h.x = __uint_as_float(__float_as_uint(x.x) & 0xffffe000u); l.x = x.x - h.x;
-                    h.y = __uint_as_float(__float_as_uint(x.y) & 0xffffe000u); l.y = x.y - h.y;
-                    h.z = __uint_as_float(__float_as_uint(x.z) & 0xffffe000u); l.z = x.z - h.z;
-                    h.w = __uint_as_float(__float_as_uint(x.w) & 0xffffe000u); l.w = x.w - h.w;
-                    hi[i] = h; lo[i] = l;
-                };
-#pragma unroll
-                for (int i = 0; i < (int)(A_BYTES / 16) / 128; ++i) split(a_hi, a_lo, t + 128 * i);
-#pragma unroll
-                for (int i = 0; i < (int)(B_BYTES / 16) / 128; ++i) split(b_hi, b_lo, t + 128 * i);
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // generic writes -> visible to the MMA (async proxy)
-                __syncwarp();
-                if (lane == 0) mbar_arrive(conv_bar(s));
-            }
-        }
-        mbar_wait(accum_bar, 0);
-        tc_fence_after();
+        // ===================== epilogue: TMEM -> registers -> HBM =====================
         const int q = warp & 3;                                   // TMEM lane quarter this warp may read
-        const int row = m0 + q * 32 + lane;
-        float* out = g.partial ? g.partial + (size_t)blockIdx.z * g.M * g.N : g.C;
-        const long long ldo = g.partial ? g.N : g.ldc;
-        const bool vec_ok = (ldo % 4 == 0) && ((reinterpret_cast<uintptr_t>(out) & 15u) == 0);
+        uint32_t tcount = 0;
+        for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tcount) {
+            int m0, n0, kb_begin, nkb;
+            decode(tile, m0, n0, kb_begin, nkb);
+            const uint32_t acc = tcount & 1, acc_ph = (tcount >> 1) & 1;
+            mbar_wait(acc_full_bar(acc), acc_ph);
+            tc_fence_after();
+            const int z = (int)(tile / ((long long)tiles_n * tiles_m));
+            const int row = m0 + q * 32 + lane;
+            float* out = g.partial ? g.partial + (size_t)z * g.M * g.N : g.C;
+            const long long ldo = g.partial ? g.N : g.ldc;
+            const bool vec_ok = (ldo % 4 == 0) && ((reinterpret_cast<uintptr_t>(out) & 15u) == 0);
 #pragma unroll 1
-        for (int c0 = 0; c0 < BN; c0 += 16) {
-            if (n0 + c0 >= g.N) break;                            // warp-uniform
-            uint32_t r[16];
-            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0;
-            asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
-                         : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-                           "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-                         : "r"(taddr));
-            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-            if (row < g.M) {
-                float* dst = out + (long long)row * ldo + n0 + c0;
+            for (int c0 = 0; c0 < BN; c0 += 16) {
+                if (n0 + c0 >= g.N) break;                            // warp-uniform
+                uint32_t r[16];
+                const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(q * 32) << 16) + (uint32_t)c0;
+                asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+                             : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                               "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+                             : "r"(taddr));
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                if (row < g.M) {
+                    float* dst = out + (long long)row * ldo + n0 + c0;
 #pragma unroll
-                for (int v = 0; v < 4; ++v) {
-                    const int col = n0 + c0 + 4 * v;
-                    float4 o = make_float4(__uint_as_float(r[4 * v]), __uint_as_float(r[4 * v + 1]), __uint_as_float(r[4 * v + 2]), __uint_as_float(r[4 * v + 3]));
-                    if (!g.partial && g.bias) {
-                        if (col < g.N) o.x += __ldg(g.bias + col);
-                        if (col + 1 < g.N) o.y += __ldg(g.bias + col + 1);
-                        if (col + 2 < g.N) o.z += __ldg(g.bias + col + 2);
-                        if (col + 3 < g.N) o.w += __ldg(g.bias + col + 3);
-                    }
-                    if (vec_ok && col + 3 < g.N) *reinterpret_cast<float4*>(dst + 4 * v) = o;
-                    else {
-                        if (col < g.N) dst[4 * v] = o.x;
-                        if (col + 1 < g.N) dst[4 * v + 1] = o.y;
-                        if (col + 2 < g.N) dst[4 * v + 2] = o.z;
-                        if (col + 3 < g.N) dst[4 * v + 3] = o.w;
+                    for (int v = 0; v < 4; ++v) {
+                        const int col = n0 + c0 + 4 * v;
+                        float4 o = make_float4(__uint_as_float(r[4 * v]), __uint_as_float(r[4 * v + 1]), __uint_as_float(r[4 * v + 2]), __uint_as_float(r[4 * v + 3]));
+                        if (!g.partial && g.bias) {
+                            if (col < g.N) o.x += __ldg(g.bias + col);
+                            if (col + 1 < g.N) o.y += __ldg(g.bias + col + 1);
+                            if (col + 2 < g.N) o.z += __ldg(g.bias + col + 2);
+                            if (col + 3 < g.N) o.w += __ldg(g.bias + col + 3);
+                        }
+                        if (vec_ok && col + 3 < g.N) *reinterpret_cast<float4*>(dst + 4 * v) = o;
+                        else {
+                            if (col < g.N) dst[4 * v] = o.x;
+                            if (col + 1 < g.N) dst[4 * v + 1] = o.y;
+                            if (col + 2 < g.N) dst[4 * v + 2] = o.z;
+                            if (col + 3 < g.N) dst[4 * v + 3] = o.w;
+                        }
                     }
                 }
             }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(acc_empty_bar(acc));           // this warp's quarter of the accumulator is free
         }
     }
     tc_fence_before();
@@ -309,34 +351,31 @@ bool make_map(CUtensorMap* map, const float* ptr, long long inner, long long out
               mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
-size_t tc_smem_bytes(int BN, bool split3, int stages) {
-    return (size_t)stages * (TC_BM + BN) * 128 * (split3 ? 2 : 1) + 1024 /*alignment*/ + 8 * (3 * TC_MAX_STAGES + 2) + 16;
-}
+template <int BN, bool SPLIT3> struct TcStages {
+    static constexpr int per_stage = (TC_BM + BN) * 128 * (SPLIT3 ? 2 : 1);
+    static constexpr int value = (200 * 1024) / per_stage > TC_MAX_STAGES ? TC_MAX_STAGES : (200 * 1024) / per_stage;
+};
 
 template <int BN, bool A_MN, bool B_MN, bool SPLIT3>
-int launch_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, TcArgs g, dim3 grid, cudaStream_t st) {
-    // as many stages as fit while keeping two CTAs per SM when the tile is small
-    const size_t per_stage = (size_t)(TC_BM + BN) * 128 * (SPLIT3 ? 2 : 1);
-    int stages = per_stage <= 49152 ? 2 : (int)((200 * 1024) / per_stage);
-    if (stages > TC_MAX_STAGES) stages = TC_MAX_STAGES;
-    if (stages < 2) stages = 2;
-    g.stages = stages;
-    const size_t smem = tc_smem_bytes(BN, SPLIT3, stages);
-    DC_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<BN, A_MN, B_MN, SPLIT3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    tc_gemm_kernel<BN, A_MN, B_MN, SPLIT3><<<grid, TC_THREADS, smem, st>>>(tmA, tmB, g);
+int launch_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const TcArgs& g, long long num_tiles, cudaStream_t st) {
+    constexpr int STAGES = TcStages<BN, SPLIT3>::value;
+    static_assert(STAGES >= 2, "tile too large for shared memory");
+    const size_t smem = (size_t)STAGES * TcStages<BN, SPLIT3>::per_stage + 1024 /*alignment*/ + 8 * (3 * TC_MAX_STAGES + 4) + 16;
+    DC_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<BN, A_MN, B_MN, SPLIT3, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const long long sms = dc_sm_count();
+    const unsigned grid = (unsigned)(num_tiles < sms ? num_tiles : sms);       // persistent: one CTA per SM
+    tc_gemm_kernel<BN, A_MN, B_MN, SPLIT3, STAGES><<<grid, TC_THREADS, smem, st>>>(tmA, tmB, g);
     return DC_OK;
 }
 
 template <bool A_MN, bool B_MN>
-int dispatch_tc(int BN, bool split3, const CUtensorMap& a, const CUtensorMap& b, const TcArgs& g, dim3 grid, cudaStream_t st) {
+int dispatch_tc(int BN, bool split3, const CUtensorMap& a, const CUtensorMap& b, const TcArgs& g, long long tiles, cudaStream_t st) {
     if (split3) {
-        if (BN == 64) return launch_tc<64, A_MN, B_MN, true>(a, b, g, grid, st);
-        if (BN == 128) return launch_tc<128, A_MN, B_MN, true>(a, b, g, grid, st);
-        return launch_tc<256, A_MN, B_MN, true>(a, b, g, grid, st);
+        if (BN == 64) return launch_tc<64, A_MN, B_MN, true>(a, b, g, tiles, st);
+        return launch_tc<128, A_MN, B_MN, true>(a, b, g, tiles, st);
     }
-    if (BN == 64) return launch_tc<64, A_MN, B_MN, false>(a, b, g, grid, st);
-    if (BN == 128) return launch_tc<128, A_MN, B_MN, false>(a, b, g, grid, st);
-    return launch_tc<256, A_MN, B_MN, false>(a, b, g, grid, st);
+    if (BN == 64) return launch_tc<64, A_MN, B_MN, false>(a, b, g, tiles, st);
+    return launch_tc<128, A_MN, B_MN, false>(a, b, g, tiles, st);
 }
 
 }  // namespace
@@ -361,7 +400,7 @@ int dc_tc_gemm(const float* A, long long lda, int a_mn, const float* B, long lon
     if (g_tc_mode == 0 || M < 64 || N < 16 || K < 8) return 1;
     if (lda % 4 || ldb % 4 || (reinterpret_cast<uintptr_t>(A) & 15u) || (reinterpret_cast<uintptr_t>(B) & 15u)) return 1;
     if (M >= 2147483647LL || K >= 2147483647LL) return 1;
-    const int BN = N <= 64 ? 64 : N <= 128 ? 128 : 256;
+    const int BN = N <= 64 ? 64 : 128;
     CUtensorMap tmA, tmB;
     bool ok = a_mn ? make_map(&tmA, A, M, K, lda, TC_BK, true) : make_map(&tmA, A, K, M, lda, TC_BM, false);
     ok = ok && (b_mn ? make_map(&tmB, B, N, K, ldb, TC_BK, true) : make_map(&tmB, B, K, N, ldb, BN, false));
@@ -381,13 +420,12 @@ int dc_tc_gemm(const float* A, long long lda, int a_mn, const float* B, long lon
     g.kb_per_split = (total_kb + splits - 1) / splits;
     splits = (total_kb + g.kb_per_split - 1) / g.kb_per_split;
     g.partial = splits > 1 ? (float*)ws : nullptr;
-    dim3 grid((unsigned)((N + BN - 1) / BN), (unsigned)((M + TC_BM - 1) / TC_BM), (unsigned)splits);
-    if (grid.y > 65535u) return 1;
+    const long long num_tiles = tiles * splits;
     const bool split3 = g_tc_mode == 3;
     int rc;
-    if (!a_mn && !b_mn) rc = dispatch_tc<false, false>(BN, split3, tmA, tmB, g, grid, st);
-    else if (!a_mn && b_mn) rc = dispatch_tc<false, true>(BN, split3, tmA, tmB, g, grid, st);
-    else if (a_mn && b_mn) rc = dispatch_tc<true, true>(BN, split3, tmA, tmB, g, grid, st);
+    if (!a_mn && !b_mn) rc = dispatch_tc<false, false>(BN, split3, tmA, tmB, g, num_tiles, st);
+    else if (!a_mn && b_mn) rc = dispatch_tc<false, true>(BN, split3, tmA, tmB, g, num_tiles, st);
+    else if (a_mn && b_mn) rc = dispatch_tc<true, true>(BN, split3, tmA, tmB, g, num_tiles, st);
     else return 1;
     if (rc) return rc < 0 ? rc : -rc;
     *launches = 1;
@@ -401,7 +439,7 @@ int dc_tc_gemm(const float* A, long long lda, int a_mn, const float* B, long lon
 
 // workspace for the split-K partials of a product with output M x N and reduction K
 size_t dc_tc_ws_bytes(long long M, long long N, long long K) {
-    const int BN = N <= 64 ? 64 : N <= 128 ? 128 : 256;
+    const int BN = N <= 64 ? 64 : 128;
     const long long total_kb = (K + TC_BK - 1) / TC_BK;
     const long long tiles = ((M + TC_BM - 1) / TC_BM) * ((N + BN - 1) / BN);
     const long long target = 2LL * dc_sm_count();

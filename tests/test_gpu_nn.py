@@ -399,3 +399,50 @@ def test_graphed_train_step_matches_eager():
     assert losses_g == pytest.approx(losses_e[2:], rel=1e-5)
     for (n1, p1), (n2, p2) in zip(eager.named_parameters(), graphed_net.named_parameters()):
         assert torch.allclose(p1, p2, rtol=1e-5, atol=1e-6), n1
+
+
+def test_config3_segmentation_shapenet_shape_vs_oracle():
+    """BASELINE configs[2] architecture (convs [64,128,256], depth-2 MLPs, embedding 1024, categorical vector, 50
+    classes, k=30, 2048 points) on 2 clouds: logits and loss against the fp64 oracle, training-mode BN."""
+    D = dc()
+    data = D.utils.synthetic_batch(2, 2048, config=3, num_classes=50, per_point_labels=True, categories=16)
+    kw = dict(conv_channels=[64, 128, 256], mlp_depth=2, embedding_size=1024, categorical_vector=True, num_neighbors=30)
+    model = no_dropout(D.utils.fill_deterministic(D.models.DeltaNetSegmentation(3, 50, **kw), 7))
+    oracle = no_dropout(on.DeltaNetSegmentation(3, 50, **kw)).double()
+    oracle.load_state_dict({k_: (v_.double() if v_.is_floating_point() else v_) for k_, v_ in model.state_dict().items()})
+    model = model.to(DEV).train()
+    oracle.train()
+    logits = model(data.to(DEV))
+    with torch.no_grad():
+        ref = oracle(data.double())
+    assert tuple(logits.shape) == (4096, 50)
+    assert report('config3_seg.logits_train', rel_err(logits.detach().cpu(), ref)) < LOGIT_REL
+    F.cross_entropy(logits, data.y.to(DEV)).backward()
+    assert all(torch.isfinite(p.grad).all() for p in model.parameters() if p.grad is not None)
+
+
+def test_full_size_configs_run_and_are_deterministic():
+    """configs[2] (16 x 2048, k=30, segmentation) and configs[4] (32 x 2048, k=20, no normals -> estimated frames,
+    15 classes) at full size: a training step is finite and bitwise reproducible run to run."""
+    D = dc()
+    cases = [
+        (lambda: D.models.DeltaNetSegmentation(3, 50, conv_channels=[64, 128, 256], mlp_depth=2, embedding_size=1024,
+                                               categorical_vector=True, num_neighbors=30),
+         D.utils.synthetic_batch(16, 2048, config=3, num_classes=50, per_point_labels=True, categories=16)),
+        (lambda: D.models.DeltaNetClassification(3, 15, conv_channels=[64, 64, 64, 128], num_neighbors=20),
+         D.utils.synthetic_batch(32, 2048, config=5, num_classes=15, normals=False)),
+    ]
+    for build, data in cases:
+        data = data.to(DEV)
+        if not hasattr(data, 'norm'):
+            data.norm = None
+        outs = []
+        for _ in range(2):
+            model = no_dropout(D.utils.fill_deterministic(build(), 3)).to(DEV).train()
+            logits = model(data)
+            loss = F.cross_entropy(logits, data.y)
+            loss.backward()
+            g = torch.cat([p.grad.flatten() for p in model.parameters() if p.grad is not None])
+            assert torch.isfinite(logits).all() and torch.isfinite(g).all()
+            outs.append((logits.detach().clone(), g.clone()))
+        assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
