@@ -91,6 +91,9 @@ __global__ void cloud_mean_kernel(const float* __restrict__ m, const int* __rest
 }
 
 // ---- pass B ---------------------------------------------------------------------------------
+// One thread per point; its k slots live slot-major in shared memory.  Gathers are issued four
+// slots at a time before any dependent arithmetic (the compiler cannot hoist them across the
+// shared-memory stores itself), which is what hides the L2 latency at 12-16 resident warps.
 template <int T, bool WRITE>
 __global__ void __launch_bounds__(T)
 fit_kernel(const float* __restrict__ pos, const float* __restrict__ normal, const float* __restrict__ xb,
@@ -100,7 +103,7 @@ fit_kernel(const float* __restrict__ pos, const float* __restrict__ normal, cons
            float* __restrict__ dbg_coords, float* __restrict__ dbg_weights, float* __restrict__ dbg_mapping) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int STRIDE = T + 1;
-    float4* s_dat = reinterpret_cast<float4*>(smem_raw);                        // [k][STRIDE]
+    float4* s_dat = reinterpret_cast<float4*>(smem_raw);                                   // [k][STRIDE]
     int* s_idx = reinterpret_cast<int*>(smem_raw + (size_t)k * STRIDE * sizeof(float4));   // [k][STRIDE]
 
     const int base = blockIdx.x * T;
@@ -108,9 +111,10 @@ fit_kernel(const float* __restrict__ pos, const float* __restrict__ normal, cons
     const int tile = npts * k;
     // coalesced idx tile load, transposed into slot-major shared memory
     const int* gidx = idx + (size_t)base * k;
-    for (int l = threadIdx.x; l < tile; l += T) {
-        int p = l / k, e = l - p * k;
+    for (int l = threadIdx.x, p = threadIdx.x / k, e = threadIdx.x % k; l < tile; l += T) {
         s_idx[e * STRIDE + p] = __ldg(gidx + l);
+        e += T % k; p += T / k;
+        if (e >= k) { e -= k; ++p; }
     }
     __syncthreads();
 
@@ -124,7 +128,19 @@ fit_kernel(const float* __restrict__ pos, const float* __restrict__ normal, cons
         const V3 ex = v3_load(xb + 3 * (size_t)i), ey = v3_load(yb + 3 * (size_t)i);
         const int c = cloud_of(cloud_ptr, B, i);
         const float sc = kernel_width * __ldg(abar + c);
-        const float wsum = fit_pass1(pos, N, i, k, p, n, ex, ey, sc * sc, sv);
+        const float denom = sc * sc;
+        // pass 1, four gathers in flight
+        float wsum = 0.f;
+        int e = 0;
+        for (; e + 4 <= k; e += 4) {
+            int j[4];
+            V3 pj[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { j[u] = sv.j(e + u); int jj = (j[u] < 0 || j[u] >= N) ? 0 : j[u]; pj[u] = v3_load(pos + 3 * (size_t)jj); }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { float4 cc = fit_slot_coords_loaded(pj[u], p, n, ex, ey, denom); wsum += cc.z; sv.d(e + u) = cc; }
+        }
+        for (; e < k; ++e) { float4 cc = fit_slot_coords(pos, N, sv.j(e), p, n, ex, ey, denom); wsum += cc.z; sv.d(e) = cc; }
         float z1[6], z2[6], coef[6];
         fit_pass2(N, k, wsum, fp, sv, z1, z2, coef);
         if (!WRITE) {
@@ -134,10 +150,27 @@ fit_kernel(const float* __restrict__ pos, const float* __restrict__ normal, cons
             atomicMax(S + c, __float_as_uint(s_i));
         } else {
             const float Sc = normalized ? __uint_as_float(S[c]) : 0.f;
-            fit_pass3(xb, yb, N, k, n, ex, ey, Sc, sv, z1, z2, coef,
-                      dbg_coords ? dbg_coords + (size_t)i * k * 2 : nullptr,
-                      dbg_weights ? dbg_weights + (size_t)i * k : nullptr,
-                      dbg_mapping ? dbg_mapping + (size_t)i * k * 4 : nullptr);
+            float* dc_ = dbg_coords ? dbg_coords + (size_t)i * k * 2 : nullptr;
+            float* dw_ = dbg_weights ? dbg_weights + (size_t)i * k : nullptr;
+            float* dm_ = dbg_mapping ? dbg_mapping + (size_t)i * k * 4 : nullptr;
+            e = 0;
+            for (; e + 2 <= k; e += 2) {        // pass 3, neighbour frames of two slots in flight
+                int j[2];
+                V3 xj[2], yj[2];
+#pragma unroll
+                for (int u = 0; u < 2; ++u) {
+                    j[u] = sv.j(e + u);
+                    int jj = (j[u] < 0 || j[u] >= N) ? 0 : j[u];
+                    xj[u] = v3_load(xb + 3 * (size_t)jj); yj[u] = v3_load(yb + 3 * (size_t)jj);
+                }
+#pragma unroll
+                for (int u = 0; u < 2; ++u)
+                    sv.d(e + u) = fit_slot_entry_loaded(xj[u], yj[u], !(j[u] < 0 || j[u] >= N), sv.d(e + u), n, ex, ey, Sc, z1, z2, coef,
+                                                        dc_ ? dc_ + 2 * (e + u) : nullptr, dw_ ? dw_ + (e + u) : nullptr, dm_ ? dm_ + 4 * (e + u) : nullptr);
+            }
+            for (; e < k; ++e)
+                sv.d(e) = fit_slot_entry(xb, yb, N, sv.j(e), sv.d(e), n, ex, ey, Sc, z1, z2, coef, dc_ ? dc_ + 2 * e : nullptr,
+                                         dw_ ? dw_ + e : nullptr, dm_ ? dm_ + 4 * e : nullptr);
         }
     }
     if (!WRITE) return;
@@ -145,11 +178,12 @@ fit_kernel(const float* __restrict__ pos, const float* __restrict__ normal, cons
     // coalesced G / D tile stores (float2 per slot)
     float2* gG = reinterpret_cast<float2*>(G) + (size_t)base * k;
     float2* gD = reinterpret_cast<float2*>(D) + (size_t)base * k;
-    for (int l = threadIdx.x; l < tile; l += T) {
-        int p = l / k, e = l - p * k;
+    for (int l = threadIdx.x, p = threadIdx.x / k, e = threadIdx.x % k; l < tile; l += T) {
         float4 v = s_dat[e * STRIDE + p];
         gG[l] = make_float2(v.x, v.y);
         gD[l] = make_float2(v.z, v.w);
+        e += T % k; p += T / k;
+        if (e >= k) { e -= k; ++p; }
     }
 }
 

@@ -186,7 +186,7 @@ __global__ void __launch_bounds__(FIN_T) central_bwd_finalize_kernel(const doubl
                                                                      float* __restrict__ dW, float* __restrict__ dgamma, float* __restrict__ dbeta) {
     double r[2 + CIN];
     if (!finalize_sums<2 + CIN>(partial, chunks, Cout, r)) return;
-    const int c = blockIdx.x * 32 + (threadIdx.x & 31);
+    const int c = blockIdx.x * FIN_COLS + (threadIdx.x >> 5);
     dbeta[c] = (float)r[0];
     dgamma[c] = (float)r[1];
     const double is = (double)invstd[c], a = (gamma ? (double)gamma[c] : 1.0) * is, mu = (double)mean[c];
@@ -258,7 +258,7 @@ int launch_bwd_reduce(const CentralBwdVal<CIN>& f, int N, int Cout, const float*
     ColLayout L = col_layout(N, Cout);
     dim3 grid(L.chunks, L.col_blocks);
     col_reduce_kernel<2 + CIN><<<grid, RED_T, 0, st>>>(f, (long long)N, Cout, L.col_lanes, L.rows_per_chunk, partial);
-    central_bwd_finalize_kernel<CIN><<<dc_ceil_div(Cout, 32), FIN_T, 0, st>>>(partial, L.chunks, Cout, W, gamma, mean, invstd, moments,
+    central_bwd_finalize_kernel<CIN><<<dc_ceil_div(Cout, FIN_COLS), FIN_T, 0, st>>>(partial, L.chunks, Cout, W, gamma, mean, invstd, moments,
                                                                              training, dW, dgamma, dbeta);
     return DC_OK;
 }

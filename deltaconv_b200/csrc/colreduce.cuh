@@ -27,7 +27,7 @@ ColLayout col_layout(long long M, int C) {
     L.col_lanes = cl;
     L.row_lanes = RED_T / cl;
     L.col_blocks = (C + cl - 1) / cl;
-    long long want = (long long)dc_sm_count() * 4 / L.col_blocks;
+    long long want = (long long)dc_sm_count() * 2 / L.col_blocks;
     if (want < 1) want = 1;
     long long by_rows = (M + L.row_lanes * 4 - 1) / (L.row_lanes * 4);   // at least 4 rows per thread
     if (by_rows < 1) by_rows = 1;
@@ -79,35 +79,25 @@ __global__ void __launch_bounds__(RED_T) col_reduce_kernel(F f, long long M, int
 }
 
 
-// Sum partial[q][v][c] over the chunks q for one column c and value v.  A CTA of 256 threads
-// owns 32 columns: lane = column, the 8 warps stride over the chunks (coalesced 256-byte rows),
-// then the 8 per-warp sums are added in a fixed order -> deterministic.
+// Sum partial[q][v][c] over the chunks q for one column c and value v.  A CTA of 256 threads owns
+// 8 columns; the 32 lanes of a warp stride over the chunks of one column and the lane sums are
+// combined by a shuffle tree — a fixed order, so the result is deterministic.
 constexpr int FIN_T = 256;
+constexpr int FIN_COLS = 8;
 template <int NV>
 __device__ __forceinline__ bool finalize_sums(const double* __restrict__ partial, int chunks, int C, double (&out)[NV]) {
-    __shared__ double sh[NV][8][33];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    const int c = blockIdx.x * 32 + lane;
+    const int c = blockIdx.x * FIN_COLS + w;
     double acc[NV];
 #pragma unroll
     for (int v = 0; v < NV; ++v) acc[v] = 0.0;
     if (c < C)
-        for (int q = w; q < chunks; q += 8)
+        for (int q = lane; q < chunks; q += 32)
 #pragma unroll
             for (int v = 0; v < NV; ++v) acc[v] += partial[((size_t)q * NV + v) * C + c];
 #pragma unroll
-    for (int v = 0; v < NV; ++v) sh[v][w][lane] = acc[v];
-    __syncthreads();
-    if (w != 0 || c >= C) return false;
-#pragma unroll
-    for (int v = 0; v < NV; ++v) {
-        double s = 0.0;
-#pragma unroll
-        for (int q = 0; q < 8; ++q) s += sh[v][q][lane];
-        out[v] = s;
-    }
-    return true;
+    for (int v = 0; v < NV; ++v) out[v] = warp_sum(acc[v]);
+    return lane == 0 && c < C;
 }
-
 
 }  // namespace

@@ -87,6 +87,23 @@ __device__ __forceinline__ void umma_tf32(uint32_t tmem_c, uint64_t da, uint64_t
         "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
         "}" ::"r"(tmem_c), "l"(da), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
 }
+// A operand read from tensor memory (128 lanes x 8 columns of tf32 per instruction), B from shared memory
+__device__ __forceinline__ void umma_tf32_ts(uint32_t tmem_c, uint32_t tmem_a, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t"
+        "}" ::"r"(tmem_c), "r"(tmem_a), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32]) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,"
+                 "%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};"
+                 ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+                   "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]), "r"(r[19]),
+                   "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]), "r"(r[28]), "r"(r[29]),
+                   "r"(r[30]), "r"(r[31]) : "memory");
+}
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
@@ -94,13 +111,18 @@ __device__ __forceinline__ void umma_commit(uint32_t bar) {
 // Persistent kernel: every CTA walks the tile list (n fastest, so CTAs that run together share the A rows in L2)
 // with five roles that only meet at mbarriers.  Two TMEM accumulators let the epilogue of tile t overlap the
 // main loop of tile t+1.
-template <int BN, bool A_MN, bool B_MN, bool SPLIT3, int STAGES>
+template <int BN, bool A_MN, bool B_MN, bool SPLIT3, int STAGES, bool TS>
 __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA,
                                                                 const __grid_constant__ CUtensorMap tmB, TcArgs g) {
     constexpr uint32_t A_BYTES = TC_BM * 128, B_BYTES = BN * 128;
-    constexpr uint32_t STAGE_BYTES = (A_BYTES + B_BYTES) * (SPLIT3 ? 2 : 1);
+    static_assert(!TS || (SPLIT3 && !A_MN), "A-from-TMEM is used for the split of a K-major A only");
+    // TS: the split A operand lives in tensor memory, so shared memory holds raw A (16 KB) + B hi/lo
+    constexpr uint32_t STAGE_BYTES = TS ? A_BYTES + 2 * B_BYTES : (A_BYTES + B_BYTES) * (SPLIT3 ? 2 : 1);
     constexpr uint32_t CHUNK_BYTES = TC_BK * 128;                 // one 32-wide MN chunk of an MN-major tile
-    constexpr uint32_t TMEM_COLS = 2 * BN <= 32 ? 32 : 2 * BN <= 64 ? 64 : 2 * BN <= 128 ? 128 : 2 * BN <= 256 ? 256 : 512;
+    constexpr uint32_t TMEM_NEED = 2 * BN + (TS ? 64 * STAGES : 0);   // 2 accumulators (+ A_hi/A_lo k-blocks per stage)
+    constexpr uint32_t TMEM_COLS = TMEM_NEED <= 32 ? 32 : TMEM_NEED <= 64 ? 64 : TMEM_NEED <= 128 ? 128 : TMEM_NEED <= 256 ? 256 : 512;
+    static_assert(TMEM_NEED <= 512, "tensor memory exhausted");
+    constexpr uint32_t TMEM_A0 = 2 * BN;                          // first column of the A operand ring (TS)
     // instruction descriptor (cute::UMMA::InstrDescriptor): c=F32, a=b=TF32, majors, N>>3, M>>4
     constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
                                ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
@@ -139,8 +161,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
 
     auto stage_a = [&](int s) { return base + s * STAGE_BYTES; };
     auto stage_a_lo = [&](int s) { return base + s * STAGE_BYTES + A_BYTES; };
-    auto stage_b = [&](int s) { return base + s * STAGE_BYTES + (SPLIT3 ? 2 : 1) * A_BYTES; };
-    auto stage_b_lo = [&](int s) { return base + s * STAGE_BYTES + 2 * A_BYTES + B_BYTES; };
+    auto stage_b = [&](int s) { return base + s * STAGE_BYTES + ((SPLIT3 && !TS) ? 2 : 1) * A_BYTES; };
+    auto stage_b_lo = [&](int s) { return base + s * STAGE_BYTES + (TS ? 1 : 2) * A_BYTES + B_BYTES; };
     // tile id -> (m0, n0, first k-block, number of k-blocks)
     auto decode = [&](long long tile, int& m0, int& n0, int& kb_begin, int& nkb) {
         const int nt = (int)(tile % tiles_n);
@@ -202,8 +224,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
                         const uint32_t a_lbo = A_MN ? CHUNK_BYTES : 16u, b_lbo = B_MN ? CHUNK_BYTES : 16u;
                         const uint32_t a_sbo = A_MN ? 512u : 1024u, b_sbo = B_MN ? 512u : 1024u;
                         const uint32_t a_lt = A_MN ? 1u : 2u, b_lt = B_MN ? 1u : 2u;
-                        const uint64_t da = umma_desc(stage_a(s) + a_off, a_lbo, a_sbo, a_lt);
                         const uint64_t db = umma_desc(stage_b(s) + b_off, b_lbo, b_sbo, b_lt);
+                        if (TS) {
+                            const uint32_t ta_hi = tmem_base + TMEM_A0 + (uint32_t)s * 64u + (uint32_t)kk * 8u, ta_lo = ta_hi + 32u;
+                            const uint64_t db_lo = umma_desc(stage_b_lo(s) + b_off, b_lbo, b_sbo, b_lt);
+                            umma_tf32_ts(tmem_acc, ta_hi, db, IDESC, (kb > 0 || kk > 0) ? 1u : 0u);
+                            umma_tf32_ts(tmem_acc, ta_lo, db, IDESC, 1u);
+                            umma_tf32_ts(tmem_acc, ta_hi, db_lo, IDESC, 1u);
+                            continue;
+                        }
+                        const uint64_t da = umma_desc(stage_a(s) + a_off, a_lbo, a_sbo, a_lt);
                         umma_tf32(tmem_acc, da, db, IDESC, (kb > 0 || kk > 0) ? 1u : 0u);
                         if (SPLIT3) {
                             const uint64_t da_lo = umma_desc(stage_a_lo(s) + a_off, a_lbo, a_sbo, a_lt);
@@ -242,10 +272,33 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
                         h.w = __uint_as_float(__float_as_uint(x.w) & 0xffffe000u); l.w = x.w - h.w;
                         hi[i] = h; lo[i] = l;
                     };
+                    if (TS) {
+                        // this thread owns one row of the A tile: read it through the 128-byte swizzle, split it, and
+                        // store hi / lo into the row's TMEM lane (32 columns each)
+                        const int row = (warp & 3) * 32 + lane;
+                        const float4* arow = reinterpret_cast<const float4*>(base_ptr + (stage_a(s) - base) + row * 128);
+                        uint32_t hi[32], lo[32];
 #pragma unroll
-                    for (int i = 0; i < (int)(A_BYTES / 16) / 128; ++i) split(a_hi, a_lo, t + 128 * i);
+                        for (int c = 0; c < 8; ++c) {
+                            const float4 x = arow[c ^ (row & 7)];
+                            const float v[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+                            for (int u = 0; u < 4; ++u) {
+                                const uint32_t h = __float_as_uint(v[u]) & 0xffffe000u;
+                                hi[4 * c + u] = h;
+                                lo[4 * c + u] = __float_as_uint(v[u] - __uint_as_float(h));
+                            }
+                        }
+                        const uint32_t ta = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + TMEM_A0 + (uint32_t)s * 64u;
+                        tmem_st32(ta, hi);
+                        tmem_st32(ta + 32u, lo);
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < (int)(A_BYTES / 16) / 128; ++i) split(a_hi, a_lo, t + 128 * i);
+                    }
 #pragma unroll
                     for (int i = 0; i < (int)(B_BYTES / 16) / 128; ++i) split(b_hi, b_lo, t + 128 * i);
+                    if (TS) { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); tc_fence_before(); }
                     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // generic writes -> visible to the MMA (async proxy)
                     __syncwarp();
                     if (lane == 0) mbar_arrive(conv_bar(s));
@@ -351,20 +404,33 @@ bool make_map(CUtensorMap* map, const float* ptr, long long inner, long long out
               mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
-template <int BN, bool SPLIT3> struct TcStages {
-    static constexpr int per_stage = (TC_BM + BN) * 128 * (SPLIT3 ? 2 : 1);
-    static constexpr int value = (200 * 1024) / per_stage > TC_MAX_STAGES ? TC_MAX_STAGES : (200 * 1024) / per_stage;
+int g_tc_no_ts = 0;      // experiment switch: 1 = keep the split A operand in shared memory (SS MMAs)
+
+template <int BN, bool SPLIT3, bool TS> struct TcStages {
+    static constexpr int per_stage = TS ? (TC_BM + 2 * BN) * 128 : (TC_BM + BN) * 128 * (SPLIT3 ? 2 : 1);
+    static constexpr int by_smem = (200 * 1024) / per_stage > TC_MAX_STAGES ? TC_MAX_STAGES : (200 * 1024) / per_stage;
+    static constexpr int by_tmem = TS ? (512 - 2 * BN) / 64 : TC_MAX_STAGES;      // A ring: 64 TMEM columns per stage
+    static constexpr int value = by_smem < by_tmem ? by_smem : by_tmem;
 };
 
 template <int BN, bool A_MN, bool B_MN, bool SPLIT3>
 int launch_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const TcArgs& g, long long num_tiles, cudaStream_t st) {
-    constexpr int STAGES = TcStages<BN, SPLIT3>::value;
+    constexpr bool TS = SPLIT3 && !A_MN;       // K-major A: split into tensor memory instead of shared memory
+    constexpr int STAGES = TcStages<BN, SPLIT3, TS>::value;
     static_assert(STAGES >= 2, "tile too large for shared memory");
-    const size_t smem = (size_t)STAGES * TcStages<BN, SPLIT3>::per_stage + 1024 /*alignment*/ + 8 * (3 * TC_MAX_STAGES + 4) + 16;
-    DC_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<BN, A_MN, B_MN, SPLIT3, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const size_t smem = (size_t)STAGES * TcStages<BN, SPLIT3, TS>::per_stage + 1024 /*alignment*/ + 8 * (3 * TC_MAX_STAGES + 4) + 16;
+    if (g_tc_no_ts && TS) {
+        constexpr int ST2 = TcStages<BN, SPLIT3, false>::value;
+        const size_t smem2 = (size_t)ST2 * TcStages<BN, SPLIT3, false>::per_stage + 1024 + 8 * (3 * TC_MAX_STAGES + 4) + 16;
+        DC_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<BN, A_MN, B_MN, SPLIT3, ST2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+        const long long sms2 = dc_sm_count();
+        tc_gemm_kernel<BN, A_MN, B_MN, SPLIT3, ST2, false><<<(unsigned)(num_tiles < sms2 ? num_tiles : sms2), TC_THREADS, smem2, st>>>(tmA, tmB, g);
+        return DC_OK;
+    }
+    DC_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<BN, A_MN, B_MN, SPLIT3, STAGES, TS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const long long sms = dc_sm_count();
     const unsigned grid = (unsigned)(num_tiles < sms ? num_tiles : sms);       // persistent: one CTA per SM
-    tc_gemm_kernel<BN, A_MN, B_MN, SPLIT3, STAGES><<<grid, TC_THREADS, smem, st>>>(tmA, tmB, g);
+    tc_gemm_kernel<BN, A_MN, B_MN, SPLIT3, STAGES, TS><<<grid, TC_THREADS, smem, st>>>(tmA, tmB, g);
     return DC_OK;
 }
 
@@ -388,6 +454,8 @@ extern "C" int dc_set_gemm_mode(int mode) {
     return DC_OK;
 }
 extern "C" int dc_get_gemm_mode(void) { return g_tc_mode; }
+// experiment switch: A operand of the 3xTF32 split in shared memory (1) instead of tensor memory (0, default)
+extern "C" int dc_set_gemm_no_ts(int v) { g_tc_no_ts = v; return DC_OK; }
 
 // Generic tensor-core product  C[M,N] = op(A) op(B)^T (+bias).  a_mn / b_mn select the operand layout:
 //   a_mn = 0: A is [M, K] with K contiguous (lda = row pitch);  a_mn = 1: A is stored [K, M] with M contiguous.

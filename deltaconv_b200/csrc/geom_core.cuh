@@ -165,21 +165,28 @@ struct SlotView {
 };
 
 // Pass 1 (grad_div_mls.py:91-95, :233): tangent-plane coordinates, height over the plane, raw
-// gaussian weight.  `denom` = (kernel_width * mean edge length of the cloud)^2.  Neighbour
+// gaussian weight of ONE slot.  `denom` = (kernel_width * mean edge length of the cloud)^2.  Neighbour
 // index N is the padding sentinel (:226-227): treated as neighbour 0 with final weight 0.
+DC_HD float4 fit_slot_coords_loaded(V3 pj, V3 p, V3 n, V3 ex, V3 ey, float denom) {
+    V3 d = pj - p;
+    float h = dot(n, d);
+    V3 t = d - n * h;
+    float r = sqrtf(dot(d, d));
+    float w = expf(-(r * r) / denom);
+    return make_float4(dot(t, ex), dot(t, ey), w, h);
+}
+DC_HD float4 fit_slot_coords(const float* __restrict__ pos, int N, int j, V3 p, V3 n, V3 ex, V3 ey, float denom) {
+    int jj = (j < 0 || j >= N) ? 0 : j;
+    return fit_slot_coords_loaded(v3_load(pos + 3 * (size_t)jj), p, n, ex, ey, denom);
+}
+
 DC_HD float fit_pass1(const float* __restrict__ pos, int N, int i, int k, V3 p, V3 n, V3 ex, V3 ey,
                       float denom, const SlotView& s) {
     float wsum = 0.f;
     for (int e = 0; e < k; ++e) {
-        int j = s.j(e);
-        int jj = (j < 0 || j >= N) ? 0 : j;
-        V3 d = v3_load(pos + 3 * (size_t)jj) - p;
-        float h = dot(n, d);
-        V3 t = d - n * h;
-        float r = sqrtf(dot(d, d));
-        float w = expf(-(r * r) / denom);
-        wsum += w;
-        s.d(e) = make_float4(dot(t, ex), dot(t, ey), w, h);
+        float4 c = fit_slot_coords(pos, N, s.j(e), p, n, ex, ey, denom);
+        wsum += c.z;
+        s.d(e) = c;
     }
     return wsum;
 }
@@ -194,11 +201,11 @@ DC_HD void fit_pass2(int N, int k, float wsum, const FitParams& fp, const SlotVi
     for (int q = 0; q < 21; ++q) A[q] = 0.f;
 #pragma unroll
     for (int q = 0; q < 6; ++q) rhs[q] = 0.f;
-    const float wnorm = fmaxf(wsum, DC_GEOM_EPS);
+    const float inv_wnorm = 1.f / fmaxf(wsum, DC_GEOM_EPS);
     for (int e = 0; e < k; ++e) {
         float4 c = s.d(e);
         int j = s.j(e);
-        float w = (j < 0 || j >= N) ? 0.f : c.z / wnorm;
+        float w = (j < 0 || j >= N) ? 0.f : c.z * inv_wnorm;
         c.z = w;
         s.d(e) = c;
         float b[6];
@@ -255,41 +262,50 @@ DC_HD float fit_row_norm(int k, const SlotView& s, const float z1[6], const floa
     return sqrtf(ax * ax + ay * ay);
 }
 
-// Pass 3b: final entries.  `S` is the cloud's infinity norm (<= 0 means "do not normalise");
+// Pass 3b: final entries of ONE slot.  `S` is the cloud's infinity norm (<= 0 means "do not normalise");
 // the frame mapping follows fit_vector_mapping (:168-194) and the divergence row :271-272.
-// Optional debug outputs mirror the reference's public helpers: coords [k,2], weights [k],
-// mapping [k,4] for this point.
+// Optional debug outputs mirror the reference's public helpers (coords [2], weights [1], mapping [4]).
+// Returns (g_x, g_y, D_0, D_1).
+DC_HD float4 fit_slot_entry_loaded(V3 xj, V3 yj, bool valid, float4 c, V3 n, V3 ex, V3 ey, float S,
+                                   const float z1[6], const float z2[6], const float coef[6],
+                                   float* dbg_coords, float* dbg_weights, float* dbg_mapping) {
+    float gx, gy;
+    fit_grad_entry(c, z1, z2, gx, gy);
+    if (S > 1e-5f) { gx = gx / S; gy = gy / S; }
+    float u = c.x, v = c.y;
+    float hx = coef[1] + 2.f * coef[3] * u + coef[4] * v;
+    float hy = coef[2] + coef[4] * u + 2.f * coef[5] * v;
+    V3 gam_x = ex + n * hx, gam_y = ey + n * hy;
+    float inv_det = 1.f / (1.f + hx * hx + hy * hy);
+    float Eb = 1.f + hx * hx, Fb = hx * hy, Gb = 1.f + hy * hy;
+    float t00 = dot(gam_x, xj), t01 = dot(gam_x, yj), t10 = dot(gam_y, xj), t11 = dot(gam_y, yj);
+    float m00 = (Gb * t00 - Fb * t10) * inv_det, m01 = (Gb * t01 - Fb * t11) * inv_det;
+    float m10 = (-Fb * t00 + Eb * t10) * inv_det, m11 = (-Fb * t01 + Eb * t11) * inv_det;
+    if (dbg_coords) { dbg_coords[0] = u; dbg_coords[1] = v; }
+    if (dbg_weights) dbg_weights[0] = c.z;
+    if (dbg_mapping) { dbg_mapping[0] = m00; dbg_mapping[1] = m01; dbg_mapping[2] = m10; dbg_mapping[3] = m11; }
+    float4 out;
+    out.x = valid ? gx : 0.f;
+    out.y = valid ? gy : 0.f;
+    out.z = valid ? gx * m00 + gy * m10 : 0.f;
+    out.w = valid ? gx * m01 + gy * m11 : 0.f;
+    return out;
+}
+DC_HD float4 fit_slot_entry(const float* __restrict__ xb_all, const float* __restrict__ yb_all, int N, int j, float4 c,
+                            V3 n, V3 ex, V3 ey, float S, const float z1[6], const float z2[6], const float coef[6],
+                            float* dbg_coords, float* dbg_weights, float* dbg_mapping) {
+    bool valid = !(j < 0 || j >= N);
+    int jj = valid ? j : 0;
+    return fit_slot_entry_loaded(v3_load(xb_all + 3 * (size_t)jj), v3_load(yb_all + 3 * (size_t)jj), valid, c, n, ex, ey, S,
+                                 z1, z2, coef, dbg_coords, dbg_weights, dbg_mapping);
+}
+
 DC_HD void fit_pass3(const float* __restrict__ xb_all, const float* __restrict__ yb_all, int N, int k,
                      V3 n, V3 ex, V3 ey, float S, const SlotView& s,
                      const float z1[6], const float z2[6], const float coef[6],
                      float* dbg_coords, float* dbg_weights, float* dbg_mapping) {
-    const bool scale = S > 1e-5f;
-    for (int e = 0; e < k; ++e) {
-        float4 c = s.d(e);
-        int j = s.j(e);
-        bool valid = !(j < 0 || j >= N);
-        int jj = valid ? j : 0;
-        float gx, gy;
-        fit_grad_entry(c, z1, z2, gx, gy);
-        if (scale) { gx = gx / S; gy = gy / S; }
-        float u = c.x, v = c.y;
-        float hx = coef[1] + 2.f * coef[3] * u + coef[4] * v;
-        float hy = coef[2] + coef[4] * u + 2.f * coef[5] * v;
-        V3 gam_x = ex + n * hx, gam_y = ey + n * hy;
-        float det = 1.f + hx * hx + hy * hy;
-        float Eb = 1.f + hx * hx, Fb = hx * hy, Gb = 1.f + hy * hy;
-        V3 xj = v3_load(xb_all + 3 * (size_t)jj), yj = v3_load(yb_all + 3 * (size_t)jj);
-        float t00 = dot(gam_x, xj), t01 = dot(gam_x, yj), t10 = dot(gam_y, xj), t11 = dot(gam_y, yj);
-        float m00 = (Gb * t00 - Fb * t10) / det, m01 = (Gb * t01 - Fb * t11) / det;
-        float m10 = (-Fb * t00 + Eb * t10) / det, m11 = (-Fb * t01 + Eb * t11) / det;
-        if (dbg_coords) { dbg_coords[2 * e] = u; dbg_coords[2 * e + 1] = v; }
-        if (dbg_weights) dbg_weights[e] = c.z;
-        if (dbg_mapping) { dbg_mapping[4 * e] = m00; dbg_mapping[4 * e + 1] = m01; dbg_mapping[4 * e + 2] = m10; dbg_mapping[4 * e + 3] = m11; }
-        float4 out;
-        out.x = valid ? gx : 0.f;
-        out.y = valid ? gy : 0.f;
-        out.z = valid ? gx * m00 + gy * m10 : 0.f;
-        out.w = valid ? gx * m01 + gy * m11 : 0.f;
-        s.d(e) = out;
-    }
+    for (int e = 0; e < k; ++e)
+        s.d(e) = fit_slot_entry(xb_all, yb_all, N, s.j(e), s.d(e), n, ex, ey, S, z1, z2, coef,
+                                dbg_coords ? dbg_coords + 2 * e : nullptr, dbg_weights ? dbg_weights + e : nullptr,
+                                dbg_mapping ? dbg_mapping + 4 * e : nullptr);
 }

@@ -20,7 +20,7 @@ struct SumVal {        // plain column sums of a [M,C] matrix
 __global__ void sum1_finalize_kernel(const double* __restrict__ partial, int chunks, int C, float* __restrict__ s0) {
     double r[1];
     if (!finalize_sums<1>(partial, chunks, C, r)) return;
-    s0[blockIdx.x * 32 + (threadIdx.x & 31)] = (float)r[0];
+    s0[blockIdx.x * FIN_COLS + (threadIdx.x >> 5)] = (float)r[0];
 }
 
 // ---- BatchNorm statistics ------------------------------------------------------------------
@@ -44,7 +44,7 @@ __global__ void bn_finalize_kernel(const double* __restrict__ partial, int chunk
                                    float* __restrict__ running_mean, float* __restrict__ running_var) {
     double r[2];
     if (!finalize_sums<2>(partial, chunks, C, r)) return;
-    const int c = blockIdx.x * 32 + (threadIdx.x & 31);
+    const int c = blockIdx.x * FIN_COLS + (threadIdx.x >> 5);
     double s = r[0], s2 = r[1];
     double mu = s / (double)M;
     double var = s2 / (double)M - mu * mu;
@@ -117,7 +117,7 @@ struct BnBwdVal {
 __global__ void sum2_finalize_kernel(const double* __restrict__ partial, int chunks, int C, float* __restrict__ s0, float* __restrict__ s1) {
     double r[2];
     if (!finalize_sums<2>(partial, chunks, C, r)) return;
-    const int c = blockIdx.x * 32 + (threadIdx.x & 31);
+    const int c = blockIdx.x * FIN_COLS + (threadIdx.x >> 5);
     s0[c] = (float)r[0]; s1[c] = (float)r[1];
 }
 
@@ -547,7 +547,7 @@ extern "C" int dc_bn_stats(const float* x, int64_t ldx, int64_t M, int C, int mo
     double* partial = (double*)ws;
     if (mode == 0) { PlainVal f = {x, ldx}; col_reduce_kernel<2><<<grid, RED_T, 0, st>>>(f, M, C, L.col_lanes, L.rows_per_chunk, partial); }
     else { NormVal f = {x, ldx}; col_reduce_kernel<2><<<grid, RED_T, 0, st>>>(f, M, C, L.col_lanes, L.rows_per_chunk, partial); }
-    bn_finalize_kernel<<<dc_ceil_div(C, 32), FIN_T, 0, st>>>(partial, L.chunks, M, C, eps, momentum, mean, invstd,
+    bn_finalize_kernel<<<dc_ceil_div(C, FIN_COLS), FIN_T, 0, st>>>(partial, L.chunks, M, C, eps, momentum, mean, invstd,
                                                             running_mean_or_null, running_var_or_null);
     return dc_check_launch_n("dc_bn_stats", 2);
 }
@@ -561,7 +561,7 @@ extern "C" int dc_col_sum(const float* x, int64_t ldx, int64_t M, int C, float* 
     dim3 grid(L.chunks, L.col_blocks);
     SumVal f = {x, ldx};
     col_reduce_kernel<1><<<grid, RED_T, 0, st>>>(f, M, C, L.col_lanes, L.rows_per_chunk, (double*)ws);
-    sum1_finalize_kernel<<<dc_ceil_div(C, 32), FIN_T, 0, st>>>((double*)ws, L.chunks, C, out);
+    sum1_finalize_kernel<<<dc_ceil_div(C, FIN_COLS), FIN_T, 0, st>>>((double*)ws, L.chunks, C, out);
     return dc_check_launch_n("dc_col_sum", 2);
 }
 
@@ -591,7 +591,7 @@ extern "C" int dc_bn_act_bwd(const float* y, int64_t ldy, const float* dout, int
     double* partial = (double*)ws;
     BnBwdVal f = {y, ldy, dout, ldd, mean, invstd, gamma_or_null, beta_or_null, slope};
     col_reduce_kernel<2><<<grid, RED_T, 0, st>>>(f, M, C, L.col_lanes, L.rows_per_chunk, partial);
-    sum2_finalize_kernel<<<dc_ceil_div(C, 32), FIN_T, 0, st>>>(partial, L.chunks, C, d_beta, d_gamma);
+    sum2_finalize_kernel<<<dc_ceil_div(C, FIN_COLS), FIN_T, 0, st>>>(partial, L.chunks, C, d_beta, d_gamma);
     if (C % 4 == 0 && ldy % 4 == 0 && ldd % 4 == 0 && ld_dy % 4 == 0 && all_aligned16(y, dout, dy, mean, invstd, gamma_or_null, beta_or_null) &&
         all_aligned16(d_beta, d_gamma))
         bn_act_bwd_vec4_kernel<<<elementwise_grid(M * C / 4), 256, 0, st>>>(y, ldy, dout, ldd, M, C / 4, mean, invstd, gamma_or_null, beta_or_null,
@@ -628,7 +628,7 @@ extern "C" int dc_vecnonlin_bwd(const float* v, int64_t ldv, const float* dout, 
         double* partial = (double*)ws;
         VnlBwdVal f = {v, ldv, dout, ldd, mean_or_null, invstd_or_null, gamma_or_null, beta_or_null};
         col_reduce_kernel<2><<<grid, RED_T, 0, st>>>(f, M, C, L.col_lanes, L.rows_per_chunk, partial);
-        sum2_finalize_kernel<<<dc_ceil_div(C, 32), FIN_T, 0, st>>>(partial, L.chunks, C, d_beta, d_gamma);
+        sum2_finalize_kernel<<<dc_ceil_div(C, FIN_COLS), FIN_T, 0, st>>>(partial, L.chunks, C, d_beta, d_gamma);
     }
     vecnonlin_bwd_kernel<<<elementwise_grid(M * C), 256, 0, st>>>(v, ldv, dout, ldd, M, C, mean_or_null, invstd_or_null, gamma_or_null,
                                                                   beta_or_null, bias_or_null, d_beta, d_gamma, training, dv, ld_dv,
