@@ -246,9 +246,9 @@ def run_cuda_arm(args):
     flat = FlatGradients(model.parameters())
     opt = torch.optim.SGD(model.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4)
     host = D.utils.synthetic_batch(CLOUDS, POINTS, config=2, rank=rank, num_classes=CLASSES).pin_memory()
-    host._num_clouds = CLOUDS
+    host._num_clouds, host._max_points = CLOUDS, POINTS
     resident = host.to(dev)
-    resident._num_clouds = CLOUDS
+    resident._num_clouds, resident._max_points = CLOUDS, POINTS
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)             # > 126 MB L2
 
     def step(data):
@@ -286,7 +286,7 @@ def run_cuda_arm(args):
     graphed = None
     if not args.no_graph:
         static = host.to(dev)
-        static._num_clouds = CLOUDS
+        static._num_clouds, static._max_points = CLOUDS, POINTS
         graphed = D.utils.GraphedTrainStep(model, opt, smoothed_loss, static, flat=flat)
         for _ in range(3):
             graphed()
@@ -304,7 +304,7 @@ def run_cuda_arm(args):
     # (2) end to end: pinned host buffers -> device inside the timed region, loss read back every step
     def e2e_step():
         data = host.to(dev, non_blocking=True)
-        data._num_clouds = CLOUDS
+        data._num_clouds, data._max_points = CLOUDS, POINTS
         return step(data).item()
     def e2e_graph_step():
         graphed.load(host)

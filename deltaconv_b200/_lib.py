@@ -33,12 +33,13 @@ _SIGNATURES = {
     'dc_build_static_max_points': [],
     'dc_build_static_max_clouds': [],
     'dc_build_grad_div_static': [_P, _P, _P, _P, _P, _P, _I, _I, _I, _F, _F, _F, _I, _I, _P, _P, _P],
-    'dc_grad_fwd': [_P, _P, _I, _I, _I, _P, _L, _P, _L, _P],
-    'dc_grad_bwd': [_P, _P, _P, _I, _I, _I, _P, _L, _P, _L, _P],
-    'dc_divcurlnorm_fwd': [_P, _P, _I, _I, _I, _P, _L, _P, _L, _P, _L, _P, _L, _P],
-    'dc_divcurlnorm_bwd': [_P, _P, _P, _I, _I, _I, _P, _L, _P, _L, _P, _L, _P, _L, _P, _L, _P],
-    'dc_hodge_fwd': [_P, _P, _I, _I, _I, _P, _L, _P, _L, _P, _L, _P],
-    'dc_hodge_bwd': [_P, _P, _P, _I, _I, _I, _P, _L, _P, _L, _P, _L, _P],
+    'dc_set_spmm_staged': [_I],
+    'dc_grad_fwd': [_P, _P, _I, _I, _I, _P, _L, _P, _L, _P, _I, _I, _P],
+    'dc_grad_bwd': [_P, _P, _P, _I, _I, _I, _P, _L, _P, _L, _P, _I, _I, _P],
+    'dc_divcurlnorm_fwd': [_P, _P, _I, _I, _I, _P, _L, _P, _L, _P, _L, _P, _L, _P, _I, _I, _P],
+    'dc_divcurlnorm_bwd': [_P, _P, _P, _I, _I, _I, _P, _L, _P, _L, _P, _L, _P, _L, _P, _L, _P, _I, _I, _P],
+    'dc_hodge_fwd': [_P, _P, _I, _I, _I, _P, _L, _P, _L, _P, _L, _P, _I, _I, _P],
+    'dc_hodge_bwd': [_P, _P, _P, _I, _I, _I, _P, _L, _P, _L, _P, _L, _P, _I, _I, _P],
     'dc_gathermax_fwd': [_P, _I, _I, _I, _P, _L, _P, _L, _P, _P],
     'dc_gathermax_bwd': [_P, _P, _I, _I, _I, _P, _P, _L, _P, _L, _P],
     'dc_edge_diff_fwd': [_P, _I, _I, _I, _P, _L, _P, _P],

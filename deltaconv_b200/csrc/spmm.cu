@@ -40,6 +40,7 @@ struct SpArgs {
     float* out0; long long ld_out0;
     float* out1; long long ld_out1;
     float* out2; long long ld_out2;
+    const int* cloud_ptr; int B; int max_cloud;   // staged variant: clouds and the size of the largest one (0 = unknown)
 };
 
 template <int VEC> struct Vec;
@@ -171,7 +172,152 @@ __global__ void __launch_bounds__(256) spmm_kernel(SpArgs a, int lpp_log2) {
     }
 }
 
+
+// ---- shared-memory staged variant ---------------------------------------------------------------
+// The gather formulation above reads every feature row k times from L2.  Clouds are small (a few
+// thousand points), so one CTA stages the rows of ONE cloud for a chunk of CH channels in shared
+// memory (one coalesced pass over HBM) and all k-fold gathers then hit shared memory.  Same
+// arithmetic, same summation order per row as spmm_kernel — results are bitwise identical.
+template <int OP> struct StagedTraits {
+    // rows staged per point for input 0 / input 1 (0 = input not staged)
+    static constexpr int m0 = (OP == OP_GRAD || OP == OP_HODGE || OP == OP_DIVCURL_T) ? 1 : 2;
+    static constexpr int m1 = (OP == OP_HODGE || OP == OP_DIVCURL_T) ? 1 : 0;
+};
+
+template <int OP>
+__global__ void __launch_bounds__(256) spmm_staged_kernel(SpArgs a, int CH, int lpp_log2) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float* t0 = reinterpret_cast<float*>(smem_raw);
+    const int b = blockIdx.y;
+    const int s = __ldg(a.cloud_ptr + b), e = __ldg(a.cloud_ptr + b + 1), P = e - s;
+    if (P <= 0) return;
+    const int ch0 = blockIdx.x * CH;
+    const int cw = min(CH, a.C - ch0);                      // channels of this chunk (multiple of 4)
+    constexpr int M0 = StagedTraits<OP>::m0, M1 = StagedTraits<OP>::m1;
+    float* t1 = t0 + (size_t)M0 * a.max_cloud * CH;
+    const bool has0 = a.in0 != nullptr, has1 = M1 > 0 && a.in1 != nullptr;
+    // stage: rows [M*s, M*e) x channels [ch0, ch0+cw), float4 granularity, coalesced along channels
+    const int q4 = cw >> 2;
+    if (has0)
+        for (int t = threadIdx.x; t < M0 * P * q4; t += blockDim.x) {
+            const int r = t / q4, c4 = t - r * q4;
+            *reinterpret_cast<float4*>(t0 + (size_t)r * CH + 4 * c4) =
+                __ldg(reinterpret_cast<const float4*>(a.in0 + ((size_t)M0 * s + r) * a.ld_in0 + ch0 + 4 * c4));
+        }
+    if (has1)
+        for (int t = threadIdx.x; t < M1 * P * q4; t += blockDim.x) {
+            const int r = t / q4, c4 = t - r * q4;
+            *reinterpret_cast<float4*>(t1 + (size_t)r * CH + 4 * c4) =
+                __ldg(reinterpret_cast<const float4*>(a.in1 + ((size_t)M1 * s + r) * a.ld_in1 + ch0 + 4 * c4));
+        }
+    __syncthreads();
+
+    typedef Vec<4> V;
+    const int lpp = 1 << lpp_log2, lane = threadIdx.x & 31, sub = lane & (lpp - 1);
+    const int rows_per_warp = 32 >> lpp_log2, groups = (blockDim.x >> 5) * rows_per_warp;
+    const int chl = sub * 4;                                // channel offset inside the chunk
+    const bool ch_ok = chl < cw;
+    const int ch = ch0 + chl;
+    auto ld0 = [&](int row) { V r; r.v = *reinterpret_cast<const float4*>(t0 + (size_t)row * CH + chl); return r; };
+    auto ld1 = [&](int row) { V r; r.v = *reinterpret_cast<const float4*>(t1 + (size_t)row * CH + chl); return r; };
+
+    for (int rbase = 0; rbase < P; rbase += groups) {
+        const int rl = rbase + (threadIdx.x >> 5) * rows_per_warp + (lane >> lpp_log2);   // local row
+        const bool row_ok = rl < P;
+        const int r = s + (row_ok ? rl : 0);
+        int t_begin, len;
+        if (OpTraits<OP>::transposed) { t_begin = row_ok ? __ldg(a.in_ptr + r) : 0; len = row_ok ? __ldg(a.in_ptr + r + 1) - t_begin : 0; }
+        else { t_begin = 0; len = row_ok ? a.k : 0; }
+        int max_len = len;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) max_len = max(max_len, __shfl_xor_sync(FULL, max_len, o));
+        V acc0 = V::zero(), acc1 = V::zero();
+        for (int t0i = 0; t0i < max_len; t0i += lpp) {
+            int my_other = 0;
+            float2 my_c = make_float2(0.f, 0.f);
+            const int t = t0i + sub;
+            if (t < len) {
+                if (OpTraits<OP>::transposed) {
+                    int edge = __ldg(a.in_edge + t_begin + t);
+                    my_other = edge / a.k - s;
+                    my_c = __ldg(a.coef + edge);
+                } else {
+                    size_t eo = (size_t)r * a.k + t;
+                    int j = __ldg(a.idx + eo);
+                    my_c = __ldg(a.coef + eo);
+                    if ((unsigned)j >= (unsigned)a.N) { j = s; my_c = make_float2(0.f, 0.f); }   // padding sentinel
+                    my_other = j - s;
+                }
+            }
+            const int cnt = min(lpp, max_len - t0i);
+#pragma unroll 4
+            for (int q = 0; q < cnt; ++q) {
+                const int o = __shfl_sync(FULL, my_other, q, lpp);
+                const float c0 = __shfl_sync(FULL, my_c.x, q, lpp);
+                const float c1 = __shfl_sync(FULL, my_c.y, q, lpp);
+                if (!ch_ok || t0i + q >= len) continue;
+                if (OP == OP_GRAD) {
+                    V sv = ld0(o);
+                    acc0.fma(c0, sv); acc1.fma(c1, sv);
+                } else if (OP == OP_DIVCURL) {
+                    V vx = ld0(2 * o), vy = ld0(2 * o + 1);
+                    acc0.fma(c0, vx); acc0.fma(c1, vy);
+                    acc1.fma(c0, vy); acc1.fma(-c1, vx);
+                } else if (OP == OP_HODGE) {
+                    V va = ld0(o), vb = ld1(o);
+                    acc0.fma(-c0, va); acc0.fma(c1, vb);
+                    acc1.fma(-c1, va); acc1.fma(-c0, vb);
+                } else if (OP == OP_GRAD_T) {
+                    V px = ld0(2 * o), py = ld0(2 * o + 1);
+                    acc0.fma(c0, px); acc0.fma(c1, py);
+                } else if (OP == OP_DIVCURL_T) {
+                    V dd = V::zero(), dc = V::zero();
+                    if (has0) dd = ld0(o);
+                    if (has1) dc = ld1(o);
+                    acc0.fma(c0, dd); acc0.fma(-c1, dc);
+                    acc1.fma(c1, dd); acc1.fma(c0, dc);
+                } else {  // OP_HODGE_T
+                    V px = ld0(2 * o), py = ld0(2 * o + 1);
+                    acc0.fma(-c0, px); acc0.fma(-c1, py);
+                    acc1.fma(c1, px); acc1.fma(-c0, py);
+                }
+            }
+        }
+        if (!row_ok || !ch_ok) continue;
+        if (OP == OP_GRAD || OP == OP_HODGE) {
+            acc0.store(a.out0 + (size_t)(2 * r) * a.ld_out0 + ch);
+            acc1.store(a.out0 + (size_t)(2 * r + 1) * a.ld_out0 + ch);
+        } else if (OP == OP_DIVCURL) {
+            if (a.out0) acc0.store(a.out0 + (size_t)r * a.ld_out0 + ch);
+            if (a.out1) acc1.store(a.out1 + (size_t)r * a.ld_out1 + ch);
+            if (a.out2) {
+                V vx = ld0(2 * rl), vy = ld0(2 * rl + 1);
+                V n = V::map2(vx, vy, [](float x, float y) { return sqrtf(x * x + y * y); });
+                n.store(a.out2 + (size_t)r * a.ld_out2 + ch);
+            }
+        } else if (OP == OP_GRAD_T) {
+            acc0.store(a.out0 + (size_t)r * a.ld_out0 + ch);
+        } else if (OP == OP_DIVCURL_T) {
+            if (a.in2) {   // d|v| : dv = dNorm * v / |v|   (0 where |v| = 0, torch's subgradient)
+                V vx = V::load(a.in3 + (size_t)(2 * r) * a.ld_in3 + ch), vy = V::load(a.in3 + (size_t)(2 * r + 1) * a.ld_in3 + ch);
+                V dn = V::load(a.in2 + (size_t)r * a.ld_in2 + ch);
+                V inv = V::map2(vx, vy, [](float x, float y) { float n = sqrtf(x * x + y * y); return n > 0.f ? 1.f / n : 0.f; });
+                V sx = V::map2(dn, inv, [](float d, float w) { return d * w; });
+                acc0 = V::map2(acc0, V::map2(sx, vx, [](float s_, float x) { return s_ * x; }), [](float p, float q) { return p + q; });
+                acc1 = V::map2(acc1, V::map2(sx, vy, [](float s_, float y) { return s_ * y; }), [](float p, float q) { return p + q; });
+            }
+            acc0.store(a.out0 + (size_t)(2 * r) * a.ld_out0 + ch);
+            acc1.store(a.out0 + (size_t)(2 * r + 1) * a.ld_out0 + ch);
+        } else {  // OP_HODGE_T
+            acc0.store(a.out0 + (size_t)r * a.ld_out0 + ch);
+            acc1.store(a.out1 + (size_t)r * a.ld_out1 + ch);
+        }
+    }
+}
+
 bool aligned16(const void* p) { return p == nullptr || (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+int g_spmm_staged = 1;     // tuning switch (dc_set_spmm_staged)
 
 template <int OP>
 int launch_spmm(const SpArgs& a, cudaStream_t st) {
@@ -179,6 +325,24 @@ int launch_spmm(const SpArgs& a, cudaStream_t st) {
     const bool vec4 = (a.C % 4 == 0) && a.ld_in0 % 4 == 0 && a.ld_in1 % 4 == 0 && a.ld_in2 % 4 == 0 && a.ld_in3 % 4 == 0 &&
                       a.ld_out0 % 4 == 0 && a.ld_out1 % 4 == 0 && a.ld_out2 % 4 == 0 && aligned16(a.in0) && aligned16(a.in1) &&
                       aligned16(a.in2) && aligned16(a.in3) && aligned16(a.out0) && aligned16(a.out1) && aligned16(a.out2);
+    if (vec4 && a.cloud_ptr != nullptr && a.max_cloud > 0 && g_spmm_staged) {
+        // shared-memory staged variant: pick the channel chunk so that the staged rows fit (<= ~200 KB)
+        constexpr int M0 = StagedTraits<OP>::m0, M1 = StagedTraits<OP>::m1;
+        const int rows = (M0 + ((M1 > 0 && a.in1) ? M1 : 0)) * a.max_cloud;
+        int CH = 32;
+        while (CH > 4 && ((size_t)rows * CH * 4 > 100 * 1024 || CH > a.C)) CH >>= 1;
+        // keep the machine full: at least ~1 CTA per SM
+        while (CH > 8 && (long long)a.B * ((a.C + CH - 1) / CH) < dc_sm_count()) CH >>= 1;
+        const size_t smem = (size_t)rows * CH * 4;
+        if (smem <= 200 * 1024) {
+            int lpp_log2 = 0;
+            while ((1 << lpp_log2) < CH / 4) ++lpp_log2;
+            DC_CUDA(cudaFuncSetAttribute(spmm_staged_kernel<OP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            dim3 grid(dc_ceil_div(a.C, CH), a.B);
+            spmm_staged_kernel<OP><<<grid, 256, smem, st>>>(a, CH, lpp_log2);
+            return dc_check_launch("spmm/staged");
+        }
+    }
     const int vec = vec4 ? 4 : 1;
     const int units = (a.C + vec - 1) / vec;            // lanes needed to cover the channels once
     int lpp_log2 = 0;
@@ -281,58 +445,67 @@ extern "C" int dc_ell_transpose(const int32_t* idx, int N, int k, int32_t* in_pt
 }
 
 extern "C" int dc_grad_fwd(const int32_t* idx, const float* G, int N, int k, int C, const float* x, int64_t ldx,
-                           float* out, int64_t ldo, void* stream) {
+                           float* out, int64_t ldo, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream) {
     SpArgs a = {};
     SP_COMMON(a, N, k, C);
     a.idx = idx; a.coef = (const float2*)G; a.in0 = x; a.ld_in0 = ldx; a.out0 = out; a.ld_out0 = ldo;
+    a.cloud_ptr = cloud_ptr_or_null; a.B = B; a.max_cloud = max_cloud_points;
     return launch_spmm<OP_GRAD>(a, (cudaStream_t)stream);
 }
 
 extern "C" int dc_grad_bwd(const int32_t* in_ptr, const int32_t* in_edge, const float* G, int N, int k, int C,
-                           const float* dV, int64_t ld_dv, float* dX, int64_t ld_dx, void* stream) {
+                           const float* dV, int64_t ld_dv, float* dX, int64_t ld_dx, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream) {
     SpArgs a = {};
     SP_COMMON(a, N, k, C);
     a.in_ptr = in_ptr; a.in_edge = in_edge; a.coef = (const float2*)G; a.in0 = dV; a.ld_in0 = ld_dv; a.out0 = dX; a.ld_out0 = ld_dx;
+    a.cloud_ptr = cloud_ptr_or_null; a.B = B; a.max_cloud = max_cloud_points;
     return launch_spmm<OP_GRAD_T>(a, (cudaStream_t)stream);
 }
 
 extern "C" int dc_divcurlnorm_fwd(const int32_t* idx, const float* D, int N, int k, int C, const float* v, int64_t ldv,
                                   float* div_or_null, int64_t ld_div, float* curl_or_null, int64_t ld_curl,
-                                  float* norm_or_null, int64_t ld_norm, void* stream) {
+                                  float* norm_or_null, int64_t ld_norm, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream) {
     SpArgs a = {};
     SP_COMMON(a, N, k, C);
     a.idx = idx; a.coef = (const float2*)D; a.in0 = v; a.ld_in0 = ldv;
     a.out0 = div_or_null; a.ld_out0 = ld_div; a.out1 = curl_or_null; a.ld_out1 = ld_curl; a.out2 = norm_or_null; a.ld_out2 = ld_norm;
+    a.cloud_ptr = cloud_ptr_or_null; a.B = B; a.max_cloud = max_cloud_points;
     return launch_spmm<OP_DIVCURL>(a, (cudaStream_t)stream);
 }
 
 extern "C" int dc_divcurlnorm_bwd(const int32_t* in_ptr, const int32_t* in_edge, const float* D, int N, int k, int C,
                                   const float* d_div_or_null, int64_t ld_ddiv, const float* d_curl_or_null, int64_t ld_dcurl,
                                   const float* d_norm_or_null, int64_t ld_dnorm, const float* v, int64_t ldv,
-                                  float* dV, int64_t ld_dv, void* stream) {
+                                  float* dV, int64_t ld_dv, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream) {
     SpArgs a = {};
     SP_COMMON(a, N, k, C);
     a.in_ptr = in_ptr; a.in_edge = in_edge; a.coef = (const float2*)D;
     a.in0 = d_div_or_null; a.ld_in0 = ld_ddiv; a.in1 = d_curl_or_null; a.ld_in1 = ld_dcurl;
     a.in2 = d_norm_or_null; a.ld_in2 = ld_dnorm; a.in3 = v; a.ld_in3 = ldv;
     a.out0 = dV; a.ld_out0 = ld_dv;
+    a.cloud_ptr = cloud_ptr_or_null; a.B = B; a.max_cloud = max_cloud_points;
     return launch_spmm<OP_DIVCURL_T>(a, (cudaStream_t)stream);
 }
 
 extern "C" int dc_hodge_fwd(const int32_t* idx, const float* G, int N, int k, int C, const float* div_v, int64_t ld_a,
-                            const float* curl_v, int64_t ld_b, float* out, int64_t ldo, void* stream) {
+                            const float* curl_v, int64_t ld_b, float* out, int64_t ldo, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream) {
     SpArgs a = {};
     SP_COMMON(a, N, k, C);
     a.idx = idx; a.coef = (const float2*)G; a.in0 = div_v; a.ld_in0 = ld_a; a.in1 = curl_v; a.ld_in1 = ld_b; a.out0 = out; a.ld_out0 = ldo;
+    a.cloud_ptr = cloud_ptr_or_null; a.B = B; a.max_cloud = max_cloud_points;
     return launch_spmm<OP_HODGE>(a, (cudaStream_t)stream);
 }
 
 extern "C" int dc_hodge_bwd(const int32_t* in_ptr, const int32_t* in_edge, const float* G, int N, int k, int C,
                             const float* d_out, int64_t ld_do, float* d_div, int64_t ld_da, float* d_curl, int64_t ld_db,
-                            void* stream) {
+                            const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream) {
     SpArgs a = {};
     SP_COMMON(a, N, k, C);
     a.in_ptr = in_ptr; a.in_edge = in_edge; a.coef = (const float2*)G; a.in0 = d_out; a.ld_in0 = ld_do;
     a.out0 = d_div; a.ld_out0 = ld_da; a.out1 = d_curl; a.ld_out1 = ld_db;
+    a.cloud_ptr = cloud_ptr_or_null; a.B = B; a.max_cloud = max_cloud_points;
     return launch_spmm<OP_HODGE_T>(a, (cudaStream_t)stream);
 }
+
+// tuning switch: 1 (default) = stage a cloud's rows in shared memory when the cloud layout is known, 0 = always gather from L2
+extern "C" int dc_set_spmm_staged(int v) { g_spmm_staged = v; return DC_OK; }

@@ -28,12 +28,11 @@ def build_tangent_basis(normal):
 
 def _prepare(pos, edge_index, batch):
     graph = ops.graph_of(edge_index, pos.size(0))
-    if batch is None:
-        cp, B = ops.cloud_ptr_of(None, pos.size(0), pos.device)
-    elif graph.cloud_ptr is not None and getattr(batch, '_dc_cloud', None) is not None and batch._dc_cloud[0] is graph.cloud_ptr:
-        cp, B = graph.cloud_ptr, graph.B
-    else:
-        cp, B = ops.cloud_ptr_of(batch, pos.size(0), pos.device)
+    if graph.cloud_ptr is not None and (batch is None or getattr(batch, '_dc_cloud', (None,))[0] is graph.cloud_ptr):
+        return graph, graph.cloud_ptr, graph.B
+    cp, B, maxp = ops.cloud_layout(batch, pos.size(0), pos.device)
+    if graph.cloud_ptr is None:          # a foreign edge_index: remember the cloud layout for the SpMM kernels
+        graph.cloud_ptr, graph.B, graph.max_cloud = cp, B, maxp
     return graph, cp, B
 
 

@@ -22,15 +22,16 @@ class DeltaNetBase(torch.nn.Module):
 
     def forward(self, data):
         pos, batch = data.pos, data.batch
-        clouds = getattr(data, '_num_clouds', None)      # optional hint that avoids one device sync
+        # optional hints (number of clouds, size of the largest one) that avoid a device sync
+        clouds, maxp = getattr(data, '_num_clouds', None), getattr(data, '_max_points', None)
 
         # operator construction (deltanet_base.py:52-69): kNN graph -> frames -> grad/div
-        edge_index = knn_graph(pos, self.k, batch, loop=True, flow='target_to_source', num_clouds=clouds)
+        edge_index = knn_graph(pos, self.k, batch, loop=True, flow='target_to_source', num_clouds=clouds, max_points=maxp)
         if hasattr(data, 'norm') and data.norm is not None:
             normal = data.norm
             x_basis, y_basis = build_tangent_basis(normal)
         else:
-            edge_index_normal = knn_graph(pos, 10, batch, loop=True, flow='target_to_source', num_clouds=clouds)
+            edge_index_normal = knn_graph(pos, 10, batch, loop=True, flow='target_to_source', num_clouds=clouds, max_points=maxp)
             normal, x_basis, y_basis = estimate_basis(pos, edge_index_normal, orientation=pos)
         grad, div = build_grad_div(pos, normal, x_basis, y_basis, edge_index, batch,
                                    kernel_width=self.grad_kernel_width, regularizer=self.grad_regularizer)

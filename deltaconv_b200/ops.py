@@ -46,37 +46,49 @@ def _mat(t, name='tensor'):
 # clouds and graphs
 # ------------------------------------------------------------------------------------------------
 
-def cloud_ptr_of(batch, num_points, device, num_clouds=None):
-    """(cloud_ptr int32 [B+1], B) for a sorted PyG batch vector; cached on the tensor object.
-    `batch=None` means one cloud.  Without `num_clouds` the count is read back from the device
-    (one sync, as the reference's scatter calls do)."""
+def cloud_layout(batch, num_points, device, num_clouds=None, max_points=None):
+    """(cloud_ptr int32 [B+1], B, size of the largest cloud) for a sorted PyG batch vector; cached on the
+    tensor object.  `batch=None` means one cloud.  Without the hints the two integers are read back from
+    the device (one sync, as the reference's scatter calls do)."""
     if batch is None:
-        return torch.tensor([0, num_points], dtype=_I32, device=device), 1
+        return torch.tensor([0, num_points], dtype=_I32, device=device), 1, num_points
     cached = getattr(batch, '_dc_cloud', None)
-    if cached is not None and cached[2] == num_points:
-        return cached[0], cached[1]
+    if cached is not None and cached[3] == num_points:
+        return cached[0], cached[1], cached[2]
     if not batch.is_cuda or batch.dtype != _I64:
         raise _lib.DeltaConvLibraryError("batch must be an int64 CUDA tensor")
     batch = batch.contiguous()
     B = int(num_clouds) if num_clouds is not None else (int(batch[-1].item()) + 1 if num_points else 1)
     cp = torch.empty(B + 1, dtype=_I32, device=device)
     call('dc_cloud_ptr', ptr(batch), num_points, B, ptr(cp))
+    maxp = int(max_points) if max_points is not None else (int((cp[1:] - cp[:-1]).max().item()) if num_points else 0)
     try:
-        batch._dc_cloud = (cp, B, num_points)
+        batch._dc_cloud = (cp, B, maxp, num_points)
     except Exception:
         pass
+    return cp, B, maxp
+
+
+def cloud_ptr_of(batch, num_points, device, num_clouds=None):
+    cp, B, _ = cloud_layout(batch, num_points, device, num_clouds)
     return cp, B
 
 
 class EllGraph:
     """Fixed-k neighbourhood graph in ELL form plus, lazily, its incoming-edge CSR."""
 
-    def __init__(self, idx, cloud_ptr=None, num_clouds=None):
+    def __init__(self, idx, cloud_ptr=None, num_clouds=None, max_cloud=0):
         self.idx = idx
         self.N, self.k = idx.shape
-        self.cloud_ptr, self.B = cloud_ptr, num_clouds
+        self.cloud_ptr, self.B, self.max_cloud = cloud_ptr, num_clouds, int(max_cloud or 0)
         self._transpose = None
         self._edge_index = None
+
+    def clouds(self):
+        """(cloud_ptr pointer or None, B, largest cloud) as the SpMM entry points take them."""
+        if self.cloud_ptr is None:
+            return None, 0, 0
+        return self.cloud_ptr.data_ptr(), self.B, self.max_cloud
 
     def transpose(self):
         if self._transpose is None:
@@ -98,17 +110,17 @@ class EllGraph:
         return self._edge_index
 
 
-def knn(pos, k, batch=None, num_clouds=None, want_edge_index=True):
+def knn(pos, k, batch=None, num_clouds=None, want_edge_index=True, max_points=None):
     """ELL kNN graph of `pos` [N,3] per cloud (self included, ascending (d2, index))."""
     pos = _f32(pos, 'pos').contiguous()
     if pos.dim() != 2 or pos.size(1) != 3:
         raise _lib.DeltaConvLibraryError(f"knn: expected pos of shape [N,3], got {tuple(pos.shape)}")
     N = pos.size(0)
-    cp, B = cloud_ptr_of(batch, N, pos.device, num_clouds)
+    cp, B, maxp = cloud_layout(batch, N, pos.device, num_clouds, max_points)
     idx = torch.empty(N, k, dtype=_I32, device=pos.device)
     ei = torch.empty(2, N * k, dtype=_I64, device=pos.device) if want_edge_index else None
     call('dc_knn', ptr(pos), ptr(cp), B, N, k, ptr(idx), ptr(ei), None)
-    graph = EllGraph(idx, cp, B)
+    graph = EllGraph(idx, cp, B, maxp)
     if ei is not None:
         ei._dc_graph = graph
         graph._edge_index = ei
@@ -195,7 +207,7 @@ class _GradApply(torch.autograd.Function):
         if x.size(0) != g.N:
             raise _lib.DeltaConvLibraryError(f"grad @ x: x has {x.size(0)} rows, operator has {g.N} columns")
         out = torch.empty(2 * g.N, x.size(1), dtype=_F32, device=x.device)
-        call('dc_grad_fwd', ptr(g.idx), ptr(op.G), g.N, g.k, x.size(1), ptr(x), ldx, ptr(out), out.size(1))
+        call('dc_grad_fwd', ptr(g.idx), ptr(op.G), g.N, g.k, x.size(1), ptr(x), ldx, ptr(out), out.size(1), *g.clouds())
         ctx.op = op
         return out
 
@@ -205,7 +217,7 @@ class _GradApply(torch.autograd.Function):
         dv, ld = _mat(dv, 'grad_output')
         in_ptr, in_edge = g.transpose()
         dx = torch.empty(g.N, dv.size(1), dtype=_F32, device=dv.device)
-        call('dc_grad_bwd', ptr(in_ptr), ptr(in_edge), ptr(op.G), g.N, g.k, dv.size(1), ptr(dv), ld, ptr(dx), dx.size(1))
+        call('dc_grad_bwd', ptr(in_ptr), ptr(in_edge), ptr(op.G), g.N, g.k, dv.size(1), ptr(dv), ld, ptr(dx), dx.size(1), *g.clouds())
         return dx, None
 
 
@@ -218,7 +230,7 @@ class _DivApply(torch.autograd.Function):
             raise _lib.DeltaConvLibraryError(f"div @ v: v has {v.size(0)} rows, operator has {2 * g.N} columns")
         C = v.size(1)
         out = torch.empty(g.N, C, dtype=_F32, device=v.device)
-        call('dc_divcurlnorm_fwd', ptr(g.idx), ptr(op.D), g.N, g.k, C, ptr(v), ldv, ptr(out), C, None, 0, None, 0)
+        call('dc_divcurlnorm_fwd', ptr(g.idx), ptr(op.D), g.N, g.k, C, ptr(v), ldv, ptr(out), C, None, 0, None, 0, *g.clouds())
         ctx.op = op
         return out
 
@@ -230,7 +242,7 @@ class _DivApply(torch.autograd.Function):
         C = dd.size(1)
         dv = torch.empty(2 * g.N, C, dtype=_F32, device=dd.device)
         call('dc_divcurlnorm_bwd', ptr(in_ptr), ptr(in_edge), ptr(op.D), g.N, g.k, C, ptr(dd), ld, None, 0, None, 0,
-             None, 0, ptr(dv), C)
+             None, 0, ptr(dv), C, *g.clouds())
         return dv, None
 
 
@@ -299,7 +311,7 @@ class _ScalarCat(torch.autograd.Function):
         cat = torch.empty(g.N, 4 * C, dtype=_F32, device=x.device)
         cat[:, :C].copy_(x)
         call('dc_divcurlnorm_fwd', ptr(g.idx), ptr(op.D), g.N, g.k, C, ptr(v), ldv,
-             cat.data_ptr() + 4 * C, 4 * C, cat.data_ptr() + 8 * C, 4 * C, cat.data_ptr() + 12 * C, 4 * C)
+             cat.data_ptr() + 4 * C, 4 * C, cat.data_ptr() + 8 * C, 4 * C, cat.data_ptr() + 12 * C, 4 * C, *g.clouds())
         dc = cat[:, C:3 * C].contiguous()
         ctx.op, ctx.C = op, C
         ctx.save_for_backward(v)
@@ -319,7 +331,7 @@ class _ScalarCat(torch.autograd.Function):
         in_ptr, in_edge = g.transpose()
         dv = torch.empty(2 * g.N, C, dtype=_F32, device=dcat.device)
         call('dc_divcurlnorm_bwd', ptr(in_ptr), ptr(in_edge), ptr(op.D), g.N, g.k, C, d_div, ldt, d_curl, ldt,
-             dcat.data_ptr() + 12 * C, ld, ptr(v), ldv, ptr(dv), C)
+             dcat.data_ptr() + 12 * C, ld, ptr(v), ldv, ptr(dv), C, *g.clouds())
         return dcat[:, :C], dv, None
 
 
@@ -338,8 +350,8 @@ class _VectorCat(torch.autograd.Function):
         cat = torch.empty(2 * g.N, W, dtype=_F32, device=v.device)
         cat[:, :Cin].copy_(v)
         call('dc_hodge_fwd', ptr(g.idx), ptr(op.G), g.N, g.k, Cin, ptr(dc), ld_dc, dc.data_ptr() + 4 * Cin, ld_dc,
-             cat.data_ptr() + 4 * Cin, W)
-        call('dc_grad_fwd', ptr(g.idx), ptr(op.G), g.N, g.k, Cout, ptr(x_new), ldx, cat.data_ptr() + 8 * Cin, W)
+             cat.data_ptr() + 4 * Cin, W, *g.clouds())
+        call('dc_grad_fwd', ptr(g.idx), ptr(op.G), g.N, g.k, Cout, ptr(x_new), ldx, cat.data_ptr() + 8 * Cin, W, *g.clouds())
         ctx.op, ctx.Cin, ctx.Cout = op, Cin, Cout
         return cat
 
@@ -350,9 +362,9 @@ class _VectorCat(torch.autograd.Function):
         in_ptr, in_edge = g.transpose()
         ddc = torch.empty(g.N, 2 * Cin, dtype=_F32, device=dcat.device)
         call('dc_hodge_bwd', ptr(in_ptr), ptr(in_edge), ptr(op.G), g.N, g.k, Cin, dcat.data_ptr() + 4 * Cin, ld,
-             ptr(ddc), 2 * Cin, ddc.data_ptr() + 4 * Cin, 2 * Cin)
+             ptr(ddc), 2 * Cin, ddc.data_ptr() + 4 * Cin, 2 * Cin, *g.clouds())
         dx = torch.empty(g.N, Cout, dtype=_F32, device=dcat.device)
-        call('dc_grad_bwd', ptr(in_ptr), ptr(in_edge), ptr(op.G), g.N, g.k, Cout, dcat.data_ptr() + 8 * Cin, ld, ptr(dx), Cout)
+        call('dc_grad_bwd', ptr(in_ptr), ptr(in_edge), ptr(op.G), g.N, g.k, Cout, dcat.data_ptr() + 8 * Cin, ld, ptr(dx), Cout, *g.clouds())
         return dcat[:, :Cin], ddc, dx, None
 
 
@@ -376,7 +388,7 @@ class _CurlApply(torch.autograd.Function):
         g = op.graph
         C = v.size(1)
         out = torch.empty(g.N, C, dtype=_F32, device=v.device)
-        call('dc_divcurlnorm_fwd', ptr(g.idx), ptr(op.D), g.N, g.k, C, ptr(v), ldv, None, 0, ptr(out), C, None, 0)
+        call('dc_divcurlnorm_fwd', ptr(g.idx), ptr(op.D), g.N, g.k, C, ptr(v), ldv, None, 0, ptr(out), C, None, 0, *g.clouds())
         ctx.op = op
         return out
 
@@ -388,7 +400,7 @@ class _CurlApply(torch.autograd.Function):
         C = dcurl.size(1)
         dv = torch.empty(2 * g.N, C, dtype=_F32, device=dcurl.device)
         call('dc_divcurlnorm_bwd', ptr(in_ptr), ptr(in_edge), ptr(op.D), g.N, g.k, C, None, 0, ptr(dcurl), ld, None, 0,
-             None, 0, ptr(dv), C)
+             None, 0, ptr(dv), C, *g.clouds())
         return dv, None
 
 

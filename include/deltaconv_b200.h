@@ -92,29 +92,33 @@ int dc_build_grad_div_static(const float* pos, const float* normal, const float*
 
 /* ---- operator application (SparseTensor @ dense and operators.py) --------------------------- */
 
+/* All six entry points below take (cloud_ptr_or_null, B, max_cloud_points): when the cloud layout is given and the largest
+ * cloud fits, a CTA stages one cloud's rows in shared memory so the k-fold gathers never leave the SM; otherwise rows are
+ * gathered from L2.  Both paths give bitwise identical results. */
+int dc_set_spmm_staged(int v);
 /* grad @ x — deltanet_base.py:78, deltaconv.py:66:  out[2i+a,:] = sum_e G[i,e,a] x[idx[i,e],:] */
 int dc_grad_fwd(const int32_t* idx, const float* G, int N, int k, int C, const float* x, int64_t ldx,
-                float* out, int64_t ldo, void* stream);
+                float* out, int64_t ldo, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream);
 /* its transpose (autograd of the above w.r.t. x): dX[j,:] = sum_{(i,e)->j} G[i,e,:] . dV[2i:2i+2,:] */
 int dc_grad_bwd(const int32_t* in_ptr, const int32_t* in_edge, const float* G, int N, int k, int C,
-                const float* dV, int64_t ld_dv, float* dX, int64_t ld_dx, void* stream);
+                const float* dV, int64_t ld_dv, float* dX, int64_t ld_dx, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream);
 
 /* [div @ v | curl(v, div) | norm(v)] in one pass — deltaconv.py:57, operators.py:4-7,23-27. */
 int dc_divcurlnorm_fwd(const int32_t* idx, const float* D, int N, int k, int C, const float* v, int64_t ldv,
                        float* div_or_null, int64_t ld_div, float* curl_or_null, int64_t ld_curl,
-                       float* norm_or_null, int64_t ld_norm, void* stream);
+                       float* norm_or_null, int64_t ld_norm, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream);
 int dc_divcurlnorm_bwd(const int32_t* in_ptr, const int32_t* in_edge, const float* D, int N, int k, int C,
                        const float* d_div_or_null, int64_t ld_ddiv, const float* d_curl_or_null, int64_t ld_dcurl,
                        const float* d_norm_or_null, int64_t ld_dnorm, const float* v, int64_t ldv,
-                       float* dV, int64_t ld_dv, void* stream);
+                       float* dV, int64_t ld_dv, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream);
 
 /* hodge_laplacian(v, grad, div) given div v and curl v — operators.py:35-46:
  * out = -(grad(div_v) + J grad(curl_v)), rows interleaved like every vector field. */
 int dc_hodge_fwd(const int32_t* idx, const float* G, int N, int k, int C, const float* div_v, int64_t ld_a,
-                 const float* curl_v, int64_t ld_b, float* out, int64_t ldo, void* stream);
+                 const float* curl_v, int64_t ld_b, float* out, int64_t ldo, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream);
 int dc_hodge_bwd(const int32_t* in_ptr, const int32_t* in_edge, const float* G, int N, int k, int C,
                  const float* d_out, int64_t ld_do, float* d_div, int64_t ld_da, float* d_curl, int64_t ld_db,
-                 void* stream);
+                 const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream);
 
 /* ---- scalar stream: kNN max aggregation ------------------------------------------------------ */
 

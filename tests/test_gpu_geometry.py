@@ -320,3 +320,30 @@ def test_full_size_properties_and_determinism():
     y = grad @ x
     (y * w).sum().backward()
     assert abs((y.detach() * w).sum().item() - (x.detach() * x.grad).sum().item()) < 1e-3 * (y.detach() * w).abs().sum().item()
+
+
+@pytest.mark.parametrize('C', [4, 16, 64, 200])
+def test_staged_spmm_is_bitwise_equal_to_the_gather_kernels(C):
+    """Shared-memory staged SpMMs (cloud layout known) vs L2-gather SpMMs: same arithmetic in the same order."""
+    from deltaconv_b200 import _lib
+    lib = _lib.load()
+    grad, div, idx, G, D = _ops_and_oracle(B=3, P=300, k=12, cfg=6)
+    assert grad.graph.max_cloud == 300 and grad.graph.cloud_ptr is not None
+    N = idx.size(0)
+    ops = dc().ops
+    x0, v0 = torch.randn(N, C, device=DEV), torch.randn(2 * N, C, device=DEV)
+    results = []
+    for staged in (1, 0):
+        lib.dc_set_spmm_staged(staged)
+        try:
+            x, v = x0.clone().requires_grad_(True), v0.clone().requires_grad_(True)
+            cat, dcu = ops.scalar_cat(x, v, div)
+            xn = (x * 2).contiguous()
+            vcat = ops.vector_cat(v, dcu, xn, grad)
+            y = grad @ x
+            (cat.sum() * 0.5 + (vcat * vcat).sum() + (y * y).sum()).backward()
+            results.append([t_.detach().clone() for t_ in (cat, vcat, y, x.grad, v.grad)])
+        finally:
+            lib.dc_set_spmm_staged(1)
+    for a, b in zip(*results):
+        assert torch.equal(a, b)

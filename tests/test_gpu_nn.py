@@ -376,7 +376,7 @@ def test_graphed_train_step_matches_eager():
     from deltaconv_b200.parallel import FlatGradients
     from deltaconv_b200.utils.losses import calc_loss
     data = D.utils.synthetic_batch(4, 256, config=2, num_classes=10).to(DEV)
-    data._num_clouds = 4
+    data._num_clouds, data._max_points = 4, 256
     nets = []
     for _ in range(2):
         torch.manual_seed(0)
