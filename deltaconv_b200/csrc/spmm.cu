@@ -317,7 +317,7 @@ __global__ void __launch_bounds__(256) spmm_staged_kernel(SpArgs a, int CH, int 
 
 bool aligned16(const void* p) { return p == nullptr || (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
-int g_spmm_staged = 1;     // tuning switch (dc_set_spmm_staged)
+int g_spmm_staged = 0;     // tuning switch (dc_set_spmm_staged); off: measured slower than the L2-gather kernel, see DESIGN.md
 
 template <int OP>
 int launch_spmm(const SpArgs& a, cudaStream_t st) {
@@ -507,5 +507,5 @@ extern "C" int dc_hodge_bwd(const int32_t* in_ptr, const int32_t* in_edge, const
     return launch_spmm<OP_HODGE_T>(a, (cudaStream_t)stream);
 }
 
-// tuning switch: 1 (default) = stage a cloud's rows in shared memory when the cloud layout is known, 0 = always gather from L2
+// tuning switch: 1 = stage a cloud's rows in shared memory when the cloud layout is known, 0 (default) = gather from L2
 extern "C" int dc_set_spmm_staged(int v) { g_spmm_staged = v; return DC_OK; }

@@ -92,9 +92,10 @@ int dc_build_grad_div_static(const float* pos, const float* normal, const float*
 
 /* ---- operator application (SparseTensor @ dense and operators.py) --------------------------- */
 
-/* All six entry points below take (cloud_ptr_or_null, B, max_cloud_points): when the cloud layout is given and the largest
- * cloud fits, a CTA stages one cloud's rows in shared memory so the k-fold gathers never leave the SM; otherwise rows are
- * gathered from L2.  Both paths give bitwise identical results. */
+/* All six entry points below take (cloud_ptr_or_null, B, max_cloud_points).  They are used by an alternative kernel that
+ * stages one cloud's rows in shared memory so the k-fold gathers never leave the SM (dc_set_spmm_staged(1); needs the
+ * cloud layout and a cloud that fits).  It gives bitwise identical results but measured slower than the default L2-gather
+ * kernel on B200, so it is off by default. */
 int dc_set_spmm_staged(int v);
 /* grad @ x — deltanet_base.py:78, deltaconv.py:66:  out[2i+a,:] = sum_e G[i,e,a] x[idx[i,e],:] */
 int dc_grad_fwd(const int32_t* idx, const float* G, int N, int k, int C, const float* x, int64_t ldx,

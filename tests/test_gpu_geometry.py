@@ -344,6 +344,6 @@ def test_staged_spmm_is_bitwise_equal_to_the_gather_kernels(C):
             (cat.sum() * 0.5 + (vcat * vcat).sum() + (y * y).sum()).backward()
             results.append([t_.detach().clone() for t_ in (cat, vcat, y, x.grad, v.grad)])
         finally:
-            lib.dc_set_spmm_staged(1)
+            lib.dc_set_spmm_staged(0)
     for a, b in zip(*results):
         assert torch.equal(a, b)
