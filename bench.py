@@ -349,15 +349,22 @@ def run_cuda_arm(args):
                           gbps=round(r['bytes'] / sec / 1e9, 1) if sec > 0 else None,
                           tflops=round(r['flops'] / sec / 1e12, 2) if r['flops'] else None)
     tr = fam[top]
-    traffic = None
+    traffic, ncu = None, {}
     tpath = os.path.join(ROOT, 'profiles', 'ncu_traffic.json')
     if os.path.exists(tpath):
-        traffic = json.load(open(tpath)).get(top)
+        ncu = json.load(open(tpath)).get(top) or {}
+        traffic = ncu.get('dram_bytes_per_launch_avg')
     if tr['flops']:
         ach = tr['flops'] / (tr['ms'] / 1000) / 1e12
+        mode = int(lib.dc_get_gemm_mode())
         roof = dict(bound='tensor', kernel=KERNEL_OF.get(top, top), achieved=round(ach, 3), peak=pk['tensor'], unit='TFLOP/s',
                     frac=round(ach / pk['tensor'], 5), traffic=traffic, peak_source=pk['source'] + ', sustained bf16 (kernel timed inside a long step)',
-                    share_of_step=kernels[top]['share'])
+                    share_of_step=kernels[top]['share'],
+                    note=('achieved counts the 2*M*K*N algorithmic flops; in 3xTF32 mode the tensor cores execute 3x that in TF32 '
+                          '(whose dense peak is half the bf16 peak)') if mode == 3 else None,
+                    executed_tf32_tflops=round(ach * (3 if mode == 3 else 1), 2),
+                    algorithmic_bytes_per_launch=round(tr['bytes'] / max(tr['launches'], 1)),
+                    tensor_pipe_active_pct_ncu=ncu.get('tensor_pipe_active_pct_time_weighted'))
     else:
         ach = tr['bytes'] / (tr['ms'] / 1000) / 1e9
         roof = dict(bound='hbm', kernel=KERNEL_OF.get(top, top), achieved=round(ach, 1), peak=pk['hbm'], unit='GB/s',
