@@ -70,12 +70,12 @@ __global__ void central_stats_finalize_kernel(const double* __restrict__ partial
                                               double* __restrict__ moments, float* __restrict__ mean, float* __restrict__ invstd,
                                               float* __restrict__ running_mean, float* __restrict__ running_var) {
     __shared__ double mom[NMOM];
-    if (threadIdx.x < NMOM) {
+    {   // one warp per moment (blockDim.x = 32 * NMOM), lanes stride over the per-CTA partials, fixed-order shuffle tree
+        const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
         double s = 0.0;
-        for (int q = 0; q < chunks; ++q) s += partial[(size_t)q * NMOM + threadIdx.x];
-        s /= (double)E;
-        mom[threadIdx.x] = s;
-        moments[threadIdx.x] = s;
+        for (int q = lane; q < chunks; q += 32) s += partial[(size_t)q * NMOM + w];
+        s = warp_sum(s) / (double)E;
+        if (lane == 0) { mom[w] = s; moments[w] = s; }
     }
     __syncthreads();
     for (int c = threadIdx.x; c < Cout; c += blockDim.x) {
@@ -286,7 +286,7 @@ extern "C" int dc_central_stats(const int32_t* idx, int N, int k, int Cin, int C
     const long long E = (long long)N * k;
     const int chunks = moments_chunks(E);
     edge_moments_kernel<<<chunks, 256, 0, st>>>(idx, N, k, Cin, x, ldx, (double*)ws);
-    central_stats_finalize_kernel<<<1, 128, 0, st>>>((const double*)ws, chunks, E, Cin, Cout, W, eps, momentum, moments, mean, invstd,
+    central_stats_finalize_kernel<<<1, 32 * NMOM, 0, st>>>((const double*)ws, chunks, E, Cin, Cout, W, eps, momentum, moments, mean, invstd,
                                                      running_mean_or_null, running_var_or_null);
     return dc_check_launch_n("dc_central_stats", 2);
 }

@@ -115,7 +115,7 @@ template <int BN, bool A_MN, bool B_MN, bool SPLIT3, int STAGES, bool TS>
 __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA,
                                                                 const __grid_constant__ CUtensorMap tmB, TcArgs g) {
     constexpr uint32_t A_BYTES = TC_BM * 128, B_BYTES = BN * 128;
-    static_assert(!TS || (SPLIT3 && !A_MN), "A-from-TMEM is used for the split of a K-major A only");
+    static_assert(!TS || SPLIT3, "A-from-TMEM is the 3xTF32 path");
     // TS: the split A operand lives in tensor memory, so shared memory holds raw A (16 KB) + B hi/lo
     constexpr uint32_t STAGE_BYTES = TS ? A_BYTES + 2 * B_BYTES : (A_BYTES + B_BYTES) * (SPLIT3 ? 2 : 1);
     constexpr uint32_t CHUNK_BYTES = TC_BK * 128;                 // one 32-wide MN chunk of an MN-major tile
@@ -124,7 +124,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
     static_assert(TMEM_NEED <= 512, "tensor memory exhausted");
     constexpr uint32_t TMEM_A0 = 2 * BN;                          // first column of the A operand ring (TS)
     // instruction descriptor (cute::UMMA::InstrDescriptor): c=F32, a=b=TF32, majors, N>>3, M>>4
-    constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
+    constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | (((A_MN && !TS) ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
                                ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
 
     extern __shared__ unsigned char smem_raw[];
@@ -276,17 +276,31 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
                         // this thread owns one row of the A tile: read it through the 128-byte swizzle, split it, and
                         // store hi / lo into the row's TMEM lane (32 columns each)
                         const int row = (warp & 3) * 32 + lane;
-                        const float4* arow = reinterpret_cast<const float4*>(base_ptr + (stage_a(s) - base) + row * 128);
                         uint32_t hi[32], lo[32];
+                        if (A_MN) {
+                            // the tile was fetched unswizzled as 4 chunks of [32 reduction rows][32 columns]: this
+                            // thread's operand row is a COLUMN of its chunk (lanes hit consecutive banks) — the
+                            // transpose the MMA cannot do for an A operand in tensor memory happens here for free
+                            const float* acol = reinterpret_cast<const float*>(base_ptr + (stage_a(s) - base) + (row >> 5) * CHUNK_BYTES) + (row & 31);
 #pragma unroll
-                        for (int c = 0; c < 8; ++c) {
-                            const float4 x = arow[c ^ (row & 7)];
-                            const float v[4] = {x.x, x.y, x.z, x.w};
+                            for (int kx = 0; kx < 32; ++kx) {
+                                const float x = acol[kx * 32];
+                                const uint32_t h = __float_as_uint(x) & 0xffffe000u;
+                                hi[kx] = h;
+                                lo[kx] = __float_as_uint(x - __uint_as_float(h));
+                            }
+                        } else {
+                            const float4* arow = reinterpret_cast<const float4*>(base_ptr + (stage_a(s) - base) + row * 128);
 #pragma unroll
-                            for (int u = 0; u < 4; ++u) {
-                                const uint32_t h = __float_as_uint(v[u]) & 0xffffe000u;
-                                hi[4 * c + u] = h;
-                                lo[4 * c + u] = __float_as_uint(v[u] - __uint_as_float(h));
+                            for (int c = 0; c < 8; ++c) {
+                                const float4 x = arow[c ^ (row & 7)];
+                                const float v[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+                                for (int u = 0; u < 4; ++u) {
+                                    const uint32_t h = __float_as_uint(v[u]) & 0xffffe000u;
+                                    hi[4 * c + u] = h;
+                                    lo[4 * c + u] = __float_as_uint(v[u] - __uint_as_float(h));
+                                }
                             }
                         }
                         const uint32_t ta = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + TMEM_A0 + (uint32_t)s * 64u;
@@ -393,7 +407,8 @@ EncodeTiledFn encode_fn() {
 
 // 2-D fp32 tensor map: inner (contiguous) extent x outer extent with row pitch ld elements; 128-byte swizzle;
 // out-of-bounds elements read as zero (that is what pads ragged M / N / K edges).
-bool make_map(CUtensorMap* map, const float* ptr, long long inner, long long outer, long long ld, int box_outer, bool mn_major) {
+// swizzle: 0 = none (tile only read by threads), 1 = 128B (K-major UMMA operand), 2 = 128B with 32-byte atoms (MN-major tf32 operand)
+bool make_map(CUtensorMap* map, const float* ptr, long long inner, long long outer, long long ld, int box_outer, int swizzle) {
     EncodeTiledFn fn = encode_fn();
     if (!fn) return false;
     cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
@@ -401,7 +416,8 @@ bool make_map(CUtensorMap* map, const float* ptr, long long inner, long long out
     cuuint32_t box[2] = {32u, (cuuint32_t)box_outer};
     cuuint32_t estr[2] = {1u, 1u};
     return fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-              mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+              swizzle == 0 ? CU_TENSOR_MAP_SWIZZLE_NONE : swizzle == 1 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B,
+              CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
 int g_tc_no_ts = 0;      // experiment switch: 1 = keep the split A operand in shared memory (SS MMAs)
@@ -415,7 +431,7 @@ template <int BN, bool SPLIT3, bool TS> struct TcStages {
 
 template <int BN, bool A_MN, bool B_MN, bool SPLIT3>
 int launch_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const TcArgs& g, long long num_tiles, cudaStream_t st) {
-    constexpr bool TS = SPLIT3 && !A_MN;       // K-major A: split into tensor memory instead of shared memory
+    constexpr bool TS = SPLIT3;                // the split A operand lives in tensor memory instead of shared memory
     constexpr int STAGES = TcStages<BN, SPLIT3, TS>::value;
     static_assert(STAGES >= 2, "tile too large for shared memory");
     const size_t smem = (size_t)STAGES * TcStages<BN, SPLIT3, TS>::per_stage + 1024 /*alignment*/ + 8 * (3 * TC_MAX_STAGES + 4) + 16;
@@ -470,8 +486,10 @@ int dc_tc_gemm(const float* A, long long lda, int a_mn, const float* B, long lon
     if (M >= 2147483647LL || K >= 2147483647LL) return 1;
     const int BN = N <= 64 ? 64 : 128;
     CUtensorMap tmA, tmB;
-    bool ok = a_mn ? make_map(&tmA, A, M, K, lda, TC_BK, true) : make_map(&tmA, A, K, M, lda, TC_BM, false);
-    ok = ok && (b_mn ? make_map(&tmB, B, N, K, ldb, TC_BK, true) : make_map(&tmB, B, K, N, ldb, BN, false));
+    // an MN-major A goes through tensor memory in the 3xTF32 path (the converters transpose it), so it is fetched unswizzled
+    const bool a_via_tmem = g_tc_mode == 3 && !g_tc_no_ts;
+    bool ok = a_mn ? make_map(&tmA, A, M, K, lda, TC_BK, a_via_tmem ? 0 : 2) : make_map(&tmA, A, K, M, lda, TC_BM, 1);
+    ok = ok && (b_mn ? make_map(&tmB, B, N, K, ldb, TC_BK, 2) : make_map(&tmB, B, K, N, ldb, BN, 1));
     if (!ok) return 1;
     const int total_kb = (int)((K + TC_BK - 1) / TC_BK);
     const long long tiles = ((M + TC_BM - 1) / TC_BM) * ((N + BN - 1) / BN);

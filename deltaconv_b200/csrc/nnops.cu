@@ -218,6 +218,59 @@ struct VnlBwdVal {
     }
 };
 
+// float4 variants of the two element-wise VectorNonLin kernels (C % 4 == 0, aligned): same per-element math
+__global__ void vecnonlin_fwd_vec4_kernel(const float* __restrict__ v, long long ldv, long long M, int C4,
+                                          const float* __restrict__ mean, const float* __restrict__ invstd,
+                                          const float* __restrict__ gamma, const float* __restrict__ beta,
+                                          const float* __restrict__ bias, float* __restrict__ out, long long ldo) {
+    const long long total = M * (long long)C4;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+        const long long r = t / C4;
+        const int c = (int)(t - r * C4) * 4;
+        const float4 a = ld_stream4(reinterpret_cast<const float4*>(v + (2 * r) * ldv + c));
+        const float4 b = ld_stream4(reinterpret_cast<const float4*>(v + (2 * r + 1) * ldv + c));
+        const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+        float oa[4], ob[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            float n = sqrtf(av[u] * av[u] + bv[u] * bv[u]);
+            float s_ = fmaxf(vnl_shift(n, c + u, mean, invstd, gamma, beta, bias), 0.f) / fmaxf(n, 1e-8f);
+            oa[u] = av[u] * s_; ob[u] = bv[u] * s_;
+        }
+        *reinterpret_cast<float4*>(out + (2 * r) * ldo + c) = make_float4(oa[0], oa[1], oa[2], oa[3]);
+        *reinterpret_cast<float4*>(out + (2 * r + 1) * ldo + c) = make_float4(ob[0], ob[1], ob[2], ob[3]);
+    }
+}
+
+__device__ __forceinline__ void vnl_bwd_one(float a, float b, float da, float db, int c, long long r, int C, const float* mean, const float* invstd,
+                                            const float* gamma, const float* beta, const float* bias, const float* sum_dz,
+                                            const float* sum_dz_xh, int training, float invM, float* dbias_rows, float& oa, float& ob) {
+    float n = sqrtf(a * a + b * b), nc = fmaxf(n, 1e-8f);
+    float z, dn_from_q;        // dn_from_q: gradient w.r.t. n through q = relu(shift(n))
+    float dq = (da * a + db * b) / nc;
+    if (mean) {
+        float is = __ldg(invstd + c);
+        float xh = (n - __ldg(mean + c)) * is;
+        float g = gamma ? __ldg(gamma + c) : 1.f, be = beta ? __ldg(beta + c) : 0.f;
+        z = g * xh + be;
+        float dz = z > 0.f ? dq : 0.f;
+        float core = training ? dz - __ldg(sum_dz + c) * invM - xh * (__ldg(sum_dz_xh + c) * invM) : dz;
+        dn_from_q = g * is * core;
+    } else {
+        z = n + __ldg(bias + c);
+        dn_from_q = z > 0.f ? dq : 0.f;
+        if (dbias_rows) dbias_rows[r * C + c] = dn_from_q;
+    }
+    float q = fmaxf(z, 0.f);
+    float h = q / nc;
+    // through the 1/max(n,eps) factor: -q/n^2 * (dout . v) when n > eps
+    float dn_from_h = n > 1e-8f ? -(da * a + db * b) * q / (nc * nc) : 0.f;
+    float dn = dn_from_q + dn_from_h;
+    float inv_n = n > 0.f ? 1.f / n : 0.f;     // d n / d v = v / n   (0 at the origin)
+    oa = da * h + dn * a * inv_n;
+    ob = db * h + dn * b * inv_n;
+}
+
 __global__ void vecnonlin_bwd_kernel(const float* __restrict__ v, long long ldv, const float* __restrict__ dout, long long ldd,
                                      long long M, int C, const float* __restrict__ mean, const float* __restrict__ invstd,
                                      const float* __restrict__ gamma, const float* __restrict__ beta, const float* __restrict__ bias,
@@ -227,32 +280,38 @@ __global__ void vecnonlin_bwd_kernel(const float* __restrict__ v, long long ldv,
     const float invM = 1.f / (float)M;
     for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
         long long r = t / C; int c = (int)(t - r * C);
-        float a = __ldg(v + (2 * r) * ldv + c), b = __ldg(v + (2 * r + 1) * ldv + c);
-        float da = __ldg(dout + (2 * r) * ldd + c), db = __ldg(dout + (2 * r + 1) * ldd + c);
-        float n = sqrtf(a * a + b * b), nc = fmaxf(n, 1e-8f);
-        float z, dn_from_q;        // dn_from_q: gradient w.r.t. n through q = relu(shift(n))
-        float dq = (da * a + db * b) / nc;
-        if (mean) {
-            float is = __ldg(invstd + c);
-            float xh = (n - __ldg(mean + c)) * is;
-            float g = gamma ? __ldg(gamma + c) : 1.f, be = beta ? __ldg(beta + c) : 0.f;
-            z = g * xh + be;
-            float dz = z > 0.f ? dq : 0.f;
-            float core = training ? dz - __ldg(sum_dz + c) * invM - xh * (__ldg(sum_dz_xh + c) * invM) : dz;
-            dn_from_q = g * is * core;
-        } else {
-            z = n + __ldg(bias + c);
-            dn_from_q = z > 0.f ? dq : 0.f;
-            if (dbias_rows) dbias_rows[r * C + c] = dn_from_q;
-        }
-        float q = fmaxf(z, 0.f);
-        float h = q / nc;
-        // through the 1/max(n,eps) factor: -q/n^2 * (dout . v) when n > eps
-        float dn_from_h = n > 1e-8f ? -(da * a + db * b) * q / (nc * nc) : 0.f;
-        float dn = dn_from_q + dn_from_h;
-        float inv_n = n > 0.f ? 1.f / n : 0.f;     // d n / d v = v / n   (0 at the origin)
-        dv[(2 * r) * ld_dv + c] = da * h + dn * a * inv_n;
-        dv[(2 * r + 1) * ld_dv + c] = db * h + dn * b * inv_n;
+        float oa, ob;
+        vnl_bwd_one(__ldg(v + (2 * r) * ldv + c), __ldg(v + (2 * r + 1) * ldv + c), __ldg(dout + (2 * r) * ldd + c),
+                    __ldg(dout + (2 * r + 1) * ldd + c), c, r, C, mean, invstd, gamma, beta, bias, sum_dz, sum_dz_xh, training, invM,
+                    dbias_rows, oa, ob);
+        dv[(2 * r) * ld_dv + c] = oa;
+        dv[(2 * r + 1) * ld_dv + c] = ob;
+    }
+}
+
+__global__ void vecnonlin_bwd_vec4_kernel(const float* __restrict__ v, long long ldv, const float* __restrict__ dout, long long ldd,
+                                          long long M, int C, const float* __restrict__ mean, const float* __restrict__ invstd,
+                                          const float* __restrict__ gamma, const float* __restrict__ beta, const float* __restrict__ bias,
+                                          const float* __restrict__ sum_dz, const float* __restrict__ sum_dz_xh, int training,
+                                          float* __restrict__ dv, long long ld_dv, float* __restrict__ dbias_rows) {
+    const int C4 = C >> 2;
+    const long long total = M * (long long)C4;
+    const float invM = 1.f / (float)M;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+        const long long r = t / C4;
+        const int c = (int)(t - r * C4) * 4;
+        const float4 a = ld_stream4(reinterpret_cast<const float4*>(v + (2 * r) * ldv + c));
+        const float4 b = ld_stream4(reinterpret_cast<const float4*>(v + (2 * r + 1) * ldv + c));
+        const float4 da = ld_stream4(reinterpret_cast<const float4*>(dout + (2 * r) * ldd + c));
+        const float4 db = ld_stream4(reinterpret_cast<const float4*>(dout + (2 * r + 1) * ldd + c));
+        const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w}, dav[4] = {da.x, da.y, da.z, da.w}, dbv[4] = {db.x, db.y, db.z, db.w};
+        float oa[4], ob[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            vnl_bwd_one(av[u], bv[u], dav[u], dbv[u], c + u, r, C, mean, invstd, gamma, beta, bias, sum_dz, sum_dz_xh, training, invM,
+                        dbias_rows, oa[u], ob[u]);
+        *reinterpret_cast<float4*>(dv + (2 * r) * ld_dv + c) = make_float4(oa[0], oa[1], oa[2], oa[3]);
+        *reinterpret_cast<float4*>(dv + (2 * r + 1) * ld_dv + c) = make_float4(ob[0], ob[1], ob[2], ob[3]);
     }
 }
 
@@ -607,8 +666,12 @@ extern "C" int dc_vecnonlin_fwd(const float* v, int64_t ldv, int64_t M, int C, c
                                 const float* bias_or_null, float* out, int64_t ldo, void* stream) {
     DC_REQUIRE(mean_or_null != nullptr || bias_or_null != nullptr, "dc_vecnonlin_fwd: need BN statistics or a bias");
     if (M <= 0 || C <= 0) return DC_OK;
-    vecnonlin_fwd_kernel<<<elementwise_grid(M * C), 256, 0, (cudaStream_t)stream>>>(v, ldv, M, C, mean_or_null, invstd_or_null,
-                                                                                    gamma_or_null, beta_or_null, bias_or_null, out, ldo);
+    if (C % 4 == 0 && ldv % 4 == 0 && ldo % 4 == 0 && all_aligned16(v, out))
+        vecnonlin_fwd_vec4_kernel<<<elementwise_grid(M * C / 4), 256, 0, (cudaStream_t)stream>>>(v, ldv, M, C / 4, mean_or_null, invstd_or_null,
+                                                                                             gamma_or_null, beta_or_null, bias_or_null, out, ldo);
+    else
+        vecnonlin_fwd_kernel<<<elementwise_grid(M * C), 256, 0, (cudaStream_t)stream>>>(v, ldv, M, C, mean_or_null, invstd_or_null,
+                                                                                        gamma_or_null, beta_or_null, bias_or_null, out, ldo);
     return dc_check_launch("dc_vecnonlin_fwd");
 }
 
@@ -630,9 +693,14 @@ extern "C" int dc_vecnonlin_bwd(const float* v, int64_t ldv, const float* dout, 
         col_reduce_kernel<2><<<grid, RED_T, 0, st>>>(f, M, C, L.col_lanes, L.rows_per_chunk, partial);
         sum2_finalize_kernel<<<dc_ceil_div(C, FIN_COLS), FIN_T, 0, st>>>(partial, L.chunks, C, d_beta, d_gamma);
     }
-    vecnonlin_bwd_kernel<<<elementwise_grid(M * C), 256, 0, st>>>(v, ldv, dout, ldd, M, C, mean_or_null, invstd_or_null, gamma_or_null,
-                                                                  beta_or_null, bias_or_null, d_beta, d_gamma, training, dv, ld_dv,
-                                                                  dbias_rows_or_null);
+    if (C % 4 == 0 && ldv % 4 == 0 && ldd % 4 == 0 && ld_dv % 4 == 0 && all_aligned16(v, dout, dv))
+        vecnonlin_bwd_vec4_kernel<<<elementwise_grid(M * C / 4), 256, 0, st>>>(v, ldv, dout, ldd, M, C, mean_or_null, invstd_or_null, gamma_or_null,
+                                                                           beta_or_null, bias_or_null, d_beta, d_gamma, training, dv, ld_dv,
+                                                                           dbias_rows_or_null);
+    else
+        vecnonlin_bwd_kernel<<<elementwise_grid(M * C), 256, 0, st>>>(v, ldv, dout, ldd, M, C, mean_or_null, invstd_or_null, gamma_or_null,
+                                                                      beta_or_null, bias_or_null, d_beta, d_gamma, training, dv, ld_dv,
+                                                                      dbias_rows_or_null);
     return dc_check_launch_n("dc_vecnonlin_bwd", mean_or_null ? 3 : 1);
 }
 
