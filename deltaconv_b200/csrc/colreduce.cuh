@@ -27,7 +27,7 @@ ColLayout col_layout(long long M, int C) {
     L.col_lanes = cl;
     L.row_lanes = RED_T / cl;
     L.col_blocks = (C + cl - 1) / cl;
-    long long want = (long long)dc_sm_count() * 2 / L.col_blocks;
+    long long want = (long long)dc_sm_count() * 4 / L.col_blocks;
     if (want < 1) want = 1;
     long long by_rows = (M + L.row_lanes * 4 - 1) / (L.row_lanes * 4);   // at least 4 rows per thread
     if (by_rows < 1) by_rows = 1;

@@ -37,10 +37,14 @@ class GraphedTrainStep:
         torch.cuda.synchronize()
         self.graph_fb = torch.cuda.CUDAGraph()
         self.graph_opt = None
+        self._graph_grads = None
         if self.distributed:
-            # the collective stays outside the graphs: fwd+bwd graph -> NCCL all-reduce -> optimizer graph
+            # the collective stays outside the graphs: fwd+bwd graph -> pack + NCCL all-reduce -> optimizer graph.
+            # The gradients a replay produces live in graph memory: keep the tensors so every step can pack them.
             with torch.cuda.graph(self.graph_fb):
                 self.loss = self._forward_backward()
+            self._graph_grads = [p.grad for p in self.flat.params if p.grad is not None]
+            self.flat.all_reduce(sources=self._graph_grads)          # p.grad now are views of the (static) flat buffer
             self.graph_opt = torch.cuda.CUDAGraph()
             with torch.cuda.graph(self.graph_opt, pool=self.graph_fb.pool()):
                 self.optimizer.step()
@@ -64,6 +68,6 @@ class GraphedTrainStep:
     def __call__(self):
         self.graph_fb.replay()
         if self.graph_opt is not None:
-            self.flat.all_reduce()
+            self.flat.all_reduce(sources=self._graph_grads)
             self.graph_opt.replay()
         return self.loss

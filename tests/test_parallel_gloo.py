@@ -45,9 +45,11 @@ def _worker(rank, world, port, out):
     flat.zero()
     loss = ((model(x[b:e]) - y[b:e]) ** 2).sum() / 8 * world      # local mean scaled so the rank-average is the global mean
     loss.backward()
-    flat.all_reduce()
+    reduced = flat.all_reduce()
+    assert model.extra.grad is None                                 # never used: skipped on every rank
+    assert model[0].weight.grad.data_ptr() == reduced.data_ptr()    # grads are views of the reduced flat buffer
     if rank == 0:
-        torch.save(flat.flat.clone(), out)
+        torch.save(reduced.clone(), out)
     dist.destroy_process_group()
 
 
@@ -61,6 +63,8 @@ def test_flat_gradient_allreduce_matches_single_process(tmp_path):
     model = _model()
     flat = FlatGradients(model.parameters())
     (((model(x) - y) ** 2).sum() / 8).backward()
-    assert torch.allclose(got, flat.flat, atol=1e-6)
-    assert (model.extra.grad == 0).all() and (got[:4] == 0).all()      # `extra` is registered first
-    assert model[0].weight.grad.data_ptr() == flat.flat.data_ptr() + 16      # grads are views of the flat buffer
+    assert flat.all_reduce() is None                                # single process: nothing to pack or reduce
+    want = torch.cat([p.grad.reshape(-1) for p in model.parameters() if p.grad is not None])
+    assert torch.allclose(got, want, atol=1e-6)
+    flat.zero()
+    assert all(p.grad is None for p in model.parameters())
