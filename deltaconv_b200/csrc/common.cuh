@@ -42,7 +42,12 @@ static inline int dc_ceil_div(long long a, long long b) { return (int)((a + b - 
 // back to the fp32 SIMT kernel), <0 on error; *launches = kernels launched
 int dc_tc_gemm(const float* A, long long lda, int a_mn, const float* B, long long ldb, int b_mn, const float* bias,
                long long M, int N, long long K, float* C, long long ldc, void* ws, size_t ws_bytes, cudaStream_t st,
-               int* launches);
+               int* launches, double* stats, int* stats_chunks);
+// stats (optional): [ceil(M/128)][2][N] doubles receiving per-128-row column sums of C and C^2; *stats_chunks = number of
+// chunks written (0 when the product was split along K or did not run on the tensor-core path)
+// BatchNorm finalize over such partials (nnops.cu)
+int dc_bn_finalize_launch(const double* partial, int chunks, long long M, int C, float eps, float momentum, float* mean,
+                          float* invstd, float* running_mean, float* running_var, cudaStream_t st);
 size_t dc_tc_ws_bytes(long long M, long long N, long long K);
 
 // cached SM count of the current device (148 on B200)

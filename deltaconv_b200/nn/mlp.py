@@ -38,6 +38,11 @@ class _LinBNAct(torch.nn.Sequential):
     def forward(self, x, addend=None):
         lin, bn, act = self[0], self[1], self[2]
         slope = _slope_of(act)
+        inner = bn.bn
+        batch_stats = inner.training or not inner.track_running_stats or inner.running_mean is None
+        if slope is not None and lin.bias is None and batch_stats and x.dim() == 2:
+            # Linear + BatchNorm statistics + activation as one node (statistics come out of the GEMM epilogue)
+            return ops.linear_bn_act(x, lin.weight, inner, slope, addend)
         y = lin(x)
         if slope is None:
             out = act(bn(y))

@@ -557,6 +557,77 @@ def bn_act(y, bn, slope=1.0, addend=None):
     return _BNAct.apply(y, bn.weight, bn.bias, addend, bn, float(slope))
 
 
+class _LinearBNAct(torch.autograd.Function):
+    """Linear (no bias) -> BatchNorm1d (batch statistics) -> LeakyReLU(slope) (+ addend) as ONE autograd node
+    (mlp.py:9): the GEMM epilogue already produces the column sums BatchNorm needs, so the pre-activation is
+    written once and read once."""
+
+    @staticmethod
+    def forward(ctx, x, weight, gamma, beta, addend, bn, slope):
+        x, ldx = _mat(x, 'input')
+        weight, ldw = _mat(weight, 'weight')
+        if x.size(1) != weight.size(1):
+            raise _lib.DeltaConvLibraryError(f"Linear: input has {x.size(1)} features, weight expects {weight.size(1)}")
+        M, K, C = x.size(0), x.size(1), weight.size(0)
+        if M == 0:
+            raise _lib.DeltaConvLibraryError("BatchNorm1d: empty batch")
+        dev = x.device
+        y = torch.empty(M, C, dtype=_F32, device=dev)
+        mean = torch.empty(C, dtype=_F32, device=dev)
+        invstd = torch.empty(C, dtype=_F32, device=dev)
+        update = bn.training and bn.track_running_stats and bn.running_mean is not None
+        momentum = 0.0
+        if update:
+            bn.num_batches_tracked += 1
+            momentum = bn.momentum if bn.momentum is not None else 1.0 / float(bn.num_batches_tracked)
+        nb = query('dc_linear_bnstats_ws_bytes', M, C, K)
+        ws = workspace(nb, dev)
+        call('dc_linear_fwd_bnstats', ptr(x), ldx, ptr(weight), ldw, M, K, C, ptr(y), C, float(bn.eps), float(momentum),
+             ptr(mean), ptr(invstd), ptr(bn.running_mean) if update else None, ptr(bn.running_var) if update else None,
+             ptr(ws), nb)
+        out = torch.empty(M, C, dtype=_F32, device=dev)
+        add_p, ld_add = None, 0
+        if addend is not None:
+            addend, ld_add = _mat(addend, 'addend')
+            add_p = ptr(addend)
+        call('dc_bn_act_fwd', ptr(y), C, M, C, ptr(mean), ptr(invstd), ptr(gamma), ptr(beta), float(slope), add_p, ld_add, ptr(out), C)
+        ctx.save_for_backward(x, weight, y, mean, invstd, gamma, beta)
+        ctx.slope, ctx.has_add = slope, addend is not None
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        x, weight, y, mean, invstd, gamma, beta = ctx.saved_tensors
+        x, ldx = _mat(x)
+        weight, ldw = _mat(weight)
+        dout, ldd = _mat(dout, 'grad_output')
+        M, K, C = x.size(0), x.size(1), weight.size(0)
+        dev = x.device
+        dgamma = torch.empty(C, dtype=_F32, device=dev)
+        dbeta = torch.empty(C, dtype=_F32, device=dev)
+        dy = torch.empty(M, C, dtype=_F32, device=dev)
+        nb = query('dc_colreduce_ws_bytes', C)
+        ws = workspace(nb, dev)
+        call('dc_bn_act_bwd', ptr(y), C, ptr(dout), ldd, M, C, ptr(mean), ptr(invstd), ptr(gamma), ptr(beta), float(ctx.slope), 1,
+             ptr(dgamma), ptr(dbeta), ptr(dy), C, ptr(ws), nb)
+        dx = dw = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty(M, K, dtype=_F32, device=dev)
+            ws, nb = _gemm_ws(M, K, C, dev)
+            call('dc_linear_bwd_input', ptr(dy), C, ptr(weight), ldw, M, K, C, ptr(dx), K, ptr(ws), nb)
+        if ctx.needs_input_grad[1]:
+            dw = torch.empty(C, K, dtype=_F32, device=dev)
+            ws, nb = _gemm_ws(C, K, M, dev)
+            call('dc_linear_bwd_weight', ptr(dy), C, ptr(x), ldx, M, K, C, ptr(dw), K, ptr(ws), nb)
+        return (dx, dw, dgamma if gamma is not None else None, dbeta if beta is not None else None,
+                dout if ctx.has_add else None, None, None)
+
+
+def linear_bn_act(x, weight, bn, slope=1.0, addend=None):
+    """act(BatchNorm1d(x @ weight.T)) + addend with batch statistics (training mode)."""
+    return _LinearBNAct.apply(x, weight, bn.weight, bn.bias, addend, bn, float(slope))
+
+
 class _VecNonLin(torch.autograd.Function):
     @staticmethod
     def forward(ctx, v, gamma, beta, bias, bn):

@@ -446,3 +446,31 @@ def test_full_size_configs_run_and_are_deterministic():
             assert torch.isfinite(logits).all() and torch.isfinite(g).all()
             outs.append((logits.detach().clone(), g.clone()))
         assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+
+
+@pytest.mark.parametrize('M,K,C', [(32768, 256, 64), (5000, 64, 128), (4096, 512, 1024), (777, 12, 40), (100, 36, 20)])
+def test_fused_linear_batchnorm_block(M, K, C):
+    """MLP block with BatchNorm statistics taken from the GEMM epilogue vs torch fp64 (Linear -> BN(train) -> LeakyReLU + addend)."""
+    D = dc()
+    mlp = D.nn.MLP([K, C]).to(DEV).train()
+    with torch.no_grad():
+        mlp[0][1].bn.weight.copy_(torch.randn(C) * 0.3 + 1)
+        mlp[0][1].bn.bias.copy_(torch.randn(C) * 0.3)
+    ref_lin = torch.nn.Linear(K, C, bias=False).double()
+    ref_bn = torch.nn.BatchNorm1d(C).double()
+    ref_lin.weight.data.copy_(mlp[0][0].weight.detach().cpu().double())
+    ref_bn.weight.data.copy_(mlp[0][1].bn.weight.detach().cpu().double())
+    ref_bn.bias.data.copy_(mlp[0][1].bn.bias.detach().cpu().double())
+    x0, add0, g0 = torch.randn(M, K) + 0.5, torch.randn(M, C), torch.randn(M, C)
+    x, add = x0.to(DEV).requires_grad_(True), add0.to(DEV).requires_grad_(True)
+    out = mlp(x, add)
+    (out * g0.to(DEV)).sum().backward()
+    xr, addr = x0.double().requires_grad_(True), add0.double().requires_grad_(True)
+    outr = F.leaky_relu(ref_bn(ref_lin(xr)), 0.2) + addr
+    (outr * g0.double()).sum().backward()
+    assert report(f'fused_lin_bn.{M}x{K}x{C}.out', rel_err(out.detach().cpu(), outr.detach())) < 1e-5
+    assert rel_err(x.grad.cpu(), xr.grad) < 1e-4 and rel_err(add.grad.cpu(), addr.grad) < 1e-6
+    assert rel_err(mlp[0][0].weight.grad.cpu(), ref_lin.weight.grad) < 1e-4
+    assert rel_err(mlp[0][1].bn.weight.grad.cpu(), ref_bn.weight.grad) < 1e-4
+    assert rel_err(mlp[0][1].bn.running_mean.cpu(), ref_bn.running_mean) < 1e-5
+    assert rel_err(mlp[0][1].bn.running_var.cpu(), ref_bn.running_var) < 1e-5
