@@ -27,7 +27,6 @@ constexpr int TC_BM = 128;          // UMMA_M (cta_group::1)
 constexpr int TC_BK = 32;           // fp32 elements per k-block = one 128-byte swizzle span
 constexpr int TC_THREADS = 320;       // TMA, MMA, 4 converter warps, 4 epilogue warps
 constexpr int TC_MAX_STAGES = 4;
-#define TC_EPI_BYTES(BN) (4 * 32 * 33 * 4 + 4 * 2 * (BN) * 4)     // epilogue transpose tiles + BatchNorm partial sums
 
 struct TcArgs {
     float* C; long long ldc;
@@ -35,7 +34,6 @@ struct TcArgs {
     int M, N, K;
     int kb_per_split;       // k-blocks per grid.z slice
     float* partial;         // [splits][M][N] when split-K
-    double* stats;          // optional [tiles_m][2][N]: per-m-tile column sums of C and C^2 (BatchNorm statistics), splits == 1 only
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -139,7 +137,6 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
     auto acc_full_bar = [&](int a) { return bar_base + 8u * (3 * TC_MAX_STAGES + a); };
     auto acc_empty_bar = [&](int a) { return bar_base + 8u * (3 * TC_MAX_STAGES + 2 + a); };
     const uint32_t tmem_slot = bar_base + 8u * (3 * TC_MAX_STAGES + 4);
-    const uint32_t epi_base = (tmem_slot + 16u + 15u) & ~15u;          // 4 transpose tiles [32][33] + statistics [4][2][BN]
     volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(base_ptr + (tmem_slot - base));
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -323,76 +320,55 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
             }
         }
     } else {
-        // ===================== epilogue: TMEM -> registers -> smem transpose -> HBM =====================
-        // A thread reads one accumulator ROW from tensor memory; writing rows straight out would cost 32 memory
-        // transactions per store instruction.  Each warp therefore transposes 32x32 slabs through a private
-        // shared-memory tile so that every store instruction writes one contiguous 128-byte row segment, and each
-        // lane then owns one COLUMN — which is exactly what the fused BatchNorm statistics need.
+        // ===================== epilogue: TMEM -> registers -> HBM =====================
         const int q = warp & 3;                                   // TMEM lane quarter this warp may read
-        float* tile = reinterpret_cast<float*>(base_ptr + (epi_base - base)) + q * (32 * 33);
-        float* stat_sh = reinterpret_cast<float*>(base_ptr + (epi_base - base)) + 4 * (32 * 33);      // [4][2][BN]
         uint32_t tcount = 0;
-        for (long long tile_id = blockIdx.x; tile_id < num_tiles; tile_id += gridDim.x, ++tcount) {
+        for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tcount) {
             int m0, n0, kb_begin, nkb;
-            decode(tile_id, m0, n0, kb_begin, nkb);
+            decode(tile, m0, n0, kb_begin, nkb);
             const uint32_t acc = tcount & 1, acc_ph = (tcount >> 1) & 1;
             mbar_wait(acc_full_bar(acc), acc_ph);
             tc_fence_after();
-            const int z = (int)(tile_id / ((long long)tiles_n * tiles_m));
-            const int row0 = m0 + q * 32;
+            const int z = (int)(tile / ((long long)tiles_n * tiles_m));
+            const int row = m0 + q * 32 + lane;
             float* out = g.partial ? g.partial + (size_t)z * g.M * g.N : g.C;
             const long long ldo = g.partial ? g.N : g.ldc;
-            const int rows_here = min(32, g.M - row0);              // may be <= 0 for the ragged last tile
+            const bool vec_ok = (ldo % 4 == 0) && ((reinterpret_cast<uintptr_t>(out) & 15u) == 0);
 #pragma unroll 1
-            for (int c0 = 0; c0 < BN; c0 += 32) {
+            for (int c0 = 0; c0 < BN; c0 += 16) {
                 if (n0 + c0 >= g.N) break;                            // warp-uniform
-                uint32_t r[32];
+                uint32_t r[16];
                 const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(q * 32) << 16) + (uint32_t)c0;
-                asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
-                             "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+                asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
                              : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-                               "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
-                               "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
-                               "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+                               "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
                              : "r"(taddr));
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                if (row < g.M) {
+                    float* dst = out + (long long)row * ldo + n0 + c0;
 #pragma unroll
-                for (int c = 0; c < 32; ++c) tile[lane * 33 + c] = __uint_as_float(r[c]);     // row = lane
-                __syncwarp();
-                const int col = n0 + c0 + lane;                       // column = lane
-                const bool col_ok = col < g.N;
-                const float bias = (!g.partial && g.bias && col_ok) ? __ldg(g.bias + col) : 0.f;
-                float s1 = 0.f, s2 = 0.f;
-#pragma unroll 8
-                for (int rr = 0; rr < 32; ++rr) {
-                    if (rr < rows_here) {                              // warp-uniform
-                        const float v = tile[rr * 33 + lane] + bias;
-                        s1 += v; s2 += v * v;
-                        if (col_ok) out[(long long)(row0 + rr) * ldo + col] = v;
+                    for (int v = 0; v < 4; ++v) {
+                        const int col = n0 + c0 + 4 * v;
+                        float4 o = make_float4(__uint_as_float(r[4 * v]), __uint_as_float(r[4 * v + 1]), __uint_as_float(r[4 * v + 2]), __uint_as_float(r[4 * v + 3]));
+                        if (!g.partial && g.bias) {
+                            if (col < g.N) o.x += __ldg(g.bias + col);
+                            if (col + 1 < g.N) o.y += __ldg(g.bias + col + 1);
+                            if (col + 2 < g.N) o.z += __ldg(g.bias + col + 2);
+                            if (col + 3 < g.N) o.w += __ldg(g.bias + col + 3);
+                        }
+                        if (vec_ok && col + 3 < g.N) *reinterpret_cast<float4*>(dst + 4 * v) = o;
+                        else {
+                            if (col < g.N) dst[4 * v] = o.x;
+                            if (col + 1 < g.N) dst[4 * v + 1] = o.y;
+                            if (col + 2 < g.N) dst[4 * v + 2] = o.z;
+                            if (col + 3 < g.N) dst[4 * v + 3] = o.w;
+                        }
                     }
                 }
-                if (g.stats) { stat_sh[(q * 2 + 0) * BN + c0 + lane] = s1; stat_sh[(q * 2 + 1) * BN + c0 + lane] = s2; }
-                __syncwarp();
             }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(acc_empty_bar(acc));           // this warp's quarter of the accumulator is free
-            if (g.stats) {
-                // combine the four 32-row quarters of the tile (fixed order) and publish one partial per column
-                asm volatile("bar.sync 1, 128;" ::: "memory");
-                const int mt = (int)((tile_id / tiles_n) % tiles_m);
-                for (int c = threadIdx.x - 192; c < BN; c += 128) {
-                    const int col = n0 + c;
-                    if (col < g.N) {
-                        double a1 = 0.0, a2 = 0.0;
-#pragma unroll
-                        for (int qq = 0; qq < 4; ++qq) { a1 += (double)stat_sh[(qq * 2 + 0) * BN + c]; a2 += (double)stat_sh[(qq * 2 + 1) * BN + c]; }
-                        g.stats[((size_t)mt * 2 + 0) * g.N + col] = a1;
-                        g.stats[((size_t)mt * 2 + 1) * g.N + col] = a2;
-                    }
-                }
-                asm volatile("bar.sync 1, 128;" ::: "memory");        // stat_sh is reused by the next tile
-            }
         }
     }
     tc_fence_before();
@@ -448,7 +424,7 @@ int g_tc_no_ts = 0;      // experiment switch: 1 = keep the split A operand in s
 
 template <int BN, bool SPLIT3, bool TS> struct TcStages {
     static constexpr int per_stage = TS ? (TC_BM + 2 * BN) * 128 : (TC_BM + BN) * 128 * (SPLIT3 ? 2 : 1);
-    static constexpr int by_smem = (196 * 1024) / per_stage > TC_MAX_STAGES ? TC_MAX_STAGES : (196 * 1024) / per_stage;
+    static constexpr int by_smem = (200 * 1024) / per_stage > TC_MAX_STAGES ? TC_MAX_STAGES : (200 * 1024) / per_stage;
     static constexpr int by_tmem = TS ? (512 - 2 * BN) / 64 : TC_MAX_STAGES;      // A ring: 64 TMEM columns per stage
     static constexpr int value = by_smem < by_tmem ? by_smem : by_tmem;
 };
@@ -458,10 +434,10 @@ int launch_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const TcArgs& g, l
     constexpr bool TS = SPLIT3;                // the split A operand lives in tensor memory instead of shared memory
     constexpr int STAGES = TcStages<BN, SPLIT3, TS>::value;
     static_assert(STAGES >= 2, "tile too large for shared memory");
-    const size_t smem = (size_t)STAGES * TcStages<BN, SPLIT3, TS>::per_stage + 1024 /*alignment*/ + 8 * (3 * TC_MAX_STAGES + 4) + 32 + TC_EPI_BYTES(BN);
+    const size_t smem = (size_t)STAGES * TcStages<BN, SPLIT3, TS>::per_stage + 1024 /*alignment*/ + 8 * (3 * TC_MAX_STAGES + 4) + 16;
     if (g_tc_no_ts && TS) {
         constexpr int ST2 = TcStages<BN, SPLIT3, false>::value;
-        const size_t smem2 = (size_t)ST2 * TcStages<BN, SPLIT3, false>::per_stage + 1024 + 8 * (3 * TC_MAX_STAGES + 4) + 32 + TC_EPI_BYTES(BN);
+        const size_t smem2 = (size_t)ST2 * TcStages<BN, SPLIT3, false>::per_stage + 1024 + 8 * (3 * TC_MAX_STAGES + 4) + 16;
         DC_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<BN, A_MN, B_MN, SPLIT3, ST2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
         const long long sms2 = dc_sm_count();
         tc_gemm_kernel<BN, A_MN, B_MN, SPLIT3, ST2, false><<<(unsigned)(num_tiles < sms2 ? num_tiles : sms2), TC_THREADS, smem2, st>>>(tmA, tmB, g);
@@ -531,8 +507,7 @@ int dc_tc_gemm(const float* A, long long lda, int a_mn, const float* B, long lon
     g.kb_per_split = (total_kb + splits - 1) / splits;
     splits = (total_kb + g.kb_per_split - 1) / g.kb_per_split;
     g.partial = splits > 1 ? (float*)ws : nullptr;
-    g.stats = (stats && splits == 1) ? stats : nullptr;          // per-m-tile column sums, only for an unsplit product
-    if (g.stats && stats_chunks) *stats_chunks = (int)((M + TC_BM - 1) / TC_BM);
+    (void)stats;      // column statistics in the epilogue were measured to cost more than the separate pass they save
     const long long num_tiles = tiles * splits;
     const bool split3 = g_tc_mode == 3;
     int rc;

@@ -41,7 +41,7 @@ class _LinBNAct(torch.nn.Sequential):
         inner = bn.bn
         batch_stats = inner.training or not inner.track_running_stats or inner.running_mean is None
         if slope is not None and lin.bias is None and batch_stats and x.dim() == 2:
-            # Linear + BatchNorm statistics + activation as one node (statistics come out of the GEMM epilogue)
+            # Linear + BatchNorm statistics + activation as one autograd node
             return ops.linear_bn_act(x, lin.weight, inner, slope, addend)
         y = lin(x)
         if slope is None:

@@ -559,8 +559,7 @@ def bn_act(y, bn, slope=1.0, addend=None):
 
 class _LinearBNAct(torch.autograd.Function):
     """Linear (no bias) -> BatchNorm1d (batch statistics) -> LeakyReLU(slope) (+ addend) as ONE autograd node
-    (mlp.py:9): the GEMM epilogue already produces the column sums BatchNorm needs, so the pre-activation is
-    written once and read once."""
+    (mlp.py:9) — one node instead of two keeps the pre-activation the only saved intermediate."""
 
     @staticmethod
     def forward(ctx, x, weight, gamma, beta, addend, bn, slope):

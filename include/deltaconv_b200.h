@@ -215,8 +215,7 @@ int dc_linear_bwd_input(const float* dY, int64_t ld_dy, const float* W, int64_t 
                         float* dX, int64_t ld_dx, void* ws, size_t ws_bytes, void* stream);
 int dc_linear_bwd_weight(const float* dY, int64_t ld_dy, const float* X, int64_t ldx, int64_t M, int K, int Nout,
                          float* dW, int64_t ld_dw, void* ws, size_t ws_bytes, void* stream);
-/* Linear (no bias) + the training-mode BatchNorm statistics of its output in one call (mlp.py:9: Lin -> BatchNorm1d):
- * on the tensor-core path the GEMM epilogue produces the column sums, so Y is not re-read. */
+/* Linear (no bias) + the training-mode BatchNorm statistics of its output in one call (mlp.py:9: Lin -> BatchNorm1d). */
 size_t dc_linear_bnstats_ws_bytes(int64_t M, int Nout, int64_t K);
 int dc_linear_fwd_bnstats(const float* X, int64_t ldx, const float* W, int64_t ldw, int64_t M, int K, int Nout,
                           float* Y, int64_t ldy, float eps, float momentum, float* mean, float* invstd,
