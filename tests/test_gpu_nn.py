@@ -448,11 +448,15 @@ def test_full_size_configs_run_and_are_deterministic():
         assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
 
 
-@pytest.mark.parametrize('M,K,C', [(32768, 256, 64), (5000, 64, 128), (4096, 512, 1024), (777, 12, 40), (100, 36, 20)])
-def test_fused_linear_batchnorm_block(M, K, C):
-    """One-node MLP block (Linear -> BN(train) -> LeakyReLU + addend) vs torch fp64."""
+@pytest.mark.parametrize('M,K,C,leaky', [(32768, 256, 64, False), (5000, 64, 128, False), (4096, 512, 1024, False),
+                                         (777, 12, 40, True), (100, 36, 20, True)])
+def test_fused_linear_batchnorm_block(M, K, C, leaky):
+    """One-node MLP block (Linear -> BN(train) -> activation + addend) vs torch fp64.  The large shapes use the
+    identity activation: among millions of pre-activations a few fall within rounding distance of zero, where the
+    LeakyReLU derivative jumps, which makes an fp32-vs-fp64 gradient comparison ill-posed."""
     D = dc()
-    mlp = D.nn.MLP([K, C]).to(DEV).train()
+    act = torch.nn.LeakyReLU(0.2) if leaky else torch.nn.Identity()
+    mlp = D.nn.MLP([K, C], nonlin=act).to(DEV).train()
     with torch.no_grad():
         mlp[0][1].bn.weight.copy_(torch.randn(C) * 0.3 + 1)
         mlp[0][1].bn.bias.copy_(torch.randn(C) * 0.3)
@@ -466,11 +470,10 @@ def test_fused_linear_batchnorm_block(M, K, C):
     out = mlp(x, add)
     (out * g0.to(DEV)).sum().backward()
     xr, addr = x0.double().requires_grad_(True), add0.double().requires_grad_(True)
-    outr = F.leaky_relu(ref_bn(ref_lin(xr)), 0.2) + addr
+    outr = act(ref_bn(ref_lin(xr))) + addr
     (outr * g0.double()).sum().backward()
     assert report(f'fused_lin_bn.{M}x{K}x{C}.out', rel_err(out.detach().cpu(), outr.detach())) < 1e-5
-    # dx goes through the cancellation in the BatchNorm backward and a 3xTF32 product
-    assert report(f'fused_lin_bn.{M}x{K}x{C}.dx', rel_err(x.grad.cpu(), xr.grad)) < 5e-4 and rel_err(add.grad.cpu(), addr.grad) < 1e-6
+    assert report(f'fused_lin_bn.{M}x{K}x{C}.dx', rel_err(x.grad.cpu(), xr.grad)) < 1e-4 and rel_err(add.grad.cpu(), addr.grad) < 1e-6
     assert rel_err(mlp[0][0].weight.grad.cpu(), ref_lin.weight.grad) < 1e-4
     assert rel_err(mlp[0][1].bn.weight.grad.cpu(), ref_bn.weight.grad) < 1e-4
     assert rel_err(mlp[0][1].bn.running_mean.cpu(), ref_bn.running_mean) < 1e-5
