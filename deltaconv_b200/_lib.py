@@ -67,8 +67,6 @@ _SIGNATURES = {
     'dc_gemm_ws_bytes': [_L, _L, _L],
     'dc_gemm_tc_raw': [_P, _L, _I, _P, _L, _I, _P, _L, _I, _L, _P, _L, _P, _Z, _P],
     'dc_linear_fwd': [_P, _L, _P, _L, _P, _L, _I, _I, _P, _L, _P, _Z, _P],
-    'dc_linear_bnstats_ws_bytes': [_L, _I, _L],
-    'dc_linear_fwd_bnstats': [_P, _L, _P, _L, _L, _I, _I, _P, _L, _F, _F, _P, _P, _P, _P, _P, _Z, _P],
     'dc_linear_bwd_input': [_P, _L, _P, _L, _L, _I, _I, _P, _L, _P, _Z, _P],
     'dc_linear_bwd_weight': [_P, _L, _P, _L, _L, _I, _I, _P, _L, _P, _Z, _P],
     'dc_expand_vec_weight': [_P, _I, _I, _P, _P],
@@ -76,7 +74,7 @@ _SIGNATURES = {
 }
 _RESTYPES = {'dc_launch_count': ctypes.c_longlong, 'dc_reset_launch_count': None,
              'dc_ell_transpose_ws_bytes': _Z, 'dc_build_ws_bytes': _Z, 'dc_colreduce_ws_bytes': _Z,
-             'dc_gemm_ws_bytes': _Z, 'dc_central_ws_bytes': _Z, 'dc_linear_bnstats_ws_bytes': _Z}
+             'dc_gemm_ws_bytes': _Z, 'dc_central_ws_bytes': _Z}
 
 _lib = None
 

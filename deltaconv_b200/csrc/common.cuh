@@ -42,12 +42,7 @@ static inline int dc_ceil_div(long long a, long long b) { return (int)((a + b - 
 // back to the fp32 SIMT kernel), <0 on error; *launches = kernels launched
 int dc_tc_gemm(const float* A, long long lda, int a_mn, const float* B, long long ldb, int b_mn, const float* bias,
                long long M, int N, long long K, float* C, long long ldc, void* ws, size_t ws_bytes, cudaStream_t st,
-               int* launches, double* stats, int* stats_chunks);
-// stats / stats_chunks: reserved for column statistics produced by the GEMM epilogue; currently always reports 0 chunks
-// (measured slower than the separate reduction pass), so callers fall back to dc_bn_stats
-// BatchNorm finalize over such partials (nnops.cu)
-int dc_bn_finalize_launch(const double* partial, int chunks, long long M, int C, float eps, float momentum, float* mean,
-                          float* invstd, float* running_mean, float* running_var, cudaStream_t st);
+               int* launches);
 size_t dc_tc_ws_bytes(long long M, long long N, long long K);
 
 // cached SM count of the current device (148 on B200)

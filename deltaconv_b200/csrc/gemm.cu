@@ -171,7 +171,7 @@ extern "C" int dc_linear_fwd(const float* X, int64_t ldx, const float* W, int64_
     DC_REQUIRE(M < 2147483647LL, "dc_linear_fwd: M must fit in int32");
     {
         int n = 0;
-        int rc = dc_tc_gemm(X, ldx, 0, W, ldw, 0, bias_or_null, M, Nout, K, Y, ldy, ws, ws_bytes, (cudaStream_t)stream, &n, nullptr, nullptr);
+        int rc = dc_tc_gemm(X, ldx, 0, W, ldw, 0, bias_or_null, M, Nout, K, Y, ldy, ws, ws_bytes, (cudaStream_t)stream, &n);
         if (rc <= 0) return rc < 0 ? rc : dc_check_launch_n("dc_linear_fwd/tc", n);
     }
     GemmArgs g = {};
@@ -187,7 +187,7 @@ extern "C" int dc_linear_bwd_input(const float* dY, int64_t ld_dy, const float* 
     DC_REQUIRE(M < 2147483647LL, "dc_linear_bwd_input: M must fit in int32");
     {   // A = dY (reduction over Nout, contiguous); B = W stored [Nout, K] i.e. reduction rows, output index contiguous
         int n = 0;
-        int rc = dc_tc_gemm(dY, ld_dy, 0, W, ldw, 1, nullptr, M, K, Nout, dX, ld_dx, ws, ws_bytes, (cudaStream_t)stream, &n, nullptr, nullptr);
+        int rc = dc_tc_gemm(dY, ld_dy, 0, W, ldw, 1, nullptr, M, K, Nout, dX, ld_dx, ws, ws_bytes, (cudaStream_t)stream, &n);
         if (rc <= 0) return rc < 0 ? rc : dc_check_launch_n("dc_linear_bwd_input/tc", n);
     }
     GemmArgs g = {};
@@ -203,7 +203,7 @@ extern "C" int dc_linear_bwd_weight(const float* dY, int64_t ld_dy, const float*
     DC_REQUIRE(M < 2147483647LL, "dc_linear_bwd_weight: M must fit in int32");
     {   // reduction over the M rows: both operands have their output index contiguous (MN-major)
         int n = 0;
-        int rc = dc_tc_gemm(dY, ld_dy, 1, X, ldx, 1, nullptr, Nout, K, M, dW, ld_dw, ws, ws_bytes, (cudaStream_t)stream, &n, nullptr, nullptr);
+        int rc = dc_tc_gemm(dY, ld_dy, 1, X, ldx, 1, nullptr, Nout, K, M, dW, ld_dw, ws, ws_bytes, (cudaStream_t)stream, &n);
         if (rc <= 0) return rc < 0 ? rc : dc_check_launch_n("dc_linear_bwd_weight/tc", n);
     }
     GemmArgs g = {};
@@ -225,41 +225,3 @@ extern "C" int dc_fold_vec_weight_grad(const float* dW_expanded, int Cout, int K
     return dc_check_launch("dc_fold_vec_weight_grad");
 }
 
-// Linear followed by the BatchNorm statistics of its output (training mode), in one entry point:
-// Y = X W^T, then mean / invstd of Y's columns (+ running-stat update) by the deterministic column reduction.
-// (Producing the column sums inside the GEMM epilogue was tried and measured slower)
-extern "C" size_t dc_colreduce_ws_bytes(int C);
-extern "C" int dc_bn_stats(const float* x, int64_t ldx, int64_t M, int C, int mode, float eps, float momentum,
-                           float* mean, float* invstd, float* running_mean_or_null, float* running_var_or_null,
-                           void* ws, size_t ws_bytes, void* stream);
-
-extern "C" size_t dc_linear_bnstats_ws_bytes(int64_t M, int Nout, int64_t K) {
-    size_t a = dc_gemm_ws_bytes(M, Nout, K);
-    size_t b = dc_colreduce_ws_bytes(Nout);
-    size_t c = (size_t)((M + 127) / 128) * 2 * (size_t)Nout * sizeof(double);
-    return a + (b > c ? b : c) + 256;
-}
-
-extern "C" int dc_linear_fwd_bnstats(const float* X, int64_t ldx, const float* W, int64_t ldw, int64_t M, int K, int Nout,
-                                     float* Y, int64_t ldy, float eps, float momentum, float* mean, float* invstd,
-                                     float* running_mean_or_null, float* running_var_or_null,
-                                     void* ws, size_t ws_bytes, void* stream) {
-    DC_REQUIRE(M >= 1 && M < 2147483647LL, "dc_linear_fwd_bnstats: bad M");
-    DC_REQUIRE(ws_bytes >= dc_linear_bnstats_ws_bytes(M, Nout, K), "dc_linear_fwd_bnstats: workspace too small");
-    const size_t gemm_ws = (dc_gemm_ws_bytes(M, Nout, K) + 255) / 256 * 256;
-    double* stats = (double*)((char*)ws + gemm_ws);
-    const size_t stats_bytes = ws_bytes - gemm_ws;
-    int n = 0, chunks = 0;
-    int rc = dc_tc_gemm(X, ldx, 0, W, ldw, 0, nullptr, M, Nout, K, Y, ldy, ws, gemm_ws, (cudaStream_t)stream, &n, stats, &chunks);
-    if (rc < 0) return rc;
-    if (rc == 0 && chunks > 0) {
-        int r2 = dc_check_launch_n("dc_linear_fwd_bnstats/tc", n);
-        if (r2) return r2;
-        r2 = dc_bn_finalize_launch(stats, chunks, M, Nout, eps, momentum, mean, invstd, running_mean_or_null, running_var_or_null,
-                                   (cudaStream_t)stream);
-        return r2 ? r2 : dc_check_launch("dc_linear_fwd_bnstats/finalize");
-    }
-    if (rc == 0) { int r2 = dc_check_launch_n("dc_linear_fwd_bnstats/tc", n); if (r2) return r2; }
-    else { int r2 = dc_linear_fwd(X, ldx, W, ldw, nullptr, M, K, Nout, Y, ldy, ws, gemm_ws, stream); if (r2) return r2; }
-    return dc_bn_stats(Y, ldy, M, Nout, 0, eps, momentum, mean, invstd, running_mean_or_null, running_var_or_null, stats, stats_bytes, stream);
-}

@@ -479,9 +479,8 @@ extern "C" int dc_set_gemm_no_ts(int v) { g_tc_no_ts = v; return DC_OK; }
 // Returns 1 (not an error) when the shape is not eligible, so the caller can use the SIMT kernel.
 int dc_tc_gemm(const float* A, long long lda, int a_mn, const float* B, long long ldb, int b_mn, const float* bias,
                long long M, int N, long long K, float* C, long long ldc, void* ws, size_t ws_bytes, cudaStream_t st,
-               int* launches, double* stats, int* stats_chunks) {
+               int* launches) {
     *launches = 0;
-    if (stats_chunks) *stats_chunks = 0;
     if (g_tc_mode == 0 || M < 64 || N < 16 || K < 8) return 1;
     if (lda % 4 || ldb % 4 || (reinterpret_cast<uintptr_t>(A) & 15u) || (reinterpret_cast<uintptr_t>(B) & 15u)) return 1;
     if (M >= 2147483647LL || K >= 2147483647LL) return 1;
@@ -507,7 +506,6 @@ int dc_tc_gemm(const float* A, long long lda, int a_mn, const float* B, long lon
     g.kb_per_split = (total_kb + splits - 1) / splits;
     splits = (total_kb + g.kb_per_split - 1) / g.kb_per_split;
     g.partial = splits > 1 ? (float*)ws : nullptr;
-    (void)stats;      // column statistics in the epilogue were measured to cost more than the separate pass they save
     const long long num_tiles = tiles * splits;
     const bool split3 = g_tc_mode == 3;
     int rc;
@@ -543,7 +541,7 @@ extern "C" int dc_gemm_tc_raw(const float* A, int64_t lda, int a_mn, const float
                               const float* bias_or_null, int64_t M, int N, int64_t K, float* C, int64_t ldc,
                               void* ws, size_t ws_bytes, void* stream) {
     int n = 0;
-    int rc = dc_tc_gemm(A, lda, a_mn, B, ldb, b_mn, bias_or_null, M, N, K, C, ldc, ws, ws_bytes, (cudaStream_t)stream, &n, nullptr, nullptr);
+    int rc = dc_tc_gemm(A, lda, a_mn, B, ldb, b_mn, bias_or_null, M, N, K, C, ldc, ws, ws_bytes, (cudaStream_t)stream, &n);
     if (rc == 1) { dc_set_error("dc_gemm_tc_raw: shape/layout not eligible for the tensor-core kernel"); return 1; }
     if (rc) return rc;
     return dc_check_launch_n("dc_gemm_tc_raw", n);

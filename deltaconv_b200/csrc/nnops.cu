@@ -590,12 +590,6 @@ int elementwise_grid(long long total) {
 
 }  // namespace
 
-int dc_bn_finalize_launch(const double* partial, int chunks, long long M, int C, float eps, float momentum, float* mean,
-                          float* invstd, float* running_mean, float* running_var, cudaStream_t st) {
-    bn_finalize_kernel<<<dc_ceil_div(C, FIN_COLS), FIN_T, 0, st>>>(partial, chunks, M, C, eps, momentum, mean, invstd, running_mean, running_var);
-    return DC_OK;
-}
-
 // ================================ C ABI ===========================================================
 
 extern "C" size_t dc_colreduce_ws_bytes(int C) { return (size_t)RED_MAX_CHUNKS * 2 * (size_t)C * sizeof(double); }

@@ -579,11 +579,12 @@ class _LinearBNAct(torch.autograd.Function):
         if update:
             bn.num_batches_tracked += 1
             momentum = bn.momentum if bn.momentum is not None else 1.0 / float(bn.num_batches_tracked)
-        nb = query('dc_linear_bnstats_ws_bytes', M, C, K)
+        ws, nb = _gemm_ws(M, C, K, dev)
+        call('dc_linear_fwd', ptr(x), ldx, ptr(weight), ldw, None, M, K, C, ptr(y), C, ptr(ws), nb)
+        nb = query('dc_colreduce_ws_bytes', C)
         ws = workspace(nb, dev)
-        call('dc_linear_fwd_bnstats', ptr(x), ldx, ptr(weight), ldw, M, K, C, ptr(y), C, float(bn.eps), float(momentum),
-             ptr(mean), ptr(invstd), ptr(bn.running_mean) if update else None, ptr(bn.running_var) if update else None,
-             ptr(ws), nb)
+        call('dc_bn_stats', ptr(y), C, M, C, 0, float(bn.eps), float(momentum), ptr(mean), ptr(invstd),
+             ptr(bn.running_mean) if update else None, ptr(bn.running_var) if update else None, ptr(ws), nb)
         out = torch.empty(M, C, dtype=_F32, device=dev)
         add_p, ld_add = None, 0
         if addend is not None:

@@ -215,11 +215,6 @@ int dc_linear_bwd_input(const float* dY, int64_t ld_dy, const float* W, int64_t 
                         float* dX, int64_t ld_dx, void* ws, size_t ws_bytes, void* stream);
 int dc_linear_bwd_weight(const float* dY, int64_t ld_dy, const float* X, int64_t ldx, int64_t M, int K, int Nout,
                          float* dW, int64_t ld_dw, void* ws, size_t ws_bytes, void* stream);
-/* Linear (no bias) + the training-mode BatchNorm statistics of its output in one call (mlp.py:9: Lin -> BatchNorm1d). */
-size_t dc_linear_bnstats_ws_bytes(int64_t M, int Nout, int64_t K);
-int dc_linear_fwd_bnstats(const float* X, int64_t ldx, const float* W, int64_t ldw, int64_t M, int K, int Nout,
-                          float* Y, int64_t ldy, float eps, float momentum, float* mean, float* invstd,
-                          float* running_mean_or_null, float* running_var_or_null, void* ws, size_t ws_bytes, void* stream);
 /* I_J folded into the weights (operators.py:19-21, deltaconv.py:68): W [Cout,2K] -> [[W1,-W2],[W2,W1]] */
 int dc_expand_vec_weight(const float* W, int Cout, int K, float* W_expanded, void* stream);
 int dc_fold_vec_weight_grad(const float* dW_expanded, int Cout, int K, float* dW, void* stream);
