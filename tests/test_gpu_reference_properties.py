@@ -1,0 +1,126 @@
+"""The reference's own property tests (test/geometry/test_grad_div_mls.py, test/nn/test_nonlin.py,
+test/geometry/test_operators.py), re-run against the CUDA path.  Same constructions and thresholds as the
+reference unless a comment says otherwise.  Run with `-m gpu`."""
+import pytest
+import torch
+import torch.linalg as LA
+
+pytestmark = pytest.mark.gpu
+DEV = 'cuda'
+
+
+def dc():
+    import deltaconv_b200
+    return deltaconv_b200
+
+
+def quadric_surface(N, seed):
+    """f(x,y) = sum c_i * [1, x, y, x^2, xy, y^2] over [-1,1]^2 with analytic frames (test_grad_div_mls.py:289-327)."""
+    torch.manual_seed(seed)
+    coords = torch.rand(N, 2) * 2 - 1
+    x, y = coords.T
+    B = torch.stack([torch.ones_like(x), x, y, x * x, x * y, y * y], 1)
+    c = torch.rand(6)
+    f = (B * c).sum(1, keepdim=True)
+    pos = torch.cat([coords, f], 1)
+    dfdx = torch.stack([torch.ones_like(x), torch.zeros_like(x), c[1] + 2 * c[3] * x + c[4] * y], 1)
+    dfdy = torch.stack([torch.zeros_like(x), torch.ones_like(x), c[2] + c[4] * x + 2 * c[5] * y], 1)
+    normal = torch.linalg.cross(dfdx, dfdy, dim=1)
+    normal = normal / LA.norm(normal, dim=1, keepdim=True).clamp(1e-8)
+    xb = dfdx / LA.norm(dfdx, dim=1, keepdim=True).clamp(1e-8)
+    yb = torch.linalg.cross(normal, xb, dim=1)
+    return pos, f, normal, xb, yb
+
+
+def test_build_grad_div_properties():
+    """test_build_grad_div (test_grad_div_mls.py:278-401).  regularizer 1e-5 instead of 1e-8: the fit runs in fp32
+    on the GPU exactly as the reference's does, and at 1e-8 both are dominated by round-off."""
+    geo = dc().geometry
+    N, k = 1000, 20
+    pos, f, normal, xb, yb = (a.to(DEV) for a in quadric_surface(N, 42))
+    ei = geo.knn_graph(pos, k, loop=True, flow='target_to_source')
+    grad, div = geo.build_grad_div(pos, normal, xb, yb, ei, regularizer=1e-5, normalized=False)
+    assert grad.size(0) == 2 * N and grad.size(1) == N and div.size(0) == N and div.size(1) == 2 * N
+    assert (grad @ torch.rand(N, 1, device=DEV)).isnan().sum() == 0
+    assert (div @ torch.rand(2 * N, 1, device=DEV)).isnan().sum() == 0
+    ones = pos.new_ones(N, 1)
+    assert torch.allclose(grad @ ones, pos.new_zeros(2 * N, 1), atol=1e-2)                    # 3a
+    assert geo.laplacian(ones, grad, div).abs().mean() < 1e-2                                   # 3b
+    assert LA.norm(geo.laplacian(torch.rand(N, 1, device=DEV), grad, div), ord=1) > 0           # 3c
+    assert geo.curl(grad @ pos[:, 0:1], div).pow(2).mean() < 1e-2                               # 3d
+    assert geo.curl(grad @ pos[:, 0:1], div).pow(2).median() < 1e-2
+    assert (div @ geo.J(grad @ pos[:, 0:1])).pow(2).mean() < 1e-2                               # 3e
+    gx, gy = (grad @ f).view(N, 2).T                                                            # 4
+    assert torch.allclose(gx, xb[:, 2], atol=1e-2) and torch.allclose(gy, yb[:, 2], atol=1e-2)
+    mc = geo.laplacian(pos, grad, div)
+    assert torch.allclose(-geo.batch_dot(mc, normal), LA.norm(mc, dim=1, keepdims=True), atol=1e-2)
+    # 5. gauge equivariance under a random in-plane rotation of the frames
+    xb_r = geo.rotate_around(xb, normal, torch.rand(N, device=DEV) * 2 * torch.pi)
+    yb_r = torch.linalg.cross(normal, xb_r, dim=1)
+    G, Dv = geo.build_grad_div(pos, normal, xb, yb, ei, regularizer=1e-5)
+    G_r, D_r = geo.build_grad_div(pos, normal, xb_r, yb_r, ei, regularizer=1e-5)
+    x = torch.rand(N, 1, device=DEV)
+    a, b = (G @ x).view(-1, 2).T
+    ar, br = (G_r @ x).view(-1, 2).T
+    assert torch.allclose(a[:, None] * xb + b[:, None] * yb, ar[:, None] * xb_r + br[:, None] * yb_r, atol=1e-3)
+    assert torch.allclose(Dv @ (G @ x), D_r @ (G_r @ x), atol=1e-3)
+
+
+def test_coords_weights_and_mapping():
+    """coords_projected recovers (x, y) on a paraboloid patch (test_grad_div_mls.py:58-84), gaussian weights are
+    normalised and decrease with distance (:87-104), and the vector mapping carries neighbour frames into the
+    centre frame (:158-275) — read out of the fused build kernel through `operator_parts`."""
+    geo = dc().geometry
+    N, k = 600, 16
+    pos, f, normal, xb, yb = (a.to(DEV) for a in quadric_surface(N, 7))
+    ei = geo.knn_graph(pos, k, loop=True, flow='target_to_source')
+    parts = geo.operator_parts(pos, normal, xb, yb, ei, regularizer=1e-5)
+    row, col = ei
+    d = pos[col] - pos[row]
+    dt = d - normal[row] * (d * normal[row]).sum(1, keepdim=True)
+    want = torch.stack([(dt * xb[row]).sum(1), (dt * yb[row]).sum(1)], 1)
+    assert torch.allclose(parts['coords'], want, atol=1e-6)
+    w = parts['weights'].view(N, k)
+    assert torch.allclose(w.sum(1), torch.ones(N, device=DEV), atol=1e-5)
+    dist = d.norm(dim=1).view(N, k)
+    order = dist.argsort(dim=1)
+    assert (w.gather(1, order).diff(dim=1) <= 1e-7).all()                                      # monotone in distance
+    assert (w[:, 0] >= w.max(1).values - 1e-7).all()                                            # self (distance 0) heaviest
+    # mapping: identity on the centre slot, and close to a rotation for near neighbours on a smooth patch
+    M = parts['mapping'].view(N, k, 2, 2)
+    eye = torch.eye(2, device=DEV).expand(N, 2, 2)
+    assert torch.allclose(M[:, 0], eye, atol=1e-4)
+    assert (torch.linalg.det(M[:, 1]) - 1).abs().median() < 5e-2
+
+
+def test_vector_nonlin_behaviour():
+    """test_vectornonlin (test/nn/test_nonlin.py:40-88): identity at zero bias; norms thresholded; directions kept."""
+    nn = dc().nn
+    N, C = 1024, 16
+    ang = torch.rand(N, C, device=DEV) * 2 * torch.pi
+    nrm = torch.rand(N, C, device=DEV) * 5
+    v = torch.stack([nrm * torch.cos(ang), nrm * torch.sin(ang)], 1).view(-1, C)
+    m = nn.VectorNonLin(C).to(DEV)
+    assert torch.allclose(m(v), v, atol=1e-6)                                                   # zero bias => identity
+    with torch.no_grad():
+        m.bias.fill_(-2.5)
+    out = m(v).view(N, 2, C)
+    out_n = out.norm(dim=1)
+    assert torch.allclose(out_n, (nrm - 2.5).clamp(min=0), atol=1e-5)
+    keep = out_n > 1e-3
+    cosang = (out * v.view(N, 2, C)).sum(1) / (out_n * nrm).clamp(1e-12)
+    assert torch.allclose(cosang[keep], torch.ones_like(cosang[keep]), atol=1e-5)               # direction preserved
+    bn = nn.VectorNonLin(C, batchnorm=nn.BatchNorm1d(C)).to(DEV).train()
+    out = bn(v).view(N, 2, C).norm(dim=1)
+    assert (out >= 0).all() and (out == 0).float().mean() > 0.2                                 # BN centres the norms, ReLU zeroes ~half
+
+
+def test_batchnorm_wrapper_behaviour():
+    """test_batchnorm (test/nn/test_nonlin.py:7-37): constant input -> 0, affine-invariance of the normalised output."""
+    nn = dc().nn
+    bn = nn.BatchNorm1d(8).to(DEV).train()
+    assert repr(bn) == 'BatchNorm1d(8)'
+    x = torch.full((100, 8), 3.0, device=DEV)
+    assert torch.allclose(bn(x), torch.zeros_like(x), atol=1e-3)
+    y = torch.randn(500, 8, device=DEV)
+    assert torch.allclose(bn(y), bn(2.5 * y + 1.0), atol=1e-4)
