@@ -62,7 +62,20 @@ def test_build_grad_div_properties():
     a, b = (G @ x).view(-1, 2).T
     ar, br = (G_r @ x).view(-1, 2).T
     assert torch.allclose(a[:, None] * xb + b[:, None] * yb, ar[:, None] * xb_r + br[:, None] * yb_r, atol=1e-3)
-    assert torch.allclose(Dv @ (G @ x), D_r @ (G_r @ x), atol=1e-3)
+    # 5b. div grad x in both gauges.  The regulariser is not rotation invariant, so even the fp64 reference arithmetic
+    # shows a small, sample-dependent gauge difference (the reference asserts 1e-3 for its own seed); require that the
+    # CUDA path adds nothing to it.
+    from oracle import geometry as og
+    idx = ei._dc_graph.idx.cpu().long()
+    p64, n64, x64 = pos.cpu().double(), normal.cpu().double(), x.cpu().double()
+    lap = []
+    for fx, fy in ((xb, yb), (xb_r, yb_r)):
+        Go, Do = og.fit_operators(p64, n64, fx.cpu().double(), fy.cpu().double(), idx, None, 1.0, 1e-8)
+        lap.append(og.apply_div(idx, Do, og.apply_grad(idx, Go, x64)))
+    inherent = (lap[0] - lap[1]).abs().max().item()
+    ours = (Dv @ (G @ x) - D_r @ (G_r @ x)).abs().max().item()
+    assert ours <= inherent + 1e-4 and ours < 5e-3, (ours, inherent)
+    assert ((Dv @ (G @ x)).cpu().double() - lap[0]).abs().max() < 1e-5
 
 
 def test_coords_weights_and_mapping():
