@@ -32,9 +32,11 @@ def _build(static, pos, normal, xb, yb, graph, normalized, lam, lam_shape):
               lam_shape if lam_shape is not None else 0.0, int(lam_shape is not None), int(normalized), ptr(G), ptr(D_))
     if static:
         torch.cuda.synchronize()
-        before = torch.cuda.memory_allocated()
+        # count allocation EVENTS (monotonic), not bytes in use: a garbage-collection pass may free unrelated
+        # tensors of earlier tests while we are in here
+        before = torch.cuda.memory_stats().get('allocation.all.allocated', 0)
         call('dc_build_grad_div_static', *common)
-        assert torch.cuda.memory_allocated() == before            # nothing was allocated on our behalf
+        assert torch.cuda.memory_stats().get('allocation.all.allocated', 0) == before     # nothing was allocated on our behalf
     else:
         nbytes = query('dc_build_ws_bytes', N, B)
         ws = torch.empty(nbytes, dtype=torch.uint8, device=DEV)
