@@ -59,19 +59,27 @@ def test_build_grad_div_properties():
     G, Dv = geo.build_grad_div(pos, normal, xb, yb, ei, regularizer=1e-8)
     G_r, D_r = geo.build_grad_div(pos, normal, xb_r, yb_r, ei, regularizer=1e-8)
     x = torch.rand(N, 1, device=DEV)
-    a, b = (G @ x).view(-1, 2).T
-    ar, br = (G_r @ x).view(-1, 2).T
-    assert torch.allclose(a[:, None] * xb + b[:, None] * yb, ar[:, None] * xb_r + br[:, None] * yb_r, atol=1e-3)
-    # 5b. div grad x in both gauges.  The regulariser is not rotation invariant, so even the fp64 reference arithmetic
-    # shows a small, sample-dependent gauge difference (the reference asserts 1e-3 for its own seed); require that the
-    # CUDA path adds nothing to it.
+
+    def ambient(op, field, fx, fy):
+        gx, gy = (op @ field).view(-1, 2).T
+        return gx[:, None] * fx + gy[:, None] * fy
+    # 5a/5b: grad x as an ambient vector, and div grad x, in both gauges.  The regulariser is not rotation invariant,
+    # so even the fp64 reference arithmetic shows a small, sample-dependent gauge difference (the reference asserts
+    # 1e-3 for its own seed); require that the CUDA path adds nothing to it.
     from oracle import geometry as og
     idx = ei._dc_graph.idx.cpu().long()
     p64, n64, x64 = pos.cpu().double(), normal.cpu().double(), x.cpu().double()
-    lap = []
+    lap, amb = [], []
     for fx, fy in ((xb, yb), (xb_r, yb_r)):
-        Go, Do = og.fit_operators(p64, n64, fx.cpu().double(), fy.cpu().double(), idx, None, 1.0, 1e-8)
-        lap.append(og.apply_div(idx, Do, og.apply_grad(idx, Go, x64)))
+        fx64, fy64 = fx.cpu().double(), fy.cpu().double()
+        Go, Do = og.fit_operators(p64, n64, fx64, fy64, idx, None, 1.0, 1e-8)
+        gv = og.apply_grad(idx, Go, x64)
+        lap.append(og.apply_div(idx, Do, gv))
+        g2 = gv.view(-1, 2)
+        amb.append(g2[:, :1] * fx64 + g2[:, 1:] * fy64)
+    inherent_a = (amb[0] - amb[1]).abs().max().item()
+    ours_a = (ambient(G, x, xb, yb) - ambient(G_r, x, xb_r, yb_r)).abs().max().item()
+    assert ours_a <= inherent_a + 1e-4 and ours_a < 2e-2, (ours_a, inherent_a)
     inherent = (lap[0] - lap[1]).abs().max().item()
     ours = (Dv @ (G @ x) - D_r @ (G_r @ x)).abs().max().item()
     assert ours <= inherent + 1e-4 and ours < 5e-3, (ours, inherent)
