@@ -34,6 +34,7 @@ struct TcArgs {
     int M, N, K;
     int kb_per_split;       // k-blocks per grid.z slice
     float* partial;         // [splits][M][N] when split-K
+    int keep_raw_hi;        // 1: leave the raw fp32 tile as the 'hi' B operand (valid iff the MMA truncates fp32 -> tf32)
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -264,13 +265,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
                     float4* a_lo = reinterpret_cast<float4*>(base_ptr + (stage_a_lo(s) - base));
                     float4* b_hi = reinterpret_cast<float4*>(base_ptr + (stage_b(s) - base));
                     float4* b_lo = reinterpret_cast<float4*>(base_ptr + (stage_b_lo(s) - base));
-                    auto split = [](float4* hi, float4* lo, int i) {
+                    const bool keep_raw = g.keep_raw_hi != 0;
+                    auto split = [keep_raw](float4* hi, float4* lo, int i) {
                         float4 x = hi[i], h, l;
                         h.x = __uint_as_float(__float_as_uint(x.x) & 0xffffe000u); l.x = x.x - h.x;
                         h.y = __uint_as_float(__float_as_uint(x.y) & 0xffffe000u); l.y = x.y - h.y;
                         h.z = __uint_as_float(__float_as_uint(x.z) & 0xffffe000u); l.z = x.z - h.z;
                         h.w = __uint_as_float(__float_as_uint(x.w) & 0xffffe000u); l.w = x.w - h.w;
-                        hi[i] = h; lo[i] = l;
+                        if (!keep_raw) hi[i] = h;
+                        lo[i] = l;
                     };
                     if (TS) {
                         // this thread owns one row of the A tile: read it through the 128-byte swizzle, split it, and
@@ -420,6 +423,8 @@ bool make_map(CUtensorMap* map, const float* ptr, long long inner, long long out
               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+int g_tc_keep_raw_hi = 1;   // B_hi is the raw fp32 tile: the MMA truncates fp32 -> tf32 on read (measured bit-identical to an explicit
+                            // hi = x & 0xffffe000 rewrite, dc_set_gemm_keep_raw_hi(0) restores the rewrite)
 int g_tc_no_ts = 0;      // experiment switch: 1 = keep the split A operand in shared memory (SS MMAs)
 
 template <int BN, bool SPLIT3, bool TS> struct TcStages {
@@ -472,6 +477,8 @@ extern "C" int dc_set_gemm_mode(int mode) {
 extern "C" int dc_get_gemm_mode(void) { return g_tc_mode; }
 // experiment switch: A operand of the 3xTF32 split in shared memory (1) instead of tensor memory (0, default)
 extern "C" int dc_set_gemm_no_ts(int v) { g_tc_no_ts = v; return DC_OK; }
+// tuning switch: 1 (default) = do not rewrite the hi part of B in shared memory (the MMA truncates fp32 operands to tf32), 0 = rewrite
+extern "C" int dc_set_gemm_keep_raw_hi(int v) { g_tc_keep_raw_hi = v; return DC_OK; }
 
 // Generic tensor-core product  C[M,N] = op(A) op(B)^T (+bias).  a_mn / b_mn select the operand layout:
 //   a_mn = 0: A is [M, K] with K contiguous (lda = row pitch);  a_mn = 1: A is stored [K, M] with M contiguous.
@@ -506,6 +513,7 @@ int dc_tc_gemm(const float* A, long long lda, int a_mn, const float* B, long lon
     g.kb_per_split = (total_kb + splits - 1) / splits;
     splits = (total_kb + g.kb_per_split - 1) / g.kb_per_split;
     g.partial = splits > 1 ? (float*)ws : nullptr;
+    g.keep_raw_hi = g_tc_keep_raw_hi;
     const long long num_tiles = tiles * splits;
     const bool split3 = g_tc_mode == 3;
     int rc;

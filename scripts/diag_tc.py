@@ -43,11 +43,12 @@ for (M, N, K) in [(32768, 1024, 512), (32768, 256, 512), (32768, 64, 256), (3276
     a = torch.randn(M, K, device=dev); b = torch.randn(N, K, device=dev); C = torch.empty(M, N, device=dev)
     ref = a.double() @ b.double().t()
     out = []
-    for no_ts in (0, 1):
-        lib.dc_set_gemm_no_ts(no_ts)
+    for no_ts in (0, 2):
+        lib.dc_set_gemm_no_ts(0)
+        lib.dc_set_gemm_keep_raw_hi(1 if no_ts == 2 else 0)
         f = lambda: _lib.call('dc_gemm_tc_raw', a.data_ptr(), K, 0, b.data_ptr(), K, 0, None, M, N, K, C.data_ptr(), N, ws.data_ptr(), ws.numel())
         t = timeit(f)
         err = ((C.double() - ref).abs().max() / ref.abs().max()).item()
-        out.append(f'{"SS" if no_ts else "TS"} {t:.4f} ms {2*M*N*K/t/1e9:.0f} TF/s err {err:.1e}')
-    lib.dc_set_gemm_no_ts(0)
+        out.append(f'{"TS+rawhi" if no_ts else "TS"} {t:.4f} ms {2*M*N*K/t/1e9:.0f} TF/s err {err:.1e}')
+    lib.dc_set_gemm_no_ts(0); lib.dc_set_gemm_keep_raw_hi(0)
     print(f'M{M} N{N} K{K}:', ' | '.join(out), flush=True)
