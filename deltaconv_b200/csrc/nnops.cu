@@ -438,13 +438,11 @@ __global__ void __launch_bounds__(256) gathermax_bwd_vec4_kernel(const int* __re
             const int i = edge / k;
             const unsigned char e = (unsigned char)(edge - i * k);
             const uchar4 a = *reinterpret_cast<const uchar4*>(arg + (size_t)i * C + ch);
-            if (a.x == e || a.y == e || a.z == e || a.w == e) {       // ~1/k of the (edge, channel) pairs won the max
-                const float4 d = __ldg(reinterpret_cast<const float4*>(dout + (size_t)i * ldd + ch));
-                if (a.x == e) acc.x += d.x;
-                if (a.y == e) acc.y += d.y;
-                if (a.z == e) acc.z += d.z;
-                if (a.w == e) acc.w += d.w;
-            }
+            const float4 d = __ldg(reinterpret_cast<const float4*>(dout + (size_t)i * ldd + ch));
+            if (a.x == e) acc.x += d.x;
+            if (a.y == e) acc.y += d.y;
+            if (a.z == e) acc.z += d.z;
+            if (a.w == e) acc.w += d.w;
         }
     }
     if (row_ok && ch_ok) *reinterpret_cast<float4*>(dy + (size_t)j * ld_dy + ch) = acc;
