@@ -77,8 +77,8 @@ def main():
                 t_gt = time_ms(lambda: torch.autograd.grad(yv, xr, gy, retain_graph=True), flush)
                 rec[f'grad_C{C}_gbps'] = round(N * (12 * k + 12 * C) / t_g / 1e6, 1)
                 rec[f'gradT_C{C}_gbps'] = round(N * (12 * k + 12 * C) / t_gt / 1e6, 1)
-                # scalar_cat = x copy (8C) + fused div/curl/norm (12k + 20C) + compact [div|curl] copy (16C)
-                rec[f'divcurlnorm_C{C}_gbps'] = round(N * (12 * k + 20 * C + 24 * C) / t_d / 1e6, 1)
+                # scalar_cat = fused div/curl/norm (12k + 20C) with x copied through into the concatenation (8C)
+                rec[f'divcurlnorm_C{C}_gbps'] = round(N * (12 * k + 28 * C) / t_d / 1e6, 1)
                 del x, v, xr, yv, gy
             rows.append(rec)
             print(json.dumps(rec), flush=True)

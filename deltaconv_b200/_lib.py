@@ -36,9 +36,9 @@ _SIGNATURES = {
     'dc_set_spmm_staged': [_I],
     'dc_grad_fwd': [_P, _P, _I, _I, _I, _P, _L, _P, _L, _P, _I, _I, _P],
     'dc_grad_bwd': [_P, _P, _P, _I, _I, _I, _P, _L, _P, _L, _P, _I, _I, _P],
-    'dc_divcurlnorm_fwd': [_P, _P, _I, _I, _I, _P, _L, _P, _L, _P, _L, _P, _L, _P, _I, _I, _P],
+    'dc_divcurlnorm_fwd': [_P, _P, _I, _I, _I, _P, _L, _P, _L, _P, _L, _P, _L, _P, _L, _P, _L, _P, _I, _I, _P],
     'dc_divcurlnorm_bwd': [_P, _P, _P, _I, _I, _I, _P, _L, _P, _L, _P, _L, _P, _L, _P, _L, _P, _I, _I, _P],
-    'dc_hodge_fwd': [_P, _P, _I, _I, _I, _P, _L, _P, _L, _P, _L, _P, _I, _I, _P],
+    'dc_hodge_fwd': [_P, _P, _I, _I, _I, _P, _L, _P, _L, _P, _L, _P, _L, _P, _L, _P, _I, _I, _P],
     'dc_hodge_bwd': [_P, _P, _P, _I, _I, _I, _P, _L, _P, _L, _P, _L, _P, _I, _I, _P],
     'dc_gathermax_fwd': [_P, _I, _I, _I, _P, _L, _P, _L, _P, _P],
     'dc_gathermax_bwd': [_P, _P, _I, _I, _I, _P, _P, _L, _P, _L, _P],
@@ -48,11 +48,11 @@ _SIGNATURES = {
     'dc_segmax_bwd': [_P, _L, _I, _I, _I, _P, _P, _P],
     'dc_central_max_cin': [],
     'dc_central_ws_bytes': [_I, _I, _I, _I],
-    'dc_central_stats': [_P, _I, _I, _I, _I, _P, _L, _P, _F, _F, _P, _P, _P, _P, _P, _P, _Z, _P],
+    'dc_central_stats': [_P, _I, _I, _I, _I, _P, _L, _P, _F, _F, _P, _P, _P, _P, _P, _P, _P, _Z, _P],
     'dc_central_fwd': [_P, _I, _I, _I, _I, _P, _L, _P, _P, _P, _P, _P, _F, _P, _L, _P, _P],
     'dc_central_bwd': [_P, _P, _P, _I, _I, _I, _I, _P, _L, _P, _P, _P, _P, _P, _P, _F, _I, _P, _P, _L, _P, _P, _P, _P, _L, _P, _Z, _P],
     'dc_colreduce_ws_bytes': [_I],
-    'dc_bn_stats': [_P, _L, _L, _I, _I, _F, _F, _P, _P, _P, _P, _P, _Z, _P],
+    'dc_bn_stats': [_P, _L, _L, _I, _I, _F, _F, _P, _P, _P, _P, _P, _P, _Z, _P],
     'dc_bn_act_fwd': [_P, _L, _L, _I, _P, _P, _P, _P, _F, _P, _L, _P, _L, _P],
     'dc_bn_act_bwd': [_P, _L, _P, _L, _L, _I, _P, _P, _P, _P, _F, _I, _P, _P, _P, _L, _P, _Z, _P],
     'dc_col_sum': [_P, _L, _L, _I, _P, _P, _Z, _P],
@@ -60,6 +60,8 @@ _SIGNATURES = {
     'dc_vecnonlin_bwd': [_P, _L, _P, _L, _L, _I, _P, _P, _P, _P, _P, _I, _P, _P, _P, _P, _L, _P, _Z, _P],
     'dc_pool_fwd': [_P, _L, _P, _I, _I, _P, _L, _P, _L, _P, _P],
     'dc_pool_bwd': [_P, _I, _I, _I, _P, _P, _L, _P, _L, _P, _L, _P],
+    'dc_bn_act_pool_fwd': [_P, _L, _P, _I, _I, _P, _P, _P, _P, _F, _P, _L, _P, _L, _P, _P],
+    'dc_bn_act_pool_bwd': [_P, _L, _L, _I, _P, _P, _I, _P, _P, _L, _P, _L, _P, _P, _P, _P, _F, _P, _P, _P, _L, _P, _Z, _P],
     'dc_bcast_rows': [_P, _L, _P, _I, _I, _I, _P, _L, _P],
     'dc_set_gemm_mode': [_I],
     'dc_get_gemm_mode': [],

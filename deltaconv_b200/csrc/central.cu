@@ -68,8 +68,10 @@ __global__ void __launch_bounds__(256) edge_moments_kernel(const int* __restrict
 __global__ void central_stats_finalize_kernel(const double* __restrict__ partial, int chunks, long long E, int Cin, int Cout,
                                               const float* __restrict__ W, float eps, float momentum,
                                               double* __restrict__ moments, float* __restrict__ mean, float* __restrict__ invstd,
-                                              float* __restrict__ running_mean, float* __restrict__ running_var) {
+                                              float* __restrict__ running_mean, float* __restrict__ running_var,
+                                              long long* __restrict__ num_batches_tracked) {
     __shared__ double mom[NMOM];
+    if (num_batches_tracked && threadIdx.x == 0) *num_batches_tracked += 1;
     {   // one warp per moment (blockDim.x = 32 * NMOM), lanes stride over the per-CTA partials, fixed-order shuffle tree
         const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
         double s = 0.0;
@@ -278,7 +280,8 @@ extern "C" size_t dc_central_ws_bytes(int N, int k, int Cin, int Cout) {
 // for the backward pass; mean/invstd [Cout]; running stats updated like torch.nn.BatchNorm1d.
 extern "C" int dc_central_stats(const int32_t* idx, int N, int k, int Cin, int Cout, const float* x, int64_t ldx, const float* W,
                                 float eps, float momentum, double* moments, float* mean, float* invstd,
-                                float* running_mean_or_null, float* running_var_or_null, void* ws, size_t ws_bytes, void* stream) {
+                                float* running_mean_or_null, float* running_var_or_null, int64_t* num_batches_tracked_or_null,
+                                void* ws, size_t ws_bytes, void* stream) {
     DC_REQUIRE(Cin >= 1 && Cin <= CIN_MAX, "dc_central_stats: Cin must be in [1,%d]", CIN_MAX);
     DC_REQUIRE(N >= 1 && k >= 1 && Cout >= 1, "dc_central_stats: empty input");
     DC_REQUIRE(ws_bytes >= dc_central_ws_bytes(N, k, Cin, Cout), "dc_central_stats: workspace too small");
@@ -287,7 +290,7 @@ extern "C" int dc_central_stats(const int32_t* idx, int N, int k, int Cin, int C
     const int chunks = moments_chunks(E);
     edge_moments_kernel<<<chunks, 256, 0, st>>>(idx, N, k, Cin, x, ldx, (double*)ws);
     central_stats_finalize_kernel<<<1, 32 * NMOM, 0, st>>>((const double*)ws, chunks, E, Cin, Cout, W, eps, momentum, moments, mean, invstd,
-                                                     running_mean_or_null, running_var_or_null);
+                                                     running_mean_or_null, running_var_or_null, (long long*)num_batches_tracked_or_null);
     return dc_check_launch_n("dc_central_stats", 2);
 }
 

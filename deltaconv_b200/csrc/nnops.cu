@@ -41,7 +41,9 @@ struct NormVal {       // |v| and |v|^2 of a [2M,C] vector field (nonlin.py:68)
 // (momentum, unbiased variance).  One thread per column, partials added in chunk order.
 __global__ void bn_finalize_kernel(const double* __restrict__ partial, int chunks, long long M, int C, float eps,
                                    float momentum, float* __restrict__ mean, float* __restrict__ invstd,
-                                   float* __restrict__ running_mean, float* __restrict__ running_var) {
+                                   float* __restrict__ running_mean, float* __restrict__ running_var,
+                                   long long* __restrict__ num_batches_tracked) {
+    if (num_batches_tracked && blockIdx.x == 0 && threadIdx.x == 0) *num_batches_tracked += 1;
     double r[2];
     if (!finalize_sums<2>(partial, chunks, C, r)) return;
     const int c = blockIdx.x * FIN_COLS + (threadIdx.x >> 5);
@@ -168,6 +170,74 @@ __global__ void bn_act_bwd_vec4_kernel(const float* __restrict__ y, long long ld
         float4 o;
         o.x = one(yv.x, dv.x, mu.x, is.x, g.x, b.x, s1.x, s2.x); o.y = one(yv.y, dv.y, mu.y, is.y, g.y, b.y, s1.y, s2.y);
         o.z = one(yv.z, dv.z, mu.z, is.z, g.z, b.z, s1.z, s2.z); o.w = one(yv.w, dv.w, mu.w, is.w, g.w, b.w, s1.w, s2.w);
+        *reinterpret_cast<float4*>(dy + r * ld_dy + c) = o;
+    }
+}
+
+// ---- BatchNorm + activation fused with the global pools, backward -------------------------------
+// gradient of [max | mean] pooling w.r.t. the pooled activation at (r, c), rebuilt on the fly (same expression as pool_bwd)
+struct PoolGrad {
+    const long long* batch; const int* cloud_ptr; const int* arg;
+    const float* d_max; long long ld_dmax; const float* d_mean; long long ld_dmean; int C;
+    __device__ __forceinline__ int cloud(long long r) const { return batch ? (int)__ldg(batch + r) : 0; }
+    __device__ __forceinline__ float inv_count(int b) const { return 1.f / (float)max(__ldg(cloud_ptr + b + 1) - __ldg(cloud_ptr + b), 1); }
+    __device__ __forceinline__ float operator()(long long r, int b, float inv, int c) const {
+        const float gm = (d_max && __ldg(arg + (size_t)b * C + c) == (int)r) ? __ldg(d_max + (size_t)b * ld_dmax + c) : 0.f;
+        const float ga = d_mean ? __ldg(d_mean + (size_t)b * ld_dmean + c) * inv : 0.f;
+        return gm + ga;
+    }
+};
+
+struct PoolBnBwdVal {
+    const float* y; long long ldy; PoolGrad pg;
+    const float* mean; const float* invstd; const float* gamma; const float* beta; float slope;
+    __device__ void operator()(long long r, int c, float (&o)[2]) const {
+        const int b = pg.cloud(r);
+        float xh = (__ldg(y + r * ldy + c) - __ldg(mean + c)) * __ldg(invstd + c);
+        float g = gamma ? __ldg(gamma + c) : 1.f, bt = beta ? __ldg(beta + c) : 0.f;
+        float z = g * xh + bt;
+        float dz = pg(r, b, pg.inv_count(b), c) * (z > 0.f ? 1.f : slope);
+        o[0] = dz; o[1] = dz * xh;
+    }
+};
+
+__global__ void bn_act_pool_bwd_vec4_kernel(const float* __restrict__ y, long long ldy, PoolGrad pg, long long M, int C4,
+                                            const float* __restrict__ mean, const float* __restrict__ invstd,
+                                            const float* __restrict__ gamma, const float* __restrict__ beta, float slope,
+                                            const float* __restrict__ sum_dz, const float* __restrict__ sum_dz_xh,
+                                            float* __restrict__ dy, long long ld_dy) {
+    const long long total = M * (long long)C4;
+    const float invM = 1.f / (float)M;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+        const long long r = t / C4;
+        const int c = (int)(t - r * C4) * 4;
+        const int b = pg.cloud(r);
+        const float inv = pg.inv_count(b);
+        const float4 yv = ld_stream4(reinterpret_cast<const float4*>(y + r * ldy + c));
+        float4 dv = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (pg.d_max) {
+            const int4 am = __ldg(reinterpret_cast<const int4*>(pg.arg + (size_t)b * pg.C + c));
+            const float4 gm = __ldg(reinterpret_cast<const float4*>(pg.d_max + (size_t)b * pg.ld_dmax + c));
+            dv.x = am.x == (int)r ? gm.x : 0.f; dv.y = am.y == (int)r ? gm.y : 0.f;
+            dv.z = am.z == (int)r ? gm.z : 0.f; dv.w = am.w == (int)r ? gm.w : 0.f;
+        }
+        if (pg.d_mean) {
+            const float4 ga = __ldg(reinterpret_cast<const float4*>(pg.d_mean + (size_t)b * pg.ld_dmean + c));
+            dv.x += ga.x * inv; dv.y += ga.y * inv; dv.z += ga.z * inv; dv.w += ga.w * inv;
+        }
+        const float4 mu = __ldg(reinterpret_cast<const float4*>(mean + c)), is = __ldg(reinterpret_cast<const float4*>(invstd + c));
+        const float4 g = gamma ? __ldg(reinterpret_cast<const float4*>(gamma + c)) : make_float4(1.f, 1.f, 1.f, 1.f);
+        const float4 bt = beta ? __ldg(reinterpret_cast<const float4*>(beta + c)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        const float4 s1 = __ldg(reinterpret_cast<const float4*>(sum_dz + c)), s2 = __ldg(reinterpret_cast<const float4*>(sum_dz_xh + c));
+        auto one = [&](float yy, float dd, float m, float i_, float gg, float bb, float a1, float a2) {
+            float xh = (yy - m) * i_;
+            float z = gg * xh + bb;
+            float dz = dd * (z > 0.f ? 1.f : slope);
+            return gg * i_ * (dz - a1 * invM - xh * (a2 * invM));
+        };
+        float4 o;
+        o.x = one(yv.x, dv.x, mu.x, is.x, g.x, bt.x, s1.x, s2.x); o.y = one(yv.y, dv.y, mu.y, is.y, g.y, bt.y, s1.y, s2.y);
+        o.z = one(yv.z, dv.z, mu.z, is.z, g.z, bt.z, s1.z, s2.z); o.w = one(yv.w, dv.w, mu.w, is.w, g.w, bt.w, s1.w, s2.w);
         *reinterpret_cast<float4*>(dy + r * ld_dy + c) = o;
     }
 }
@@ -504,9 +574,16 @@ __global__ void segmax_bwd_kernel(const float* __restrict__ dout, long long ldd,
 
 // ---- global pools (one CTA per (cloud, 32-channel block); rows of a cloud are contiguous) ------
 // out_max[b,c] = max_i x[i,c] (arg kept), out_mean[b,c] = mean_i x[i,c]
+// With BN the pooled quantity is leaky_relu(gamma * (x - mean) * invstd + beta): the activation of the embedding layer is
+// applied while its pre-activation is read, so the [N,C] activation never exists in memory.
+struct BnAct {
+    const float* mean; const float* invstd; const float* gamma; const float* beta; float slope;
+};
+
+template <bool BN>
 __global__ void __launch_bounds__(256) pool_fwd_kernel(const float* __restrict__ x, long long ldx, const int* __restrict__ cloud_ptr,
                                                        int C, float* __restrict__ out_max, long long ld_max,
-                                                       float* __restrict__ out_mean, long long ld_mean, int* __restrict__ arg) {
+                                                       float* __restrict__ out_mean, long long ld_mean, int* __restrict__ arg, BnAct bn) {
     __shared__ float smax[8][32];
     __shared__ int sarg[8][32];
     __shared__ float ssum[8][32];
@@ -515,8 +592,14 @@ __global__ void __launch_bounds__(256) pool_fwd_kernel(const float* __restrict__
     const int s = __ldg(cloud_ptr + b), e = __ldg(cloud_ptr + b + 1);
     float best = -INFINITY, sum = 0.f; int bi = s;
     if (c < C) {
+        float mu = 0.f, is = 1.f, g = 1.f, bt = 0.f;
+        if (BN) {
+            mu = __ldg(bn.mean + c); is = __ldg(bn.invstd + c);
+            g = bn.gamma ? __ldg(bn.gamma + c) : 1.f; bt = bn.beta ? __ldg(bn.beta + c) : 0.f;
+        }
         for (int i = s + rl; i < e; i += 8) {
             float v = __ldg(x + (size_t)i * ldx + c);
+            if (BN) { v = g * ((v - mu) * is) + bt; v = v > 0.f ? v : bn.slope * v; }
             sum += v;
             if (v > best) { best = v; bi = i; }
         }
@@ -597,7 +680,7 @@ extern "C" size_t dc_colreduce_ws_bytes(int C) { return (size_t)RED_MAX_CHUNKS *
 // mode 0: statistics of x [M,C]; mode 1: statistics of the norms of a vector field x [2M,C]
 extern "C" int dc_bn_stats(const float* x, int64_t ldx, int64_t M, int C, int mode, float eps, float momentum,
                            float* mean, float* invstd, float* running_mean_or_null, float* running_var_or_null,
-                           void* ws, size_t ws_bytes, void* stream) {
+                           int64_t* num_batches_tracked_or_null, void* ws, size_t ws_bytes, void* stream) {
     DC_REQUIRE(M >= 1 && C >= 1, "dc_bn_stats: empty input");
     DC_REQUIRE(ws_bytes >= dc_colreduce_ws_bytes(C), "dc_bn_stats: workspace too small");
     cudaStream_t st = (cudaStream_t)stream;
@@ -607,7 +690,8 @@ extern "C" int dc_bn_stats(const float* x, int64_t ldx, int64_t M, int C, int mo
     if (mode == 0) { PlainVal f = {x, ldx}; col_reduce_kernel<2><<<grid, RED_T, 0, st>>>(f, M, C, L.col_lanes, L.rows_per_chunk, partial); }
     else { NormVal f = {x, ldx}; col_reduce_kernel<2><<<grid, RED_T, 0, st>>>(f, M, C, L.col_lanes, L.rows_per_chunk, partial); }
     bn_finalize_kernel<<<dc_ceil_div(C, FIN_COLS), FIN_T, 0, st>>>(partial, L.chunks, M, C, eps, momentum, mean, invstd,
-                                                            running_mean_or_null, running_var_or_null);
+                                                            running_mean_or_null, running_var_or_null,
+                                                            (long long*)num_batches_tracked_or_null);
     return dc_check_launch_n("dc_bn_stats", 2);
 }
 
@@ -762,8 +846,45 @@ extern "C" int dc_pool_fwd(const float* x, int64_t ldx, const int32_t* cloud_ptr
                            int64_t ld_max, float* out_mean_or_null, int64_t ld_mean, int32_t* arg, void* stream) {
     if (B <= 0 || C <= 0) return DC_OK;
     dim3 grid(B, dc_ceil_div(C, 32));
-    pool_fwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, ldx, cloud_ptr, C, out_max_or_null, ld_max, out_mean_or_null, ld_mean, arg);
+    pool_fwd_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(x, ldx, cloud_ptr, C, out_max_or_null, ld_max, out_mean_or_null, ld_mean, arg, BnAct{});
     return dc_check_launch("dc_pool_fwd");
+}
+
+extern "C" int dc_bn_act_pool_fwd(const float* y, int64_t ldy, const int32_t* cloud_ptr, int B, int C, const float* mean, const float* invstd,
+                                  const float* gamma_or_null, const float* beta_or_null, float slope, float* out_max_or_null, int64_t ld_max,
+                                  float* out_mean_or_null, int64_t ld_mean, int32_t* arg, void* stream) {
+    DC_REQUIRE(mean != nullptr && invstd != nullptr, "dc_bn_act_pool_fwd: statistics missing");
+    if (B <= 0 || C <= 0) return DC_OK;
+    dim3 grid(B, dc_ceil_div(C, 32));
+    BnAct bn = {mean, invstd, gamma_or_null, beta_or_null, slope};
+    pool_fwd_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(y, ldy, cloud_ptr, C, out_max_or_null, ld_max, out_mean_or_null, ld_mean, arg, bn);
+    return dc_check_launch("dc_bn_act_pool_fwd");
+}
+
+// Backward of pool([max|mean]) o leaky_relu o BatchNorm in two passes over y: the pooled gradient of row r is rebuilt from the
+// [B,C] gradients (the argmax row receives d_max, every row d_mean / count), so neither it nor the activation is ever stored.
+extern "C" int dc_bn_act_pool_bwd(const float* y, int64_t ldy, int64_t M, int C, const int64_t* batch_or_null, const int32_t* cloud_ptr, int B,
+                                  const int32_t* arg, const float* d_max_or_null, int64_t ld_dmax, const float* d_mean_or_null, int64_t ld_dmean,
+                                  const float* mean, const float* invstd, const float* gamma_or_null, const float* beta_or_null, float slope,
+                                  float* d_gamma, float* d_beta, float* dy, int64_t ld_dy, void* ws, size_t ws_bytes, void* stream) {
+    DC_REQUIRE(M >= 1 && C >= 1 && B >= 1, "dc_bn_act_pool_bwd: empty input");
+    DC_REQUIRE(batch_or_null != nullptr || B == 1, "dc_bn_act_pool_bwd: batch vector needed for more than one cloud");
+    DC_REQUIRE(d_max_or_null == nullptr || arg != nullptr, "dc_bn_act_pool_bwd: d_max without the argmax rows");
+    DC_REQUIRE(C % 4 == 0 && ldy % 4 == 0 && ld_dy % 4 == 0 && ld_dmax % 4 == 0 && ld_dmean % 4 == 0 &&
+               all_aligned16(y, dy, mean, invstd, gamma_or_null, beta_or_null) && all_aligned16(d_gamma, d_beta, d_max_or_null, d_mean_or_null, arg),
+               "dc_bn_act_pool_bwd: needs C %% 4 == 0 and 16-byte aligned rows");
+    DC_REQUIRE(ws_bytes >= dc_colreduce_ws_bytes(C), "dc_bn_act_pool_bwd: workspace too small");
+    cudaStream_t st = (cudaStream_t)stream;
+    ColLayout L = col_layout(M, C);
+    dim3 grid(L.chunks, L.col_blocks);
+    double* partial = (double*)ws;
+    PoolGrad pg = {(const long long*)batch_or_null, cloud_ptr, arg, d_max_or_null, ld_dmax, d_mean_or_null, ld_dmean, C};
+    PoolBnBwdVal f = {y, ldy, pg, mean, invstd, gamma_or_null, beta_or_null, slope};
+    col_reduce_kernel<2><<<grid, RED_T, 0, st>>>(f, M, C, L.col_lanes, L.rows_per_chunk, partial);
+    sum2_finalize_kernel<<<dc_ceil_div(C, FIN_COLS), FIN_T, 0, st>>>(partial, L.chunks, C, d_beta, d_gamma);
+    bn_act_pool_bwd_vec4_kernel<<<elementwise_grid(M * C / 4), 256, 0, st>>>(y, ldy, pg, M, C / 4, mean, invstd, gamma_or_null, beta_or_null,
+                                                                         slope, d_beta, d_gamma, dy, ld_dy);
+    return dc_check_launch_n("dc_bn_act_pool_bwd", 3);
 }
 
 extern "C" int dc_pool_bwd(const int32_t* cloud_ptr, int B, int N, int C, const int32_t* arg, const float* d_max_or_null,

@@ -40,6 +40,8 @@ struct SpArgs {
     float* out0; long long ld_out0;
     float* out1; long long ld_out1;
     float* out2; long long ld_out2;
+    const float* cp_src; long long ld_cp_src;   // OP_DIVCURL: x [N,C], OP_HODGE: v [2N,C] — copied through into a column
+    float* cp_dst; long long ld_cp_dst;         // slice of the concatenation buffer (saves a strided copy launch)
     const int* cloud_ptr; int B; int max_cloud;   // staged variant: clouds and the size of the largest one (0 = unknown)
 };
 
@@ -142,6 +144,11 @@ __global__ void __launch_bounds__(256) spmm_kernel(SpArgs a, int lpp_log2) {
         }
     }
     if (!row_ok || !ch_ok) return;
+    if (OP == OP_DIVCURL && a.cp_src) V::load(a.cp_src + (size_t)r * a.ld_cp_src + ch).store(a.cp_dst + (size_t)r * a.ld_cp_dst + ch);
+    if (OP == OP_HODGE && a.cp_src) {
+        V::load(a.cp_src + (size_t)(2 * r) * a.ld_cp_src + ch).store(a.cp_dst + (size_t)(2 * r) * a.ld_cp_dst + ch);
+        V::load(a.cp_src + (size_t)(2 * r + 1) * a.ld_cp_src + ch).store(a.cp_dst + (size_t)(2 * r + 1) * a.ld_cp_dst + ch);
+    }
     if (OP == OP_GRAD || OP == OP_HODGE) {
         acc0.store(a.out0 + (size_t)(2 * r) * a.ld_out0 + ch);
         acc1.store(a.out0 + (size_t)(2 * r + 1) * a.ld_out0 + ch);
@@ -284,6 +291,11 @@ __global__ void __launch_bounds__(256) spmm_staged_kernel(SpArgs a, int CH, int 
             }
         }
         if (!row_ok || !ch_ok) continue;
+        if (OP == OP_DIVCURL && a.cp_src) V::load(a.cp_src + (size_t)r * a.ld_cp_src + ch).store(a.cp_dst + (size_t)r * a.ld_cp_dst + ch);
+        if (OP == OP_HODGE && a.cp_src) {
+            V::load(a.cp_src + (size_t)(2 * r) * a.ld_cp_src + ch).store(a.cp_dst + (size_t)(2 * r) * a.ld_cp_dst + ch);
+            V::load(a.cp_src + (size_t)(2 * r + 1) * a.ld_cp_src + ch).store(a.cp_dst + (size_t)(2 * r + 1) * a.ld_cp_dst + ch);
+        }
         if (OP == OP_GRAD || OP == OP_HODGE) {
             acc0.store(a.out0 + (size_t)(2 * r) * a.ld_out0 + ch);
             acc1.store(a.out0 + (size_t)(2 * r + 1) * a.ld_out0 + ch);
@@ -323,7 +335,8 @@ template <int OP>
 int launch_spmm(const SpArgs& a, cudaStream_t st) {
     if (a.N <= 0 || a.C <= 0) return DC_OK;
     const bool vec4 = (a.C % 4 == 0) && a.ld_in0 % 4 == 0 && a.ld_in1 % 4 == 0 && a.ld_in2 % 4 == 0 && a.ld_in3 % 4 == 0 &&
-                      a.ld_out0 % 4 == 0 && a.ld_out1 % 4 == 0 && a.ld_out2 % 4 == 0 && aligned16(a.in0) && aligned16(a.in1) &&
+                      a.ld_out0 % 4 == 0 && a.ld_out1 % 4 == 0 && a.ld_out2 % 4 == 0 && a.ld_cp_src % 4 == 0 && a.ld_cp_dst % 4 == 0 &&
+                      aligned16(a.cp_src) && aligned16(a.cp_dst) && aligned16(a.in0) && aligned16(a.in1) &&
                       aligned16(a.in2) && aligned16(a.in3) && aligned16(a.out0) && aligned16(a.out1) && aligned16(a.out2);
     if (vec4 && a.cloud_ptr != nullptr && a.max_cloud > 0 && g_spmm_staged) {
         // shared-memory staged variant: pick the channel chunk so that the staged rows fit (<= ~200 KB)
@@ -464,9 +477,12 @@ extern "C" int dc_grad_bwd(const int32_t* in_ptr, const int32_t* in_edge, const 
 
 extern "C" int dc_divcurlnorm_fwd(const int32_t* idx, const float* D, int N, int k, int C, const float* v, int64_t ldv,
                                   float* div_or_null, int64_t ld_div, float* curl_or_null, int64_t ld_curl,
-                                  float* norm_or_null, int64_t ld_norm, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream) {
+                                  float* norm_or_null, int64_t ld_norm, const float* x_or_null, int64_t ldx, float* x_copy, int64_t ld_copy,
+                                  const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream) {
     SpArgs a = {};
     SP_COMMON(a, N, k, C);
+    DC_REQUIRE(x_or_null == nullptr || x_copy != nullptr, "dc_divcurlnorm_fwd: x given without a destination");
+    a.cp_src = x_or_null; a.ld_cp_src = ldx; a.cp_dst = x_copy; a.ld_cp_dst = ld_copy;
     a.idx = idx; a.coef = (const float2*)D; a.in0 = v; a.ld_in0 = ldv;
     a.out0 = div_or_null; a.ld_out0 = ld_div; a.out1 = curl_or_null; a.ld_out1 = ld_curl; a.out2 = norm_or_null; a.ld_out2 = ld_norm;
     a.cloud_ptr = cloud_ptr_or_null; a.B = B; a.max_cloud = max_cloud_points;
@@ -488,9 +504,12 @@ extern "C" int dc_divcurlnorm_bwd(const int32_t* in_ptr, const int32_t* in_edge,
 }
 
 extern "C" int dc_hodge_fwd(const int32_t* idx, const float* G, int N, int k, int C, const float* div_v, int64_t ld_a,
-                            const float* curl_v, int64_t ld_b, float* out, int64_t ldo, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream) {
+                            const float* curl_v, int64_t ld_b, float* out, int64_t ldo, const float* v_or_null, int64_t ldv,
+                            float* v_copy, int64_t ld_copy, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream) {
     SpArgs a = {};
     SP_COMMON(a, N, k, C);
+    DC_REQUIRE(v_or_null == nullptr || v_copy != nullptr, "dc_hodge_fwd: v given without a destination");
+    a.cp_src = v_or_null; a.ld_cp_src = ldv; a.cp_dst = v_copy; a.ld_cp_dst = ld_copy;
     a.idx = idx; a.coef = (const float2*)G; a.in0 = div_v; a.ld_in0 = ld_a; a.in1 = curl_v; a.ld_in1 = ld_b; a.out0 = out; a.ld_out0 = ldo;
     a.cloud_ptr = cloud_ptr_or_null; a.B = B; a.max_cloud = max_cloud_points;
     return launch_spmm<OP_HODGE>(a, (cudaStream_t)stream);

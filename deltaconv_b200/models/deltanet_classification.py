@@ -20,7 +20,7 @@ class DeltaNetClassification(torch.nn.Module):
 
     def forward(self, data):
         conv_out = self.deltanet_base(data)
-        x = self.lin_embedding(torch.cat(conv_out, dim=1))
-        # [global max | global mean] in one segmented pass (deltanet_classification.py:46-49)
-        x = ops.pool(x, data.batch, 'maxmean', getattr(data, '_num_clouds', None))
+        # lin_embedding, then [global max | global mean] in one segmented pass that also applies the layer's BatchNorm and
+        # activation (deltanet_classification.py:45-49)
+        x = self.lin_embedding.forward_pooled(torch.cat(conv_out, dim=1), data.batch, 'maxmean', getattr(data, '_num_clouds', None))
         return self.classification_head(x)

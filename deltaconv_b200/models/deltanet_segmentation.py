@@ -25,10 +25,10 @@ class DeltaNetSegmentation(torch.nn.Module):
 
     def forward(self, data):
         conv_out = self.deltanet_base(data)
-        x = self.lin_global(torch.cat(conv_out, dim=1))
         batch, N = data.batch, data.pos.size(0)
         clouds = getattr(data, '_num_clouds', None)
-        x_max = ops.broadcast_rows(ops.pool(x, batch, 'max', clouds), batch, N)       # global_max_pool(x, batch)[batch]
+        # global_max_pool(lin_global(x), batch)[batch]  (deltanet_segmentation.py:58-61)
+        x_max = ops.broadcast_rows(self.lin_global.forward_pooled(torch.cat(conv_out, dim=1), batch, 'max', clouds), batch, N)
         parts = [x_max]
         if self.categorical_vector:
             parts.append(ops.broadcast_rows(self.lin_categorical(data.category), batch, N))

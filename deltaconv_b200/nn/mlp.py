@@ -57,6 +57,19 @@ class _MLP(torch.nn.Sequential):
             x = block(x, addend if i == last else None) if isinstance(block, _LinBNAct) else block(x)
         return x
 
+    def forward_pooled(self, x, batch, mode, num_clouds=None):
+        """global pool ('max' | 'mean' | 'maxmean') of this MLP's output over the clouds of `batch`; when the last block
+        qualifies, its BatchNorm + activation are evaluated inside the pooling pass (ops.linear_bn_act_pool)."""
+        blocks = list(self)
+        for block in blocks[:-1]:
+            x = block(x)
+        tail = blocks[-1]
+        if isinstance(tail, _LinBNAct) and x.dim() == 2:
+            lin, inner, slope = tail[0], tail[1].bn, _slope_of(tail[2])
+            if ops.pool_fusable(inner, lin.out_features, lin.bias, slope):
+                return ops.linear_bn_act_pool(x, lin.weight, inner, slope, batch, mode, num_clouds)
+        return ops.pool(tail(x), batch, mode, num_clouds)
+
 
 def MLP(channels, bias=False, nonlin=LeakyReLU(negative_slope=0.2)):
     """Stack of Linear -> BatchNorm1d -> nonlin blocks (mlp.py:7-11)."""

@@ -230,7 +230,7 @@ class _DivApply(torch.autograd.Function):
             raise _lib.DeltaConvLibraryError(f"div @ v: v has {v.size(0)} rows, operator has {2 * g.N} columns")
         C = v.size(1)
         out = torch.empty(g.N, C, dtype=_F32, device=v.device)
-        call('dc_divcurlnorm_fwd', ptr(g.idx), ptr(op.D), g.N, g.k, C, ptr(v), ldv, ptr(out), C, None, 0, None, 0, *g.clouds())
+        call('dc_divcurlnorm_fwd', ptr(g.idx), ptr(op.D), g.N, g.k, C, ptr(v), ldv, ptr(out), C, None, 0, None, 0, None, 0, None, 0, *g.clouds())
         ctx.op = op
         return out
 
@@ -297,22 +297,23 @@ class EllOperator:
 
 
 class _ScalarCat(torch.autograd.Function):
-    """[x | div v | curl v | |v|] (deltaconv.py:57) in one pass over v, plus a compact [div|curl]
-    copy for the Hodge Laplacian of the vector stream."""
+    """[x | div v | curl v | |v|] (deltaconv.py:57) in one pass over v (x is copied into its column block by
+    the same kernel); the second output is the [div|curl] column block, a view, for the Hodge Laplacian of the
+    vector stream."""
 
     @staticmethod
     def forward(ctx, x, v, op):
-        x, _ = _mat(x, 'x')
+        x, ldx = _mat(x, 'x')
         v, ldv = _mat(v, 'v')
         g = op.graph
         C = x.size(1)
         if v.size(0) != 2 * g.N or v.size(1) != C or x.size(0) != g.N:
             raise _lib.DeltaConvLibraryError(f"DeltaConv: x {tuple(x.shape)} / v {tuple(v.shape)} do not match N={g.N}")
         cat = torch.empty(g.N, 4 * C, dtype=_F32, device=x.device)
-        cat[:, :C].copy_(x)
         call('dc_divcurlnorm_fwd', ptr(g.idx), ptr(op.D), g.N, g.k, C, ptr(v), ldv,
-             cat.data_ptr() + 4 * C, 4 * C, cat.data_ptr() + 8 * C, 4 * C, cat.data_ptr() + 12 * C, 4 * C, *g.clouds())
-        dc = cat[:, C:3 * C].contiguous()
+             cat.data_ptr() + 4 * C, 4 * C, cat.data_ptr() + 8 * C, 4 * C, cat.data_ptr() + 12 * C, 4 * C,
+             ptr(x), ldx, cat.data_ptr(), 4 * C, *g.clouds())
+        dc = cat[:, C:3 * C]
         ctx.op, ctx.C = op, C
         ctx.save_for_backward(v)
         return cat, dc
@@ -341,16 +342,15 @@ class _VectorCat(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, v, dc, x_new, op):
-        v, _ = _mat(v, 'v')
+        v, ldv = _mat(v, 'v')
         dc, ld_dc = _mat(dc, 'div_curl')
         x_new, ldx = _mat(x_new, 'x')
         g = op.graph
         Cin, Cout = v.size(1), x_new.size(1)
         W = 2 * Cin + Cout
         cat = torch.empty(2 * g.N, W, dtype=_F32, device=v.device)
-        cat[:, :Cin].copy_(v)
         call('dc_hodge_fwd', ptr(g.idx), ptr(op.G), g.N, g.k, Cin, ptr(dc), ld_dc, dc.data_ptr() + 4 * Cin, ld_dc,
-             cat.data_ptr() + 4 * Cin, W, *g.clouds())
+             cat.data_ptr() + 4 * Cin, W, ptr(v), ldv, cat.data_ptr(), W, *g.clouds())
         call('dc_grad_fwd', ptr(g.idx), ptr(op.G), g.N, g.k, Cout, ptr(x_new), ldx, cat.data_ptr() + 8 * Cin, W, *g.clouds())
         ctx.op, ctx.Cin, ctx.Cout = op, Cin, Cout
         return cat
@@ -388,7 +388,7 @@ class _CurlApply(torch.autograd.Function):
         g = op.graph
         C = v.size(1)
         out = torch.empty(g.N, C, dtype=_F32, device=v.device)
-        call('dc_divcurlnorm_fwd', ptr(g.idx), ptr(op.D), g.N, g.k, C, ptr(v), ldv, None, 0, ptr(out), C, None, 0, *g.clouds())
+        call('dc_divcurlnorm_fwd', ptr(g.idx), ptr(op.D), g.N, g.k, C, ptr(v), ldv, None, 0, ptr(out), C, None, 0, None, 0, None, 0, *g.clouds())
         ctx.op = op
         return out
 
@@ -493,6 +493,22 @@ def vector_linear_with_rotation(v_cat, weight):
 # BatchNorm + activation, VectorNonLin
 # ------------------------------------------------------------------------------------------------
 
+def _running_update(bn):
+    """(update, momentum, counter pointer) for a training-mode statistics pass.  With a fixed momentum the kernel
+    increments `num_batches_tracked` itself; the cumulative average (momentum=None) needs the count on the host."""
+    update = bn.training and bn.track_running_stats and bn.running_mean is not None
+    if not update:
+        return False, 0.0, None
+    if bn.momentum is None:
+        bn.num_batches_tracked += 1
+        return True, 1.0 / float(bn.num_batches_tracked), None
+    nbt = bn.num_batches_tracked
+    counted = nbt is not None and nbt.is_cuda and nbt.dtype == torch.int64
+    if nbt is not None and not counted:
+        bn.num_batches_tracked += 1
+    return True, float(bn.momentum), (nbt.data_ptr() if counted else None)
+
+
 def _bn_moments(bn, x, ldx, M, C, mode):
     """(mean, invstd) to normalise with: batch statistics in training mode (running stats are
     updated in place like torch.nn.BatchNorm1d), running statistics in eval mode."""
@@ -501,15 +517,11 @@ def _bn_moments(bn, x, ldx, M, C, mode):
     if use_batch:
         mean = torch.empty(C, dtype=_F32, device=dev)
         invstd = torch.empty(C, dtype=_F32, device=dev)
-        update = bn.training and bn.track_running_stats and bn.running_mean is not None
-        momentum = 0.0
-        if update:
-            bn.num_batches_tracked += 1
-            momentum = bn.momentum if bn.momentum is not None else 1.0 / float(bn.num_batches_tracked)
+        update, momentum, nbt = _running_update(bn)
         nb = query('dc_colreduce_ws_bytes', C)
         ws = workspace(nb, dev)
         call('dc_bn_stats', x.data_ptr(), ldx, M, C, mode, float(bn.eps), float(momentum), ptr(mean), ptr(invstd),
-             ptr(bn.running_mean) if update else None, ptr(bn.running_var) if update else None, ptr(ws), nb)
+             ptr(bn.running_mean) if update else None, ptr(bn.running_var) if update else None, nbt, ptr(ws), nb)
         return mean, invstd, True
     mean = bn.running_mean.contiguous()
     invstd = torch.rsqrt(bn.running_var + bn.eps)
@@ -574,17 +586,13 @@ class _LinearBNAct(torch.autograd.Function):
         y = torch.empty(M, C, dtype=_F32, device=dev)
         mean = torch.empty(C, dtype=_F32, device=dev)
         invstd = torch.empty(C, dtype=_F32, device=dev)
-        update = bn.training and bn.track_running_stats and bn.running_mean is not None
-        momentum = 0.0
-        if update:
-            bn.num_batches_tracked += 1
-            momentum = bn.momentum if bn.momentum is not None else 1.0 / float(bn.num_batches_tracked)
+        update, momentum, nbt = _running_update(bn)
         ws, nb = _gemm_ws(M, C, K, dev)
         call('dc_linear_fwd', ptr(x), ldx, ptr(weight), ldw, None, M, K, C, ptr(y), C, ptr(ws), nb)
         nb = query('dc_colreduce_ws_bytes', C)
         ws = workspace(nb, dev)
         call('dc_bn_stats', ptr(y), C, M, C, 0, float(bn.eps), float(momentum), ptr(mean), ptr(invstd),
-             ptr(bn.running_mean) if update else None, ptr(bn.running_var) if update else None, ptr(ws), nb)
+             ptr(bn.running_mean) if update else None, ptr(bn.running_var) if update else None, nbt, ptr(ws), nb)
         out = torch.empty(M, C, dtype=_F32, device=dev)
         add_p, ld_add = None, 0
         if addend is not None:
@@ -780,14 +788,10 @@ class _CentralizedMax(torch.autograd.Function):
             moments = torch.empty(20, dtype=torch.float64, device=dev)
             mean = torch.empty(Cout, dtype=_F32, device=dev)
             invstd = torch.empty(Cout, dtype=_F32, device=dev)
-            update = bn.training and bn.track_running_stats and bn.running_mean is not None
-            momentum = 0.0
-            if update:
-                bn.num_batches_tracked += 1
-                momentum = bn.momentum if bn.momentum is not None else 1.0 / float(bn.num_batches_tracked)
+            update, momentum, nbt = _running_update(bn)
             call('dc_central_stats', ptr(graph.idx), N, k, Cin, Cout, ptr(x), ldx, ptr(weight), float(bn.eps), float(momentum),
                  ptr(moments), ptr(mean), ptr(invstd), ptr(bn.running_mean) if update else None,
-                 ptr(bn.running_var) if update else None, ptr(ws), nbytes)
+                 ptr(bn.running_var) if update else None, nbt, ptr(ws), nbytes)
         else:
             mean = bn.running_mean.contiguous()
             invstd = torch.rsqrt(bn.running_var + bn.eps)
@@ -862,6 +866,87 @@ class _Pool(torch.autograd.Function):
 def pool(x, batch, mode, size=None):
     cp, B = cloud_ptr_of(batch, x.size(0), x.device, size)
     return _Pool.apply(x, cp, B, mode)
+
+
+class _LinearBNActPool(torch.autograd.Function):
+    """pool(act(BatchNorm1d(x @ W.T))) with batch statistics — the embedding layer and the global pools that consume it
+    (deltanet_classification.py:45-49, deltanet_segmentation.py:58-61) as one node: the [N,C] activation and its
+    gradient are never written (dc_bn_act_pool_fwd / dc_bn_act_pool_bwd)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, gamma, beta, bn, slope, batch, cloud_ptr, B, mode):
+        x, ldx = _mat(x, 'input')
+        weight, ldw = _mat(weight, 'weight')
+        if x.size(1) != weight.size(1):
+            raise _lib.DeltaConvLibraryError(f"Linear: input has {x.size(1)} features, weight expects {weight.size(1)}")
+        M, K, C = x.size(0), x.size(1), weight.size(0)
+        if M == 0:
+            raise _lib.DeltaConvLibraryError("BatchNorm1d: empty batch")
+        dev = x.device
+        y = torch.empty(M, C, dtype=_F32, device=dev)
+        mean = torch.empty(C, dtype=_F32, device=dev)
+        invstd = torch.empty(C, dtype=_F32, device=dev)
+        update, momentum, nbt = _running_update(bn)
+        ws, nb = _gemm_ws(M, C, K, dev)
+        call('dc_linear_fwd', ptr(x), ldx, ptr(weight), ldw, None, M, K, C, ptr(y), C, ptr(ws), nb)
+        nb = query('dc_colreduce_ws_bytes', C)
+        ws = workspace(nb, dev)
+        call('dc_bn_stats', ptr(y), C, M, C, 0, float(bn.eps), float(momentum), ptr(mean), ptr(invstd),
+             ptr(bn.running_mean) if update else None, ptr(bn.running_var) if update else None, nbt, ptr(ws), nb)
+        want_max, want_mean = mode in ('max', 'maxmean'), mode in ('mean', 'maxmean')
+        width = C * (2 if mode == 'maxmean' else 1)
+        out = torch.empty(B, width, dtype=_F32, device=dev)
+        arg = torch.empty(B, C, dtype=_I32, device=dev) if want_max else None
+        mean_p = (out.data_ptr() + (4 * C if mode == 'maxmean' else 0)) if want_mean else None
+        call('dc_bn_act_pool_fwd', ptr(y), C, ptr(cloud_ptr), B, C, ptr(mean), ptr(invstd), ptr(gamma), ptr(beta), float(slope),
+             ptr(out) if want_max else None, width, mean_p, width, ptr(arg))
+        ctx.save_for_backward(x, weight, y, mean, invstd, gamma, beta, batch, cloud_ptr, arg)
+        ctx.slope, ctx.mode, ctx.B = slope, mode, B
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        x, weight, y, mean, invstd, gamma, beta, batch, cloud_ptr, arg = ctx.saved_tensors
+        x, ldx = _mat(x)
+        weight, ldw = _mat(weight)
+        dout, ld = _mat(dout, 'grad_output')
+        M, K, C = x.size(0), x.size(1), weight.size(0)
+        dev, mode = x.device, ctx.mode
+        dgamma = torch.empty(C, dtype=_F32, device=dev)
+        dbeta = torch.empty(C, dtype=_F32, device=dev)
+        dy = torch.empty(M, C, dtype=_F32, device=dev)
+        dmax = dout.data_ptr() if mode in ('max', 'maxmean') else None
+        dmean = (dout.data_ptr() + (4 * C if mode == 'maxmean' else 0)) if mode in ('mean', 'maxmean') else None
+        nb = query('dc_colreduce_ws_bytes', C)
+        ws = workspace(nb, dev)
+        call('dc_bn_act_pool_bwd', ptr(y), C, M, C, ptr(batch), ptr(cloud_ptr), ctx.B, ptr(arg), dmax, ld, dmean, ld,
+             ptr(mean), ptr(invstd), ptr(gamma), ptr(beta), float(ctx.slope), ptr(dgamma), ptr(dbeta), ptr(dy), C, ptr(ws), nb)
+        dx = dw = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty(M, K, dtype=_F32, device=dev)
+            ws, nb = _gemm_ws(M, K, C, dev)
+            call('dc_linear_bwd_input', ptr(dy), C, ptr(weight), ldw, M, K, C, ptr(dx), K, ptr(ws), nb)
+        if ctx.needs_input_grad[1]:
+            dw = torch.empty(C, K, dtype=_F32, device=dev)
+            ws, nb = _gemm_ws(C, K, M, dev)
+            call('dc_linear_bwd_weight', ptr(dy), C, ptr(x), ldx, M, K, C, ptr(dw), K, ptr(ws), nb)
+        return (dx, dw, dgamma if gamma is not None else None, dbeta if beta is not None else None) + (None,) * 6
+
+
+def linear_bn_act_pool(x, weight, bn, slope, batch, mode, size=None):
+    """pool(act(BatchNorm1d(x @ weight.T)), batch) with batch statistics; mode 'max' | 'mean' | 'maxmean'.
+    Needs out_features % 4 == 0 (see `pool_fusable`)."""
+    cp, B = cloud_ptr_of(batch, x.size(0), x.device, size)
+    if batch is not None:
+        batch = batch.contiguous()
+    return _LinearBNActPool.apply(x, weight, bn.weight, bn.bias, bn, float(slope), batch, cp, B, mode)
+
+
+def pool_fusable(bn, out_features, bias, slope):
+    """True when Linear -> BatchNorm1d -> LeakyReLU -> pool can run as the fused node: training-mode statistics, no
+    Linear bias, a LeakyReLU-family activation and a channel count the float4 kernels take."""
+    batch_stats = bn.training or not bn.track_running_stats or bn.running_mean is None
+    return batch_stats and bias is None and slope is not None and out_features % 4 == 0
 
 
 class _BcastRows(torch.autograd.Function):

@@ -104,19 +104,23 @@ int dc_grad_fwd(const int32_t* idx, const float* G, int N, int k, int C, const f
 int dc_grad_bwd(const int32_t* in_ptr, const int32_t* in_edge, const float* G, int N, int k, int C,
                 const float* dV, int64_t ld_dv, float* dX, int64_t ld_dx, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream);
 
-/* [div @ v | curl(v, div) | norm(v)] in one pass — deltaconv.py:57, operators.py:4-7,23-27. */
+/* [div @ v | curl(v, div) | norm(v)] in one pass — deltaconv.py:57, operators.py:4-7,23-27.  With x given, x [N,C] is also
+ * copied to x_copy (the first column block of the same torch.cat) by the same threads. */
 int dc_divcurlnorm_fwd(const int32_t* idx, const float* D, int N, int k, int C, const float* v, int64_t ldv,
                        float* div_or_null, int64_t ld_div, float* curl_or_null, int64_t ld_curl,
-                       float* norm_or_null, int64_t ld_norm, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream);
+                       float* norm_or_null, int64_t ld_norm, const float* x_or_null, int64_t ldx, float* x_copy, int64_t ld_copy,
+                       const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream);
 int dc_divcurlnorm_bwd(const int32_t* in_ptr, const int32_t* in_edge, const float* D, int N, int k, int C,
                        const float* d_div_or_null, int64_t ld_ddiv, const float* d_curl_or_null, int64_t ld_dcurl,
                        const float* d_norm_or_null, int64_t ld_dnorm, const float* v, int64_t ldv,
                        float* dV, int64_t ld_dv, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream);
 
 /* hodge_laplacian(v, grad, div) given div v and curl v — operators.py:35-46:
- * out = -(grad(div_v) + J grad(curl_v)), rows interleaved like every vector field. */
+ * out = -(grad(div_v) + J grad(curl_v)), rows interleaved like every vector field.  With v given, v [2N,C] is also copied to
+ * v_copy (the first column block of torch.cat([v, hodge, grad x]), deltaconv.py:66). */
 int dc_hodge_fwd(const int32_t* idx, const float* G, int N, int k, int C, const float* div_v, int64_t ld_a,
-                 const float* curl_v, int64_t ld_b, float* out, int64_t ldo, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream);
+                 const float* curl_v, int64_t ld_b, float* out, int64_t ldo, const float* v_or_null, int64_t ldv,
+                 float* v_copy, int64_t ld_copy, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream);
 int dc_hodge_bwd(const int32_t* in_ptr, const int32_t* in_edge, const float* G, int N, int k, int C,
                  const float* d_out, int64_t ld_do, float* d_div, int64_t ld_da, float* d_curl, int64_t ld_db,
                  const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream);
@@ -147,7 +151,8 @@ int dc_central_max_cin(void);
 size_t dc_central_ws_bytes(int N, int k, int Cin, int Cout);
 int dc_central_stats(const int32_t* idx, int N, int k, int Cin, int Cout, const float* x, int64_t ldx, const float* W,
                      float eps, float momentum, double* moments, float* mean, float* invstd,
-                     float* running_mean_or_null, float* running_var_or_null, void* ws, size_t ws_bytes, void* stream);
+                     float* running_mean_or_null, float* running_var_or_null, int64_t* num_batches_tracked_or_null,
+                     void* ws, size_t ws_bytes, void* stream);
 int dc_central_fwd(const int32_t* idx, int N, int k, int Cin, int Cout, const float* x, int64_t ldx, const float* W,
                    const float* gamma_or_null, const float* beta_or_null, const float* mean, const float* invstd, float slope,
                    float* out, int64_t ldo, uint8_t* arg, void* stream);
@@ -164,7 +169,7 @@ size_t dc_colreduce_ws_bytes(int C);
  * Writes mean/invstd (biased variance, eps) and updates running stats like torch.nn.BatchNorm1d. */
 int dc_bn_stats(const float* x, int64_t ldx, int64_t M, int C, int mode, float eps, float momentum,
                 float* mean, float* invstd, float* running_mean_or_null, float* running_var_or_null,
-                void* ws, size_t ws_bytes, void* stream);
+                int64_t* num_batches_tracked_or_null, void* ws, size_t ws_bytes, void* stream);
 /* out = leaky_relu(gamma*(y-mean)*invstd+beta, slope) + addend   (addend: `x_max +`, deltaconv.py:59) */
 int dc_bn_act_fwd(const float* y, int64_t ldy, int64_t M, int C, const float* mean, const float* invstd,
                   const float* gamma_or_null, const float* beta_or_null, float slope,
@@ -190,6 +195,18 @@ int dc_pool_fwd(const float* x, int64_t ldx, const int32_t* cloud_ptr, int B, in
                 int64_t ld_max, float* out_mean_or_null, int64_t ld_mean, int32_t* arg, void* stream);
 int dc_pool_bwd(const int32_t* cloud_ptr, int B, int N, int C, const int32_t* arg, const float* d_max_or_null,
                 int64_t ld_dmax, const float* d_mean_or_null, int64_t ld_dmean, float* dx, int64_t ld_dx, void* stream);
+/* The embedding layer's BatchNorm + LeakyReLU fused with the pools that consume it (deltanet_classification.py:45-49,
+ * deltanet_segmentation.py:58-61: `lin_embedding`/`lin_global` -> global_max_pool / global_mean_pool): the pooled value is
+ * leaky_relu(gamma*(y-mean)*invstd+beta) evaluated while y is read, and the backward rebuilds the pooled gradient of each row from
+ * the [B,C] gradients, so neither the [N,C] activation nor its gradient is stored.  Training-mode statistics (dc_bn_stats).
+ * batch = the PyG batch vector (int64 [N], sorted), NULL when B == 1.  bwd needs C % 4 == 0. */
+int dc_bn_act_pool_fwd(const float* y, int64_t ldy, const int32_t* cloud_ptr, int B, int C, const float* mean, const float* invstd,
+                       const float* gamma_or_null, const float* beta_or_null, float slope, float* out_max_or_null, int64_t ld_max,
+                       float* out_mean_or_null, int64_t ld_mean, int32_t* arg, void* stream);
+int dc_bn_act_pool_bwd(const float* y, int64_t ldy, int64_t M, int C, const int64_t* batch_or_null, const int32_t* cloud_ptr, int B,
+                       const int32_t* arg, const float* d_max_or_null, int64_t ld_dmax, const float* d_mean_or_null, int64_t ld_dmean,
+                       const float* mean, const float* invstd, const float* gamma_or_null, const float* beta_or_null, float slope,
+                       float* d_gamma, float* d_beta, float* dy, int64_t ld_dy, void* ws, size_t ws_bytes, void* stream);
 /* out[i,:] = src[cloud(i),:] — `global_max_pool(x, batch)[batch]`, deltanet_segmentation.py:61,64 */
 int dc_bcast_rows(const float* src, int64_t lds, const int32_t* cloud_ptr, int B, int N, int C, float* out, int64_t ldo,
                   void* stream);

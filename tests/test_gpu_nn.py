@@ -399,6 +399,11 @@ def test_graphed_train_step_matches_eager():
     assert losses_g == pytest.approx(losses_e[2:], rel=1e-5)
     for (n1, p1), (n2, p2) in zip(eager.named_parameters(), graphed_net.named_parameters()):
         assert torch.allclose(p1, p2, rtol=1e-5, atol=1e-6), n1
+    for (n1, b1), (n2, b2) in zip(eager.named_buffers(), graphed_net.named_buffers()):
+        if n1.endswith('num_batches_tracked'):
+            assert int(b1) == int(b2) == 5, n1                # incremented by the statistics kernels, also under replay
+        else:
+            assert torch.allclose(b1, b2, rtol=1e-5, atol=1e-6), n1
 
 
 def test_config3_segmentation_shapenet_shape_vs_oracle():
@@ -478,3 +483,42 @@ def test_fused_linear_batchnorm_block(M, K, C, leaky):
     assert rel_err(mlp[0][1].bn.weight.grad.cpu(), ref_bn.weight.grad) < 1e-4
     assert rel_err(mlp[0][1].bn.running_mean.cpu(), ref_bn.running_mean) < 1e-5
     assert rel_err(mlp[0][1].bn.running_var.cpu(), ref_bn.running_var) < 1e-5
+    assert int(mlp[0][1].bn.num_batches_tracked) == int(ref_bn.num_batches_tracked) == 1      # counted by the kernel
+
+
+@pytest.mark.parametrize('sizes,K,C,mode', [([100, 37, 263], 36, 64, 'maxmean'), ([1024] * 8, 128, 1024, 'maxmean'),
+                                            ([500], 20, 32, 'max'), ([64, 64, 1, 300], 16, 40, 'mean'),
+                                            ([90, 10], 24, 30, 'maxmean')])
+def test_embedding_pool_fusion_matches_unfused(sizes, K, C, mode):
+    """lin_embedding + BatchNorm + LeakyReLU evaluated inside the pooling pass (dc_bn_act_pool_*) = the unfused
+    sequence MLP -> pool: same output, same gradients for the input and every parameter, same running statistics.
+    C = 30 is not a multiple of 4: forward_pooled must fall back to the unfused kernels by itself."""
+    import copy
+    D = dc()
+    from deltaconv_b200 import ops
+    torch.manual_seed(3)
+    N = sum(sizes)
+    batch = torch.repeat_interleave(torch.arange(len(sizes)), torch.tensor(sizes)).to(DEV)
+    fused = D.nn.MLP([K, C]).to(DEV).train()
+    with torch.no_grad():
+        fused[0][1].bn.weight.copy_(torch.randn(C) * 0.5)            # both signs: the max can sit at the column minimum
+        fused[0][1].bn.bias.copy_(torch.randn(C) * 0.3)
+    plain = copy.deepcopy(fused)
+    x0 = torch.randn(N, K)
+    width = C * (2 if mode == 'maxmean' else 1)
+    g0 = torch.randn(len(sizes), width, device=DEV)
+    xa, xb = x0.to(DEV).requires_grad_(True), x0.to(DEV).requires_grad_(True)
+    out_f = fused.forward_pooled(xa, batch, mode, len(sizes))
+    out_p = ops.pool(plain(xb), batch, mode, len(sizes))
+    (out_f * g0).sum().backward()
+    (out_p * g0).sum().backward()
+    assert report(f'embed_pool.{mode}.{C}.out', rel_err(out_f.detach().cpu(), out_p.detach().cpu())) < 1e-6
+    assert report(f'embed_pool.{mode}.{C}.dx', rel_err(xa.grad.cpu(), xb.grad.cpu())) < 1e-5
+    for (n1, p1), (_, p2) in zip(fused.named_parameters(), plain.named_parameters()):
+        assert rel_err(p1.grad.cpu(), p2.grad.cpu()) < 1e-5, n1
+    for (n1, b1), (_, b2) in zip(fused.named_buffers(), plain.named_buffers()):
+        assert torch.allclose(b1.float(), b2.float(), rtol=1e-6, atol=1e-7), n1
+    # eval mode uses the running statistics: unfused path, same numbers as MLP -> pool
+    fused.eval(), plain.eval()
+    with torch.no_grad():
+        assert torch.equal(fused.forward_pooled(xa, batch, mode, len(sizes)), ops.pool(plain(xb), batch, mode, len(sizes)))
