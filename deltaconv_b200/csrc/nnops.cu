@@ -175,70 +175,118 @@ __global__ void bn_act_bwd_vec4_kernel(const float* __restrict__ y, long long ld
 }
 
 // ---- BatchNorm + activation fused with the global pools, backward -------------------------------
-// gradient of [max | mean] pooling w.r.t. the pooled activation at (r, c), rebuilt on the fly (same expression as pool_bwd)
+// The gradient of [max | mean] pooling w.r.t. the pooled activation at (r, c) is (r == arg[b,c] ? d_max[b,c] : 0) + d_mean[b,c] / n_b
+// (same expression as pool_bwd): it is rebuilt on the fly.  Work is split by cloud so that the [B,C] quantities are loaded once per
+// thread: a unit = (cloud, split of its rows); a CTA = 32 float4 column lanes x 8 row lanes.
 struct PoolGrad {
-    const long long* batch; const int* cloud_ptr; const int* arg;
+    const int* cloud_ptr; const int* arg;
     const float* d_max; long long ld_dmax; const float* d_mean; long long ld_dmean; int C;
-    __device__ __forceinline__ int cloud(long long r) const { return batch ? (int)__ldg(batch + r) : 0; }
-    __device__ __forceinline__ float inv_count(int b) const { return 1.f / (float)max(__ldg(cloud_ptr + b + 1) - __ldg(cloud_ptr + b), 1); }
-    __device__ __forceinline__ float operator()(long long r, int b, float inv, int c) const {
-        const float gm = (d_max && __ldg(arg + (size_t)b * C + c) == (int)r) ? __ldg(d_max + (size_t)b * ld_dmax + c) : 0.f;
-        const float ga = d_mean ? __ldg(d_mean + (size_t)b * ld_dmean + c) * inv : 0.f;
-        return gm + ga;
-    }
 };
 
-struct PoolBnBwdVal {
-    const float* y; long long ldy; PoolGrad pg;
-    const float* mean; const float* invstd; const float* gamma; const float* beta; float slope;
-    __device__ void operator()(long long r, int c, float (&o)[2]) const {
-        const int b = pg.cloud(r);
-        float xh = (__ldg(y + r * ldy + c) - __ldg(mean + c)) * __ldg(invstd + c);
-        float g = gamma ? __ldg(gamma + c) : 1.f, bt = beta ? __ldg(beta + c) : 0.f;
-        float z = g * xh + bt;
-        float dz = pg(r, b, pg.inv_count(b), c) * (z > 0.f ? 1.f : slope);
-        o[0] = dz; o[1] = dz * xh;
-    }
-};
-
-__global__ void bn_act_pool_bwd_vec4_kernel(const float* __restrict__ y, long long ldy, PoolGrad pg, long long M, int C4,
-                                            const float* __restrict__ mean, const float* __restrict__ invstd,
-                                            const float* __restrict__ gamma, const float* __restrict__ beta, float slope,
-                                            const float* __restrict__ sum_dz, const float* __restrict__ sum_dz_xh,
-                                            float* __restrict__ dy, long long ld_dy) {
-    const long long total = M * (long long)C4;
-    const float invM = 1.f / (float)M;
-    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
-        const long long r = t / C4;
-        const int c = (int)(t - r * C4) * 4;
-        const int b = pg.cloud(r);
-        const float inv = pg.inv_count(b);
-        const float4 yv = ld_stream4(reinterpret_cast<const float4*>(y + r * ldy + c));
-        float4 dv = make_float4(0.f, 0.f, 0.f, 0.f);
+struct PoolGradCol {      // the per-(cloud, 4 columns) part, loaded once
+    int4 am; float4 gm, ga;
+    __device__ __forceinline__ void load(const PoolGrad& pg, int b, int c, float inv) {
+        am = make_int4(-1, -1, -1, -1); gm = make_float4(0.f, 0.f, 0.f, 0.f); ga = gm;
         if (pg.d_max) {
-            const int4 am = __ldg(reinterpret_cast<const int4*>(pg.arg + (size_t)b * pg.C + c));
-            const float4 gm = __ldg(reinterpret_cast<const float4*>(pg.d_max + (size_t)b * pg.ld_dmax + c));
-            dv.x = am.x == (int)r ? gm.x : 0.f; dv.y = am.y == (int)r ? gm.y : 0.f;
-            dv.z = am.z == (int)r ? gm.z : 0.f; dv.w = am.w == (int)r ? gm.w : 0.f;
+            am = __ldg(reinterpret_cast<const int4*>(pg.arg + (size_t)b * pg.C + c));
+            gm = __ldg(reinterpret_cast<const float4*>(pg.d_max + (size_t)b * pg.ld_dmax + c));
         }
         if (pg.d_mean) {
-            const float4 ga = __ldg(reinterpret_cast<const float4*>(pg.d_mean + (size_t)b * pg.ld_dmean + c));
-            dv.x += ga.x * inv; dv.y += ga.y * inv; dv.z += ga.z * inv; dv.w += ga.w * inv;
+            ga = __ldg(reinterpret_cast<const float4*>(pg.d_mean + (size_t)b * pg.ld_dmean + c));
+            ga.x *= inv; ga.y *= inv; ga.z *= inv; ga.w *= inv;
         }
-        const float4 mu = __ldg(reinterpret_cast<const float4*>(mean + c)), is = __ldg(reinterpret_cast<const float4*>(invstd + c));
-        const float4 g = gamma ? __ldg(reinterpret_cast<const float4*>(gamma + c)) : make_float4(1.f, 1.f, 1.f, 1.f);
-        const float4 bt = beta ? __ldg(reinterpret_cast<const float4*>(beta + c)) : make_float4(0.f, 0.f, 0.f, 0.f);
-        const float4 s1 = __ldg(reinterpret_cast<const float4*>(sum_dz + c)), s2 = __ldg(reinterpret_cast<const float4*>(sum_dz_xh + c));
+    }
+    __device__ __forceinline__ float4 at(int r) const {
+        return make_float4((am.x == r ? gm.x : 0.f) + ga.x, (am.y == r ? gm.y : 0.f) + ga.y,
+                           (am.z == r ? gm.z : 0.f) + ga.z, (am.w == r ? gm.w : 0.f) + ga.w);
+    }
+};
+
+struct BnCol {            // BatchNorm constants of 4 columns
+    float4 mu, is, g, bt;
+    __device__ __forceinline__ void load(const float* mean, const float* invstd, const float* gamma, const float* beta, int c) {
+        mu = __ldg(reinterpret_cast<const float4*>(mean + c)); is = __ldg(reinterpret_cast<const float4*>(invstd + c));
+        g = gamma ? __ldg(reinterpret_cast<const float4*>(gamma + c)) : make_float4(1.f, 1.f, 1.f, 1.f);
+        bt = beta ? __ldg(reinterpret_cast<const float4*>(beta + c)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+};
+
+// pass 1: per-CTA fp64 partial sums of dz and dz * xhat; partial[(q * 2 + v) * C + c], q = blockIdx.x
+__global__ void __launch_bounds__(256) pool_bn_bwd_reduce_kernel(const float* __restrict__ y, long long ldy, PoolGrad pg, int B, int splits, int C,
+                                                                 const float* __restrict__ mean, const float* __restrict__ invstd,
+                                                                 const float* __restrict__ gamma, const float* __restrict__ beta, float slope,
+                                                                 double* __restrict__ partial) {
+    __shared__ double sh[8][2][128];
+    const int lane = threadIdx.x & 31, rl = threadIdx.x >> 5;
+    const int c = (blockIdx.y * 32 + lane) * 4;
+    double a0[4] = {0.0, 0.0, 0.0, 0.0}, a1[4] = {0.0, 0.0, 0.0, 0.0};
+    if (c < C) {
+        BnCol k; k.load(mean, invstd, gamma, beta, c);
+        for (int u = blockIdx.x; u < B * splits; u += gridDim.x) {          // units in a fixed order: deterministic
+            const int b = u / splits, sp = u - b * splits;
+            const int s = __ldg(pg.cloud_ptr + b), e = __ldg(pg.cloud_ptr + b + 1);
+            const int per = (e - s + splits - 1) / splits;
+            const int r0 = s + sp * per, r1 = min(e, r0 + per);
+            PoolGradCol col; col.load(pg, b, c, 1.f / (float)max(e - s, 1));
+#pragma unroll 4
+            for (int r = r0 + rl; r < r1; r += 8) {
+                const float4 yv = ld_stream4(reinterpret_cast<const float4*>(y + (size_t)r * ldy + c));
+                const float4 d = col.at(r);
+                auto one = [&](float yy, float dd, float m, float i_, float gg, float bb, double& s0, double& s1) {
+                    float xh = (yy - m) * i_;
+                    float z = gg * xh + bb;
+                    float dz = dd * (z > 0.f ? 1.f : slope);
+                    s0 += (double)dz; s1 += (double)(dz * xh);
+                };
+                one(yv.x, d.x, k.mu.x, k.is.x, k.g.x, k.bt.x, a0[0], a1[0]); one(yv.y, d.y, k.mu.y, k.is.y, k.g.y, k.bt.y, a0[1], a1[1]);
+                one(yv.z, d.z, k.mu.z, k.is.z, k.g.z, k.bt.z, a0[2], a1[2]); one(yv.w, d.w, k.mu.w, k.is.w, k.g.w, k.bt.w, a0[3], a1[3]);
+            }
+        }
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) { sh[rl][0][lane * 4 + q] = a0[q]; sh[rl][1][lane * 4 + q] = a1[q]; }
+    __syncthreads();
+    const int v = threadIdx.x >> 7, cc = threadIdx.x & 127;                 // 256 threads = 2 values x 128 columns
+    const int col = blockIdx.y * 128 + cc;
+    if (col < C) {
+        double t = 0.0;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) t += sh[q][v][cc];
+        partial[((size_t)blockIdx.x * 2 + v) * C + col] = t;
+    }
+}
+
+// pass 2: dy = gamma * invstd * (dz - sum_dz / M - xhat * sum_dz_xhat / M), grid (splits, column blocks, B)
+__global__ void __launch_bounds__(256) pool_bn_bwd_apply_kernel(const float* __restrict__ y, long long ldy, PoolGrad pg, long long M, int C,
+                                                                const float* __restrict__ mean, const float* __restrict__ invstd,
+                                                                const float* __restrict__ gamma, const float* __restrict__ beta, float slope,
+                                                                const float* __restrict__ sum_dz, const float* __restrict__ sum_dz_xh,
+                                                                float* __restrict__ dy, long long ld_dy) {
+    const int lane = threadIdx.x & 31, rl = threadIdx.x >> 5;
+    const int c = (blockIdx.y * 32 + lane) * 4;
+    if (c >= C) return;
+    const int b = blockIdx.z;
+    const int s = __ldg(pg.cloud_ptr + b), e = __ldg(pg.cloud_ptr + b + 1);
+    const float invM = 1.f / (float)M;
+    BnCol k; k.load(mean, invstd, gamma, beta, c);
+    PoolGradCol col; col.load(pg, b, c, 1.f / (float)max(e - s, 1));
+    float4 s1 = __ldg(reinterpret_cast<const float4*>(sum_dz + c)), s2 = __ldg(reinterpret_cast<const float4*>(sum_dz_xh + c));
+    s1.x *= invM; s1.y *= invM; s1.z *= invM; s1.w *= invM;
+    s2.x *= invM; s2.y *= invM; s2.z *= invM; s2.w *= invM;
+#pragma unroll 4
+    for (int r = s + blockIdx.x * 8 + rl; r < e; r += gridDim.x * 8) {
+        const float4 yv = ld_stream4(reinterpret_cast<const float4*>(y + (size_t)r * ldy + c));
+        const float4 d = col.at(r);
         auto one = [&](float yy, float dd, float m, float i_, float gg, float bb, float a1, float a2) {
             float xh = (yy - m) * i_;
             float z = gg * xh + bb;
             float dz = dd * (z > 0.f ? 1.f : slope);
-            return gg * i_ * (dz - a1 * invM - xh * (a2 * invM));
+            return gg * i_ * (dz - a1 - xh * a2);
         };
         float4 o;
-        o.x = one(yv.x, dv.x, mu.x, is.x, g.x, bt.x, s1.x, s2.x); o.y = one(yv.y, dv.y, mu.y, is.y, g.y, bt.y, s1.y, s2.y);
-        o.z = one(yv.z, dv.z, mu.z, is.z, g.z, bt.z, s1.z, s2.z); o.w = one(yv.w, dv.w, mu.w, is.w, g.w, bt.w, s1.w, s2.w);
-        *reinterpret_cast<float4*>(dy + r * ld_dy + c) = o;
+        o.x = one(yv.x, d.x, k.mu.x, k.is.x, k.g.x, k.bt.x, s1.x, s2.x); o.y = one(yv.y, d.y, k.mu.y, k.is.y, k.g.y, k.bt.y, s1.y, s2.y);
+        o.z = one(yv.z, d.z, k.mu.z, k.is.z, k.g.z, k.bt.z, s1.z, s2.z); o.w = one(yv.w, d.w, k.mu.w, k.is.w, k.g.w, k.bt.w, s1.w, s2.w);
+        *reinterpret_cast<float4*>(dy + (size_t)r * ld_dy + c) = o;
     }
 }
 
@@ -863,27 +911,33 @@ extern "C" int dc_bn_act_pool_fwd(const float* y, int64_t ldy, const int32_t* cl
 
 // Backward of pool([max|mean]) o leaky_relu o BatchNorm in two passes over y: the pooled gradient of row r is rebuilt from the
 // [B,C] gradients (the argmax row receives d_max, every row d_mean / count), so neither it nor the activation is ever stored.
-extern "C" int dc_bn_act_pool_bwd(const float* y, int64_t ldy, int64_t M, int C, const int64_t* batch_or_null, const int32_t* cloud_ptr, int B,
+extern "C" int dc_bn_act_pool_bwd(const float* y, int64_t ldy, int64_t M, int C, const int32_t* cloud_ptr, int B,
                                   const int32_t* arg, const float* d_max_or_null, int64_t ld_dmax, const float* d_mean_or_null, int64_t ld_dmean,
                                   const float* mean, const float* invstd, const float* gamma_or_null, const float* beta_or_null, float slope,
                                   float* d_gamma, float* d_beta, float* dy, int64_t ld_dy, void* ws, size_t ws_bytes, void* stream) {
     DC_REQUIRE(M >= 1 && C >= 1 && B >= 1, "dc_bn_act_pool_bwd: empty input");
-    DC_REQUIRE(batch_or_null != nullptr || B == 1, "dc_bn_act_pool_bwd: batch vector needed for more than one cloud");
+    DC_REQUIRE(M <= 0x7fffffffLL, "dc_bn_act_pool_bwd: too many rows");
     DC_REQUIRE(d_max_or_null == nullptr || arg != nullptr, "dc_bn_act_pool_bwd: d_max without the argmax rows");
     DC_REQUIRE(C % 4 == 0 && ldy % 4 == 0 && ld_dy % 4 == 0 && ld_dmax % 4 == 0 && ld_dmean % 4 == 0 &&
                all_aligned16(y, dy, mean, invstd, gamma_or_null, beta_or_null) && all_aligned16(d_gamma, d_beta, d_max_or_null, d_mean_or_null, arg),
                "dc_bn_act_pool_bwd: needs C %% 4 == 0 and 16-byte aligned rows");
     DC_REQUIRE(ws_bytes >= dc_colreduce_ws_bytes(C), "dc_bn_act_pool_bwd: workspace too small");
     cudaStream_t st = (cudaStream_t)stream;
-    ColLayout L = col_layout(M, C);
-    dim3 grid(L.chunks, L.col_blocks);
+    const int col_blocks = dc_ceil_div(C, 128);
+    // about four CTAs per SM in total, at least 32 rows per thread
+    int splits = dc_ceil_div((long long)dc_sm_count() * 4, (long long)col_blocks * B);
+    const int by_rows = (int)dc_ceil_div(dc_ceil_div(M, B), 8 * 32);
+    if (splits > by_rows) splits = by_rows;
+    if (splits < 1) splits = 1;
+    long long units = (long long)B * splits;
+    const int chunks = (int)(units < RED_MAX_CHUNKS ? units : RED_MAX_CHUNKS);
     double* partial = (double*)ws;
-    PoolGrad pg = {(const long long*)batch_or_null, cloud_ptr, arg, d_max_or_null, ld_dmax, d_mean_or_null, ld_dmean, C};
-    PoolBnBwdVal f = {y, ldy, pg, mean, invstd, gamma_or_null, beta_or_null, slope};
-    col_reduce_kernel<2><<<grid, RED_T, 0, st>>>(f, M, C, L.col_lanes, L.rows_per_chunk, partial);
-    sum2_finalize_kernel<<<dc_ceil_div(C, FIN_COLS), FIN_T, 0, st>>>(partial, L.chunks, C, d_beta, d_gamma);
-    bn_act_pool_bwd_vec4_kernel<<<elementwise_grid(M * C / 4), 256, 0, st>>>(y, ldy, pg, M, C / 4, mean, invstd, gamma_or_null, beta_or_null,
-                                                                         slope, d_beta, d_gamma, dy, ld_dy);
+    PoolGrad pg = {cloud_ptr, arg, d_max_or_null, ld_dmax, d_mean_or_null, ld_dmean, C};
+    pool_bn_bwd_reduce_kernel<<<dim3(chunks, col_blocks), 256, 0, st>>>(y, ldy, pg, B, splits, C, mean, invstd, gamma_or_null, beta_or_null, slope, partial);
+    sum2_finalize_kernel<<<dc_ceil_div(C, FIN_COLS), FIN_T, 0, st>>>(partial, chunks, C, d_beta, d_gamma);
+    DC_REQUIRE(B <= 65535, "dc_bn_act_pool_bwd: more than 65535 clouds");
+    pool_bn_bwd_apply_kernel<<<dim3(splits, col_blocks, B), 256, 0, st>>>(y, ldy, pg, M, C, mean, invstd, gamma_or_null, beta_or_null, slope,
+                                                                        d_beta, d_gamma, dy, ld_dy);
     return dc_check_launch_n("dc_bn_act_pool_bwd", 3);
 }
 

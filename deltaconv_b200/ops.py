@@ -874,7 +874,7 @@ class _LinearBNActPool(torch.autograd.Function):
     gradient are never written (dc_bn_act_pool_fwd / dc_bn_act_pool_bwd)."""
 
     @staticmethod
-    def forward(ctx, x, weight, gamma, beta, bn, slope, batch, cloud_ptr, B, mode):
+    def forward(ctx, x, weight, gamma, beta, bn, slope, cloud_ptr, B, mode):
         x, ldx = _mat(x, 'input')
         weight, ldw = _mat(weight, 'weight')
         if x.size(1) != weight.size(1):
@@ -900,13 +900,13 @@ class _LinearBNActPool(torch.autograd.Function):
         mean_p = (out.data_ptr() + (4 * C if mode == 'maxmean' else 0)) if want_mean else None
         call('dc_bn_act_pool_fwd', ptr(y), C, ptr(cloud_ptr), B, C, ptr(mean), ptr(invstd), ptr(gamma), ptr(beta), float(slope),
              ptr(out) if want_max else None, width, mean_p, width, ptr(arg))
-        ctx.save_for_backward(x, weight, y, mean, invstd, gamma, beta, batch, cloud_ptr, arg)
+        ctx.save_for_backward(x, weight, y, mean, invstd, gamma, beta, cloud_ptr, arg)
         ctx.slope, ctx.mode, ctx.B = slope, mode, B
         return out
 
     @staticmethod
     def backward(ctx, dout):
-        x, weight, y, mean, invstd, gamma, beta, batch, cloud_ptr, arg = ctx.saved_tensors
+        x, weight, y, mean, invstd, gamma, beta, cloud_ptr, arg = ctx.saved_tensors
         x, ldx = _mat(x)
         weight, ldw = _mat(weight)
         dout, ld = _mat(dout, 'grad_output')
@@ -919,7 +919,7 @@ class _LinearBNActPool(torch.autograd.Function):
         dmean = (dout.data_ptr() + (4 * C if mode == 'maxmean' else 0)) if mode in ('mean', 'maxmean') else None
         nb = query('dc_colreduce_ws_bytes', C)
         ws = workspace(nb, dev)
-        call('dc_bn_act_pool_bwd', ptr(y), C, M, C, ptr(batch), ptr(cloud_ptr), ctx.B, ptr(arg), dmax, ld, dmean, ld,
+        call('dc_bn_act_pool_bwd', ptr(y), C, M, C, ptr(cloud_ptr), ctx.B, ptr(arg), dmax, ld, dmean, ld,
              ptr(mean), ptr(invstd), ptr(gamma), ptr(beta), float(ctx.slope), ptr(dgamma), ptr(dbeta), ptr(dy), C, ptr(ws), nb)
         dx = dw = None
         if ctx.needs_input_grad[0]:
@@ -930,16 +930,14 @@ class _LinearBNActPool(torch.autograd.Function):
             dw = torch.empty(C, K, dtype=_F32, device=dev)
             ws, nb = _gemm_ws(C, K, M, dev)
             call('dc_linear_bwd_weight', ptr(dy), C, ptr(x), ldx, M, K, C, ptr(dw), K, ptr(ws), nb)
-        return (dx, dw, dgamma if gamma is not None else None, dbeta if beta is not None else None) + (None,) * 6
+        return (dx, dw, dgamma if gamma is not None else None, dbeta if beta is not None else None) + (None,) * 5
 
 
 def linear_bn_act_pool(x, weight, bn, slope, batch, mode, size=None):
     """pool(act(BatchNorm1d(x @ weight.T)), batch) with batch statistics; mode 'max' | 'mean' | 'maxmean'.
     Needs out_features % 4 == 0 (see `pool_fusable`)."""
     cp, B = cloud_ptr_of(batch, x.size(0), x.device, size)
-    if batch is not None:
-        batch = batch.contiguous()
-    return _LinearBNActPool.apply(x, weight, bn.weight, bn.bias, bn, float(slope), batch, cp, B, mode)
+    return _LinearBNActPool.apply(x, weight, bn.weight, bn.bias, bn, float(slope), cp, B, mode)
 
 
 def pool_fusable(bn, out_features, bias, slope):

@@ -199,11 +199,11 @@ int dc_pool_bwd(const int32_t* cloud_ptr, int B, int N, int C, const int32_t* ar
  * deltanet_segmentation.py:58-61: `lin_embedding`/`lin_global` -> global_max_pool / global_mean_pool): the pooled value is
  * leaky_relu(gamma*(y-mean)*invstd+beta) evaluated while y is read, and the backward rebuilds the pooled gradient of each row from
  * the [B,C] gradients, so neither the [N,C] activation nor its gradient is stored.  Training-mode statistics (dc_bn_stats).
- * batch = the PyG batch vector (int64 [N], sorted), NULL when B == 1.  bwd needs C % 4 == 0. */
+ * bwd needs C % 4 == 0 and B <= 65535. */
 int dc_bn_act_pool_fwd(const float* y, int64_t ldy, const int32_t* cloud_ptr, int B, int C, const float* mean, const float* invstd,
                        const float* gamma_or_null, const float* beta_or_null, float slope, float* out_max_or_null, int64_t ld_max,
                        float* out_mean_or_null, int64_t ld_mean, int32_t* arg, void* stream);
-int dc_bn_act_pool_bwd(const float* y, int64_t ldy, int64_t M, int C, const int64_t* batch_or_null, const int32_t* cloud_ptr, int B,
+int dc_bn_act_pool_bwd(const float* y, int64_t ldy, int64_t M, int C, const int32_t* cloud_ptr, int B,
                        const int32_t* arg, const float* d_max_or_null, int64_t ld_dmax, const float* d_mean_or_null, int64_t ld_dmean,
                        const float* mean, const float* invstd, const float* gamma_or_null, const float* beta_or_null, float slope,
                        float* d_gamma, float* d_beta, float* dy, int64_t ld_dy, void* ws, size_t ws_bytes, void* stream);
