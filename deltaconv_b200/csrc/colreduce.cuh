@@ -91,10 +91,25 @@ __device__ __forceinline__ bool finalize_sums(const double* __restrict__ partial
     double acc[NV];
 #pragma unroll
     for (int v = 0; v < NV; ++v) acc[v] = 0.0;
-    if (c < C)
-        for (int q = lane; q < chunks; q += 32)
+    if (c < C) {
+        int q = lane;
+        // four chunks in flight per lane: the loads of one round are independent, only the adds are ordered
+        for (; q + 96 < chunks; q += 128) {
+            double t0[NV], t1[NV], t2[NV], t3[NV];
+#pragma unroll
+            for (int v = 0; v < NV; ++v) {
+                t0[v] = partial[((size_t)q * NV + v) * C + c];
+                t1[v] = partial[((size_t)(q + 32) * NV + v) * C + c];
+                t2[v] = partial[((size_t)(q + 64) * NV + v) * C + c];
+                t3[v] = partial[((size_t)(q + 96) * NV + v) * C + c];
+            }
+#pragma unroll
+            for (int v = 0; v < NV; ++v) acc[v] += (t0[v] + t1[v]) + (t2[v] + t3[v]);
+        }
+        for (; q < chunks; q += 32)
 #pragma unroll
             for (int v = 0; v < NV; ++v) acc[v] += partial[((size_t)q * NV + v) * C + c];
+    }
 #pragma unroll
     for (int v = 0; v < NV; ++v) out[v] = warp_sum(acc[v]);
     return lane == 0 && c < C;

@@ -379,15 +379,50 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
     if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
 }
 
+// Split-K partials [splits][M*N] -> C (+ bias).  Fixed summation order for a given (shape, split count): deterministic.
+// One thread per output; the loads of a round are independent so that four of them are in flight.
 __global__ void tc_splitk_reduce_kernel(const float* __restrict__ partial, int splits, long long MN, int N, float* __restrict__ C,
                                         long long ldc, const float* __restrict__ bias) {
     long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
     if (t >= MN) return;
     float s = 0.f;
-    for (int z = 0; z < splits; ++z) s += partial[(size_t)z * MN + t];          // fixed order: deterministic
+    int z = 0;
+    for (; z + 3 < splits; z += 4) {
+        const float a = partial[(size_t)z * MN + t], b = partial[(size_t)(z + 1) * MN + t];
+        const float c = partial[(size_t)(z + 2) * MN + t], d = partial[(size_t)(z + 3) * MN + t];
+        s += (a + b) + (c + d);
+    }
+    for (; z < splits; ++z) s += partial[(size_t)z * MN + t];
     long long i = t / N; int j = (int)(t - i * N);
     if (bias) s += __ldg(bias + j);
     C[i * ldc + j] = s;
+}
+
+// Many splits of a small output (the weight gradients of the narrow layers): 8 threads share one output, each sums every 8th
+// partial (four loads in flight), the 8 lane sums are combined in a fixed order through shared memory.
+__global__ void __launch_bounds__(256) tc_splitk_reduce_wide_kernel(const float* __restrict__ partial, int splits, long long MN, int N,
+                                                                    float* __restrict__ C, long long ldc, const float* __restrict__ bias) {
+    __shared__ float sh[8][32];
+    const int lane = threadIdx.x & 31, zl = threadIdx.x >> 5;
+    const long long t = blockIdx.x * 32LL + lane;
+    float s = 0.f;
+    if (t < MN) {
+        int z = zl;
+        for (; z + 24 < splits; z += 32) {
+            const float a = partial[(size_t)z * MN + t], b = partial[(size_t)(z + 8) * MN + t];
+            const float c = partial[(size_t)(z + 16) * MN + t], d = partial[(size_t)(z + 24) * MN + t];
+            s += (a + b) + (c + d);
+        }
+        for (; z < splits; z += 8) s += partial[(size_t)z * MN + t];
+    }
+    sh[zl][lane] = s;
+    __syncthreads();
+    if (zl == 0 && t < MN) {
+        float r = ((sh[0][lane] + sh[1][lane]) + (sh[2][lane] + sh[3][lane])) + ((sh[4][lane] + sh[5][lane]) + (sh[6][lane] + sh[7][lane]));
+        long long i = t / N; int j = (int)(t - i * N);
+        if (bias) r += __ldg(bias + j);
+        C[i * ldc + j] = r;
+    }
 }
 
 // ---- host side ------------------------------------------------------------------------------------
@@ -480,6 +515,31 @@ extern "C" int dc_set_gemm_no_ts(int v) { g_tc_no_ts = v; return DC_OK; }
 // tuning switch: 1 (default) = do not rewrite the hi part of B in shared memory (the MMA truncates fp32 operands to tf32), 0 = rewrite
 extern "C" int dc_set_gemm_keep_raw_hi(int v) { g_tc_keep_raw_hi = v; return DC_OK; }
 
+// Split-K factor for an M x N output with reduction K.  Cost model in units of one k-block (128 x BN x 32) of main loop: the
+// persistent grid runs ceil(units / SMs) waves of (k-blocks per split + pipeline fill), the reduce pass costs a launch plus a
+// term per split.  Picks the cheapest factor whose partials fit the workspace; the same function sizes the workspace.
+int tc_choose_splits(long long M, int N, long long K, size_t ws_cap) {
+    const int BN = N <= 64 ? 64 : 128;
+    const long long total_kb = (K + TC_BK - 1) / TC_BK;
+    const long long tiles = ((M + TC_BM - 1) / TC_BM) * ((N + BN - 1) / BN);
+    const long long sms = dc_sm_count();
+    if (total_kb < 16 || tiles >= 2 * sms) return 1;
+    long long max_s = total_kb / 8;
+    if (max_s > 256) max_s = 256;
+    const double per_split = 0.2 + (double)M * N / 300000.0;
+    double best_cost = 1e300;
+    int best = 1;
+    for (long long sp = 1; sp <= max_s; ++sp) {
+        if (sp > 1 && (size_t)sp * M * N * sizeof(float) > ws_cap) break;
+        const long long kb = (total_kb + sp - 1) / sp;
+        const long long eff = (total_kb + kb - 1) / kb;              // splits actually produced
+        const long long waves = (tiles * eff + sms - 1) / sms;
+        const double cost = (double)waves * ((double)kb + 5.0) + (eff > 1 ? 8.0 + (double)eff * per_split : 0.0);
+        if (cost < best_cost - 1e-9) { best_cost = cost; best = (int)sp; }
+    }
+    return best;
+}
+
 // Generic tensor-core product  C[M,N] = op(A) op(B)^T (+bias).  a_mn / b_mn select the operand layout:
 //   a_mn = 0: A is [M, K] with K contiguous (lda = row pitch);  a_mn = 1: A is stored [K, M] with M contiguous.
 //   b_mn = 0: B is [N, K] with K contiguous;                    b_mn = 1: B is stored [K, N] with N contiguous.
@@ -500,14 +560,7 @@ int dc_tc_gemm(const float* A, long long lda, int a_mn, const float* B, long lon
     if (!ok) return 1;
     const int total_kb = (int)((K + TC_BK - 1) / TC_BK);
     const long long tiles = ((M + TC_BM - 1) / TC_BM) * ((N + BN - 1) / BN);
-    int splits = 1;
-    const long long target = 2LL * dc_sm_count();
-    if (tiles < target && total_kb >= 8) {
-        long long s = (target + tiles - 1) / tiles;
-        if (s > total_kb / 4) s = total_kb / 4;
-        while (s > 1 && (size_t)s * M * N * sizeof(float) > ws_bytes) --s;
-        splits = (int)(s < 1 ? 1 : s);
-    }
+    int splits = tc_choose_splits(M, N, K, ws_bytes);
     TcArgs g = {};
     g.C = C; g.ldc = ldc; g.bias = bias; g.M = (int)M; g.N = N; g.K = (int)K;
     g.kb_per_split = (total_kb + splits - 1) / splits;
@@ -525,7 +578,10 @@ int dc_tc_gemm(const float* A, long long lda, int a_mn, const float* B, long lon
     *launches = 1;
     if (splits > 1) {
         const long long MN = M * N;
-        tc_splitk_reduce_kernel<<<dc_ceil_div(MN, 256), 256, 0, st>>>(g.partial, splits, MN, N, C, ldc, bias);
+        if (splits >= 16 && MN <= (1LL << 20))
+            tc_splitk_reduce_wide_kernel<<<dc_ceil_div(MN, 32), 256, 0, st>>>(g.partial, splits, MN, N, C, ldc, bias);
+        else
+            tc_splitk_reduce_kernel<<<dc_ceil_div(MN, 256), 256, 0, st>>>(g.partial, splits, MN, N, C, ldc, bias);
         *launches = 2;
     }
     return DC_OK;
@@ -533,14 +589,9 @@ int dc_tc_gemm(const float* A, long long lda, int a_mn, const float* B, long lon
 
 // workspace for the split-K partials of a product with output M x N and reduction K
 size_t dc_tc_ws_bytes(long long M, long long N, long long K) {
-    const int BN = N <= 64 ? 64 : 128;
-    const long long total_kb = (K + TC_BK - 1) / TC_BK;
-    const long long tiles = ((M + TC_BM - 1) / TC_BM) * ((N + BN - 1) / BN);
-    const long long target = 2LL * dc_sm_count();
-    if (tiles >= target || total_kb < 8) return 0;
-    long long s = (target + tiles - 1) / tiles;
-    if (s > total_kb / 4) s = total_kb / 4;
-    return s > 1 ? (size_t)s * M * N * sizeof(float) : 0;
+    if (M < 1 || N < 1 || K < 1 || N > 2147483647LL) return 0;
+    const int sp = tc_choose_splits(M, (int)N, K, (size_t)-1);
+    return sp > 1 ? (size_t)sp * M * N * sizeof(float) : 0;
 }
 
 // Raw access to the tensor-core product for tests and experiments (no SIMT fallback: returns 1 when the
