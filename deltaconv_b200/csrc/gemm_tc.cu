@@ -20,6 +20,7 @@
 // two TMEM accumulators so the epilogue of one tile overlaps the main loop of the next.
 #include "common.cuh"
 #include <cuda.h>
+#include <cstring>
 
 namespace {
 
@@ -35,6 +36,7 @@ struct TcArgs {
     int kb_per_split;       // k-blocks per grid.z slice
     float* partial;         // [splits][M][N] when split-K
     int keep_raw_hi;        // 1: leave the raw fp32 tile as the 'hi' B operand (valid iff the MMA truncates fp32 -> tf32)
+    int tma_store;          // 1: the epilogue stages 32 x 32 blocks in shared memory and writes them with TMA (tmC is valid)
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -105,6 +107,23 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32
                    "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]), "r"(r[28]), "r"(r[29]),
                    "r"(r[30]), "r"(r[31]) : "memory");
 }
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+                 "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+                   "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]),
+                   "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]),
+                   "=r"(r[30]), "=r"(r[31])
+                 : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+// TMA store of one [32 rows][128 B] block (128-byte swizzled in shared memory) to coordinates (c0, c1, c2) of a 3-D tensor;
+// elements outside the tensor are not written, which is what clips the ragged M / N edges.
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, uint32_t src, int c0, int c1, int c2) {
+    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+                 ::"l"(map), "r"(src), "r"(c0), "r"(c1), "r"(c2) : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
@@ -114,7 +133,8 @@ __device__ __forceinline__ void umma_commit(uint32_t bar) {
 // main loop of tile t+1.
 template <int BN, bool A_MN, bool B_MN, bool SPLIT3, int STAGES, bool TS>
 __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA,
-                                                                const __grid_constant__ CUtensorMap tmB, TcArgs g) {
+                                                                const __grid_constant__ CUtensorMap tmB,
+                                                                const __grid_constant__ CUtensorMap tmC, TcArgs g) {
     constexpr uint32_t A_BYTES = TC_BM * 128, B_BYTES = BN * 128;
     static_assert(!TS || SPLIT3, "A-from-TMEM is the 3xTF32 path");
     // TS: the split A operand lives in tensor memory, so shared memory holds raw A (16 KB) + B hi/lo
@@ -131,7 +151,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
     extern __shared__ unsigned char smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;          // swizzle atoms are 1024-byte aligned
     unsigned char* base_ptr = smem_raw + (base - smem_u32(smem_raw));
-    const uint32_t bar_base = base + STAGES * STAGE_BYTES;
+    constexpr uint32_t EPI_BYTES = 4 * 2 * 4096;                  // per epilogue warp: two 32 x 32 fp32 staging blocks
+    const uint32_t epi_base = base + STAGES * STAGE_BYTES;
+    const uint32_t bar_base = epi_base + EPI_BYTES;
     auto full_bar = [&](int s) { return bar_base + 8u * s; };
     auto empty_bar = [&](int s) { return bar_base + 8u * (TC_MAX_STAGES + s); };
     auto conv_bar = [&](int s) { return bar_base + 8u * (2 * TC_MAX_STAGES + s); };
@@ -325,7 +347,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
     } else {
         // ===================== epilogue: TMEM -> registers -> HBM =====================
         const int q = warp & 3;                                   // TMEM lane quarter this warp may read
-        uint32_t tcount = 0;
+        uint32_t tcount = 0, epi_it = 0;
         for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tcount) {
             int m0, n0, kb_begin, nkb;
             decode(tile, m0, n0, kb_begin, nkb);
@@ -337,6 +359,35 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
             float* out = g.partial ? g.partial + (size_t)z * g.M * g.N : g.C;
             const long long ldo = g.partial ? g.N : g.ldc;
             const bool vec_ok = (ldo % 4 == 0) && ((reinterpret_cast<uintptr_t>(out) & 15u) == 0);
+            if (g.tma_store) {
+                // Row-per-lane stores touch 32 different 128-byte lines per instruction (measured: a fifth of the L1 data pipe
+                // of this kernel).  Instead each warp stages a 32 x 32 block in shared memory (its row as 8 swizzled 16-byte
+                // chunks: conflict-free) and one lane hands the block to TMA, which writes full lines and clips the edges.
+#pragma unroll 1
+                for (int c0 = 0; c0 < BN; c0 += 32) {
+                    if (n0 + c0 >= g.N) break;                        // warp-uniform
+                    uint32_t r[32];
+                    tmem_ld32(tmem_base + acc * BN + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, r);
+                    if (!g.partial && g.bias) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j)
+                            if (n0 + c0 + j < g.N) r[j] = __float_as_uint(__uint_as_float(r[j]) + __ldg(g.bias + n0 + c0 + j));
+                    }
+                    const uint32_t buf = epi_base + (uint32_t)q * 8192u + (epi_it & 1u) * 4096u;
+                    // the store that read this buffer two blocks ago must have finished reading it
+                    if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+                    __syncwarp();
+                    float4* dstrow = reinterpret_cast<float4*>(base_ptr + (buf - base) + lane * 128);
+#pragma unroll
+                    for (int c = 0; c < 8; ++c)
+                        dstrow[c ^ (lane & 7)] = make_float4(__uint_as_float(r[4 * c]), __uint_as_float(r[4 * c + 1]),
+                                                             __uint_as_float(r[4 * c + 2]), __uint_as_float(r[4 * c + 3]));
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    __syncwarp();
+                    if (lane == 0) tma_store_3d(&tmC, buf, n0 + c0, m0 + q * 32, z);
+                    ++epi_it;
+                }
+            } else {
 #pragma unroll 1
             for (int c0 = 0; c0 < BN; c0 += 16) {
                 if (n0 + c0 >= g.N) break;                            // warp-uniform
@@ -369,10 +420,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
                     }
                 }
             }
+            }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(acc_empty_bar(acc));           // this warp's quarter of the accumulator is free
         }
+        if (g.tma_store && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");     // staging buffers stay valid until read
     }
     tc_fence_before();
     __syncthreads();
@@ -458,6 +511,19 @@ bool make_map(CUtensorMap* map, const float* ptr, long long inner, long long out
               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// 3-D fp32 tensor map for the output (N x M x Z, row pitch ld, plane pitch `plane` elements), 32 x 32 boxes, 128-byte swizzle
+bool make_out_map(CUtensorMap* map, float* ptr, long long N, long long M, long long Z, long long ld, long long plane) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn || (ld % 4) || (plane % 4) || (reinterpret_cast<uintptr_t>(ptr) & 15u)) return false;
+    cuuint64_t dims[3] = {(cuuint64_t)N, (cuuint64_t)M, (cuuint64_t)Z};
+    cuuint64_t strides[2] = {(cuuint64_t)ld * 4, (cuuint64_t)plane * 4};
+    cuuint32_t box[3] = {32u, 32u, 1u};
+    cuuint32_t estr[3] = {1u, 1u, 1u};
+    return fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void*)ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+int g_tc_tma_store = 1;     // epilogue through shared memory + TMA stores (0 = row-per-lane direct stores)
 int g_tc_keep_raw_hi = 1;   // B_hi is the raw fp32 tile: the MMA truncates fp32 -> tf32 on read (measured bit-identical to an explicit
                             // hi = x & 0xffffe000 rewrite, dc_set_gemm_keep_raw_hi(0) restores the rewrite)
 int g_tc_no_ts = 0;      // experiment switch: 1 = keep the split A operand in shared memory (SS MMAs)
@@ -470,34 +536,34 @@ template <int BN, bool SPLIT3, bool TS> struct TcStages {
 };
 
 template <int BN, bool A_MN, bool B_MN, bool SPLIT3>
-int launch_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const TcArgs& g, long long num_tiles, cudaStream_t st) {
+int launch_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const TcArgs& g, long long num_tiles, cudaStream_t st) {
     constexpr bool TS = SPLIT3;                // the split A operand lives in tensor memory instead of shared memory
     constexpr int STAGES = TcStages<BN, SPLIT3, TS>::value;
     static_assert(STAGES >= 2, "tile too large for shared memory");
-    const size_t smem = (size_t)STAGES * TcStages<BN, SPLIT3, TS>::per_stage + 1024 /*alignment*/ + 8 * (3 * TC_MAX_STAGES + 4) + 16;
+    const size_t smem = (size_t)STAGES * TcStages<BN, SPLIT3, TS>::per_stage + 32768 /*epilogue staging*/ + 1024 /*alignment*/ + 8 * (3 * TC_MAX_STAGES + 4) + 16;
     if (g_tc_no_ts && TS) {
         constexpr int ST2 = TcStages<BN, SPLIT3, false>::value;
-        const size_t smem2 = (size_t)ST2 * TcStages<BN, SPLIT3, false>::per_stage + 1024 + 8 * (3 * TC_MAX_STAGES + 4) + 16;
+        const size_t smem2 = (size_t)ST2 * TcStages<BN, SPLIT3, false>::per_stage + 32768 + 1024 + 8 * (3 * TC_MAX_STAGES + 4) + 16;
         DC_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<BN, A_MN, B_MN, SPLIT3, ST2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
         const long long sms2 = dc_sm_count();
-        tc_gemm_kernel<BN, A_MN, B_MN, SPLIT3, ST2, false><<<(unsigned)(num_tiles < sms2 ? num_tiles : sms2), TC_THREADS, smem2, st>>>(tmA, tmB, g);
+        tc_gemm_kernel<BN, A_MN, B_MN, SPLIT3, ST2, false><<<(unsigned)(num_tiles < sms2 ? num_tiles : sms2), TC_THREADS, smem2, st>>>(tmA, tmB, tmC, g);
         return DC_OK;
     }
     DC_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<BN, A_MN, B_MN, SPLIT3, STAGES, TS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const long long sms = dc_sm_count();
     const unsigned grid = (unsigned)(num_tiles < sms ? num_tiles : sms);       // persistent: one CTA per SM
-    tc_gemm_kernel<BN, A_MN, B_MN, SPLIT3, STAGES, TS><<<grid, TC_THREADS, smem, st>>>(tmA, tmB, g);
+    tc_gemm_kernel<BN, A_MN, B_MN, SPLIT3, STAGES, TS><<<grid, TC_THREADS, smem, st>>>(tmA, tmB, tmC, g);
     return DC_OK;
 }
 
 template <bool A_MN, bool B_MN>
-int dispatch_tc(int BN, bool split3, const CUtensorMap& a, const CUtensorMap& b, const TcArgs& g, long long tiles, cudaStream_t st) {
+int dispatch_tc(int BN, bool split3, const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& c, const TcArgs& g, long long tiles, cudaStream_t st) {
     if (split3) {
-        if (BN == 64) return launch_tc<64, A_MN, B_MN, true>(a, b, g, tiles, st);
-        return launch_tc<128, A_MN, B_MN, true>(a, b, g, tiles, st);
+        if (BN == 64) return launch_tc<64, A_MN, B_MN, true>(a, b, c, g, tiles, st);
+        return launch_tc<128, A_MN, B_MN, true>(a, b, c, g, tiles, st);
     }
-    if (BN == 64) return launch_tc<64, A_MN, B_MN, false>(a, b, g, tiles, st);
-    return launch_tc<128, A_MN, B_MN, false>(a, b, g, tiles, st);
+    if (BN == 64) return launch_tc<64, A_MN, B_MN, false>(a, b, c, g, tiles, st);
+    return launch_tc<128, A_MN, B_MN, false>(a, b, c, g, tiles, st);
 }
 
 }  // namespace
@@ -514,6 +580,8 @@ extern "C" int dc_get_gemm_mode(void) { return g_tc_mode; }
 extern "C" int dc_set_gemm_no_ts(int v) { g_tc_no_ts = v; return DC_OK; }
 // tuning switch: 1 (default) = do not rewrite the hi part of B in shared memory (the MMA truncates fp32 operands to tf32), 0 = rewrite
 extern "C" int dc_set_gemm_keep_raw_hi(int v) { g_tc_keep_raw_hi = v; return DC_OK; }
+// tuning switch: 1 (default) = epilogue through shared memory and TMA stores, 0 = row-per-lane direct stores
+extern "C" int dc_set_gemm_tma_store(int v) { g_tc_tma_store = v; return DC_OK; }
 
 // Split-K factor for an M x N output with reduction K.  Cost model in units of one k-block (128 x BN x 32) of main loop: the
 // persistent grid runs ceil(units / SMs) waves of (k-blocks per split + pipeline fill), the reduce pass costs a launch plus a
@@ -567,12 +635,16 @@ int dc_tc_gemm(const float* A, long long lda, int a_mn, const float* B, long lon
     splits = (total_kb + g.kb_per_split - 1) / g.kb_per_split;
     g.partial = splits > 1 ? (float*)ws : nullptr;
     g.keep_raw_hi = g_tc_keep_raw_hi;
+    CUtensorMap tmC;
+    memset(&tmC, 0, sizeof(tmC));
+    g.tma_store = g_tc_tma_store && (g.partial ? make_out_map(&tmC, g.partial, N, M, splits, N, M * (long long)N)
+                                               : make_out_map(&tmC, C, N, M, 1, ldc, M * ldc)) ? 1 : 0;
     const long long num_tiles = tiles * splits;
     const bool split3 = g_tc_mode == 3;
     int rc;
-    if (!a_mn && !b_mn) rc = dispatch_tc<false, false>(BN, split3, tmA, tmB, g, num_tiles, st);
-    else if (!a_mn && b_mn) rc = dispatch_tc<false, true>(BN, split3, tmA, tmB, g, num_tiles, st);
-    else if (a_mn && b_mn) rc = dispatch_tc<true, true>(BN, split3, tmA, tmB, g, num_tiles, st);
+    if (!a_mn && !b_mn) rc = dispatch_tc<false, false>(BN, split3, tmA, tmB, tmC, g, num_tiles, st);
+    else if (!a_mn && b_mn) rc = dispatch_tc<false, true>(BN, split3, tmA, tmB, tmC, g, num_tiles, st);
+    else if (a_mn && b_mn) rc = dispatch_tc<true, true>(BN, split3, tmA, tmB, tmC, g, num_tiles, st);
     else return 1;
     if (rc) return rc < 0 ? rc : -rc;
     *launches = 1;

@@ -220,6 +220,8 @@ int dc_get_gemm_mode(void);
 /* tuning switch: 1 = keep the split A operand in shared memory (SS MMAs) instead of tensor memory (default 0) */
 int dc_set_gemm_no_ts(int v);
 int dc_set_gemm_keep_raw_hi(int v);
+/* tuning switch: 1 (default) = GEMM epilogue through shared memory and TMA stores, 0 = row-per-lane direct stores */
+int dc_set_gemm_tma_store(int v);
 size_t dc_gemm_ws_bytes(int64_t M, int64_t N, int64_t K);
 /* The tensor-core product itself, C[M,N] = op(A) op(B)^T: a_mn/b_mn = 0 when the reduction index is contiguous
  * ([M,K] / [N,K] storage), 1 when the M / N index is contiguous ([K,M] / [K,N] storage).  Returns 1 if the shape is
