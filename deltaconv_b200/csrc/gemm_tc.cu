@@ -37,6 +37,7 @@ struct TcArgs {
     float* partial;         // [splits][M][N] when split-K
     int keep_raw_hi;        // 1: leave the raw fp32 tile as the 'hi' B operand (valid iff the MMA truncates fp32 -> tf32)
     int tma_store;          // 1: the epilogue stages 32 x 32 blocks in shared memory and writes them with TMA (tmC is valid)
+    long long* trace;       // debug: [2 CTAs][8 events][256 k-blocks] clock64 stamps of CTA 0 and its peer (pair kernel), or null
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -65,6 +66,19 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
             else if (clock64() - t0 > 4000000000LL) __trap();
         }
     } while (!done);
+}
+// One non-blocking probe of a barrier phase.  mbarrier operations travel through the same queue as the shared-memory loads
+// and stores of the converter / epilogue warps (measured: ~270 cycles for a probe of a phase that completed long ago), so the
+// MMA-issuing thread probes the NEXT k-block's barrier before it issues the current k-block's MMAs and reads the answer after.
+__device__ __forceinline__ uint32_t mbar_try(uint32_t bar, uint32_t parity) {
+    uint32_t done;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}" : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+    return done;
 }
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
     asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
@@ -223,8 +237,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
             }
         }
     } else if (warp == 1) {
-        // ===================== MMA issuer =====================
+        // ===================== MMA issuer (one thread: every instruction it executes besides the MMAs is tensor idle time) =====================
         uint32_t it = 0, tcount = 0;
+        if (lane == 0)
         for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tcount) {
             int m0, n0, kb_begin, nkb;
             decode(tile, m0, n0, kb_begin, nkb);
@@ -237,7 +252,18 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
                 const uint32_t ph = (it / STAGES) & 1;
                 mbar_wait(SPLIT3 ? conv_bar(s) : full_bar(s), ph);
                 tc_fence_after();
-                if (lane == 0) {
+                {
+                    if (TS)
+                        for (int rep = 0; rep < (g.keep_raw_hi >> 8); ++rep)      // debug: extra copies of the MMAs (measures the tensor rate)
+#pragma unroll
+                            for (int kk = 0; kk < TC_BK / 8; ++kk) {
+                                const uint32_t b_off = B_MN ? kk * 1024u : kk * 32u;
+                                const uint64_t db = umma_desc(stage_b(s) + b_off, B_MN ? CHUNK_BYTES : 16u, B_MN ? 512u : 1024u, B_MN ? 1u : 2u);
+                                const uint32_t ta_hi = tmem_base + TMEM_A0 + (uint32_t)s * 64u + (uint32_t)kk * 8u;
+                                umma_tf32_ts(tmem_acc, ta_hi, db, IDESC, 1u);
+                                umma_tf32_ts(tmem_acc, ta_hi + 32u, db, IDESC, 1u);
+                                umma_tf32_ts(tmem_acc, ta_hi, db, IDESC, 1u);
+                            }
 #pragma unroll
                     for (int kk = 0; kk < TC_BK / 8; ++kk) {          // UMMA_K = 8 for tf32
                         // K-major: +32 B inside the swizzle span; MN-major: next 8-row group (+1024 B)
@@ -268,11 +294,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
                     umma_commit(empty_bar(s));                        // frees the stage when the MMAs have read it
                     if (kb == nkb - 1) umma_commit(acc_full_bar(acc)); // accumulator complete
                 }
-                __syncwarp();
             }
         }
     } else if (warp < 6) {
         // ===================== converters (3xTF32 split of every landed stage) =====================
+        // (a second group of converter warps on alternate k-blocks was measured neutral here: at M = 128 per CTA the
+        // tensor pipe, ~110 cycles per MMA, paces this kernel)
         if (SPLIT3) {
             const int t = threadIdx.x - 64;                           // 0..127
             uint32_t it = 0;
@@ -432,6 +459,367 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
     if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// CTA-pair version of the 3xTF32 kernel (cta_group::2, UMMA_M = 256).  Measured on the single-CTA kernel above (ncu, large
+// layers): the L1/shared-memory data pipe is ~85 % busy — converter loads/stores 36 %, tensor-core reads of B 27 %, epilogue
+// stores 21 % — while the tensor pipe waits.  A pair of CTAs on the two SMs of a TPC computes a 256 x BN tile: each CTA
+// holds its own 128 rows of A (tensor memory) and only HALF of the B tile (BN/2 rows), so per flop the converter traffic
+// for B, the tensor-core reads of B and the L2 traffic for B are all halved.  Rank 0 issues the MMAs for both CTAs;
+// stage release and accumulator-ready are multicast commits; "operands converted" and "accumulator drained" of the peer
+// reach rank 0 as remote mbarrier arrivals.
+__device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// arrive on the barrier at the same shared-memory offset in CTA `cta` of the cluster (default .release.cta — the form of
+// CUTLASS's ClusterBarrier::arrive; measured: .release.cluster costs the arriving thread ~1200 cycles more per arrive)
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t local_bar, uint32_t cta) {
+    uint32_t remote;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local_bar), "r"(cta));
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory");
+}
+__device__ __forceinline__ void umma2_tf32_ts(uint32_t tmem_c, uint32_t tmem_a, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::tf32 [%0], [%1], %2, %3, p;\n\t"
+        "}" ::"r"(tmem_c), "r"(tmem_a), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
+}
+// completion of all MMAs issued so far -> arrive on the barrier at this offset in both CTAs of the pair
+__device__ __forceinline__ void umma2_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(bar), "h"((uint16_t)3) : "memory");
+}
+
+// Latency, not bandwidth, bounds a ring whose slots stay occupied from the TMA request until the MMAs that read them have
+// completed (commit -> refill -> land -> convert -> multiply is ~3 us, so 4 slots give one k-block per 0.75 us against
+// 0.4 us of tensor work).  The pair kernel therefore uses three rings of different depth:
+//   A ring   (PA_SLOTS x 16 KB): raw fp32 A tiles; a slot is released by the converters as soon as it is in tensor memory;
+//   B ring   (PB_SLOTS x BN/2 rows x (raw + lo)): only 2 x 8 KB per k-block in pair mode; released by the MMAs;
+//   TMEM ring (PT_SLOTS x 64 columns): A hi / lo; released by the MMAs.
+// The MMA-issuing thread is the clock of the whole kernel: a tcgen05.mma occupies it for as long as the tensor pipe takes to
+// accept the instruction (~54 cycles at M = 256, N = 128, measured), so every other instruction it executes is tensor idle
+// time.  It therefore runs alone (no warp-wide waits), and signals "the MMAs of k-block it have completed" with a single
+// commit per k-block on done[it % PD_SLOTS], which both the converters (tensor-memory slot it % PT_SLOTS) and the B
+// producer (slot it % PB_SLOTS) wait on.
+// Every hand-off between the roles costs the MMA thread a few hundred cycles (measured ~650 per hand-off against 69 per MMA),
+// so one hand-off carries PK = 2 k-blocks of 32: a slot holds two [rows x 32] sub-tiles, 24 MMAs are issued per wait / commit.
+constexpr int PK = 2;                // 32-wide k-blocks per slot
+constexpr int PA_SLOTS = 3;
+constexpr int PB_SLOTS = 3;
+constexpr int PT_SLOTS = 2;
+constexpr int PD_SLOTS = 4;          // >= PB_SLOTS and >= PT_SLOTS: nobody waits for a completion more than 4 slots old
+constexpr int TCP_THREADS = 480;     // A producer, MMA, 2 x 4 converter warps (alternate k-blocks), 4 epilogue warps, B producer
+
+template <int BN, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(TCP_THREADS, 1) tc_pair_gemm_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                                      const __grid_constant__ CUtensorMap tmB,
+                                                                      const __grid_constant__ CUtensorMap tmC, TcArgs g) {
+    constexpr int BH = BN / 2;                                    // B rows held by one CTA
+    constexpr uint32_t A_BYTES = TC_BM * 128, BH_BYTES = BH * 128;
+    constexpr uint32_t A_SLOT_BYTES = PK * A_BYTES;               // PK raw [128 x 32] sub-tiles
+    constexpr uint32_t B_SLOT_BYTES = 2 * PK * BH_BYTES;          // B half: PK raw (= hi) sub-tiles, then their PK lo sub-tiles
+    constexpr uint32_t CHUNK_BYTES = TC_BK * 128;
+    constexpr uint32_t TMEM_NEED = 2 * BN + 64 * PK * PT_SLOTS;
+    constexpr uint32_t TMEM_COLS = TMEM_NEED <= 256 ? 256 : 512;
+    static_assert(TMEM_NEED <= 512, "tensor memory exhausted");
+    constexpr uint32_t TMEM_A0 = 2 * BN;
+    // c=F32, a=b=TF32, A K-major (tensor memory), B major, N = BN, M = 256
+    constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((B_MN ? 1u : 0u) << 16) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(256 >> 4) << 24);
+
+    extern __shared__ unsigned char smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    unsigned char* base_ptr = smem_raw + (base - smem_u32(smem_raw));
+    constexpr uint32_t EPI_BYTES = 4 * 2 * 4096;
+    const uint32_t b_base = base + PA_SLOTS * A_SLOT_BYTES;
+    const uint32_t epi_base = b_base + PB_SLOTS * B_SLOT_BYTES;
+    const uint32_t bar_base = epi_base + EPI_BYTES;
+    auto a_full = [&](int q) { return bar_base + 8u * q; };                                   // TMA bytes of the raw A tile
+    auto a_empty = [&](int q) { return bar_base + 8u * (PA_SLOTS + q); };                      // 4 local converter warps
+    auto b_full = [&](int sb) { return bar_base + 8u * (2 * PA_SLOTS + sb); };
+    auto ready = [&](int q) { return bar_base + 8u * (2 * PA_SLOTS + PB_SLOTS + q); };          // converters of both CTAs (rank 0's copy)
+    auto done = [&](int d) { return bar_base + 8u * (2 * PA_SLOTS + PB_SLOTS + PT_SLOTS + d); }; // MMA commit (multicast to both CTAs)
+    auto acc_full_bar = [&](int a) { return bar_base + 8u * (2 * PA_SLOTS + PB_SLOTS + PT_SLOTS + PD_SLOTS + a); };
+    auto acc_empty_bar = [&](int a) { return bar_base + 8u * (2 * PA_SLOTS + PB_SLOTS + PT_SLOTS + PD_SLOTS + 2 + a); };
+    const uint32_t tmem_slot = bar_base + 8u * (2 * PA_SLOTS + PB_SLOTS + PT_SLOTS + PD_SLOTS + 4);
+    volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(base_ptr + (tmem_slot - base));
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const bool leader = rank == 0;
+    const int tiles_n = (g.N + BN - 1) / BN, tiles_m = (g.M + TC_BM - 1) / TC_BM;
+    const int pairs_m = (tiles_m + 1) / 2;
+    const int total_kb = (g.K + TC_BK - 1) / TC_BK;
+    const int splits = (total_kb + g.kb_per_split - 1) / g.kb_per_split;
+    const long long num_units = (long long)tiles_n * pairs_m * splits;
+    const long long first_unit = blockIdx.x >> 1, unit_stride = gridDim.x >> 1;
+    long long* const trace = (g.trace && blockIdx.x < 2) ? g.trace + blockIdx.x * 8 * 256 : nullptr;   // CTA 0 and its peer
+#define TC_TRACE(ev, it) do { if (trace && (it) < 256u) trace[(ev) * 256 + (it)] = clock64(); } while (0)
+
+    if (threadIdx.x == 0) {
+        for (int q = 0; q < PA_SLOTS; ++q) { mbar_init(a_full(q), 1); mbar_init(a_empty(q), 4); }
+        for (int sb = 0; sb < PB_SLOTS; ++sb) mbar_init(b_full(sb), 1);
+        for (int q = 0; q < PT_SLOTS; ++q) mbar_init(ready(q), 8);
+        for (int d = 0; d < PD_SLOTS; ++d) mbar_init(done(d), 1);
+        for (int a = 0; a < 2; ++a) { mbar_init(acc_full_bar(a), 1); mbar_init(acc_empty_bar(a), 8); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();                      // both CTAs' barriers and tensor memory exist before anything crosses the pair
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot_ptr;
+    if (trace && threadIdx.x == 0) trace[7 * 256 + 255] = clock64();        // right after the cluster barrier: clock offset between the two SMs
+
+    auto slot_a = [&](int q) { return base + q * A_SLOT_BYTES; };
+    auto slot_b = [&](int sb) { return b_base + sb * B_SLOT_BYTES; };
+    auto slot_b_lo = [&](int sb) { return b_base + sb * B_SLOT_BYTES + PK * BH_BYTES; };
+    // unit id -> (first row of this CTA's A tile, n0 of the pair's tile, first k-block, number of k-blocks, split)
+    auto decode = [&](long long unit, int& m0, int& n0, int& kb_begin, int& nkb, int& z) {
+        const int nt = (int)(unit % tiles_n);
+        const long long rr = unit / tiles_n;
+        const int mp = (int)(rr % pairs_m);
+        z = (int)(rr / pairs_m);
+        m0 = (2 * mp + (int)rank) * TC_BM; n0 = nt * BN;           // m0 >= M for the padding half of an odd tile count: TMA reads zeros
+        kb_begin = z * g.kb_per_split;
+        nkb = (min(total_kb, kb_begin + g.kb_per_split) - kb_begin + PK - 1) / PK;      // hand-offs of PK k-blocks (kb_per_split is a multiple
+    };                                                                                   // of PK; beyond K the TMA reads zeros)
+
+    if (warp == 0) {
+        // ===================== A producer (this CTA's 128 rows) =====================
+        if (lane == 0) {
+            asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
+            uint32_t it = 0;
+            for (long long unit = first_unit; unit < num_units; unit += unit_stride) {
+                int m0, n0, kb_begin, nkb, z;
+                decode(unit, m0, n0, kb_begin, nkb, z);
+                for (int kb = 0; kb < nkb; ++kb, ++it) {
+                    const int q = it % PA_SLOTS;
+                    const uint32_t ph = (it / PA_SLOTS) & 1;
+                    mbar_wait(a_empty(q), ph ^ 1u);
+                    mbar_expect_tx(a_full(q), A_SLOT_BYTES);
+#pragma unroll
+                    for (int j = 0; j < PK; ++j) {
+                        const int k0 = (kb_begin + kb * PK + j) * TC_BK;
+                        if (!A_MN) tma_load_2d(slot_a(q) + j * A_BYTES, &tmA, a_full(q), k0, m0);
+                        else
+#pragma unroll
+                            for (int c = 0; c < TC_BM / 32; ++c) tma_load_2d(slot_a(q) + j * A_BYTES + c * CHUNK_BYTES, &tmA, a_full(q), m0 + 32 * c, k0);
+                    }
+                }
+            }
+        }
+    } else if (warp == 14) {
+        // ===================== B producer (this CTA's half of the B tile) =====================
+        if (lane == 0) {
+            asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
+            uint32_t it = 0;
+            for (long long unit = first_unit; unit < num_units; unit += unit_stride) {
+                int m0, n0, kb_begin, nkb, z;
+                decode(unit, m0, n0, kb_begin, nkb, z);
+                const int nb0 = n0 + (int)rank * BH;
+                for (int kb = 0; kb < nkb; ++kb, ++it) {
+                    const int sb = it % PB_SLOTS;
+                    if (it >= (uint32_t)PB_SLOTS) {                     // the MMAs of the k-block that used this slot have completed
+                        const uint32_t prev = it - PB_SLOTS;
+                        mbar_wait(done(prev % PD_SLOTS), (prev / PD_SLOTS) & 1);
+                    }
+                    mbar_expect_tx(b_full(sb), PK * BH_BYTES);
+#pragma unroll
+                    for (int j = 0; j < PK; ++j) {
+                        const int k0 = (kb_begin + kb * PK + j) * TC_BK;
+                        if (!B_MN) tma_load_2d(slot_b(sb) + j * BH_BYTES, &tmB, b_full(sb), k0, nb0);
+                        else
+#pragma unroll
+                            for (int c = 0; c < BH / 32; ++c) tma_load_2d(slot_b(sb) + j * BH_BYTES + c * CHUNK_BYTES, &tmB, b_full(sb), nb0 + 32 * c, k0);
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer (one thread of rank 0, for both CTAs) =====================
+        if (leader && lane == 0) {
+            uint32_t it = 0, tcount = 0;
+            const uint32_t b_lbo = B_MN ? CHUNK_BYTES : 16u, b_sbo = B_MN ? 512u : 1024u, b_lt = B_MN ? 1u : 2u;
+            uint32_t peek = 0;                                     // answer of the probe of ready(it) issued one k-block earlier
+            for (long long unit = first_unit; unit < num_units; unit += unit_stride, ++tcount) {
+                int m0, n0, kb_begin, nkb, z;
+                decode(unit, m0, n0, kb_begin, nkb, z);
+                const uint32_t acc = tcount & 1, acc_ph = (tcount >> 1) & 1;
+                mbar_wait(acc_empty_bar(acc), acc_ph ^ 1u);        // both CTAs' epilogues have drained this accumulator
+                tc_fence_after();
+                const uint32_t tmem_acc = tmem_base + acc * BN;
+                for (int kb = 0; kb < nkb; ++kb, ++it) {
+                    const int q = it % PT_SLOTS, sb = it % PB_SLOTS;
+                    TC_TRACE(0, it);                                   // (rows 0/1 of the MMA thread's CTA are shared with the producers: debug only)
+                    if (!peek) mbar_wait(ready(q), (it / PT_SLOTS) & 1);   // both CTAs: A in tensor memory, B lo written
+                    TC_TRACE(1, it);
+                    tc_fence_after();
+                    peek = mbar_try(ready((it + 1) % PT_SLOTS), ((it + 1) / PT_SLOTS) & 1);   // in flight while the MMAs below issue
+                    TC_TRACE(2, it);
+                    const uint64_t db0 = umma_desc(slot_b(sb), b_lbo, b_sbo, b_lt), dl0 = umma_desc(slot_b_lo(sb), b_lbo, b_sbo, b_lt);
+                    const uint32_t ta0 = tmem_base + TMEM_A0 + (uint32_t)q * (64u * PK);
+                    for (int rep = 0; rep < (g.keep_raw_hi >> 8); ++rep)      // debug: extra copies of the MMAs (measures the tensor rate)
+#pragma unroll
+                        for (int kk = 0; kk < PK * (TC_BK / 8); ++kk) {
+                            const uint64_t adv = (uint64_t)(((kk >> 2) * BH_BYTES + (B_MN ? (kk & 3) * 1024u : (kk & 3) * 32u)) >> 4);
+                            const uint32_t ta_hi = ta0 + (uint32_t)(kk >> 2) * 64u + (uint32_t)(kk & 3) * 8u;
+                            umma2_tf32_ts(tmem_acc, ta_hi, db0 + adv, IDESC, 1u);
+                            umma2_tf32_ts(tmem_acc, ta_hi + 32u, db0 + adv, IDESC, 1u);
+                            umma2_tf32_ts(tmem_acc, ta_hi, db0 + adv, IDESC, 1u);
+                        }
+#pragma unroll
+                    for (int kk = 0; kk < PK * (TC_BK / 8); ++kk) {
+                        // sub-tile kk / 4; inside it the start address advances by 32 B (K-major) / one 8-row group (MN-major) per UMMA_K
+                        const uint64_t adv = (uint64_t)(((kk >> 2) * BH_BYTES + (B_MN ? (kk & 3) * 1024u : (kk & 3) * 32u)) >> 4);
+                        const uint32_t ta_hi = ta0 + (uint32_t)(kk >> 2) * 64u + (uint32_t)(kk & 3) * 8u, ta_lo = ta_hi + 32u;
+                        umma2_tf32_ts(tmem_acc, ta_hi, db0 + adv, IDESC, (kb > 0 || kk > 0) ? 1u : 0u);
+                        umma2_tf32_ts(tmem_acc, ta_lo, db0 + adv, IDESC, 1u);
+                        umma2_tf32_ts(tmem_acc, ta_hi, dl0 + adv, IDESC, 1u);
+                    }
+                    umma2_commit(done(it % PD_SLOTS));                 // B slot and tensor-memory A slot of this k-block free in both CTAs
+                    if (kb == nkb - 1) umma2_commit(acc_full_bar(acc));
+                    TC_TRACE(3, it);
+                }
+            }
+        }
+    } else if (warp < 10) {
+        // ===================== converters =====================
+        // The chain load -> split -> tcgen05.st -> wait::st -> fence -> arrive of one k-block is longer than its 12 MMAs, and a
+        // warp runs it serially: two groups of four warps take alternate k-blocks so that two chains are in flight.
+        const int grp = (warp - 2) >> 2;
+        const int t = (threadIdx.x - 64) & 127;
+        uint32_t it = 0;
+        for (long long unit = first_unit; unit < num_units; unit += unit_stride) {
+            int m0, n0, kb_begin, nkb, z;
+            decode(unit, m0, n0, kb_begin, nkb, z);
+            for (int kb = 0; kb < nkb; ++kb, ++it) {
+                if ((int)(it & 1u) != grp) continue;
+                const int qa = it % PA_SLOTS, q = it % PT_SLOTS, sb = it % PB_SLOTS;
+                const uint32_t aph = (it / PA_SLOTS) & 1, bph = (it / PB_SLOTS) & 1;
+                mbar_wait(a_full(qa), aph);
+                if ((warp & 3) == 2 && lane == 0) TC_TRACE(4, it);
+                const int row = (warp & 3) * 32 + lane;
+                if (it >= (uint32_t)PT_SLOTS) {                        // the MMAs that read this tensor-memory slot have completed
+                    const uint32_t prev = it - PT_SLOTS;
+                    mbar_wait(done(prev % PD_SLOTS), (prev / PD_SLOTS) & 1);
+                }
+                tc_fence_after();
+                if ((warp & 3) == 2 && lane == 0) TC_TRACE(5, it);
+#pragma unroll
+                for (int j = 0; j < PK; ++j) {
+                    uint32_t hi[32], lo[32];
+                    if (A_MN) {
+                        const float* acol = reinterpret_cast<const float*>(base_ptr + (slot_a(qa) - base) + j * A_BYTES + (row >> 5) * CHUNK_BYTES) + (row & 31);
+#pragma unroll
+                        for (int kx = 0; kx < 32; ++kx) {
+                            const float x = acol[kx * 32];
+                            const uint32_t h = __float_as_uint(x) & 0xffffe000u;
+                            hi[kx] = h;
+                            lo[kx] = __float_as_uint(x - __uint_as_float(h));
+                        }
+                    } else {
+                        const float4* arow = reinterpret_cast<const float4*>(base_ptr + (slot_a(qa) - base) + j * A_BYTES + row * 128);
+#pragma unroll
+                        for (int c = 0; c < 8; ++c) {
+                            const float4 x = arow[c ^ (row & 7)];
+                            const float v[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+                            for (int u = 0; u < 4; ++u) {
+                                const uint32_t h = __float_as_uint(v[u]) & 0xffffe000u;
+                                hi[4 * c + u] = h;
+                                lo[4 * c + u] = __float_as_uint(v[u] - __uint_as_float(h));
+                            }
+                        }
+                    }
+                    const uint32_t ta = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + TMEM_A0 + (uint32_t)q * (64u * PK) + (uint32_t)j * 64u;
+                    tmem_st32(ta, hi);
+                    tmem_st32(ta + 32u, lo);
+                }
+                // The raw A slot goes back to the producer only now: the tcgen05.st above could not issue before every load
+                // from the slot had returned its data (an arrive right after the loads can overtake them in the LSU queue).
+                __syncwarp();
+                if (lane == 0) mbar_arrive(a_empty(qa));
+                // B half: lo next to the raw tile (the MMA truncates the raw fp32 words to tf32 itself)
+                mbar_wait(b_full(sb), bph);
+                if ((warp & 3) == 2 && lane == 0) TC_TRACE(6, it);
+                const float4* b_hi = reinterpret_cast<const float4*>(base_ptr + (slot_b(sb) - base));
+                float4* b_lo = reinterpret_cast<float4*>(base_ptr + (slot_b_lo(sb) - base));
+#pragma unroll
+                for (int i = 0; i < (int)(PK * BH_BYTES / 16) / 128; ++i) {
+                    const float4 x = b_hi[t + 128 * i];
+                    float4 l;
+                    l.x = x.x - __uint_as_float(__float_as_uint(x.x) & 0xffffe000u);
+                    l.y = x.y - __uint_as_float(__float_as_uint(x.y) & 0xffffe000u);
+                    l.z = x.z - __uint_as_float(__float_as_uint(x.z) & 0xffffe000u);
+                    l.w = x.w - __uint_as_float(__float_as_uint(x.w) & 0xffffe000u);
+                    b_lo[t + 128 * i] = l;
+                }
+                asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+                tc_fence_before();
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                __syncwarp();
+                if (lane == 0) {
+                    if (leader) mbar_arrive(ready(q));
+                    else mbar_arrive_cluster(ready(q), 0);
+                    if ((warp & 3) == 2) TC_TRACE(7, it);
+                }
+            }
+        }
+    } else if (warp < 14) {
+        // ===================== epilogue: own 128 rows, TMEM -> shared memory -> TMA store =====================
+        const int q = warp & 3;
+        uint32_t tcount = 0, epi_it = 0;
+        for (long long unit = first_unit; unit < num_units; unit += unit_stride, ++tcount) {
+            int m0, n0, kb_begin, nkb, z;
+            decode(unit, m0, n0, kb_begin, nkb, z);
+            const uint32_t acc = tcount & 1, acc_ph = (tcount >> 1) & 1;
+            mbar_wait(acc_full_bar(acc), acc_ph);
+            tc_fence_after();
+#pragma unroll 1
+            for (int c0 = 0; c0 < BN; c0 += 32) {
+                if (n0 + c0 >= g.N) break;
+                uint32_t r[32];
+                tmem_ld32(tmem_base + acc * BN + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, r);
+                if (!g.partial && g.bias) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (n0 + c0 + j < g.N) r[j] = __float_as_uint(__uint_as_float(r[j]) + __ldg(g.bias + n0 + c0 + j));
+                }
+                const uint32_t buf = epi_base + (uint32_t)q * 8192u + (epi_it & 1u) * 4096u;
+                if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+                __syncwarp();
+                float4* dstrow = reinterpret_cast<float4*>(base_ptr + (buf - base) + lane * 128);
+#pragma unroll
+                for (int c = 0; c < 8; ++c)
+                    dstrow[c ^ (lane & 7)] = make_float4(__uint_as_float(r[4 * c]), __uint_as_float(r[4 * c + 1]),
+                                                         __uint_as_float(r[4 * c + 2]), __uint_as_float(r[4 * c + 3]));
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                __syncwarp();
+                if (lane == 0) tma_store_3d(&tmC, buf, n0 + c0, m0 + q * 32, z);
+                ++epi_it;
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+                if (leader) mbar_arrive(acc_empty_bar(acc));
+                else mbar_arrive_cluster(acc_empty_bar(acc), 0);
+            }
+        }
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();                      // the peer may still read this CTA's shared / tensor memory through the pair's MMAs
+    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
+}
+#undef TC_TRACE
+
 // Split-K partials [splits][M*N] -> C (+ bias).  Fixed summation order for a given (shape, split count): deterministic.
 // One thread per output; the loads of a round are independent so that four of them are in flight.
 __global__ void tc_splitk_reduce_kernel(const float* __restrict__ partial, int splits, long long MN, int N, float* __restrict__ C,
@@ -523,6 +911,7 @@ bool make_out_map(CUtensorMap* map, float* ptr, long long N, long long M, long l
               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+long long* g_tc_trace = nullptr;   // debug: device buffer of 8 x 256 clock stamps (dc_set_gemm_trace)
 int g_tc_tma_store = 1;     // epilogue through shared memory + TMA stores (0 = row-per-lane direct stores)
 int g_tc_keep_raw_hi = 1;   // B_hi is the raw fp32 tile: the MMA truncates fp32 -> tf32 on read (measured bit-identical to an explicit
                             // hi = x & 0xffffe000 rewrite, dc_set_gemm_keep_raw_hi(0) restores the rewrite)
@@ -556,6 +945,36 @@ int launch_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap&
     return DC_OK;
 }
 
+int g_tc_pair = 1;          // 1: CTA pairs (cta_group::2) for the 3xTF32 product when the shape allows
+
+template <int BN, bool A_MN, bool B_MN>
+int launch_tc_pair(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const TcArgs& g, int splits, cudaStream_t st) {
+    const size_t smem = (size_t)PA_SLOTS * PK * TC_BM * 128 + (size_t)PB_SLOTS * PK * BN * 128 + 32768 + 1024 + 8 * (2 * PA_SLOTS + PB_SLOTS + PT_SLOTS + PD_SLOTS + 4) + 16;
+    auto kern = tc_pair_gemm_kernel<BN, A_MN, B_MN>;
+    DC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const long long tiles_n = (g.N + BN - 1) / BN, tiles_m = (g.M + TC_BM - 1) / TC_BM;
+    const long long units = tiles_n * ((tiles_m + 1) / 2) * splits;
+    const long long slots = dc_sm_count() / 2;                                  // persistent: one CTA pair per TPC
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)((units < slots ? units : slots) * 2));
+    cfg.blockDim = dim3(TCP_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    DC_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, g));
+    return DC_OK;
+}
+
+template <bool A_MN, bool B_MN>
+int dispatch_tc_pair(int BN, const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& c, const TcArgs& g, int splits, cudaStream_t st) {
+    if (BN == 64) return launch_tc_pair<64, A_MN, B_MN>(a, b, c, g, splits, st);
+    return launch_tc_pair<128, A_MN, B_MN>(a, b, c, g, splits, st);
+}
+
 template <bool A_MN, bool B_MN>
 int dispatch_tc(int BN, bool split3, const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& c, const TcArgs& g, long long tiles, cudaStream_t st) {
     if (split3) {
@@ -582,6 +1001,10 @@ extern "C" int dc_set_gemm_no_ts(int v) { g_tc_no_ts = v; return DC_OK; }
 extern "C" int dc_set_gemm_keep_raw_hi(int v) { g_tc_keep_raw_hi = v; return DC_OK; }
 // tuning switch: 1 (default) = epilogue through shared memory and TMA stores, 0 = row-per-lane direct stores
 extern "C" int dc_set_gemm_tma_store(int v) { g_tc_tma_store = v; return DC_OK; }
+// tuning switch: 1 (default) = CTA pairs (cta_group::2, 256-row tiles, B split across the pair), 0 = one CTA per tile
+extern "C" int dc_set_gemm_pair(int v) { g_tc_pair = v; return DC_OK; }
+// debug: device buffer (8 x 256 int64) that CTA 0 of the pair kernel fills with clock64 stamps of its pipeline events; null = off
+extern "C" int dc_set_gemm_trace(void* buf) { g_tc_trace = (long long*)buf; return DC_OK; }
 
 // Split-K factor for an M x N output with reduction K.  Cost model in units of one k-block (128 x BN x 32) of main loop: the
 // persistent grid runs ceil(units / SMs) waves of (k-blocks per split + pipeline fill), the reduce pass costs a launch plus a
@@ -623,26 +1046,43 @@ int dc_tc_gemm(const float* A, long long lda, int a_mn, const float* B, long lon
     CUtensorMap tmA, tmB;
     // an MN-major A goes through tensor memory in the 3xTF32 path (the converters transpose it), so it is fetched unswizzled
     const bool a_via_tmem = g_tc_mode == 3 && !g_tc_no_ts;
-    bool ok = a_mn ? make_map(&tmA, A, M, K, lda, TC_BK, a_via_tmem ? 0 : 2) : make_map(&tmA, A, K, M, lda, TC_BM, 1);
-    ok = ok && (b_mn ? make_map(&tmB, B, N, K, ldb, TC_BK, 2) : make_map(&tmB, B, K, N, ldb, BN, 1));
-    if (!ok) return 1;
     const int total_kb = (int)((K + TC_BK - 1) / TC_BK);
-    const long long tiles = ((M + TC_BM - 1) / TC_BM) * ((N + BN - 1) / BN);
-    int splits = tc_choose_splits(M, N, K, ws_bytes);
+    const long long tiles_m_ = (M + TC_BM - 1) / TC_BM;
+    const long long tiles = tiles_m_ * ((N + BN - 1) / BN);
     TcArgs g = {};
     g.C = C; g.ldc = ldc; g.bias = bias; g.M = (int)M; g.N = N; g.K = (int)K;
-    g.kb_per_split = (total_kb + splits - 1) / splits;
-    splits = (total_kb + g.kb_per_split - 1) / g.kb_per_split;
-    g.partial = splits > 1 ? (float*)ws : nullptr;
     g.keep_raw_hi = g_tc_keep_raw_hi;
+    g.trace = g_tc_trace;
     CUtensorMap tmC;
-    memset(&tmC, 0, sizeof(tmC));
-    g.tma_store = g_tc_tma_store && (g.partial ? make_out_map(&tmC, g.partial, N, M, splits, N, M * (long long)N)
-                                               : make_out_map(&tmC, C, N, M, 1, ldc, M * ldc)) ? 1 : 0;
+    int splits = 1;
+    // CTA pairs (two M tiles per unit): worth it when at most one tile in nine is padding; they need the TMA-store epilogue,
+    // i.e. an output (or split-K partial buffer) with 16-byte aligned rows — otherwise the single-CTA kernel is planned
+    bool pair = g_tc_pair && g_tc_tma_store && g_tc_mode == 3 && a_via_tmem && tiles_m_ >= 2 && (tiles_m_ % 2 == 0 || tiles_m_ >= 9);
+    for (int attempt = 0; attempt < 2; ++attempt) {
+        splits = tc_choose_splits(M, N, K, ws_bytes);
+        g.kb_per_split = (total_kb + splits - 1) / splits;
+        if (pair) g.kb_per_split = (g.kb_per_split + PK - 1) / PK * PK;   // the pair kernel hands over PK k-blocks at a time
+        splits = (total_kb + g.kb_per_split - 1) / g.kb_per_split;
+        g.partial = splits > 1 ? (float*)ws : nullptr;
+        memset(&tmC, 0, sizeof(tmC));
+        g.tma_store = g_tc_tma_store && (g.partial ? make_out_map(&tmC, g.partial, N, M, splits, N, M * (long long)N)
+                                                   : make_out_map(&tmC, C, N, M, 1, ldc, M * ldc)) ? 1 : 0;
+        if (!pair || g.tma_store) break;
+        pair = false;
+    }
+    bool ok = a_mn ? make_map(&tmA, A, M, K, lda, TC_BK, a_via_tmem ? 0 : 2) : make_map(&tmA, A, K, M, lda, TC_BM, 1);
+    ok = ok && (b_mn ? make_map(&tmB, B, N, K, ldb, TC_BK, 2) : make_map(&tmB, B, K, N, ldb, pair ? BN / 2 : BN, 1));
+    if (!ok) return 1;
     const long long num_tiles = tiles * splits;
     const bool split3 = g_tc_mode == 3;
     int rc;
-    if (!a_mn && !b_mn) rc = dispatch_tc<false, false>(BN, split3, tmA, tmB, tmC, g, num_tiles, st);
+    if (pair) {
+        if (!a_mn && !b_mn) rc = dispatch_tc_pair<false, false>(BN, tmA, tmB, tmC, g, splits, st);
+        else if (!a_mn && b_mn) rc = dispatch_tc_pair<false, true>(BN, tmA, tmB, tmC, g, splits, st);
+        else if (a_mn && b_mn) rc = dispatch_tc_pair<true, true>(BN, tmA, tmB, tmC, g, splits, st);
+        else return 1;
+    }
+    else if (!a_mn && !b_mn) rc = dispatch_tc<false, false>(BN, split3, tmA, tmB, tmC, g, num_tiles, st);
     else if (!a_mn && b_mn) rc = dispatch_tc<false, true>(BN, split3, tmA, tmB, tmC, g, num_tiles, st);
     else if (a_mn && b_mn) rc = dispatch_tc<true, true>(BN, split3, tmA, tmB, tmC, g, num_tiles, st);
     else return 1;

@@ -222,6 +222,10 @@ int dc_set_gemm_no_ts(int v);
 int dc_set_gemm_keep_raw_hi(int v);
 /* tuning switch: 1 (default) = GEMM epilogue through shared memory and TMA stores, 0 = row-per-lane direct stores */
 int dc_set_gemm_tma_store(int v);
+/* tuning switch: 1 (default) = CTA pairs (tcgen05 cta_group::2: 256-row tiles, each CTA holds half of the B tile), 0 = one CTA per tile */
+int dc_set_gemm_pair(int v);
+/* debug: device buffer of 8 x 256 int64 that CTA 0 of the pair kernel fills with clock stamps of its pipeline events (NULL = off) */
+int dc_set_gemm_trace(void* device_buffer_or_null);
 size_t dc_gemm_ws_bytes(int64_t M, int64_t N, int64_t K);
 /* The tensor-core product itself, C[M,N] = op(A) op(B)^T: a_mn/b_mn = 0 when the reduction index is contiguous
  * ([M,K] / [N,K] storage), 1 when the M / N index is contiguous ([K,M] / [K,N] storage).  Returns 1 if the shape is

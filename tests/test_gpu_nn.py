@@ -522,3 +522,35 @@ def test_embedding_pool_fusion_matches_unfused(sizes, K, C, mode):
     fused.eval(), plain.eval()
     with torch.no_grad():
         assert torch.equal(fused.forward_pooled(xa, batch, mode, len(sizes)), ops.pool(plain(xb), batch, mode, len(sizes)))
+
+
+@pytest.mark.parametrize('switch', ['dc_set_gemm_pair', 'dc_set_gemm_tma_store'])
+def test_gemm_kernel_variants_agree(switch):
+    """The single-CTA kernel (dc_set_gemm_pair(0)) and the direct-store epilogue (dc_set_gemm_tma_store(0), single-CTA only)
+    compute the same products as the default CTA-pair kernel (tcgen05 cta_group::2, TMA-store epilogue): all three layouts, ragged M / N / K, bias, split-K partials."""
+    from deltaconv_b200 import _lib
+    lib = _lib.load()
+    torch.manual_seed(5)
+    ws = torch.zeros(64 << 20, dtype=torch.uint8, device=DEV)
+    on = 0                                                 # the non-default setting of either switch
+    try:
+        for (M, N, K, a_mn, b_mn, with_bias) in [(1300, 72, 100, 0, 0, True), (2049, 200, 64, 0, 1, False), (640, 136, 4000, 1, 1, False),
+                                                 (4096, 64, 256, 0, 0, True), (1153, 128, 96, 0, 0, False)]:
+            a, b = torch.randn(M, K, device=DEV), torch.randn(N, K, device=DEV)
+            bias = torch.randn(N, device=DEV) if with_bias else None
+            A = a.t().contiguous() if a_mn else a
+            B = b.t().contiguous() if b_mn else b
+            outs = []
+            for setting in (1 - on, on):
+                getattr(lib, switch)(setting)
+                C = torch.full((M, N), float('nan'), device=DEV)
+                _lib.call('dc_gemm_tc_raw', A.data_ptr(), A.stride(0), a_mn, B.data_ptr(), B.stride(0), b_mn,
+                          bias.data_ptr() if with_bias else None, M, N, K, C.data_ptr(), N, ws.data_ptr(), ws.numel())
+                outs.append(C)
+            ref = a.double() @ b.double().t() + (bias.double() if with_bias else 0)
+            scale = ref.abs().max()
+            assert ((outs[1].double() - ref).abs().max() / scale) < 2e-5, (M, N, K)
+            assert ((outs[1] - outs[0]).abs().max() / scale) < 4e-6, (M, N, K)      # same terms, different accumulation grouping at most
+    finally:
+        lib.dc_set_gemm_pair(1)
+        lib.dc_set_gemm_tma_store(1)
