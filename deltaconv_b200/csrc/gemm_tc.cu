@@ -669,9 +669,12 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) tc_pair_gemm_kernel(const __gr
                         for (int kk = 0; kk < PK * (TC_BK / 8); ++kk) {
                             const uint64_t adv = (uint64_t)(((kk >> 2) * BH_BYTES + (B_MN ? (kk & 3) * 1024u : (kk & 3) * 32u)) >> 4);
                             const uint32_t ta_hi = ta0 + (uint32_t)(kk >> 2) * 64u + (uint32_t)(kk & 3) * 8u;
-                            umma2_tf32_ts(tmem_acc, ta_hi, db0 + adv, IDESC, 1u);
-                            umma2_tf32_ts(tmem_acc, ta_hi + 32u, db0 + adv, IDESC, 1u);
-                            umma2_tf32_ts(tmem_acc, ta_hi, db0 + adv, IDESC, 1u);
+                            // debug bit 4: N = 256 per instruction (reads past the B half and writes both accumulators: timing only)
+                            const uint32_t idx = (g.keep_raw_hi & 4) ? ((IDESC & ~(0x3fu << 17)) | ((256u >> 3) << 17)) : IDESC;
+                            const uint32_t tacc = (g.keep_raw_hi & 4) ? tmem_base : tmem_acc;
+                            umma2_tf32_ts(tacc, ta_hi, db0 + adv, idx, 1u);
+                            umma2_tf32_ts(tacc, ta_hi + 32u, db0 + adv, idx, 1u);
+                            umma2_tf32_ts(tacc, ta_hi, db0 + adv, idx, 1u);
                         }
 #pragma unroll
                     for (int kk = 0; kk < PK * (TC_BK / 8); ++kk) {

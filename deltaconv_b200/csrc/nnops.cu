@@ -174,6 +174,23 @@ __global__ void bn_act_bwd_vec4_kernel(const float* __restrict__ y, long long ld
     }
 }
 
+// out[r, :] = a[r, :] + b[r, :] on column slices of wider buffers (gradient of a tensor that feeds two consumers)
+__global__ void add_rows_kernel(const float* __restrict__ a, long long lda, const float* __restrict__ b, long long ldb,
+                                long long M, int C, int vec, float* __restrict__ out, long long ldo) {
+    const int cw = vec ? C / 4 : C;
+    const long long total = M * (long long)cw;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+        const long long r = t / cw;
+        const int c = (int)(t - r * cw);
+        if (vec) {
+            const float4 x = ld_stream4(reinterpret_cast<const float4*>(a + r * lda) + c), y = ld_stream4(reinterpret_cast<const float4*>(b + r * ldb) + c);
+            reinterpret_cast<float4*>(out + r * ldo)[c] = make_float4(x.x + y.x, x.y + y.y, x.z + y.z, x.w + y.w);
+        } else {
+            out[r * ldo + c] = __ldg(a + r * lda + c) + __ldg(b + r * ldb + c);
+        }
+    }
+}
+
 // ---- BatchNorm + activation fused with the global pools, backward -------------------------------
 // The gradient of [max | mean] pooling w.r.t. the pooled activation at (r, c) is (r == arg[b,c] ? d_max[b,c] : 0) + d_mean[b,c] / n_b
 // (same expression as pool_bwd): it is rebuilt on the fly.  Work is split by cloud so that the [B,C] quantities are loaded once per
@@ -546,15 +563,22 @@ __global__ void __launch_bounds__(256) gathermax_bwd_vec4_kernel(const int* __re
     for (int o = 16; o > 0; o >>= 1) max_len = max(max_len, __shfl_xor_sync(FULL, max_len, o));
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     for (int t0 = 0; t0 < max_len; t0 += lpp) {
-        int my_edge = -1;
-        if (t0 + sub < len) my_edge = __ldg(in_edge + t_begin + t0 + sub);
+        // the lane that loads an edge id also splits it into (source row, slot): one integer division per edge, not per lane
+        int my_src = -1, my_slot = 0;
+        if (t0 + sub < len) {
+            const int edge = __ldg(in_edge + t_begin + t0 + sub);
+            my_src = edge / k;
+            my_slot = edge - my_src * k;
+        }
         const int cnt = min(lpp, max_len - t0);
+        // (loading dout only where one of the lane's four channels matches — per edge, or batched four edges at a time with the
+        // arg bytes first — was measured 1.5-1.7x slower than this unconditional form: the kernel is bound by instruction issue
+        // and load latency, not by the L2 traffic of the gather)
 #pragma unroll 4
         for (int q = 0; q < cnt; ++q) {
-            const int edge = __shfl_sync(FULL, my_edge, q, lpp);
-            if (!ch_ok || edge < 0) continue;
-            const int i = edge / k;
-            const unsigned char e = (unsigned char)(edge - i * k);
+            const int i = __shfl_sync(FULL, my_src, q, lpp);
+            const unsigned char e = (unsigned char)__shfl_sync(FULL, my_slot, q, lpp);
+            if (!ch_ok || i < 0) continue;
             const uchar4 a = *reinterpret_cast<const uchar4*>(arg + (size_t)i * C + ch);
             const float4 d = __ldg(reinterpret_cast<const float4*>(dout + (size_t)i * ldd + ch));
             if (a.x == e) acc.x += d.x;
@@ -953,6 +977,13 @@ extern "C" int dc_pool_bwd(const int32_t* cloud_ptr, int B, int N, int C, const 
         pool_bwd_cloud_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(cloud_ptr, C, arg, d_max_or_null, ld_dmax, d_mean_or_null, ld_dmean, dx, ld_dx);
     }
     return dc_check_launch("dc_pool_bwd");
+}
+
+extern "C" int dc_add_rows(const float* a, int64_t lda, const float* b, int64_t ldb, int64_t M, int C, float* out, int64_t ldo, void* stream) {
+    if (M <= 0 || C <= 0) return DC_OK;
+    const int vec = (C % 4 == 0 && lda % 4 == 0 && ldb % 4 == 0 && ldo % 4 == 0 && all_aligned16(a, b, out)) ? 1 : 0;
+    add_rows_kernel<<<elementwise_grid(M * (vec ? C / 4 : C)), 256, 0, (cudaStream_t)stream>>>(a, lda, b, ldb, M, C, vec, out, ldo);
+    return dc_check_launch("dc_add_rows");
 }
 
 extern "C" int dc_bcast_rows(const float* src, int64_t lds, const int32_t* cloud_ptr, int B, int N, int C, float* out, int64_t ldo,

@@ -377,7 +377,8 @@ __global__ void count_in_kernel(const int* __restrict__ idx, long long E, int N,
 }
 
 constexpr int SCAN_T = 1024;
-// exclusive scan of cnt[0..n) into out[0..n], out[n] = total; single CTA, chunked with a carry.
+constexpr int SCAN_V = 4;            // elements per thread and round
+// exclusive scan of cnt[0..n) into out[0..n], out[n] = total; single CTA, 4096 elements per round with a carry.
 // n is at most a few million and the kernel runs once per batch, so one CTA is enough.
 __global__ void __launch_bounds__(SCAN_T) scan_kernel(const int* __restrict__ cnt, int n, int* __restrict__ out) {
     __shared__ int warp_tot[32];
@@ -385,10 +386,12 @@ __global__ void __launch_bounds__(SCAN_T) scan_kernel(const int* __restrict__ cn
     if (threadIdx.x == 0) carry_s = 0;
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int base = 0; base < n; base += SCAN_T) {
-        int i = base + threadIdx.x;
-        int v = i < n ? cnt[i] : 0;
-        int x = v;
+    for (int base = 0; base < n; base += SCAN_T * SCAN_V) {
+        const int i0 = base + threadIdx.x * SCAN_V;
+        int v[SCAN_V], sum = 0;
+#pragma unroll
+        for (int u = 0; u < SCAN_V; ++u) { v[u] = (i0 + u < n) ? cnt[i0 + u] : 0; sum += v[u]; }
+        int x = sum;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(FULL, x, o); if (lane >= o) x += y; }
         if (lane == 31) warp_tot[warp] = x;
@@ -400,9 +403,11 @@ __global__ void __launch_bounds__(SCAN_T) scan_kernel(const int* __restrict__ cn
             warp_tot[lane] = w;
         }
         __syncthreads();
-        int carry = carry_s;
-        int incl = x + (warp > 0 ? warp_tot[warp - 1] : 0);
-        if (i < n) out[i] = carry + incl - v;
+        const int carry = carry_s;
+        const int incl = x + (warp > 0 ? warp_tot[warp - 1] : 0);
+        int run = carry + incl - sum;
+#pragma unroll
+        for (int u = 0; u < SCAN_V; ++u) { if (i0 + u < n) out[i0 + u] = run; run += v[u]; }
         __syncthreads();
         if (threadIdx.x == SCAN_T - 1) carry_s = carry + incl;
         __syncthreads();
@@ -421,15 +426,33 @@ __global__ void fill_in_kernel(const int* __restrict__ idx, long long E, int N, 
 }
 
 // The atomic fill order is arbitrary; sorting each row makes the structure (and therefore every
-// backward sum) bit-reproducible.  Rows are short (mean k), one thread sorts one row in place.
-__global__ void sort_rows_kernel(const int* __restrict__ in_ptr, int N, int* __restrict__ in_edge) {
-    int j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= N) return;
-    int b = in_ptr[j], e = in_ptr[j + 1];
-    for (int p = b + 1; p < e; ++p) {
-        int key = in_edge[p], q = p - 1;
-        while (q >= b && in_edge[q] > key) { in_edge[q + 1] = in_edge[q]; --q; }
-        in_edge[q + 1] = key;
+// backward sum) bit-reproducible.  Rows are short (mean k): a CTA stages the entries of SORT_ROWS consecutive rows in
+// shared memory (one coalesced pass each way), one thread insertion-sorts one row there; blocks of rows with more
+// entries than the staging buffer (very uneven in-degrees) are sorted in place in global memory.
+constexpr int SORT_ROWS = 128;
+constexpr int SORT_CAP = 8192;       // staged entries per CTA (32 KB)
+__global__ void __launch_bounds__(SORT_ROWS) sort_rows_kernel(const int* __restrict__ in_ptr, int N, int* __restrict__ in_edge) {
+    __shared__ int buf[SORT_CAP];
+    const int j0 = blockIdx.x * SORT_ROWS;
+    const int j = j0 + threadIdx.x;
+    const int lo = in_ptr[j0], hi = in_ptr[min(j0 + SORT_ROWS, N)];
+    const bool staged = hi - lo <= SORT_CAP;
+    if (staged) {
+        for (int t = threadIdx.x; t < hi - lo; t += SORT_ROWS) buf[t] = in_edge[lo + t];
+        __syncthreads();
+    }
+    if (j < N) {
+        int* a = staged ? buf - lo : in_edge;
+        const int b = in_ptr[j], e = in_ptr[j + 1];
+        for (int p = b + 1; p < e; ++p) {
+            int key = a[p], q = p - 1;
+            while (q >= b && a[q] > key) { a[q + 1] = a[q]; --q; }
+            a[q + 1] = key;
+        }
+    }
+    if (staged) {
+        __syncthreads();
+        for (int t = threadIdx.x; t < hi - lo; t += SORT_ROWS) in_edge[lo + t] = buf[t];
     }
 }
 
@@ -453,7 +476,7 @@ extern "C" int dc_ell_transpose(const int32_t* idx, int N, int k, int32_t* in_pt
     count_in_kernel<<<dc_ceil_div(E, 256), 256, 0, st>>>(idx, E, N, cnt);
     scan_kernel<<<1, SCAN_T, 0, st>>>(cnt, N, in_ptr);
     fill_in_kernel<<<dc_ceil_div(E, 256), 256, 0, st>>>(idx, E, N, in_ptr, cursor, in_edge);
-    sort_rows_kernel<<<dc_ceil_div(N, 128), 128, 0, st>>>(in_ptr, N, in_edge);
+    sort_rows_kernel<<<dc_ceil_div(N, SORT_ROWS), SORT_ROWS, 0, st>>>(in_ptr, N, in_edge);
     return dc_check_launch_n("dc_ell_transpose", 4);
 }
 

@@ -325,7 +325,9 @@ class _ScalarCat(torch.autograd.Function):
         v, ldv = _mat(v)
         dcat, ld = _mat(dcat.contiguous(), 'grad_output')
         if ddc is not None:
-            t = dcat[:, C:3 * C] + ddc
+            ddc, ld_ddc = _mat(ddc, 'grad_output')
+            t = torch.empty(g.N, 2 * C, dtype=_F32, device=dcat.device)
+            call('dc_add_rows', dcat.data_ptr() + 4 * C, ld, ptr(ddc), ld_ddc, g.N, 2 * C, ptr(t), 2 * C)
             d_div, d_curl, ldt = t.data_ptr(), t.data_ptr() + 4 * C, 2 * C
         else:
             d_div, d_curl, ldt = dcat.data_ptr() + 4 * C, dcat.data_ptr() + 8 * C, ld

@@ -22,7 +22,7 @@ for pair in (0, 1):
     lib.dc_set_gemm_pair(pair)
     res = []
     for rep in (0, 2, 4):
-        lib.dc_set_gemm_keep_raw_hi(1 + 256 * rep)
+        lib.dc_set_gemm_keep_raw_hi(1 + 256 * rep + int(os.environ.get('DC_DBG', '0')))
         res.append(t_ms())
     lib.dc_set_gemm_keep_raw_hi(1)
     # k-blocks executed per SM: tiles per SM (ceil) x 16
