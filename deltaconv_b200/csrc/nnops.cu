@@ -13,6 +13,18 @@
 
 namespace {
 
+// Grid-stride iteration over an [M, W] index space: (row, column) advance by the constant (stride / W, stride % W) instead
+// of a 64-bit division per element (which cost more instructions than the element's arithmetic).
+struct RowCol {
+    long long r, dr; int c, dc, W;
+    __device__ __forceinline__ explicit RowCol(int W_) : W(W_) {
+        const long long start = blockIdx.x * (long long)blockDim.x + threadIdx.x, stride = (long long)gridDim.x * blockDim.x;
+        r = start / W; c = (int)(start - r * W);
+        dr = stride / W; dc = (int)(stride - dr * W);
+    }
+    __device__ __forceinline__ void next() { r += dr; c += dc; if (c >= W) { c -= W; ++r; } }
+};
+
 struct SumVal {        // plain column sums of a [M,C] matrix
     const float* x; long long ld;
     __device__ void operator()(long long r, int c, float (&o)[1]) const { o[0] = __ldg(x + r * ld + c); }
@@ -83,9 +95,9 @@ __global__ void bn_act_fwd_vec4_kernel(const float* __restrict__ y, long long ld
                                        const float* __restrict__ gamma, const float* __restrict__ beta, float slope,
                                        const float* __restrict__ addend, long long ld_add, float* __restrict__ out, long long ldo) {
     const long long total = M * (long long)C4;
-    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
-        const long long r = t / C4;
-        const int c = (int)(t - r * C4) * 4;
+    for (RowCol rc(C4); rc.r < M; rc.next()) {            // grid-stride over [M, C4] without a 64-bit division per element
+        const long long r = rc.r;
+        const int c = rc.c * 4;
         const float4 v = ld_stream4(reinterpret_cast<const float4*>(y + r * ldy + c));
         const float4 mu = __ldg(reinterpret_cast<const float4*>(mean + c)), is = __ldg(reinterpret_cast<const float4*>(invstd + c));
         const float4 g = gamma ? __ldg(reinterpret_cast<const float4*>(gamma + c)) : make_float4(1.f, 1.f, 1.f, 1.f);
@@ -151,9 +163,9 @@ __global__ void bn_act_bwd_vec4_kernel(const float* __restrict__ y, long long ld
                                        float* __restrict__ dy, long long ld_dy) {
     const long long total = M * (long long)C4;
     const float invM = 1.f / (float)M;
-    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
-        const long long r = t / C4;
-        const int c = (int)(t - r * C4) * 4;
+    for (RowCol rc(C4); rc.r < M; rc.next()) {            // grid-stride over [M, C4] without a 64-bit division per element
+        const long long r = rc.r;
+        const int c = rc.c * 4;
         const float4 yv = ld_stream4(reinterpret_cast<const float4*>(y + r * ldy + c));
         const float4 dv = ld_stream4(reinterpret_cast<const float4*>(dout + r * ldd + c));
         const float4 mu = __ldg(reinterpret_cast<const float4*>(mean + c)), is = __ldg(reinterpret_cast<const float4*>(invstd + c));
@@ -179,9 +191,9 @@ __global__ void add_rows_kernel(const float* __restrict__ a, long long lda, cons
                                 long long M, int C, int vec, float* __restrict__ out, long long ldo) {
     const int cw = vec ? C / 4 : C;
     const long long total = M * (long long)cw;
-    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
-        const long long r = t / cw;
-        const int c = (int)(t - r * cw);
+    for (RowCol rc(cw); rc.r < M; rc.next()) {
+        const long long r = rc.r;
+        const int c = rc.c;
         if (vec) {
             const float4 x = ld_stream4(reinterpret_cast<const float4*>(a + r * lda) + c), y = ld_stream4(reinterpret_cast<const float4*>(b + r * ldb) + c);
             reinterpret_cast<float4*>(out + r * ldo)[c] = make_float4(x.x + y.x, x.y + y.y, x.z + y.z, x.w + y.w);
@@ -359,9 +371,9 @@ __global__ void vecnonlin_fwd_vec4_kernel(const float* __restrict__ v, long long
                                           const float* __restrict__ gamma, const float* __restrict__ beta,
                                           const float* __restrict__ bias, float* __restrict__ out, long long ldo) {
     const long long total = M * (long long)C4;
-    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
-        const long long r = t / C4;
-        const int c = (int)(t - r * C4) * 4;
+    for (RowCol rc(C4); rc.r < M; rc.next()) {            // grid-stride over [M, C4] without a 64-bit division per element
+        const long long r = rc.r;
+        const int c = rc.c * 4;
         const float4 a = ld_stream4(reinterpret_cast<const float4*>(v + (2 * r) * ldv + c));
         const float4 b = ld_stream4(reinterpret_cast<const float4*>(v + (2 * r + 1) * ldv + c));
         const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
@@ -432,9 +444,9 @@ __global__ void vecnonlin_bwd_vec4_kernel(const float* __restrict__ v, long long
     const int C4 = C >> 2;
     const long long total = M * (long long)C4;
     const float invM = 1.f / (float)M;
-    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
-        const long long r = t / C4;
-        const int c = (int)(t - r * C4) * 4;
+    for (RowCol rc(C4); rc.r < M; rc.next()) {            // grid-stride over [M, C4] without a 64-bit division per element
+        const long long r = rc.r;
+        const int c = rc.c * 4;
         const float4 a = ld_stream4(reinterpret_cast<const float4*>(v + (2 * r) * ldv + c));
         const float4 b = ld_stream4(reinterpret_cast<const float4*>(v + (2 * r + 1) * ldv + c));
         const float4 da = ld_stream4(reinterpret_cast<const float4*>(dout + (2 * r) * ldd + c));
