@@ -374,7 +374,7 @@ def run_cuda_arm(args):
                           '(whose dense peak is half the bf16 peak)') if mode == 3 else None,
                     executed_tf32_tflops=round(ach * (3 if mode == 3 else 1), 2),
                     algorithmic_bytes_per_launch=round(tr['bytes'] / max(tr['launches'], 1)),
-                    tensor_pipe_active_pct_ncu=ncu.get('tensor_pipe_active_pct_time_weighted'))
+                    tensor_busy_share_in_kernel=ncu.get('in_kernel_mma_share_large_layers'))
     else:
         ach = tr['bytes'] / (tr['ms'] / 1000) / 1e9
         roof = dict(bound='hbm', kernel=KERNEL_OF.get(top, top), achieved=round(ach, 1), peak=pk['hbm'], unit='GB/s',
