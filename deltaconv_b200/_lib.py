@@ -71,6 +71,7 @@ _SIGNATURES = {
     'dc_set_gemm_tma_store': [_I],
     'dc_set_gemm_pair': [_I],
     'dc_set_gemm_trace': [_P],
+    'dc_set_gemm_debug': [_I, _I],
     'dc_gemm_ws_bytes': [_L, _L, _L],
     'dc_gemm_tc_raw': [_P, _L, _I, _P, _L, _I, _P, _L, _I, _L, _P, _L, _P, _Z, _P],
     'dc_linear_fwd': [_P, _L, _P, _L, _P, _L, _I, _I, _P, _L, _P, _Z, _P],

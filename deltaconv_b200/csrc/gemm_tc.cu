@@ -36,6 +36,8 @@ struct TcArgs {
     int kb_per_split;       // k-blocks per grid.z slice
     float* partial;         // [splits][M][N] when split-K
     int keep_raw_hi;        // 1: leave the raw fp32 tile as the 'hi' B operand (valid iff the MMA truncates fp32 -> tf32)
+    int extra_mma;          // measurement only (dc_set_gemm_debug): extra copies of every k-block's MMAs; results are then garbage
+    int wide_mma;           // measurement only: the extra copies use N = 256 per instruction
     int tma_store;          // 1: the epilogue stages 32 x 32 blocks in shared memory and writes them with TMA (tmC is valid)
     long long* trace;       // debug: [2 CTAs][8 events][256 k-blocks] clock64 stamps of CTA 0 and its peer (pair kernel), or null
 };
@@ -254,7 +256,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const __grid_con
                 tc_fence_after();
                 {
                     if (TS)
-                        for (int rep = 0; rep < (g.keep_raw_hi >> 8); ++rep)      // debug: extra copies of the MMAs (measures the tensor rate)
+                        for (int rep = 0; rep < g.extra_mma; ++rep)               // measurement only: extra copies of the MMAs (tensor rate)
 #pragma unroll
                             for (int kk = 0; kk < TC_BK / 8; ++kk) {
                                 const uint32_t b_off = B_MN ? kk * 1024u : kk * 32u;
@@ -664,14 +666,14 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) tc_pair_gemm_kernel(const __gr
                     TC_TRACE(2, it);
                     const uint64_t db0 = umma_desc(slot_b(sb), b_lbo, b_sbo, b_lt), dl0 = umma_desc(slot_b_lo(sb), b_lbo, b_sbo, b_lt);
                     const uint32_t ta0 = tmem_base + TMEM_A0 + (uint32_t)q * (64u * PK);
-                    for (int rep = 0; rep < (g.keep_raw_hi >> 8); ++rep)      // debug: extra copies of the MMAs (measures the tensor rate)
+                    for (int rep = 0; rep < g.extra_mma; ++rep)               // measurement only: extra copies of the MMAs (tensor rate)
 #pragma unroll
                         for (int kk = 0; kk < PK * (TC_BK / 8); ++kk) {
                             const uint64_t adv = (uint64_t)(((kk >> 2) * BH_BYTES + (B_MN ? (kk & 3) * 1024u : (kk & 3) * 32u)) >> 4);
                             const uint32_t ta_hi = ta0 + (uint32_t)(kk >> 2) * 64u + (uint32_t)(kk & 3) * 8u;
-                            // debug bit 4: N = 256 per instruction (reads past the B half and writes both accumulators: timing only)
-                            const uint32_t idx = (g.keep_raw_hi & 4) ? ((IDESC & ~(0x3fu << 17)) | ((256u >> 3) << 17)) : IDESC;
-                            const uint32_t tacc = (g.keep_raw_hi & 4) ? tmem_base : tmem_acc;
+                            // wide_mma: N = 256 per instruction (reads past the B half and writes both accumulators: timing only)
+                            const uint32_t idx = g.wide_mma ? ((IDESC & ~(0x3fu << 17)) | ((256u >> 3) << 17)) : IDESC;
+                            const uint32_t tacc = g.wide_mma ? tmem_base : tmem_acc;
                             umma2_tf32_ts(tacc, ta_hi, db0 + adv, idx, 1u);
                             umma2_tf32_ts(tacc, ta_hi + 32u, db0 + adv, idx, 1u);
                             umma2_tf32_ts(tacc, ta_hi, db0 + adv, idx, 1u);
@@ -914,6 +916,7 @@ bool make_out_map(CUtensorMap* map, float* ptr, long long N, long long M, long l
               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+int g_tc_extra_mma = 0, g_tc_wide_mma = 0;   // measurement only (dc_set_gemm_debug)
 long long* g_tc_trace = nullptr;   // debug: device buffer of 8 x 256 clock stamps (dc_set_gemm_trace)
 int g_tc_tma_store = 1;     // epilogue through shared memory + TMA stores (0 = row-per-lane direct stores)
 int g_tc_keep_raw_hi = 1;   // B_hi is the raw fp32 tile: the MMA truncates fp32 -> tf32 on read (measured bit-identical to an explicit
@@ -1008,6 +1011,13 @@ extern "C" int dc_set_gemm_tma_store(int v) { g_tc_tma_store = v; return DC_OK; 
 extern "C" int dc_set_gemm_pair(int v) { g_tc_pair = v; return DC_OK; }
 // debug: device buffer (8 x 256 int64) that CTA 0 of the pair kernel fills with clock64 stamps of its pipeline events; null = off
 extern "C" int dc_set_gemm_trace(void* buf) { g_tc_trace = (long long*)buf; return DC_OK; }
+// measurement only: issue `extra_mma` additional copies of every k-block's MMAs (wide != 0: with N = 256 per instruction, pair
+// kernel); the products are garbage while this is set — scripts/diag_tc_rate.py derives the cost of one tcgen05.mma from the slope
+extern "C" int dc_set_gemm_debug(int extra_mma, int wide) {
+    DC_REQUIRE(extra_mma >= 0 && extra_mma <= 64, "dc_set_gemm_debug: extra_mma must be in [0,64]");
+    g_tc_extra_mma = extra_mma; g_tc_wide_mma = wide != 0;
+    return DC_OK;
+}
 
 // Split-K factor for an M x N output with reduction K.  Cost model in units of one k-block (128 x BN x 32) of main loop: the
 // persistent grid runs ceil(units / SMs) waves of (k-blocks per split + pipeline fill), the reduce pass costs a launch plus a
@@ -1055,6 +1065,8 @@ int dc_tc_gemm(const float* A, long long lda, int a_mn, const float* B, long lon
     TcArgs g = {};
     g.C = C; g.ldc = ldc; g.bias = bias; g.M = (int)M; g.N = N; g.K = (int)K;
     g.keep_raw_hi = g_tc_keep_raw_hi;
+    g.extra_mma = g_tc_extra_mma;
+    g.wide_mma = g_tc_wide_mma;
     g.trace = g_tc_trace;
     CUtensorMap tmC;
     int splits = 1;

@@ -229,6 +229,8 @@ int dc_set_gemm_tma_store(int v);
 int dc_set_gemm_pair(int v);
 /* debug: device buffer of 8 x 256 int64 that CTA 0 of the pair kernel fills with clock stamps of its pipeline events (NULL = off) */
 int dc_set_gemm_trace(void* device_buffer_or_null);
+/* measurement only: extra copies of every k-block's MMAs (wide: N = 256 per instruction); products are garbage while set */
+int dc_set_gemm_debug(int extra_mma, int wide);
 size_t dc_gemm_ws_bytes(int64_t M, int64_t N, int64_t K);
 /* The tensor-core product itself, C[M,N] = op(A) op(B)^T: a_mn/b_mn = 0 when the reduction index is contiguous
  * ([M,K] / [N,K] storage), 1 when the M / N index is contiguous ([K,M] / [K,N] storage).  Returns 1 if the shape is

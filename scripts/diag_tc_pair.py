@@ -32,7 +32,7 @@ for (M, N, K, a_mn, b_mn, with_bias) in shapes:
     ref = a.double() @ b.double().t() + (bias.double() if with_bias else 0)
     out = []
     for tma in (0, 1):  # here: CTA pairs off / on
-        lib.dc_set_gemm_pair(tma); lib.dc_set_gemm_keep_raw_hi(1 + int(os.environ.get('DC_DBG', '0')))
+        lib.dc_set_gemm_pair(tma)
         ld = N + (4 if M < 2000 else 0)                       # a padded output pitch on the small cases
         Cbuf = torch.full((M, ld), float('nan'), device=dev)
         f = lambda: _lib.call('dc_gemm_tc_raw', A.data_ptr(), A.stride(0), a_mn, B.data_ptr(), B.stride(0), b_mn, bias.data_ptr() if with_bias else None,

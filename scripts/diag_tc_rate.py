@@ -1,5 +1,5 @@
 """Tensor rate of the two 3xTF32 kernels: time of the 32768 x 1024 x 512 product with 0 / 2 / 4 extra copies of every k-block's
-12 MMAs (dc_set_gemm_keep_raw_hi bits 8+, debug); the slope is the cost of one tcgen05.mma in the running pipeline."""
+12 MMAs (dc_set_gemm_debug); the slope is the cost of one tcgen05.mma in the running pipeline."""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
@@ -22,9 +22,9 @@ for pair in (0, 1):
     lib.dc_set_gemm_pair(pair)
     res = []
     for rep in (0, 2, 4):
-        lib.dc_set_gemm_keep_raw_hi(1 + 256 * rep + int(os.environ.get('DC_DBG', '0')))
+        lib.dc_set_gemm_debug(rep, int(os.environ.get('DC_WIDE', '0')))
         res.append(t_ms())
-    lib.dc_set_gemm_keep_raw_hi(1)
+    lib.dc_set_gemm_debug(0, 0)
     # k-blocks executed per SM: tiles per SM (ceil) x 16
     per_sm_kb = -(-(256 * 8) // 148) * 16
     slope_us = (res[2] - res[0]) * 1000 / (per_sm_kb * 48)

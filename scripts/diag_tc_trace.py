@@ -9,13 +9,14 @@ ws = torch.zeros(256 << 20, dtype=torch.uint8, device=dev)
 M, N, K = 32768, 1024, 512
 a = torch.randn(M, K, device=dev); b = torch.randn(N, K, device=dev); C = torch.empty(M, N, device=dev)
 f = lambda: _lib.call('dc_gemm_tc_raw', a.data_ptr(), K, 0, b.data_ptr(), K, 0, None, M, N, K, C.data_ptr(), N, ws.data_ptr(), ws.numel())
-lib.dc_set_gemm_keep_raw_hi(1 + 256 * int(os.environ.get('DC_REP', '0')) + int(os.environ.get('DC_DBG', '0')))
+lib.dc_set_gemm_debug(int(os.environ.get('DC_REP', '0')), 0)
 lib.dc_set_gemm_pair(1)
 for _ in range(3): f()
 trace = torch.zeros(2, 8, 256, dtype=torch.int64, device=dev)
 lib.dc_set_gemm_trace(trace.data_ptr())
 f(); torch.cuda.synchronize()
 lib.dc_set_gemm_trace(None)
+lib.dc_set_gemm_debug(0, 0)
 tt = trace.cpu()
 sync0, sync1 = int(tt[0, 7, 255]), int(tt[1, 7, 255])
 tt[:, 7, 255] = 0
