@@ -97,6 +97,7 @@ def _w_ediff(a): N, k, C = a[1], a[2], a[3]; return N * (4 * k + 4 * C + 4 * k *
 def _w_segmax(a): N, k, C = a[1], a[2], a[3]; return N * C * (4 * k + 5), 0
 def _w_segmax_t(a): N, k, C = a[2], a[3], a[4]; return N * C * (4 * k + 5), 0
 def _w_pool(a): return 0, 0
+def _w_sgd(a): return a[3] * 20, 0                               # p, buf read and written, g read
 def _w_bnpool(a): return CLOUDS * POINTS * a[4] * 4, 0          # y read once, only [B,2C] written
 def _w_bnpool_t(a): M, C = a[2], a[3]; return M * C * 8, 0    # y read, dy written
 
@@ -108,6 +109,7 @@ WORK = {
     'dc_hodge_fwd': (_w_hodge, 'spmm'), 'dc_hodge_bwd': (_w_hodge_t, 'spmm'),
     'dc_gathermax_fwd': (_w_gmax, 'gathermax'), 'dc_gathermax_bwd': (_w_gmax_t, 'gathermax'),
     'dc_bn_act_pool_fwd': (_w_bnpool, 'batchnorm'), 'dc_bn_act_pool_bwd': (_w_bnpool_t, 'batchnorm'),
+    'dc_sgd_step': (_w_sgd, 'optimizer'),
     'dc_bn_stats': (_w_stats, 'batchnorm'), 'dc_bn_act_fwd': (_w_bnf, 'batchnorm'), 'dc_bn_act_bwd': (_w_bnb, 'batchnorm'),
     'dc_vecnonlin_fwd': (_w_vnf, 'vecnonlin'), 'dc_vecnonlin_bwd': (_w_vnb, 'vecnonlin'),
     'dc_linear_fwd': (_w_lin, 'gemm'), 'dc_linear_bwd_input': (_w_linb, 'gemm'), 'dc_linear_bwd_weight': (_w_linb, 'gemm'),
@@ -230,7 +232,7 @@ def run_cuda_arm(args):
     import torch.distributed as dist
     import deltaconv_b200 as D
     from deltaconv_b200 import _lib
-    from deltaconv_b200.parallel import FlatGradients
+    from deltaconv_b200.parallel import FlatGradients, FlatSGD
 
     world = int(os.environ.get('WORLD_SIZE', '1'))
     rank = int(os.environ.get('RANK', '0'))
@@ -247,7 +249,7 @@ def run_cuda_arm(args):
     torch.manual_seed(1)
     model = D.utils.fill_deterministic(D.models.DeltaNetClassification(3, CLASSES, num_neighbors=K_NN), 1).to(dev).train()
     flat = FlatGradients(model.parameters())
-    opt = torch.optim.SGD(model.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4)
+    opt = FlatSGD(flat, lr=0.1, momentum=0.9, weight_decay=1e-4)          # torch.optim.SGD's update as one kernel on flat buffers
     host = D.utils.synthetic_batch(CLOUDS, POINTS, config=2, rank=rank, num_classes=CLASSES).pin_memory()
     host._num_clouds, host._max_points = CLOUDS, POINTS
     resident = host.to(dev)

@@ -69,19 +69,6 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         }
     } while (!done);
 }
-// One non-blocking probe of a barrier phase.  mbarrier operations travel through the same queue as the shared-memory loads
-// and stores of the converter / epilogue warps (measured: ~270 cycles for a probe of a phase that completed long ago), so the
-// MMA-issuing thread probes the NEXT k-block's barrier before it issues the current k-block's MMAs and reads the answer after.
-__device__ __forceinline__ uint32_t mbar_try(uint32_t bar, uint32_t parity) {
-    uint32_t done;
-    asm volatile(
-        "{\n\t"
-        ".reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t"
-        "}" : "=r"(done) : "r"(bar), "r"(parity) : "memory");
-    return done;
-}
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
     asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
                  ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
@@ -502,7 +489,8 @@ __device__ __forceinline__ void umma2_commit(uint32_t bar) {
 //   TMEM ring (PT_SLOTS x 64 columns): A hi / lo; released by the MMAs.
 // The MMA-issuing thread is the clock of the whole kernel: a tcgen05.mma occupies it for as long as the tensor pipe takes to
 // accept the instruction (~54 cycles at M = 256, N = 128, measured), so every other instruction it executes is tensor idle
-// time.  It therefore runs alone (no warp-wide waits), and signals "the MMAs of k-block it have completed" with a single
+// time (a probe of the next hand-off's barrier issued ahead of the MMAs does not help: it queues behind them).  It therefore
+// runs alone (no warp-wide waits), and signals "the MMAs of k-block it have completed" with a single
 // commit per k-block on done[it % PD_SLOTS], which both the converters (tensor-memory slot it % PT_SLOTS) and the B
 // producer (slot it % PB_SLOTS) wait on.
 // Every hand-off between the roles costs the MMA thread a few hundred cycles (measured ~650 per hand-off against 69 per MMA),
@@ -648,7 +636,6 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) tc_pair_gemm_kernel(const __gr
         if (leader && lane == 0) {
             uint32_t it = 0, tcount = 0;
             const uint32_t b_lbo = B_MN ? CHUNK_BYTES : 16u, b_sbo = B_MN ? 512u : 1024u, b_lt = B_MN ? 1u : 2u;
-            uint32_t peek = 0;                                     // answer of the probe of ready(it) issued one k-block earlier
             for (long long unit = first_unit; unit < num_units; unit += unit_stride, ++tcount) {
                 int m0, n0, kb_begin, nkb, z;
                 decode(unit, m0, n0, kb_begin, nkb, z);
@@ -659,10 +646,9 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) tc_pair_gemm_kernel(const __gr
                 for (int kb = 0; kb < nkb; ++kb, ++it) {
                     const int q = it % PT_SLOTS, sb = it % PB_SLOTS;
                     TC_TRACE(0, it);                                   // (rows 0/1 of the MMA thread's CTA are shared with the producers: debug only)
-                    if (!peek) mbar_wait(ready(q), (it / PT_SLOTS) & 1);   // both CTAs: A in tensor memory, B lo written
+                    mbar_wait(ready(q), (it / PT_SLOTS) & 1);          // both CTAs: A in tensor memory, B lo written
                     TC_TRACE(1, it);
                     tc_fence_after();
-                    peek = mbar_try(ready((it + 1) % PT_SLOTS), ((it + 1) / PT_SLOTS) & 1);   // in flight while the MMAs below issue
                     TC_TRACE(2, it);
                     const uint64_t db0 = umma_desc(slot_b(sb), b_lbo, b_sbo, b_lt), dl0 = umma_desc(slot_b_lo(sb), b_lbo, b_sbo, b_lt);
                     const uint32_t ta0 = tmem_base + TMEM_A0 + (uint32_t)q * (64u * PK);

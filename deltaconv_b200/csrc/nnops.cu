@@ -203,6 +203,30 @@ __global__ void add_rows_kernel(const float* __restrict__ a, long long lda, cons
     }
 }
 
+// ---- SGD with momentum and weight decay on flat buffers (torch.optim.SGD, dampening 0, no Nesterov) ----------------
+// g' = g + wd * p;  buf = mu * buf + g';  p -= lr * buf.   A zero-initialised buf makes the first step buf = g' as in torch.
+// lr is read from device memory so that a captured step follows learning-rate schedules.
+__global__ void sgd_step_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ buf, long long n,
+                                const float* __restrict__ lr_ptr, float momentum, float weight_decay) {
+    const float lr = __ldg(lr_ptr);
+    const long long n4 = n >> 2;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < n4; t += (long long)gridDim.x * blockDim.x) {
+        float4 pv = reinterpret_cast<float4*>(p)[t], bv = reinterpret_cast<float4*>(buf)[t];
+        const float4 gv = ld_stream4(reinterpret_cast<const float4*>(g) + t);
+        bv.x = fmaf(momentum, bv.x, fmaf(weight_decay, pv.x, gv.x)); pv.x = fmaf(-lr, bv.x, pv.x);
+        bv.y = fmaf(momentum, bv.y, fmaf(weight_decay, pv.y, gv.y)); pv.y = fmaf(-lr, bv.y, pv.y);
+        bv.z = fmaf(momentum, bv.z, fmaf(weight_decay, pv.z, gv.z)); pv.z = fmaf(-lr, bv.z, pv.z);
+        bv.w = fmaf(momentum, bv.w, fmaf(weight_decay, pv.w, gv.w)); pv.w = fmaf(-lr, bv.w, pv.w);
+        reinterpret_cast<float4*>(buf)[t] = bv;
+        reinterpret_cast<float4*>(p)[t] = pv;
+    }
+    for (long long t = (n4 << 2) + blockIdx.x * (long long)blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x) {
+        const float b = fmaf(momentum, buf[t], fmaf(weight_decay, p[t], g[t]));
+        buf[t] = b;
+        p[t] = fmaf(-lr, b, p[t]);
+    }
+}
+
 // ---- BatchNorm + activation fused with the global pools, backward -------------------------------
 // The gradient of [max | mean] pooling w.r.t. the pooled activation at (r, c) is (r == arg[b,c] ? d_max[b,c] : 0) + d_mean[b,c] / n_b
 // (same expression as pool_bwd): it is rebuilt on the fly.  Work is split by cloud so that the [B,C] quantities are loaded once per
@@ -989,6 +1013,15 @@ extern "C" int dc_pool_bwd(const int32_t* cloud_ptr, int B, int N, int C, const 
         pool_bwd_cloud_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(cloud_ptr, C, arg, d_max_or_null, ld_dmax, d_mean_or_null, ld_dmean, dx, ld_dx);
     }
     return dc_check_launch("dc_pool_bwd");
+}
+
+extern "C" int dc_sgd_step(float* params, const float* grads, float* momentum_buf, int64_t n, const float* lr_device,
+                           float momentum, float weight_decay, void* stream) {
+    DC_REQUIRE(lr_device != nullptr, "dc_sgd_step: the learning rate is read from device memory");
+    DC_REQUIRE(all_aligned16(params, grads, momentum_buf), "dc_sgd_step: buffers must be 16-byte aligned");
+    if (n <= 0) return DC_OK;
+    sgd_step_kernel<<<elementwise_grid((n + 3) / 4), 256, 0, (cudaStream_t)stream>>>(params, grads, momentum_buf, n, lr_device, momentum, weight_decay);
+    return dc_check_launch("dc_sgd_step");
 }
 
 extern "C" int dc_add_rows(const float* a, int64_t lda, const float* b, int64_t ldb, int64_t M, int C, float* out, int64_t ldo, void* stream) {

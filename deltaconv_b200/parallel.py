@@ -28,10 +28,12 @@ class FlatGradients:
         if not self.params:
             raise ValueError("no trainable parameters")
         self.flat = None
+        self.packed = False          # True between pack() and the next zero(): `flat` holds this step's gradients
 
     def zero(self):
         for p in self.params:
             p.grad = None
+        self.packed = False
 
     def _world(self, group):
         if not (dist.is_available() and dist.is_initialized()):
@@ -54,6 +56,7 @@ class FlatGradients:
             n = p.numel()
             p.grad = self.flat[offset:offset + n].view_as(p)
             offset += n
+        self.packed = True
         return self.flat
 
     def all_reduce(self, group=None, average=True, sources=None):
@@ -69,3 +72,69 @@ class FlatGradients:
 
     def nbytes(self):
         return sum(p.numel() * p.element_size() for p in self.params)
+
+
+class FlatSGD:
+    """torch.optim.SGD(lr, momentum, weight_decay) — the optimizer of experiments/train_*.py — as ONE kernel per step
+    (`dc_sgd_step`) over flat parameter / gradient / momentum buffers instead of a few foreach launches over ~130
+    tensors.  The parameters that receive gradients become views of one flat buffer at the first step (state dicts are
+    unaffected); gradients come from `FlatGradients.pack()` (already packed when they were all-reduced).  The learning
+    rate lives in a device scalar, so a CUDA-graph-captured step follows `set_lr` / `param_groups[0]['lr']` changes."""
+
+    def __init__(self, flat, lr, momentum=0.0, weight_decay=0.0):
+        if not isinstance(flat, FlatGradients):
+            raise TypeError("FlatSGD works on a FlatGradients object")
+        self.flat = flat
+        self.param_groups = [dict(params=flat.params, lr=float(lr), momentum=float(momentum), weight_decay=float(weight_decay))]
+        self._live = None
+        self._p = self._buf = self._lr = None
+        self._lr_value = None
+
+    def _materialise(self):
+        live = [p for p in self.flat.params if p.grad is not None]
+        if not live or not live[0].is_cuda:
+            from ._lib import DeltaConvLibraryError
+            raise DeltaConvLibraryError("FlatSGD needs CUDA parameters with gradients (there is no CPU path)")
+        with torch.no_grad():
+            self._p = torch.cat([p.data.reshape(-1) for p in live])
+            offset = 0
+            for p in live:
+                n = p.numel()
+                p.data = self._p[offset:offset + n].view_as(p)
+                offset += n
+        self._buf = torch.zeros_like(self._p)
+        self._lr = torch.empty(1, dtype=torch.float32, device=self._p.device)
+        self._live = live
+
+    def set_lr(self, lr):
+        self.param_groups[0]['lr'] = float(lr)
+        if self._lr is not None and self._lr_value != float(lr):
+            self._lr.fill_(float(lr))
+            self._lr_value = float(lr)
+
+    def zero_grad(self, set_to_none=True):
+        self.flat.zero()
+
+    @torch.no_grad()
+    def step(self):
+        from ._lib import call, DeltaConvLibraryError
+        g = self.flat.flat if self.flat.packed else self.flat.pack()
+        if self._live is None:
+            self._materialise()
+        if g.numel() != self._p.numel():
+            raise DeltaConvLibraryError("FlatSGD: the set of parameters with gradients changed between steps")
+        group = self.param_groups[0]
+        if self._lr_value != group['lr']:
+            self._lr.fill_(group['lr'])
+            self._lr_value = group['lr']
+        call('dc_sgd_step', self._p.data_ptr(), g.data_ptr(), self._buf.data_ptr(), self._p.numel(), self._lr.data_ptr(),
+             group['momentum'], group['weight_decay'])
+
+    def state_dict(self):
+        return dict(param_groups=[{k: v for k, v in self.param_groups[0].items() if k != 'params'}],
+                    momentum_buffer=None if self._buf is None else self._buf.clone())
+
+    def load_state_dict(self, state):
+        self.param_groups[0].update(state['param_groups'][0])
+        if state.get('momentum_buffer') is not None and self._buf is not None:
+            self._buf.copy_(state['momentum_buffer'])

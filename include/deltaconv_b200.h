@@ -207,6 +207,10 @@ int dc_bn_act_pool_bwd(const float* y, int64_t ldy, int64_t M, int C, const int3
                        const int32_t* arg, const float* d_max_or_null, int64_t ld_dmax, const float* d_mean_or_null, int64_t ld_dmean,
                        const float* mean, const float* invstd, const float* gamma_or_null, const float* beta_or_null, float slope,
                        float* d_gamma, float* d_beta, float* dy, int64_t ld_dy, void* ws, size_t ws_bytes, void* stream);
+/* One SGD step (momentum, weight decay; dampening 0, no Nesterov — torch.optim.SGD as experiments/train_*.py configure it) on flat
+ * parameter / gradient / momentum buffers of n floats: buf = momentum*buf + grad + weight_decay*p; p -= lr*buf.  lr is a device scalar. */
+int dc_sgd_step(float* params, const float* grads, float* momentum_buf, int64_t n, const float* lr_device,
+                float momentum, float weight_decay, void* stream);
 /* out = a + b on [M,C] column slices of wider row-major buffers: the sum of the two gradients of [div v | curl v], which feeds both
  * the scalar concatenation (deltaconv.py:57) and the Hodge Laplacian of the vector stream (deltaconv.py:66) */
 int dc_add_rows(const float* a, int64_t lda, const float* b, int64_t ldb, int64_t M, int C, float* out, int64_t ldo, void* stream);

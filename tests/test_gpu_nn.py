@@ -555,3 +555,44 @@ def test_gemm_kernel_variants_agree(switch):
     finally:
         lib.dc_set_gemm_pair(1)
         lib.dc_set_gemm_tma_store(1)
+
+
+def test_flat_sgd_matches_torch_sgd_eager_and_graphed():
+    """FlatSGD (one dc_sgd_step launch on flat buffers) follows torch.optim.SGD(momentum, weight_decay) step for step, eagerly
+    and inside a captured training step; a learning-rate change reaches the captured kernel through the device scalar."""
+    D = dc()
+    from deltaconv_b200.parallel import FlatGradients, FlatSGD
+    from deltaconv_b200.utils.losses import calc_loss
+    data = D.utils.synthetic_batch(4, 256, config=2, num_classes=10).to(DEV)
+    data._num_clouds, data._max_points = 4, 256
+    nets = []
+    for _ in range(3):
+        torch.manual_seed(0)
+        nets.append(no_dropout(D.utils.fill_deterministic(D.models.DeltaNetClassification(3, 10, conv_channels=[16, 32]), 5)).to(DEV).train())
+    ref_net, flat_net, graph_net = nets
+    ref_flat = FlatGradients(ref_net.parameters())
+    ref_opt = torch.optim.SGD(ref_net.parameters(), lr=0.05, momentum=0.9, weight_decay=1e-4)
+    fg = FlatGradients(flat_net.parameters())
+    opt = FlatSGD(fg, lr=0.05, momentum=0.9, weight_decay=1e-4)
+    gg = FlatGradients(graph_net.parameters())
+    gopt = FlatSGD(gg, lr=0.05, momentum=0.9, weight_decay=1e-4)
+    step = D.utils.GraphedTrainStep(graph_net, gopt, calc_loss, data, flat=gg, warmup=2)
+    lrs = [0.05, 0.05, 0.05, 0.02, 0.02]
+    for it, lr in enumerate(lrs):
+        ref_opt.param_groups[0]['lr'] = lr
+        ref_flat.zero()
+        calc_loss(ref_net(data), data.y).backward()
+        ref_opt.step()
+        opt.set_lr(lr)
+        opt.zero_grad()
+        calc_loss(flat_net(data), data.y).backward()
+        opt.step()
+        if it >= 2:                                   # the graphed net already took 2 warm-up steps at lr 0.05
+            gopt.set_lr(lr)
+            step()
+    for (n1, p1), (_, p2), (_, p3) in zip(ref_net.named_parameters(), flat_net.named_parameters(), graph_net.named_parameters()):
+        scale = p1.abs().max().item() + 1e-12
+        assert (p1 - p2).abs().max().item() < 2e-5 * scale, n1
+        assert (p1 - p3).abs().max().item() < 2e-5 * scale, n1
+    sd = flat_net.state_dict()                        # parameters are views of one flat buffer: state dicts keep their shapes
+    assert all(sd[k].shape == v.shape for k, v in ref_net.state_dict().items())
