@@ -311,10 +311,27 @@ def run_cuda_arm(args):
         data = host.to(dev, non_blocking=True)
         data._num_clouds, data._max_points = CLOUDS, POINTS
         return step(data).item()
+    # Graph replay: the next batch's host->device copy runs on a side stream while the current step computes (prefetch /
+    # commit), and each step's loss is copied to pinned host memory asynchronously and read one step later — the usual
+    # input pipeline of a training loop.  Every step still moves its own inputs H2D and its own loss D2H inside the timed region.
+    loss_host = torch.empty(2, dtype=torch.float32).pin_memory()
+    loss_ready = [torch.cuda.Event(), torch.cuda.Event()]
+    pipe = dict(i=0, last=None)
     def e2e_graph_step():
-        graphed.load(host)
-        return graphed().item()
+        i = pipe['i']
+        graphed.commit()
+        loss = graphed()
+        loss_host[i & 1].copy_(loss, non_blocking=True)
+        loss_ready[i & 1].record()
+        graphed.prefetch(host)
+        if i > 0:
+            loss_ready[(i - 1) & 1].synchronize()
+            pipe['last'] = float(loss_host[(i - 1) & 1])
+        pipe['i'] = i + 1
+        return pipe['last']
     e2e_fn = e2e_graph_step if graphed else e2e_step
+    if graphed:
+        graphed.prefetch(host)
     for _ in range(2):
         e2e_fn()
     e2e_ms = timed(e2e_fn, args.steps)
@@ -403,7 +420,8 @@ def run_cuda_arm(args):
                             launch='CUDA-graph replay of the whole step' if graphed else 'eager (one Python launch per kernel)',
                             eager_ms_per_step=round(eager_ms / args.steps, 4), e2e_eager_ms_per_step=round(e2e_eager_ms / args.steps, 4)),
                 e2e=dict(value=round(e2e_value, 2), unit='clouds/s', h2d_bytes_per_step=host.nbytes(), d2h_bytes_per_step=4,
-                         ms_per_step=round(e2e_ms / args.steps, 4)),
+                         ms_per_step=round(e2e_ms / args.steps, 4),
+                         pipeline='next batch copied on a side stream during the step, loss read one step later' if graphed else 'serial'),
                 gpu_launches=launches, roofline=roof, cpu_baseline=cpu, clocks=clocks,
                 kernels=kernels,
                 hbm_bound_kernels=dict(gbps=round(hbm_bytes / (hbm_ms / 1000) / 1e9, 1) if hbm_ms else None,

@@ -38,6 +38,7 @@ class GraphedTrainStep:
         self.graph_fb = torch.cuda.CUDAGraph()
         self.graph_opt = None
         self._graph_grads = None
+        self._stage = None
         if self.distributed:
             # the collective stays outside the graphs: fwd+bwd graph -> pack + NCCL all-reduce -> optimizer graph.
             # The gradients a replay produces live in graph memory: keep the tensors so every step can pack them.
@@ -64,6 +65,29 @@ class GraphedTrainStep:
         for name, dst in self.static.__dict__.items():
             if torch.is_tensor(dst):
                 dst.copy_(getattr(batch, name), non_blocking=True)
+
+    def prefetch(self, batch):
+        """Start copying the NEXT batch (pinned host memory) into device staging buffers on a side stream, so that the
+        transfer overlaps the step that is running; `commit()` then moves it into the static inputs device-to-device."""
+        if self._stage is None:
+            self._stage = {name: torch.empty_like(t) for name, t in self.static.__dict__.items() if torch.is_tensor(t)}
+            self._copy_stream = torch.cuda.Stream()
+            self._staged = torch.cuda.Event()
+            self._consumed = torch.cuda.Event()
+            self._consumed.record()
+        self._copy_stream.wait_event(self._consumed)                 # the previous commit() has read the staging buffers
+        with torch.cuda.stream(self._copy_stream):
+            for name, dst in self._stage.items():
+                dst.copy_(getattr(batch, name), non_blocking=True)
+            self._staged.record()
+
+    def commit(self):
+        """Make the prefetched batch the input of the next replay (waits for its transfer on the device, not the host)."""
+        cur = torch.cuda.current_stream()
+        cur.wait_event(self._staged)
+        for name, src in self._stage.items():
+            getattr(self.static, name).copy_(src, non_blocking=True)
+        self._consumed.record(cur)
 
     def __call__(self):
         self.graph_fb.replay()

@@ -394,8 +394,13 @@ def test_graphed_train_step_matches_eager():
         loss.backward()
         opt.step()
         losses_e.append(loss.item())
-    for _ in range(3):
-        step.load(data)
+    host = data.to('cpu').pin_memory()
+    for it in range(3):
+        if it == 1:                                  # side-stream prefetch + device-to-device commit instead of load()
+            step.prefetch(host)
+            step.commit()
+        else:
+            step.load(data)
         losses_g.append(step().item())
     assert losses_g == pytest.approx(losses_e[2:], rel=1e-5)
     for (n1, p1), (n2, p2) in zip(eager.named_parameters(), graphed_net.named_parameters()):
