@@ -227,6 +227,26 @@ __global__ void sgd_step_kernel(float* __restrict__ p, const float* __restrict__
     }
 }
 
+// ---- Adam on flat buffers (torch.optim.Adam: L2 weight decay added to the gradient, no amsgrad) -----------------
+// t = *step + 1;  m = b1 m + (1-b1) g;  v = b2 v + (1-b2) g^2;  p -= lr / (1 - b1^t) * m / (sqrt(v) / sqrt(1 - b2^t) + eps).
+// The step counter and the learning rate live in device memory (captured steps); adam_advance_kernel increments the counter.
+__global__ void adam_step_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
+                                 long long n, const float* __restrict__ lr_ptr, const int* __restrict__ step_ptr,
+                                 float beta1, float beta2, float eps, float weight_decay) {
+    const float t = (float)(__ldg(step_ptr) + 1);
+    const float bc1 = 1.f - powf(beta1, t), bc2_sqrt = sqrtf(1.f - powf(beta2, t));
+    const float step_size = __ldg(lr_ptr) / bc1;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const float pi = p[i];
+        const float gi = fmaf(weight_decay, pi, g[i]);
+        const float mi = fmaf(beta1, m[i], (1.f - beta1) * gi);
+        const float vi = fmaf(beta2, v[i], (1.f - beta2) * gi * gi);
+        m[i] = mi; v[i] = vi;
+        p[i] = pi - step_size * (mi / (sqrtf(vi) / bc2_sqrt + eps));
+    }
+}
+__global__ void adam_advance_kernel(int* step_ptr) { *step_ptr += 1; }
+
 // ---- BatchNorm + activation fused with the global pools, backward -------------------------------
 // The gradient of [max | mean] pooling w.r.t. the pooled activation at (r, c) is (r == arg[b,c] ? d_max[b,c] : 0) + d_mean[b,c] / n_b
 // (same expression as pool_bwd): it is rebuilt on the fly.  Work is split by cloud so that the [B,C] quantities are loaded once per
@@ -1022,6 +1042,16 @@ extern "C" int dc_sgd_step(float* params, const float* grads, float* momentum_bu
     if (n <= 0) return DC_OK;
     sgd_step_kernel<<<elementwise_grid((n + 3) / 4), 256, 0, (cudaStream_t)stream>>>(params, grads, momentum_buf, n, lr_device, momentum, weight_decay);
     return dc_check_launch("dc_sgd_step");
+}
+
+extern "C" int dc_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, const float* lr_device,
+                            int32_t* step_device, float beta1, float beta2, float eps, float weight_decay, void* stream) {
+    DC_REQUIRE(lr_device != nullptr && step_device != nullptr, "dc_adam_step: learning rate and step counter are read from device memory");
+    if (n <= 0) return DC_OK;
+    adam_step_kernel<<<elementwise_grid(n), 256, 0, (cudaStream_t)stream>>>(params, grads, exp_avg, exp_avg_sq, n, lr_device, step_device,
+                                                                           beta1, beta2, eps, weight_decay);
+    adam_advance_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(step_device);
+    return dc_check_launch_n("dc_adam_step", 2);
 }
 
 extern "C" int dc_add_rows(const float* a, int64_t lda, const float* b, int64_t ldb, int64_t M, int C, float* out, int64_t ldo, void* stream) {

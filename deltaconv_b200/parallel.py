@@ -74,18 +74,22 @@ class FlatGradients:
         return sum(p.numel() * p.element_size() for p in self.params)
 
 
-class FlatSGD:
+class FlatSGD(torch.optim.Optimizer):
     """torch.optim.SGD(lr, momentum, weight_decay) — the optimizer of experiments/train_*.py — as ONE kernel per step
     (`dc_sgd_step`) over flat parameter / gradient / momentum buffers instead of a few foreach launches over ~130
-    tensors.  The parameters that receive gradients become views of one flat buffer at the first step (state dicts are
-    unaffected); gradients come from `FlatGradients.pack()` (already packed when they were all-reduced).  The learning
-    rate lives in a device scalar, so a CUDA-graph-captured step follows `set_lr` / `param_groups[0]['lr']` changes."""
+    tensors.  A `torch.optim.Optimizer` (learning-rate schedulers attach to it as to SGD).  The parameters that receive
+    gradients become views of one flat buffer at the first step (state dicts are unaffected); gradients come from
+    `FlatGradients.pack()` (already packed when they were all-reduced).  The learning rate lives in a device scalar, so
+    a CUDA-graph-captured step follows schedulers: `sync_lr()` (called by GraphedTrainStep before every replay) copies
+    `param_groups[0]['lr']` to the device when it changed."""
 
     def __init__(self, flat, lr, momentum=0.0, weight_decay=0.0):
         if not isinstance(flat, FlatGradients):
             raise TypeError("FlatSGD works on a FlatGradients object")
+        super().__init__(flat.params, dict(lr=float(lr), momentum=float(momentum), weight_decay=float(weight_decay)))
+        if len(self.param_groups) != 1:
+            raise ValueError("FlatSGD supports one parameter group")
         self.flat = flat
-        self.param_groups = [dict(params=flat.params, lr=float(lr), momentum=float(momentum), weight_decay=float(weight_decay))]
         self._live = None
         self._p = self._buf = self._lr = None
         self._lr_value = None
@@ -106,29 +110,36 @@ class FlatSGD:
         self._lr = torch.empty(1, dtype=torch.float32, device=self._p.device)
         self._live = live
 
+    def sync_lr(self):
+        lr = float(self.param_groups[0]['lr'])
+        if self._lr is not None and self._lr_value != lr:
+            self._lr.fill_(lr)
+            self._lr_value = lr
+
     def set_lr(self, lr):
         self.param_groups[0]['lr'] = float(lr)
-        if self._lr is not None and self._lr_value != float(lr):
-            self._lr.fill_(float(lr))
-            self._lr_value = float(lr)
+        self.sync_lr()
 
     def zero_grad(self, set_to_none=True):
         self.flat.zero()
 
     @torch.no_grad()
-    def step(self):
+    def step(self, closure=None):
         from ._lib import call, DeltaConvLibraryError
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
         g = self.flat.flat if self.flat.packed else self.flat.pack()
         if self._live is None:
             self._materialise()
         if g.numel() != self._p.numel():
             raise DeltaConvLibraryError("FlatSGD: the set of parameters with gradients changed between steps")
+        self.sync_lr()
         group = self.param_groups[0]
-        if self._lr_value != group['lr']:
-            self._lr.fill_(group['lr'])
-            self._lr_value = group['lr']
         call('dc_sgd_step', self._p.data_ptr(), g.data_ptr(), self._buf.data_ptr(), self._p.numel(), self._lr.data_ptr(),
-             group['momentum'], group['weight_decay'])
+             float(group['momentum']), float(group['weight_decay']))
+        return loss
 
     def state_dict(self):
         return dict(param_groups=[{k: v for k, v in self.param_groups[0].items() if k != 'params'}],
@@ -138,3 +149,49 @@ class FlatSGD:
         self.param_groups[0].update(state['param_groups'][0])
         if state.get('momentum_buffer') is not None and self._buf is not None:
             self._buf.copy_(state['momentum_buffer'])
+
+
+class FlatAdam(FlatSGD):
+    """torch.optim.Adam(lr, betas, eps, weight_decay) (experiments/train_shapeseg.py:82) on the flat buffers: one
+    `dc_adam_step` call per step; step counter and learning rate are device scalars, so captured steps stay correct."""
+
+    def __init__(self, flat, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0):
+        if not isinstance(flat, FlatGradients):
+            raise TypeError("FlatAdam works on a FlatGradients object")
+        torch.optim.Optimizer.__init__(self, flat.params, dict(lr=float(lr), betas=(float(betas[0]), float(betas[1])), eps=float(eps),
+                                                               weight_decay=float(weight_decay)))
+        self.flat = flat
+        self._live = None
+        self._p = self._buf = self._lr = None
+        self._lr_value = None
+        self._v = self._step = None
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        from ._lib import call, DeltaConvLibraryError
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        g = self.flat.flat if self.flat.packed else self.flat.pack()
+        if self._live is None:
+            self._materialise()
+            self._v = torch.zeros_like(self._p)
+            self._step = torch.zeros(1, dtype=torch.int32, device=self._p.device)
+        if g.numel() != self._p.numel():
+            raise DeltaConvLibraryError("FlatAdam: the set of parameters with gradients changed between steps")
+        self.sync_lr()
+        group = self.param_groups[0]
+        call('dc_adam_step', self._p.data_ptr(), g.data_ptr(), self._buf.data_ptr(), self._v.data_ptr(), self._p.numel(),
+             self._lr.data_ptr(), self._step.data_ptr(), group['betas'][0], group['betas'][1], group['eps'], group['weight_decay'])
+        return loss
+
+    def state_dict(self):
+        return dict(param_groups=[{k: v for k, v in self.param_groups[0].items() if k != 'params'}],
+                    exp_avg=None if self._buf is None else self._buf.clone(), exp_avg_sq=None if self._v is None else self._v.clone(),
+                    step=None if self._step is None else int(self._step))
+
+    def load_state_dict(self, state):
+        self.param_groups[0].update(state['param_groups'][0])
+        if state.get('exp_avg') is not None and self._buf is not None:
+            self._buf.copy_(state['exp_avg']); self._v.copy_(state['exp_avg_sq']); self._step.fill_(int(state['step']))

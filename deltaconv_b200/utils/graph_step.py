@@ -90,6 +90,9 @@ class GraphedTrainStep:
         self._consumed.record(cur)
 
     def __call__(self):
+        sync_lr = getattr(self.optimizer, 'sync_lr', None)
+        if sync_lr is not None:
+            sync_lr()                    # a scheduler may have changed the learning rate: the captured kernel reads it from the device
         self.graph_fb.replay()
         if self.graph_opt is not None:
             self.flat.all_reduce(sources=self._graph_grads)
