@@ -131,6 +131,68 @@ int run_gemm(GemmArgs g, bool a_pc, bool b_jc, void* ws, size_t ws_bytes, cudaSt
     return dc_check_launch_n("gemm", splits > 1 ? 2 : 1);
 }
 
+
+// ---- weight gradient of a thin layer: dW[n, k] = sum_m dY[m, n] X[m, k] with K <= 16 (the first layer: 4 x 3 input channels) ----
+// The tiled kernel spends a 128 x 64 tile on 64 x 12 outputs and needs ~100 split-K slices.  Here a CTA walks a chunk of rows in
+// 64-row tiles staged in shared memory; thread (n, g) owns dW[n, g*KG .. g*KG+KG) in registers; per-CTA partials are added in a
+// fixed order by a second small kernel (deterministic).
+constexpr int THIN_ROWS = 64;
+template <int KG>            // k values per thread; 256 / 64 = 4 groups cover K <= 4 * KG
+__global__ void __launch_bounds__(256) thin_dw_kernel(const float* __restrict__ dY, long long ld_dy, const float* __restrict__ X, long long ldx,
+                                                      int M, int K, int N, int rows_per_cta, float* __restrict__ partial) {
+    __shared__ float dys[THIN_ROWS][64 + 1];
+    __shared__ float xs[THIN_ROWS][4 * KG];
+    const int n_local = threadIdx.x & 63, g = threadIdx.x >> 6;
+    const int n0 = blockIdx.y * 64;
+    const int r_begin = blockIdx.x * rows_per_cta, r_end = min(M, r_begin + rows_per_cta);
+    float acc[KG];
+#pragma unroll
+    for (int u = 0; u < KG; ++u) acc[u] = 0.f;
+    for (int r0 = r_begin; r0 < r_end; r0 += THIN_ROWS) {
+        __syncthreads();
+        for (int e = threadIdx.x; e < THIN_ROWS * 64; e += 256) {
+            const int m = e >> 6, c = e & 63;
+            dys[m][c] = (r0 + m < r_end && n0 + c < N) ? __ldg(dY + (long long)(r0 + m) * ld_dy + n0 + c) : 0.f;
+        }
+        for (int e = threadIdx.x; e < THIN_ROWS * 4 * KG; e += 256) {
+            const int m = e / (4 * KG), c = e - m * 4 * KG;
+            xs[m][c] = (r0 + m < r_end && c < K) ? __ldg(X + (long long)(r0 + m) * ldx + c) : 0.f;
+        }
+        __syncthreads();
+#pragma unroll 8
+        for (int m = 0; m < THIN_ROWS; ++m) {
+            const float d = dys[m][n_local];
+#pragma unroll
+            for (int u = 0; u < KG; ++u) acc[u] = fmaf(d, xs[m][g * KG + u], acc[u]);
+        }
+    }
+    if (n0 + n_local < N)
+#pragma unroll
+        for (int u = 0; u < KG; ++u)
+            if (g * KG + u < K) partial[((size_t)blockIdx.x * N + n0 + n_local) * K + g * KG + u] = acc[u];
+}
+
+__global__ void thin_dw_reduce_kernel(const float* __restrict__ partial, int chunks, int NK, int K, float* __restrict__ dW, long long ld_dw) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= NK) return;
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    int q = 0;
+    for (; q + 3 < chunks; q += 4) {          // four independent loads in flight, fixed order
+        s0 += partial[(size_t)q * NK + t]; s1 += partial[(size_t)(q + 1) * NK + t];
+        s2 += partial[(size_t)(q + 2) * NK + t]; s3 += partial[(size_t)(q + 3) * NK + t];
+    }
+    for (; q < chunks; ++q) s0 += partial[(size_t)q * NK + t];
+    const int n = t / K, k = t - n * K;
+    dW[(long long)n * ld_dw + k] = (s0 + s1) + (s2 + s3);
+}
+
+int thin_dw_chunks(long long M) {
+    long long c = (M + 4 * THIN_ROWS - 1) / (4 * THIN_ROWS);       // at least four tiles per CTA
+    const long long cap = 2LL * dc_sm_count();
+    if (c > cap) c = cap;
+    return (int)(c < 1 ? 1 : c);
+}
+
 // W [Cout, 2K] = [W1 | W2]  ->  W' [2Cout, 2K] = [[W1, -W2], [W2, W1]]
 // so that VectorMLP's Linear on I_J(v) (deltaconv.py:68, operators.py:19-21) becomes one plain
 // GEMM on the [N, 2K] view of the interleaved vector field: [v_x | v_y] W'^T = [out_x | out_y].
@@ -162,7 +224,13 @@ extern "C" size_t dc_gemm_ws_bytes(int64_t M, int64_t N, int64_t K) {
     int s = choose_splits((int)M, (int)N, (int)K);
     size_t simt = s > 1 ? (size_t)s * (size_t)M * (size_t)N * sizeof(float) : 0;
     size_t tc = dc_tc_ws_bytes(M, N, K);
-    return simt > tc ? simt : tc;
+    size_t need = simt > tc ? simt : tc;
+    // thin weight gradient (dc_linear_bwd_weight passes output rows as M, reduction length as K): per-CTA partials
+    if (N >= 1 && N <= 16 && M >= 1 && M <= 512 && K >= 1024) {
+        const size_t thin = (size_t)thin_dw_chunks(K) * (size_t)M * (size_t)N * sizeof(float);
+        if (thin > need) need = thin;
+    }
+    return need;
 }
 
 // Y[M,Nout] = X[M,K] W[Nout,K]^T (+ bias)              — torch.nn.Linear forward
@@ -205,6 +273,20 @@ extern "C" int dc_linear_bwd_weight(const float* dY, int64_t ld_dy, const float*
         int n = 0;
         int rc = dc_tc_gemm(dY, ld_dy, 1, X, ldx, 1, nullptr, Nout, K, M, dW, ld_dw, ws, ws_bytes, (cudaStream_t)stream, &n);
         if (rc <= 0) return rc < 0 ? rc : dc_check_launch_n("dc_linear_bwd_weight/tc", n);
+    }
+    if (K >= 1 && K <= 16 && Nout >= 1 && Nout <= 512 && M >= 1024) {      // thin layer: see thin_dw_kernel
+        const int chunks = thin_dw_chunks(M);
+        const size_t need = (size_t)chunks * Nout * K * sizeof(float);
+        if (ws_bytes >= need) {
+            const int rows_per_cta = (int)((M + chunks - 1) / chunks);
+            dim3 grid(chunks, dc_ceil_div(Nout, 64));
+            if (K <= 4) thin_dw_kernel<1><<<grid, 256, 0, (cudaStream_t)stream>>>(dY, ld_dy, X, ldx, (int)M, K, Nout, rows_per_cta, (float*)ws);
+            else if (K <= 8) thin_dw_kernel<2><<<grid, 256, 0, (cudaStream_t)stream>>>(dY, ld_dy, X, ldx, (int)M, K, Nout, rows_per_cta, (float*)ws);
+            else if (K <= 12) thin_dw_kernel<3><<<grid, 256, 0, (cudaStream_t)stream>>>(dY, ld_dy, X, ldx, (int)M, K, Nout, rows_per_cta, (float*)ws);
+            else thin_dw_kernel<4><<<grid, 256, 0, (cudaStream_t)stream>>>(dY, ld_dy, X, ldx, (int)M, K, Nout, rows_per_cta, (float*)ws);
+            thin_dw_reduce_kernel<<<dc_ceil_div(Nout * K, 256), 256, 0, (cudaStream_t)stream>>>((const float*)ws, chunks, Nout * K, K, dW, ld_dw);
+            return dc_check_launch_n("dc_linear_bwd_weight/thin", 2);
+        }
     }
     GemmArgs g = {};
     g.A = dY; g.sa_i = 1; g.sa_p = ld_dy;

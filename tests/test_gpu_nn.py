@@ -33,7 +33,8 @@ def no_dropout(m):
 
 @pytest.mark.parametrize('M,K,N,bias', [(1, 1, 1, False), (37, 3, 64, False), (1000, 12, 1, True), (4096, 256, 64, False),
                                         (333, 517, 129, True), (32, 2048, 512, False), (20000, 24, 16, False),
-                                        (4, 64, 40, True), (64, 36, 20, True), (33, 100, 7, True), (17, 30, 12, True), (63, 512, 256, False)])
+                                        (4, 64, 40, True), (64, 36, 20, True), (33, 100, 7, True), (17, 30, 12, True), (63, 512, 256, False),
+                                        (4096, 12, 64, False), (2000, 3, 130, True), (5000, 16, 512, False), (32768, 7, 64, False)])
 def test_linear_forward_backward(M, K, N, bias):
     x0, w0 = torch.randn(M, K), torch.randn(N, K) / K ** 0.5
     b0 = torch.randn(N) if bias else None
