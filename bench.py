@@ -116,7 +116,7 @@ WORK = {
     'dc_edge_diff_fwd': (_w_ediff, 'centralized'), 'dc_segmax_fwd': (_w_segmax, 'centralized'),
     'dc_segmax_bwd': (_w_segmax_t, 'centralized'),
 }
-KERNEL_OF = {'gemm': 'tc_gemm_kernel / sgemm_kernel (dc_linear_fwd / _bwd_input / _bwd_weight)', 'spmm': 'spmm_kernel (grad/div/curl/hodge and transposes)',
+KERNEL_OF = {'gemm': 'tc_pair_gemm_kernel / tc_gemm_kernel / sgemm_kernel (dc_linear_fwd / _bwd_input / _bwd_weight)', 'spmm': 'spmm_kernel (grad/div/curl/hodge and transposes)',
              'batchnorm': 'col_reduce/bn_act kernels', 'knn': 'knn_kernel', 'build_grad_div': 'fit_kernel (+ edge/cloud means)',
              'gathermax': 'gathermax kernels', 'vecnonlin': 'vecnonlin kernels', 'centralized': 'edge_diff/segmax kernels'}
 
@@ -358,7 +358,7 @@ def run_cuda_arm(args):
     fam = prof.families()
     prof_total_ms = sum(a.elapsed_time(b) for a, b in spans)
     if args.detail and rank == 0:
-        open(args.detail, 'w').write(prof.detail(args.steps) + '\n')
+        open(args.detail, "w").write(prof.detail(args.steps, top=120) + "\n")
 
     if rank != 0:
         if world > 1:
