@@ -9,74 +9,13 @@
 // 64-bit integer, so ties resolve to the lower index and results are bit-reproducible.
 #include "common.cuh"
 #include "geom_core.cuh"
+#include "knn_list.cuh"
 
 namespace {
 
 constexpr int KNN_WARPS = 8;
 constexpr int KNN_TILE = 32;        // queries per CTA
 constexpr int KNN_CHUNK = 4096;     // points staged per pass: 3 * 4096 * 4 B = 48 KB static smem
-typedef unsigned long long u64;
-constexpr u64 KEY_INF = ~0ull;
-
-template <int SLOTS>
-__device__ __forceinline__ u64 list_get(const u64 (&keys)[SLOTS], int p) {
-    u64 r = __shfl_sync(FULL, keys[0], p & 31);
-#pragma unroll
-    for (int s = 1; s < SLOTS; ++s) {
-        u64 t = __shfl_sync(FULL, keys[s], p & 31);
-        if ((p >> 5) == s) r = t;
-    }
-    return r;
-}
-
-template <int SLOTS>
-__device__ __forceinline__ void list_insert(u64 (&keys)[SLOTS], u64 c, int lane) {
-    int pos = 0;
-#pragma unroll
-    for (int s = 0; s < SLOTS; ++s) pos += __popc(__ballot_sync(FULL, keys[s] < c));
-#pragma unroll
-    for (int s = SLOTS - 1; s >= 0; --s) {
-        u64 up = __shfl_up_sync(FULL, keys[s], 1);
-        if (s > 0) {
-            u64 carry = __shfl_sync(FULL, keys[s - 1], 31);
-            if (lane == 0) up = carry;
-        }
-        int p = s * 32 + lane;
-        if (p == pos) keys[s] = c;
-        else if (p > pos) keys[s] = up;
-    }
-}
-
-__device__ __forceinline__ u64 shfl_xor64(u64 v, int m) { return __shfl_xor_sync(FULL, v, m); }
-
-// One compare-exchange step of a bitonic network over the 32 lanes: the lower lane of each pair keeps the minimum when the
-// pair's block is ascending.
-__device__ __forceinline__ u64 bitonic_step(u64 key, int lane, int stride, bool ascending) {
-    const u64 other = shfl_xor64(key, stride);
-    const bool lower = (lane & stride) == 0;
-    const u64 lo = key < other ? key : other, hi = key < other ? other : key;
-    return (lower == ascending) ? lo : hi;
-}
-
-// Merge 32 new candidates into the sorted 32-entry list (k <= 32): sort them across the warp (15 steps), pair the list with
-// their reverse (the element-wise minimum is the bitonic lower half of the union), sort that (5 steps).  About 170
-// instructions whatever the number of survivors, against ~22 per single insertion: used when a round has many survivors,
-// i.e. in the first few rounds of every query.  Keys are unique (they carry the index), so the result is the same list.
-__device__ __forceinline__ u64 list_merge32(u64 list, u64 key, int lane) {
-#pragma unroll
-    for (int size = 2; size <= 32; size <<= 1)
-#pragma unroll
-        for (int stride = size >> 1; stride > 0; stride >>= 1)
-            key = bitonic_step(key, lane, stride, size == 32 || (lane & size) == 0);
-    const u64 rev = __shfl_sync(FULL, key, 31 - lane);
-    u64 m = list < rev ? list : rev;
-#pragma unroll
-    for (int stride = 16; stride > 0; stride >>= 1) m = bitonic_step(m, lane, stride, true);
-    return m;
-}
-
-constexpr int KNN_MERGE_MIN = 12;     // survivors in a round from which the merge is cheaper than single insertions (5 / 8 / 12 / 16 / 24 measured: 12 is best)
-
 // Offer `count` candidates (local indices base..base+count) to the warp's list.
 template <int SLOTS, bool STAGED>
 __device__ __forceinline__ void scan(u64 (&keys)[SLOTS], u64& tau, int k, int lane, float qx, float qy, float qz,
@@ -93,19 +32,7 @@ __device__ __forceinline__ void scan(u64 (&keys)[SLOTS], u64& tau, int k, int la
             float d2 = knn_dist2(qx, qy, qz, px, py, pz);
             key = ((u64)__float_as_uint(d2) << 32) | (unsigned)(base + j);
         }
-        unsigned mask = __ballot_sync(FULL, key < tau);
-        if (SLOTS == 1 && __popc(mask) >= KNN_MERGE_MIN) {
-            keys[0] = list_merge32(keys[0], key, lane);
-            tau = list_get<SLOTS>(keys, k - 1);
-            continue;
-        }
-        while (mask) {
-            int b = __ffs(mask) - 1;
-            u64 c = __shfl_sync(FULL, key, b);
-            list_insert<SLOTS>(keys, c, lane);
-            tau = list_get<SLOTS>(keys, k - 1);
-            mask = __ballot_sync(FULL, key < tau) & ~((2u << b) - 1u);
-        }
+        list_offer<SLOTS>(keys, tau, k, lane, key);
     }
 }
 

@@ -110,6 +110,10 @@ class EllGraph:
         return self._edge_index
 
 
+KNN_GRID_FROM = 1536      # points in the largest cloud from which the grid search replaces the brute-force scan (measured crossover)
+KNN_METHOD = 'auto'       # 'auto' | 'brute' | 'grid' (tests and benchmarks force one)
+
+
 def knn(pos, k, batch=None, num_clouds=None, want_edge_index=True, max_points=None):
     """ELL kNN graph of `pos` [N,3] per cloud (self included, ascending (d2, index))."""
     pos = _f32(pos, 'pos').contiguous()
@@ -119,7 +123,13 @@ def knn(pos, k, batch=None, num_clouds=None, want_edge_index=True, max_points=No
     cp, B, maxp = cloud_layout(batch, N, pos.device, num_clouds, max_points)
     idx = torch.empty(N, k, dtype=_I32, device=pos.device)
     ei = torch.empty(2, N * k, dtype=_I64, device=pos.device) if want_edge_index else None
-    call('dc_knn', ptr(pos), ptr(cp), B, N, k, ptr(idx), ptr(ei), None)
+    method = KNN_METHOD if KNN_METHOD != 'auto' else ('grid' if maxp > KNN_GRID_FROM else 'brute')
+    if method == 'grid':                 # large clouds: uniform grid + ring search, same exact result (dc_knn_grid)
+        nb = query('dc_knn_grid_ws_bytes', N, B)
+        ws = workspace(nb, pos.device)
+        call('dc_knn_grid', ptr(pos), ptr(cp), B, N, k, ptr(idx), ptr(ei), None, ptr(ws), nb)
+    else:
+        call('dc_knn', ptr(pos), ptr(cp), B, N, k, ptr(idx), ptr(ei), None)
     graph = EllGraph(idx, cp, B, maxp)
     if ei is not None:
         ei._dc_graph = graph

@@ -45,6 +45,13 @@ int dc_cloud_ptr(const int64_t* batch, int N, int B, int32_t* cloud_ptr, void* s
 int dc_knn(const float* pos, const int32_t* cloud_ptr, int B, int N, int k, int32_t* idx,
            int64_t* edge_index_or_null, float* d2_or_null, void* stream);
 
+/* The same graph for large clouds: a uniform grid per cloud (counting sort by cell) and a ring search per query instead of the
+ * O(P^2) scan; exact, so bit-identical to dc_knn.  Worth it from a few thousand points per cloud (deltaconv_b200.ops.knn switches at
+ * 1536).  Workspace from dc_knn_grid_ws_bytes(N, B); no host synchronisation. */
+size_t dc_knn_grid_ws_bytes(int N, int B);
+int dc_knn_grid(const float* pos, const int32_t* cloud_ptr, int B, int N, int k, int32_t* idx,
+                int64_t* edge_index_or_null, float* d2_or_null, void* ws, size_t ws_bytes, void* stream);
+
 /* [2,N*k] int64 edge_index (rows grouped by centre, fixed k — grad_div_mls.py:24-25,224) <-> ELL idx. */
 int dc_ell_from_edge_index(const int64_t* edge_index, int N, int k, int32_t* idx, void* stream);
 int dc_edge_index_from_ell(const int32_t* idx, int N, int k, int64_t* edge_index, void* stream);

@@ -347,3 +347,37 @@ def test_staged_spmm_is_bitwise_equal_to_the_gather_kernels(C):
             lib.dc_set_spmm_staged(0)
     for a, b in zip(*results):
         assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize('sizes,k', [([5000, 7000], 20), ([300, 9000, 17, 4200], 10), ([6000], 40), ([20000], 16), ([4500, 4500], 70)])
+def test_grid_knn_is_bit_identical_to_brute_force(sizes, k):
+    """dc_knn_grid (uniform grid + ring search, used for clouds of more than 1536 points) returns exactly the graph of the
+    brute-force kernel: indices and squared distances, ties by lower index.  Clouds: uniform volume, a thin shell, a planar
+    sheet with duplicated points, a line — the grid must stay exact where its cells are badly filled."""
+    from deltaconv_b200 import ops
+    torch.manual_seed(11)
+    parts = []
+    for c, n in enumerate(sizes):
+        kind = c % 4
+        if kind == 0:
+            p = torch.rand(n, 3) * torch.tensor([2.0, 1.0, 0.5])
+        elif kind == 1:
+            p = torch.nn.functional.normalize(torch.randn(n, 3), dim=1) * (1 + 0.001 * torch.randn(n, 1)) + 5.0
+        elif kind == 2:
+            p = torch.cat([torch.rand(n, 2), torch.zeros(n, 1)], 1)
+            p[n // 2:] = p[:n - n // 2].clone()                          # exact duplicates: ties decided by index
+        else:
+            p = torch.linspace(0, 1, n)[:, None] * torch.tensor([[1.0, 2.0, -1.0]])
+        parts.append(p)
+    pos = torch.cat(parts).to(DEV)
+    batch = torch.repeat_interleave(torch.arange(len(sizes)), torch.tensor(sizes)).to(DEV)
+    out = {}
+    for method in ('brute', 'grid'):
+        ops.KNN_METHOD = method
+        try:
+            g = ops.knn(pos, k, batch, num_clouds=len(sizes), want_edge_index=True)
+        finally:
+            ops.KNN_METHOD = 'auto'
+        out[method] = (g.idx.clone(), g.edge_index().clone())
+    assert torch.equal(out['brute'][0], out['grid'][0])
+    assert torch.equal(out['brute'][1], out['grid'][1])
