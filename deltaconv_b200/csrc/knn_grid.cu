@@ -42,7 +42,7 @@ __global__ void bbox_kernel(const float* __restrict__ pos, const int* __restrict
 // the bounding box; surface samples fill far fewer cells, so occupied cells hold a few tens of points), at most
 // 4 P + 64 cells per cloud so that the cell arrays have a fixed size.
 __global__ void grid_params_kernel(const int* __restrict__ cloud_ptr, int B, const int* __restrict__ bbox, GridCloud* __restrict__ clouds,
-                                   int* __restrict__ total_cells) {
+                                   int* __restrict__ total_cells, float points_per_cell) {
     if (blockIdx.x != 0 || threadIdx.x != 0) return;
     int base = 0;
     for (int b = 0; b < B; ++b) {
@@ -57,7 +57,7 @@ __global__ void grid_params_kernel(const int* __restrict__ cloud_ptr, int B, con
         // degenerate extents (planar or collinear clouds) count as one cell layer
         const float floor_ext = fmaxf(emax * 1e-3f, 1e-30f);
         const float vol = fmaxf(ex, floor_ext) * fmaxf(ey, floor_ext) * fmaxf(ez, floor_ext);
-        float h = cbrtf(vol / fmaxf((float)P * 0.5f, 1.f));
+        float h = cbrtf(vol / fmaxf((float)P / points_per_cell, 1.f));
         h = fmaxf(h, emax / (float)(GRID_MAX_DIM - 1));
         if (!(h > 0.f)) h = 1.f;                                    // all points coincide
         const long long cap = 4LL * P + 64;
@@ -227,10 +227,18 @@ grid_query_kernel(const float4* __restrict__ sorted, const int* __restrict__ cel
     }
 }
 
+float g_points_per_cell = 2.f;       // target occupancy of a bounding-box cell (dc_set_knn_grid_density)
 size_t align256(size_t n) { return (n + 255) / 256 * 256; }
 long long grid_cell_cap(int N, int B) { return 4LL * N + 65LL * B; }
 
 }  // namespace
+
+// tuning: points per bounding-box cell the grid aims at (default 2)
+extern "C" int dc_set_knn_grid_density(float points_per_cell) {
+    DC_REQUIRE(points_per_cell >= 0.25f && points_per_cell <= 64.f, "dc_set_knn_grid_density: out of range");
+    g_points_per_cell = points_per_cell;
+    return DC_OK;
+}
 
 extern "C" size_t dc_knn_grid_ws_bytes(int N, int B) {
     const size_t cap = (size_t)grid_cell_cap(N, B);
@@ -260,7 +268,7 @@ extern "C" int dc_knn_grid(const float* pos, const int32_t* cloud_ptr, int B, in
     DC_CUDA(cudaMemsetAsync(cursor, 0, ((size_t)cap + 2) * 4, st));
     bbox_init_kernel<<<dc_ceil_div(B * 6, 256), 256, 0, st>>>(bbox, B);
     bbox_kernel<<<dc_ceil_div(N, 256), 256, 0, st>>>(pos, cloud_ptr, B, N, bbox);
-    grid_params_kernel<<<1, 32, 0, st>>>(cloud_ptr, B, bbox, clouds, total);
+    grid_params_kernel<<<1, 32, 0, st>>>(cloud_ptr, B, bbox, clouds, total, g_points_per_cell);
     grid_count_kernel<<<dc_ceil_div(N, 256), 256, 0, st>>>(pos, cloud_ptr, B, N, clouds, cell_of, cnt);
     grid_scan_kernel<<<1, GSCAN_T, 0, st>>>(cnt, total, cell_start);
     grid_fill_kernel<<<dc_ceil_div(N, 256), 256, 0, st>>>(pos, cloud_ptr, B, N, cell_of, cell_start, cursor, sorted);
