@@ -22,6 +22,7 @@ _SIGNATURES = {
     'dc_reset_launch_count': [],
     'dc_cloud_ptr': [_P, _I, _I, _P, _P],
     'dc_knn': [_P, _P, _I, _I, _I, _P, _P, _P, _P],
+    'dc_morton_keys': [_P, _P, _I, _I, _P, _P, _Z, _P],
     'dc_knn_grid_ws_bytes': [_I, _I],
     'dc_set_knn_grid_density': [_F],
     'dc_knn_grid': [_P, _P, _I, _I, _I, _P, _P, _P, _P, _Z, _P],

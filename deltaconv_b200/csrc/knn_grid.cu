@@ -228,10 +228,45 @@ grid_query_kernel(const float4* __restrict__ sorted, const int* __restrict__ cel
 }
 
 float g_points_per_cell = 2.f;       // target occupancy of a bounding-box cell (dc_set_knn_grid_density)
+// 30-bit Morton code of a point inside its cloud's bounding box (10 bits per axis), cloud index above it: sorting by this key
+// orders every cloud along a space-filling curve without mixing clouds.
+__device__ __forceinline__ unsigned spread10(unsigned v) {
+    v = (v | (v << 16)) & 0x030000FFu; v = (v | (v << 8)) & 0x0300F00Fu; v = (v | (v << 4)) & 0x030C30C3u; v = (v | (v << 2)) & 0x09249249u;
+    return v;
+}
+__global__ void morton_key_kernel(const float* __restrict__ pos, const int* __restrict__ cloud_ptr, int B, int N, const int* __restrict__ bbox,
+                                  long long* __restrict__ keys) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    const int b = cloud_of(cloud_ptr, B, i);
+    const float x0 = ord2f(bbox[b * 6]), y0 = ord2f(bbox[b * 6 + 1]), z0 = ord2f(bbox[b * 6 + 2]);
+    const float ext = fmaxf(fmaxf(ord2f(bbox[b * 6 + 3]) - x0, ord2f(bbox[b * 6 + 4]) - y0), fmaxf(ord2f(bbox[b * 6 + 5]) - z0, 1e-30f));
+    const float sc = 1023.999f / ext;
+    const unsigned cx = min(1023u, (unsigned)fmaxf((pos[3 * (size_t)i] - x0) * sc, 0.f));
+    const unsigned cy = min(1023u, (unsigned)fmaxf((pos[3 * (size_t)i + 1] - y0) * sc, 0.f));
+    const unsigned cz = min(1023u, (unsigned)fmaxf((pos[3 * (size_t)i + 2] - z0) * sc, 0.f));
+    keys[i] = ((long long)b << 30) | (long long)(spread10(cx) | (spread10(cy) << 1) | (spread10(cz) << 2));
+}
+
 size_t align256(size_t n) { return (n + 255) / 256 * 256; }
 long long grid_cell_cap(int N, int B) { return 4LL * N + 65LL * B; }
 
 }  // namespace
+
+// keys[i] = (cloud of i) << 30 | Morton code of point i in its cloud's bounding box; ws: B * 24 bytes.  Sorting the points of a
+// large cloud by this key (stable) keeps the kNN neighbourhoods of consecutive points in the same cache lines: measured 2-2.3x on
+// the SpMM gathers of a 2^20-point cloud (scripts/exp_point_order.py).
+extern "C" int dc_morton_keys(const float* pos, const int32_t* cloud_ptr, int B, int N, int64_t* keys, void* ws, size_t ws_bytes, void* stream) {
+    DC_REQUIRE(B >= 1 && N >= 0, "dc_morton_keys: need B >= 1, N >= 0");
+    DC_REQUIRE(ws_bytes >= (size_t)B * 24, "dc_morton_keys: workspace too small");
+    if (N == 0) return DC_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    int* bbox = (int*)ws;
+    bbox_init_kernel<<<dc_ceil_div(B * 6, 256), 256, 0, st>>>(bbox, B);
+    bbox_kernel<<<dc_ceil_div(N, 256), 256, 0, st>>>(pos, cloud_ptr, B, N, bbox);
+    morton_key_kernel<<<dc_ceil_div(N, 256), 256, 0, st>>>(pos, cloud_ptr, B, N, bbox, (long long*)keys);
+    return dc_check_launch_n("dc_morton_keys", 3);
+}
 
 // tuning: points per bounding-box cell the grid aims at (default 2)
 extern "C" int dc_set_knn_grid_density(float points_per_cell) {

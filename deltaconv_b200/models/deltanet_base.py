@@ -1,6 +1,7 @@
 """DeltaNet backbone (reference: deltaconv/models/deltanet_base.py:8-87)."""
 import torch
 
+from .. import ops
 from ..geometry.graph import knn_graph
 from ..geometry.grad_div_mls import build_grad_div, build_tangent_basis, estimate_basis
 from ..nn import DeltaConv
@@ -20,15 +21,30 @@ class DeltaNetBase(torch.nn.Module):
             self.convs.append(DeltaConv(conv_channels[i], conv_channels[i + 1], depth=mlp_depth,
                                         centralized=(centralize_first and i == 0), vector=not last_layer))
 
+    # Large-cloud mode (no counterpart in the reference): when set, batches whose largest cloud has at least this many
+    # points are processed in Morton order inside every cloud (ops.spatial_order) — the gathers of the operators then stay in
+    # cache (2x on a 2^20-point cloud).  The returned features are in that order; `data._dc_perm` holds the permutation and
+    # the segmentation head undoes it.  Off by default: exact distance ties in the kNN resolve by index, so a reordering can
+    # change which of two equidistant neighbours is kept.
+    reorder_min_points = None
+
     def forward(self, data):
         pos, batch = data.pos, data.batch
         # optional hints (number of clouds, size of the largest one) that avoid a device sync
         clouds, maxp = getattr(data, '_num_clouds', None), getattr(data, '_max_points', None)
+        data._dc_perm = None
+        if self.reorder_min_points is not None:
+            if maxp is None:
+                _, clouds, maxp = ops.cloud_layout(batch, pos.size(0), pos.device, clouds)
+            if maxp >= self.reorder_min_points:
+                perm = ops.spatial_order(pos, batch, clouds)
+                data._dc_perm = perm
+                pos = pos[perm]
 
         # operator construction (deltanet_base.py:52-69): kNN graph -> frames -> grad/div
         edge_index = knn_graph(pos, self.k, batch, loop=True, flow='target_to_source', num_clouds=clouds, max_points=maxp)
         if hasattr(data, 'norm') and data.norm is not None:
-            normal = data.norm
+            normal = data.norm if data._dc_perm is None else data.norm[data._dc_perm]
             x_basis, y_basis = build_tangent_basis(normal)
         else:
             edge_index_normal = knn_graph(pos, 10, batch, loop=True, flow='target_to_source', num_clouds=clouds, max_points=maxp)
@@ -37,7 +53,10 @@ class DeltaNetBase(torch.nn.Module):
                                    kernel_width=self.grad_kernel_width, regularizer=self.grad_regularizer)
 
         # convolutions (deltanet_base.py:76-87)
-        x = data.x if hasattr(data, 'x') and data.x is not None else pos
+        if hasattr(data, 'x') and data.x is not None:
+            x = data.x if data._dc_perm is None else data.x[data._dc_perm]
+        else:
+            x = pos
         v = grad @ x
         out = []
         for conv in self.convs:

@@ -32,4 +32,10 @@ class DeltaNetSegmentation(torch.nn.Module):
         parts = [x_max]
         if self.categorical_vector:
             parts.append(ops.broadcast_rows(self.lin_categorical(data.category), batch, N))
-        return self.segmentation_head(torch.cat(parts + conv_out, dim=1))
+        out = self.segmentation_head(torch.cat(parts + conv_out, dim=1))
+        perm = getattr(data, '_dc_perm', None)
+        if perm is not None:                         # large-cloud mode: rows are in Morton order, hand them back in the caller's
+            restored = torch.empty_like(out)
+            restored[perm] = out
+            out = restored
+        return out

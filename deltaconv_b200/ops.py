@@ -137,6 +137,19 @@ def knn(pos, k, batch=None, num_clouds=None, want_edge_index=True, max_points=No
     return graph
 
 
+def spatial_order(pos, batch=None, num_clouds=None):
+    """Permutation that orders the points of every cloud along a Morton curve (clouds stay where they are, so a sorted
+    `batch` vector is unchanged by it).  For clouds of 10^5 points and more the operators built on `pos[perm]` gather from
+    nearby rows: 2x on the SpMMs of a 2^20-point cloud.  The sort itself is torch's (a pre-transform, not on the hot path)."""
+    pos = _f32(pos, 'pos').contiguous()
+    N = pos.size(0)
+    cp, B, _ = cloud_layout(batch, N, pos.device, num_clouds)
+    keys = torch.empty(N, dtype=_I64, device=pos.device)
+    ws = workspace(B * 24, pos.device)
+    call('dc_morton_keys', ptr(pos), ptr(cp), B, N, ptr(keys), ptr(ws), B * 24)
+    return torch.argsort(keys, stable=True)
+
+
 def graph_of(edge_index, num_points):
     """EllGraph behind a [2,E] int64 edge_index: the one `knn_graph` attached, else a conversion
     under the reference's own assumption (rows grouped by centre, same k everywhere —

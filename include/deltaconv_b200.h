@@ -53,6 +53,10 @@ int dc_set_knn_grid_density(float points_per_bounding_box_cell);   /* tuning kno
 int dc_knn_grid(const float* pos, const int32_t* cloud_ptr, int B, int N, int k, int32_t* idx,
                 int64_t* edge_index_or_null, float* d2_or_null, void* ws, size_t ws_bytes, void* stream);
 
+/* Sort key for a cache-friendly point order of large clouds: (cloud << 30) | 30-bit Morton code inside the cloud's bounding box.
+ * No counterpart in the reference (its point order is whatever the dataset has); ws: B * 24 bytes. */
+int dc_morton_keys(const float* pos, const int32_t* cloud_ptr, int B, int N, int64_t* keys, void* ws, size_t ws_bytes, void* stream);
+
 /* [2,N*k] int64 edge_index (rows grouped by centre, fixed k — grad_div_mls.py:24-25,224) <-> ELL idx. */
 int dc_ell_from_edge_index(const int64_t* edge_index, int N, int k, int32_t* idx, void* stream);
 int dc_edge_index_from_ell(const int32_t* idx, int N, int k, int64_t* edge_index, void* stream);

@@ -631,3 +631,34 @@ def test_flat_adam_matches_torch_adam():
     for (n1, p1), (_, p2) in zip(ref_net.named_parameters(), flat_net.named_parameters()):
         scale = p1.abs().max().item() + 1e-12
         assert (p1 - p2).abs().max().item() < 5e-4 * scale, n1        # Adam divides by sqrt(v): early steps amplify fp32 rounding of the gradients
+
+
+def test_large_cloud_mode_morton_order_is_transparent():
+    """DeltaNetBase.reorder_min_points: clouds processed in Morton order give the same per-point logits (handed back in the
+    caller's order) and the same gradients as the plain order; the permutation never mixes clouds."""
+    D = dc()
+    from deltaconv_b200 import ops
+    torch.manual_seed(2)
+    data = D.utils.synthetic_batch(3, 700, config=3, num_classes=6).to(DEV)
+    perm = ops.spatial_order(data.pos, data.batch, 3)
+    assert torch.equal(torch.sort(perm).values, torch.arange(2100, device=DEV)) and torch.equal(data.batch[perm], data.batch)
+    cell = ((data.pos[perm] - data.pos.min(0).values) * 4).long()          # consecutive points are spatially close
+    assert (cell[1:] - cell[:-1]).abs().sum(1).float().mean() < (cell[torch.randperm(2100, device=DEV)] - cell).abs().sum(1).float().mean() * 0.5
+    nets = []
+    for _ in range(2):
+        torch.manual_seed(0)
+        nets.append(no_dropout(D.utils.fill_deterministic(D.models.DeltaNetSegmentation(3, 6, conv_channels=[16, 32], embedding_size=64), 4)).to(DEV).train())
+    plain, reordered = nets
+    reordered.deltanet_base.reorder_min_points = 1
+    y = torch.randint(0, 6, (2100,), device=DEV)
+    outs = []
+    for net in nets:
+        logits = net(data)
+        torch.nn.functional.cross_entropy(logits, y).backward()
+        outs.append(logits.detach())
+    assert data._dc_perm is not None
+    assert rel_err(outs[1].cpu(), outs[0].cpu()) < 1e-4
+    scale = max(p.grad.abs().max().item() for p in plain.parameters() if p.grad is not None)     # some gradients are pure rounding noise
+    for (n1, p1), (_, p2) in zip(plain.named_parameters(), reordered.named_parameters()):
+        if p1.grad is not None:
+            assert (p1.grad - p2.grad).abs().max().item() < 2e-3 * scale, n1
