@@ -2,14 +2,14 @@
 
 `install()` makes these imports resolve on a box without PyG, to this package's CUDA implementations:
 
-    import deltaconv                      ->  deltaconv_b200 (geometry, nn, models sub-packages too)
+    import deltaconv                      ->  deltaconv_b200 (geometry, nn, models, transforms too)
     from torch_geometric.data import Data, Batch
     from torch_geometric.loader import DataLoader
     from torch_geometric.transforms import Compose, BaseTransform
     from torch_geometric.nn import knn_graph, global_max_pool, global_mean_pool
 
 A real `torch_geometric`, if importable, is left alone (its `Batch` objects work with the models as they are).
-Datasets and the reference's augmentation transforms are not part of the hot path and are not provided."""
+Datasets, `SamplePoints` and `GeodesicFPS` are not provided (deltaconv_b200/transforms.py has the other transforms)."""
 import importlib
 import sys
 import types
@@ -52,7 +52,7 @@ def install(alias_reference=True, provide_pyg=None):
     from . import geometry
     if alias_reference:
         sys.modules.setdefault('deltaconv', pkg)
-        for sub in ('geometry', 'nn', 'models', 'utils'):
+        for sub in ('geometry', 'nn', 'models', 'utils', 'transforms'):
             sys.modules.setdefault(f'deltaconv.{sub}', importlib.import_module(f'deltaconv_b200.{sub}'))
     if provide_pyg is None:
         try:

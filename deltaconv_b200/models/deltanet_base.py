@@ -32,19 +32,20 @@ class DeltaNetBase(torch.nn.Module):
         pos, batch = data.pos, data.batch
         # optional hints (number of clouds, size of the largest one) that avoid a device sync
         clouds, maxp = getattr(data, '_num_clouds', None), getattr(data, '_max_points', None)
-        data._dc_perm = None
+        perm = None
         if self.reorder_min_points is not None:
             if maxp is None:
                 _, clouds, maxp = ops.cloud_layout(batch, pos.size(0), pos.device, clouds)
             if maxp >= self.reorder_min_points:
                 perm = ops.spatial_order(pos, batch, clouds)
-                data._dc_perm = perm
                 pos = pos[perm]
+        if perm is not None or getattr(data, '_dc_perm', None) is not None:
+            data._dc_perm = perm                     # the batch object is only touched in large-cloud mode
 
         # operator construction (deltanet_base.py:52-69): kNN graph -> frames -> grad/div
         edge_index = knn_graph(pos, self.k, batch, loop=True, flow='target_to_source', num_clouds=clouds, max_points=maxp)
         if hasattr(data, 'norm') and data.norm is not None:
-            normal = data.norm if data._dc_perm is None else data.norm[data._dc_perm]
+            normal = data.norm if perm is None else data.norm[perm]
             x_basis, y_basis = build_tangent_basis(normal)
         else:
             edge_index_normal = knn_graph(pos, 10, batch, loop=True, flow='target_to_source', num_clouds=clouds, max_points=maxp)
@@ -54,7 +55,7 @@ class DeltaNetBase(torch.nn.Module):
 
         # convolutions (deltanet_base.py:76-87)
         if hasattr(data, 'x') and data.x is not None:
-            x = data.x if data._dc_perm is None else data.x[data._dc_perm]
+            x = data.x if perm is None else data.x[perm]
         else:
             x = pos
         v = grad @ x

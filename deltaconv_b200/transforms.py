@@ -1,0 +1,183 @@
+"""Augmentation / normalisation transforms with the reference's names and arguments (deltaconv/transforms/*.py), written
+so that they also run on a whole device-resident `Batch`: with a `batch` vector every cloud draws its own random
+parameters and all clouds are transformed in one vectorised pass on the GPU; without one they act on a
+single cloud exactly like the reference's per-sample CPU transforms.  Plain torch — they are not on the hot path.
+
+Not provided: `SamplePoints` (needs mesh faces) and `GeodesicFPS` (the reference's C++ pre-transform, §8f-3).
+"""
+import math
+import numbers
+
+import torch
+
+__all__ = ['NormalizeScale', 'NormalizeAxes', 'RandomScale', 'RandomTranslateGlobal', 'RandomRotate', 'RandomNormals']
+
+
+def _clouds(data):
+    """(cloud index per point [N] int64, number of clouds) — one cloud when the object carries no batch vector."""
+    pos = data.pos
+    batch = getattr(data, 'batch', None)
+    if batch is None:
+        return torch.zeros(pos.size(0), dtype=torch.long, device=pos.device), 1
+    hint = getattr(data, '_num_clouds', None)
+    return batch, int(hint) if hint is not None else (int(batch.max()) + 1 if batch.numel() else 1)
+
+
+def _per_cloud_extreme(values, batch, B, largest):
+    """max (or min) over the points of every cloud -> [B, C]"""
+    fill = float('-inf') if largest else float('inf')
+    out = torch.full((B, values.size(1)), fill, dtype=values.dtype, device=values.device)
+    index = batch[:, None].expand_as(values)
+    return out.scatter_reduce(0, index, values, 'amax' if largest else 'amin', include_self=True)
+
+
+def _has_normals(data):
+    return getattr(data, 'norm', None) is not None
+
+
+def _per_axis(value, dim):
+    if isinstance(value, numbers.Number):
+        return [float(value)] * dim
+    assert len(value) == dim
+    return [float(v) for v in value]
+
+
+class NormalizeScale(object):
+    """Centre every cloud on the middle of its bounding box and scale it into the unit ball (normalize_scale.py:14-22)."""
+
+    def __init__(self, norm_ord=2, scaling_factor=None):
+        self.norm_ord = norm_ord
+        self.scaling_factor = scaling_factor
+
+    def __call__(self, data):
+        batch, B = _clouds(data)
+        pos = data.pos
+        centre = (_per_cloud_extreme(pos, batch, B, True) + _per_cloud_extreme(pos, batch, B, False)) / 2
+        pos = pos - centre[batch]
+        if self.scaling_factor is None:
+            radius = torch.linalg.norm(pos, ord=self.norm_ord, dim=1, keepdim=True)
+            scale = (1 / _per_cloud_extreme(radius, batch, B, True)) * 0.999999
+            pos = pos * scale[batch]
+        else:
+            pos = pos * ((1 / self.scaling_factor) * 0.999999)
+        data.pos = pos
+        return data
+
+    def __repr__(self):
+        return '{}()'.format(self.__class__.__name__)
+
+
+class NormalizeAxes(object):
+    """Permute the axes of every cloud from smallest to widest standard deviation, then scale so that the last axis
+    reaches 1/2 (normalize_axes.py:17-26)."""
+
+    def __init__(self, max_points=-1):
+        self.max_points = max_points
+
+    def __call__(self, data):
+        batch, B = _clouds(data)
+        pos = data.pos
+        count = torch.zeros(B, 1, dtype=pos.dtype, device=pos.device).index_add_(0, batch, torch.ones_like(pos[:, :1]))
+        mean = torch.zeros(B, pos.size(1), dtype=pos.dtype, device=pos.device).index_add_(0, batch, pos) / count.clamp(min=1)
+        var = torch.zeros_like(mean).index_add_(0, batch, (pos - mean[batch]) ** 2) / (count - 1).clamp(min=1)     # unbiased, as torch.std
+        order = torch.sort(var, dim=1)[1]                                  # sorting by variance = sorting by std
+        pos = torch.gather(pos, 1, order[batch])
+        top = _per_cloud_extreme(pos, batch, B, True)[:, -1:]
+        data.pos = pos * (1 / (2 * top))[batch]
+        return data
+
+    def __repr__(self):
+        return '{}()'.format(self.__class__.__name__)
+
+
+class RandomScale(object):
+    """Scale every cloud by its own random factor per axis drawn from `scales = (a, b)`; normals are transformed with the
+    inverse scale and renormalised (random_scale.py:28-34)."""
+
+    def __init__(self, scales):
+        assert isinstance(scales, (tuple, list)) and len(scales) == 2
+        self.scales = scales
+
+    def __call__(self, data):
+        batch, B = _clouds(data)
+        scale = data.pos.new_empty(B, data.pos.size(1)).uniform_(*self.scales)
+        data.pos = data.pos * scale[batch]
+        if _has_normals(data):
+            n = data.norm * (1 / scale)[batch]
+            data.norm = n / torch.linalg.norm(n, dim=1, keepdim=True)
+        return data
+
+    def __repr__(self):
+        return '{}({})'.format(self.__class__.__name__, self.scales)
+
+
+class RandomTranslateGlobal(object):
+    """Translate every cloud as a whole by its own random offset in (-translate, +translate) per axis
+    (random_translate_global.py:23-34)."""
+
+    def __init__(self, translate):
+        self.translate = translate
+
+    def __call__(self, data):
+        batch, B = _clouds(data)
+        limit = data.pos.new_tensor([abs(t) for t in _per_axis(self.translate, data.pos.size(1))])
+        offset = (data.pos.new_empty(B, data.pos.size(1)).uniform_(-1, 1)) * limit
+        data.pos = data.pos + offset[batch]
+        return data
+
+    def __repr__(self):
+        return '{}({})'.format(self.__class__.__name__, self.translate)
+
+
+class RandomRotate(object):
+    """Rotate every cloud (positions and normals) about `axis` by its own random angle from `degrees`
+    (random_rotate.py:20-45; same matrices, applied as `pos @ matrix`)."""
+
+    def __init__(self, degrees, axis=0):
+        if isinstance(degrees, numbers.Number):
+            degrees = (-abs(degrees), abs(degrees))
+        assert isinstance(degrees, (tuple, list)) and len(degrees) == 2
+        self.degrees = degrees
+        self.axis = axis
+
+    def __call__(self, data):
+        batch, B = _clouds(data)
+        pos = data.pos
+        angle = pos.new_empty(B).uniform_(*self.degrees) * (math.pi / 180.0)
+        sin, cos = torch.sin(angle), torch.cos(angle)
+        one, zero = torch.ones_like(sin), torch.zeros_like(sin)
+        if pos.size(-1) == 2:
+            rows = [[cos, sin], [-sin, cos]]
+        elif self.axis == 0:
+            rows = [[one, zero, zero], [zero, cos, sin], [zero, -sin, cos]]
+        elif self.axis == 1:
+            rows = [[cos, zero, -sin], [zero, one, zero], [sin, zero, cos]]
+        else:
+            rows = [[cos, sin, zero], [-sin, cos, zero], [zero, zero, one]]
+        matrix = torch.stack([torch.stack(r, dim=-1) for r in rows], dim=-2)          # [B, d, d]
+        per_point = matrix[batch]
+        data.pos = torch.bmm(pos.unsqueeze(1), per_point).squeeze(1)
+        if _has_normals(data):
+            data.norm = torch.bmm(data.norm.unsqueeze(1), per_point.to(data.norm.dtype)).squeeze(1)
+        return data
+
+    def __repr__(self):
+        return '{}({}, axis={})'.format(self.__class__.__name__, self.degrees, self.axis)
+
+
+class RandomNormals(object):
+    """Jitter every normal by a random offset in (-translate, +translate) per axis and renormalise
+    (random_normals.py:23-35)."""
+
+    def __init__(self, translate):
+        self.translate = translate
+
+    def __call__(self, data):
+        n = data.norm
+        limit = n.new_tensor([abs(t) for t in _per_axis(self.translate, n.size(1))])
+        n = n + n.new_empty(n.shape).uniform_(-1, 1) * limit
+        data.norm = n / torch.linalg.norm(n, dim=-1, keepdim=True).clamp(1e-5)
+        return data
+
+    def __repr__(self):
+        return '{}({})'.format(self.__class__.__name__, self.translate)

@@ -662,3 +662,21 @@ def test_large_cloud_mode_morton_order_is_transparent():
     for (n1, p1), (_, p2) in zip(plain.named_parameters(), reordered.named_parameters()):
         if p1.grad is not None:
             assert (p1.grad - p2.grad).abs().max().item() < 2e-3 * scale, n1
+
+
+def test_transforms_run_on_a_device_batch():
+    """The augmentations act on a whole device-resident batch (per-cloud parameters, no host round trip) and the result feeds
+    the model as is."""
+    D = dc()
+    import deltaconv_b200.transforms as T
+    from deltaconv_b200.compat import Compose
+    torch.manual_seed(1)
+    data = D.utils.synthetic_batch(4, 256, config=2, num_classes=10).to(DEV)
+    data._num_clouds, data._max_points = 4, 256
+    p0 = data.pos.clone()
+    aug = Compose([T.NormalizeScale(), T.RandomScale((0.8, 1.25)), T.RandomRotate(20, axis=1), T.RandomTranslateGlobal(0.1), T.RandomNormals(0.02)])
+    out = aug(data)
+    assert out.pos.is_cuda and out.norm.is_cuda and not torch.equal(out.pos, p0)
+    assert (out.norm.norm(dim=1) - 1).abs().max() < 1e-5
+    net = no_dropout(D.utils.fill_deterministic(D.models.DeltaNetClassification(3, 10, conv_channels=[16, 32]), 5)).to(DEV).train()
+    assert torch.isfinite(net(out)).all()

@@ -16,6 +16,8 @@ import deltaconv
 from deltaconv.models import DeltaNetClassification, DeltaNetSegmentation
 from deltaconv.nn import DeltaConv, MLP
 from deltaconv.geometry import build_grad_div, estimate_basis
+import deltaconv.transforms as T
+assert repr(T.RandomScale((0.8, 1.2))) == 'RandomScale((0.8, 1.2))'
 assert deltaconv.__name__ == 'deltaconv_b200'
 if provided:
     from torch_geometric.data import Data, Batch
