@@ -45,11 +45,18 @@ def _worker(rank, world, port, out):
     flat.zero()
     loss = ((model(x[b:e]) - y[b:e]) ** 2).sum() / 8 * world      # local mean scaled so the rank-average is the global mean
     loss.backward()
+    assert not flat.packed
     reduced = flat.all_reduce()
+    assert flat.packed and flat.flat.data_ptr() == reduced.data_ptr()   # what FlatSGD.step() reads instead of packing again
     assert model.extra.grad is None                                 # never used: skipped on every rank
     assert model[0].weight.grad.data_ptr() == reduced.data_ptr()    # grads are views of the reduced flat buffer
     if rank == 0:
         torch.save(reduced.clone(), out)
+    address = reduced.data_ptr()
+    flat.zero()
+    assert not flat.packed                                          # a new step starts unpacked ...
+    (((model(x[b:e]) - y[b:e]) ** 2).sum() / 8 * world).backward()
+    assert flat.all_reduce().data_ptr() == address and flat.packed  # ... and packs into the same (stable) buffer
     dist.destroy_process_group()
 
 
@@ -64,6 +71,8 @@ def test_flat_gradient_allreduce_matches_single_process(tmp_path):
     flat = FlatGradients(model.parameters())
     (((model(x) - y) ** 2).sum() / 8).backward()
     assert flat.all_reduce() is None                                # single process: nothing to pack or reduce
+    assert not flat.packed                                          # so an optimizer on the flat buffer packs itself
+    assert flat.pack().numel() == sum(p.numel() for p in model.parameters() if p.grad is not None) and flat.packed
     want = torch.cat([p.grad.reshape(-1) for p in model.parameters() if p.grad is not None])
     assert torch.allclose(got, want, atol=1e-6)
     flat.zero()
