@@ -1,7 +1,9 @@
-"""Diagnostic (GPU box): error budget of the CUDA path vs the fp64 oracle on awkward inputs."""
+"""Diagnostic (GPU box): error budget of the CUDA path vs the fp64 oracle on awkward inputs.  Test infrastructure — it
+lives under tests/ because it imports the oracle; run as `python tests/tools/diag_parity.py`."""
 import sys, os
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), 'tests'))
+_TESTS = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.dirname(_TESTS))
+sys.path.insert(0, _TESTS)
 import torch
 import torch.nn.functional as F
 import deltaconv_b200 as D
