@@ -431,6 +431,83 @@ def run_cuda_arm(args):
         dist.destroy_process_group()
 
 
+# ------------------------------------------------------------------------------------------------
+# second workload (not the contract line): the dataset pre-transform, geodesic farthest-point sampling
+# ------------------------------------------------------------------------------------------------
+
+FPS_CLOUDS, FPS_POINTS, FPS_SAMPLES = 296, 8192, 1024       # train_modelnet.py:32-33: 8 x 1024 sampled points -> 1024
+
+
+def _fps_clouds(count, seed=5):
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    out = []
+    for _ in range(count):
+        u = rng.standard_normal((FPS_POINTS, 3))
+        u /= np.linalg.norm(u, axis=1, keepdims=True)
+        r = 1 + 0.15 * np.sin(3 * np.arctan2(u[:, 1], u[:, 0])) * u[:, 2]
+        out.append((u * r[:, None] * rng.uniform(0.8, 1.25, 3)).astype(np.float32))
+    return out
+
+
+def run_fps_workload(args):
+    """One step = sampling FPS_CLOUDS clouds of 8192 points down to 1024 in one call of ops.geodesic_fps.  CPU beside it: the
+    reference's own sampler (oracle/_ref/libref_fps.so) where it was built, else the C restatement, one cloud per host thread."""
+    import numpy as np
+    from concurrent.futures import ThreadPoolExecutor
+    import deltaconv_b200 as D
+    dev = torch.device('cuda', 0)
+    torch.cuda.set_device(dev)
+    base = _fps_clouds(8)
+    host = torch.from_numpy(np.concatenate([base[b % 8] for b in range(FPS_CLOUDS)])).pin_memory()
+    batch = torch.arange(FPS_CLOUDS, device=dev).repeat_interleave(FPS_POINTS)
+    start = torch.arange(FPS_CLOUDS, dtype=torch.int32, device=dev) * 7 % FPS_POINTS
+    pos = host.to(dev)
+    kw = dict(batch=batch, num_clouds=FPS_CLOUDS, max_points=FPS_POINTS, start=start)
+    out_host = torch.empty(FPS_CLOUDS, FPS_SAMPLES, dtype=torch.int64).pin_memory()
+    for _ in range(max(args.warmup, 3)):
+        D.ops.geodesic_fps(pos, FPS_SAMPLES, **kw)
+    torch.cuda.synchronize()
+    sampler = ClockSampler(0)
+    D._lib.load().dc_reset_launch_count()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    t0 = time.time()
+    ev[0].record()
+    for _ in range(args.steps):
+        D.ops.geodesic_fps(pos, FPS_SAMPLES, **kw)
+    ev[1].record()
+    torch.cuda.synchronize()
+    ms = ev[0].elapsed_time(ev[1]) / args.steps
+    launches = int(D._lib.load().dc_launch_count())
+    t_e2e = time.perf_counter()
+    for _ in range(args.steps):                       # host buffers in, host buffer out
+        out_host.copy_(D.ops.geodesic_fps(host.to(dev, non_blocking=True), FPS_SAMPLES, **kw), non_blocking=True)
+        torch.cuda.synchronize()
+    e2e_ms = 1000 * (time.perf_counter() - t_e2e) / args.steps
+    clocks = sampler.summary(t0, time.time())
+    line = dict(metric='geodesic farthest-point sampling (pre-transform), clouds/s', value=round(FPS_CLOUDS / (ms / 1000), 1), unit='clouds/s',
+                n_gpus=1, steps=args.steps, warmup=max(args.warmup, 3), ms_per_step=round(ms, 3), higher_is_better=True, scaling='weak',
+                vs_baseline=None, dtype='f64', data='synthetic',
+                config=dict(workload=f'{FPS_CLOUDS} clouds x {FPS_POINTS} pts -> {FPS_SAMPLES} samples per call (train_modelnet.py:32-33), 10-NN graph in fp64',
+                            l2='inputs 28 MB fp64 + 28 MB graph per call, resident in L2 by design: the sampler is a latency-bound traversal'),
+                e2e=dict(value=round(FPS_CLOUDS / (e2e_ms / 1000), 1), unit='clouds/s', h2d_bytes_per_step=host.numel() * 4,
+                         d2h_bytes_per_step=out_host.numel() * 8),
+                gpu_launches=launches, clocks=clocks)
+    if not args.no_cpu_baseline:
+        from oracle import fps as ofps
+        cores = os.cpu_count() or 1
+        kind = 'reference' if ofps.have_reference() else 'port'
+        one = (lambda x: ofps.reference_fps(x, FPS_SAMPLES)) if kind == 'reference' else (lambda x: ofps.restated_fps(x, FPS_SAMPLES, 0))
+        sample = [base[i % 8] for i in range(4 * cores)]
+        t = time.perf_counter()
+        with ThreadPoolExecutor(cores) as pool:
+            list(pool.map(one, sample))
+        cpu = len(sample) / (time.perf_counter() - t)
+        line['cpu_baseline'] = dict(value=round(cpu, 1), unit='clouds/s', cores=cores, kind=kind,
+                                    sample=f'{len(sample)} clouds of the same shape, one cloud per host thread ({cores} threads)')
+    print(json.dumps(line), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
@@ -440,7 +517,11 @@ def main():
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-graph', action='store_true', help='time eager launches instead of CUDA-graph replays')
     ap.add_argument('--detail', default=None, help='write the per-call device-time table to this file')
+    ap.add_argument('--workload', default='train', choices=['train', 'fps'],
+                    help="'fps': time the geodesic farthest-point sampling pre-transform instead of the training step (1 GPU)")
     args = ap.parse_args()
+    if args.workload == 'fps':
+        return run_fps_workload(args)
     if args.impl == 'reference':
         run_reference_arm(args)
     else:

@@ -9,5 +9,6 @@ from . import ops            # noqa: F401
 from . import geometry       # noqa: F401
 from . import nn             # noqa: F401
 from . import models         # noqa: F401
+from . import transforms     # noqa: F401
 
 __version__ = (0, 1, 0)

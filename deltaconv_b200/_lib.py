@@ -24,6 +24,8 @@ _SIGNATURES = {
     'dc_knn': [_P, _P, _I, _I, _I, _P, _P, _P, _P],
     'dc_morton_keys': [_P, _P, _I, _I, _P, _P, _Z, _P],
     'dc_knn_grid_ws_bytes': [_I, _I],
+    'dc_geodesic_fps_ws_bytes': [_I],
+    'dc_geodesic_fps': [_P, _P, _I, _I, _I, _I, _P, _P, _P, _P, _Z, _P],
     'dc_set_knn_grid_density': [_F],
     'dc_knn_grid': [_P, _P, _I, _I, _I, _P, _P, _P, _P, _Z, _P],
     'dc_ell_from_edge_index': [_P, _I, _I, _P, _P],
@@ -88,7 +90,7 @@ _SIGNATURES = {
 }
 _RESTYPES = {'dc_launch_count': ctypes.c_longlong, 'dc_reset_launch_count': None,
              'dc_ell_transpose_ws_bytes': _Z, 'dc_build_ws_bytes': _Z, 'dc_colreduce_ws_bytes': _Z,
-             'dc_gemm_ws_bytes': _Z, 'dc_central_ws_bytes': _Z, 'dc_knn_grid_ws_bytes': _Z}
+             'dc_gemm_ws_bytes': _Z, 'dc_central_ws_bytes': _Z, 'dc_knn_grid_ws_bytes': _Z, 'dc_geodesic_fps_ws_bytes': _Z}
 
 _lib = None
 

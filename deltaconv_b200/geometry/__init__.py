@@ -1,4 +1,5 @@
 from .operators import *          # noqa: F401,F403
+from .fps import *                # noqa: F401,F403
 from .grad_div_mls import *       # noqa: F401,F403
 from .helpers import *            # noqa: F401,F403
 from .connection import *         # noqa: F401,F403

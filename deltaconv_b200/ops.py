@@ -150,6 +150,33 @@ def spatial_order(pos, batch=None, num_clouds=None):
     return torch.argsort(keys, stable=True)
 
 
+def geodesic_fps(pos, n_samples, batch=None, num_clouds=None, start=None, max_points=None, return_dist=False):
+    """Geodesic farthest-point sampling of every cloud at once (dc_geodesic_fps; reference sampling.cpp:21-81 does one cloud
+    per call on one CPU thread).  `pos` [N,3] CUDA, fp32 or fp64 (the reference computes in fp64 whatever it is given);
+    `start` [B] = first sample of every cloud as an index inside the cloud, drawn uniformly when None like the reference.
+    Returns [B, n_samples] int64 indices inside each cloud (and the distance of every point to its nearest sample)."""
+    if not (torch.is_tensor(pos) and pos.is_cuda and pos.dtype in (_F32, torch.float64)):
+        raise _lib.DeltaConvLibraryError("geodesic_fps: expected an fp32 or fp64 CUDA tensor (deltaconv_b200 has no CPU path)")
+    if pos.dim() != 2 or pos.size(1) != 3:
+        raise _lib.DeltaConvLibraryError(f"geodesic_fps: expected pos of shape [N,3], got {tuple(pos.shape)}")
+    N = pos.size(0)
+    cp, B, maxp = cloud_layout(batch, N, pos.device, num_clouds, max_points)
+    pos64 = pos.to(torch.float64).contiguous()
+    if start is None:
+        sizes = (cp[1:] - cp[:-1]).to(torch.float64)
+        start = (torch.rand(B, device=pos.device, dtype=torch.float64) * sizes).floor().clamp_(min=0).to(_I32)
+        start = torch.minimum(start, (sizes - 1).clamp_(min=0).to(_I32))
+    else:
+        start = torch.as_tensor(start, device=pos.device).to(_I32).reshape(B).contiguous()
+    samples = torch.empty(B, n_samples, dtype=_I32, device=pos.device)
+    dist = torch.empty(N, dtype=torch.float64, device=pos.device) if return_dist else None
+    nb = query('dc_geodesic_fps_ws_bytes', N)
+    ws = workspace(nb, pos.device)
+    call('dc_geodesic_fps', ptr(pos64), ptr(cp), B, N, min(maxp, N), int(n_samples), ptr(start), ptr(samples), ptr(dist), ptr(ws), nb)
+    samples = samples.long()
+    return (samples, dist) if return_dist else samples
+
+
 def graph_of(edge_index, num_points):
     """EllGraph behind a [2,E] int64 edge_index: the one `knn_graph` attached, else a conversion
     under the reference's own assumption (rows grouped by centre, same k everywhere —

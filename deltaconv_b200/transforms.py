@@ -3,14 +3,16 @@ so that they also run on a whole device-resident `Batch`: with a `batch` vector 
 parameters and all clouds are transformed in one vectorised pass on the GPU; without one they act on a
 single cloud exactly like the reference's per-sample CPU transforms.  Plain torch — they are not on the hot path.
 
-Not provided: `SamplePoints` (needs mesh faces) and `GeodesicFPS` (the reference's C++ pre-transform, §8f-3).
+`GeodesicFPS` is the exception: it runs on the CUDA library (dc_geodesic_fps), on one cloud or on a whole batch.
+
+Not provided: `SamplePoints` (needs mesh faces).
 """
 import math
 import numbers
 
 import torch
 
-__all__ = ['NormalizeScale', 'NormalizeAxes', 'RandomScale', 'RandomTranslateGlobal', 'RandomRotate', 'RandomNormals']
+__all__ = ['NormalizeScale', 'NormalizeAxes', 'RandomScale', 'RandomTranslateGlobal', 'RandomRotate', 'RandomNormals', 'GeodesicFPS']
 
 
 def _clouds(data):
@@ -181,3 +183,63 @@ class RandomNormals(object):
 
     def __repr__(self):
         return '{}({})'.format(self.__class__.__name__, self.translate)
+
+
+class GeodesicFPS(object):
+    """Keep `n_samples` points of every cloud, chosen by geodesic farthest-point sampling (geodesic_fps.py:14-43; the
+    sampler is the CUDA one, `ops.geodesic_fps`).  On a single cloud the fields are handled exactly like the reference's:
+    `sample_idx` is stored, `pos`, `norm` (or `normal`, moved to `norm`), `x` and a per-point `y` are indexed, a cloud
+    smaller than `n_samples` is tiled.  With a `batch` vector every cloud is sampled in the same launch and `batch` is
+    rebuilt; `sample_idx` then indexes the rows of the incoming batch."""
+
+    def __init__(self, n_samples=None, store_original=False):
+        self.n_samples = n_samples
+        self.store_original = store_original
+
+    def __call__(self, data):
+        from . import ops
+        pos = data.pos
+        if self.n_samples is None:
+            self.n_samples = pos.size(0)
+        n = self.n_samples
+        batch = getattr(data, 'batch', None)
+        device_pos = pos if pos.is_cuda else pos.cuda()
+        if batch is None:
+            P = pos.size(0)
+            idx = ops.geodesic_fps(device_pos, n)[0]
+            if P < n:
+                idx = idx[:P].repeat(math.ceil(n / P))
+            idx = idx[:n]
+        else:
+            device_batch = batch if batch.is_cuda else batch.cuda()
+            cp, B, _ = ops.cloud_layout(device_batch, pos.size(0), device_pos.device, getattr(data, '_num_clouds', None),
+                                        getattr(data, '_max_points', None))
+            local = ops.geodesic_fps(device_pos, n, batch=device_batch, num_clouds=B)           # [B, n]
+            sizes = (cp[1:] - cp[:-1]).long()
+            # a cloud smaller than n: its first P samples, tiled (geodesic_fps.py:24-25)
+            slot = torch.arange(n, device=local.device)[None, :] % sizes.clamp(min=1)[:, None]
+            idx = (torch.gather(local, 1, slot) + cp[:-1].long()[:, None]).reshape(-1)
+            data.batch = torch.arange(B, device=batch.device).repeat_interleave(n)
+            if hasattr(data, '_max_points'):
+                data._num_clouds, data._max_points = B, n
+        idx = idx.to(pos.device)
+        assert idx.max() <= pos.size(0)
+        assert idx.min() >= 0
+        data.sample_idx = idx
+        if self.store_original:
+            data.pos_original = data.pos
+            data.y_original = data.y
+        data.pos = pos[idx]
+        if getattr(data, 'norm', None) is not None:
+            data.norm = data.norm[idx]
+        if getattr(data, 'normal', None) is not None:
+            data.norm = data.normal[idx]
+        if getattr(data, 'x', None) is not None:
+            data.x = data.x[idx]
+        y = getattr(data, 'y', None)
+        if y is not None and type(y) is not int and y.size(0) > 1 and y.size(0) == pos.size(0):
+            data.y = y[idx]
+        return data
+
+    def __repr__(self):
+        return '{}()'.format(self.__class__.__name__)

@@ -57,6 +57,20 @@ int dc_knn_grid(const float* pos, const int32_t* cloud_ptr, int B, int N, int k,
  * No counterpart in the reference (its point order is whatever the dataset has); ws: B * 24 bytes. */
 int dc_morton_keys(const float* pos, const int32_t* cloud_ptr, int B, int N, int64_t* keys, void* ws, size_t ws_bytes, void* stream);
 
+/* geodesicFPS(points, n_samples) — deltaconv/cpp/core.cpp:17-27, sampling.cpp:21-81 (pybind11 module deltaconv_bindings;
+ * Python face deltaconv/geometry/fps.py:5-19, transform deltaconv/transforms/geodesic_fps.py:14-43) for a whole batch of clouds:
+ * farthest-point sampling by shortest-path distance on the 10-nearest-neighbour graph of every cloud, fp64 like the reference
+ * (pos is [N,3] DOUBLE), the same sample sequence bit for bit when started from the same point.
+ * start[B]: first sample of every cloud (index inside the cloud; the reference draws it at random, sampling.cpp:33-40);
+ * samples[B, n_samples] int32: indices inside the cloud (-1 for an empty cloud); n_samples may exceed a cloud's size (the
+ * surplus repeats index 0 as in the reference); dist_or_null[N]: distance of every point to its nearest sample.
+ * max_cloud_points: an upper bound on the cloud sizes (N is always valid); clouds up to 11,264 points are sampled from
+ * shared memory, larger ones from the workspace.  Clouds of fewer than 11 points use the neighbours they have (the
+ * reference throws there).  Workspace from dc_geodesic_fps_ws_bytes(N). */
+size_t dc_geodesic_fps_ws_bytes(int N);
+int dc_geodesic_fps(const double* pos, const int32_t* cloud_ptr, int B, int N, int max_cloud_points, int n_samples,
+                    const int32_t* start, int32_t* samples, double* dist_or_null, void* ws, size_t ws_bytes, void* stream);
+
 /* [2,N*k] int64 edge_index (rows grouped by centre, fixed k — grad_div_mls.py:24-25,224) <-> ELL idx. */
 int dc_ell_from_edge_index(const int64_t* edge_index, int N, int k, int32_t* idx, void* stream);
 int dc_edge_index_from_ell(const int32_t* idx, int N, int k, int64_t* edge_index, void* stream);
