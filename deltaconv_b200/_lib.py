@@ -25,7 +25,7 @@ _SIGNATURES = {
     'dc_morton_keys': [_P, _P, _I, _I, _P, _P, _Z, _P],
     'dc_knn_grid_ws_bytes': [_I, _I],
     'dc_geodesic_fps_ws_bytes': [_I],
-    'dc_geodesic_fps': [_P, _P, _I, _I, _I, _I, _P, _P, _P, _P, _Z, _P],
+    'dc_geodesic_fps': [_P, _P, _I, _I, _I, _I, _P, _P, _P, _P, _P, _Z, _P],
     'dc_set_knn_grid_density': [_F],
     'dc_knn_grid': [_P, _P, _I, _I, _I, _P, _P, _P, _P, _Z, _P],
     'dc_ell_from_edge_index': [_P, _I, _I, _P, _P],

@@ -3,66 +3,128 @@
 //
 // The reference handles one cloud on one CPU thread: kd-tree 10-NN graph, then per sample one Dijkstra pass into a distance
 // vector D shared by all passes (D = geodesic distance to the nearest sample so far), then argmax D.  Clouds are
-// independent, so here a batch of clouds is sampled at once, one CTA per cloud, with the cloud's state (D, two work
-// queues, round stamps: 20 bytes per point) in shared memory up to 11,264 points per cloud and in the caller's workspace
-// beyond that.
+// independent, so here a batch of clouds is sampled at once:
+//   1. fps_sort_box_kernel   points gathered into the caller's visiting order (a space-filling-curve order makes step 2 fast;
+//                            any order is correct) + one bounding box per 64 consecutive points;
+//   2. fps_knn_kernel        the 10 nearest other points of every point, a thread per query: boxes that lie farther than the
+//                            current 10th distance are skipped, the rest is scanned exhaustively;
+//   3. fps_sample_kernel     one CTA per cloud, the cloud's state (D, two work queues, two bit masks: 12.25 bytes per point)
+//                            in shared memory up to 18,432 points per cloud — two clouds of 8,192 per SM — and in the
+//                            caller's workspace beyond that.
 //
 // Same numbers as the reference, not just the same algorithm: all arithmetic is fp64 in the reference's order
 // (d2 = (dx*dx + dy*dy) + dz*dz, w = sqrt(d2), no contraction).  A Dijkstra pass is replaced by label-correcting
 // relaxation rounds over a work queue — D[v] = min(D[v], D[u] + w(u,v)) with an atomic min on the bit pattern of the
 // non-negative double.  Rounded addition is monotone and edge weights are non-negative, so the fixed point these rounds
 // reach is exactly the vector Dijkstra returns, bit for bit, whatever the order of the relaxations; the argmax takes the
-// lowest index among equal maxima like Eigen's maxCoeff.  What is NOT pinned: which of several exactly equidistant
-// neighbours the kd-tree of the reference keeps (here: lowest index).
+// lowest ORIGINAL index among equal maxima like Eigen's maxCoeff.  The box test is exact as well: the distance to a box is
+// computed with the same operations as the distance to a point, and each of them is monotone, so it never exceeds the
+// computed distance to any point inside.  What is NOT pinned: which of several exactly equidistant neighbours the
+// kd-tree of the reference keeps (here: lowest original index).
 #include "common.cuh"
 
 namespace {
 
 constexpr int FPS_K = 10;            // neighbours per point, fixed in the reference (sampling.cpp:23)
-constexpr int KNN_T = 256;           // queries per CTA of the graph kernel
-constexpr int KNN_TILE = 1024;       // candidates staged per round (24 KB)
+constexpr int BOX_TILE = 64;         // consecutive points (in visiting order) per bounding box
+constexpr int KNN_WARPS = 8;         // warps of 32 queries per CTA of the graph kernel
 constexpr int FPS_T = 512;           // threads of a sampling CTA
-constexpr int FPS_SMEM_POINTS = 11264;   // 20 B per point -> 220 KB
+constexpr int FPS_SMEM_POINTS = 18432;  // < 65,536: queue entries of shared-memory clouds are 16-bit
 constexpr unsigned long long INF_BITS = 0x7ff0000000000000ULL;
 
-// ---- 10 nearest OTHER points of every point, fp64, ascending (d2, index) ------------------------------------------
+__host__ __device__ constexpr size_t fps_smem_bytes(int points) { return (size_t)points * 12 + 8 * (size_t)((points + 31) / 32); }
+
+__device__ __forceinline__ int orig_of(const int* __restrict__ order, int j) { return order != nullptr ? __ldg(order + j) : j; }
+
+// ---- 1. gather into visiting order + boxes ----------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) fps_sort_box_kernel(const double* __restrict__ pos, const int* __restrict__ order, int N,
+                                                           double* __restrict__ spos, double* __restrict__ boxes) {
+    const int lane = threadIdx.x & 31;
+    const int g = blockIdx.x * 4 + (threadIdx.x >> 5);
+    if ((long long)g * BOX_TILE >= N) return;
+    const double inf = __longlong_as_double(INF_BITS);
+    double lo[3] = {inf, inf, inf}, hi[3] = {-inf, -inf, -inf};
+#pragma unroll
+    for (int h = 0; h < BOX_TILE / 32; ++h) {
+        const int i = g * BOX_TILE + h * 32 + lane;
+        if (i < N) {
+            const int o = orig_of(order, i);
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                const double p = pos[3 * (size_t)o + a];
+                spos[3 * (size_t)i + a] = p;
+                lo[a] = fmin(lo[a], p); hi[a] = fmax(hi[a], p);
+            }
+        }
+    }
+#pragma unroll
+    for (int a = 0; a < 3; ++a)
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            lo[a] = fmin(lo[a], __shfl_xor_sync(FULL, lo[a], o));
+            hi[a] = fmax(hi[a], __shfl_xor_sync(FULL, hi[a], o));
+        }
+    if (lane == 0) {
+#pragma unroll
+        for (int a = 0; a < 3; ++a) { boxes[6 * (size_t)g + a] = lo[a]; boxes[6 * (size_t)g + 3 + a] = hi[a]; }
+    }
+}
+
+// ---- 2. 10 nearest OTHER points of every point, fp64, ascending (d2, original index) ---------------------------------
 // generateKNN (sampling.cpp:5-17) = nanoflann L2_Simple_Adaptor<double>: d2 accumulated x, y, z from zero.  The point
 // itself, which the reference puts in front as a zero-length self loop, is left out: it can never shorten a path.
-__global__ void __launch_bounds__(KNN_T) fps_knn_kernel(const double* __restrict__ pos, const int* __restrict__ cloud_ptr, int B, int N,
-                                                        int* __restrict__ nbr, double* __restrict__ wgt) {
-    __shared__ double tile[KNN_TILE * 3];
-    const int i = blockIdx.x * KNN_T + threadIdx.x;
-    const int first = blockIdx.x * KNN_T, last = min(N, first + KNN_T) - 1;
-    // candidates any query of this CTA can need: from the start of the first query's cloud to the end of the last one's
-    const int c_first = cloud_of(cloud_ptr, B, first), c_last = cloud_of(cloud_ptr, B, last);
-    const int span_s = cloud_ptr[c_first], span_e = cloud_ptr[c_last + 1];
-    int s = 0, e = 0;
-    double qx = 0., qy = 0., qz = 0.;
-    if (i < N) {
-        const int c = cloud_of(cloud_ptr, B, i);
-        s = cloud_ptr[c]; e = cloud_ptr[c + 1];
-        qx = pos[3 * (size_t)i]; qy = pos[3 * (size_t)i + 1]; qz = pos[3 * (size_t)i + 2];
-    }
+// Indices here are positions in visiting order; `order` maps them back where ties have to be broken.
+__device__ __forceinline__ double dist2_rn(double dx, double dy, double dz) {
+    return __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
+}
+
+__global__ void __launch_bounds__(KNN_WARPS * 32) fps_knn_kernel(const double* __restrict__ spos, const double* __restrict__ boxes,
+                                                                 const int* __restrict__ order, const int* __restrict__ cloud_ptr,
+                                                                 int B, int N, int* __restrict__ nbr, double* __restrict__ wgt) {
+    const int lane = threadIdx.x & 31;
+    const int qbase = (blockIdx.x * KNN_WARPS + (threadIdx.x >> 5)) * 32;
+    if (qbase >= N) return;                                    // whole warp
+    const int i = qbase + lane;
+    const bool valid = i < N;
+    const int iq = valid ? i : N - 1;
+    const int c = cloud_of(cloud_ptr, B, iq);
+    const int s = cloud_ptr[c], e = cloud_ptr[c + 1];
+    const double qx = spos[3 * (size_t)iq], qy = spos[3 * (size_t)iq + 1], qz = spos[3 * (size_t)iq + 2];
+    const int g_lo = __reduce_min_sync(FULL, s) / BOX_TILE, g_hi = (__reduce_max_sync(FULL, e) - 1) / BOX_TILE;
+    const int g0 = qbase / BOX_TILE;
+
     double bd[FPS_K];
     int bi[FPS_K];
 #pragma unroll
     for (int t = 0; t < FPS_K; ++t) { bd[t] = __longlong_as_double(INF_BITS); bi[t] = -1; }
 
-    for (int base = span_s; base < span_e; base += KNN_TILE) {
-        const int n_tile = min(KNN_TILE, span_e - base);
-        __syncthreads();
-        for (int t = threadIdx.x; t < n_tile * 3; t += KNN_T) tile[t] = pos[3 * (size_t)base + t];
-        __syncthreads();
-        const int lo = max(base, s) - base, hi = min(base + n_tile, e) - base;
-        for (int j = lo; j < hi; ++j) {
-            const double dx = __dsub_rn(qx, tile[3 * j]), dy = __dsub_rn(qy, tile[3 * j + 1]), dz = __dsub_rn(qz, tile[3 * j + 2]);
-            const double d = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
-            // candidates arrive in ascending index, so a strict comparison keeps the lower index among equals
-            if (d < bd[FPS_K - 1] && base + j != i) {
-                bd[FPS_K - 1] = d; bi[FPS_K - 1] = base + j;
+    // own box first, then outwards in both directions: neighbours in a space-filling order are mostly neighbours in space,
+    // so the 10th distance is tight after the first boxes and most of the others fail the test
+    const int reach = max(g0 - g_lo, g_hi - g0);
+    for (int step = 0; step <= reach; ++step) {
+#pragma unroll 1
+        for (int side = 0; side < 2; ++side) {
+            const int g = side == 0 ? g0 + step : g0 - step;
+            if (g > g_hi || g < g_lo || (side == 1 && step == 0)) continue;
+            const double* bx = boxes + 6 * (size_t)g;
+            const double ax = fmax(fmax(__dsub_rn(__ldg(bx), qx), __dsub_rn(qx, __ldg(bx + 3))), 0.);
+            const double ay = fmax(fmax(__dsub_rn(__ldg(bx + 1), qy), __dsub_rn(qy, __ldg(bx + 4))), 0.);
+            const double az = fmax(fmax(__dsub_rn(__ldg(bx + 2), qz), __dsub_rn(qz, __ldg(bx + 5))), 0.);
+            const int j_first = g * BOX_TILE, j_last = min(j_first + BOX_TILE, N);
+            const bool near = valid && max(j_first, s) < min(j_last, e) && dist2_rn(ax, ay, az) <= bd[FPS_K - 1];
+            if (!__any_sync(FULL, near)) continue;
+#pragma unroll 4
+            for (int j = j_first; j < j_last; ++j) {
+                const double d = dist2_rn(__dsub_rn(qx, __ldg(spos + 3 * (size_t)j)), __dsub_rn(qy, __ldg(spos + 3 * (size_t)j + 1)),
+                                          __dsub_rn(qz, __ldg(spos + 3 * (size_t)j + 2)));
+                if (!(d <= bd[FPS_K - 1]) || !near || (unsigned)(j - s) >= (unsigned)(e - s) || j == i) continue;
+                if (d == bd[FPS_K - 1] && (bi[FPS_K - 1] < 0 || orig_of(order, j) > orig_of(order, bi[FPS_K - 1]))) continue;
+                bd[FPS_K - 1] = d; bi[FPS_K - 1] = j;
 #pragma unroll
                 for (int t = FPS_K - 1; t > 0; --t) {
-                    if (bd[t] < bd[t - 1]) {
+                    const bool up = bd[t] < bd[t - 1] ||
+                                    (bd[t] == bd[t - 1] && bi[t - 1] >= 0 && orig_of(order, bi[t]) < orig_of(order, bi[t - 1]));
+                    if (up) {
                         const double td = bd[t]; bd[t] = bd[t - 1]; bd[t - 1] = td;
                         const int ti = bi[t]; bi[t] = bi[t - 1]; bi[t - 1] = ti;
                     }
@@ -70,84 +132,77 @@ __global__ void __launch_bounds__(KNN_T) fps_knn_kernel(const double* __restrict
             }
         }
     }
-    if (i >= N) return;
+    if (!valid) return;
 #pragma unroll
     for (int t = 0; t < FPS_K; ++t) {
         // clouds of fewer than 11 points: the free slots become self loops of length zero
         const bool have = bi[t] >= 0;
-        nbr[(size_t)i * FPS_K + t] = have ? bi[t] - s : i - s;             // index inside the cloud
+        nbr[(size_t)i * FPS_K + t] = have ? bi[t] - s : i - s;             // position inside the cloud, visiting order
         wgt[(size_t)i * FPS_K + t] = have ? __dsqrt_rn(bd[t]) : 0.;        // Vector3::norm of the edge (sampling.cpp:71)
     }
 }
 
-// ---- the sampler: one CTA per cloud ----------------------------------------------------------------------------------
-struct FpsState {
-    unsigned long long* D;   // bit patterns of non-negative doubles: unsigned order = numeric order
-    int* q[2];
-    int* stamp;              // round in which the point was last queued
+// ---- 3. the sampler: one CTA per cloud ---------------------------------------------------------------------------------
+struct FpsShared {
+    int cnt[3];
+    unsigned long long red_v[FPS_T / 32];
+    int red_i[FPS_T / 32], red_o[FPS_T / 32];
+    int next_src, start_pos;
 };
 
-__global__ void __launch_bounds__(FPS_T) fps_sample_kernel(const int* __restrict__ cloud_ptr, const int* __restrict__ nbr,
-                                                           const double* __restrict__ wgt, const int* __restrict__ start,
-                                                           int n_samples, int* __restrict__ samples, double* __restrict__ dist_or_null,
-                                                           int smem_points, unsigned long long* gD, int* gq0, int* gq1, int* gstamp) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    __shared__ int cnt[3];
-    __shared__ unsigned long long red_v[FPS_T / 32];
-    __shared__ int red_i[FPS_T / 32];
-    __shared__ int next_src;
+// (value, original index) order of the argmax: larger value first, then the lower original index (Eigen maxCoeff keeps the first)
+__device__ __forceinline__ bool better(unsigned long long v, int o, unsigned long long bv, int bo) { return v > bv || (v == bv && o < bo); }
 
-    const int b = blockIdx.x;
-    const int s = cloud_ptr[b], P = cloud_ptr[b + 1] - s;
-    int* out = samples + (size_t)b * n_samples;
-    if (P <= 0) {
-        for (int t = threadIdx.x; t < n_samples; t += FPS_T) out[t] = -1;
-        return;
-    }
-    FpsState st;
-    if (P <= smem_points) {
-        st.D = (unsigned long long*)smem_raw;
-        st.q[0] = (int*)(st.D + P);
-        st.q[1] = st.q[0] + P;
-        st.stamp = st.q[1] + P;
-    } else {
-        st.D = gD + s; st.q[0] = gq0 + s; st.q[1] = gq1 + s; st.stamp = gstamp + s;
-    }
-    const int* my_nbr = nbr + (size_t)s * FPS_K;
-    const double* my_w = wgt + (size_t)s * FPS_K;
+// D: bit patterns of non-negative doubles (unsigned order = numeric order).  Queue `round & 1` holds the points whose
+// distance dropped in the round before; mask `round & 1` has a bit per point in that queue, so a point enters it once.
+template <typename QT>
+__device__ void fps_run(FpsShared& sh, unsigned long long* D, QT* q0, QT* q1, unsigned* m0, unsigned* m1, int mbase, bool own_masks, int s, int P,
+                        const int* __restrict__ my_nbr, const double* __restrict__ my_w, const int* __restrict__ order, int want_start,
+                        int n_samples, int* __restrict__ out, double* __restrict__ dist_or_null) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-
-    for (int t = threadIdx.x; t < P; t += FPS_T) { st.D[t] = INF_BITS; st.stamp[t] = -1; }
-    int src = min(max(start[b], 0), P - 1);
-    int round = 0;                                   // grows over the whole kernel: stamps never repeat
-    if (threadIdx.x == 0) out[0] = src;
+    for (int t = threadIdx.x; t < P; t += FPS_T) D[t] = INF_BITS;
+    if (own_masks)                                                   // workspace masks are cleared by the host (clouds share words)
+        for (int t = threadIdx.x; t < (P + 31) / 32 + 1; t += FPS_T) { m0[t] = 0u; m1[t] = 0u; }
+    if (threadIdx.x == 0) sh.start_pos = order != nullptr ? 0 : want_start;
     __syncthreads();
+    if (order != nullptr)
+        for (int t = threadIdx.x; t < P; t += FPS_T)
+            if (order[s + t] - s == want_start) sh.start_pos = t;
+    __syncthreads();
+    int src = sh.start_pos;
+    int round = 0;
+    if (threadIdx.x == 0) out[0] = want_start;
 
     for (int smp = 1; smp <= n_samples; ++smp) {
         if (smp == n_samples && dist_or_null == nullptr) break;      // the pass after the last sample only serves `dist`
         // one Dijkstra pass of the reference (sampling.cpp:56-81) from `src`, into the shared D
         if (threadIdx.x == 0) {
-            st.D[src] = 0ULL;
-            st.q[round & 1][0] = src;
-            cnt[round % 3] = 1; cnt[(round + 1) % 3] = 0;
+            D[src] = 0ULL;
+            ((round & 1) ? q1 : q0)[0] = (QT)src;
+            atomicOr(((round & 1) ? m1 : m0) + ((mbase + src) >> 5), 1u << ((mbase + src) & 31));
+            sh.cnt[round % 3] = 1; sh.cnt[(round + 1) % 3] = 0;
         }
         __syncthreads();
         while (true) {
-            const int F = cnt[round % 3];
+            const int F = sh.cnt[round % 3];
             if (F == 0) break;
-            if (threadIdx.x == 0) cnt[(round + 2) % 3] = 0;
-            const int* qc = st.q[round & 1];
-            int* qn = st.q[(round + 1) & 1];
-            int* cn = &cnt[(round + 1) % 3];
+            if (threadIdx.x == 0) sh.cnt[(round + 2) % 3] = 0;
+            const QT* qc = (round & 1) ? q1 : q0;
+            QT* qn = (round & 1) ? q0 : q1;
+            unsigned* mc = (round & 1) ? m1 : m0;
+            unsigned* mn = (round & 1) ? m0 : m1;
+            int* cn = &sh.cnt[(round + 1) % 3];
             for (int it = threadIdx.x; it < F * FPS_K; it += FPS_T) {
-                const int u = qc[it / FPS_K], j = it % FPS_K;
+                const int u = (int)qc[it / FPS_K], j = it % FPS_K;
+                if (j == 0) atomicAnd(mc + ((mbase + u) >> 5), ~(1u << ((mbase + u) & 31)));     // free the bit for round + 2
                 const int v = my_nbr[(size_t)u * FPS_K + j];
-                const double du = __longlong_as_double(*(volatile unsigned long long*)(st.D + u));
+                const double du = __longlong_as_double(*(volatile unsigned long long*)(D + u));
                 const unsigned long long nd = (unsigned long long)__double_as_longlong(__dadd_rn(du, my_w[(size_t)u * FPS_K + j]));
-                if (nd < *(volatile unsigned long long*)(st.D + v)) {
-                    const unsigned long long old = atomicMin(st.D + v, nd);
-                    if (nd < old && atomicExch(st.stamp + v, round + 1) != round + 1) {
-                        qn[atomicAdd(cn, 1)] = v;
+                if (nd < *(volatile unsigned long long*)(D + v)) {
+                    const unsigned long long old = atomicMin(D + v, nd);
+                    const unsigned bit = 1u << ((mbase + v) & 31);
+                    if (nd < old && !(atomicOr(mn + ((mbase + v) >> 5), bit) & bit)) {
+                        qn[atomicAdd(cn, 1)] = (QT)v;
                         // next round starts with v's edges: pull them from L2 while this round finishes
                         asm volatile("prefetch.global.L1 [%0];" :: "l"(my_nbr + (size_t)v * FPS_K));
                         asm volatile("prefetch.global.L1 [%0];" :: "l"(my_w + (size_t)v * FPS_K));
@@ -159,72 +214,120 @@ __global__ void __launch_bounds__(FPS_T) fps_sample_kernel(const int* __restrict
             __syncthreads();
         }
         if (smp == n_samples) break;
-        // farthest point: largest D, lowest index among equals (Eigen maxCoeff, sampling.cpp:47)
+        // farthest point: largest D, lowest original index among equals (Eigen maxCoeff, sampling.cpp:47)
         unsigned long long bv = 0ULL;
-        int bidx = 0x7fffffff;
+        int bidx = 0, bo = 0x7fffffff;
         for (int t = threadIdx.x; t < P; t += FPS_T) {
-            const unsigned long long v = st.D[t];
-            if (v > bv || (v == bv && t < bidx)) { bv = v; bidx = t; }
+            const unsigned long long v = D[t];
+            if (v > bv) { bv = v; bidx = t; bo = -1; }                                  // original index fetched only if a tie needs it
+            else if (v == bv) {
+                if (bo == -1) bo = orig_of(order, s + bidx);
+                const int o = orig_of(order, s + t);
+                if (o < bo) { bidx = t; bo = o; }
+            }
         }
+        if (bo == -1) bo = orig_of(order, s + bidx);
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             const unsigned long long ov = __shfl_xor_sync(FULL, bv, o);
-            const int oi = __shfl_xor_sync(FULL, bidx, o);
-            if (ov > bv || (ov == bv && oi < bidx)) { bv = ov; bidx = oi; }
+            const int oi = __shfl_xor_sync(FULL, bidx, o), oo = __shfl_xor_sync(FULL, bo, o);
+            if (better(ov, oo, bv, bo)) { bv = ov; bidx = oi; bo = oo; }
         }
-        if (lane == 0) { red_v[warp] = bv; red_i[warp] = bidx; }
+        if (lane == 0) { sh.red_v[warp] = bv; sh.red_i[warp] = bidx; sh.red_o[warp] = bo; }
         __syncthreads();
         if (warp == 0) {
-            bv = lane < FPS_T / 32 ? red_v[lane] : 0ULL;
-            bidx = lane < FPS_T / 32 ? red_i[lane] : 0x7fffffff;
+            bv = lane < FPS_T / 32 ? sh.red_v[lane] : 0ULL;
+            bidx = lane < FPS_T / 32 ? sh.red_i[lane] : 0;
+            bo = lane < FPS_T / 32 ? sh.red_o[lane] : 0x7fffffff;
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) {
                 const unsigned long long ov = __shfl_xor_sync(FULL, bv, o);
-                const int oi = __shfl_xor_sync(FULL, bidx, o);
-                if (ov > bv || (ov == bv && oi < bidx)) { bv = ov; bidx = oi; }
+                const int oi = __shfl_xor_sync(FULL, bidx, o), oo = __shfl_xor_sync(FULL, bo, o);
+                if (better(ov, oo, bv, bo)) { bv = ov; bidx = oi; bo = oo; }
             }
-            if (lane == 0) { next_src = bidx; out[smp] = bidx; }
+            if (lane == 0) { sh.next_src = bidx; out[smp] = bo - s; }
         }
         __syncthreads();
-        src = next_src;
+        src = sh.next_src;
     }
     if (dist_or_null != nullptr)
-        for (int t = threadIdx.x; t < P; t += FPS_T) dist_or_null[s + t] = __longlong_as_double((long long)st.D[t]);
+        for (int t = threadIdx.x; t < P; t += FPS_T) dist_or_null[orig_of(order, s + t)] = __longlong_as_double((long long)D[t]);
+}
+
+__global__ void __launch_bounds__(FPS_T, 2) fps_sample_kernel(const int* __restrict__ cloud_ptr, const int* __restrict__ nbr,
+                                                              const double* __restrict__ wgt, const int* __restrict__ order,
+                                                              const int* __restrict__ start, int n_samples, int* __restrict__ samples,
+                                                              double* __restrict__ dist_or_null, int smem_points,
+                                                              unsigned long long* gD, int* gq0, int* gq1, unsigned* gm0, unsigned* gm1) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ FpsShared sh;
+    const int b = blockIdx.x;
+    const int s = cloud_ptr[b], P = cloud_ptr[b + 1] - s;
+    int* out = samples + (size_t)b * n_samples;
+    if (P <= 0) {
+        for (int t = threadIdx.x; t < n_samples; t += FPS_T) out[t] = -1;
+        return;
+    }
+    const int want = min(max(start[b], 0), P - 1);
+    const int* my_nbr = nbr + (size_t)s * FPS_K;
+    const double* my_w = wgt + (size_t)s * FPS_K;
+    if (P <= smem_points) {
+        unsigned long long* D = (unsigned long long*)smem_raw;
+        unsigned short* q0 = (unsigned short*)(D + P);
+        unsigned short* q1 = q0 + P;
+        unsigned* m0 = (unsigned*)(q1 + P);
+        unsigned* m1 = m0 + (P + 31) / 32 + 1;
+        fps_run<unsigned short>(sh, D, q0, q1, m0, m1, 0, true, s, P, my_nbr, my_w, order, want, n_samples, out, dist_or_null);
+        return;
+    }
+    fps_run<int>(sh, gD + s, gq0 + s, gq1 + s, gm0, gm1, s, false, s, P, my_nbr, my_w, order, want, n_samples, out, dist_or_null);
 }
 
 size_t align256(size_t n) { return (n + 255) / 256 * 256; }
 
 }  // namespace
 
-// nbr + weights, then the out-of-shared-memory state (D, two queues, stamps) that only clouds above 11,264 points use
+// ordered positions + boxes + graph (neighbours, edge lengths), then the out-of-shared-memory state (D, two queues, two
+// masks) that only clouds above 18,432 points use
 extern "C" size_t dc_geodesic_fps_ws_bytes(int N) {
     const size_t n = (size_t)(N > 0 ? N : 0);
-    return align256(n * FPS_K * 4) + align256(n * FPS_K * 8) + align256(n * 8) + 3 * align256(n * 4);
+    const size_t tiles = (n + BOX_TILE - 1) / BOX_TILE;
+    return align256(n * 24) + align256(tiles * 48) + align256(n * FPS_K * 4) + align256(n * FPS_K * 8) + align256(n * 8) +
+           2 * align256(n * 4) + 2 * align256((n / 32 + 2) * 4);
 }
 
 extern "C" int dc_geodesic_fps(const double* pos, const int32_t* cloud_ptr, int B, int N, int max_cloud_points, int n_samples,
-                               const int32_t* start, int32_t* samples, double* dist_or_null, void* ws, size_t ws_bytes, void* stream) {
+                               const int32_t* order_or_null, const int32_t* start, int32_t* samples, double* dist_or_null,
+                               void* ws, size_t ws_bytes, void* stream) {
     DC_REQUIRE(B >= 1 && N >= 0 && n_samples >= 1, "dc_geodesic_fps: need B >= 1, N >= 0, n_samples >= 1");
     DC_REQUIRE(max_cloud_points >= 0 && max_cloud_points <= N, "dc_geodesic_fps: max_cloud_points must be in [0, N]");
     DC_REQUIRE(ws_bytes >= dc_geodesic_fps_ws_bytes(N), "dc_geodesic_fps: workspace too small");
     cudaStream_t st = (cudaStream_t)stream;
+    const size_t tiles = ((size_t)N + BOX_TILE - 1) / BOX_TILE;
     char* w = (char*)ws;
+    double* spos = (double*)w; w += align256((size_t)N * 24);
+    double* boxes = (double*)w; w += align256(tiles * 48);
     int* nbr = (int*)w; w += align256((size_t)N * FPS_K * 4);
     double* wgt = (double*)w; w += align256((size_t)N * FPS_K * 8);
     unsigned long long* gD = (unsigned long long*)w; w += align256((size_t)N * 8);
     int* gq0 = (int*)w; w += align256((size_t)N * 4);
     int* gq1 = (int*)w; w += align256((size_t)N * 4);
-    int* gstamp = (int*)w;
+    unsigned* gm0 = (unsigned*)w; w += align256(((size_t)N / 32 + 2) * 4);
+    unsigned* gm1 = (unsigned*)w;
     int launches = 1;
     if (N > 0) {
-        fps_knn_kernel<<<dc_ceil_div(N, KNN_T), KNN_T, 0, st>>>(pos, cloud_ptr, B, N, nbr, wgt);
-        ++launches;
+        fps_sort_box_kernel<<<dc_ceil_div((long long)tiles, 4), 128, 0, st>>>(pos, order_or_null, N, spos, boxes);
+        fps_knn_kernel<<<dc_ceil_div(N, KNN_WARPS * 32), KNN_WARPS * 32, 0, st>>>(spos, boxes, order_or_null, cloud_ptr, B, N, nbr, wgt);
+        launches += 2;
     }
     // clouds up to `smem_points` keep their state in shared memory; larger ones (only if the caller's bound says they exist) in ws
     const int smem_points = max_cloud_points < FPS_SMEM_POINTS ? max_cloud_points : FPS_SMEM_POINTS;
-    const size_t smem = (size_t)smem_points * 20;
+    const size_t smem = fps_smem_bytes(smem_points) + 8;
+    if (max_cloud_points > smem_points)
+        DC_CUDA(cudaMemsetAsync(gm0, 0, 2 * align256(((size_t)N / 32 + 2) * 4), st));
     if (smem > 48 * 1024)
-        DC_CUDA(cudaFuncSetAttribute(fps_sample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FPS_SMEM_POINTS * 20));
-    fps_sample_kernel<<<B, FPS_T, smem, st>>>(cloud_ptr, nbr, wgt, start, n_samples, samples, dist_or_null, smem_points, gD, gq0, gq1, gstamp);
+        DC_CUDA(cudaFuncSetAttribute(fps_sample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(fps_smem_bytes(FPS_SMEM_POINTS) + 8)));
+    fps_sample_kernel<<<B, FPS_T, smem, st>>>(cloud_ptr, nbr, wgt, order_or_null, start, n_samples, samples, dist_or_null, smem_points,
+                                              gD, gq0, gq1, gm0, gm1);
     return dc_check_launch_n("dc_geodesic_fps", launches);
 }

@@ -150,10 +150,12 @@ def spatial_order(pos, batch=None, num_clouds=None):
     return torch.argsort(keys, stable=True)
 
 
-def geodesic_fps(pos, n_samples, batch=None, num_clouds=None, start=None, max_points=None, return_dist=False):
+def geodesic_fps(pos, n_samples, batch=None, num_clouds=None, start=None, max_points=None, return_dist=False, ordered=True):
     """Geodesic farthest-point sampling of every cloud at once (dc_geodesic_fps; reference sampling.cpp:21-81 does one cloud
     per call on one CPU thread).  `pos` [N,3] CUDA, fp32 or fp64 (the reference computes in fp64 whatever it is given);
     `start` [B] = first sample of every cloud as an index inside the cloud, drawn uniformly when None like the reference.
+    `ordered`: visit the points of every cloud along a Morton curve (the neighbour search then skips most of the cloud per
+    query; the result is the same either way).
     Returns [B, n_samples] int64 indices inside each cloud (and the distance of every point to its nearest sample)."""
     if not (torch.is_tensor(pos) and pos.is_cuda and pos.dtype in (_F32, torch.float64)):
         raise _lib.DeltaConvLibraryError("geodesic_fps: expected an fp32 or fp64 CUDA tensor (deltaconv_b200 has no CPU path)")
@@ -172,7 +174,9 @@ def geodesic_fps(pos, n_samples, batch=None, num_clouds=None, start=None, max_po
     dist = torch.empty(N, dtype=torch.float64, device=pos.device) if return_dist else None
     nb = query('dc_geodesic_fps_ws_bytes', N)
     ws = workspace(nb, pos.device)
-    call('dc_geodesic_fps', ptr(pos64), ptr(cp), B, N, min(maxp, N), int(n_samples), ptr(start), ptr(samples), ptr(dist), ptr(ws), nb)
+    order = spatial_order(pos.float(), batch, B).to(_I32) if (ordered and maxp > 2 * 64) else None
+    call('dc_geodesic_fps', ptr(pos64), ptr(cp), B, N, min(maxp, N), int(n_samples), ptr(order), ptr(start), ptr(samples), ptr(dist),
+         ptr(ws), nb)
     samples = samples.long()
     return (samples, dist) if return_dist else samples
 

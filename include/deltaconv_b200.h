@@ -64,12 +64,16 @@ int dc_morton_keys(const float* pos, const int32_t* cloud_ptr, int B, int N, int
  * start[B]: first sample of every cloud (index inside the cloud; the reference draws it at random, sampling.cpp:33-40);
  * samples[B, n_samples] int32: indices inside the cloud (-1 for an empty cloud); n_samples may exceed a cloud's size (the
  * surplus repeats index 0 as in the reference); dist_or_null[N]: distance of every point to its nearest sample.
- * max_cloud_points: an upper bound on the cloud sizes (N is always valid); clouds up to 11,264 points are sampled from
+ * order_or_null[N]: a permutation of the points that keeps every cloud in its own range, order[t] = the point visited t-th.
+ * The result does not depend on it; the time of the neighbour search does: in a space-filling-curve order (dc_morton_keys)
+ * most of a cloud is skipped per query, in an arbitrary order (or NULL) every pair of points of a cloud is examined.
+ * max_cloud_points: an upper bound on the cloud sizes (N is always valid); clouds up to 18,432 points are sampled from
  * shared memory, larger ones from the workspace.  Clouds of fewer than 11 points use the neighbours they have (the
  * reference throws there).  Workspace from dc_geodesic_fps_ws_bytes(N). */
 size_t dc_geodesic_fps_ws_bytes(int N);
 int dc_geodesic_fps(const double* pos, const int32_t* cloud_ptr, int B, int N, int max_cloud_points, int n_samples,
-                    const int32_t* start, int32_t* samples, double* dist_or_null, void* ws, size_t ws_bytes, void* stream);
+                    const int32_t* order_or_null, const int32_t* start, int32_t* samples, double* dist_or_null,
+                    void* ws, size_t ws_bytes, void* stream);
 
 /* [2,N*k] int64 edge_index (rows grouped by centre, fixed k — grad_div_mls.py:24-25,224) <-> ELL idx. */
 int dc_ell_from_edge_index(const int64_t* edge_index, int N, int k, int32_t* idx, void* stream);

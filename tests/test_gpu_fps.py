@@ -78,6 +78,25 @@ def test_disconnected_graph_and_fp64_input():
     assert np.array_equal(got[0].cpu().numpy(), ofps.restated_fps(x, 50, 3))
 
 
+def test_visiting_order_changes_nothing_and_exact_ties_go_to_the_lower_index():
+    rng = np.random.default_rng(21)
+    # a lattice (many exactly equal distances) with every point present twice (zero distances), shuffled
+    g = np.stack(np.meshgrid(np.arange(12), np.arange(12), np.arange(3), indexing='ij'), -1).reshape(-1, 3).astype(np.float32) * 0.25
+    x = np.concatenate([g, g])[rng.permutation(2 * len(g))]
+    clouds = [x, _shape(3000, rng), x[:500]]
+    start = [5, 17, 0]
+    pos, batch = _batch(clouds)
+    a, da = dc().ops.geodesic_fps(pos, 300, batch=batch, start=start, return_dist=True, ordered=True)
+    b, db = dc().ops.geodesic_fps(pos, 300, batch=batch, start=start, return_dist=True, ordered=False)
+    assert torch.equal(a, b) and torch.equal(da, db)
+    off = 0
+    for i, c in enumerate(clouds):
+        want, want_dist = ofps.restated_fps(c, 300, start[i], want_dist=True)
+        assert np.array_equal(a[i].cpu().numpy(), want), f'cloud {i}'
+        assert np.array_equal(da[off:off + len(c)].cpu().numpy(), want_dist), f'cloud {i}'
+        off += len(c)
+
+
 @pytest.mark.skipif(not ofps.have_reference(), reason='compiled reference (oracle/_ref) not on this box')
 def test_against_the_compiled_reference_itself():
     rng = np.random.default_rng(99)
