@@ -5,9 +5,10 @@
 // vector D shared by all passes (D = geodesic distance to the nearest sample so far), then argmax D.  Clouds are
 // independent, so here a batch of clouds is sampled at once:
 //   1. fps_sort_box_kernel   points gathered into the caller's visiting order (a space-filling-curve order makes step 2 fast;
-//                            any order is correct) + one bounding box per 64 consecutive points;
+//                            any order is correct) + one bounding box per 64 consecutive points, one per 8 boxes;
 //   2. fps_knn_kernel        the 10 nearest other points of every point, a thread per query: boxes that lie farther than the
-//                            current 10th distance are skipped, the rest is scanned exhaustively;
+//                            current 10th distance are skipped, the others are screened in fp32 with a proven error margin
+//                            and only the few survivors are evaluated in fp64;
 //   3. fps_sample_kernel     one CTA per cloud, the cloud's state (D, two work queues, two bit masks: 12.25 bytes per point)
 //                            in shared memory up to 18,432 points per cloud — two clouds of 8,192 per SM — and in the
 //                            caller's workspace beyond that.
@@ -27,6 +28,7 @@ namespace {
 
 constexpr int FPS_K = 10;            // neighbours per point, fixed in the reference (sampling.cpp:23)
 constexpr int BOX_TILE = 64;         // consecutive points (in visiting order) per bounding box
+constexpr int SUPER = 8;              // boxes per super box
 constexpr int KNN_WARPS = 8;         // warps of 32 queries per CTA of the graph kernel
 constexpr int FPS_T = 512;           // threads of a sampling CTA
 constexpr int FPS_SMEM_POINTS = 18432;  // < 65,536: queue entries of shared-memory clouds are 16-bit
@@ -38,7 +40,8 @@ __device__ __forceinline__ int orig_of(const int* __restrict__ order, int j) { r
 
 // ---- 1. gather into visiting order + boxes ----------------------------------------------------------------------------
 __global__ void __launch_bounds__(128) fps_sort_box_kernel(const double* __restrict__ pos, const int* __restrict__ order, int N,
-                                                           double* __restrict__ spos, double* __restrict__ boxes) {
+                                                           double* __restrict__ spos, float4* __restrict__ spos32,
+                                                           float4* __restrict__ boxes) {
     const int lane = threadIdx.x & 31;
     const int g = blockIdx.x * 4 + (threadIdx.x >> 5);
     if ((long long)g * BOX_TILE >= N) return;
@@ -47,15 +50,19 @@ __global__ void __launch_bounds__(128) fps_sort_box_kernel(const double* __restr
 #pragma unroll
     for (int h = 0; h < BOX_TILE / 32; ++h) {
         const int i = g * BOX_TILE + h * 32 + lane;
+        float4 f = make_float4(0.f, 0.f, 0.f, 0.f);               // the fp32 copy is padded to whole tiles
         if (i < N) {
             const int o = orig_of(order, i);
+            double p[3];
 #pragma unroll
             for (int a = 0; a < 3; ++a) {
-                const double p = pos[3 * (size_t)o + a];
-                spos[3 * (size_t)i + a] = p;
-                lo[a] = fmin(lo[a], p); hi[a] = fmax(hi[a], p);
+                p[a] = pos[3 * (size_t)o + a];
+                spos[3 * (size_t)i + a] = p[a];
+                lo[a] = fmin(lo[a], p[a]); hi[a] = fmax(hi[a], p[a]);
             }
+            f = make_float4(__double2float_rn(p[0]), __double2float_rn(p[1]), __double2float_rn(p[2]), 0.f);
         }
+        spos32[i] = f;
     }
 #pragma unroll
     for (int a = 0; a < 3; ++a)
@@ -64,10 +71,25 @@ __global__ void __launch_bounds__(128) fps_sort_box_kernel(const double* __restr
             lo[a] = fmin(lo[a], __shfl_xor_sync(FULL, lo[a], o));
             hi[a] = fmax(hi[a], __shfl_xor_sync(FULL, hi[a], o));
         }
+    // stored in fp32, rounded outwards: the box can only grow, so a distance to it stays a lower bound
     if (lane == 0) {
-#pragma unroll
-        for (int a = 0; a < 3; ++a) { boxes[6 * (size_t)g + a] = lo[a]; boxes[6 * (size_t)g + 3 + a] = hi[a]; }
+        boxes[2 * (size_t)g] = make_float4(__double2float_rd(lo[0]), __double2float_rd(lo[1]), __double2float_rd(lo[2]), 0.f);
+        boxes[2 * (size_t)g + 1] = make_float4(__double2float_ru(hi[0]), __double2float_ru(hi[1]), __double2float_ru(hi[2]), 0.f);
     }
+}
+
+// one box around every SUPER consecutive boxes: the search tests these first
+__global__ void fps_super_box_kernel(const float4* __restrict__ boxes, int tiles, float4* __restrict__ super_boxes) {
+    const int G = blockIdx.x * blockDim.x + threadIdx.x;
+    if ((long long)G * SUPER >= tiles) return;
+    const float inf = __int_as_float(0x7f800000);
+    float4 lo = make_float4(inf, inf, inf, 0.f), hi = make_float4(-inf, -inf, -inf, 0.f);
+    for (int g = G * SUPER; g < min(tiles, G * SUPER + SUPER); ++g) {
+        const float4 a = boxes[2 * (size_t)g], b = boxes[2 * (size_t)g + 1];
+        lo.x = fminf(lo.x, a.x); lo.y = fminf(lo.y, a.y); lo.z = fminf(lo.z, a.z);
+        hi.x = fmaxf(hi.x, b.x); hi.y = fmaxf(hi.y, b.y); hi.z = fmaxf(hi.z, b.z);
+    }
+    super_boxes[2 * (size_t)G] = lo; super_boxes[2 * (size_t)G + 1] = hi;
 }
 
 // ---- 2. 10 nearest OTHER points of every point, fp64, ascending (d2, original index) ---------------------------------
@@ -78,7 +100,27 @@ __device__ __forceinline__ double dist2_rn(double dx, double dy, double dz) {
     return __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
 }
 
-__global__ void __launch_bounds__(KNN_WARPS * 32) fps_knn_kernel(const double* __restrict__ spos, const double* __restrict__ boxes,
+// Lower bound, in fp32 with every operation rounded down, of the squared distance from a query (given as the fp32 values just
+// above and just below its coordinates) to an outward-rounded box.  It never exceeds the exact squared distance to any
+// point inside; the fp64-computed d2 of such a point is below its exact value by at most a few 2^-53, which the caller's
+// factor (1 - 1e-15) absorbs.  Rounding down also turns fp32 overflow into FLT_MAX, still a lower bound.
+__device__ __forceinline__ float box_lower_bound(const float4 lo, const float4 hi, float xu, float xd, float yu, float yd, float zu, float zd) {
+    const float ax = fmaxf(fmaxf(__fsub_rd(lo.x, xu), __fsub_rd(xd, hi.x)), 0.f);
+    const float ay = fmaxf(fmaxf(__fsub_rd(lo.y, yu), __fsub_rd(yd, hi.y)), 0.f);
+    const float az = fmaxf(fmaxf(__fsub_rd(lo.z, zu), __fsub_rd(zd, hi.z)), 0.f);
+    return __fadd_rd(__fadd_rd(__fmul_rd(ax, ax), __fmul_rd(ay, ay)), __fmul_rd(az, az));
+}
+
+// A box that survives the test is scanned in two phases.  Phase A runs over its 64 points in fp32 and only marks the ones
+// that may be at least as near as the current 10th neighbour; phase B evaluates the marked ones (a handful) in fp64 and
+// inserts them.  Phase A can not lose a neighbour: with u = 2^-24, S = largest |coordinate| of the cloud, T = current 10th d2,
+//   fp32 inputs differ from the fp64 ones by at most u S, each fp32 difference by another u |a|, the fp32 sum of squares
+//   d32 <= |a|^2 (1+u)^3, hence the true distance d >= sqrt(d32) (1 - 3u) - 2 sqrt(3) u S;
+//   a point is dropped only if d32 > R^2, R = (sqrt(T) (1 + 1e-15) + 2 sqrt(3) u S) / (1 - 3u), which implies that its
+//   fp64-computed d2 exceeds T.  (Threshold rounded up, 1e-12 of slack for the fp64 roundings in R and fp32 underflow.)
+// Outside 1e-9 <= S <= 1e18 (fp32 squares would underflow or overflow) phase A marks everything.
+__global__ void __launch_bounds__(KNN_WARPS * 32, 3) fps_knn_kernel(const double* __restrict__ spos, const float4* __restrict__ spos32,
+                                                                 const float4* __restrict__ boxes, const float4* __restrict__ super_boxes,
                                                                  const int* __restrict__ order, const int* __restrict__ cloud_ptr,
                                                                  int B, int N, int* __restrict__ nbr, double* __restrict__ wgt) {
     const int lane = threadIdx.x & 31;
@@ -90,34 +132,72 @@ __global__ void __launch_bounds__(KNN_WARPS * 32) fps_knn_kernel(const double* _
     const int c = cloud_of(cloud_ptr, B, iq);
     const int s = cloud_ptr[c], e = cloud_ptr[c + 1];
     const double qx = spos[3 * (size_t)iq], qy = spos[3 * (size_t)iq + 1], qz = spos[3 * (size_t)iq + 2];
+    const float fx = __double2float_rn(qx), fy = __double2float_rn(qy), fz = __double2float_rn(qz);
+    const float xu = __double2float_ru(qx), xd = __double2float_rd(qx), yu = __double2float_ru(qy), yd = __double2float_rd(qy),
+                zu = __double2float_ru(qz), zd = __double2float_rd(qz);
     const int g_lo = __reduce_min_sync(FULL, s) / BOX_TILE, g_hi = (__reduce_max_sync(FULL, e) - 1) / BOX_TILE;
     const int g0 = qbase / BOX_TILE;
+    const int G_lo = g_lo / SUPER, G_hi = g_hi / SUPER, G0 = g0 / SUPER;
+
+    // S over every box this warp can visit (boxes shared with a neighbouring cloud, and the outward rounding, only make it
+    // larger: still a bound)
+    float S32 = 0.f;
+    for (int G = G_lo + lane; G <= G_hi; G += 32) {
+        const float4 a = __ldg(super_boxes + 2 * (size_t)G), b = __ldg(super_boxes + 2 * (size_t)G + 1);
+        S32 = fmaxf(S32, fmaxf(fmaxf(fmaxf(fabsf(a.x), fabsf(a.y)), fmaxf(fabsf(a.z), fabsf(b.x))), fmaxf(fabsf(b.y), fabsf(b.z))));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) S32 = fmaxf(S32, __shfl_xor_sync(FULL, S32, o));
+    const double S = (double)S32;
+    const bool use32 = S >= 1e-9 && S <= 1e18;
+    const double u = 5.9604644775390625e-08;                   // 2^-24
+    const double slack = 2. * 1.7320508075688774 * u * S * (1. + 1e-6);
 
     double bd[FPS_K];
     int bi[FPS_K];
 #pragma unroll
     for (int t = 0; t < FPS_K; ++t) { bd[t] = __longlong_as_double(INF_BITS); bi[t] = -1; }
 
-    // own box first, then outwards in both directions: neighbours in a space-filling order are mostly neighbours in space,
-    // so the 10th distance is tight after the first boxes and most of the others fail the test
-    const int reach = max(g0 - g_lo, g_hi - g0);
-    for (int step = 0; step <= reach; ++step) {
-#pragma unroll 1
-        for (int side = 0; side < 2; ++side) {
-            const int g = side == 0 ? g0 + step : g0 - step;
-            if (g > g_hi || g < g_lo || (side == 1 && step == 0)) continue;
-            const double* bx = boxes + 6 * (size_t)g;
-            const double ax = fmax(fmax(__dsub_rn(__ldg(bx), qx), __dsub_rn(qx, __ldg(bx + 3))), 0.);
-            const double ay = fmax(fmax(__dsub_rn(__ldg(bx + 1), qy), __dsub_rn(qy, __ldg(bx + 4))), 0.);
-            const double az = fmax(fmax(__dsub_rn(__ldg(bx + 2), qz), __dsub_rn(qz, __ldg(bx + 5))), 0.);
-            const int j_first = g * BOX_TILE, j_last = min(j_first + BOX_TILE, N);
-            const bool near = valid && max(j_first, s) < min(j_last, e) && dist2_rn(ax, ay, az) <= bd[FPS_K - 1];
-            if (!__any_sync(FULL, near)) continue;
-#pragma unroll 4
-            for (int j = j_first; j < j_last; ++j) {
+    auto scan_box = [&](int g) {
+        const int j_first = g * BOX_TILE, count = min(BOX_TILE, N - j_first);
+        const float lb = box_lower_bound(__ldg(boxes + 2 * (size_t)g), __ldg(boxes + 2 * (size_t)g + 1), xu, xd, yu, yd, zu, zd);
+        const bool near = valid && max(j_first, s) < min(j_first + count, e) && (double)lb * (1. - 1e-15) <= bd[FPS_K - 1];
+        if (!__any_sync(FULL, near)) return;
+
+        // phase A
+        float thr = __int_as_float(0x7f800000);
+        if (use32) {
+            const double R = (sqrt(bd[FPS_K - 1]) * (1. + 1e-15) + slack) / (1. - 3. * u);
+            thr = __double2float_ru(R * R * (1. + 1e-12));
+        }
+        if (!near) thr = -1.f;
+        unsigned marks[BOX_TILE / 32];
+#pragma unroll
+        for (int h = 0; h < BOX_TILE / 32; ++h) {
+            unsigned m = 0u;
+#pragma unroll 8
+            for (int jj = 0; jj < 32; ++jj) {
+                const float4 p = __ldg(spos32 + j_first + h * 32 + jj);
+                const float dx = fx - p.x, dy = fy - p.y, dz = fz - p.z;
+                const float d32 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+                m |= (d32 > thr ? 0u : 1u) << jj;
+            }
+            const int left = count - h * 32;
+            marks[h] = left >= 32 ? m : (left <= 0 ? 0u : m & ((1u << left) - 1u));
+        }
+        if (!near) return;
+
+        // phase B
+#pragma unroll
+        for (int h = 0; h < BOX_TILE / 32; ++h) {
+            unsigned m = marks[h];
+            while (m != 0u) {
+                const int j = j_first + h * 32 + __ffs(m) - 1;
+                m &= m - 1u;
+                if ((unsigned)(j - s) >= (unsigned)(e - s) || j == i) continue;
                 const double d = dist2_rn(__dsub_rn(qx, __ldg(spos + 3 * (size_t)j)), __dsub_rn(qy, __ldg(spos + 3 * (size_t)j + 1)),
                                           __dsub_rn(qz, __ldg(spos + 3 * (size_t)j + 2)));
-                if (!(d <= bd[FPS_K - 1]) || !near || (unsigned)(j - s) >= (unsigned)(e - s) || j == i) continue;
+                if (!(d <= bd[FPS_K - 1])) continue;
                 if (d == bd[FPS_K - 1] && (bi[FPS_K - 1] < 0 || orig_of(order, j) > orig_of(order, bi[FPS_K - 1]))) continue;
                 bd[FPS_K - 1] = d; bi[FPS_K - 1] = j;
 #pragma unroll
@@ -130,6 +210,23 @@ __global__ void __launch_bounds__(KNN_WARPS * 32) fps_knn_kernel(const double* _
                     }
                 }
             }
+        }
+    };
+
+    // own box first: neighbours in a space-filling order are mostly neighbours in space, so the 10th distance is tight
+    // right away; then the super boxes from the own one outwards, and inside a near one its boxes
+    scan_box(g0);
+    const int reach = max(G0 - G_lo, G_hi - G0);
+    for (int step = 0; step <= reach; ++step) {
+#pragma unroll 1
+        for (int side = 0; side < 2; ++side) {
+            const int G = side == 0 ? G0 + step : G0 - step;
+            if (G > G_hi || G < G_lo || (side == 1 && step == 0)) continue;
+            const float lb = box_lower_bound(__ldg(super_boxes + 2 * (size_t)G), __ldg(super_boxes + 2 * (size_t)G + 1), xu, xd, yu, yd, zu, zd);
+            if (!__any_sync(FULL, valid && (double)lb * (1. - 1e-15) <= bd[FPS_K - 1])) continue;
+#pragma unroll 1
+            for (int g = max(G * SUPER, g_lo); g <= min(G * SUPER + SUPER - 1, g_hi); ++g)
+                if (g != g0) scan_box(g);
         }
     }
     if (!valid) return;
@@ -147,7 +244,7 @@ struct FpsShared {
     int cnt[3];
     unsigned long long red_v[FPS_T / 32];
     int red_i[FPS_T / 32], red_o[FPS_T / 32];
-    int next_src, start_pos;
+    int start_pos;
 };
 
 // (value, original index) order of the argmax: larger value first, then the lower original index (Eigen maxCoeff keeps the first)
@@ -171,18 +268,19 @@ __device__ void fps_run(FpsShared& sh, unsigned long long* D, QT* q0, QT* q1, un
     __syncthreads();
     int src = sh.start_pos;
     int round = 0;
-    if (threadIdx.x == 0) out[0] = want_start;
+    // a pass starts from `src` with distance zero, alone in the work queue (thread 0 sets it up, one barrier publishes it)
+    auto begin_pass = [&](int from) {
+        D[from] = 0ULL;
+        ((round & 1) ? q1 : q0)[0] = (QT)from;
+        atomicOr(((round & 1) ? m1 : m0) + ((mbase + from) >> 5), 1u << ((mbase + from) & 31));
+        sh.cnt[round % 3] = 1; sh.cnt[(round + 1) % 3] = 0;
+    };
+    if (threadIdx.x == 0) { out[0] = want_start; begin_pass(src); }
+    __syncthreads();
 
     for (int smp = 1; smp <= n_samples; ++smp) {
         if (smp == n_samples && dist_or_null == nullptr) break;      // the pass after the last sample only serves `dist`
-        // one Dijkstra pass of the reference (sampling.cpp:56-81) from `src`, into the shared D
-        if (threadIdx.x == 0) {
-            D[src] = 0ULL;
-            ((round & 1) ? q1 : q0)[0] = (QT)src;
-            atomicOr(((round & 1) ? m1 : m0) + ((mbase + src) >> 5), 1u << ((mbase + src) & 31));
-            sh.cnt[round % 3] = 1; sh.cnt[(round + 1) % 3] = 0;
-        }
-        __syncthreads();
+        // one Dijkstra pass of the reference (sampling.cpp:56-81) into the shared D
         while (true) {
             const int F = sh.cnt[round % 3];
             if (F == 0) break;
@@ -235,20 +333,19 @@ __device__ void fps_run(FpsShared& sh, unsigned long long* D, QT* q0, QT* q1, un
         }
         if (lane == 0) { sh.red_v[warp] = bv; sh.red_i[warp] = bidx; sh.red_o[warp] = bo; }
         __syncthreads();
-        if (warp == 0) {
-            bv = lane < FPS_T / 32 ? sh.red_v[lane] : 0ULL;
-            bidx = lane < FPS_T / 32 ? sh.red_i[lane] : 0;
-            bo = lane < FPS_T / 32 ? sh.red_o[lane] : 0x7fffffff;
+        // every warp finishes the reduction for itself: no second barrier, no broadcast
+        bv = lane < FPS_T / 32 ? sh.red_v[lane] : 0ULL;
+        bidx = lane < FPS_T / 32 ? sh.red_i[lane] : 0;
+        bo = lane < FPS_T / 32 ? sh.red_o[lane] : 0x7fffffff;
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {
-                const unsigned long long ov = __shfl_xor_sync(FULL, bv, o);
-                const int oi = __shfl_xor_sync(FULL, bidx, o), oo = __shfl_xor_sync(FULL, bo, o);
-                if (better(ov, oo, bv, bo)) { bv = ov; bidx = oi; bo = oo; }
-            }
-            if (lane == 0) { sh.next_src = bidx; out[smp] = bo - s; }
+        for (int o = 8; o > 0; o >>= 1) {
+            const unsigned long long ov = __shfl_xor_sync(FULL, bv, o);
+            const int oi = __shfl_xor_sync(FULL, bidx, o), oo = __shfl_xor_sync(FULL, bo, o);
+            if (better(ov, oo, bv, bo)) { bv = ov; bidx = oi; bo = oo; }
         }
+        src = __shfl_sync(FULL, bidx, 0);
+        if (threadIdx.x == 0) { out[smp] = bo - s; begin_pass(src); }
         __syncthreads();
-        src = sh.next_src;
     }
     if (dist_or_null != nullptr)
         for (int t = threadIdx.x; t < P; t += FPS_T) dist_or_null[orig_of(order, s + t)] = __longlong_as_double((long long)D[t]);
@@ -292,7 +389,7 @@ size_t align256(size_t n) { return (n + 255) / 256 * 256; }
 extern "C" size_t dc_geodesic_fps_ws_bytes(int N) {
     const size_t n = (size_t)(N > 0 ? N : 0);
     const size_t tiles = (n + BOX_TILE - 1) / BOX_TILE;
-    return align256(n * 24) + align256(tiles * 48) + align256(n * FPS_K * 4) + align256(n * FPS_K * 8) + align256(n * 8) +
+    return align256(n * 24) + align256(tiles * BOX_TILE * 16) + align256(tiles * 32) + align256((tiles / SUPER + 1) * 32) + align256(n * FPS_K * 4) + align256(n * FPS_K * 8) + align256(n * 8) +
            2 * align256(n * 4) + 2 * align256((n / 32 + 2) * 4);
 }
 
@@ -306,7 +403,9 @@ extern "C" int dc_geodesic_fps(const double* pos, const int32_t* cloud_ptr, int 
     const size_t tiles = ((size_t)N + BOX_TILE - 1) / BOX_TILE;
     char* w = (char*)ws;
     double* spos = (double*)w; w += align256((size_t)N * 24);
-    double* boxes = (double*)w; w += align256(tiles * 48);
+    float4* spos32 = (float4*)w; w += align256(tiles * BOX_TILE * 16);
+    float4* boxes = (float4*)w; w += align256(tiles * 32);
+    float4* super_boxes = (float4*)w; w += align256((tiles / SUPER + 1) * 32);
     int* nbr = (int*)w; w += align256((size_t)N * FPS_K * 4);
     double* wgt = (double*)w; w += align256((size_t)N * FPS_K * 8);
     unsigned long long* gD = (unsigned long long*)w; w += align256((size_t)N * 8);
@@ -316,9 +415,11 @@ extern "C" int dc_geodesic_fps(const double* pos, const int32_t* cloud_ptr, int 
     unsigned* gm1 = (unsigned*)w;
     int launches = 1;
     if (N > 0) {
-        fps_sort_box_kernel<<<dc_ceil_div((long long)tiles, 4), 128, 0, st>>>(pos, order_or_null, N, spos, boxes);
-        fps_knn_kernel<<<dc_ceil_div(N, KNN_WARPS * 32), KNN_WARPS * 32, 0, st>>>(spos, boxes, order_or_null, cloud_ptr, B, N, nbr, wgt);
-        launches += 2;
+        fps_sort_box_kernel<<<dc_ceil_div((long long)tiles, 4), 128, 0, st>>>(pos, order_or_null, N, spos, spos32, boxes);
+        fps_super_box_kernel<<<dc_ceil_div((long long)dc_ceil_div((long long)tiles, SUPER), 128), 128, 0, st>>>(boxes, (int)tiles, super_boxes);
+        fps_knn_kernel<<<dc_ceil_div(N, KNN_WARPS * 32), KNN_WARPS * 32, 0, st>>>(spos, spos32, boxes, super_boxes, order_or_null, cloud_ptr,
+                                                                                 B, N, nbr, wgt);
+        launches += 3;
     }
     // clouds up to `smem_points` keep their state in shared memory; larger ones (only if the caller's bound says they exist) in ws
     const int smem_points = max_cloud_points < FPS_SMEM_POINTS ? max_cloud_points : FPS_SMEM_POINTS;

@@ -29,13 +29,27 @@ __global__ void bbox_init_kernel(int* __restrict__ bbox, int B) {
     if (t < B * 6) bbox[t] = (t % 6) < 3 ? 0x7fffffff : (int)0x80000000;
 }
 
+// A warp whose points all belong to one cloud (the usual case) reduces its 32 points first and sends six atomics instead
+// of 192: with hundreds of thousands of points per cloud the atomics on one cloud's six words are the whole cost.
 __global__ void bbox_kernel(const float* __restrict__ pos, const int* __restrict__ cloud_ptr, int B, int N, int* __restrict__ bbox) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= N) return;
+    const bool valid = i < N;
+    if (!valid) i = N - 1;                                         // keeps the warp whole for the reductions; same values, harmless
     const int b = cloud_of(cloud_ptr, B, i);
-    const float x = pos[3 * (size_t)i], y = pos[3 * (size_t)i + 1], z = pos[3 * (size_t)i + 2];
-    atomicMin(bbox + b * 6 + 0, f2ord(x)); atomicMin(bbox + b * 6 + 1, f2ord(y)); atomicMin(bbox + b * 6 + 2, f2ord(z));
-    atomicMax(bbox + b * 6 + 3, f2ord(x)); atomicMax(bbox + b * 6 + 4, f2ord(y)); atomicMax(bbox + b * 6 + 5, f2ord(z));
+    const int x = f2ord(pos[3 * (size_t)i]), y = f2ord(pos[3 * (size_t)i + 1]), z = f2ord(pos[3 * (size_t)i + 2]);
+    const int b0 = __shfl_sync(FULL, b, 0);
+    if (__all_sync(FULL, b == b0)) {
+        const int x0 = __reduce_min_sync(FULL, x), y0 = __reduce_min_sync(FULL, y), z0 = __reduce_min_sync(FULL, z);
+        const int x1 = __reduce_max_sync(FULL, x), y1 = __reduce_max_sync(FULL, y), z1 = __reduce_max_sync(FULL, z);
+        if ((threadIdx.x & 31) == 0) {
+            atomicMin(bbox + b * 6 + 0, x0); atomicMin(bbox + b * 6 + 1, y0); atomicMin(bbox + b * 6 + 2, z0);
+            atomicMax(bbox + b * 6 + 3, x1); atomicMax(bbox + b * 6 + 4, y1); atomicMax(bbox + b * 6 + 5, z1);
+        }
+        return;
+    }
+    if (!valid) return;
+    atomicMin(bbox + b * 6 + 0, x); atomicMin(bbox + b * 6 + 1, y); atomicMin(bbox + b * 6 + 2, z);
+    atomicMax(bbox + b * 6 + 3, x); atomicMax(bbox + b * 6 + 4, y); atomicMax(bbox + b * 6 + 5, z);
 }
 
 // One thread lays out all grids: cell size from the bounding volume and the point count (about two points per cell of
