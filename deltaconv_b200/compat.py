@@ -5,11 +5,11 @@
     import deltaconv                      ->  deltaconv_b200 (geometry, nn, models, transforms too)
     from torch_geometric.data import Data, Batch
     from torch_geometric.loader import DataLoader
-    from torch_geometric.transforms import Compose, BaseTransform
+    from torch_geometric.transforms import Compose, BaseTransform, SamplePoints
     from torch_geometric.nn import knn_graph, global_max_pool, global_mean_pool
 
 A real `torch_geometric`, if importable, is left alone (its `Batch` objects work with the models as they are).
-Datasets, `SamplePoints` and `GeodesicFPS` are not provided (deltaconv_b200/transforms.py has the other transforms)."""
+Datasets are not provided; deltaconv_b200/transforms.py has all nine transforms of the reference (`GeodesicFPS` on the GPU)."""
 import importlib
 import sys
 import types
@@ -49,7 +49,7 @@ def install(alias_reference=True, provide_pyg=None):
     """Register the stand-in modules.  provide_pyg=None: only when the real torch_geometric is absent."""
     import deltaconv_b200 as pkg
     from .utils import Data, Batch, DataLoader
-    from . import geometry
+    from . import geometry, transforms
     if alias_reference:
         sys.modules.setdefault('deltaconv', pkg)
         for sub in ('geometry', 'nn', 'models', 'utils', 'transforms'):
@@ -64,7 +64,8 @@ def install(alias_reference=True, provide_pyg=None):
         root = _module('torch_geometric', __version__='0.0-deltaconv_b200-standin')
         root.data = _module('torch_geometric.data', Data=Data, Batch=Batch)
         root.loader = _module('torch_geometric.loader', DataLoader=DataLoader)
-        root.transforms = _module('torch_geometric.transforms', Compose=Compose, BaseTransform=BaseTransform)
+        root.transforms = _module('torch_geometric.transforms', Compose=Compose, BaseTransform=BaseTransform,
+                                  SamplePoints=transforms.SamplePoints)
         root.nn = _module('torch_geometric.nn', knn_graph=geometry.knn_graph, global_max_pool=geometry.global_max_pool,
                           global_mean_pool=geometry.global_mean_pool)
     return provide_pyg

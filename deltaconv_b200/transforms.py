@@ -4,15 +4,15 @@ parameters and all clouds are transformed in one vectorised pass on the GPU (SUR
 single cloud exactly like the reference's per-sample CPU transforms.  Plain torch — they are not on the hot path.
 
 `GeodesicFPS` is the exception: it runs on the CUDA library (dc_geodesic_fps), on one cloud or on a whole batch.
-
-Not provided: `SamplePoints` (needs mesh faces).
+`SamplePoints` and `NormalizeArea` are the reference's two mesh pre-transforms (`data.face` [3,F]); they act on one mesh.
 """
 import math
 import numbers
 
 import torch
 
-__all__ = ['NormalizeScale', 'NormalizeAxes', 'RandomScale', 'RandomTranslateGlobal', 'RandomRotate', 'RandomNormals', 'GeodesicFPS']
+__all__ = ['NormalizeScale', 'NormalizeAxes', 'RandomScale', 'RandomTranslateGlobal', 'RandomRotate', 'RandomNormals', 'GeodesicFPS',
+           'SamplePoints', 'NormalizeArea']
 
 
 def _clouds(data):
@@ -239,6 +239,62 @@ class GeodesicFPS(object):
         y = getattr(data, 'y', None)
         if y is not None and type(y) is not int and y.size(0) > 1 and y.size(0) == pos.size(0):
             data.y = y[idx]
+        return data
+
+    def __repr__(self):
+        return '{}()'.format(self.__class__.__name__)
+
+
+class SamplePoints(object):
+    """Draw `num` points on the faces of a mesh, faces chosen in proportion to their area, uniformly inside each face
+    (sample_points.py:23-60).  The random draws come in the reference's order — one `multinomial` over the faces, then one
+    `rand(num, 2)` — so a seeded run gives the reference's points.  `include_normals` stores the face normal of every
+    sample in `data.norm`; `include_labels` takes the per-vertex label of the sampled face's first corner."""
+
+    def __init__(self, num, remove_faces=True, include_normals=False, include_labels=False):
+        self.num = num
+        self.remove_faces = remove_faces
+        self.include_normals = include_normals
+        self.include_labels = include_labels
+
+    def __call__(self, data):
+        vertices, face = data.pos, data.face
+        assert vertices.size(1) == 3 and face.size(0) == 3
+        scale = vertices.max()                                    # the reference samples on the mesh scaled by its largest coordinate
+        vertices = vertices / scale
+        corner = vertices[face[0]]
+        doubled_area = torch.linalg.cross(vertices[face[1]] - corner, vertices[face[2]] - corner, dim=1).norm(p=2, dim=1)
+        weight = doubled_area.abs() / 2
+        chosen = face[:, torch.multinomial(weight / weight.sum(), self.num, replacement=True)]
+        st = torch.rand(self.num, 2, device=vertices.device)
+        outside = st.sum(dim=-1) > 1                              # fold the unit square onto the triangle
+        st[outside] = 1 - st[outside]
+        origin = vertices[chosen[0]]
+        edge_a, edge_b = vertices[chosen[1]] - origin, vertices[chosen[2]] - origin
+        if self.include_normals:
+            data.norm = torch.nn.functional.normalize(torch.linalg.cross(edge_a, edge_b, dim=1), p=2)
+        data.pos = (origin + st[:, :1] * edge_a + st[:, 1:] * edge_b) * scale
+        if self.include_labels:
+            data.y = data.y[chosen[0]]
+        if self.remove_faces:
+            data.face = None
+        return data
+
+    def __repr__(self):
+        return '{}({})'.format(self.__class__.__name__, self.num)
+
+
+class NormalizeArea(object):
+    """Centre a mesh on the middle of its bounding box and scale it by 1/sqrt(area) (normalize_area.py:12-20).  Kept
+    result-compatible with the reference, which indexes `data.face[:, 0..2]` on the [3,F] face tensor: the "area" it sums is
+    that of the three triangles spanned by the corner triples of faces 0, 1 and 2, not the surface area of the mesh."""
+
+    def __call__(self, data):
+        pos = data.pos
+        pos = pos - (pos.max(dim=0)[0] + pos.min(dim=0)[0]) / 2
+        first, second, third = pos[data.face[:, 0]], pos[data.face[:, 1]], pos[data.face[:, 2]]
+        summed = torch.linalg.norm(torch.linalg.cross(second - first, third - first, dim=-1), dim=-1).sum() / 2
+        data.pos = pos * (1 / torch.sqrt(summed))
         return data
 
     def __repr__(self):

@@ -91,3 +91,29 @@ def test_random_transforms_act_per_cloud():
     out = T.RandomNormals(0.05)(b)
     assert (out.norm.norm(dim=1) - 1).abs().max() < 1e-5 and 0 < (out.norm - n0).abs().max() < 0.11
     assert repr(T.RandomRotate(15, axis=1)) == 'RandomRotate((-15, 15), axis=1)' and repr(T.NormalizeScale()) == 'NormalizeScale()'
+
+
+def test_mesh_transforms_reproduce_the_reference_under_the_same_seed():
+    """SamplePoints draws its random numbers in the reference's order, so the same seed gives the same points, normals and
+    labels; NormalizeArea is deterministic (including the reference's way of reading the face tensor)."""
+    import deltaconv_b200.transforms as T
+    from deltaconv_b200.utils import Data
+    g = np.load(GOLDEN)
+    verts, faces = torch.from_numpy(g['mesh_pos']), torch.from_numpy(g['mesh_face'])
+    labels = torch.arange(verts.size(0)) % 5
+    torch.manual_seed(4321)
+    plain = T.SamplePoints(200)(Data(pos=verts.clone(), face=faces.clone(), y=labels.clone()))
+    assert plain.face is None and plain.pos.shape == (200, 3)
+    assert (plain.pos - torch.from_numpy(g['sample_plain_pos'])).abs().max() < 1e-6
+    torch.manual_seed(4321)
+    full = T.SamplePoints(200, include_normals=True, include_labels=True, remove_faces=False)(
+        Data(pos=verts.clone(), face=faces.clone(), y=labels.clone()))
+    assert full.face is not None
+    assert (full.pos - torch.from_numpy(g['sample_full_pos'])).abs().max() < 1e-6
+    assert (full.norm - torch.from_numpy(g['sample_full_norm'])).abs().max() < 1e-5
+    assert torch.equal(full.y, torch.from_numpy(g['sample_full_y']))
+    # the samples lie on the surface: on this ellipsoid-like mesh every sample is inside the vertices' bounding box
+    assert (full.pos >= verts.min(0)[0] - 1e-6).all() and (full.pos <= verts.max(0)[0] + 1e-6).all()
+    area = T.NormalizeArea()(Data(pos=verts.clone(), face=faces.clone()))
+    assert (area.pos - torch.from_numpy(g['area_pos'])).abs().max() < 1e-6
+    assert repr(T.SamplePoints(7)) == 'SamplePoints(7)' and repr(T.NormalizeArea()) == 'NormalizeArea()'
