@@ -164,16 +164,16 @@ __global__ void __launch_bounds__(KNN_WARPS * 32, 3) fps_knn_kernel(const double
         const bool near = valid && max(j_first, s) < min(j_first + count, e) && (double)lb * (1. - 1e-15) <= bd[FPS_K - 1];
         if (!__any_sync(FULL, near)) return;
 
-        // phase A
-        float thr = __int_as_float(0x7f800000);
-        if (use32) {
-            const double R = (sqrt(bd[FPS_K - 1]) * (1. + 1e-15) + slack) / (1. - 3. * u);
-            thr = __double2float_ru(R * R * (1. + 1e-12));
-        }
-        if (!near) thr = -1.f;
-        unsigned marks[BOX_TILE / 32];
+        // 32 points at a time: phase A with the threshold of the moment, then phase B, so that the second half of a box is
+        // already screened against what the first half found (in the own box nothing is known before)
 #pragma unroll
         for (int h = 0; h < BOX_TILE / 32; ++h) {
+            float thr = __int_as_float(0x7f800000);
+            if (use32) {
+                const double R = (sqrt(bd[FPS_K - 1]) * (1. + 1e-15) + slack) / (1. - 3. * u);
+                thr = __double2float_ru(R * R * (1. + 1e-12));
+            }
+            if (!near) thr = -1.f;
             unsigned m = 0u;
 #pragma unroll 8
             for (int jj = 0; jj < 32; ++jj) {
@@ -183,14 +183,9 @@ __global__ void __launch_bounds__(KNN_WARPS * 32, 3) fps_knn_kernel(const double
                 m |= (d32 > thr ? 0u : 1u) << jj;
             }
             const int left = count - h * 32;
-            marks[h] = left >= 32 ? m : (left <= 0 ? 0u : m & ((1u << left) - 1u));
-        }
-        if (!near) return;
+            m = left >= 32 ? m : (left <= 0 ? 0u : m & ((1u << left) - 1u));
+            if (!near) m = 0u;
 
-        // phase B
-#pragma unroll
-        for (int h = 0; h < BOX_TILE / 32; ++h) {
-            unsigned m = marks[h];
             while (m != 0u) {
                 const int j = j_first + h * 32 + __ffs(m) - 1;
                 m &= m - 1u;
@@ -198,6 +193,21 @@ __global__ void __launch_bounds__(KNN_WARPS * 32, 3) fps_knn_kernel(const double
                 const double d = dist2_rn(__dsub_rn(qx, __ldg(spos + 3 * (size_t)j)), __dsub_rn(qy, __ldg(spos + 3 * (size_t)j + 1)),
                                           __dsub_rn(qz, __ldg(spos + 3 * (size_t)j + 2)));
                 if (!(d <= bd[FPS_K - 1])) continue;
+                bool below[FPS_K], tie = false;
+#pragma unroll
+                for (int t = 0; t < FPS_K; ++t) { below[t] = d < bd[t]; tie |= d == bd[t]; }
+                if (!tie) {
+                    // d differs from every entry (so d < bd[9]): shift the tail and drop it in, without branches
+#pragma unroll
+                    for (int t = FPS_K - 1; t > 0; --t) {
+                        bd[t] = below[t - 1] ? bd[t - 1] : (below[t] ? d : bd[t]);
+                        bi[t] = below[t - 1] ? bi[t - 1] : (below[t] ? j : bi[t]);
+                    }
+                    bd[0] = below[0] ? d : bd[0];
+                    bi[0] = below[0] ? j : bi[0];
+                    continue;
+                }
+                // equal distances: order by original index
                 if (d == bd[FPS_K - 1] && (bi[FPS_K - 1] < 0 || orig_of(order, j) > orig_of(order, bi[FPS_K - 1]))) continue;
                 bd[FPS_K - 1] = d; bi[FPS_K - 1] = j;
 #pragma unroll
