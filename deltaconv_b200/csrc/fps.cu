@@ -260,6 +260,25 @@ struct FpsShared {
 // (value, original index) order of the argmax: larger value first, then the lower original index (Eigen maxCoeff keeps the first)
 __device__ __forceinline__ bool better(unsigned long long v, int o, unsigned long long bv, int bo) { return v > bv || (v == bv && o < bo); }
 
+// Arg-max over the lanes of a warp with three warp-wide integer reductions instead of a shuffle tree: the high words, the
+// low words among the lanes that hold the largest high word, then the lowest original index among the lanes that hold the
+// largest value (`o` < 0 = not looked up yet: only those lanes fetch it).  Every lane returns the winner; no lane taking
+// part gives (0, 0, INT_MAX).
+__device__ __forceinline__ void warp_argmax(bool takes_part, unsigned long long v, int idx, int& o, const int* __restrict__ order, int s,
+                                            unsigned long long& best_v, int& best_idx, int& best_o) {
+    const unsigned hi = takes_part ? (unsigned)(v >> 32) : 0u, lo = takes_part ? (unsigned)v : 0u;
+    const unsigned mh = __reduce_max_sync(FULL, hi);
+    const unsigned ml = __reduce_max_sync(FULL, hi == mh ? lo : 0u);
+    const bool top = takes_part && hi == mh && lo == ml;
+    if (top && o < 0) o = orig_of(order, s + idx);
+    const int mo = __reduce_min_sync(FULL, top ? o : 0x7fffffff);
+    const unsigned who = __ballot_sync(FULL, top && o == mo);
+    const int winner = who != 0u ? __ffs(who) - 1 : 0;
+    best_idx = who != 0u ? __shfl_sync(FULL, idx, winner) : 0;
+    best_v = who != 0u ? (((unsigned long long)mh << 32) | ml) : 0ULL;
+    best_o = who != 0u ? mo : 0x7fffffff;
+}
+
 // D: bit patterns of non-negative doubles (unsigned order = numeric order).  Queue `round & 1` holds the points whose
 // distance dropped in the round before; mask `round & 1` has a bit per point in that queue, so a point enters it once.
 template <typename QT>
@@ -278,6 +297,9 @@ __device__ void fps_run(FpsShared& sh, unsigned long long* D, QT* q0, QT* q1, un
     __syncthreads();
     int src = sh.start_pos;
     int round = 0;
+    unsigned long long cv = 0ULL;                     // this thread's own maximum (value, point, original index), kept between samples
+    int cidx = 0, co = 0x7fffffff;
+    bool have = false;
     // a pass starts from `src` with distance zero, alone in the work queue (thread 0 sets it up, one barrier publishes it)
     auto begin_pass = [&](int from) {
         D[from] = 0ULL;
@@ -322,36 +344,34 @@ __device__ void fps_run(FpsShared& sh, unsigned long long* D, QT* q0, QT* q1, un
             __syncthreads();
         }
         if (smp == n_samples) break;
-        // farthest point: largest D, lowest original index among equals (Eigen maxCoeff, sampling.cpp:47)
-        unsigned long long bv = 0ULL;
-        int bidx = 0, bo = 0x7fffffff;
-        for (int t = threadIdx.x; t < P; t += FPS_T) {
-            const unsigned long long v = D[t];
-            if (v > bv) { bv = v; bidx = t; bo = -1; }                                  // original index fetched only if a tie needs it
-            else if (v == bv) {
-                if (bo == -1) bo = orig_of(order, s + bidx);
-                const int o = orig_of(order, s + t);
-                if (o < bo) { bidx = t; bo = o; }
+        // farthest point: largest D, lowest original index among equals (Eigen maxCoeff, sampling.cpp:47).
+        // Distances only ever decrease, so the maximum a thread found among its own points last time still stands unless
+        // that very point was lowered since: one load instead of a scan for most threads.
+        if (!(have && D[cidx] == cv)) {
+            cv = 0ULL; cidx = threadIdx.x < P ? threadIdx.x : 0; co = 0x7fffffff;
+            for (int t = threadIdx.x; t < P; t += FPS_T) {
+                const unsigned long long v = D[t];
+                if (v > cv) { cv = v; cidx = t; co = -1; }                              // original index fetched only if a tie needs it
+                else if (v == cv) {
+                    if (co == -1) co = orig_of(order, s + cidx);
+                    const int o = orig_of(order, s + t);
+                    if (o < co) { cidx = t; co = o; }
+                }
             }
+            have = threadIdx.x < P;
         }
-        if (bo == -1) bo = orig_of(order, s + bidx);
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            const unsigned long long ov = __shfl_xor_sync(FULL, bv, o);
-            const int oi = __shfl_xor_sync(FULL, bidx, o), oo = __shfl_xor_sync(FULL, bo, o);
-            if (better(ov, oo, bv, bo)) { bv = ov; bidx = oi; bo = oo; }
-        }
+        unsigned long long bv;
+        int bidx, bo;
+        warp_argmax(have, cv, cidx, co, order, s, bv, bidx, bo);
         if (lane == 0) { sh.red_v[warp] = bv; sh.red_i[warp] = bidx; sh.red_o[warp] = bo; }
         __syncthreads();
         // every warp finishes the reduction for itself: no second barrier, no broadcast
-        bv = lane < FPS_T / 32 ? sh.red_v[lane] : 0ULL;
-        bidx = lane < FPS_T / 32 ? sh.red_i[lane] : 0;
-        bo = lane < FPS_T / 32 ? sh.red_o[lane] : 0x7fffffff;
-#pragma unroll
-        for (int o = 8; o > 0; o >>= 1) {
-            const unsigned long long ov = __shfl_xor_sync(FULL, bv, o);
-            const int oi = __shfl_xor_sync(FULL, bidx, o), oo = __shfl_xor_sync(FULL, bo, o);
-            if (better(ov, oo, bv, bo)) { bv = ov; bidx = oi; bo = oo; }
+        {
+            const bool mine = lane < FPS_T / 32 && sh.red_o[lane < FPS_T / 32 ? lane : 0] != 0x7fffffff;
+            const unsigned long long pv = lane < FPS_T / 32 ? sh.red_v[lane] : 0ULL;
+            const int pi = lane < FPS_T / 32 ? sh.red_i[lane] : 0;
+            int po = lane < FPS_T / 32 ? sh.red_o[lane] : 0x7fffffff;
+            warp_argmax(mine, pv, pi, po, nullptr, 0, bv, bidx, bo);
         }
         src = __shfl_sync(FULL, bidx, 0);
         if (threadIdx.x == 0) { out[smp] = bo - s; begin_pass(src); }
