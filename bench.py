@@ -493,6 +493,13 @@ def run_fps_workload(args):
                 e2e=dict(value=round(FPS_CLOUDS / (e2e_ms / 1000), 1), unit='clouds/s', h2d_bytes_per_step=host.numel() * 4,
                          d2h_bytes_per_step=out_host.numel() * 8),
                 gpu_launches=launches, clocks=clocks)
+    pk = peaks()
+    algorithmic = host.numel() * 8 + out_host.numel() * 4          # fp64 positions read once, int32 samples written once
+    line['roofline'] = dict(bound='hbm', kernel='dc_geodesic_fps (fps_knn_kernel + fps_sample_kernel)', achieved=round(algorithmic / (ms / 1000) / 1e9, 2),
+                            peak=pk['hbm'], unit='GB/s', frac=round(algorithmic / (ms / 1000) / 1e9 / pk['hbm'], 5), traffic=None,
+                            peak_source=pk['source'],
+                            note='not a bandwidth-bound path: the graph kernel is bound by instruction issue, the sampler by DRAM latency per '
+                                 'relaxation round (profiles/r01_fps_ncu.md); the fraction is reported for completeness')
     if not args.no_cpu_baseline:
         from oracle import fps as ofps
         cores = os.cpu_count() or 1
