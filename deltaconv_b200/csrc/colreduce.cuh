@@ -27,7 +27,7 @@ ColLayout col_layout(long long M, int C) {
     L.col_lanes = cl;
     L.row_lanes = RED_T / cl;
     L.col_blocks = (C + cl - 1) / cl;
-    long long want = (long long)dc_sm_count() * 4 / L.col_blocks;
+    long long want = (long long)dc_sm_count() * 4 / L.col_blocks;     // measured: 1, 2, 6 and 8 chunks per SM are all slower
     if (want < 1) want = 1;
     long long by_rows = (M + L.row_lanes * 4 - 1) / (L.row_lanes * 4);   // at least 4 rows per thread
     if (by_rows < 1) by_rows = 1;
@@ -51,7 +51,17 @@ __global__ void __launch_bounds__(RED_T) col_reduce_kernel(F f, long long M, int
     for (int v = 0; v < NV; ++v) acc[v] = 0.0;
     if (c < C) {
         long long r = r0 + rl;
-        // four independent rows in flight per thread (the loads do not depend on the accumulators)
+        // eight independent rows in flight per thread (the loads do not depend on the accumulators): these reductions are
+        // bound by latency x bytes in flight, and fewer, longer chunks keep the finalize step short
+        for (; r + 7LL * row_lanes < r1; r += 8LL * row_lanes) {
+            float v0[NV], v1[NV], v2[NV], v3[NV], v4[NV], v5[NV], v6[NV], v7[NV];
+            f(r, c, v0); f(r + row_lanes, c, v1); f(r + 2LL * row_lanes, c, v2); f(r + 3LL * row_lanes, c, v3);
+            f(r + 4LL * row_lanes, c, v4); f(r + 5LL * row_lanes, c, v5); f(r + 6LL * row_lanes, c, v6); f(r + 7LL * row_lanes, c, v7);
+#pragma unroll
+            for (int v = 0; v < NV; ++v)
+                acc[v] += (((double)v0[v] + (double)v1[v]) + ((double)v2[v] + (double)v3[v])) +
+                          (((double)v4[v] + (double)v5[v]) + ((double)v6[v] + (double)v7[v]));
+        }
         for (; r + 3LL * row_lanes < r1; r += 4LL * row_lanes) {
             float v0[NV], v1[NV], v2[NV], v3[NV];
             f(r, c, v0); f(r + row_lanes, c, v1); f(r + 2LL * row_lanes, c, v2); f(r + 3LL * row_lanes, c, v3);
