@@ -188,7 +188,7 @@ __global__ void __launch_bounds__(FIN_T) central_bwd_finalize_kernel(const doubl
                                                                      float* __restrict__ dW, float* __restrict__ dgamma, float* __restrict__ dbeta) {
     double r[2 + CIN];
     if (!finalize_sums<2 + CIN>(partial, chunks, Cout, r)) return;
-    const int c = blockIdx.x * FIN_COLS + (threadIdx.x >> 5);
+    const int c = finalize_column();
     dbeta[c] = (float)r[0];
     dgamma[c] = (float)r[1];
     const double is = (double)invstd[c], a = (gamma ? (double)gamma[c] : 1.0) * is, mu = (double)mean[c];

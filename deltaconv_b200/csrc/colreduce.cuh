@@ -89,40 +89,53 @@ __global__ void __launch_bounds__(RED_T) col_reduce_kernel(F f, long long M, int
 }
 
 
-// Sum partial[q][v][c] over the chunks q for one column c and value v.  A CTA of 256 threads owns
-// 8 columns; the 32 lanes of a warp stride over the chunks of one column and the lane sums are
-// combined by a shuffle tree — a fixed order, so the result is deterministic.
+// Sum partial[q][v][c] over the chunks q for one column c and value v.  A CTA of 256 threads owns 2 columns, four warps
+// per column: each warp takes every fourth group of 32 chunks (with ~600 chunks that is 4-5 independent loads per lane, all
+// in flight at once: the step is pure latency), lane sums are combined by a shuffle tree and the four warp sums in a
+// fixed order through shared memory — deterministic.  Every thread of the CTA must call it (it holds a barrier).
 constexpr int FIN_T = 256;
-constexpr int FIN_COLS = 8;
+constexpr int FIN_SPLIT = 4;                       // warps per column
+constexpr int FIN_COLS = FIN_T / 32 / FIN_SPLIT;   // columns per CTA
+__device__ __forceinline__ int finalize_column() { return blockIdx.x * FIN_COLS + (threadIdx.x >> 5) / FIN_SPLIT; }
+
 template <int NV>
 __device__ __forceinline__ bool finalize_sums(const double* __restrict__ partial, int chunks, int C, double (&out)[NV]) {
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    const int c = blockIdx.x * FIN_COLS + w;
+    __shared__ double comb[NV][FIN_T / 32];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, sub = w % FIN_SPLIT;
+    const int c = finalize_column();
+    constexpr int STRIDE = 32 * FIN_SPLIT;
     double acc[NV];
 #pragma unroll
     for (int v = 0; v < NV; ++v) acc[v] = 0.0;
     if (c < C) {
-        int q = lane;
+        int q = sub * 32 + lane;
         // four chunks in flight per lane: the loads of one round are independent, only the adds are ordered
-        for (; q + 96 < chunks; q += 128) {
+        for (; q + 3 * STRIDE < chunks; q += 4 * STRIDE) {
             double t0[NV], t1[NV], t2[NV], t3[NV];
 #pragma unroll
             for (int v = 0; v < NV; ++v) {
                 t0[v] = partial[((size_t)q * NV + v) * C + c];
-                t1[v] = partial[((size_t)(q + 32) * NV + v) * C + c];
-                t2[v] = partial[((size_t)(q + 64) * NV + v) * C + c];
-                t3[v] = partial[((size_t)(q + 96) * NV + v) * C + c];
+                t1[v] = partial[((size_t)(q + STRIDE) * NV + v) * C + c];
+                t2[v] = partial[((size_t)(q + 2 * STRIDE) * NV + v) * C + c];
+                t3[v] = partial[((size_t)(q + 3 * STRIDE) * NV + v) * C + c];
             }
 #pragma unroll
             for (int v = 0; v < NV; ++v) acc[v] += (t0[v] + t1[v]) + (t2[v] + t3[v]);
         }
-        for (; q < chunks; q += 32)
+        for (; q < chunks; q += STRIDE)
 #pragma unroll
             for (int v = 0; v < NV; ++v) acc[v] += partial[((size_t)q * NV + v) * C + c];
     }
 #pragma unroll
-    for (int v = 0; v < NV; ++v) out[v] = warp_sum(acc[v]);
-    return lane == 0 && c < C;
+    for (int v = 0; v < NV; ++v) {
+        const double t = warp_sum(acc[v]);
+        if (lane == 0) comb[v][w] = t;
+    }
+    __syncthreads();
+    if (lane != 0 || sub != 0 || c >= C) return false;
+#pragma unroll
+    for (int v = 0; v < NV; ++v) out[v] = (comb[v][w] + comb[v][w + 1]) + (comb[v][w + 2] + comb[v][w + 3]);
+    return true;
 }
 
 }  // namespace

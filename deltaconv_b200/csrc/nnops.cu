@@ -32,7 +32,7 @@ struct SumVal {        // plain column sums of a [M,C] matrix
 __global__ void sum1_finalize_kernel(const double* __restrict__ partial, int chunks, int C, float* __restrict__ s0) {
     double r[1];
     if (!finalize_sums<1>(partial, chunks, C, r)) return;
-    s0[blockIdx.x * FIN_COLS + (threadIdx.x >> 5)] = (float)r[0];
+    s0[finalize_column()] = (float)r[0];
 }
 
 // ---- BatchNorm statistics ------------------------------------------------------------------
@@ -58,7 +58,7 @@ __global__ void bn_finalize_kernel(const double* __restrict__ partial, int chunk
     if (num_batches_tracked && blockIdx.x == 0 && threadIdx.x == 0) *num_batches_tracked += 1;
     double r[2];
     if (!finalize_sums<2>(partial, chunks, C, r)) return;
-    const int c = blockIdx.x * FIN_COLS + (threadIdx.x >> 5);
+    const int c = finalize_column();
     double s = r[0], s2 = r[1];
     double mu = s / (double)M;
     double var = s2 / (double)M - mu * mu;
@@ -131,7 +131,7 @@ struct BnBwdVal {
 __global__ void sum2_finalize_kernel(const double* __restrict__ partial, int chunks, int C, float* __restrict__ s0, float* __restrict__ s1) {
     double r[2];
     if (!finalize_sums<2>(partial, chunks, C, r)) return;
-    const int c = blockIdx.x * FIN_COLS + (threadIdx.x >> 5);
+    const int c = finalize_column();
     s0[c] = (float)r[0]; s1[c] = (float)r[1];
 }
 
