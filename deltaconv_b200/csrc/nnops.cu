@@ -39,6 +39,11 @@ __global__ void sum1_finalize_kernel(const double* __restrict__ partial, int chu
 struct PlainVal {      // x and x^2 of a [M,C] matrix
     const float* x; long long ld;
     __device__ void operator()(long long r, int c, float (&o)[2]) const { float v = __ldg(x + r * ld + c); o[0] = v; o[1] = v * v; }
+    __device__ NoColumns columns(int) const { return NoColumns(); }
+    __device__ void quad(long long r, int c, const NoColumns&, float (&o)[4][2]) const {
+        const float4 q = __ldg((const float4*)(x + r * ld + c));
+        o[0][0] = q.x; o[0][1] = q.x * q.x; o[1][0] = q.y; o[1][1] = q.y * q.y; o[2][0] = q.z; o[2][1] = q.z * q.z; o[3][0] = q.w; o[3][1] = q.w * q.w;
+    }
 };
 struct NormVal {       // |v| and |v|^2 of a [2M,C] vector field (nonlin.py:68)
     const float* x; long long ld;
@@ -46,6 +51,13 @@ struct NormVal {       // |v| and |v|^2 of a [2M,C] vector field (nonlin.py:68)
         float a = __ldg(x + (2 * r) * ld + c), b = __ldg(x + (2 * r + 1) * ld + c);
         float n2 = a * a + b * b;
         o[0] = sqrtf(n2); o[1] = n2;
+    }
+    __device__ NoColumns columns(int) const { return NoColumns(); }
+    __device__ void quad(long long r, int c, const NoColumns&, float (&o)[4][2]) const {
+        const float4 a = __ldg((const float4*)(x + (2 * r) * ld + c)), b = __ldg((const float4*)(x + (2 * r + 1) * ld + c));
+        const float aa[4] = {a.x, a.y, a.z, a.w}, bb[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+        for (int u = 0; u < 4; ++u) { const float n2 = aa[u] * aa[u] + bb[u] * bb[u]; o[u][0] = sqrtf(n2); o[u][1] = n2; }
     }
 };
 
@@ -116,6 +128,19 @@ __global__ void bn_act_fwd_vec4_kernel(const float* __restrict__ y, long long ld
 }
 
 // backward, reduction part: dz = dOut * act'(bn); sums of dz and dz * xhat per column
+// mean / invstd / gamma / beta of columns c..c+3 (BatchNorm backward reductions)
+__device__ __forceinline__ BnColumns bn_columns(const float* mean, const float* invstd, const float* gamma, const float* beta, int c) {
+    BnColumns k;
+    const float4 mu = __ldg((const float4*)(mean + c)), is = __ldg((const float4*)(invstd + c));
+    const float4 g = gamma ? __ldg((const float4*)(gamma + c)) : make_float4(1.f, 1.f, 1.f, 1.f);
+    const float4 b = beta ? __ldg((const float4*)(beta + c)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    k.mean[0] = mu.x; k.mean[1] = mu.y; k.mean[2] = mu.z; k.mean[3] = mu.w;
+    k.invstd[0] = is.x; k.invstd[1] = is.y; k.invstd[2] = is.z; k.invstd[3] = is.w;
+    k.gamma[0] = g.x; k.gamma[1] = g.y; k.gamma[2] = g.z; k.gamma[3] = g.w;
+    k.beta[0] = b.x; k.beta[1] = b.y; k.beta[2] = b.z; k.beta[3] = b.w;
+    return k;
+}
+
 struct BnBwdVal {
     const float* y; long long ldy; const float* dout; long long ldd;
     const float* mean; const float* invstd; const float* gamma; const float* beta; float slope;
@@ -125,6 +150,18 @@ struct BnBwdVal {
         float z = g * xh + b;
         float dz = __ldg(dout + r * ldd + c) * (z > 0.f ? 1.f : slope);
         o[0] = dz; o[1] = dz * xh;
+    }
+    __device__ BnColumns columns(int c) const { return bn_columns(mean, invstd, gamma, beta, c); }
+    __device__ void quad(long long r, int c, const BnColumns& k, float (&o)[4][2]) const {
+        const float4 yv = __ldg((const float4*)(y + r * ldy + c)), dv = __ldg((const float4*)(dout + r * ldd + c));
+        const float yy[4] = {yv.x, yv.y, yv.z, yv.w}, dd[4] = {dv.x, dv.y, dv.z, dv.w};
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const float xh = (yy[u] - k.mean[u]) * k.invstd[u];
+            const float z = k.gamma[u] * xh + k.beta[u];
+            const float dz = dd[u] * (z > 0.f ? 1.f : slope);
+            o[u][0] = dz; o[u][1] = dz * xh;
+        }
     }
 };
 
@@ -406,6 +443,22 @@ struct VnlBwdVal {
         float dq = (__ldg(dout + (2 * r) * ldd + c) * a + __ldg(dout + (2 * r + 1) * ldd + c) * b) / fmaxf(n, 1e-8f);
         float dz = z > 0.f ? dq : 0.f;
         o[0] = dz; o[1] = dz * xh;
+    }
+    __device__ BnColumns columns(int c) const { return bn_columns(mean, invstd, gamma, beta, c); }
+    __device__ void quad(long long r, int c, const BnColumns& k, float (&o)[4][2]) const {
+        const float4 a4 = __ldg((const float4*)(v + (2 * r) * ldv + c)), b4 = __ldg((const float4*)(v + (2 * r + 1) * ldv + c));
+        const float4 da4 = __ldg((const float4*)(dout + (2 * r) * ldd + c)), db4 = __ldg((const float4*)(dout + (2 * r + 1) * ldd + c));
+        const float aa[4] = {a4.x, a4.y, a4.z, a4.w}, bb[4] = {b4.x, b4.y, b4.z, b4.w}, da[4] = {da4.x, da4.y, da4.z, da4.w},
+                    db[4] = {db4.x, db4.y, db4.z, db4.w};
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const float n = sqrtf(aa[u] * aa[u] + bb[u] * bb[u]);
+            const float xh = (n - k.mean[u]) * k.invstd[u];
+            const float z = k.gamma[u] * xh + k.beta[u];
+            const float dq = (da[u] * aa[u] + db[u] * bb[u]) / fmaxf(n, 1e-8f);
+            const float dz = z > 0.f ? dq : 0.f;
+            o[u][0] = dz; o[u][1] = dz * xh;
+        }
     }
 };
 
@@ -812,12 +865,12 @@ extern "C" int dc_bn_stats(const float* x, int64_t ldx, int64_t M, int C, int mo
     DC_REQUIRE(M >= 1 && C >= 1, "dc_bn_stats: empty input");
     DC_REQUIRE(ws_bytes >= dc_colreduce_ws_bytes(C), "dc_bn_stats: workspace too small");
     cudaStream_t st = (cudaStream_t)stream;
-    ColLayout L = col_layout(M, C);
-    dim3 grid(L.chunks, L.col_blocks);
     double* partial = (double*)ws;
-    if (mode == 0) { PlainVal f = {x, ldx}; col_reduce_kernel<2><<<grid, RED_T, 0, st>>>(f, M, C, L.col_lanes, L.rows_per_chunk, partial); }
-    else { NormVal f = {x, ldx}; col_reduce_kernel<2><<<grid, RED_T, 0, st>>>(f, M, C, L.col_lanes, L.rows_per_chunk, partial); }
-    bn_finalize_kernel<<<dc_ceil_div(C, FIN_COLS), FIN_T, 0, st>>>(partial, L.chunks, M, C, eps, momentum, mean, invstd,
+    const bool vec4_ok = ldx % 4 == 0 && all_aligned16(x);
+    int chunks;
+    if (mode == 0) { PlainVal f = {x, ldx}; chunks = col_reduce_launch<2>(f, M, C, vec4_ok, partial, st); }
+    else { NormVal f = {x, ldx}; chunks = col_reduce_launch<2>(f, M, C, vec4_ok, partial, st); }
+    bn_finalize_kernel<<<dc_ceil_div(C, FIN_COLS), FIN_T, 0, st>>>(partial, chunks, M, C, eps, momentum, mean, invstd,
                                                             running_mean_or_null, running_var_or_null,
                                                             (long long*)num_batches_tracked_or_null);
     return dc_check_launch_n("dc_bn_stats", 2);
@@ -857,12 +910,11 @@ extern "C" int dc_bn_act_bwd(const float* y, int64_t ldy, const float* dout, int
     DC_REQUIRE(M >= 1 && C >= 1, "dc_bn_act_bwd: empty input");
     DC_REQUIRE(ws_bytes >= dc_colreduce_ws_bytes(C), "dc_bn_act_bwd: workspace too small");
     cudaStream_t st = (cudaStream_t)stream;
-    ColLayout L = col_layout(M, C);
-    dim3 grid(L.chunks, L.col_blocks);
     double* partial = (double*)ws;
     BnBwdVal f = {y, ldy, dout, ldd, mean, invstd, gamma_or_null, beta_or_null, slope};
-    col_reduce_kernel<2><<<grid, RED_T, 0, st>>>(f, M, C, L.col_lanes, L.rows_per_chunk, partial);
-    sum2_finalize_kernel<<<dc_ceil_div(C, FIN_COLS), FIN_T, 0, st>>>(partial, L.chunks, C, d_beta, d_gamma);
+    const int chunks = col_reduce_launch<2>(f, M, C, ldy % 4 == 0 && ldd % 4 == 0 && all_aligned16(y, dout, mean, invstd, gamma_or_null, beta_or_null),
+                                            partial, st);
+    sum2_finalize_kernel<<<dc_ceil_div(C, FIN_COLS), FIN_T, 0, st>>>(partial, chunks, C, d_beta, d_gamma);
     if (C % 4 == 0 && ldy % 4 == 0 && ldd % 4 == 0 && ld_dy % 4 == 0 && all_aligned16(y, dout, dy, mean, invstd, gamma_or_null, beta_or_null) &&
         all_aligned16(d_beta, d_gamma))
         bn_act_bwd_vec4_kernel<<<elementwise_grid(M * C / 4), 256, 0, st>>>(y, ldy, dout, ldd, M, C / 4, mean, invstd, gamma_or_null, beta_or_null,
@@ -898,12 +950,11 @@ extern "C" int dc_vecnonlin_bwd(const float* v, int64_t ldv, const float* dout, 
     cudaStream_t st = (cudaStream_t)stream;
     if (mean_or_null) {
         DC_REQUIRE(ws_bytes >= dc_colreduce_ws_bytes(C), "dc_vecnonlin_bwd: workspace too small");
-        ColLayout L = col_layout(M, C);
-        dim3 grid(L.chunks, L.col_blocks);
         double* partial = (double*)ws;
         VnlBwdVal f = {v, ldv, dout, ldd, mean_or_null, invstd_or_null, gamma_or_null, beta_or_null};
-        col_reduce_kernel<2><<<grid, RED_T, 0, st>>>(f, M, C, L.col_lanes, L.rows_per_chunk, partial);
-        sum2_finalize_kernel<<<dc_ceil_div(C, FIN_COLS), FIN_T, 0, st>>>(partial, L.chunks, C, d_beta, d_gamma);
+        const int chunks = col_reduce_launch<2>(f, M, C, ldv % 4 == 0 && ldd % 4 == 0 &&
+                                                all_aligned16(v, dout, mean_or_null, invstd_or_null, gamma_or_null, beta_or_null), partial, st);
+        sum2_finalize_kernel<<<dc_ceil_div(C, FIN_COLS), FIN_T, 0, st>>>(partial, chunks, C, d_beta, d_gamma);
     }
     if (C % 4 == 0 && ldv % 4 == 0 && ldd % 4 == 0 && ld_dv % 4 == 0 && all_aligned16(v, dout, dv))
         vecnonlin_bwd_vec4_kernel<<<elementwise_grid(M * C / 4), 256, 0, st>>>(v, ldv, dout, ldd, M, C, mean_or_null, invstd_or_null, gamma_or_null,
