@@ -97,6 +97,24 @@ def test_visiting_order_changes_nothing_and_exact_ties_go_to_the_lower_index():
         off += len(c)
 
 
+@pytest.mark.parametrize('offset,scale', [(0.0, 1.0), (3.0e4, 1.0), (-7.0e6, 1.0), (0.0, 1e-11), (0.0, 3e19), (1e-3, 1e-7)])
+def test_fp32_screening_never_costs_a_neighbour(offset, scale):
+    """The neighbour search screens candidates in fp32 with a margin derived from the largest coordinate.  Far from the
+    origin that margin is wide (coordinates lose most of their fp32 digits), at extreme scales the screening is off:
+    either way graph, sample sequence and fp64 distances must stay those of the all-fp64 restatement."""
+    rng = np.random.default_rng(17)
+    clouds = [(_shape(n, rng).astype(np.float64) + offset) * scale for n in (1500, 700)]      # genuinely double coordinates
+    pos = torch.from_numpy(np.concatenate(clouds)).to(DEV)
+    batch = torch.arange(2, device=DEV).repeat_interleave(torch.tensor([1500, 700], device=DEV))
+    got, dist = dc().ops.geodesic_fps(pos, 200, batch=batch, start=[11, 5], return_dist=True)
+    off = 0
+    for b, x in enumerate(clouds):
+        want, want_dist = ofps.restated_fps(x, 200, [11, 5][b], want_dist=True)
+        assert np.array_equal(got[b].cpu().numpy(), want), f'cloud {b}'
+        assert np.array_equal(dist[off:off + len(x)].cpu().numpy(), want_dist), f'cloud {b}'
+        off += len(x)
+
+
 @pytest.mark.skipif(not ofps.have_reference(), reason='compiled reference (oracle/_ref) not on this box')
 def test_against_the_compiled_reference_itself():
     rng = np.random.default_rng(99)
