@@ -242,7 +242,12 @@ def run_cuda_arm(args):
     torch.cuda.set_device(local)
     dev = torch.device('cuda', local)
     if world > 1:
-        os.environ['NCCL_DEBUG'] = os.environ.get('DC_NCCL_DEBUG', 'WARN')     # stdout must carry exactly one JSON line
+        # stdout must carry exactly one JSON line: NCCL writes its version banner (at WARN and above) to stdout, so its log is
+        # off unless asked for through DC_NCCL_DEBUG, and then it goes to stderr
+        os.environ.pop('NCCL_DEBUG', None)
+        if os.environ.get('DC_NCCL_DEBUG'):
+            os.environ['NCCL_DEBUG'] = os.environ['DC_NCCL_DEBUG']
+            os.environ.setdefault('NCCL_DEBUG_FILE', '/dev/stderr')
         dist.init_process_group('nccl', device_id=dev)
     lib = _lib.load()
 
