@@ -494,7 +494,7 @@ def run_fps_workload(args):
                 n_gpus=1, steps=args.steps, warmup=max(args.warmup, 3), ms_per_step=round(ms, 3), higher_is_better=True, scaling='weak',
                 vs_baseline=None, dtype='f64', data='synthetic',
                 config=dict(workload=f'{FPS_CLOUDS} clouds x {FPS_POINTS} pts -> {FPS_SAMPLES} samples per call (train_modelnet.py:32-33), 10-NN graph in fp64',
-                            l2='no flush: one call streams 58 MB of positions and builds a 291 MB graph (more than L2); the sampler is bound by DRAM latency per relaxation round, not by bandwidth'),
+                            l2='no flush: one call streams 58 MB of positions and builds a 310 MB graph (more than L2); the sampler is bound by DRAM latency per relaxation round, not by bandwidth'),
                 e2e=dict(value=round(FPS_CLOUDS / (e2e_ms / 1000), 1), unit='clouds/s', h2d_bytes_per_step=host.numel() * 4,
                          d2h_bytes_per_step=out_host.numel() * 8),
                 gpu_launches=launches, clocks=clocks)

@@ -34,6 +34,14 @@ constexpr int FPS_T = 512;           // threads of a sampling CTA
 constexpr int FPS_SMEM_POINTS = 18432;  // < 65,536: queue entries of shared-memory clouds are 16-bit
 constexpr unsigned long long INF_BITS = 0x7ff0000000000000ULL;
 
+// the graph: one 128-byte record (one cache line) per point, so that a relaxation round fetches one line per frontier point
+struct __align__(128) FpsEdges {
+    double len[FPS_K];       // edge lengths
+    int to[FPS_K];           // neighbours, as positions inside the cloud (visiting order)
+    int pad[2];
+};
+static_assert(sizeof(FpsEdges) == 128, "one line per point");
+
 __host__ __device__ constexpr size_t fps_smem_bytes(int points) { return (size_t)points * 12 + 8 * (size_t)((points + 31) / 32); }
 
 __device__ __forceinline__ int orig_of(const int* __restrict__ order, int j) { return order != nullptr ? __ldg(order + j) : j; }
@@ -122,7 +130,7 @@ __device__ __forceinline__ float box_lower_bound(const float4 lo, const float4 h
 __global__ void __launch_bounds__(KNN_WARPS * 32, 3) fps_knn_kernel(const double* __restrict__ spos, const float4* __restrict__ spos32,
                                                                  const float4* __restrict__ boxes, const float4* __restrict__ super_boxes,
                                                                  const int* __restrict__ order, const int* __restrict__ cloud_ptr,
-                                                                 int B, int N, int* __restrict__ nbr, double* __restrict__ wgt) {
+                                                                 int B, int N, FpsEdges* __restrict__ edges) {
     const int lane = threadIdx.x & 31;
     const int qbase = (blockIdx.x * KNN_WARPS + (threadIdx.x >> 5)) * 32;
     if (qbase >= N) return;                                    // whole warp
@@ -244,8 +252,8 @@ __global__ void __launch_bounds__(KNN_WARPS * 32, 3) fps_knn_kernel(const double
     for (int t = 0; t < FPS_K; ++t) {
         // clouds of fewer than 11 points: the free slots become self loops of length zero
         const bool have = bi[t] >= 0;
-        nbr[(size_t)i * FPS_K + t] = have ? bi[t] - s : i - s;             // position inside the cloud, visiting order
-        wgt[(size_t)i * FPS_K + t] = have ? __dsqrt_rn(bd[t]) : 0.;        // Vector3::norm of the edge (sampling.cpp:71)
+        edges[i].to[t] = have ? bi[t] - s : i - s;                          // position inside the cloud, visiting order
+        edges[i].len[t] = have ? __dsqrt_rn(bd[t]) : 0.;                    // Vector3::norm of the edge (sampling.cpp:71)
     }
 }
 
@@ -283,7 +291,7 @@ __device__ __forceinline__ void warp_argmax(bool takes_part, unsigned long long 
 // distance dropped in the round before; mask `round & 1` has a bit per point in that queue, so a point enters it once.
 template <typename QT>
 __device__ void fps_run(FpsShared& sh, unsigned long long* D, QT* q0, QT* q1, unsigned* m0, unsigned* m1, int mbase, bool own_masks, int s, int P,
-                        const int* __restrict__ my_nbr, const double* __restrict__ my_w, const int* __restrict__ order, int want_start,
+                        const FpsEdges* __restrict__ my_edges, const int* __restrict__ order, int want_start,
                         int n_samples, int* __restrict__ out, double* __restrict__ dist_or_null) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int t = threadIdx.x; t < P; t += FPS_T) D[t] = INF_BITS;
@@ -325,18 +333,16 @@ __device__ void fps_run(FpsShared& sh, unsigned long long* D, QT* q0, QT* q1, un
             for (int it = threadIdx.x; it < F * FPS_K; it += FPS_T) {
                 const int u = (int)qc[it / FPS_K], j = it % FPS_K;
                 if (j == 0) atomicAnd(mc + ((mbase + u) >> 5), ~(1u << ((mbase + u) & 31)));     // free the bit for round + 2
-                const int v = my_nbr[(size_t)u * FPS_K + j];
+                const int v = my_edges[u].to[j];
                 const double du = __longlong_as_double(*(volatile unsigned long long*)(D + u));
-                const unsigned long long nd = (unsigned long long)__double_as_longlong(__dadd_rn(du, my_w[(size_t)u * FPS_K + j]));
+                const unsigned long long nd = (unsigned long long)__double_as_longlong(__dadd_rn(du, my_edges[u].len[j]));
                 if (nd < *(volatile unsigned long long*)(D + v)) {
                     const unsigned long long old = atomicMin(D + v, nd);
                     const unsigned bit = 1u << ((mbase + v) & 31);
                     if (nd < old && !(atomicOr(mn + ((mbase + v) >> 5), bit) & bit)) {
                         qn[atomicAdd(cn, 1)] = (QT)v;
                         // next round starts with v's edges: pull them from L2 while this round finishes
-                        asm volatile("prefetch.global.L1 [%0];" :: "l"(my_nbr + (size_t)v * FPS_K));
-                        asm volatile("prefetch.global.L1 [%0];" :: "l"(my_w + (size_t)v * FPS_K));
-                        asm volatile("prefetch.global.L1 [%0];" :: "l"(my_w + (size_t)v * FPS_K + FPS_K - 1));
+                        asm volatile("prefetch.global.L1 [%0];" :: "l"(my_edges + v));
                     }
                 }
             }
@@ -381,8 +387,8 @@ __device__ void fps_run(FpsShared& sh, unsigned long long* D, QT* q0, QT* q1, un
         for (int t = threadIdx.x; t < P; t += FPS_T) dist_or_null[orig_of(order, s + t)] = __longlong_as_double((long long)D[t]);
 }
 
-__global__ void __launch_bounds__(FPS_T, 2) fps_sample_kernel(const int* __restrict__ cloud_ptr, const int* __restrict__ nbr,
-                                                              const double* __restrict__ wgt, const int* __restrict__ order,
+__global__ void __launch_bounds__(FPS_T, 2) fps_sample_kernel(const int* __restrict__ cloud_ptr, const FpsEdges* __restrict__ edges,
+                                                              const int* __restrict__ order,
                                                               const int* __restrict__ start, int n_samples, int* __restrict__ samples,
                                                               double* __restrict__ dist_or_null, int smem_points,
                                                               unsigned long long* gD, int* gq0, int* gq1, unsigned* gm0, unsigned* gm1) {
@@ -396,30 +402,29 @@ __global__ void __launch_bounds__(FPS_T, 2) fps_sample_kernel(const int* __restr
         return;
     }
     const int want = min(max(start[b], 0), P - 1);
-    const int* my_nbr = nbr + (size_t)s * FPS_K;
-    const double* my_w = wgt + (size_t)s * FPS_K;
+    const FpsEdges* my_edges = edges + s;
     if (P <= smem_points) {
         unsigned long long* D = (unsigned long long*)smem_raw;
         unsigned short* q0 = (unsigned short*)(D + P);
         unsigned short* q1 = q0 + P;
         unsigned* m0 = (unsigned*)(q1 + P);
         unsigned* m1 = m0 + (P + 31) / 32 + 1;
-        fps_run<unsigned short>(sh, D, q0, q1, m0, m1, 0, true, s, P, my_nbr, my_w, order, want, n_samples, out, dist_or_null);
+        fps_run<unsigned short>(sh, D, q0, q1, m0, m1, 0, true, s, P, my_edges, order, want, n_samples, out, dist_or_null);
         return;
     }
-    fps_run<int>(sh, gD + s, gq0 + s, gq1 + s, gm0, gm1, s, false, s, P, my_nbr, my_w, order, want, n_samples, out, dist_or_null);
+    fps_run<int>(sh, gD + s, gq0 + s, gq1 + s, gm0, gm1, s, false, s, P, my_edges, order, want, n_samples, out, dist_or_null);
 }
 
 size_t align256(size_t n) { return (n + 255) / 256 * 256; }
 
 }  // namespace
 
-// ordered positions + boxes + graph (neighbours, edge lengths), then the out-of-shared-memory state (D, two queues, two
+// ordered positions (fp64 and fp32) + boxes + graph (one 128-byte record per point), then the out-of-shared-memory state (D, two queues, two
 // masks) that only clouds above 18,432 points use
 extern "C" size_t dc_geodesic_fps_ws_bytes(int N) {
     const size_t n = (size_t)(N > 0 ? N : 0);
     const size_t tiles = (n + BOX_TILE - 1) / BOX_TILE;
-    return align256(n * 24) + align256(tiles * BOX_TILE * 16) + align256(tiles * 32) + align256((tiles / SUPER + 1) * 32) + align256(n * FPS_K * 4) + align256(n * FPS_K * 8) + align256(n * 8) +
+    return align256(n * 24) + align256(tiles * BOX_TILE * 16) + align256(tiles * 32) + align256((tiles / SUPER + 1) * 32) + align256(n * sizeof(FpsEdges)) + align256(n * 8) +
            2 * align256(n * 4) + 2 * align256((n / 32 + 2) * 4);
 }
 
@@ -436,8 +441,7 @@ extern "C" int dc_geodesic_fps(const double* pos, const int32_t* cloud_ptr, int 
     float4* spos32 = (float4*)w; w += align256(tiles * BOX_TILE * 16);
     float4* boxes = (float4*)w; w += align256(tiles * 32);
     float4* super_boxes = (float4*)w; w += align256((tiles / SUPER + 1) * 32);
-    int* nbr = (int*)w; w += align256((size_t)N * FPS_K * 4);
-    double* wgt = (double*)w; w += align256((size_t)N * FPS_K * 8);
+    FpsEdges* edges = (FpsEdges*)w; w += align256((size_t)N * sizeof(FpsEdges));
     unsigned long long* gD = (unsigned long long*)w; w += align256((size_t)N * 8);
     int* gq0 = (int*)w; w += align256((size_t)N * 4);
     int* gq1 = (int*)w; w += align256((size_t)N * 4);
@@ -448,7 +452,7 @@ extern "C" int dc_geodesic_fps(const double* pos, const int32_t* cloud_ptr, int 
         fps_sort_box_kernel<<<dc_ceil_div((long long)tiles, 4), 128, 0, st>>>(pos, order_or_null, N, spos, spos32, boxes);
         fps_super_box_kernel<<<dc_ceil_div((long long)dc_ceil_div((long long)tiles, SUPER), 128), 128, 0, st>>>(boxes, (int)tiles, super_boxes);
         fps_knn_kernel<<<dc_ceil_div(N, KNN_WARPS * 32), KNN_WARPS * 32, 0, st>>>(spos, spos32, boxes, super_boxes, order_or_null, cloud_ptr,
-                                                                                 B, N, nbr, wgt);
+                                                                                 B, N, edges);
         launches += 3;
     }
     // clouds up to `smem_points` keep their state in shared memory; larger ones (only if the caller's bound says they exist) in ws
@@ -458,7 +462,7 @@ extern "C" int dc_geodesic_fps(const double* pos, const int32_t* cloud_ptr, int 
         DC_CUDA(cudaMemsetAsync(gm0, 0, 2 * align256(((size_t)N / 32 + 2) * 4), st));
     if (smem > 48 * 1024)
         DC_CUDA(cudaFuncSetAttribute(fps_sample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(fps_smem_bytes(FPS_SMEM_POINTS) + 8)));
-    fps_sample_kernel<<<B, FPS_T, smem, st>>>(cloud_ptr, nbr, wgt, order_or_null, start, n_samples, samples, dist_or_null, smem_points,
+    fps_sample_kernel<<<B, FPS_T, smem, st>>>(cloud_ptr, edges, order_or_null, start, n_samples, samples, dist_or_null, smem_points,
                                               gD, gq0, gq1, gm0, gm1);
     return dc_check_launch_n("dc_geodesic_fps", launches);
 }
