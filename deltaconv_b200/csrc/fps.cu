@@ -18,10 +18,11 @@
 // relaxation rounds over a work queue — D[v] = min(D[v], D[u] + w(u,v)) with an atomic min on the bit pattern of the
 // non-negative double.  Rounded addition is monotone and edge weights are non-negative, so the fixed point these rounds
 // reach is exactly the vector Dijkstra returns, bit for bit, whatever the order of the relaxations; the argmax takes the
-// lowest ORIGINAL index among equal maxima like Eigen's maxCoeff.  The box test is exact as well: the distance to a box is
-// computed with the same operations as the distance to a point, and each of them is monotone, so it never exceeds the
-// computed distance to any point inside.  What is NOT pinned: which of several exactly equidistant neighbours the
-// kd-tree of the reference keeps (here: lowest original index).
+// lowest ORIGINAL index among equal maxima like Eigen's maxCoeff.  The pruning of the neighbour search can not change the
+// result either: boxes are stored rounded outwards and their distance is computed with round-down fp32 operations (a lower
+// bound of the fp64 distance to every point inside), the fp32 screening of single points carries a proven margin
+// (see fps_knn_kernel), and whatever survives is evaluated in fp64.  What is NOT pinned: which of several exactly
+// equidistant neighbours the kd-tree of the reference keeps (here: lowest original index).
 #include "common.cuh"
 
 namespace {
