@@ -1,5 +1,5 @@
 """The reference's own property tests (test/geometry/test_grad_div_mls.py, test/nn/test_nonlin.py,
-test/geometry/test_operators.py), re-run against the CUDA path.  Same constructions and thresholds as the
+test/geometry/test_operators.py, test/geometry/test_fps.py), re-run against the CUDA path.  Same constructions and thresholds as the
 reference unless a comment says otherwise.  Run with `-m gpu`."""
 import pytest
 import torch
@@ -145,3 +145,23 @@ def test_batchnorm_wrapper_behaviour():
     assert torch.allclose(bn(x), torch.zeros_like(x), atol=1e-3)
     y = torch.randn(500, 8, device=DEV)
     assert torch.allclose(bn(y), bn(2.5 * y + 1.0), atol=1e-4)
+
+
+def test_geodesic_fps_like_the_reference_test():
+    """test/geometry/test_fps.py: every point can be sampled exactly once, the requested number comes back, wrong inputs
+    raise ValueError — same calls, on the GPU sampler behind the reference's signature."""
+    import numpy as np
+    geodesic_fps = dc().geometry.geodesic_fps
+    n, n_samples = 1024, 512
+    rng = np.random.default_rng(0)
+    pos = rng.standard_normal((n, 3))                     # float64, as np.random.randn gives the reference
+    samples1 = geodesic_fps(pos, n)
+    assert samples1.shape[0] == n
+    assert np.unique(samples1).shape[0] == n
+    samples2 = geodesic_fps(pos, n_samples)
+    assert samples2.shape[0] == n_samples
+    assert np.unique(samples2).shape[0] == n_samples
+    with pytest.raises(ValueError):
+        geodesic_fps(torch.rand(n, 3), n)
+    with pytest.raises(ValueError):
+        geodesic_fps(rng.standard_normal((n, 2, 3)), n)
