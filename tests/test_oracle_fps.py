@@ -75,3 +75,46 @@ def test_relaxation_rounds_in_any_order_end_in_dijkstras_vector_bit_for_bit():
     for s in samples:
         d = _relaxation_rounds(nbr, length, int(s), d, rng)
     assert np.array_equal(d, final)
+
+
+def test_fp32_screening_margin_holds_on_random_and_adversarial_pairs():
+    """The neighbour search of fps.cu drops a candidate without an fp64 evaluation when its fp32 squared distance exceeds
+    R^2, R = (sqrt(T)(1 + 1e-15) + 2 sqrt(3) u S) / (1 - 3u), u = 2^-24, S = largest |coordinate|, T = current 10th d2.
+    The claim behind it: then the fp64 d2 exceeds T.  Checked here in numpy (fp32 arithmetic emulated with float32 ops) on
+    pairs placed right at the threshold, where a wrong margin would show."""
+    rng = np.random.default_rng(1)
+    u = 2.0 ** -24
+    n = 200000
+    for S_scale, offset in ((1.0, 0.0), (1.0, 50.0), (1.0, 4.0e4), (1e-6, 0.0), (1e9, 3e9)):
+        q = (rng.uniform(-1, 1, (n, 3)) + offset) * S_scale
+        direction = rng.standard_normal((n, 3))
+        direction /= np.linalg.norm(direction, axis=1, keepdims=True)
+        radius = rng.uniform(1e-3, 0.3, (n, 1)) * S_scale
+        p = q + direction * radius                                   # fp64 points at distance ~radius
+        S = max(np.abs(q).max(), np.abs(p).max())
+        d = q - p
+        d64 = (d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1]) + d[:, 2] * d[:, 2]
+        # thresholds just around the true distance: T in [d64 (1 - 1e-5), d64 (1 + 1e-5)]
+        T = d64 * (1 + rng.uniform(-1e-5, 1e-5, n))
+        R = (np.sqrt(T) * (1 + 1e-15) + 2 * np.sqrt(3.0) * u * S * (1 + 1e-6)) / (1 - 3 * u)
+        thr = np.nextafter((R * R * (1 + 1e-12)).astype(np.float32), np.float32(np.inf))       # rounded up, as __double2float_ru
+        q32, p32 = q.astype(np.float32), p.astype(np.float32)
+        e = q32 - p32
+        d32 = (e[:, 0] * e[:, 0] + e[:, 1] * e[:, 1]) + e[:, 2] * e[:, 2]
+        dropped = d32 > thr
+        assert not (dropped & (d64 <= T)).any(), (S_scale, offset)
+        # and the screening is not vacuous: near the origin a candidate twice as far as the 10th neighbour is always dropped
+        if offset == 0.0:
+            R_far = (np.sqrt(d64 / 4) * (1 + 1e-15) + 2 * np.sqrt(3.0) * u * S * (1 + 1e-6)) / (1 - 3 * u)
+            assert (d32 > (R_far * R_far * (1 + 1e-12)).astype(np.float32)).mean() > 0.999
+    # a wrong (too small) margin is caught by this construction: without the 2 sqrt(3) u S term pairs at offset 4e4 fail
+    q = (rng.uniform(-1, 1, (n, 3)) + 4.0e4)
+    direction = rng.standard_normal((n, 3)); direction /= np.linalg.norm(direction, axis=1, keepdims=True)
+    p = q + direction * rng.uniform(1e-3, 0.3, (n, 1))
+    d = q - p
+    d64 = (d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1]) + d[:, 2] * d[:, 2]
+    T = d64 * (1 + rng.uniform(0, 1e-5, n))
+    e = q.astype(np.float32) - p.astype(np.float32)
+    d32 = (e[:, 0] * e[:, 0] + e[:, 1] * e[:, 1]) + e[:, 2] * e[:, 2]
+    naive = (T * (1 + 1e-12)).astype(np.float32)
+    assert ((d32 > naive) & (d64 <= T)).any()
