@@ -459,7 +459,7 @@ extern "C" int dc_geodesic_fps(const double* pos, const int32_t* cloud_ptr, int 
     // clouds up to `smem_points` keep their state in shared memory; larger ones (only if the caller's bound says they exist) in ws
     const int smem_points = max_cloud_points < FPS_SMEM_POINTS ? max_cloud_points : FPS_SMEM_POINTS;
     const size_t smem = fps_smem_bytes(smem_points) + 8;
-    if (max_cloud_points > smem_points)
+    if (N > smem_points)      // a cloud that does not fit may exist (also when the caller's bound was too low): it needs clean masks
         DC_CUDA(cudaMemsetAsync(gm0, 0, 2 * align256(((size_t)N / 32 + 2) * 4), st));
     if (smem > 48 * 1024)
         DC_CUDA(cudaFuncSetAttribute(fps_sample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(fps_smem_bytes(FPS_SMEM_POINTS) + 8)));

@@ -61,12 +61,17 @@ def test_ragged_batch_matches_the_restatement_samples_and_distances(sizes, n_sam
 
 def test_cloud_too_large_for_shared_memory_takes_the_workspace_path():
     rng = np.random.default_rng(5)
-    clouds = [_shape(20000, rng), _shape(500, rng)]                 # above and below the 11,264-point limit, one launch
+    # above the 18,432-point limit of the shared-memory path, far below it, and just below it (one CTA per SM), one launch
+    clouds = [_shape(20000, rng), _shape(500, rng), _shape(17000, rng)]
     pos, batch = _batch(clouds)
-    got, dist = dc().ops.geodesic_fps(pos, 200, batch=batch, start=[123, 7], return_dist=True)
+    got, dist = dc().ops.geodesic_fps(pos, 200, batch=batch, start=[123, 7, 9999], return_dist=True)
     for b, x in enumerate(clouds):
-        want, want_dist = ofps.restated_fps(x, 200, [123, 7][b], want_dist=True)
+        want, want_dist = ofps.restated_fps(x, 200, [123, 7, 9999][b], want_dist=True)
         assert np.array_equal(got[b].cpu().numpy(), want)
+    # the same large cloud alone with a bound that is too low: it still takes the workspace path and stays correct
+    one = torch.zeros(20000, dtype=torch.int64, device=DEV)
+    alone = dc().ops.geodesic_fps(pos[:20000].clone(), 200, batch=one, num_clouds=1, start=[123], max_points=1000)
+    assert torch.equal(alone[0], got[0])
     assert np.array_equal(dist[:20000].cpu().numpy(), ofps.restated_fps(clouds[0], 200, 123, want_dist=True)[1])
 
 
