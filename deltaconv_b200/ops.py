@@ -174,7 +174,17 @@ def geodesic_fps(pos, n_samples, batch=None, num_clouds=None, start=None, max_po
     dist = torch.empty(N, dtype=torch.float64, device=pos.device) if return_dist else None
     nb = query('dc_geodesic_fps_ws_bytes', N)
     ws = workspace(nb, pos.device)
-    order = spatial_order(pos.float(), batch, B).to(_I32) if (ordered and maxp > 2 * 64) else None
+    order = None
+    if ordered and maxp > 2 * 64:
+        # visiting order: Morton curve inside every cloud.  Any order gives the same samples, so the sort key may be coarse:
+        # with up to 1023 clouds, (cloud, 21 Morton bits) fits 32 bits and torch's radix sort does half the passes on half
+        # the bytes of the 64-bit key (cloud << 30 | 30 bits)
+        keys = torch.empty(N, dtype=_I64, device=pos.device)
+        kws = workspace(B * 24, pos.device)
+        call('dc_morton_keys', ptr(pos.float().contiguous()), ptr(cp), B, N, ptr(keys), ptr(kws), B * 24)
+        if B <= 1023:
+            keys = (((keys >> 30) << 21) | ((keys & ((1 << 30) - 1)) >> 9)).to(_I32)
+        order = torch.argsort(keys, stable=True).to(_I32)
     call('dc_geodesic_fps', ptr(pos64), ptr(cp), B, N, min(maxp, N), int(n_samples), ptr(order), ptr(start), ptr(samples), ptr(dist),
          ptr(ws), nb)
     samples = samples.long()
