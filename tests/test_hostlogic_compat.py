@@ -15,14 +15,19 @@ provided = compat.install()
 import deltaconv
 from deltaconv.models import DeltaNetClassification, DeltaNetSegmentation
 from deltaconv.nn import DeltaConv, MLP
-from deltaconv.geometry import build_grad_div, estimate_basis
+from deltaconv.geometry import build_grad_div, estimate_basis, geodesic_fps
 import deltaconv.transforms as T
+# the nine transforms of the reference (deltaconv/transforms/__init__.py)
+for name in ('NormalizeScale', 'NormalizeArea', 'NormalizeAxes', 'RandomScale', 'RandomTranslateGlobal', 'RandomRotate',
+             'RandomNormals', 'SamplePoints', 'GeodesicFPS'):
+    assert hasattr(T, name), name
+assert repr(T.GeodesicFPS(1024)) == 'GeodesicFPS()'
 assert repr(T.RandomScale((0.8, 1.2))) == 'RandomScale((0.8, 1.2))'
 assert deltaconv.__name__ == 'deltaconv_b200'
 if provided:
     from torch_geometric.data import Data, Batch
     from torch_geometric.loader import DataLoader
-    from torch_geometric.transforms import Compose
+    from torch_geometric.transforms import Compose, SamplePoints
     from torch_geometric.nn import knn_graph, global_max_pool, global_mean_pool
     import torch
     class Shift:
