@@ -1,12 +1,16 @@
 #!/usr/bin/env python
 """Benchmark of the DeltaConv hot path on B200 (contract: see DESIGN.md §Measurement).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W]           # this repo's CUDA path
-    python bench.py --impl reference [--steps K] [--warmup W]     # the CPU oracle port on the host cores
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload train|seg|infer]   # this repo's CUDA path
+    python bench.py --impl reference [--steps K] [--warmup W] [--workload ...]          # the CPU arm on the host cores
 
-A step = one training step (forward + backward + gradient all-reduce + SGD) of
-DeltaNetClassification on BASELINE.json configs[1]: 32 clouds x 1024 points per GPU, k=20, 40
-classes, synthetic data, random-init weights.  One JSON line is printed by rank 0.
+A step = one pass of the workload over one synthetic batch with random-init weights:
+  train (default, the contract line)  configs[1]: DeltaNetClassification training step (forward + backward + gradient
+                                      all-reduce + SGD), 32 clouds x 1024 points per GPU, k=20, 40 classes
+  seg                                 configs[2]: DeltaNetSegmentation training step, 16 clouds x 2048 points per GPU, k=30
+  infer                               configs[4]: DeltaNetClassification evaluation forward, 32 clouds x 2048 points per GPU,
+                                      k=20, no normals (estimated frames), no collective
+One JSON line is printed by rank 0.
 """
 import argparse
 import json
@@ -23,10 +27,45 @@ if ROOT not in sys.path:
 
 import torch                                                   # noqa: E402
 
-CLOUDS, POINTS, K_NN, CLASSES = 32, 1024, 20, 40
-WORKLOAD = ("configs[1]: DeltaNetClassification training (fwd+bwd+SGD), 32 clouds x 1024 pts per GPU, k=20, "
-            "40 classes, convs [64,64,128,256], normals given")
-METRIC = "DeltaNetClassification training throughput (fwd+bwd+SGD), clouds/s"
+# The three model workloads BASELINE.json names (c2, c3, c5).  `train` is the contract line the driver runs.
+WORKLOADS = {
+    'train': dict(
+        tag='configs[1]', kind='cls', training=True, clouds=32, points=1024, k=20, classes=40, convs=[64, 64, 128, 256], normals=True,
+        synth=2, smoothing=True,
+        workload=("configs[1]: DeltaNetClassification training (fwd+bwd+SGD), 32 clouds x 1024 pts per GPU, k=20, "
+                  "40 classes, convs [64,64,128,256], normals given"),
+        metric="DeltaNetClassification training throughput (fwd+bwd+SGD), clouds/s"),
+    'seg': dict(
+        tag='configs[2]', kind='seg', training=True, clouds=16, points=2048, k=30, classes=50, convs=[64, 128, 256], normals=True,
+        synth=3, smoothing=False,
+        workload=("configs[2]: DeltaNetSegmentation training (fwd+bwd+SGD), ShapeNet-part shape: 16 clouds x 2048 pts per GPU, "
+                  "k=30, convs [64,128,256] with depth-2 MLPs, embedding 1024, categorical vector, 50 part classes, normals given "
+                  "(experiments/train_shapenet.py:79-89,169)"),
+        metric="DeltaNetSegmentation training throughput (fwd+bwd+SGD), clouds/s"),
+    'infer': dict(
+        tag='configs[4]', kind='cls', training=False, clouds=32, points=2048, k=20, classes=15, convs=[64, 64, 64, 128], normals=False,
+        synth=5, smoothing=True,
+        workload=("configs[4]: DeltaNetClassification inference (eval forward), ScanObjectNN shape: 32 clouds x 2048 pts per GPU, "
+                  "k=20, 15 classes, convs [64,64,64,128], no normals (second kNN k=10 + estimated frames), sharded by cloud, "
+                  "no collective (experiments/train_scanobjectnn.py:69-76)"),
+        metric="DeltaNetClassification inference throughput (eval forward), clouds/s"),
+}
+WL = WORKLOADS['train']                 # set by main()
+
+
+def make_model(pkg, wl):
+    """The workload's architecture from `pkg` (deltaconv_b200.models, oracle.network or the reference's deltaconv.models)."""
+    if wl['kind'] == 'seg':
+        return pkg.DeltaNetSegmentation(3, wl['classes'], conv_channels=list(wl['convs']), mlp_depth=2, embedding_size=1024,
+                                        categorical_vector=True, num_neighbors=wl['k'])
+    return pkg.DeltaNetClassification(3, wl['classes'], conv_channels=list(wl['convs']), num_neighbors=wl['k'])
+
+
+def make_batch(wl, rank=0, clouds=None):
+    from deltaconv_b200.utils import synthetic_batch
+    seg = wl['kind'] == 'seg'
+    return synthetic_batch(clouds or wl['clouds'], wl['points'], config=wl['synth'], rank=rank, normals=wl['normals'],
+                           num_classes=wl['classes'], per_point_labels=seg, categories=16 if seg else 0)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -45,7 +84,7 @@ def peaks():
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled every 50 ms while the timed region runs (a default run's timed region is ~0.25 s)."""
     QUERY = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
-             'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+             'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap,power.draw')
 
     def __init__(self, gpu_index):
         self.rows, self.proc = [], None
@@ -71,12 +110,16 @@ class ClockSampler:
         sm = [float(r[0]) for r in rows if r[0].replace('.', '').isdigit()]
         names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
         reasons = [n for i, n in enumerate(names) if any(r[2 + i].lower().startswith('active') for r in rows)]
+        power = [float(r[6]) for r in rows if len(r) > 6 and r[6].replace('.', '').isdigit()]
         return dict(sm_mhz=statistics.median(sm) if sm else None, sm_max_mhz=float(rows[0][1]) if rows[0][1].replace('.', '').isdigit() else None,
-                    reasons=reasons, samples=len(rows))
+                    reasons=reasons, samples=len(rows), power_w_median=statistics.median(power) if power else None,
+                    power_w_max=max(power) if power else None)
 
 
 # algorithmic work per entry point: name -> (args -> (bytes, flops)), family
 def _w_knn(a): N, k = a[3], a[4]; return N * (12 + 4 * k + (16 * k if a[6] else 0)), 0
+def _w_knn_grid(a): N, k = a[3], a[4]; return N * (12 + 4 * k + (16 * k if a[6] else 0)), 0
+def _w_basis(a): N, k = a[2], a[3]; return N * (48 + 4 * k), 0
 def _w_build(a): N, k = a[7], a[8]; return N * (48 + 20 * k), 0
 def _w_grad(a): N, k, C = a[2], a[3], a[4]; return N * (12 * k + 12 * C), 0
 def _w_grad_t(a): N, k, C = a[3], a[4], a[5]; return N * (12 * k + 12 * C), 0
@@ -98,18 +141,19 @@ def _w_segmax(a): N, k, C = a[1], a[2], a[3]; return N * C * (4 * k + 5), 0
 def _w_segmax_t(a): N, k, C = a[2], a[3], a[4]; return N * C * (4 * k + 5), 0
 def _w_pool(a): return 0, 0
 def _w_sgd(a): return a[3] * 20, 0                               # p, buf read and written, g read
-def _w_bnpool(a): return CLOUDS * POINTS * a[4] * 4, 0          # y read once, only [B,2C] written
+def _w_bnpool(a): return WL['clouds'] * WL['points'] * a[4] * 4, 0          # y read once, only [B,2C] written
 def _w_bnpool_t(a): M, C = a[2], a[3]; return M * C * 8, 0    # y read, dy written
 
 
 WORK = {
-    'dc_knn': (_w_knn, 'knn'), 'dc_build_grad_div': (_w_build, 'build_grad_div'),
+    'dc_knn': (_w_knn, 'knn'), 'dc_knn_grid': (_w_knn_grid, 'knn'), 'dc_build_grad_div': (_w_build, 'build_grad_div'),
+    'dc_estimate_basis': (_w_basis, 'frames'),
     'dc_grad_fwd': (_w_grad, 'spmm'), 'dc_grad_bwd': (_w_grad_t, 'spmm'),
     'dc_divcurlnorm_fwd': (_w_dcn, 'spmm'), 'dc_divcurlnorm_bwd': (_w_dcn_t, 'spmm'),
     'dc_hodge_fwd': (_w_hodge, 'spmm'), 'dc_hodge_bwd': (_w_hodge_t, 'spmm'),
     'dc_gathermax_fwd': (_w_gmax, 'gathermax'), 'dc_gathermax_bwd': (_w_gmax_t, 'gathermax'),
     'dc_bn_act_pool_fwd': (_w_bnpool, 'batchnorm'), 'dc_bn_act_pool_bwd': (_w_bnpool_t, 'batchnorm'),
-    'dc_sgd_step': (_w_sgd, 'optimizer'),
+    'dc_sgd_step': (_w_sgd, 'optimizer'), 'dc_pool_fwd': (_w_pool, 'pool'), 'dc_pool_bwd': (_w_pool, 'pool'), 'dc_bcast_rows': (_w_pool, 'pool'),
     'dc_bn_stats': (_w_stats, 'batchnorm'), 'dc_bn_act_fwd': (_w_bnf, 'batchnorm'), 'dc_bn_act_bwd': (_w_bnb, 'batchnorm'),
     'dc_vecnonlin_fwd': (_w_vnf, 'vecnonlin'), 'dc_vecnonlin_bwd': (_w_vnb, 'vecnonlin'),
     'dc_linear_fwd': (_w_lin, 'gemm'), 'dc_linear_bwd_input': (_w_linb, 'gemm'), 'dc_linear_bwd_weight': (_w_linb, 'gemm'),
@@ -166,60 +210,97 @@ class EntryPointProfiler:
         return '\n'.join(lines)
 
 
-def smoothed_loss(logits, target):
+def workload_loss(logits, target):
+    """calc_loss as the workload's script calls it: label smoothing for the classifiers (train_modelnet.py:104), plain cross
+    entropy for the part segmentation (train_shapenet.py:107)."""
     from deltaconv_b200.utils.losses import calc_loss
-    return calc_loss(logits, target)
+    return calc_loss(logits, target, smoothing=WL['smoothing'])
 
 
 # ------------------------------------------------------------------------------------------------
-# CPU baseline / reference arm: the oracle port of the reference's algorithm on the host cores
+# CPU baseline / reference arm.  Where a checkout of the reference is importable (DELTACONV_REFERENCE, default
+# /root/reference — the build container), its own unmodified deltaconv/**/*.py is timed through the fast stand-ins of
+# oracle/ref_standins_fast (kind "reference"); on the GPU box the checkout does not exist and the oracle port of the same
+# algorithm is timed (kind "port").  Both run the SAME workload as the CUDA arm: same model, same batch size.
 # ------------------------------------------------------------------------------------------------
 
-def cpu_port_steps(steps, warmup, clouds):
-    """Training steps of the oracle port (oracle/network.py, fast cdist+topk kNN) on the CPU."""
-    from oracle import network as on
-    from deltaconv_b200.utils import synthetic_batch, fill_deterministic
-    torch.manual_seed(1)
-    model = fill_deterministic(on.DeltaNetClassification(3, CLASSES, num_neighbors=K_NN), 1)
-    model.deltanet_base.fast_knn = True
-    model.train()
-    opt = torch.optim.SGD(model.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4)
-    data = synthetic_batch(clouds, POINTS, config=2, num_classes=CLASSES)
-    times = []
-    for i in range(warmup + steps):
+def reference_checkout():
+    path = os.environ.get('DELTACONV_REFERENCE', '/root/reference')
+    return path if os.path.isdir(os.path.join(path, 'deltaconv', 'models')) else None
+
+
+def _cpu_model_and_loss(wl):
+    """(model, loss_fn, kind, how) on the CPU with the deterministic weights every arm uses."""
+    from deltaconv_b200.utils import fill_deterministic
+    from deltaconv_b200.utils.losses import calc_loss
+    ref = reference_checkout()
+    if ref is not None and not os.environ.get('DC_BENCH_FORCE_PORT'):
+        here = os.path.join(ROOT, 'oracle')
+        for extra in (ref, os.path.join(here, 'ref_standins'), os.path.join(here, 'ref_standins_fast')):
+            if extra not in sys.path:
+                sys.path.insert(0, extra)
+        import deltaconv.models as ref_models                      # the reference itself
+        model = fill_deterministic(make_model(ref_models, wl), 1)
+        kind, how = 'reference', ("the unmodified reference's deltaconv/**/*.py (torch CPU) with cdist+topk kNN, CSR torch.sparse.mm "
+                                  "and index_add/scatter_reduce in place of the absent torch_cluster/torch_sparse/torch_scatter")
+    else:
+        from oracle import network as on
+        model = fill_deterministic(make_model(on, wl), 1)
+        model.deltanet_base.fast_knn = True
+        kind, how = 'port', 'the oracle port of the reference algorithm (torch CPU, ELL operators, cdist+topk kNN)'
+    return model, (lambda out, y: calc_loss(out, y, smoothing=wl['smoothing'])), kind, how
+
+
+def cpu_steps(wl, steps, warmup, budget_s=None):
+    """Steps of the workload on the host cores; returns (seconds of every timed step, kind, how).  With `budget_s` the number
+    of timed steps is trimmed (never the batch) so that the run ends in time; the warm-up steps size it."""
+    model, loss_fn, kind, how = _cpu_model_and_loss(wl)
+    data = make_batch(wl)
+    if wl['training']:
+        model.train()
+        opt = torch.optim.SGD(model.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4)
+    else:
+        model.eval()
+
+    def one():
         t0 = time.perf_counter()
-        opt.zero_grad()
-        loss = on.smoothed_cross_entropy(model(data), data.y)
-        loss.backward()
-        opt.step()
-        loss.item()
-        if i >= warmup:
-            times.append(time.perf_counter() - t0)
-    return times
+        if wl['training']:
+            opt.zero_grad()
+            loss = loss_fn(model(data), data.y)
+            loss.backward()
+            opt.step()
+            loss.item()
+        else:
+            with torch.no_grad():
+                model(data).sum().item()
+        return time.perf_counter() - t0
+
+    warm = [one() for _ in range(max(warmup, 1))]          # discarded (the first one pays allocator, thread pools, lazy imports)
+    if budget_s is not None:
+        steps = max(1, min(steps, int((budget_s - sum(warm)) / max(warm[-1], 1e-9))))
+    return [one() for _ in range(steps)], kind, how
 
 
 def run_reference_arm(args):
     rank = int(os.environ.get('RANK', '0'))
     if rank != 0:
         return
+    wl = WL
     torch.set_num_threads(os.cpu_count() or 1)          # torchrun pins OMP_NUM_THREADS=1; use all host cores
     cores = torch.get_num_threads()
-    clouds = 4
-    probe = cpu_port_steps(1, 0, 2)[0] / 2                                   # size the sample: seconds per cloud
-    budget = 150.0
-    while clouds > 2 and probe * clouds * (args.steps + args.warmup) > budget:   # >= 2 clouds: BatchNorm in the head
-        clouds //= 2
-    steps = args.steps
-    while steps > 1 and probe * clouds * (steps + args.warmup) > budget:
-        steps -= 1
-    times = cpu_port_steps(steps, args.warmup, clouds)
+    warm = max(min(args.warmup, 2), 1)
+    times, kind, how = cpu_steps(wl, args.steps, warm, budget_s=args.cpu_budget)
     ms = 1000 * sum(times) / len(times)
-    value = clouds / (ms / 1000)
-    sample = f"{steps} training steps of {clouds} clouds x {POINTS} pts (k={K_NN}) through the oracle port (torch CPU, cdist+topk kNN)"
-    line = dict(metric=METRIC, value=round(value, 3), unit='clouds/s', impl='reference', n_gpus=args.gpus, steps=steps,
-                warmup=args.warmup, ms_per_step=round(ms, 2), higher_is_better=True, scaling='weak', vs_baseline=None,
-                dtype='f32', data='synthetic', config=dict(workload=WORKLOAD, sample_clouds_per_step=clouds),
-                cpu_baseline=dict(value=round(value, 3), unit='clouds/s', cores=cores, kind='port', sample=sample),
+    value = wl['clouds'] / (ms / 1000)
+    what = 'training steps' if wl['training'] else 'evaluation forwards'
+    sample = (f"{len(times)} {what} (after {warm} warm-up) of the full {wl['clouds']} clouds x {wl['points']} pts "
+              f"(k={wl['k']}): {how}")
+    line = dict(metric=wl['metric'], value=round(value, 3), unit='clouds/s', impl='reference', n_gpus=args.gpus, steps=len(times),
+                warmup=warm, ms_per_step=round(ms, 2), higher_is_better=True, scaling='weak', vs_baseline=None,
+                dtype='f32', data='synthetic',
+                config=dict(workload=wl['workload'], clouds_per_gpu=wl['clouds'], points=wl['points'], k=wl['k'],
+                            steps_requested=args.steps, steps_timed=len(times), cpu_budget_s=args.cpu_budget),
+                cpu_baseline=dict(value=round(value, 3), unit='clouds/s', cores=cores, kind=kind, sample=sample),
                 e2e=dict(value=round(value, 3), unit='clouds/s', h2d_bytes_per_step=0, d2h_bytes_per_step=0))
     print(json.dumps(line), flush=True)
 
@@ -234,40 +315,51 @@ def run_cuda_arm(args):
     from deltaconv_b200 import _lib
     from deltaconv_b200.parallel import FlatGradients, FlatSGD
 
+    wl = WL
+    CLOUDS, POINTS, training = wl['clouds'], wl['points'], wl['training']
     world = int(os.environ.get('WORLD_SIZE', '1'))
     rank = int(os.environ.get('RANK', '0'))
     local = int(os.environ.get('LOCAL_RANK', '0'))
     if not torch.cuda.is_available():
-        raise SystemExit('bench.py: no CUDA device — the CUDA arm has no CPU fallback (use --impl reference for the CPU port)')
+        raise SystemExit('bench.py: no CUDA device — the CUDA arm has no CPU fallback (use --impl reference for the CPU arm)')
     torch.cuda.set_device(local)
     dev = torch.device('cuda', local)
     if world > 1:
-        # stdout must carry exactly one JSON line: NCCL writes its version banner (at WARN and above) to stdout, so its log is
-        # off unless asked for through DC_NCCL_DEBUG, and then it goes to stderr
-        os.environ.pop('NCCL_DEBUG', None)
-        if os.environ.get('DC_NCCL_DEBUG'):
-            os.environ['NCCL_DEBUG'] = os.environ['DC_NCCL_DEBUG']
-            os.environ.setdefault('NCCL_DEBUG_FILE', '/dev/stderr')
+        # stdout carries exactly one JSON line (printed last): whatever NCCL logs (the caller's NCCL_DEBUG setting is kept)
+        # goes to stderr unless the caller chose a file
+        os.environ.setdefault('NCCL_DEBUG_FILE', '/dev/stderr')
         dist.init_process_group('nccl', device_id=dev)
     lib = _lib.load()
+    if args.gemm_mode is not None:
+        lib.dc_set_gemm_mode(int(args.gemm_mode))
 
     torch.manual_seed(1)
-    model = D.utils.fill_deterministic(D.models.DeltaNetClassification(3, CLASSES, num_neighbors=K_NN), 1).to(dev).train()
-    flat = FlatGradients(model.parameters())
-    opt = FlatSGD(flat, lr=0.1, momentum=0.9, weight_decay=1e-4)          # torch.optim.SGD's update as one kernel on flat buffers
-    host = D.utils.synthetic_batch(CLOUDS, POINTS, config=2, rank=rank, num_classes=CLASSES).pin_memory()
-    host._num_clouds, host._max_points = CLOUDS, POINTS
-    resident = host.to(dev)
-    resident._num_clouds, resident._max_points = CLOUDS, POINTS
+    model = D.utils.fill_deterministic(make_model(D.models, wl), 1).to(dev)
+    model = model.train() if training else model.eval()
+    flat = opt = None
+    if training:
+        flat = FlatGradients(model.parameters())
+        opt = FlatSGD(flat, lr=0.1, momentum=0.9, weight_decay=1e-4)      # torch.optim.SGD's update as one kernel on flat buffers
+
+    def hinted(data):
+        data._num_clouds, data._max_points = CLOUDS, POINTS
+        return data
+    host = hinted(make_batch(wl, rank).pin_memory())
+    resident = hinted(host.to(dev))
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)             # > 126 MB L2
 
-    def step(data):
-        flat.zero()
-        loss = smoothed_loss(model(data), data.y)
-        loss.backward()
-        flat.all_reduce()
-        opt.step()
-        return loss
+    if training:
+        def step(data):
+            flat.zero()
+            loss = workload_loss(model(data), data.y)
+            loss.backward()
+            flat.all_reduce()
+            opt.step()
+            return loss
+    else:
+        def step(data):
+            with torch.no_grad():
+                return model(data)
 
     def barrier():
         torch.cuda.synchronize()
@@ -295,9 +387,9 @@ def run_cuda_arm(args):
 
     graphed = None
     if not args.no_graph:
-        static = host.to(dev)
-        static._num_clouds, static._max_points = CLOUDS, POINTS
-        graphed = D.utils.GraphedTrainStep(model, opt, smoothed_loss, static, flat=flat)
+        static = hinted(host.to(dev))
+        graphed = (D.utils.GraphedTrainStep(model, opt, workload_loss, static, flat=flat) if training
+                   else D.utils.GraphedInference(model, static))
         for _ in range(3):
             graphed()
 
@@ -311,27 +403,30 @@ def run_cuda_arm(args):
     wall1 = time.time()
     clocks = sampler.summary(wall0, wall1) if sampler else None
 
-    # (2) end to end: pinned host buffers -> device inside the timed region, loss read back every step
+    # (2) end to end: pinned host buffers -> device inside the timed region, result (loss / logits) read back every step
+    result_numel = 1 if training else CLOUDS * wl['classes']
+
     def e2e_step():
-        data = host.to(dev, non_blocking=True)
-        data._num_clouds, data._max_points = CLOUDS, POINTS
-        return step(data).item()
+        out = step(hinted(host.to(dev, non_blocking=True)))
+        return out.item() if training else out.cpu()
     # Graph replay: the next batch's host->device copy runs on a side stream while the current step computes (prefetch /
-    # commit), and each step's loss is copied to pinned host memory asynchronously and read one step later — the usual
-    # input pipeline of a training loop.  Every step still moves its own inputs H2D and its own loss D2H inside the timed region.
-    loss_host = torch.empty(2, dtype=torch.float32).pin_memory()
-    loss_ready = [torch.cuda.Event(), torch.cuda.Event()]
+    # commit), and each step's result is copied to pinned host memory asynchronously and read one step later — the usual
+    # input pipeline of a training / serving loop.  Every step still moves its own inputs H2D and its own result D2H inside
+    # the timed region.
+    out_host = torch.empty(2, result_numel, dtype=torch.float32).pin_memory()
+    out_ready = [torch.cuda.Event(), torch.cuda.Event()]
     pipe = dict(i=0, last=None)
+
     def e2e_graph_step():
         i = pipe['i']
         graphed.commit()
-        loss = graphed()
-        loss_host[i & 1].copy_(loss, non_blocking=True)
-        loss_ready[i & 1].record()
+        out = graphed()
+        out_host[i & 1].copy_(out.reshape(-1), non_blocking=True)
+        out_ready[i & 1].record()
         graphed.prefetch(host)
         if i > 0:
-            loss_ready[(i - 1) & 1].synchronize()
-            pipe['last'] = float(loss_host[(i - 1) & 1])
+            out_ready[(i - 1) & 1].synchronize()
+            pipe['last'] = float(out_host[(i - 1) & 1][0])
         pipe['i'] = i + 1
         return pipe['last']
     e2e_fn = e2e_graph_step if graphed else e2e_step
@@ -342,7 +437,20 @@ def run_cuda_arm(args):
     e2e_ms = timed(e2e_fn, args.steps)
     e2e_eager_ms = timed(e2e_step, args.steps) if graphed else e2e_ms
 
-    # (3) per-entry-point device time (CUDA events on the launching stream), same steps
+    # (3) sustained: the same replay for >= 2 s with the clock / power record (the default timed region is a burst of ~0.1 s)
+    sustained = None
+    if graphed and args.sustain > 0:
+        n_sus = max(args.steps, int(args.sustain * 1000 / max(total_ms / args.steps, 1e-3)) + 1)
+        sus_sampler = ClockSampler(local) if rank == 0 else None
+        w0 = time.time()
+        sus_ms = timed(graphed, n_sus)
+        w1 = time.time()
+        sus_clocks = sus_sampler.summary(w0, w1) if sus_sampler else None
+        sus_value = world * CLOUDS / (sus_ms / n_sus / 1000)
+        sustained = dict(value=round(sus_value, 2), unit='clouds/s', steps=n_sus, seconds=round(sus_ms / 1000, 3),
+                         ms_per_step=round(sus_ms / n_sus, 4), clocks=sus_clocks)
+
+    # (4) per-entry-point device time (CUDA events on the launching stream), same steps
     prof = EntryPointProfiler()
     _lib.PROFILER = prof
     barrier()
@@ -374,6 +482,8 @@ def run_cuda_arm(args):
     ms_per_step = total_ms / args.steps
     value = world * CLOUDS / (ms_per_step / 1000)
     e2e_value = world * CLOUDS / (e2e_ms / args.steps / 1000)
+    if sustained:
+        sustained['vs_burst'] = round(sustained['value'] / value, 4)
     top = max(fam, key=lambda f: fam[f]['ms'])
     kernels = {}
     for f, r in sorted(fam.items(), key=lambda kv: -kv[1]['ms']):
@@ -386,11 +496,11 @@ def run_cuda_arm(args):
     traffic, ncu = None, {}
     tpath = os.path.join(ROOT, 'profiles', 'ncu_traffic.json')
     if os.path.exists(tpath):
-        ncu = json.load(open(tpath)).get(top) or {}
+        ncu = json.load(open(tpath)).get(top if args.workload == 'train' else f'{args.workload}:{top}') or {}
         traffic = ncu.get('dram_bytes_per_launch_avg')
+    mode = int(lib.dc_get_gemm_mode())
     if tr['flops']:
         ach = tr['flops'] / (tr['ms'] / 1000) / 1e12
-        mode = int(lib.dc_get_gemm_mode())
         roof = dict(bound='tensor', kernel=KERNEL_OF.get(top, top), achieved=round(ach, 3), peak=pk['tensor'], unit='TFLOP/s',
                     frac=round(ach / pk['tensor'], 5), traffic=traffic, peak_source=pk['source'] + ', sustained bf16 (kernel timed inside a long step)',
                     share_of_step=kernels[top]['share'],
@@ -411,29 +521,34 @@ def run_cuda_arm(args):
     if world == 1 and not args.no_cpu_baseline:
         torch.set_num_threads(os.cpu_count() or 1)
         cores = torch.get_num_threads()
-        t = cpu_port_steps(2, 1, 4)
-        v = 4 / (sum(t) / len(t))
-        cpu = dict(value=round(v, 3), unit='clouds/s', cores=cores, kind='port',
-                   sample=f"2 training steps (after 1 warm-up) of 4 clouds x {POINTS} pts, k={K_NN}, oracle port (torch CPU, cdist+topk kNN)")
+        t, kind, how = cpu_steps(wl, 2, 1)
+        v = CLOUDS / (sum(t) / len(t))
+        what = 'training steps' if training else 'evaluation forwards'
+        cpu = dict(value=round(v, 3), unit='clouds/s', cores=cores, kind=kind,
+                   sample=f"{len(t)} {what} (after 1 warm-up) of the full {CLOUDS} clouds x {POINTS} pts, k={wl['k']}: {how}")
 
-    line = dict(metric=METRIC, value=round(value, 2), unit='clouds/s', n_gpus=world, steps=args.steps, warmup=max(args.warmup, 3),
+    gemm_modes = {0: 'FFMA fp32 only', 1: 'tcgen05 kind::tf32, single TF32 product (~1e-3 relative per product), fp32 accumulate',
+                  3: 'tcgen05 kind::tf32, 3xTF32 split (fp32-grade accuracy), fp32 accumulate; FFMA kernel for ineligible shapes'}
+    par = (f'dp{world} (shard by cloud, flat-gradient all-reduce)' if training else
+           f'{world} independent shards by cloud, no collective')
+    line = dict(metric=wl['metric'], value=round(value, 2), unit='clouds/s', n_gpus=world, steps=args.steps, warmup=max(args.warmup, 3),
                 ms_per_step=round(ms_per_step, 4), higher_is_better=True, scaling='weak', vs_baseline=None, dtype='f32',
                 data='synthetic',
-                config=dict(workload=WORKLOAD, clouds_per_gpu=CLOUDS, points=POINTS, k=K_NN, parallelism=f'dp{world} (shard by cloud, flat-gradient all-reduce)',
+                config=dict(workload=wl['workload'], clouds_per_gpu=CLOUDS, points=POINTS, k=wl['k'], parallelism=par,
                             l2='256 MiB buffer rewritten between steps (inside the timed region)',
-                            gemm='tcgen05 kind::tf32, 3xTF32 split (fp32-grade accuracy), fp32 accumulate; FFMA kernel for ineligible shapes',
+                            gemm=gemm_modes.get(mode, str(mode)),
                             launch='CUDA-graph replay of the whole step' if graphed else 'eager (one Python launch per kernel)',
                             eager_ms_per_step=round(eager_ms / args.steps, 4), e2e_eager_ms_per_step=round(e2e_eager_ms / args.steps, 4)),
-                e2e=dict(value=round(e2e_value, 2), unit='clouds/s', h2d_bytes_per_step=host.nbytes(), d2h_bytes_per_step=4,
+                e2e=dict(value=round(e2e_value, 2), unit='clouds/s', h2d_bytes_per_step=host.nbytes(), d2h_bytes_per_step=4 * result_numel,
                          ms_per_step=round(e2e_ms / args.steps, 4),
-                         pipeline='next batch copied on a side stream during the step, loss read one step later' if graphed else 'serial'),
-                gpu_launches=launches, roofline=roof, cpu_baseline=cpu, clocks=clocks,
+                         pipeline='next batch copied on a side stream during the step, result read one step later' if graphed else 'serial'),
+                gpu_launches=launches, roofline=roof, cpu_baseline=cpu, clocks=clocks, sustained=sustained,
                 kernels=kernels,
                 hbm_bound_kernels=dict(gbps=round(hbm_bytes / (hbm_ms / 1000) / 1e9, 1) if hbm_ms else None,
                                        frac_of_peak=round(hbm_bytes / (hbm_ms / 1000) / 1e9 / pk['hbm'], 4) if hbm_ms else None))
-    print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+    print(json.dumps(line), flush=True)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -529,11 +644,19 @@ def main():
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-graph', action='store_true', help='time eager launches instead of CUDA-graph replays')
     ap.add_argument('--detail', default=None, help='write the per-call device-time table to this file')
-    ap.add_argument('--workload', default='train', choices=['train', 'fps'],
-                    help="'fps': time the geodesic farthest-point sampling pre-transform instead of the training step (1 GPU)")
+    ap.add_argument('--workload', default='train', choices=['train', 'seg', 'infer', 'fps'],
+                    help="'train' (default, the contract line): configs[1] classifier training; 'seg': configs[2] part-segmentation "
+                         "training; 'infer': configs[4] ScanObjectNN-shape inference; 'fps': the geodesic farthest-point sampling "
+                         "pre-transform (1 GPU)")
+    ap.add_argument('--sustain', type=float, default=2.0, help='seconds of back-to-back replays for the `sustained` record (0 = skip)')
+    ap.add_argument('--cpu-budget', type=float, default=150.0, help='--impl reference: seconds after which timed steps are trimmed')
+    ap.add_argument('--gemm-mode', type=int, default=None, choices=[0, 1, 3],
+                    help='opt-in GEMM arithmetic: 3 = 3xTF32 split (default, fp32-grade), 1 = single TF32 product, 0 = FFMA')
     args = ap.parse_args()
     if args.workload == 'fps':
         return run_fps_workload(args)
+    global WL
+    WL = WORKLOADS[args.workload]
     if args.impl == 'reference':
         run_reference_arm(args)
     else:

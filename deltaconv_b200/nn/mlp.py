@@ -68,6 +68,8 @@ class _MLP(torch.nn.Sequential):
             lin, inner, slope = tail[0], tail[1].bn, _slope_of(tail[2])
             if ops.pool_fusable(inner, lin.out_features, lin.bias, slope):
                 return ops.linear_bn_act_pool(x, lin.weight, inner, slope, batch, mode, num_clouds)
+            if not torch.is_grad_enabled() and ops.pool_fusable_inference(inner, lin.out_features, lin.bias, slope, x):
+                return ops.linear_bn_act_pool_inference(x, lin.weight, inner, slope, batch, mode, num_clouds)
         return ops.pool(tail(x), batch, mode, num_clouds)
 
 

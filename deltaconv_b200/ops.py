@@ -26,6 +26,13 @@ def workspace(nbytes, device):
     return buf
 
 
+def live_workspaces():
+    """The scratch buffers currently installed (one per device).  A captured CUDA graph has their addresses baked in,
+    so whoever owns the graph keeps this list: a buffer that `workspace()` later replaces by a larger one then stays
+    allocated instead of being handed to other tensors while replays still write into it."""
+    return list(_workspaces.values())
+
+
 def _f32(t, name='tensor'):
     if not (torch.is_tensor(t) and t.is_cuda and t.dtype == _F32):
         raise _lib.DeltaConvLibraryError(
@@ -1004,6 +1011,35 @@ def linear_bn_act_pool(x, weight, bn, slope, batch, mode, size=None):
     Needs out_features % 4 == 0 (see `pool_fusable`)."""
     cp, B = cloud_ptr_of(batch, x.size(0), x.device, size)
     return _LinearBNActPool.apply(x, weight, bn.weight, bn.bias, bn, float(slope), cp, B, mode)
+
+
+def linear_bn_act_pool_inference(x, weight, bn, slope, batch, mode, size=None):
+    """The same fused Linear -> BatchNorm1d -> LeakyReLU -> pool with the layer's RUNNING statistics (evaluation mode),
+    for forward passes that record no autograd tape: the [N,C] activation is never written."""
+    cp, B = cloud_ptr_of(batch, x.size(0), x.device, size)
+    x, ldx = _mat(x, 'input')
+    weight, ldw = _mat(weight, 'weight')
+    M, K, C = x.size(0), x.size(1), weight.size(0)
+    dev = x.device
+    y = torch.empty(M, C, dtype=_F32, device=dev)
+    ws, nb = _gemm_ws(M, C, K, dev)
+    call('dc_linear_fwd', ptr(x), ldx, ptr(weight), ldw, None, M, K, C, ptr(y), C, ptr(ws), nb)
+    mean = bn.running_mean.contiguous()
+    invstd = torch.rsqrt(bn.running_var + bn.eps)
+    want_max, want_mean = mode in ('max', 'maxmean'), mode in ('mean', 'maxmean')
+    width = C * (2 if mode == 'maxmean' else 1)
+    out = torch.empty(B, width, dtype=_F32, device=dev)
+    arg = torch.empty(B, C, dtype=_I32, device=dev) if want_max else None
+    mean_p = (out.data_ptr() + (4 * C if mode == 'maxmean' else 0)) if want_mean else None
+    call('dc_bn_act_pool_fwd', ptr(y), C, ptr(cp), B, C, ptr(mean), ptr(invstd), ptr(bn.weight), ptr(bn.bias), float(slope),
+         ptr(out) if want_max else None, width, mean_p, width, ptr(arg))
+    return out
+
+
+def pool_fusable_inference(bn, out_features, bias, slope, x):
+    running = not (bn.training or not bn.track_running_stats or bn.running_mean is None)
+    no_tape = not (torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in bn.parameters())))
+    return running and no_tape and bias is None and slope is not None and out_features % 4 == 0
 
 
 def pool_fusable(bn, out_features, bias, slope):

@@ -11,10 +11,79 @@ The reference's loop (experiments/train_modelnet.py:98-108) maps onto it as
 import torch
 import torch.distributed as dist
 
+from .. import ops
 from ..parallel import FlatGradients
 
 
-class GraphedTrainStep:
+class _StaticInputs:
+    """Static input tensors of a captured graph and the two ways of refilling them: `load()` (a plain copy) and
+    `prefetch()` / `commit()` (host -> staging buffers on a side stream while the previous replay runs, then device to
+    device on the replay's stream)."""
+
+    static = None
+    _stage = None
+
+    def _keep_workspaces(self):
+        # The captured kernels have the addresses of the library's scratch buffers baked in.  `ops.workspace()` replaces
+        # a buffer when a later eager call asks for a larger one; holding the ones that were live during capture keeps
+        # their memory from going back to the allocator for as long as this object (and its graphs) exists.
+        self._workspaces = ops.live_workspaces()
+
+    def load(self, batch):
+        """Copy a (pinned-host or device) batch with the captured shapes into the static inputs."""
+        for name, dst in self.static.__dict__.items():
+            if torch.is_tensor(dst):
+                dst.copy_(getattr(batch, name), non_blocking=True)
+
+    def prefetch(self, batch):
+        """Start copying the NEXT batch (pinned host memory) into device staging buffers on a side stream, so that the
+        transfer overlaps the step that is running; `commit()` then moves it into the static inputs device-to-device."""
+        if self._stage is None:
+            self._stage = {name: torch.empty_like(t) for name, t in self.static.__dict__.items() if torch.is_tensor(t)}
+            self._copy_stream = torch.cuda.Stream()
+            self._staged = torch.cuda.Event()
+            self._consumed = torch.cuda.Event()
+            self._consumed.record()
+        self._copy_stream.wait_event(self._consumed)                 # the previous commit() has read the staging buffers
+        with torch.cuda.stream(self._copy_stream):
+            for name, dst in self._stage.items():
+                dst.copy_(getattr(batch, name), non_blocking=True)
+            self._staged.record()
+
+    def commit(self):
+        """Make the prefetched batch the input of the next replay (waits for its transfer on the device, not the host)."""
+        cur = torch.cuda.current_stream()
+        cur.wait_event(self._staged)
+        for name, src in self._stage.items():
+            getattr(self.static, name).copy_(src, non_blocking=True)
+        self._consumed.record(cur)
+
+
+class GraphedInference(_StaticInputs):
+    """Evaluation forward (`model.eval()`, no autograd) captured in one CUDA graph: `load(batch)` (or `prefetch` /
+    `commit`), then `logits = runner()`.  The returned tensor is the graph's static output — copy it before the next
+    replay.  Same contract on `example` as GraphedTrainStep (same shapes and cloud layout on every batch)."""
+
+    def __init__(self, model, example, warmup=2):
+        self.model, self.static = model, example
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side), torch.no_grad():
+            for _ in range(warmup):
+                model(self.static)
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.no_grad(), torch.cuda.graph(self.graph):
+            self.out = model(self.static)
+        self._keep_workspaces()
+
+    def __call__(self):
+        self.graph.replay()
+        return self.out
+
+
+class GraphedTrainStep(_StaticInputs):
     """forward + loss + backward (+ gradient all-reduce) + optimizer step as CUDA graph replays.
 
     `example` is a device-resident `Data` batch whose tensors become the static inputs; every later
@@ -53,41 +122,13 @@ class GraphedTrainStep:
             with torch.cuda.graph(self.graph_fb):
                 self.loss = self._forward_backward()
                 self.optimizer.step()
+        self._keep_workspaces()
 
     def _forward_backward(self):
         self.flat.zero()
         loss = self.loss_fn(self.model(self.static), self.static.y)
         loss.backward()
         return loss.detach()
-
-    def load(self, batch):
-        """Copy a (pinned-host or device) batch with the captured shapes into the static inputs."""
-        for name, dst in self.static.__dict__.items():
-            if torch.is_tensor(dst):
-                dst.copy_(getattr(batch, name), non_blocking=True)
-
-    def prefetch(self, batch):
-        """Start copying the NEXT batch (pinned host memory) into device staging buffers on a side stream, so that the
-        transfer overlaps the step that is running; `commit()` then moves it into the static inputs device-to-device."""
-        if self._stage is None:
-            self._stage = {name: torch.empty_like(t) for name, t in self.static.__dict__.items() if torch.is_tensor(t)}
-            self._copy_stream = torch.cuda.Stream()
-            self._staged = torch.cuda.Event()
-            self._consumed = torch.cuda.Event()
-            self._consumed.record()
-        self._copy_stream.wait_event(self._consumed)                 # the previous commit() has read the staging buffers
-        with torch.cuda.stream(self._copy_stream):
-            for name, dst in self._stage.items():
-                dst.copy_(getattr(batch, name), non_blocking=True)
-            self._staged.record()
-
-    def commit(self):
-        """Make the prefetched batch the input of the next replay (waits for its transfer on the device, not the host)."""
-        cur = torch.cuda.current_stream()
-        cur.wait_event(self._staged)
-        for name, src in self._stage.items():
-            getattr(self.static, name).copy_(src, non_blocking=True)
-        self._consumed.record(cur)
 
     def __call__(self):
         sync_lr = getattr(self.optimizer, 'sync_lr', None)

@@ -36,6 +36,15 @@ def rel_err(ours, ref):
     return ((ours - ref).abs().max() / ref.abs().max().clamp(min=1e-300)).item()
 
 
+def elem_err(ours, ref):
+    """Per-element worst case max_i |ours_i - ref_i| / |ref_i| (entries below 1e-6 of the tensor's scale are measured against
+    that floor).  Reported beside the tensor-scaled `rel_err`, which is the reading the tolerances are stated in: a logit that
+    is small next to the largest one may be off by more than 1e-4 of ITSELF while the tensor-scaled error is within bounds."""
+    ours, ref = ours.double(), ref.double()
+    floor = 1e-6 * ref.abs().max().clamp(min=1e-300)
+    return ((ours - ref).abs() / ref.abs().clamp(min=floor)).max().item()
+
+
 def check_frames(normal, xb, yb, tol=1e-5):
     """orthonormal + right-handed (reference tests: test_grad_div_mls.py:12-24)."""
     for a in (normal, xb, yb):

@@ -1,0 +1,161 @@
+"""GPU parity at the shapes BASELINE.json names ("parity at the config shape"): the CUDA path against the
+fp64 oracle with identical deterministic weights on the same synthetic batch — logits, loss and EVERY parameter gradient.
+
+  configs[1]  DeltaNetClassification, 32 clouds x 1024 pts, k=20, 40 classes, normals given       (train mode)
+  configs[2]  DeltaNetSegmentation,  ShapeNet-part shape, 2 clouds x 2048 pts, k=30, depth 2      (train mode, + gradients)
+  configs[4]  DeltaNetClassification, ScanObjectNN shape, 4 clouds x 2048 pts, k=20, NO normals   (train mode + eval mode)
+
+Tolerances: tests/helpers.py (logits rel 1e-4 of the tensor scale; gradients GRAD_REL of the tensor scale).  The tensor-scaled
+reading and the per-element worst case are both written to gpurun_out/parity_report.txt.
+Run with `-m gpu`."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+from helpers import rel_err, elem_err, report, LOGIT_REL, GRAD_REL
+from oracle import network as on
+
+pytestmark = pytest.mark.gpu
+DEV = 'cuda'
+
+
+def dc():
+    import deltaconv_b200
+    return deltaconv_b200
+
+
+def no_dropout(m):
+    for mod in m.modules():
+        if isinstance(mod, torch.nn.Dropout):
+            mod.p = 0.0
+    return m
+
+
+def pair(build_ours, build_oracle, seed):
+    D = dc()
+    model = no_dropout(D.utils.fill_deterministic(build_ours(D.models), seed))
+    oracle = no_dropout(build_oracle(on)).double()
+    oracle.load_state_dict({k: (v.double() if v.is_floating_point() else v) for k, v in model.state_dict().items()})
+    return model.to(DEV), oracle
+
+
+def compare_train_step(name, model, oracle, data, loss_ours, loss_ref, grad_factor=5.0):
+    """Training-mode forward + backward on both sides; logits, loss, and every parameter gradient."""
+    model.train()
+    oracle.train()
+    dev_data = data.to(DEV)
+    logits = model(dev_data)
+    ref = oracle(data.double())
+    report(f'{name}.logits_train.per_element', elem_err(logits.detach().cpu(), ref.detach()))
+    assert report(f'{name}.logits_train', rel_err(logits.detach().cpu(), ref.detach())) < LOGIT_REL
+    l_ref = loss_ref(ref, data.y)
+    l_ours = loss_ours(logits, dev_data.y)
+    assert abs(l_ours.item() - l_ref.item()) < LOGIT_REL * max(1.0, abs(l_ref.item()))
+    l_ref.backward()
+    l_ours.backward()
+    ref_grads = dict(oracle.named_parameters())
+    worst, worst_name = 0.0, None
+    for pname, p in model.named_parameters():
+        if ref_grads[pname].grad is None:
+            assert p.grad is None, pname              # VectorNonLin.bias under BatchNorm
+            continue
+        assert p.grad is not None, pname
+        err = rel_err(p.grad.cpu(), ref_grads[pname].grad)
+        if err > worst:
+            worst, worst_name = err, pname
+    report(f'{name}.grad_worst[{worst_name}]', worst)
+    assert worst < grad_factor * GRAD_REL, worst_name
+    return logits, ref
+
+
+def test_config1_classifier_32x1024_vs_oracle():
+    """BASELINE configs[1] at full size: the bench workload itself."""
+    D = dc()
+    data = D.utils.synthetic_batch(32, 1024, config=2, num_classes=40)
+    model, oracle = pair(lambda m: m.DeltaNetClassification(3, 40, num_neighbors=20), lambda m: m.DeltaNetClassification(3, 40, num_neighbors=20), 1)
+    compare_train_step('config1_cls_32x1024', model, oracle, data, on.smoothed_cross_entropy, on.smoothed_cross_entropy)
+
+
+def test_config2_segmentation_gradients_vs_oracle():
+    """BASELINE configs[2] architecture on 2 x 2048 points, k=30: logits AND all parameter gradients (plain cross entropy,
+    train_shapenet.py:107)."""
+    D = dc()
+    data = D.utils.synthetic_batch(2, 2048, config=3, num_classes=50, per_point_labels=True, categories=16)
+    kw = dict(conv_channels=[64, 128, 256], mlp_depth=2, embedding_size=1024, categorical_vector=True, num_neighbors=30)
+    model, oracle = pair(lambda m: m.DeltaNetSegmentation(3, 50, **kw), lambda m: m.DeltaNetSegmentation(3, 50, **kw), 7)
+    logits, _ = compare_train_step('config2_seg_2x2048', model, oracle, data, F.cross_entropy, F.cross_entropy)
+    assert tuple(logits.shape) == (4096, 50)
+
+
+def test_config4_scanobjectnn_shape_no_normals_vs_oracle():
+    """BASELINE configs[4] architecture (convs [64,64,64,128], 15 classes, k=20) on 4 x 2048 points WITHOUT normals: second
+    kNN (k=10) + estimated frames + operator build + network, training mode (logits + gradients) and evaluation mode (the
+    mode the config is benchmarked in; running statistics)."""
+    D = dc()
+    data = D.utils.synthetic_batch(4, 2048, config=5, num_classes=15, normals=False)
+    build = lambda m: m.DeltaNetClassification(3, 15, conv_channels=[64, 64, 64, 128], num_neighbors=20)   # noqa: E731
+    model, oracle = pair(build, build, 3)
+    compare_train_step('config4_infer_4x2048_nonormal', model, oracle, data, on.smoothed_cross_entropy, on.smoothed_cross_entropy)
+    # evaluation mode with the deterministic running statistics (the train step above updated both sides identically)
+    model, oracle = pair(build, build, 3)
+    model.eval()
+    oracle.eval()
+    with torch.no_grad():
+        logits = model(data.to(DEV))
+        ref = oracle(data.double())
+    report('config4_infer_4x2048_nonormal.logits_eval.per_element', elem_err(logits.cpu(), ref))
+    assert report('config4_infer_4x2048_nonormal.logits_eval', rel_err(logits.cpu(), ref)) < LOGIT_REL
+    assert torch.equal(logits.argmax(1).cpu(), ref.argmax(1))
+
+
+def test_graphed_inference_matches_eager():
+    """GraphedInference (bench.py --workload infer) returns the eager evaluation forward bit for bit, also after an eager
+    call that grows the library's scratch buffer between capture and replay (the captured kernels keep the old buffer)."""
+    D = dc()
+    data = D.utils.synthetic_batch(4, 512, config=5, num_classes=15, normals=False).to(DEV)
+    data._num_clouds, data._max_points = 4, 512
+    model = D.utils.fill_deterministic(D.models.DeltaNetClassification(3, 15, conv_channels=[32, 32, 64], num_neighbors=16), 2).to(DEV).eval()
+    with torch.no_grad():
+        eager = model(data).clone()
+    runner = D.utils.GraphedInference(model, data)
+    assert torch.equal(runner(), eager)
+    # an eager call asks for a larger scratch buffer: ops.workspace() installs a new one.  The graph owner still holds the
+    # old one, so the allocator cannot hand its memory to the tensors allocated next.
+    old = D.ops.live_workspaces()[0]
+    old_ptr, old_bytes = old.data_ptr(), old.numel()
+    del old
+    D.ops.workspace(2 * old_bytes + (64 << 20), data.pos.device)
+    junk = [torch.full((old_bytes // 4,), float('nan'), device=DEV) for _ in range(4)]
+    assert all(j.data_ptr() != old_ptr for j in junk)
+    torch.cuda.synchronize()
+    assert torch.equal(runner(), eager)
+    torch.cuda.synchronize()
+    assert all(bool(torch.isnan(j).all()) for j in junk)          # no replayed kernel wrote into somebody else's memory
+
+
+def test_graphed_train_step_survives_workspace_growth():
+    """The same guarantee for the captured training step: capture, grow the scratch buffer with an eager
+    call, allocate and fill tensors, replay — the loss sequence equals an uninterrupted run's."""
+    D = dc()
+    from deltaconv_b200.utils.losses import calc_loss
+    losses = []
+    for disturb in (False, True):
+        torch.manual_seed(0)
+        data = D.utils.synthetic_batch(4, 256, config=2, num_classes=10).to(DEV)
+        data._num_clouds, data._max_points = 4, 256
+        net = no_dropout(D.utils.fill_deterministic(D.models.DeltaNetClassification(3, 10, conv_channels=[16, 32]), 5)).to(DEV).train()
+        opt = torch.optim.SGD(net.parameters(), lr=0.05, momentum=0.9)
+        step = D.utils.GraphedTrainStep(net, opt, calc_loss, data, warmup=2)
+        seq = [step().item()]
+        junk = None
+        if disturb:
+            nbytes = D.ops.live_workspaces()[0].numel()
+            D.ops.workspace(2 * nbytes + (64 << 20), data.pos.device)
+            junk = [torch.full((nbytes // 4,), float('nan'), device=DEV) for _ in range(4)]
+            torch.cuda.synchronize()
+        seq += [step().item() for _ in range(2)]
+        if junk is not None:
+            torch.cuda.synchronize()
+            assert all(bool(torch.isnan(j).all()) for j in junk)
+        losses.append(seq)
+    assert losses[0] == losses[1]
