@@ -36,6 +36,7 @@ _SIGNATURES = {
     'dc_estimate_basis': [_P, _P, _I, _I, _P, _P, _P, _P, _P],
     'dc_build_ws_bytes': [_I, _I],
     'dc_build_grad_div': [_P, _P, _P, _P, _P, _P, _I, _I, _I, _F, _F, _F, _I, _I, _P, _P, _P, _P, _P, _P, _Z, _P],
+    'dc_set_build_chunk': [_I],
     'dc_build_static_max_points': [],
     'dc_build_static_max_clouds': [],
     'dc_build_grad_div_static': [_P, _P, _P, _P, _P, _P, _I, _I, _I, _F, _F, _F, _I, _I, _P, _P, _P],

@@ -5,11 +5,11 @@
 //   ~70 ATen launches, [E,*] temporaries, two COO->CSR sorts become:
 //     edge_mean_kernel  (pass A: per-point mean edge length)            -> ws.m[N]
 //     cloud_mean_kernel (per-cloud mean of m, zero the cloud maxima)    -> ws.abar[B], ws.S[B]
-//     fit_kernel<REDUCE> (pass B1: fit, row norms, per-cloud max)        -> ws.S[B]   (only if normalized)
-//     fit_kernel<WRITE>  (pass B2: fit again, scale, frame mapping)      -> G[N,k,2], D[N,k,2]
+//     fit_kernel   (pass B: the fit, ONCE; un-normalised entries, per-cloud max)  -> G[N,k,2], D[N,k,2], ws.S[B]
+//     scale_kernel (pass C: entries x 1 / S_cloud, only if normalized; L2-resident) -> G, D
 // One thread owns one point; its k slots live in shared memory slot-major (stride T+1, conflict
 // free), which also turns the idx tile load and the G/D tile stores into fully coalesced
-// streams.  The 6x6 normal equations are assembled and Cholesky-solved in registers.
+// streams.  The 6x6 normal equations are assembled from 15 moments and Cholesky-solved in registers.
 #include "common.cuh"
 #include "geom_core.cuh"
 
@@ -96,24 +96,29 @@ __global__ void __launch_bounds__(CLOUD_MEAN_T) cloud_mean_kernel(const float* _
     }
 }
 
-// ---- pass B ---------------------------------------------------------------------------------
-// One thread per point; its k slots live slot-major in shared memory.  Gathers are issued four
-// slots at a time before any dependent arithmetic (the compiler cannot hoist them across the
-// shared-memory stores itself), which is what hides the L2 latency at 12-16 resident warps.
-template <int T, bool WRITE>
+// ---- the fit --------------------------------------------------------------------------------
+// One thread per point, ONE pass (geom_core.cuh).  The k slots of the CTA's T points live slot-major in shared memory (stride
+// T+1: conflict free), which also turns the idx tile load and the G/D tile stores into fully coalesced streams.  Gathers are
+// issued four slots at a time before any dependent arithmetic (the compiler cannot hoist them across the shared-memory
+// stores itself).  K is the compile-time neighbour count (0 = run-time k): with it the slot loops unroll and every
+// shared-memory address is an immediate.  Entries are written WITHOUT the per-cloud normalisation; the per-cloud maxima go to
+// S (one atomicMax per warp: s_i >= 0, so its bit pattern orders like the value and the integer max is exact and order
+// independent, replacing scatter_max of grad_div_mls.py:259) and scale_kernel applies them.
+template <int T, int K, bool DEBUG>
 __global__ void __launch_bounds__(T)
 fit_kernel(const float* __restrict__ pos, const float* __restrict__ normal, const float* __restrict__ xb,
            const float* __restrict__ yb, const int* __restrict__ idx, const int* __restrict__ cloud_ptr, int B,
-           int N, int k, float kernel_width, FitParams fp, int normalized, const float* __restrict__ abar,
+           int N, int k_rt, int n0, int n1, float kernel_width, FitParams fp, int normalized, const float* __restrict__ abar,
            unsigned* __restrict__ S, float* __restrict__ G, float* __restrict__ D,
            float* __restrict__ dbg_coords, float* __restrict__ dbg_weights, float* __restrict__ dbg_mapping) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int STRIDE = T + 1;
+    const int k = K ? K : k_rt;
     float4* s_dat = reinterpret_cast<float4*>(smem_raw);                                   // [k][STRIDE]
     int* s_idx = reinterpret_cast<int*>(smem_raw + (size_t)k * STRIDE * sizeof(float4));   // [k][STRIDE]
 
-    const int base = blockIdx.x * T;
-    const int npts = min(T, N - base);
+    const int base = n0 + blockIdx.x * T;
+    const int npts = min(T, n1 - base);
     const int tile = npts * k;
     // coalesced idx tile load, transposed into slot-major shared memory
     const int* gidx = idx + (size_t)base * k;
@@ -125,61 +130,75 @@ fit_kernel(const float* __restrict__ pos, const float* __restrict__ normal, cons
     __syncthreads();
 
     const int i = base + threadIdx.x;
-    if (threadIdx.x < npts) {
-        SlotView sv;
-        sv.idx = s_idx + threadIdx.x;
-        sv.dat = s_dat + threadIdx.x;
-        sv.stride = STRIDE;
+    const bool active = threadIdx.x < npts;
+    unsigned s_bits = 0u;
+    int c = 0;
+    if (active) {
+        float4* dat = s_dat + threadIdx.x;
+        const int* jdx = s_idx + threadIdx.x;
         const V3 p = v3_load(pos + 3 * (size_t)i), n = v3_load(normal + 3 * (size_t)i);
         const V3 ex = v3_load(xb + 3 * (size_t)i), ey = v3_load(yb + 3 * (size_t)i);
-        const int c = cloud_of(cloud_ptr, B, i);
+        c = cloud_of(cloud_ptr, B, i);
         const float sc = kernel_width * __ldg(abar + c);
-        const float denom = sc * sc;
-        // pass 1, four gathers in flight
-        float wsum = 0.f;
-        int e = 0;
-        for (; e + 4 <= k; e += 4) {
+        const float nl2 = -1.4426950408889634f / (sc * sc);
+        // pass A, four gathers in flight
+        FitSums sums;
+        fit_sums_zero(sums);
+#pragma unroll 1
+        for (int e = 0; e < k; e += 4) {
             int j[4];
             V3 pj[4];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) { j[u] = sv.j(e + u); int jj = (j[u] < 0 || j[u] >= N) ? 0 : j[u]; pj[u] = v3_load(pos + 3 * (size_t)jj); }
+            for (int u = 0; u < 4; ++u)
+                if (e + u < k) {
+                    j[u] = jdx[(e + u) * STRIDE];
+                    const int jj = ((unsigned)j[u] >= (unsigned)N) ? 0 : j[u];
+                    pj[u] = v3_load(pos + 3 * (size_t)jj);
+                }
 #pragma unroll
-            for (int u = 0; u < 4; ++u) { float4 cc = fit_slot_coords_loaded(pj[u], p, n, ex, ey, denom); wsum += cc.z; sv.d(e + u) = cc; }
+            for (int u = 0; u < 4; ++u)
+                if (e + u < k) dat[(e + u) * STRIDE] = fit_slot_accumulate(pj[u], (unsigned)j[u] < (unsigned)N, p, n, ex, ey, nl2, sums);
         }
-        for (; e < k; ++e) { float4 cc = fit_slot_coords(pos, N, sv.j(e), p, n, ex, ey, denom); wsum += cc.z; sv.d(e) = cc; }
         float z1[6], z2[6], coef[6];
-        fit_pass2(N, k, wsum, fp, sv, z1, z2, coef);
-        if (!WRITE) {
-            float s_i = fit_row_norm(k, sv, z1, z2);
-            // s_i >= 0, so its bit pattern orders like the value: integer max is exact and
-            // order-independent (deterministic), replacing scatter_max (grad_div_mls.py:259)
-            atomicMax(S + c, __float_as_uint(s_i));
-        } else {
-            const float Sc = normalized ? __uint_as_float(S[c]) : 0.f;
-            float* dc_ = dbg_coords ? dbg_coords + (size_t)i * k * 2 : nullptr;
-            float* dw_ = dbg_weights ? dbg_weights + (size_t)i * k : nullptr;
-            float* dm_ = dbg_mapping ? dbg_mapping + (size_t)i * k * 4 : nullptr;
-            e = 0;
-            for (; e + 2 <= k; e += 2) {        // pass 3, neighbour frames of two slots in flight
-                int j[2];
-                V3 xj[2], yj[2];
+        const float inv_wnorm = fit_solve(sums, fp, z1, z2, coef);
+        // pass B, neighbour frames of four slots in flight
+        float* dc_ = DEBUG && dbg_coords ? dbg_coords + (size_t)i * k * 2 : nullptr;
+        float* dw_ = DEBUG && dbg_weights ? dbg_weights + (size_t)i * k : nullptr;
+        float* dm_ = DEBUG && dbg_mapping ? dbg_mapping + (size_t)i * k * 4 : nullptr;
+        float ax = 0.f, ay = 0.f;
+#pragma unroll 1
+        for (int e = 0; e < k; e += 4) {
+            V3 xj[4], yj[4];
 #pragma unroll
-                for (int u = 0; u < 2; ++u) {
-                    j[u] = sv.j(e + u);
-                    int jj = (j[u] < 0 || j[u] >= N) ? 0 : j[u];
+            for (int u = 0; u < 4; ++u)
+                if (e + u < k) {
+                    const int j = jdx[(e + u) * STRIDE];
+                    const int jj = ((unsigned)j >= (unsigned)N) ? 0 : j;
                     xj[u] = v3_load(xb + 3 * (size_t)jj); yj[u] = v3_load(yb + 3 * (size_t)jj);
                 }
 #pragma unroll
-                for (int u = 0; u < 2; ++u)
-                    sv.d(e + u) = fit_slot_entry_loaded(xj[u], yj[u], !(j[u] < 0 || j[u] >= N), sv.d(e + u), n, ex, ey, Sc, z1, z2, coef,
-                                                        dc_ ? dc_ + 2 * (e + u) : nullptr, dw_ ? dw_ + (e + u) : nullptr, dm_ ? dm_ + 4 * (e + u) : nullptr);
-            }
-            for (; e < k; ++e)
-                sv.d(e) = fit_slot_entry(xb, yb, N, sv.j(e), sv.d(e), n, ex, ey, Sc, z1, z2, coef, dc_ ? dc_ + 2 * e : nullptr,
-                                         dw_ ? dw_ + e : nullptr, dm_ ? dm_ + 4 * e : nullptr);
+            for (int u = 0; u < 4; ++u)
+                if (e + u < k) {
+                    const float4 out = fit_slot_entry(xj[u], yj[u], dat[(e + u) * STRIDE], n, ex, ey, z1, z2, coef, inv_wnorm,
+                                                      dc_ ? dc_ + 2 * (e + u) : nullptr, dw_ ? dw_ + (e + u) : nullptr,
+                                                      dm_ ? dm_ + 4 * (e + u) : nullptr);
+                    ax += fabsf(out.x); ay += fabsf(out.y);
+                    dat[(e + u) * STRIDE] = out;
+                }
+        }
+        s_bits = __float_as_uint(fit_row_norm(ax, ay));
+    }
+    if (normalized) {
+        // one atomic per warp when the warp lies inside one cloud (points are sorted by cloud), else one per thread
+        const int c_first = __shfl_sync(FULL, c, 0);
+        const bool uniform = __all_sync(FULL, !active || c == c_first);
+        if (uniform) {
+            const unsigned m = __reduce_max_sync(FULL, s_bits);
+            if ((threadIdx.x & 31) == 0 && active) atomicMax(S + c_first, m);
+        } else if (active) {
+            atomicMax(S + c, s_bits);
         }
     }
-    if (!WRITE) return;
     __syncthreads();
     // coalesced G / D tile stores (float2 per slot)
     float2* gG = reinterpret_cast<float2*>(G) + (size_t)base * k;
@@ -193,25 +212,66 @@ fit_kernel(const float* __restrict__ pos, const float* __restrict__ normal, cons
     }
 }
 
+// ---- the per-cloud normalisation (grad_div_mls.py:258-260, :271-272) -------------------------
+// Multiplies the entries of the points [lo, hi) by 1 / S_cloud, where lo / hi are the starts of the clouds that contain
+// points n0 / n1 (hi = N when n1 >= N): after the fit of the points [.., n1) exactly the clouds that END at or before n1 have
+// their final S.  With one launch per chunk of points this runs while the chunk's entries are still in L2.
+constexpr int SCALE_T = 256;
+constexpr int SCALE_PTS = 128;
+__global__ void __launch_bounds__(SCALE_T)
+scale_kernel(float* __restrict__ G, float* __restrict__ D, const int* __restrict__ cloud_ptr, int B, const unsigned* __restrict__ S,
+             int N, int k, int n0, int n1) {
+    __shared__ float s_scale[SCALE_PTS];
+    const int lo = n0 <= 0 ? 0 : __ldg(cloud_ptr + cloud_of(cloud_ptr, B, n0));
+    const int hi = n1 >= N ? N : __ldg(cloud_ptr + cloud_of(cloud_ptr, B, n1));
+    for (int base = lo + blockIdx.x * SCALE_PTS; base < hi; base += gridDim.x * SCALE_PTS) {
+        const int npts = min(SCALE_PTS, hi - base);
+        __syncthreads();
+        if (threadIdx.x < npts) s_scale[threadIdx.x] = fit_scale(__uint_as_float(__ldg(S + cloud_of(cloud_ptr, B, base + threadIdx.x))));
+        __syncthreads();
+        float2* gG = reinterpret_cast<float2*>(G) + (size_t)base * k;
+        float2* gD = reinterpret_cast<float2*>(D) + (size_t)base * k;
+        const int tile = npts * k;
+        for (int l = threadIdx.x, p = threadIdx.x / k, e = threadIdx.x % k; l < tile; l += SCALE_T) {
+            const float f = s_scale[p];
+            float2 g = gG[l], d = gD[l];
+            gG[l] = make_float2(g.x * f, g.y * f);
+            gD[l] = make_float2(d.x * f, d.y * f);
+            e += SCALE_T % k; p += SCALE_T / k;
+            if (e >= k) { e -= k; ++p; }
+        }
+    }
+}
+
 size_t fit_smem_bytes(int T, int k) { return (size_t)k * (T + 1) * (sizeof(float4) + sizeof(int)); }
 
-template <int T>
-int launch_fit(bool write, const float* pos, const float* normal, const float* xb, const float* yb, const int* idx,
-               const int* cloud_ptr, int B, int N, int k, float kernel_width, FitParams fp, int normalized,
-               const float* abar, unsigned* S, float* G, float* D, float* dc, float* dw, float* dm, cudaStream_t st) {
-    size_t smem = fit_smem_bytes(T, k);
-    int grid = dc_ceil_div(N, T);
-    if (write) {
-        DC_CUDA(cudaFuncSetAttribute(fit_kernel<T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        fit_kernel<T, true><<<grid, T, smem, st>>>(pos, normal, xb, yb, idx, cloud_ptr, B, N, k, kernel_width, fp,
-                                                    normalized, abar, S, G, D, dc, dw, dm);
-    } else {
-        DC_CUDA(cudaFuncSetAttribute(fit_kernel<T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        fit_kernel<T, false><<<grid, T, smem, st>>>(pos, normal, xb, yb, idx, cloud_ptr, B, N, k, kernel_width, fp,
-                                                     normalized, abar, S, G, D, dc, dw, dm);
-    }
+struct FitArgs {
+    const float *pos, *normal, *xb, *yb; const int *idx, *cloud_ptr; int B, N, k; float kernel_width; FitParams fp; int normalized;
+    const float* abar; unsigned* S; float *G, *D, *dc, *dw, *dm;
+};
+
+template <int T, int K, bool DEBUG>
+int launch_fit_one(const FitArgs& a, int n0, int n1, cudaStream_t st) {
+    const size_t smem = fit_smem_bytes(T, a.k);
+    DC_CUDA(cudaFuncSetAttribute(fit_kernel<T, K, DEBUG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    fit_kernel<T, K, DEBUG><<<dc_ceil_div(n1 - n0, T), T, smem, st>>>(a.pos, a.normal, a.xb, a.yb, a.idx, a.cloud_ptr, a.B, a.N, a.k, n0, n1,
+                                                                       a.kernel_width, a.fp, a.normalized, a.abar, a.S, a.G, a.D, a.dc, a.dw, a.dm);
     return dc_check_launch("dc_build_grad_div/fit");
 }
+
+template <int T>
+int launch_fit(const FitArgs& a, int n0, int n1, cudaStream_t st) {
+    if (a.dc || a.dw || a.dm) return launch_fit_one<T, 0, true>(a, n0, n1, st);
+    switch (a.k) {
+        case 10: return launch_fit_one<T, 10, false>(a, n0, n1, st);
+        case 20: return launch_fit_one<T, 20, false>(a, n0, n1, st);
+        case 30: return launch_fit_one<T, 30, false>(a, n0, n1, st);
+        case 40: return launch_fit_one<T, 40, false>(a, n0, n1, st);
+        default: return launch_fit_one<T, 0, false>(a, n0, n1, st);
+    }
+}
+
+int g_build_chunk_points = 0;      // tuning switch (dc_set_build_chunk): points per fit/scale chunk, 0 = automatic
 
 }  // namespace
 
@@ -246,10 +306,10 @@ extern "C" int dc_build_grad_div(const float* pos, const float* normal, const fl
                dc_build_ws_bytes(N, B));
     if (N <= 0) return DC_OK;
     cudaStream_t st = (cudaStream_t)stream;
-    size_t a = ((size_t)N * 4 + 255) / 256 * 256, b = ((size_t)B * 4 + 255) / 256 * 256;
+    const size_t m_bytes = ((size_t)N * 4 + 255) / 256 * 256, b_bytes = ((size_t)B * 4 + 255) / 256 * 256;
     float* m = (float*)ws;
-    float* abar = (float*)((char*)ws + a);
-    unsigned* S = (unsigned*)((char*)ws + a + b);
+    float* abar = (float*)((char*)ws + m_bytes);
+    unsigned* S = (unsigned*)((char*)ws + m_bytes + b_bytes);
     FitParams fp;
     fp.lam = lam; fp.lam_shape = lam_shape; fp.use_shape = use_shape;
 
@@ -257,17 +317,28 @@ extern "C" int dc_build_grad_div(const float* pos, const float* normal, const fl
     cloud_mean_kernel<<<B, CLOUD_MEAN_T, 0, st>>>(m, cloud_ptr, B, abar, S);
     int rc = dc_check_launch_n("dc_build_grad_div/mean", 2);
     if (rc) return rc;
+    FitArgs a = {pos, normal, xb, yb, idx, cloud_ptr, B, N, k, kernel_width, fp, normalized, abar, S, G, D, dbg_coords, dbg_weights, dbg_mapping};
     // threads per CTA: as many as keep two CTAs resident per SM (<= ~110 KB of shared memory each)
     const size_t budget = 110 * 1024;
-    for (int pass = normalized ? 0 : 1; pass < 2; ++pass) {
-        bool write = pass == 1;
-        if (fit_smem_bytes(128, k) <= budget)
-            rc = launch_fit<128>(write, pos, normal, xb, yb, idx, cloud_ptr, B, N, k, kernel_width, fp, normalized, abar, S, G, D, dbg_coords, dbg_weights, dbg_mapping, st);
-        else if (fit_smem_bytes(64, k) <= budget)
-            rc = launch_fit<64>(write, pos, normal, xb, yb, idx, cloud_ptr, B, N, k, kernel_width, fp, normalized, abar, S, G, D, dbg_coords, dbg_weights, dbg_mapping, st);
-        else
-            rc = launch_fit<32>(write, pos, normal, xb, yb, idx, cloud_ptr, B, N, k, kernel_width, fp, normalized, abar, S, G, D, dbg_coords, dbg_weights, dbg_mapping, st);
+    const int T = fit_smem_bytes(128, k) <= budget ? 128 : (fit_smem_bytes(64, k) <= budget ? 64 : 32);
+    // Chunks of points: the fit of a chunk is followed at once by the normalisation of the clouds it completed, while their
+    // 16 k bytes per point are still in L2 (a chunk's entries + inputs stay below ~40 MB); small batches are one chunk.
+    long long chunk = g_build_chunk_points > 0 ? g_build_chunk_points : (32ll << 20) / (16ll * k);
+    chunk = (chunk + T - 1) / T * T;
+    if (!normalized || chunk > N) chunk = N;
+    for (long long n0 = 0; n0 < N; n0 += chunk) {
+        const int n1 = (int)(n0 + chunk < N ? n0 + chunk : N);
+        if (T == 128) rc = launch_fit<128>(a, (int)n0, n1, st);
+        else if (T == 64) rc = launch_fit<64>(a, (int)n0, n1, st);
+        else rc = launch_fit<32>(a, (int)n0, n1, st);
         if (rc) return rc;
+        if (normalized) {
+            const int tiles = dc_ceil_div(n1 - (int)n0, SCALE_PTS) + 1;
+            const int cap = dc_sm_count() * 8;
+            scale_kernel<<<tiles < cap ? tiles : cap, SCALE_T, 0, st>>>(G, D, cloud_ptr, B, S, N, k, (int)n0, n1);
+            rc = dc_check_launch("dc_build_grad_div/scale");
+            if (rc) return rc;
+        }
     }
     return DC_OK;
 }
@@ -293,6 +364,9 @@ extern "C" int dc_build_grad_div(const float* pos, const float* normal, const fl
 //
 // First call on each GPU: the array's device address is looked up once (cudaGetSymbolAddress, with
 // that GPU current) and cached.  Make that first call outside of any stream capture.
+//
+// Which GPU: the one that is current when the call is made; its array is used.  The buffers and the stream must belong to
+// that GPU (checked on the output buffer).
 #include <mutex>
 
 #define DC_STATIC_MAX_POINTS 262144
@@ -302,6 +376,9 @@ extern "C" int dc_build_grad_div(const float* pos, const float* normal, const fl
 
 // In host code this name is only a handle for cudaGetSymbolAddress, never a device pointer.
 static __device__ __align__(256) unsigned char g_build_scratch[DC_STATIC_SCRATCH_BYTES];
+
+// tuning switch: points per fit/normalise chunk (0 = automatic: 32 MB of entries)
+extern "C" int dc_set_build_chunk(int points) { g_build_chunk_points = points; return DC_OK; }
 
 extern "C" int dc_build_static_max_points(void) { return DC_STATIC_MAX_POINTS; }
 extern "C" int dc_build_static_max_clouds(void) { return DC_STATIC_MAX_CLOUDS; }
@@ -323,6 +400,13 @@ extern "C" int dc_build_grad_div_static(const float* pos, const float* normal, c
     int dev = -1;
     DC_CUDA(cudaGetDevice(&dev));
     DC_REQUIRE(dev >= 0 && dev < kMaxDevices, "dc_build_grad_div_static: device ordinal %d not supported", dev);
+    // The built-in array used is the CURRENT device's.  A caller whose buffers (and stream) belong to another GPU would get
+    // that GPU's kernels pointed at this GPU's array: refuse instead.
+    cudaPointerAttributes where;
+    DC_CUDA(cudaPointerGetAttributes(&where, G));
+    DC_REQUIRE(where.type != cudaMemoryTypeDevice || where.device == dev,
+               "dc_build_grad_div_static: the output buffer lives on device %d but device %d is current; make the buffers' "
+               "device current before the call", where.device, dev);
     void* scratch = nullptr;
     {
         std::lock_guard<std::mutex> lock(mu);

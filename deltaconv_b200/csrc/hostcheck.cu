@@ -42,7 +42,8 @@ extern "C" void hc_estimate_basis(const float* pos, const int* idx, int N, int k
     }
 }
 
-// Mirrors dc_build_grad_div's kernel sequence on the host (same passes, same per-point code).
+// Mirrors dc_build_grad_div's kernel sequence on the host (same passes, same per-point code): means, one fit pass that
+// writes un-normalised entries and the per-cloud maxima, then the per-cloud scale.
 extern "C" void hc_build_grad_div(const float* pos, const float* normal, const float* xb, const float* yb,
                                   const int* idx, const int* cloud_ptr, int B, int N, int k, float kernel_width,
                                   float lam, float lam_shape, int use_shape, int normalized, float* G, float* D,
@@ -66,33 +67,42 @@ extern "C" void hc_build_grad_div(const float* pos, const float* normal, const f
         abar[c] = (float)(acc / (cnt > 0 ? cnt : 1));
     }
     FitParams fp; fp.lam = lam; fp.lam_shape = lam_shape; fp.use_shape = use_shape;
-    std::vector<int> sidx(k);
     std::vector<float4> sdat(k);
-    for (int pass = normalized ? 0 : 1; pass < 2; ++pass) {
-        int c = 0;
-        for (int i = 0; i < N; ++i) {
-            while (cloud_ptr[c + 1] <= i) ++c;
-            for (int e = 0; e < k; ++e) sidx[e] = idx[(size_t)i * k + e];
-            SlotView sv; sv.idx = sidx.data(); sv.dat = sdat.data(); sv.stride = 1;
-            V3 p = v3_load(pos + 3 * i), n = v3_load(normal + 3 * i), ex = v3_load(xb + 3 * i), ey = v3_load(yb + 3 * i);
-            float sc = kernel_width * abar[c];
-            float wsum = fit_pass1(pos, N, i, k, p, n, ex, ey, sc * sc, sv);
-            float z1[6], z2[6], coef[6];
-            fit_pass2(N, k, wsum, fp, sv, z1, z2, coef);
-            if (pass == 0) {
-                float s = fit_row_norm(k, sv, z1, z2);
-                if (s > S[c]) S[c] = s;
-            } else {
-                fit_pass3(xb, yb, N, k, n, ex, ey, normalized ? S[c] : 0.f, sv, z1, z2, coef,
-                          dbg_coords ? dbg_coords + (size_t)i * k * 2 : nullptr,
-                          dbg_weights ? dbg_weights + (size_t)i * k : nullptr,
-                          dbg_mapping ? dbg_mapping + (size_t)i * k * 4 : nullptr);
-                for (int e = 0; e < k; ++e) {
-                    float4 v = sdat[e];
-                    G[((size_t)i * k + e) * 2] = v.x; G[((size_t)i * k + e) * 2 + 1] = v.y;
-                    D[((size_t)i * k + e) * 2] = v.z; D[((size_t)i * k + e) * 2 + 1] = v.w;
-                }
-            }
+    int c = 0;
+    for (int i = 0; i < N; ++i) {
+        while (cloud_ptr[c + 1] <= i) ++c;
+        V3 p = v3_load(pos + 3 * i), n = v3_load(normal + 3 * i), ex = v3_load(xb + 3 * i), ey = v3_load(yb + 3 * i);
+        float sc = kernel_width * abar[c];
+        float nl2 = -1.4426950408889634f / (sc * sc);
+        FitSums sums;
+        fit_sums_zero(sums);
+        for (int e = 0; e < k; ++e) {
+            int j = idx[(size_t)i * k + e];
+            bool valid = !(j < 0 || j >= N);
+            sdat[e] = fit_slot_accumulate(v3_load(pos + 3 * (valid ? j : 0)), valid, p, n, ex, ey, nl2, sums);
         }
+        float z1[6], z2[6], coef[6];
+        float inv_wnorm = fit_solve(sums, fp, z1, z2, coef);
+        float ax = 0.f, ay = 0.f;
+        for (int e = 0; e < k; ++e) {
+            int j = idx[(size_t)i * k + e];
+            int jj = (j < 0 || j >= N) ? 0 : j;
+            float4 v = fit_slot_entry(v3_load(xb + 3 * jj), v3_load(yb + 3 * jj), sdat[e], n, ex, ey, z1, z2, coef, inv_wnorm,
+                                      dbg_coords ? dbg_coords + ((size_t)i * k + e) * 2 : nullptr,
+                                      dbg_weights ? dbg_weights + (size_t)i * k + e : nullptr,
+                                      dbg_mapping ? dbg_mapping + ((size_t)i * k + e) * 4 : nullptr);
+            ax += fabsf(v.x); ay += fabsf(v.y);
+            G[((size_t)i * k + e) * 2] = v.x; G[((size_t)i * k + e) * 2 + 1] = v.y;
+            D[((size_t)i * k + e) * 2] = v.z; D[((size_t)i * k + e) * 2 + 1] = v.w;
+        }
+        float s = fit_row_norm(ax, ay);
+        if (s > S[c]) S[c] = s;
+    }
+    if (!normalized) return;
+    c = 0;
+    for (int i = 0; i < N; ++i) {
+        while (cloud_ptr[c + 1] <= i) ++c;
+        float f = fit_scale(S[c]);
+        for (int e = 0; e < 2 * k; ++e) { G[(size_t)i * k * 2 + e] *= f; D[(size_t)i * k * 2 + e] *= f; }
     }
 }

@@ -66,6 +66,28 @@ __device__ __forceinline__ u64 list_merge32(u64 list, u64 key, int lane) {
     return m;
 }
 
+// The same for the 64-entry list of 32 < k <= 64 (two keys per lane, position = slot * 32 + lane): sort the 32 candidates
+// (15 steps); the 64 smallest of list ∪ candidates are (slot 0, min(slot 1, reversed candidates)) — the candidates padded
+// with +inf to 64 and reversed only meet the upper half — which is a bitonic sequence of 64: one register-level
+// compare-exchange between the two slots (stride 32), then 5 cross-lane steps on each slot.
+__device__ __forceinline__ void list_merge64(u64 (&keys)[2], u64 key, int lane) {
+#pragma unroll
+    for (int size = 2; size <= 32; size <<= 1)
+#pragma unroll
+        for (int stride = size >> 1; stride > 0; stride >>= 1)
+            key = bitonic_step(key, lane, stride, size == 32 || (lane & size) == 0);
+    const u64 rev = __shfl_sync(FULL, key, 31 - lane);
+    const u64 upper = keys[1] < rev ? keys[1] : rev;
+    u64 lo = keys[0] < upper ? keys[0] : upper, hi = keys[0] < upper ? upper : keys[0];
+#pragma unroll
+    for (int stride = 16; stride > 0; stride >>= 1) {
+        lo = bitonic_step(lo, lane, stride, true);
+        hi = bitonic_step(hi, lane, stride, true);
+    }
+    keys[0] = lo;
+    keys[1] = hi;
+}
+
 constexpr int KNN_MERGE_MIN = 12;     // survivors in a round from which the merge is cheaper than single insertions (5 / 8 / 12 / 16 / 24 measured: 12 is best)
 
 
@@ -73,8 +95,9 @@ constexpr int KNN_MERGE_MIN = 12;     // survivors in a round from which the mer
 template <int SLOTS>
 __device__ __forceinline__ void list_offer(u64 (&keys)[SLOTS], u64& tau, int k, int lane, u64 key) {
     unsigned mask = __ballot_sync(FULL, key < tau);
-    if (SLOTS == 1 && __popc(mask) >= KNN_MERGE_MIN) {
-        keys[0] = list_merge32(keys[0], key, lane);
+    if (SLOTS <= 2 && __popc(mask) >= KNN_MERGE_MIN) {
+        if constexpr (SLOTS == 1) keys[0] = list_merge32(keys[0], key, lane);
+        else if constexpr (SLOTS == 2) list_merge64(keys, key, lane);
         tau = list_get<SLOTS>(keys, k - 1);
         return;
     }

@@ -36,34 +36,51 @@ __global__ void sum1_finalize_kernel(const double* __restrict__ partial, int chu
 }
 
 // ---- BatchNorm statistics ------------------------------------------------------------------
-struct PlainVal {      // x and x^2 of a [M,C] matrix
+// Sums are taken around a per-column pivot (the column's value in row 0): s = sum(x - p), s2 = sum((x - p)^2), so that
+// mean = p + s / M and var = s2 / M - (s / M)^2 do not cancel when |mean| >> std (squares of the raw values, rounded to fp32
+// before the fp64 accumulation, would lose the variance's digits there).
+struct Pivot4 { float p[4]; };
+struct PlainVal {      // (x - p) and (x - p)^2 of a [M,C] matrix
     const float* x; long long ld;
-    __device__ void operator()(long long r, int c, float (&o)[2]) const { float v = __ldg(x + r * ld + c); o[0] = v; o[1] = v * v; }
-    __device__ NoColumns columns(int) const { return NoColumns(); }
-    __device__ void quad(long long r, int c, const NoColumns&, float (&o)[4][2]) const {
+    __device__ float pivot(int c) const { return __ldg(x + c); }
+    __device__ void operator()(long long r, int c, float (&o)[2]) const { float v = __ldg(x + r * ld + c) - pivot(c); o[0] = v; o[1] = v * v; }
+    __device__ Pivot4 columns(int c) const {
+        const float4 q = __ldg((const float4*)(x + c));
+        Pivot4 k; k.p[0] = q.x; k.p[1] = q.y; k.p[2] = q.z; k.p[3] = q.w; return k;
+    }
+    __device__ void quad(long long r, int c, const Pivot4& k, float (&o)[4][2]) const {
         const float4 q = __ldg((const float4*)(x + r * ld + c));
-        o[0][0] = q.x; o[0][1] = q.x * q.x; o[1][0] = q.y; o[1][1] = q.y * q.y; o[2][0] = q.z; o[2][1] = q.z * q.z; o[3][0] = q.w; o[3][1] = q.w * q.w;
+        const float d[4] = {q.x - k.p[0], q.y - k.p[1], q.z - k.p[2], q.w - k.p[3]};
+#pragma unroll
+        for (int u = 0; u < 4; ++u) { o[u][0] = d[u]; o[u][1] = d[u] * d[u]; }
     }
 };
-struct NormVal {       // |v| and |v|^2 of a [2M,C] vector field (nonlin.py:68)
+struct NormVal {       // the same for |v| of a [2M,C] vector field (nonlin.py:68)
     const float* x; long long ld;
+    __device__ float pivot(int c) const { float a = __ldg(x + c), b = __ldg(x + ld + c); return sqrtf(a * a + b * b); }
     __device__ void operator()(long long r, int c, float (&o)[2]) const {
         float a = __ldg(x + (2 * r) * ld + c), b = __ldg(x + (2 * r + 1) * ld + c);
-        float n2 = a * a + b * b;
-        o[0] = sqrtf(n2); o[1] = n2;
+        float d = sqrtf(a * a + b * b) - pivot(c);
+        o[0] = d; o[1] = d * d;
     }
-    __device__ NoColumns columns(int) const { return NoColumns(); }
-    __device__ void quad(long long r, int c, const NoColumns&, float (&o)[4][2]) const {
+    __device__ Pivot4 columns(int c) const {
+        Pivot4 k;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) k.p[u] = pivot(c + u);
+        return k;
+    }
+    __device__ void quad(long long r, int c, const Pivot4& k, float (&o)[4][2]) const {
         const float4 a = __ldg((const float4*)(x + (2 * r) * ld + c)), b = __ldg((const float4*)(x + (2 * r + 1) * ld + c));
         const float aa[4] = {a.x, a.y, a.z, a.w}, bb[4] = {b.x, b.y, b.z, b.w};
 #pragma unroll
-        for (int u = 0; u < 4; ++u) { const float n2 = aa[u] * aa[u] + bb[u] * bb[u]; o[u][0] = sqrtf(n2); o[u][1] = n2; }
+        for (int u = 0; u < 4; ++u) { const float d = sqrtf(aa[u] * aa[u] + bb[u] * bb[u]) - k.p[u]; o[u][0] = d; o[u][1] = d * d; }
     }
 };
 
 // mean / biased variance -> (mean, invstd); running stats updated like torch.nn.BatchNorm1d
 // (momentum, unbiased variance).  One thread per column, partials added in chunk order.
-__global__ void bn_finalize_kernel(const double* __restrict__ partial, int chunks, long long M, int C, float eps,
+template <class F>
+__global__ void bn_finalize_kernel(F f, const double* __restrict__ partial, int chunks, long long M, int C, float eps,
                                    float momentum, float* __restrict__ mean, float* __restrict__ invstd,
                                    float* __restrict__ running_mean, float* __restrict__ running_var,
                                    long long* __restrict__ num_batches_tracked) {
@@ -72,9 +89,10 @@ __global__ void bn_finalize_kernel(const double* __restrict__ partial, int chunk
     if (!finalize_sums<2>(partial, chunks, C, r)) return;
     const int c = finalize_column();
     double s = r[0], s2 = r[1];
-    double mu = s / (double)M;
-    double var = s2 / (double)M - mu * mu;
+    double shifted = s / (double)M;                       // mean of (x - pivot)
+    double var = s2 / (double)M - shifted * shifted;
     if (var < 0.0) var = 0.0;
+    double mu = (double)f.pivot(c) + shifted;
     mean[c] = (float)mu;
     invstd[c] = (float)(1.0 / sqrt(var + (double)eps));
     if (running_mean) {
@@ -868,9 +886,16 @@ extern "C" int dc_bn_stats(const float* x, int64_t ldx, int64_t M, int C, int mo
     double* partial = (double*)ws;
     const bool vec4_ok = ldx % 4 == 0 && all_aligned16(x);
     int chunks;
-    if (mode == 0) { PlainVal f = {x, ldx}; chunks = col_reduce_launch<2>(f, M, C, vec4_ok, partial, st); }
-    else { NormVal f = {x, ldx}; chunks = col_reduce_launch<2>(f, M, C, vec4_ok, partial, st); }
-    bn_finalize_kernel<<<dc_ceil_div(C, FIN_COLS), FIN_T, 0, st>>>(partial, chunks, M, C, eps, momentum, mean, invstd,
+    if (mode == 0) {
+        PlainVal f = {x, ldx};
+        chunks = col_reduce_launch<2>(f, M, C, vec4_ok, partial, st);
+        bn_finalize_kernel<<<dc_ceil_div(C, FIN_COLS), FIN_T, 0, st>>>(f, partial, chunks, M, C, eps, momentum, mean, invstd,
+                                                                        running_mean_or_null, running_var_or_null, (long long*)num_batches_tracked_or_null);
+        return dc_check_launch_n("dc_bn_stats", 2);
+    }
+    NormVal f = {x, ldx};
+    chunks = col_reduce_launch<2>(f, M, C, vec4_ok, partial, st);
+    bn_finalize_kernel<<<dc_ceil_div(C, FIN_COLS), FIN_T, 0, st>>>(f, partial, chunks, M, C, eps, momentum, mean, invstd,
                                                             running_mean_or_null, running_var_or_null,
                                                             (long long*)num_batches_tracked_or_null);
     return dc_check_launch_n("dc_bn_stats", 2);

@@ -8,8 +8,12 @@ models use.  The reference's intermediate helpers (`coords_projected`, `gaussian
 import torch
 
 from .. import ops
+# the reference defines its four intermediate helpers in this module (grad_div_mls.py:72-194) and its tests reach them
+# through `from deltaconv.geometry.grad_div_mls import *`
+from .helpers import coords_projected, gaussian_weights, weighted_least_squares, fit_vector_mapping   # noqa: F401
 
-__all__ = ['estimate_basis', 'build_tangent_basis', 'build_grad_div', 'operator_parts']
+__all__ = ['estimate_basis', 'build_tangent_basis', 'build_grad_div', 'operator_parts',
+           'coords_projected', 'gaussian_weights', 'weighted_least_squares', 'fit_vector_mapping']
 
 
 def estimate_basis(pos, edge_index, k=None, orientation=None):

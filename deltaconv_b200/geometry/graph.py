@@ -15,14 +15,21 @@ def knn_graph(x, k, batch=None, loop=False, flow='source_to_target', num_clouds=
     if loop:
         graph = ops.knn(x, k, batch, num_clouds, max_points=max_points)
         ei = graph.edge_index()
-    else:                                   # drop the self slot of a (k+1)-graph
+    else:
+        # (k+1)-graph minus the self edge.  torch_cluster removes self BY INDEX: with coincident points slot 0 is the lowest
+        # index among the d2 = 0 ties, not necessarily the query, so the slot to drop is the one holding the row's own index
+        # (the last slot if self is absent, which only happens when more than k coincident points precede it)
         wide = ops.knn(x, k + 1, batch, num_clouds, want_edge_index=False, max_points=max_points)
-        idx = wide.idx[:, 1:].contiguous()
+        own = wide.idx == torch.arange(wide.N, device=wide.idx.device, dtype=wide.idx.dtype)[:, None]
+        drop = torch.where(own.any(1), own.to(torch.int8).argmax(1), torch.full_like(own[:, 0], k, dtype=torch.long))
+        slots = torch.arange(k, device=wide.idx.device)[None, :]
+        idx = wide.idx.gather(1, slots + (slots >= drop[:, None]).long()).contiguous()
         graph = ops.EllGraph(idx, wide.cloud_ptr, wide.B, wide.max_cloud)
         ei = graph.edge_index()
     if flow == 'source_to_target':
-        flipped = ei.flip(0).contiguous()
-        return flipped
+        # row 0 = neighbours, row 1 = centres.  No ELL graph rides on this tensor: the DeltaConv entry points expect the
+        # target_to_source layout and ops.graph_of() refuses (or DeltaConv goes generic on) anything else.
+        return ei.flip(0).contiguous()
     return ei
 
 

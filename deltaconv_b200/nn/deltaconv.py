@@ -26,11 +26,15 @@ class DeltaConv(torch.nn.Module):
         self.v_mlp = VectorMLP([in_channels * 4 + out_channels * 2] + [out_channels] * depth) if vector else None
 
     def forward(self, x, v, grad, div, edge_index):
-        if not (isinstance(grad, ops.EllOperator) and isinstance(div, ops.EllOperator)):
-            raise TypeError("DeltaConv expects the grad/div operators returned by deltaconv_b200's build_grad_div")
-        if self.aggr != 'max':
-            raise NotImplementedError("DeltaConv: the CUDA path implements aggr='max' (every shipped model's setting)")
-        graph = ops.graph_of(edge_index, x.size(0)) if edge_index is not None else grad.graph
+        ell = isinstance(grad, ops.EllOperator) and isinstance(div, ops.EllOperator)
+        graph = None
+        if ell and self.aggr == 'max':
+            graph = ops.graph_of(edge_index, x.size(0), strict=False) if edge_index is not None else grad.graph
+        if graph is None:
+            # anything the fused schedule does not cover — another aggregation (deltaconv.py:35,52,54 pass `aggr` to
+            # torch_scatter), an edge_index that is not a fixed-k graph, operators that only support `@` — takes the
+            # reference's own formulation step by step (correct, not fast; no shipped model comes here)
+            return self._forward_generic(x, v, grad, div, edge_index if edge_index is not None else grad.graph.edge_index())
 
         # scalar stream (deltaconv.py:50-59)
         if self.centralized:
@@ -56,5 +60,38 @@ class DeltaConv(torch.nn.Module):
                 v = block(v)
         return x, v
 
+    def _forward_generic(self, x, v, grad, div, edge_index):
+        """deltaconv.py:44-70 literally: gather, MLP, scatter-reduce; operators through `@`.  The Linear / BatchNorm /
+        VectorNonLin modules still run in the CUDA library; gathers, scatter-reduce and concatenations are torch device ops."""
+        from ..geometry.operators import I_J, curl, hodge_laplacian, norm
+        if self.aggr not in ('max', 'min', 'sum', 'add', 'mean'):
+            raise ValueError(f"DeltaConv: unknown aggr '{self.aggr}'")
+        N = x.size(0)
+        row, col = edge_index[0], edge_index[1]
+        keep = (col >= 0) & (col < N)                       # the padding sentinel of clouds with fewer than k points
+        row, col = row[keep], col[keep]
+        if self.centralized:
+            feat = self.s_mlp_max(x[col] - x[row])
+        else:
+            feat = self.s_mlp_max(x)[col]
+        x_max = _scatter_rows(feat, row, N, self.aggr)
+        x = x_max + self.s_mlp(torch.cat([x, div @ v, curl(v, div), norm(v)], dim=1))
+        if self.v_mlp is not None:
+            v = self.v_mlp(I_J(torch.cat([v, hodge_laplacian(v, grad, div), grad @ x], dim=1)))
+        return x, v
+
     def __repr__(self):
         return f'{self.__class__.__name__}({self.in_channels}, {self.out_channels})'
+
+
+def _scatter_rows(src, index, num_rows, aggr):
+    """torch_scatter.scatter(src, index, dim=0, reduce=aggr) with its conventions: empty groups give 0, mean divides by the
+    group size."""
+    out = src.new_zeros(num_rows, src.size(1))
+    expand = index[:, None].expand_as(src)
+    if aggr in ('sum', 'add'):
+        return out.index_add(0, index, src)
+    if aggr == 'mean':
+        count = torch.bincount(index, minlength=num_rows).clamp(min=1).to(src.dtype)
+        return out.index_add(0, index, src) / count[:, None]
+    return out.scatter_reduce(0, expand, src, reduce='amax' if aggr == 'max' else 'amin', include_self=False)

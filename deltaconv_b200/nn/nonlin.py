@@ -47,7 +47,14 @@ class VectorNonLin(torch.nn.Module):
 
     def forward(self, x: Tensor) -> Tensor:
         if not isinstance(self.nonlin, torch.nn.ReLU):
-            raise NotImplementedError("VectorNonLin: the CUDA kernel implements nonlin=ReLU (the reference's only use)")
+            # any other activation (nonlin.py:48,78): the formula step by step — BatchNorm through the library, the rest as
+            # torch device ops.  The fused kernel covers ReLU, the reference's own and only setting.
+            rows, C = x.shape
+            xv = x.view(-1, 2, C)
+            n = torch.linalg.norm(xv, dim=1)
+            shifted = self.batchnorm(n) if self.batchnorm is not None else n + self.bias[None, :]
+            gain = self.nonlin(shifted) / n.clamp(min=1e-8)
+            return (xv * gain[:, None, :]).reshape(rows, C)
         bn = self.batchnorm.bn if self.batchnorm is not None else None
         return ops.vec_nonlin(x, self.bias, bn)
 

@@ -5,6 +5,8 @@ current stream and the autograd tape; all arithmetic happens in the library.
 Every function here requires contiguous fp32 CUDA tensors and raises otherwise — there is no
 CPU or eager-PyTorch fallback.
 """
+import os
+
 import torch
 
 from . import _lib
@@ -13,6 +15,7 @@ from ._lib import call, ptr, query, rows_ld
 _F32, _I32, _I64 = torch.float32, torch.int32, torch.int64
 
 _workspaces = {}
+_CHECK_LAYOUT = bool(int(os.environ.get('DC_CHECK_LAYOUT', '0')))
 
 
 def workspace(nbytes, device):
@@ -56,21 +59,29 @@ def _mat(t, name='tensor'):
 def cloud_layout(batch, num_points, device, num_clouds=None, max_points=None):
     """(cloud_ptr int32 [B+1], B, size of the largest cloud) for a sorted PyG batch vector; cached on the
     tensor object.  `batch=None` means one cloud.  Without the hints the two integers are read back from
-    the device (one sync, as the reference's scatter calls do)."""
+    the device (one sync, as the reference's scatter calls do).
+
+    Contract of the cache and the hints: the entry is keyed on the tensor's in-place version counter, so writing a new
+    layout into the same `batch` tensor through torch (copy_, index assignment, ...) invalidates it.  Under CUDA-graph replay
+    nothing is recomputed at all: every replayed batch must have the captured layout (GraphedTrainStep / GraphedInference).
+    `num_clouds` / `max_points` are trusted when given: `num_clouds` must equal batch[-1] + 1 and `max_points` must bound the
+    largest cloud (a smaller `num_clouds` silently drops clouds).  Set DC_CHECK_LAYOUT=1 to verify `num_clouds` (one sync)."""
     if batch is None:
         return torch.tensor([0, num_points], dtype=_I32, device=device), 1, num_points
     cached = getattr(batch, '_dc_cloud', None)
-    if cached is not None and cached[3] == num_points:
+    if cached is not None and cached[3] == num_points and cached[4] == batch._version:
         return cached[0], cached[1], cached[2]
     if not batch.is_cuda or batch.dtype != _I64:
         raise _lib.DeltaConvLibraryError("batch must be an int64 CUDA tensor")
     batch = batch.contiguous()
     B = int(num_clouds) if num_clouds is not None else (int(batch[-1].item()) + 1 if num_points else 1)
+    if num_clouds is not None and num_points and _CHECK_LAYOUT and int(batch[-1].item()) + 1 != B:
+        raise _lib.DeltaConvLibraryError(f"cloud_layout: num_clouds={B} but batch[-1] + 1 = {int(batch[-1].item()) + 1}")
     cp = torch.empty(B + 1, dtype=_I32, device=device)
     call('dc_cloud_ptr', ptr(batch), num_points, B, ptr(cp))
     maxp = int(max_points) if max_points is not None else (int((cp[1:] - cp[:-1]).max().item()) if num_points else 0)
     try:
-        batch._dc_cloud = (cp, B, maxp, num_points)
+        batch._dc_cloud = (cp, B, maxp, num_points, batch._version)
     except Exception:
         pass
     return cp, B, maxp
@@ -198,10 +209,11 @@ def geodesic_fps(pos, n_samples, batch=None, num_clouds=None, start=None, max_po
     return (samples, dist) if return_dist else samples
 
 
-def graph_of(edge_index, num_points):
+def graph_of(edge_index, num_points, strict=True):
     """EllGraph behind a [2,E] int64 edge_index: the one `knn_graph` attached, else a conversion
     under the reference's own assumption (rows grouped by centre, same k everywhere —
-    grad_div_mls.py:24-25,224)."""
+    grad_div_mls.py:24-25,224).  A graph that does not have that form raises, or returns None with strict=False
+    (DeltaConv then takes its generic path)."""
     if isinstance(edge_index, EllGraph):
         return edge_index
     g = getattr(edge_index, '_dc_graph', None)
@@ -213,9 +225,19 @@ def graph_of(edge_index, num_points):
         raise _lib.DeltaConvLibraryError("edge_index must be a [2,E] int64 CUDA tensor")
     E = edge_index.size(1)
     if num_points == 0 or E % num_points:
+        if not strict:
+            return None
         raise _lib.DeltaConvLibraryError(f"edge_index with {E} edges is not a fixed-k graph on {num_points} points")
     k = E // num_points
     ei = edge_index.contiguous()
+    # row 0 must hold the centres, grouped: point i owns edges [i*k, (i+1)*k).  (A `source_to_target` graph, or any other
+    # layout, would otherwise be read as a degenerate ELL without complaint.)
+    centres = torch.arange(num_points, device=ei.device).repeat_interleave(k)
+    if not torch.equal(ei[0], centres):
+        if not strict:
+            return None
+        raise _lib.DeltaConvLibraryError("edge_index is not grouped by centre with the same k for every point "
+                                         "(expected flow='target_to_source' kNN layout, grad_div_mls.py:24-25)")
     idx = torch.empty(num_points, k, dtype=_I32, device=ei.device)
     call('dc_ell_from_edge_index', ptr(ei), num_points, k, ptr(idx))
     g = EllGraph(idx)

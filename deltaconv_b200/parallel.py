@@ -109,6 +109,16 @@ class FlatSGD(torch.optim.Optimizer):
         self._buf = torch.zeros_like(self._p)
         self._lr = torch.empty(1, dtype=torch.float32, device=self._p.device)
         self._live = live
+        self._apply_pending()
+
+    def _apply_pending(self):
+        """State loaded before the flat buffers existed (the usual resume order: build, load_state_dict, train)."""
+        state, self._pending_state = getattr(self, '_pending_state', None), None
+        if state is not None and state.get('momentum_buffer') is not None:
+            if state['momentum_buffer'].numel() != self._buf.numel():
+                raise ValueError(f"FlatSGD.load_state_dict: momentum buffer has {state['momentum_buffer'].numel()} elements, "
+                                 f"the parameters with gradients have {self._buf.numel()}")
+            self._buf.copy_(state['momentum_buffer'])
 
     def sync_lr(self):
         lr = float(self.param_groups[0]['lr'])
@@ -147,8 +157,11 @@ class FlatSGD(torch.optim.Optimizer):
 
     def load_state_dict(self, state):
         self.param_groups[0].update(state['param_groups'][0])
-        if state.get('momentum_buffer') is not None and self._buf is not None:
-            self._buf.copy_(state['momentum_buffer'])
+        if self._buf is None:
+            self._pending_state = state          # applied when the first step() creates the flat buffers
+        else:
+            self._pending_state = state
+            self._apply_pending()
 
 
 class FlatAdam(FlatSGD):
@@ -175,9 +188,7 @@ class FlatAdam(FlatSGD):
                 loss = closure()
         g = self.flat.flat if self.flat.packed else self.flat.pack()
         if self._live is None:
-            self._materialise()
-            self._v = torch.zeros_like(self._p)
-            self._step = torch.zeros(1, dtype=torch.int32, device=self._p.device)
+            self._materialise()          # creates the moment buffers and applies a state loaded before the first step
         if g.numel() != self._p.numel():
             raise DeltaConvLibraryError("FlatAdam: the set of parameters with gradients changed between steps")
         self.sync_lr()
@@ -191,7 +202,15 @@ class FlatAdam(FlatSGD):
                     exp_avg=None if self._buf is None else self._buf.clone(), exp_avg_sq=None if self._v is None else self._v.clone(),
                     step=None if self._step is None else int(self._step))
 
-    def load_state_dict(self, state):
-        self.param_groups[0].update(state['param_groups'][0])
-        if state.get('exp_avg') is not None and self._buf is not None:
-            self._buf.copy_(state['exp_avg']); self._v.copy_(state['exp_avg_sq']); self._step.fill_(int(state['step']))
+    def _apply_pending(self):
+        if self._v is None:
+            self._v = torch.zeros_like(self._p)
+            self._step = torch.zeros(1, dtype=torch.int32, device=self._p.device)
+        state, self._pending_state = getattr(self, '_pending_state', None), None
+        if state is not None and state.get('exp_avg') is not None:
+            if state['exp_avg'].numel() != self._buf.numel():
+                raise ValueError(f"FlatAdam.load_state_dict: state has {state['exp_avg'].numel()} elements, "
+                                 f"the parameters with gradients have {self._buf.numel()}")
+            self._buf.copy_(state['exp_avg'])
+            self._v.copy_(state['exp_avg_sq'])
+            self._step.fill_(int(state['step']))

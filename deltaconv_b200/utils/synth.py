@@ -39,3 +39,27 @@ def synthetic_batch(num_clouds, points, config=2, rank=0, normals=True, num_clas
         cat = torch.randint(0, categories, (len(sizes),), generator=gen)
         fields['category'] = torch.nn.functional.one_hot(cat, categories).float()
     return Data(**fields)
+
+
+def synthetic_mesh(label, gen, subdivisions=3):
+    """A closed triangle mesh whose shape depends on `label`: a subdivided octahedron pushed onto an ellipsoid.  Stands in for
+    a dataset shape (`pos` [V,3], `face` [3,F], `y` [1]) wherever the reference's mesh datasets would be read."""
+    v = [(1, 0, 0), (-1, 0, 0), (0, 1, 0), (0, -1, 0), (0, 0, 1), (0, 0, -1)]
+    f = [(0, 2, 4), (2, 1, 4), (1, 3, 4), (3, 0, 4), (2, 0, 5), (1, 2, 5), (3, 1, 5), (0, 3, 5)]
+    for _ in range(subdivisions):
+        mid, nf = {}, []
+
+        def m(a, b):
+            key = (min(a, b), max(a, b))
+            if key not in mid:
+                v.append(tuple((v[a][i] + v[b][i]) / 2 for i in range(3)))
+                mid[key] = len(v) - 1
+            return mid[key]
+        for a, b, c in f:
+            ab, bc, ca = m(a, b), m(b, c), m(c, a)
+            nf += [(a, ab, ca), (ab, b, bc), (ca, bc, c), (ab, bc, ca)]
+        f = nf
+    pos = torch.tensor(v, dtype=torch.float32)
+    axes = torch.tensor([1.0, 0.4 + 0.15 * (label % 4), 1.0 - 0.2 * (label % 4) + 0.05 * (label // 4)]) * (0.9 + 0.2 * torch.rand(3, generator=gen))
+    pos = pos / pos.norm(dim=1, keepdim=True) * axes
+    return Data(pos=pos, face=torch.tensor(f, dtype=torch.long).t().contiguous(), y=torch.tensor([label]))

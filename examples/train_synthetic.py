@@ -27,26 +27,8 @@ from torch_geometric.transforms import Compose, SamplePoints  # noqa: E402
 
 
 def ellipsoid_mesh(label, gen):
-    """A closed triangle mesh (subdivided octahedron pushed onto an ellipsoid whose axes depend on the class)."""
-    v = [(1, 0, 0), (-1, 0, 0), (0, 1, 0), (0, -1, 0), (0, 0, 1), (0, 0, -1)]
-    f = [(0, 2, 4), (2, 1, 4), (1, 3, 4), (3, 0, 4), (2, 0, 5), (1, 2, 5), (3, 1, 5), (0, 3, 5)]
-    for _ in range(3):
-        mid, nf = {}, []
-
-        def m(a, b):
-            key = (min(a, b), max(a, b))
-            if key not in mid:
-                v.append(tuple((v[a][i] + v[b][i]) / 2 for i in range(3)))
-                mid[key] = len(v) - 1
-            return mid[key]
-        for a, b, c in f:
-            ab, bc, ca = m(a, b), m(b, c), m(c, a)
-            nf += [(a, ab, ca), (ab, b, bc), (ca, bc, c), (ab, bc, ca)]
-        f = nf
-    pos = torch.tensor(v, dtype=torch.float32)
-    axes = torch.tensor([1.0, 0.4 + 0.15 * label, 1.0 - 0.2 * label]) * (0.9 + 0.2 * torch.rand(3, generator=gen))
-    pos = pos / pos.norm(dim=1, keepdim=True) * axes
-    return Data(pos=pos, face=torch.tensor(f, dtype=torch.long).t().contiguous(), y=torch.tensor([label]))
+    from deltaconv_b200.utils import synthetic_mesh
+    return synthetic_mesh(label, gen)
 
 
 def calc_loss(pred, gold, eps=0.2):

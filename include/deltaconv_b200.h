@@ -100,6 +100,7 @@ int dc_estimate_basis(const float* pos, const int32_t* idx, int N, int k, const 
  * gaussian_weights (:100-116), weighted_least_squares (:119-152), fit_vector_mapping (:155-194).
  * Optional debug outputs expose those helpers' results: coords [N,k,2], weights [N,k], mapping [N,k,2,2]. */
 size_t dc_build_ws_bytes(int N, int B);
+int dc_set_build_chunk(int points);    /* tuning: points per fit/normalise chunk, 0 = automatic; no reference counterpart */
 int dc_build_grad_div(const float* pos, const float* normal, const float* xb, const float* yb,
                       const int32_t* idx, const int32_t* cloud_ptr, int B, int N, int k,
                       float kernel_width, float lam, float lam_shape, int use_shape, int normalized,
@@ -112,7 +113,8 @@ int dc_build_grad_div(const float* pos, const float* normal, const float* xb, co
  * in the reference.  Limits: N <= dc_build_static_max_points() (262144), B <= dc_build_static_max_clouds()
  * (4096); larger batches return an error.  All calls on a GPU share the array: calls that can overlap on
  * the GPU race; nothing has to be cleared between calls.  The first call on each GPU looks the array's
- * address up (cudaGetSymbolAddress) — make it before any stream capture.  No debug outputs. */
+ * address up (cudaGetSymbolAddress) — make it before any stream capture.  The array used is the CURRENT
+ * device's: buffers and stream must belong to it (the output buffer is checked).  No debug outputs. */
 int dc_build_static_max_points(void);
 int dc_build_static_max_clouds(void);
 int dc_build_grad_div_static(const float* pos, const float* normal, const float* xb, const float* yb,

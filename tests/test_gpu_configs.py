@@ -54,13 +54,18 @@ def compare_train_step(name, model, oracle, data, loss_ours, loss_ref, grad_fact
     l_ref.backward()
     l_ours.backward()
     ref_grads = dict(oracle.named_parameters())
+    # Some gradients vanish analytically (a BatchNorm bias that only feeds another BatchNorm through a per-channel constant:
+    # the fp64 oracle returns ~1e-16 for them).  Each tensor is therefore measured against max(its own scale, 1e-3 x the
+    # largest gradient scale of the network), the rule tests/test_gpu_nn.py uses for the reference fixtures.
+    net_scale = max(float(g.grad.abs().max()) for g in ref_grads.values() if g.grad is not None)
     worst, worst_name = 0.0, None
     for pname, p in model.named_parameters():
         if ref_grads[pname].grad is None:
             assert p.grad is None, pname              # VectorNonLin.bias under BatchNorm
             continue
         assert p.grad is not None, pname
-        err = rel_err(p.grad.cpu(), ref_grads[pname].grad)
+        ref_g = ref_grads[pname].grad
+        err = float((p.grad.cpu().double() - ref_g).abs().max()) / max(float(ref_g.abs().max()), 1e-3 * net_scale)
         if err > worst:
             worst, worst_name = err, pname
     report(f'{name}.grad_worst[{worst_name}]', worst)

@@ -26,7 +26,8 @@ def synth(B, P, cfg=2, **kw):
 # ----------------------------------------------------------------------------------------------
 
 @pytest.mark.parametrize('sizes,k', [([128, 128], 10), ([50, 64, 80], 20), ([1024] * 8, 20), ([300, 1, 77, 2048], 1),
-                                     ([700, 900], 40), ([150, 200], 70), ([5000, 300], 12), ([2048] * 2, 30)])
+                                     ([700, 900], 40), ([150, 200], 70), ([5000, 300], 12), ([2048] * 2, 30),
+                                     ([1024] * 4, 33), ([2048, 1000], 40), ([1024, 333], 64), ([4500, 64], 64), ([3000], 48)])
 def test_knn_bit_exact(sizes, k):
     sizes = [max(s, k) for s in sizes]
     d = synth(len(sizes), 0, cfg=7, sizes=sizes)
@@ -349,7 +350,7 @@ def test_staged_spmm_is_bitwise_equal_to_the_gather_kernels(C):
         assert torch.equal(a, b)
 
 
-@pytest.mark.parametrize('sizes,k', [([5000, 7000], 20), ([300, 9000, 17, 4200], 10), ([6000], 40), ([20000], 16), ([4500, 4500], 70)])
+@pytest.mark.parametrize('sizes,k', [([5000, 7000], 20), ([300, 9000, 17, 4200], 10), ([6000], 40), ([20000], 16), ([4500, 4500], 70), ([8000], 33), ([3000, 5000], 64)])
 def test_grid_knn_is_bit_identical_to_brute_force(sizes, k):
     """dc_knn_grid (uniform grid + ring search, used for clouds of more than 1536 points) returns exactly the graph of the
     brute-force kernel: indices and squared distances, ties by lower index.  Clouds: uniform volume, a thin shell, a planar

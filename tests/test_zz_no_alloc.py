@@ -58,6 +58,17 @@ def test_static_scratch_build_matches_workspace_build_on_two_calls_in_a_row():
         assert _close(G1, G0) and _close(D1, D0)
 
 
+def test_static_scratch_build_matches_the_fp64_oracle():
+    """The same entry point against the CPU oracle directly (not only against the workspace build)."""
+    from oracle import geometry as og
+    pos, normal, xb, yb, graph = _inputs([256, 300, 77], 12, 34)
+    G, D_ = _build(True, pos, normal, xb, yb, graph, True, 1e-3, None)
+    batch = torch.repeat_interleave(torch.arange(3), torch.tensor([256, 300, 77]))
+    Go, Do = og.fit_operators(pos.double().cpu(), normal.double().cpu(), xb.double().cpu(), yb.double().cpu(),
+                              graph.idx.long().cpu(), batch, 1.0, 1e-3)
+    assert _close(G.double().cpu(), Go) and _close(D_.double().cpu(), Do)
+
+
 def test_static_scratch_build_rejects_batches_beyond_its_limit():
     from deltaconv_b200 import _lib
     pos, normal, xb, yb, graph = _inputs([64, 64], 8, 33)
