@@ -35,6 +35,7 @@ _SIGNATURES = {
     'dc_tangent_basis': [_P, _I, _P, _P, _P],
     'dc_estimate_basis': [_P, _P, _I, _I, _P, _P, _P, _P, _P],
     'dc_build_ws_bytes': [_I, _I],
+    'dc_build_ws_min_bytes': [_I, _I],
     'dc_build_grad_div': [_P, _P, _P, _P, _P, _P, _I, _I, _I, _F, _F, _F, _I, _I, _P, _P, _P, _P, _P, _P, _Z, _P],
     'dc_set_build_chunk': [_I],
     'dc_build_static_max_points': [],
@@ -90,7 +91,7 @@ _SIGNATURES = {
     'dc_fold_vec_weight_grad': [_P, _I, _I, _P, _P],
 }
 _RESTYPES = {'dc_launch_count': ctypes.c_longlong, 'dc_reset_launch_count': None,
-             'dc_ell_transpose_ws_bytes': _Z, 'dc_build_ws_bytes': _Z, 'dc_colreduce_ws_bytes': _Z,
+             'dc_ell_transpose_ws_bytes': _Z, 'dc_build_ws_bytes': _Z, 'dc_build_ws_min_bytes': _Z, 'dc_colreduce_ws_bytes': _Z,
              'dc_gemm_ws_bytes': _Z, 'dc_central_ws_bytes': _Z, 'dc_knn_grid_ws_bytes': _Z, 'dc_geodesic_fps_ws_bytes': _Z}
 
 _lib = None

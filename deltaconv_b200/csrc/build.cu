@@ -47,26 +47,73 @@ __global__ void estimate_basis_kernel(const float* __restrict__ pos, const int* 
     yb[o] = ey.x; yb[o + 1] = ey.y; yb[o + 2] = ey.z;
 }
 
+// ---- gather records ----------------------------------------------------------------------------
+// The fit gathers, per neighbour, its position (pass A) and its tangent frame (pass B).  From the [N,3] arrays that is 9
+// scalar loads per neighbour, each touching 32 different sectors per warp: the kernel is then bound by the L1's
+// sector-lookup rate, not by arithmetic or bandwidth (ncu, round 2: 15 % issue utilisation).  With a workspace that has room
+// for them, positions are repacked as one 16-byte record and frames as one 32-byte record per point (one sector each,
+// fetched with 1 + 2 LDG.128), which cuts the lookups per neighbour from 9 to 3.
+__global__ void pack_kernel(const float* __restrict__ pos, const float* __restrict__ xb, const float* __restrict__ yb, int N,
+                            float4* __restrict__ posp, float4* __restrict__ frm) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    const V3 p = v3_load(pos + 3 * (size_t)i), x = v3_load(xb + 3 * (size_t)i), y = v3_load(yb + 3 * (size_t)i);
+    posp[i] = make_float4(p.x, p.y, p.z, 0.f);
+    frm[2 * (size_t)i] = make_float4(x.x, x.y, x.z, y.x);
+    frm[2 * (size_t)i + 1] = make_float4(y.y, y.z, 0.f, 0.f);
+}
+
+template <bool PACKED>
+__device__ __forceinline__ V3 gather_pos(const float* __restrict__ pos, const float4* __restrict__ posp, int j) {
+    if (PACKED) { const float4 q = __ldg(posp + j); return v3(q.x, q.y, q.z); }
+    return v3_load(pos + 3 * (size_t)j);
+}
+
 // ---- pass A: m_i = mean_e ||p_j - p_i||  (grad_div_mls.py:233, :112 inner mean) --------------
-// 8 lanes per point keep the idx reads coalesced and the gathers parallel.
-__global__ void edge_mean_kernel(const float* __restrict__ pos, const int* __restrict__ idx, int N, int k,
-                                 float* __restrict__ m) {
-    const int sub = threadIdx.x & 7;
-    const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 3;
-    float acc = 0.f;
-    if (i < N) {
-        V3 p = v3_load(pos + 3 * (size_t)i);
-        for (int e = sub; e < k; e += 8) {
-            int j = __ldg(idx + (size_t)i * k + e);
-            if (j < 0 || j >= N) j = 0;
-            V3 d = v3_load(pos + 3 * (size_t)j) - p;
-            acc += sqrtf(dot(d, d));
-        }
+// One thread per point; the CTA's idx tile is loaded coalesced and transposed into shared memory (as in the fit), four
+// neighbour positions are in flight per thread.  (The first version spread a point over 8 lanes: 43 warp-instructions per
+// point and 91 us per 2^20 points, more than the fit itself.)
+constexpr int EDGE_T = 128;
+template <bool PACKED>
+__global__ void __launch_bounds__(EDGE_T)
+edge_mean_kernel(const float* __restrict__ pos, const float4* __restrict__ posp, const int* __restrict__ idx, int N, int k,
+                 float* __restrict__ m) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    constexpr int STRIDE = EDGE_T + 1;
+    int* s_idx = reinterpret_cast<int*>(smem_raw);                 // [k][STRIDE]
+    const int base = blockIdx.x * EDGE_T;
+    const int npts = min(EDGE_T, N - base);
+    const int tile = npts * k;
+    const int* gidx = idx + (size_t)base * k;
+    for (int l = threadIdx.x, p = threadIdx.x / k, e = threadIdx.x % k; l < tile; l += EDGE_T) {
+        s_idx[e * STRIDE + p] = __ldg(gidx + l);
+        e += EDGE_T % k; p += EDGE_T / k;
+        if (e >= k) { e -= k; ++p; }
     }
-    acc += __shfl_xor_sync(FULL, acc, 4);
-    acc += __shfl_xor_sync(FULL, acc, 2);
-    acc += __shfl_xor_sync(FULL, acc, 1);
-    if (i < N && sub == 0) m[i] = acc / (float)k;
+    __syncthreads();
+    if (threadIdx.x >= npts) return;
+    const int i = base + threadIdx.x;
+    const int* jdx = s_idx + threadIdx.x;
+    const V3 p = v3_load(pos + 3 * (size_t)i);
+    float acc = 0.f;
+#pragma unroll 1
+    for (int e = 0; e < k; e += 4) {
+        V3 pj[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (e + u < k) {
+                const int j = jdx[(e + u) * STRIDE];
+                pj[u] = gather_pos<PACKED>(pos, posp, ((unsigned)j >= (unsigned)N) ? 0 : j);
+            }
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (e + u < k) {
+                const V3 d = pj[u] - p;
+                const float d2 = dot(d, d);
+                acc += d2 > 0.f ? d2 * dc_rsqrt(d2) : 0.f;
+            }
+    }
+    m[i] = acc / (float)k;
 }
 
 // ---- per-cloud mean of m (scatter_mean, grad_div_mls.py:112); fixed-order tree => deterministic
@@ -104,10 +151,11 @@ __global__ void __launch_bounds__(CLOUD_MEAN_T) cloud_mean_kernel(const float* _
 // shared-memory address is an immediate.  Entries are written WITHOUT the per-cloud normalisation; the per-cloud maxima go to
 // S (one atomicMax per warp: s_i >= 0, so its bit pattern orders like the value and the integer max is exact and order
 // independent, replacing scatter_max of grad_div_mls.py:259) and scale_kernel applies them.
-template <int T, int K, bool DEBUG>
+template <int T, int K, bool DEBUG, bool PACKED>
 __global__ void __launch_bounds__(T)
 fit_kernel(const float* __restrict__ pos, const float* __restrict__ normal, const float* __restrict__ xb,
-           const float* __restrict__ yb, const int* __restrict__ idx, const int* __restrict__ cloud_ptr, int B,
+           const float* __restrict__ yb, const float4* __restrict__ posp, const float4* __restrict__ frm,
+           const int* __restrict__ idx, const int* __restrict__ cloud_ptr, int B,
            int N, int k_rt, int n0, int n1, float kernel_width, FitParams fp, int normalized, const float* __restrict__ abar,
            unsigned* __restrict__ S, float* __restrict__ G, float* __restrict__ D,
            float* __restrict__ dbg_coords, float* __restrict__ dbg_weights, float* __restrict__ dbg_mapping) {
@@ -153,7 +201,7 @@ fit_kernel(const float* __restrict__ pos, const float* __restrict__ normal, cons
                 if (e + u < k) {
                     j[u] = jdx[(e + u) * STRIDE];
                     const int jj = ((unsigned)j[u] >= (unsigned)N) ? 0 : j[u];
-                    pj[u] = v3_load(pos + 3 * (size_t)jj);
+                    pj[u] = gather_pos<PACKED>(pos, posp, jj);
                 }
 #pragma unroll
             for (int u = 0; u < 4; ++u)
@@ -174,7 +222,12 @@ fit_kernel(const float* __restrict__ pos, const float* __restrict__ normal, cons
                 if (e + u < k) {
                     const int j = jdx[(e + u) * STRIDE];
                     const int jj = ((unsigned)j >= (unsigned)N) ? 0 : j;
-                    xj[u] = v3_load(xb + 3 * (size_t)jj); yj[u] = v3_load(yb + 3 * (size_t)jj);
+                    if (PACKED) {
+                        const float4 a = __ldg(frm + 2 * (size_t)jj), b = __ldg(frm + 2 * (size_t)jj + 1);
+                        xj[u] = v3(a.x, a.y, a.z); yj[u] = v3(a.w, b.x, b.y);
+                    } else {
+                        xj[u] = v3_load(xb + 3 * (size_t)jj); yj[u] = v3_load(yb + 3 * (size_t)jj);
+                    }
                 }
 #pragma unroll
             for (int u = 0; u < 4; ++u)
@@ -218,9 +271,14 @@ fit_kernel(const float* __restrict__ pos, const float* __restrict__ normal, cons
 // their final S.  With one launch per chunk of points this runs while the chunk's entries are still in L2.
 constexpr int SCALE_T = 256;
 constexpr int SCALE_PTS = 128;
+__device__ __forceinline__ float2 scaled(float2 v, float f) { return make_float2(v.x * f, v.y * f); }
+__device__ __forceinline__ float4 scaled(float4 v, float f) { return make_float4(v.x * f, v.y * f, v.z * f, v.w * f); }
+
+// V = float2: one slot per element, u = k elements per point; V = float4 (k even): two slots per element, u = k / 2
+template <class V>
 __global__ void __launch_bounds__(SCALE_T)
-scale_kernel(float* __restrict__ G, float* __restrict__ D, const int* __restrict__ cloud_ptr, int B, const unsigned* __restrict__ S,
-             int N, int k, int n0, int n1) {
+scale_kernel(V* __restrict__ G, V* __restrict__ D, const int* __restrict__ cloud_ptr, int B, const unsigned* __restrict__ S,
+             int N, int u, int n0, int n1) {
     __shared__ float s_scale[SCALE_PTS];
     const int lo = n0 <= 0 ? 0 : __ldg(cloud_ptr + cloud_of(cloud_ptr, B, n0));
     const int hi = n1 >= N ? N : __ldg(cloud_ptr + cloud_of(cloud_ptr, B, n1));
@@ -229,16 +287,15 @@ scale_kernel(float* __restrict__ G, float* __restrict__ D, const int* __restrict
         __syncthreads();
         if (threadIdx.x < npts) s_scale[threadIdx.x] = fit_scale(__uint_as_float(__ldg(S + cloud_of(cloud_ptr, B, base + threadIdx.x))));
         __syncthreads();
-        float2* gG = reinterpret_cast<float2*>(G) + (size_t)base * k;
-        float2* gD = reinterpret_cast<float2*>(D) + (size_t)base * k;
-        const int tile = npts * k;
-        for (int l = threadIdx.x, p = threadIdx.x / k, e = threadIdx.x % k; l < tile; l += SCALE_T) {
+        V* gG = G + (size_t)base * u;
+        V* gD = D + (size_t)base * u;
+        const int tile = npts * u;
+        for (int l = threadIdx.x, p = threadIdx.x / u, e = threadIdx.x % u; l < tile; l += SCALE_T) {
             const float f = s_scale[p];
-            float2 g = gG[l], d = gD[l];
-            gG[l] = make_float2(g.x * f, g.y * f);
-            gD[l] = make_float2(d.x * f, d.y * f);
-            e += SCALE_T % k; p += SCALE_T / k;
-            if (e >= k) { e -= k; ++p; }
+            gG[l] = scaled(gG[l], f);
+            gD[l] = scaled(gD[l], f);
+            e += SCALE_T % u; p += SCALE_T / u;
+            if (e >= u) { e -= u; ++p; }
         }
     }
 }
@@ -246,32 +303,38 @@ scale_kernel(float* __restrict__ G, float* __restrict__ D, const int* __restrict
 size_t fit_smem_bytes(int T, int k) { return (size_t)k * (T + 1) * (sizeof(float4) + sizeof(int)); }
 
 struct FitArgs {
-    const float *pos, *normal, *xb, *yb; const int *idx, *cloud_ptr; int B, N, k; float kernel_width; FitParams fp; int normalized;
+    const float *pos, *normal, *xb, *yb; const float4 *posp, *frm; const int *idx, *cloud_ptr; int B, N, k; float kernel_width; FitParams fp; int normalized;
     const float* abar; unsigned* S; float *G, *D, *dc, *dw, *dm;
 };
 
-template <int T, int K, bool DEBUG>
+template <int T, int K, bool DEBUG, bool PACKED>
 int launch_fit_one(const FitArgs& a, int n0, int n1, cudaStream_t st) {
     const size_t smem = fit_smem_bytes(T, a.k);
-    DC_CUDA(cudaFuncSetAttribute(fit_kernel<T, K, DEBUG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    fit_kernel<T, K, DEBUG><<<dc_ceil_div(n1 - n0, T), T, smem, st>>>(a.pos, a.normal, a.xb, a.yb, a.idx, a.cloud_ptr, a.B, a.N, a.k, n0, n1,
-                                                                       a.kernel_width, a.fp, a.normalized, a.abar, a.S, a.G, a.D, a.dc, a.dw, a.dm);
+    DC_CUDA(cudaFuncSetAttribute(fit_kernel<T, K, DEBUG, PACKED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    fit_kernel<T, K, DEBUG, PACKED><<<dc_ceil_div(n1 - n0, T), T, smem, st>>>(a.pos, a.normal, a.xb, a.yb, a.posp, a.frm, a.idx, a.cloud_ptr, a.B,
+                                                                               a.N, a.k, n0, n1, a.kernel_width, a.fp, a.normalized, a.abar, a.S,
+                                                                               a.G, a.D, a.dc, a.dw, a.dm);
     return dc_check_launch("dc_build_grad_div/fit");
+}
+
+template <int T, bool PACKED>
+int launch_fit_k(const FitArgs& a, int n0, int n1, cudaStream_t st) {
+    if (a.dc || a.dw || a.dm) return launch_fit_one<T, 0, true, PACKED>(a, n0, n1, st);
+    switch (a.k) {
+        case 10: return launch_fit_one<T, 10, false, PACKED>(a, n0, n1, st);
+        case 20: return launch_fit_one<T, 20, false, PACKED>(a, n0, n1, st);
+        case 30: return launch_fit_one<T, 30, false, PACKED>(a, n0, n1, st);
+        case 40: return launch_fit_one<T, 40, false, PACKED>(a, n0, n1, st);
+        default: return launch_fit_one<T, 0, false, PACKED>(a, n0, n1, st);
+    }
 }
 
 template <int T>
 int launch_fit(const FitArgs& a, int n0, int n1, cudaStream_t st) {
-    if (a.dc || a.dw || a.dm) return launch_fit_one<T, 0, true>(a, n0, n1, st);
-    switch (a.k) {
-        case 10: return launch_fit_one<T, 10, false>(a, n0, n1, st);
-        case 20: return launch_fit_one<T, 20, false>(a, n0, n1, st);
-        case 30: return launch_fit_one<T, 30, false>(a, n0, n1, st);
-        case 40: return launch_fit_one<T, 40, false>(a, n0, n1, st);
-        default: return launch_fit_one<T, 0, false>(a, n0, n1, st);
-    }
+    return a.posp ? launch_fit_k<T, true>(a, n0, n1, st) : launch_fit_k<T, false>(a, n0, n1, st);
 }
 
-int g_build_chunk_points = 0;      // tuning switch (dc_set_build_chunk): points per fit/scale chunk, 0 = automatic
+int g_build_chunk_points = 0;      // tuning switch (dc_set_build_chunk): points per fit/scale chunk, 0 = all points in one launch
 
 }  // namespace
 
@@ -289,11 +352,15 @@ extern "C" int dc_estimate_basis(const float* pos, const int32_t* idx, int N, in
     return dc_check_launch("dc_estimate_basis");
 }
 
-extern "C" size_t dc_build_ws_bytes(int N, int B) {
-    // m[N] floats, abar[B] floats, S[B] uints; each region 256-byte aligned
+// minimum: m[N] floats, abar[B] floats, S[B] uints; each region 256-byte aligned
+static size_t build_ws_min_bytes(int N, int B) {
     size_t a = ((size_t)N * 4 + 255) / 256 * 256, b = ((size_t)B * 4 + 255) / 256 * 256;
     return a + 2 * b;
 }
+// What callers should provide: the minimum plus the 48-byte gather records per point (16 position + 32 frame).  A
+// workspace of at least build_ws_min_bytes() but less than this still works, through the slower scalar gathers.
+extern "C" size_t dc_build_ws_bytes(int N, int B) { return build_ws_min_bytes(N, B) + (((size_t)N * 48 + 255) / 256 * 256); }
+extern "C" size_t dc_build_ws_min_bytes(int N, int B) { return build_ws_min_bytes(N, B); }
 
 extern "C" int dc_build_grad_div(const float* pos, const float* normal, const float* xb, const float* yb,
                                  const int32_t* idx, const int32_t* cloud_ptr, int B, int N, int k,
@@ -302,8 +369,8 @@ extern "C" int dc_build_grad_div(const float* pos, const float* normal, const fl
                                  void* ws, size_t ws_bytes, void* stream) {
     DC_REQUIRE(k >= 1 && k <= 256, "dc_build_grad_div: k must be in [1,256] (got %d)", k);
     DC_REQUIRE(B >= 1, "dc_build_grad_div: B must be >= 1");
-    DC_REQUIRE(ws_bytes >= dc_build_ws_bytes(N, B), "dc_build_grad_div: workspace too small (%zu < %zu)", ws_bytes,
-               dc_build_ws_bytes(N, B));
+    DC_REQUIRE(ws_bytes >= build_ws_min_bytes(N, B), "dc_build_grad_div: workspace too small (%zu < %zu)", ws_bytes,
+               build_ws_min_bytes(N, B));
     if (N <= 0) return DC_OK;
     cudaStream_t st = (cudaStream_t)stream;
     const size_t m_bytes = ((size_t)N * 4 + 255) / 256 * 256, b_bytes = ((size_t)B * 4 + 255) / 256 * 256;
@@ -313,17 +380,35 @@ extern "C" int dc_build_grad_div(const float* pos, const float* normal, const fl
     FitParams fp;
     fp.lam = lam; fp.lam_shape = lam_shape; fp.use_shape = use_shape;
 
-    edge_mean_kernel<<<dc_ceil_div((long long)N * 8, 256), 256, 0, st>>>(pos, idx, N, k, m);
+    const bool packed = ws_bytes >= dc_build_ws_bytes(N, B);
+    float4* posp = packed ? (float4*)((char*)ws + build_ws_min_bytes(N, B)) : nullptr;
+    float4* frm = packed ? posp + N : nullptr;
+    int rc;
+    const size_t edge_smem = (size_t)k * (EDGE_T + 1) * 4;
+    if (edge_smem > 48 * 1024) {
+        DC_CUDA(cudaFuncSetAttribute(edge_mean_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)edge_smem));
+        DC_CUDA(cudaFuncSetAttribute(edge_mean_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)edge_smem));
+    }
+    if (packed) {
+        pack_kernel<<<dc_ceil_div(N, 256), 256, 0, st>>>(pos, xb, yb, N, posp, frm);
+        edge_mean_kernel<true><<<dc_ceil_div(N, EDGE_T), EDGE_T, edge_smem, st>>>(pos, posp, idx, N, k, m);
+        rc = dc_check_launch_n("dc_build_grad_div/pack", 1);
+        if (rc) return rc;
+    } else {
+        edge_mean_kernel<false><<<dc_ceil_div(N, EDGE_T), EDGE_T, edge_smem, st>>>(pos, nullptr, idx, N, k, m);
+    }
     cloud_mean_kernel<<<B, CLOUD_MEAN_T, 0, st>>>(m, cloud_ptr, B, abar, S);
-    int rc = dc_check_launch_n("dc_build_grad_div/mean", 2);
+    rc = dc_check_launch_n("dc_build_grad_div/mean", 2);
     if (rc) return rc;
-    FitArgs a = {pos, normal, xb, yb, idx, cloud_ptr, B, N, k, kernel_width, fp, normalized, abar, S, G, D, dbg_coords, dbg_weights, dbg_mapping};
+    FitArgs a = {pos, normal, xb, yb, posp, frm, idx, cloud_ptr, B, N, k, kernel_width, fp, normalized, abar, S, G, D, dbg_coords, dbg_weights, dbg_mapping};
     // threads per CTA: as many as keep two CTAs resident per SM (<= ~110 KB of shared memory each)
     const size_t budget = 110 * 1024;
     const int T = fit_smem_bytes(128, k) <= budget ? 128 : (fit_smem_bytes(64, k) <= budget ? 64 : 32);
-    // Chunks of points: the fit of a chunk is followed at once by the normalisation of the clouds it completed, while their
-    // 16 k bytes per point are still in L2 (a chunk's entries + inputs stay below ~40 MB); small batches are one chunk.
-    long long chunk = g_build_chunk_points > 0 ? g_build_chunk_points : (32ll << 20) / (16ll * k);
+    // Optional chunks of points (dc_set_build_chunk): the fit of a chunk followed at once by the normalisation of the clouds
+    // it completed, while their 16 k bytes per point are still in L2.  Measured on 2^20 points (scripts/exp_build_chunk.py):
+    // every chunk size LOSES against one launch each (0.57 ms) — 0.78 ms at 32 MB chunks, 0.66 ms at 80 MB — because each
+    // short fit launch ends in a partially filled wave; so the default is one chunk.
+    long long chunk = g_build_chunk_points > 0 ? g_build_chunk_points : N;
     chunk = (chunk + T - 1) / T * T;
     if (!normalized || chunk > N) chunk = N;
     for (long long n0 = 0; n0 < N; n0 += chunk) {
@@ -335,7 +420,10 @@ extern "C" int dc_build_grad_div(const float* pos, const float* normal, const fl
         if (normalized) {
             const int tiles = dc_ceil_div(n1 - (int)n0, SCALE_PTS) + 1;
             const int cap = dc_sm_count() * 8;
-            scale_kernel<<<tiles < cap ? tiles : cap, SCALE_T, 0, st>>>(G, D, cloud_ptr, B, S, N, k, (int)n0, n1);
+            const int grid = tiles < cap ? tiles : cap;
+            const bool wide = k % 2 == 0 && ((uintptr_t)G & 15u) == 0 && ((uintptr_t)D & 15u) == 0;
+            if (wide) scale_kernel<float4><<<grid, SCALE_T, 0, st>>>((float4*)G, (float4*)D, cloud_ptr, B, S, N, k / 2, (int)n0, n1);
+            else scale_kernel<float2><<<grid, SCALE_T, 0, st>>>((float2*)G, (float2*)D, cloud_ptr, B, S, N, k, (int)n0, n1);
             rc = dc_check_launch("dc_build_grad_div/scale");
             if (rc) return rc;
         }
@@ -393,7 +481,7 @@ extern "C" int dc_build_grad_div_static(const float* pos, const float* normal, c
     DC_REQUIRE(B <= DC_STATIC_MAX_CLOUDS,
                "dc_build_grad_div_static: %d clouds exceed the built-in scratch (max %d); use dc_build_grad_div with a workspace",
                B, DC_STATIC_MAX_CLOUDS);
-    DC_REQUIRE(dc_build_ws_bytes(N, B) <= DC_STATIC_SCRATCH_BYTES, "dc_build_grad_div_static: internal size mismatch");
+    DC_REQUIRE(build_ws_min_bytes(N, B) <= DC_STATIC_SCRATCH_BYTES, "dc_build_grad_div_static: internal size mismatch");
     constexpr int kMaxDevices = 64;
     static std::mutex mu;
     static void* scratch_of_device[kMaxDevices] = {nullptr};

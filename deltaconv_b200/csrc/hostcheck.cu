@@ -56,7 +56,8 @@ extern "C" void hc_build_grad_div(const float* pos, const float* normal, const f
             int j = idx[(size_t)i * k + e];
             if (j < 0 || j >= N) j = 0;
             V3 d = v3_load(pos + 3 * j) - p;
-            acc += sqrtf(dot(d, d));
+            float d2 = dot(d, d);
+            acc += d2 > 0.f ? d2 * dc_rsqrt(d2) : 0.f;
         }
         m[i] = acc / (float)k;
     }

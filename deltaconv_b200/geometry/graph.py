@@ -2,6 +2,8 @@
 reference imports (`torch_geometric.nn.knn_graph`, `global_max_pool`, `global_mean_pool`:
 deltanet_base.py:2, deltanet_classification.py:3, deltanet_segmentation.py:3), backed by the
 CUDA library."""
+import torch
+
 from .. import ops
 
 

@@ -44,16 +44,20 @@ def weighted_least_squares(coords, weights, k, regularizer, shape_regularizer=No
     """Rows of the regularised pseudo-inverse of the quadric fit [1,u,v,u^2,uv,v^2] per edge -> [E,6]; with a second
     regulariser also the variant used for the surface fit (grad_div_mls.py:119-152)."""
     k = int(k)
-    u, v = coords[:, 0], coords[:, 1]
+    out_dtype = coords.dtype
+    # The normal equations are formed and inverted in fp64 whatever the input precision: with regularizer -> 0 (as the
+    # reference's own tests call this) the 6x6 systems are badly conditioned, and a batched fp32 inverse on the GPU does not
+    # reach the 1e-6 the reference's CPU LAPACK path delivers.
+    u, v = coords[:, 0].double(), coords[:, 1].double()
     basis = torch.stack([torch.ones_like(u), u, v, u * u, u * v, v * v], dim=1).view(-1, k, 6)
-    wb = basis * weights.view(-1, k, 1)
+    wb = basis * weights.double().view(-1, k, 1)
     gram = torch.einsum('nki,nkj->nij', wb, basis)
     # the reference adds `regularizer * torch.eye(6)` built in the default dtype: lambda is rounded to fp32
-    eye = torch.eye(6, device=coords.device)
+    eye = torch.eye(6, device=coords.device, dtype=torch.float32)
 
     def solve(reg):
         inv = torch.linalg.inv(gram + (reg * eye).to(gram.dtype))
-        return torch.einsum('nij,nkj->nki', inv, wb).reshape(-1, 6)
+        return torch.einsum('nij,nkj->nki', inv, wb).reshape(-1, 6).to(out_dtype)
     if shape_regularizer is None:
         return solve(regularizer)
     return solve(regularizer), solve(shape_regularizer)

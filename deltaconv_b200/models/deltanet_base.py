@@ -28,7 +28,10 @@ class DeltaNetBase(torch.nn.Module):
     # change which of two equidistant neighbours is kept.
     reorder_min_points = None
 
-    def forward(self, data):
+    def forward(self, data, feature_slot=None):
+        """Returns the list of per-layer scalar features (deltanet_base.py:87).  They are written side by side into one
+        [N, sum(channels)] buffer — `feature_slot` = (ops.ColumnBuffer, first column) when the head provides a wider one — so
+        that the heads' `torch.cat(conv_out, dim=1)` is `ops.join_columns(conv_out)`, without a copy."""
         pos, batch = data.pos, data.batch
         # optional hints (number of clouds, size of the largest one) that avoid a device sync
         clouds, maxp = getattr(data, '_num_clouds', None), getattr(data, '_max_points', None)
@@ -59,8 +62,12 @@ class DeltaNetBase(torch.nn.Module):
         else:
             x = pos
         v = grad @ x
+        if feature_slot is None:
+            feature_slot = (ops.ColumnBuffer(pos.size(0), sum(c.out_channels for c in self.convs), pos.device), 0)
+        buffer, col = feature_slot
         out = []
         for conv in self.convs:
-            x, v = conv(x, v, grad, div, edge_index)
+            x, v = conv(x, v, grad, div, edge_index, x_slot=(buffer, col))
+            col += conv.out_channels
             out.append(x)
         return out

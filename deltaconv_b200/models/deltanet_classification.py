@@ -22,5 +22,5 @@ class DeltaNetClassification(torch.nn.Module):
         conv_out = self.deltanet_base(data)
         # lin_embedding, then [global max | global mean] in one segmented pass that also applies the layer's BatchNorm and
         # activation (deltanet_classification.py:45-49)
-        x = self.lin_embedding.forward_pooled(torch.cat(conv_out, dim=1), data.batch, 'maxmean', getattr(data, '_num_clouds', None))
+        x = self.lin_embedding.forward_pooled(ops.join_columns(conv_out), data.batch, 'maxmean', getattr(data, '_num_clouds', None))
         return self.classification_head(x)

@@ -24,15 +24,21 @@ class DeltaNetSegmentation(torch.nn.Module):
             Linear(256, 128), LeakyReLU(negative_slope=0.2), Linear(128, num_classes))
 
     def forward(self, data):
-        conv_out = self.deltanet_base(data)
         batch, N = data.batch, data.pos.size(0)
         clouds = getattr(data, '_num_clouds', None)
-        # global_max_pool(lin_global(x), batch)[batch]  (deltanet_segmentation.py:58-61)
-        x_max = ops.broadcast_rows(self.lin_global.forward_pooled(torch.cat(conv_out, dim=1), batch, 'max', clouds), batch, N)
+        # one buffer for the head's input [x_max | categorical | conv features] (deltanet_segmentation.py:66): every producer
+        # writes its own block, the backbone's features are read in place for lin_global (:57)
+        head_in = self.segmentation_head[0][0][0].in_features
+        conv_width = sum(c.out_channels for c in self.deltanet_base.convs)
+        buffer = ops.ColumnBuffer(N, head_in, data.pos.device)
+        conv_out = self.deltanet_base(data, feature_slot=(buffer, head_in - conv_width))
+        # global_max_pool(lin_global(x), batch)[batch]  (deltanet_segmentation.py:58-61); lin_global reads the features in place
+        x_max = ops.broadcast_rows(self.lin_global.forward_pooled(ops.join_columns(conv_out), batch, 'max', clouds), batch, N,
+                                   slot=(buffer, 0))
         parts = [x_max]
         if self.categorical_vector:
-            parts.append(ops.broadcast_rows(self.lin_categorical(data.category), batch, N))
-        out = self.segmentation_head(torch.cat(parts + conv_out, dim=1))
+            parts.append(ops.broadcast_rows(self.lin_categorical(data.category), batch, N, slot=(buffer, x_max.size(1))))
+        out = self.segmentation_head(ops.join_columns(parts + conv_out))
         perm = getattr(data, '_dc_perm', None)
         if perm is not None:                         # large-cloud mode: rows are in Morton order, hand them back in the caller's
             restored = torch.empty_like(out)

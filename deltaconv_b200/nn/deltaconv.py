@@ -25,7 +25,9 @@ class DeltaConv(torch.nn.Module):
         self.s_mlp = MLP([in_channels * 4] + [out_channels] * depth)
         self.v_mlp = VectorMLP([in_channels * 4 + out_channels * 2] + [out_channels] * depth) if vector else None
 
-    def forward(self, x, v, grad, div, edge_index):
+    def forward(self, x, v, grad, div, edge_index, x_slot=None):
+        """The reference's signature (deltaconv.py:44).  `x_slot` = (ops.ColumnBuffer, column), an extension used by
+        DeltaNetBase: the layer's scalar output is written into that block of the network's feature concatenation."""
         ell = isinstance(grad, ops.EllOperator) and isinstance(div, ops.EllOperator)
         graph = None
         if ell and self.aggr == 'max':
@@ -49,7 +51,7 @@ class DeltaConv(torch.nn.Module):
         else:
             x_max = ops.gather_max(self.s_mlp_max(x), graph)
         x_cat, div_curl = ops.scalar_cat(x, v, div)
-        x = self.s_mlp(x_cat, x_max)
+        x = self.s_mlp(x_cat, x_max, x_slot)
 
         # vector stream (deltaconv.py:64-68)
         if self.v_mlp is not None:

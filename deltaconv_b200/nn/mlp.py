@@ -35,26 +35,31 @@ class _LinBNAct(torch.nn.Sequential):
     BatchNorm and the activation fused into one pass; `addend` is added to the result
     (DeltaConv's `x_max + s_mlp(...)`, deltaconv.py:59)."""
 
-    def forward(self, x, addend=None):
+    def forward(self, x, addend=None, slot=None):
         lin, bn, act = self[0], self[1], self[2]
         slope = _slope_of(act)
         inner = bn.bn
         batch_stats = inner.training or not inner.track_running_stats or inner.running_mean is None
         if slope is not None and lin.bias is None and batch_stats and x.dim() == 2:
             # Linear + BatchNorm statistics + activation as one autograd node
-            return ops.linear_bn_act(x, lin.weight, inner, slope, addend)
+            return ops.linear_bn_act(x, lin.weight, inner, slope, addend, slot)
         y = lin(x)
-        if slope is None:
+        if slope is None:                      # another activation: `slot` is not honoured, the caller concatenates instead
             out = act(bn(y))
             return out if addend is None else out + addend
-        return bn(y, slope, addend)
+        return bn(y, slope, addend, slot)
 
 
 class _MLP(torch.nn.Sequential):
-    def forward(self, x, addend=None):
+    def forward(self, x, addend=None, slot=None):
+        """`addend` is added to the last block's output; `slot` = (ops.ColumnBuffer, column) lets the last block write its
+        output straight into a block of a concatenation buffer."""
         last = len(self) - 1
         for i, block in enumerate(self):
-            x = block(x, addend if i == last else None) if isinstance(block, _LinBNAct) else block(x)
+            if isinstance(block, _LinBNAct):
+                x = block(x, addend if i == last else None, slot if i == last else None)
+            else:
+                x = block(x)
         return x
 
     def forward_pooled(self, x, batch, mode, num_clouds=None):

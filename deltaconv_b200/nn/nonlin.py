@@ -22,8 +22,8 @@ class BatchNorm1d(torch.nn.Module):
     def reset_parameters(self):
         self.bn.reset_parameters()
 
-    def forward(self, x: Tensor, slope: float = 1.0, addend: Tensor = None) -> Tensor:
-        return ops.bn_act(x, self.bn, slope, addend)
+    def forward(self, x: Tensor, slope: float = 1.0, addend: Tensor = None, slot=None) -> Tensor:
+        return ops.bn_act(x, self.bn, slope, addend, slot)
 
     def __repr__(self):
         return f'{self.__class__.__name__}({self.bn.num_features})'

@@ -500,6 +500,76 @@ class _CurlApply(torch.autograd.Function):
 
 
 # ------------------------------------------------------------------------------------------------
+# column blocks: producers write straight into their slice of a concatenation buffer
+# ------------------------------------------------------------------------------------------------
+
+class ColumnBuffer:
+    """One [rows, width] fp32 buffer that several operators fill block of columns by block (through their output leading
+    dimension), so that `torch.cat(parts, dim=1)` (deltanet_classification.py:44, deltanet_segmentation.py:57,66) never
+    copies: `join_columns(parts)` hands the whole buffer to the consumer and routes the gradient back block by block.
+    `block(col, width)` is an alias of the block's memory that is NOT a view in autograd's eyes (no base tensor), so an
+    operator can return it as a fresh output."""
+
+    def __init__(self, rows, width, device):
+        self.buf = torch.empty(rows, width, dtype=_F32, device=device)
+
+    def block(self, col, width):
+        b = self.buf
+        if col < 0 or col + width > b.size(1):
+            raise _lib.DeltaConvLibraryError(f"ColumnBuffer: block [{col}, {col + width}) outside a buffer of width {b.size(1)}")
+        alias = torch.empty(0, dtype=_F32, device=b.device).set_(b.untyped_storage(), b.storage_offset() + col,
+                                                                 (b.size(0), width), (b.stride(0), 1))
+        alias._dc_colbuf = self
+        return alias
+
+
+def _out_block(slot, rows, width, device):
+    """Output tensor of an operator: a fresh [rows, width] tensor, or the block `slot = (ColumnBuffer, first column)`."""
+    if slot is None:
+        return torch.empty(rows, width, dtype=_F32, device=device)
+    cb, col = slot
+    if cb.buf.size(0) != rows:
+        raise _lib.DeltaConvLibraryError(f"ColumnBuffer has {cb.buf.size(0)} rows, the operator produces {rows}")
+    return cb.block(col, width)
+
+
+class _JoinColumns(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, cb, first_col, *parts):
+        ctx.widths = [p.size(1) for p in parts]
+        b = cb.buf
+        return torch.empty(0, dtype=_F32, device=b.device).set_(b.untyped_storage(), b.storage_offset() + first_col,
+                                                                 (b.size(0), sum(ctx.widths)), (b.stride(0), 1))
+
+    @staticmethod
+    def backward(ctx, dbuf):
+        grads, col = [], 0
+        for w in ctx.widths:
+            grads.append(dbuf[:, col:col + w])
+            col += w
+        return (None, None) + tuple(grads)
+
+
+def join_columns(parts):
+    """torch.cat(parts, dim=1); free when the parts are adjacent blocks, in order, of one ColumnBuffer: the result is then
+    the buffer's column range itself (row pitch = the buffer's width; every kernel takes a leading dimension) and the gradient
+    is handed back block by block as views."""
+    parts = list(parts)
+    cb = getattr(parts[0], '_dc_colbuf', None)
+    if cb is not None and all(getattr(p, '_dc_colbuf', None) is cb for p in parts):
+        b = cb.buf
+        first = (parts[0].data_ptr() - b.data_ptr()) // 4
+        col, ok = first, 0 <= first < b.size(1)
+        for p in parts:
+            ok = ok and p.dim() == 2 and p.data_ptr() == b.data_ptr() + 4 * col and p.size(0) == b.size(0) and \
+                (p.stride(0) == b.stride(0) or p.size(0) <= 1) and (p.stride(1) == 1 or p.size(1) <= 1)
+            col += p.size(1)
+        if ok and col <= b.size(1):
+            return _JoinColumns.apply(cb, first, *parts)
+    return torch.cat(parts, dim=1)
+
+
+# ------------------------------------------------------------------------------------------------
 # Linear
 # ------------------------------------------------------------------------------------------------
 
@@ -625,19 +695,19 @@ def _bn_moments(bn, x, ldx, M, C, mode):
 
 class _BNAct(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, y, gamma, beta, addend, bn, slope):
+    def forward(ctx, y, gamma, beta, addend, bn, slope, slot=None):
         y, ldy = _mat(y, 'input')
         M, C = y.shape
         if M == 0:
             raise _lib.DeltaConvLibraryError("BatchNorm1d: empty batch")
         mean, invstd, batch_stats = _bn_moments(bn, y, ldy, M, C, 0)
-        out = torch.empty(M, C, dtype=_F32, device=y.device)
+        out = _out_block(slot, M, C, y.device)
         add_p, ld_add = (None, 0)
         if addend is not None:
             addend, ld_add = _mat(addend, 'addend')
             add_p = ptr(addend)
         call('dc_bn_act_fwd', ptr(y), ldy, M, C, ptr(mean), ptr(invstd), ptr(gamma), ptr(beta), float(slope),
-             add_p, ld_add, ptr(out), C)
+             add_p, ld_add, ptr(out), out.stride(0) if M > 1 else C)
         ctx.save_for_backward(y, mean, invstd, gamma, beta)
         ctx.slope, ctx.batch_stats, ctx.has_add = slope, batch_stats, addend is not None
         return out
@@ -656,12 +726,13 @@ class _BNAct(torch.autograd.Function):
         call('dc_bn_act_bwd', ptr(y), ldy, ptr(dout), ldd, M, C, ptr(mean), ptr(invstd), ptr(gamma), ptr(beta),
              float(ctx.slope), int(ctx.batch_stats), ptr(dgamma), ptr(dbeta), ptr(dy), C, ptr(ws), nb)
         return (dy, dgamma if gamma is not None else None, dbeta if beta is not None else None,
-                dout if ctx.has_add else None, None, None)
+                dout if ctx.has_add else None, None, None, None)
 
 
-def bn_act(y, bn, slope=1.0, addend=None):
-    """act(BatchNorm1d(y)) + addend with act = LeakyReLU(slope) (slope 1 = identity)."""
-    return _BNAct.apply(y, bn.weight, bn.bias, addend, bn, float(slope))
+def bn_act(y, bn, slope=1.0, addend=None, slot=None):
+    """act(BatchNorm1d(y)) + addend with act = LeakyReLU(slope) (slope 1 = identity); `slot` = (ColumnBuffer, column)
+    makes the result land in that block."""
+    return _BNAct.apply(y, bn.weight, bn.bias, addend, bn, float(slope), slot)
 
 
 class _LinearBNAct(torch.autograd.Function):
@@ -669,7 +740,7 @@ class _LinearBNAct(torch.autograd.Function):
     (mlp.py:9) — one node instead of two keeps the pre-activation the only saved intermediate."""
 
     @staticmethod
-    def forward(ctx, x, weight, gamma, beta, addend, bn, slope):
+    def forward(ctx, x, weight, gamma, beta, addend, bn, slope, slot=None):
         x, ldx = _mat(x, 'input')
         weight, ldw = _mat(weight, 'weight')
         if x.size(1) != weight.size(1):
@@ -688,12 +759,13 @@ class _LinearBNAct(torch.autograd.Function):
         ws = workspace(nb, dev)
         call('dc_bn_stats', ptr(y), C, M, C, 0, float(bn.eps), float(momentum), ptr(mean), ptr(invstd),
              ptr(bn.running_mean) if update else None, ptr(bn.running_var) if update else None, nbt, ptr(ws), nb)
-        out = torch.empty(M, C, dtype=_F32, device=dev)
+        out = _out_block(slot, M, C, dev)
         add_p, ld_add = None, 0
         if addend is not None:
             addend, ld_add = _mat(addend, 'addend')
             add_p = ptr(addend)
-        call('dc_bn_act_fwd', ptr(y), C, M, C, ptr(mean), ptr(invstd), ptr(gamma), ptr(beta), float(slope), add_p, ld_add, ptr(out), C)
+        call('dc_bn_act_fwd', ptr(y), C, M, C, ptr(mean), ptr(invstd), ptr(gamma), ptr(beta), float(slope), add_p, ld_add,
+             ptr(out), out.stride(0) if M > 1 else C)
         ctx.save_for_backward(x, weight, y, mean, invstd, gamma, beta)
         ctx.slope, ctx.has_add = slope, addend is not None
         return out
@@ -723,12 +795,13 @@ class _LinearBNAct(torch.autograd.Function):
             ws, nb = _gemm_ws(C, K, M, dev)
             call('dc_linear_bwd_weight', ptr(dy), C, ptr(x), ldx, M, K, C, ptr(dw), K, ptr(ws), nb)
         return (dx, dw, dgamma if gamma is not None else None, dbeta if beta is not None else None,
-                dout if ctx.has_add else None, None, None)
+                dout if ctx.has_add else None, None, None, None)
 
 
-def linear_bn_act(x, weight, bn, slope=1.0, addend=None):
-    """act(BatchNorm1d(x @ weight.T)) + addend with batch statistics (training mode)."""
-    return _LinearBNAct.apply(x, weight, bn.weight, bn.bias, addend, bn, float(slope))
+def linear_bn_act(x, weight, bn, slope=1.0, addend=None, slot=None):
+    """act(BatchNorm1d(x @ weight.T)) + addend with batch statistics (training mode); `slot` = (ColumnBuffer, column) makes
+    the result land in that block."""
+    return _LinearBNAct.apply(x, weight, bn.weight, bn.bias, addend, bn, float(slope), slot)
 
 
 class _VecNonLin(torch.autograd.Function):
@@ -1073,11 +1146,11 @@ def pool_fusable(bn, out_features, bias, slope):
 
 class _BcastRows(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, src, cloud_ptr, B, N):
+    def forward(ctx, src, cloud_ptr, B, N, slot=None):
         src, lds = _mat(src, 'src')
         C = src.size(1)
-        out = torch.empty(N, C, dtype=_F32, device=src.device)
-        call('dc_bcast_rows', ptr(src), lds, ptr(cloud_ptr), B, N, C, ptr(out), C)
+        out = _out_block(slot, N, C, src.device)
+        call('dc_bcast_rows', ptr(src), lds, ptr(cloud_ptr), B, N, C, ptr(out), out.stride(0) if N > 1 else C)
         ctx.B, ctx.N = B, N
         ctx.save_for_backward(cloud_ptr)
         return out
@@ -1091,9 +1164,9 @@ class _BcastRows(torch.autograd.Function):
         dsrc = torch.empty(ctx.B, C, dtype=_F32, device=dout.device)
         call('dc_pool_fwd', ptr(dout), ld, ptr(cloud_ptr), ctx.B, C, None, 0, ptr(dsrc), C, None)
         counts = (cloud_ptr[1:] - cloud_ptr[:-1]).to(_F32)
-        return dsrc * counts[:, None], None, None, None
+        return dsrc * counts[:, None], None, None, None, None
 
 
-def broadcast_rows(src, batch, num_points):
+def broadcast_rows(src, batch, num_points, slot=None):
     cp, B = cloud_ptr_of(batch, num_points, src.device, src.size(0))
-    return _BcastRows.apply(src, cp, B, num_points)
+    return _BcastRows.apply(src, cp, B, num_points, slot)

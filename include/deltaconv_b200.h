@@ -99,7 +99,8 @@ int dc_estimate_basis(const float* pos, const int32_t* idx, int N, int k, const 
  * normalized, shape_regularizer) — grad_div_mls.py:197-277 with coords_projected (:72-97),
  * gaussian_weights (:100-116), weighted_least_squares (:119-152), fit_vector_mapping (:155-194).
  * Optional debug outputs expose those helpers' results: coords [N,k,2], weights [N,k], mapping [N,k,2,2]. */
-size_t dc_build_ws_bytes(int N, int B);
+size_t dc_build_ws_bytes(int N, int B);       /* recommended: includes 48 B per point of repacked gather records */
+size_t dc_build_ws_min_bytes(int N, int B);   /* accepted minimum (4 B per point + 8 B per cloud): slower scalar gathers */
 int dc_set_build_chunk(int points);    /* tuning: points per fit/normalise chunk, 0 = automatic; no reference counterpart */
 int dc_build_grad_div(const float* pos, const float* normal, const float* xb, const float* yb,
                       const int32_t* idx, const int32_t* cloud_ptr, int B, int N, int k,

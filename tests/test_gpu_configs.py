@@ -40,7 +40,16 @@ def pair(build_ours, build_oracle, seed):
 
 
 def compare_train_step(name, model, oracle, data, loss_ours, loss_ref, grad_factor=5.0):
-    """Training-mode forward + backward on both sides; logits, loss, and every parameter gradient."""
+    """Training-mode forward + backward on both sides; logits, loss, and every parameter gradient.
+
+    Gradients pass through arg-max routing (kNN max aggregation, global max pool): where two candidates are closer than fp32
+    rounding, ANY fp32 evaluation may route the gradient to the other one than the fp64 oracle does, and with a classifier's
+    gradient concentrated on ~32 pooled points per channel one such flip moves a weight gradient by percents of its scale.
+    That floor is measured, per tensor, by running the SAME oracle in fp32: a tensor passes when it is within
+    `grad_factor * GRAD_REL` of the fp64 oracle, or within three times the fp32 oracle's own distance from it (the two fp32
+    evaluations do not flip at the same near-ties)."""
+    import copy
+    oracle32 = copy.deepcopy(oracle).float().train()
     model.train()
     oracle.train()
     dev_data = data.to(DEV)
@@ -53,23 +62,30 @@ def compare_train_step(name, model, oracle, data, loss_ours, loss_ref, grad_fact
     assert abs(l_ours.item() - l_ref.item()) < LOGIT_REL * max(1.0, abs(l_ref.item()))
     l_ref.backward()
     l_ours.backward()
+    loss_ref(oracle32(data), data.y).backward()
+    floor_grads = dict(oracle32.named_parameters())
     ref_grads = dict(oracle.named_parameters())
     # Some gradients vanish analytically (a BatchNorm bias that only feeds another BatchNorm through a per-channel constant:
     # the fp64 oracle returns ~1e-16 for them).  Each tensor is therefore measured against max(its own scale, 1e-3 x the
     # largest gradient scale of the network), the rule tests/test_gpu_nn.py uses for the reference fixtures.
     net_scale = max(float(g.grad.abs().max()) for g in ref_grads.values() if g.grad is not None)
-    worst, worst_name = 0.0, None
+    worst, worst_name, worst_floor, worst_margin = 0.0, None, 0.0, 0.0
     for pname, p in model.named_parameters():
         if ref_grads[pname].grad is None:
             assert p.grad is None, pname              # VectorNonLin.bias under BatchNorm
             continue
         assert p.grad is not None, pname
         ref_g = ref_grads[pname].grad
-        err = float((p.grad.cpu().double() - ref_g).abs().max()) / max(float(ref_g.abs().max()), 1e-3 * net_scale)
+        denom = max(float(ref_g.abs().max()), 1e-3 * net_scale)
+        err = float((p.grad.cpu().double() - ref_g).abs().max()) / denom
+        floor = float((floor_grads[pname].grad.double() - ref_g).abs().max()) / denom
         if err > worst:
-            worst, worst_name = err, pname
+            worst, worst_name, worst_floor = err, pname, floor
+        worst_margin = max(worst_margin, err / max(grad_factor * GRAD_REL, 3 * floor))
+        assert err < max(grad_factor * GRAD_REL, 3 * floor), (pname, err, floor)
     report(f'{name}.grad_worst[{worst_name}]', worst)
-    assert worst < grad_factor * GRAD_REL, worst_name
+    report(f'{name}.grad_worst.fp32_oracle_floor_same_tensor', worst_floor)
+    report(f'{name}.grad_worst_fraction_of_allowance', worst_margin)
     return logits, ref
 
 
@@ -111,6 +127,28 @@ def test_config4_scanobjectnn_shape_no_normals_vs_oracle():
     report('config4_infer_4x2048_nonormal.logits_eval.per_element', elem_err(logits.cpu(), ref))
     assert report('config4_infer_4x2048_nonormal.logits_eval', rel_err(logits.cpu(), ref)) < LOGIT_REL
     assert torch.equal(logits.argmax(1).cpu(), ref.argmax(1))
+
+
+def test_config1_single_tf32_products_opt_in_mode_tolerance():
+    """The opt-in GEMM mode of `bench.py --gemm-mode 1` (one TF32 product per multiply-add instead of the 3xTF32 split; the
+    north_star allows a looser, stated tolerance for reduced-precision MLPs): logits of configs[1] (8 x 1024) within 2e-2 of
+    the fp64 oracle, tensor-scaled.  The default mode stays the fp32-grade one."""
+    D = dc()
+    lib = D._lib.load()
+    data = D.utils.synthetic_batch(8, 1024, config=2, num_classes=40)
+    build = lambda m: m.DeltaNetClassification(3, 40, num_neighbors=20)   # noqa: E731
+    model, oracle = pair(build, build, 1)
+    model.train()
+    oracle.train()
+    assert lib.dc_get_gemm_mode() == 3
+    try:
+        lib.dc_set_gemm_mode(1)
+        logits = model(data.to(DEV))
+    finally:
+        lib.dc_set_gemm_mode(3)
+    with torch.no_grad():
+        ref = oracle(data.double())
+    assert report('config1_cls_8x1024.logits_train.gemm_mode1_tf32', rel_err(logits.detach().cpu(), ref)) < 2e-2
 
 
 def test_graphed_inference_matches_eager():

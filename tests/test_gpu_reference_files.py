@@ -73,7 +73,7 @@ def test_reference_test_files_pass_against_this_package():
     if tests is None:
         pytest.skip('no reference checkout and no staged oracle/_ref/test')
     env = dict(os.environ, PYTHONPATH=STANDINS + os.pathsep + ROOT + os.pathsep + os.environ.get('PYTHONPATH', ''))
-    proc = subprocess.run([sys.executable, '-m', 'pytest', tests, '-q', '-p', 'refshim', '-p', 'no:cacheprovider', '-x'],
+    proc = subprocess.run([sys.executable, '-m', 'pytest', tests, '-q', '-p', 'refshim', '-p', 'no:cacheprovider'],
                           cwd=ROOT, env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=1500)
     report = os.path.join(ROOT, 'gpurun_out', 'reference_tests.log')
     try:
