@@ -87,8 +87,8 @@ _SIGNATURES = {
     'dc_linear_fwd': [_P, _L, _P, _L, _P, _L, _I, _I, _P, _L, _P, _Z, _P],
     'dc_linear_bwd_input': [_P, _L, _P, _L, _L, _I, _I, _P, _L, _P, _Z, _P],
     'dc_linear_bwd_weight': [_P, _L, _P, _L, _L, _I, _I, _P, _L, _P, _Z, _P],
-    'dc_expand_vec_weight': [_P, _I, _I, _P, _P],
-    'dc_fold_vec_weight_grad': [_P, _I, _I, _P, _P],
+    'dc_expand_vec_weight': [_P, _I, _I, _I, _P, _P, _P],
+    'dc_fold_vec_weight_grad': [_P, _I, _I, _I, _P, _P, _P],
 }
 _RESTYPES = {'dc_launch_count': ctypes.c_longlong, 'dc_reset_launch_count': None,
              'dc_ell_transpose_ws_bytes': _Z, 'dc_build_ws_bytes': _Z, 'dc_build_ws_min_bytes': _Z, 'dc_colreduce_ws_bytes': _Z,
@@ -130,7 +130,14 @@ def stream_ptr():
 
 
 def ptr(t):
-    return None if t is None else t.data_ptr()
+    """Device address of a tensor (None stays None).  A CPU tensor — e.g. a module parameter that was never moved to the
+    device — would hand the kernels a host address: refused here, once, for every entry point."""
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise DeltaConvLibraryError(f"expected a CUDA tensor, got a {t.dtype} tensor of shape {tuple(t.shape)} on {t.device} "
+                                    f"(deltaconv_b200 has no CPU path; move the module / data to the GPU)")
+    return t.data_ptr()
 
 
 def check(t, dtype, name):

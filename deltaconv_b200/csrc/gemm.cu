@@ -196,25 +196,33 @@ int thin_dw_chunks(long long M) {
 // W [Cout, 2K] = [W1 | W2]  ->  W' [2Cout, 2K] = [[W1, -W2], [W2, W1]]
 // so that VectorMLP's Linear on I_J(v) (deltaconv.py:68, operators.py:19-21) becomes one plain
 // GEMM on the [N, 2K] view of the interleaved vector field: [v_x | v_y] W'^T = [out_x | out_y].
-__global__ void expand_vec_weight_kernel(const float* __restrict__ W, int Cout, int K, float* __restrict__ We) {
+// Kp >= K is the padded half-width of W' ([2Cout, 2Kp], columns [K, Kp) and [Kp+K, 2Kp) zero): the vector concatenation it
+// multiplies is stored with a row pitch that is a multiple of 4 floats so that every kernel touching it takes its 16-byte path.
+// `col` (nullable) maps source column p of a half to its column in the padded half: the concatenation's blocks each start
+// at a multiple of 4 floats.  W' must be zero-filled beforehand when Kp > K (the pad columns are not touched here).
+__global__ void expand_vec_weight_kernel(const float* __restrict__ W, int Cout, int K, int Kp, const int* __restrict__ col,
+                                         float* __restrict__ We) {
     long long total = (long long)Cout * K;
     long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
     if (t >= total) return;
     int o = (int)(t / K), p = (int)(t - (long long)o * K);
-    float w1 = W[(size_t)o * 2 * K + p], w2 = W[(size_t)o * 2 * K + K + p];
-    We[(size_t)o * 2 * K + p] = w1;
-    We[(size_t)o * 2 * K + K + p] = -w2;
-    We[(size_t)(Cout + o) * 2 * K + p] = w2;
-    We[(size_t)(Cout + o) * 2 * K + K + p] = w1;
+    const float w1 = W[(size_t)o * 2 * K + p], w2 = W[(size_t)o * 2 * K + K + p];
+    const int q = col ? __ldg(col + p) : p;
+    We[(size_t)o * 2 * Kp + q] = w1;
+    We[(size_t)o * 2 * Kp + Kp + q] = -w2;
+    We[(size_t)(Cout + o) * 2 * Kp + q] = w2;
+    We[(size_t)(Cout + o) * 2 * Kp + Kp + q] = w1;
 }
 
-__global__ void fold_vec_weight_grad_kernel(const float* __restrict__ dWe, int Cout, int K, float* __restrict__ dW) {
+__global__ void fold_vec_weight_grad_kernel(const float* __restrict__ dWe, int Cout, int K, int Kp, const int* __restrict__ col,
+                                            float* __restrict__ dW) {
     long long total = (long long)Cout * K;
     long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
     if (t >= total) return;
     int o = (int)(t / K), p = (int)(t - (long long)o * K);
-    dW[(size_t)o * 2 * K + p] = dWe[(size_t)o * 2 * K + p] + dWe[(size_t)(Cout + o) * 2 * K + K + p];
-    dW[(size_t)o * 2 * K + K + p] = dWe[(size_t)(Cout + o) * 2 * K + p] - dWe[(size_t)o * 2 * K + K + p];
+    const int q = col ? __ldg(col + p) : p;
+    dW[(size_t)o * 2 * K + p] = dWe[(size_t)o * 2 * Kp + q] + dWe[(size_t)(Cout + o) * 2 * Kp + Kp + q];
+    dW[(size_t)o * 2 * K + K + p] = dWe[(size_t)(Cout + o) * 2 * Kp + q] - dWe[(size_t)o * 2 * Kp + Kp + q];
 }
 
 }  // namespace
@@ -295,15 +303,20 @@ extern "C" int dc_linear_bwd_weight(const float* dY, int64_t ld_dy, const float*
     return run_gemm(g, false, true, ws, ws_bytes, (cudaStream_t)stream);
 }
 
-extern "C" int dc_expand_vec_weight(const float* W, int Cout, int K, float* W_expanded, void* stream) {
+extern "C" int dc_expand_vec_weight(const float* W, int Cout, int K, int K_padded, const int32_t* col_map_or_null,
+                                    float* W_expanded, void* stream) {
     if (Cout <= 0 || K <= 0) return DC_OK;
-    expand_vec_weight_kernel<<<dc_ceil_div((long long)Cout * K, 256), 256, 0, (cudaStream_t)stream>>>(W, Cout, K, W_expanded);
+    DC_REQUIRE(K_padded >= K, "dc_expand_vec_weight: padded width %d < width %d", K_padded, K);
+    if (K_padded > K) DC_CUDA(cudaMemsetAsync(W_expanded, 0, (size_t)4 * Cout * K_padded * sizeof(float), (cudaStream_t)stream));
+    expand_vec_weight_kernel<<<dc_ceil_div((long long)Cout * K, 256), 256, 0, (cudaStream_t)stream>>>(W, Cout, K, K_padded, col_map_or_null, W_expanded);
     return dc_check_launch("dc_expand_vec_weight");
 }
 
-extern "C" int dc_fold_vec_weight_grad(const float* dW_expanded, int Cout, int K, float* dW, void* stream) {
+extern "C" int dc_fold_vec_weight_grad(const float* dW_expanded, int Cout, int K, int K_padded, const int32_t* col_map_or_null,
+                                       float* dW, void* stream) {
     if (Cout <= 0 || K <= 0) return DC_OK;
-    fold_vec_weight_grad_kernel<<<dc_ceil_div((long long)Cout * K, 256), 256, 0, (cudaStream_t)stream>>>(dW_expanded, Cout, K, dW);
+    DC_REQUIRE(K_padded >= K, "dc_fold_vec_weight_grad: padded width %d < width %d", K_padded, K);
+    fold_vec_weight_grad_kernel<<<dc_ceil_div((long long)Cout * K, 256), 256, 0, (cudaStream_t)stream>>>(dW_expanded, Cout, K, K_padded, col_map_or_null, dW);
     return dc_check_launch("dc_fold_vec_weight_grad");
 }
 

@@ -55,7 +55,7 @@ class DeltaConv(torch.nn.Module):
 
         # vector stream (deltaconv.py:64-68)
         if self.v_mlp is not None:
-            v_cat = ops.vector_cat(v, div_curl, x, grad)
+            v_cat = ops.vector_cat(v, div_curl, x, grad, pad=True)
             first = self.v_mlp[0]
             v = first[1](ops.vector_linear_with_rotation(v_cat, first[0].weight))
             for block in list(self.v_mlp)[1:]:

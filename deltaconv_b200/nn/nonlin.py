@@ -35,7 +35,7 @@ class VectorNonLin(torch.nn.Module):
 
     def __init__(self, in_channels, nonlin=torch.nn.ReLU(), batchnorm=None):
         super().__init__()
-        self.bias = torch.nn.Parameter(torch.Tensor(in_channels))
+        self.bias = torch.nn.Parameter(torch.empty(in_channels))      # zero-filled by reset_parameters (nonlin.py:50,58)
         self.nonlin = nonlin
         self.batchnorm = batchnorm
         self.reset_parameters()

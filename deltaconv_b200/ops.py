@@ -18,10 +18,10 @@ _workspaces = {}
 _CHECK_LAYOUT = bool(int(os.environ.get('DC_CHECK_LAYOUT', '0')))
 
 
-def workspace(nbytes, device):
-    """Cached scratch buffer (one per device, grows on demand).  All kernels that use it are
-    enqueued on the current stream, so successive users are ordered."""
-    key = (device.type, device.index)
+def workspace(nbytes, device, slot=0):
+    """Cached scratch buffer (one per device and slot, grows on demand).  All kernels that use slot 0 are enqueued on the
+    current stream, so successive users are ordered; slot 1 belongs to the side stream of `forked_backward`."""
+    key = (device.type, device.index, slot)
     buf = _workspaces.get(key)
     if buf is None or buf.numel() < nbytes:
         buf = torch.empty(max(int(nbytes), 1 << 20), dtype=torch.uint8, device=device)
@@ -431,23 +431,45 @@ class _ScalarCat(torch.autograd.Function):
         return dcat[:, :C], dv, None
 
 
+_colmaps = {}
+
+
+def _vector_cat_layout(Cin, Cout, pad, device):
+    """(column of the hodge block, column of the grad block, total width, column map or None)."""
+    if not pad or (Cin % 4 == 0 and Cout % 4 == 0):
+        return Cin, 2 * Cin, 2 * Cin + Cout, None
+    Cp = (Cin + 3) // 4 * 4
+    W = 2 * Cp + (Cout + 3) // 4 * 4
+    key = (Cin, Cout, device.index)
+    if key not in _colmaps:
+        _colmaps[key] = torch.cat([torch.arange(Cin), Cp + torch.arange(Cin), 2 * Cp + torch.arange(Cout)]).to(device=device, dtype=_I32)
+    return Cp, 2 * Cp, W, _colmaps[key]
+
+
 class _VectorCat(torch.autograd.Function):
     """[v | hodge_laplacian(v) | grad x'] (deltaconv.py:66, operators.py:35-46) from the div/curl
-    already computed for the scalar stream."""
+    already computed for the scalar stream.  pad=True: every block starts at a multiple of 4 floats (the first layer's widths
+    3, 3, 64 would otherwise put the 64-wide block at column 6 and send the kernels that read or write it down their scalar
+    path); the columns in between are zero and meet zero weight columns in the GEMM."""
 
     @staticmethod
-    def forward(ctx, v, dc, x_new, op):
+    def forward(ctx, v, dc, x_new, op, pad=False):
         v, ldv = _mat(v, 'v')
         dc, ld_dc = _mat(dc, 'div_curl')
         x_new, ldx = _mat(x_new, 'x')
         g = op.graph
         Cin, Cout = v.size(1), x_new.size(1)
-        W = 2 * Cin + Cout
-        cat = torch.empty(2 * g.N, W, dtype=_F32, device=v.device)
+        c_h, c_g, W, col_map = _vector_cat_layout(Cin, Cout, pad, v.device)
+        if col_map is None:
+            cat = torch.empty(2 * g.N, W, dtype=_F32, device=v.device)
+        else:
+            cat = torch.zeros(2 * g.N, W, dtype=_F32, device=v.device)
         call('dc_hodge_fwd', ptr(g.idx), ptr(op.G), g.N, g.k, Cin, ptr(dc), ld_dc, dc.data_ptr() + 4 * Cin, ld_dc,
-             cat.data_ptr() + 4 * Cin, W, ptr(v), ldv, cat.data_ptr(), W, *g.clouds())
-        call('dc_grad_fwd', ptr(g.idx), ptr(op.G), g.N, g.k, Cout, ptr(x_new), ldx, cat.data_ptr() + 8 * Cin, W, *g.clouds())
-        ctx.op, ctx.Cin, ctx.Cout = op, Cin, Cout
+             cat.data_ptr() + 4 * c_h, W, ptr(v), ldv, cat.data_ptr(), W, *g.clouds())
+        call('dc_grad_fwd', ptr(g.idx), ptr(op.G), g.N, g.k, Cout, ptr(x_new), ldx, cat.data_ptr() + 4 * c_g, W, *g.clouds())
+        ctx.op, ctx.Cin, ctx.Cout, ctx.c_h, ctx.c_g = op, Cin, Cout, c_h, c_g
+        if col_map is not None:
+            cat._dc_colmap = col_map
         return cat
 
     @staticmethod
@@ -456,19 +478,21 @@ class _VectorCat(torch.autograd.Function):
         dcat, ld = _mat(dcat.contiguous(), 'grad_output')
         in_ptr, in_edge = g.transpose()
         ddc = torch.empty(g.N, 2 * Cin, dtype=_F32, device=dcat.device)
-        call('dc_hodge_bwd', ptr(in_ptr), ptr(in_edge), ptr(op.G), g.N, g.k, Cin, dcat.data_ptr() + 4 * Cin, ld,
+        call('dc_hodge_bwd', ptr(in_ptr), ptr(in_edge), ptr(op.G), g.N, g.k, Cin, dcat.data_ptr() + 4 * ctx.c_h, ld,
              ptr(ddc), 2 * Cin, ddc.data_ptr() + 4 * Cin, 2 * Cin, *g.clouds())
         dx = torch.empty(g.N, Cout, dtype=_F32, device=dcat.device)
-        call('dc_grad_bwd', ptr(in_ptr), ptr(in_edge), ptr(op.G), g.N, g.k, Cout, dcat.data_ptr() + 8 * Cin, ld, ptr(dx), Cout, *g.clouds())
-        return dcat[:, :Cin], ddc, dx, None
+        call('dc_grad_bwd', ptr(in_ptr), ptr(in_edge), ptr(op.G), g.N, g.k, Cout, dcat.data_ptr() + 4 * ctx.c_g, ld, ptr(dx), Cout, *g.clouds())
+        return dcat[:, :Cin], ddc, dx, None, None
 
 
 def scalar_cat(x, v, div_op):
     return _ScalarCat.apply(x, v, div_op)
 
 
-def vector_cat(v, div_curl, x_new, grad_op):
-    return _VectorCat.apply(v, div_curl, x_new, grad_op)
+def vector_cat(v, div_curl, x_new, grad_op, pad=False):
+    """[v | hodge_laplacian(v) | grad x'] as one [2N, 2 Cin + Cout] buffer; pad=True starts every block at a multiple of 4
+    floats, with zero columns in between (the result carries the column map ops.vector_linear_with_rotation needs)."""
+    return _VectorCat.apply(v, div_curl, x_new, grad_op, pad)
 
 
 def curl_of(v, div_op):
@@ -573,9 +597,48 @@ def join_columns(parts):
 # Linear
 # ------------------------------------------------------------------------------------------------
 
-def _gemm_ws(M, N, K, device):
+def _gemm_ws(M, N, K, device, slot=0):
     nbytes = query('dc_gemm_ws_bytes', M, N, K)
-    return workspace(nbytes, device), nbytes
+    return workspace(nbytes, device, slot), nbytes
+
+
+# The input gradient and the weight gradient of a Linear are independent products.  While a step is being CAPTURED into a
+# CUDA graph the weight gradient is issued on a side stream (a parallel branch of the graph): the persistent GEMM kernels end
+# in a partially filled wave on the narrow layers (32768 x 64 is 1.7 waves of tiles), and the other product's CTAs fill the
+# SMs that fall idle.  Eager launches stay on one stream (the extra event calls would cost the host more than they gain).
+FORK_BACKWARD_GEMMS = not os.environ.get('DC_NO_FORK')
+_side_streams = {}
+
+
+def _linear_backward_pair(dy, ld, weight, ldw, x, ldx, M, K, Nout, want_dx, want_dw):
+    """(dX, dW) of Y = X W^T from dY; the two products run concurrently under graph capture."""
+    dev = dy.device
+    dx = torch.empty(M, K, dtype=_F32, device=dev) if want_dx else None
+    dw = torch.empty(Nout, K, dtype=_F32, device=dev) if want_dw else None
+    forkable = FORK_BACKWARD_GEMMS and want_dx and want_dw and M >= 4096
+    fork = forkable and torch.cuda.is_current_stream_capturing()
+    if forkable and not fork:
+        _gemm_ws(Nout, K, M, dev, slot=1)           # the side stream's scratch exists before any capture (warm-up steps are eager)
+    if want_dw:
+        ws_w, nb_w = _gemm_ws(Nout, K, M, dev, slot=1 if fork else 0)
+    if want_dx:
+        ws_x, nb_x = _gemm_ws(M, K, Nout, dev)
+    if fork:
+        cur = torch.cuda.current_stream()
+        side = _side_streams.get(dev.index)
+        if side is None:
+            side = _side_streams[dev.index] = torch.cuda.Stream(device=dev)
+        side.wait_stream(cur)
+        with torch.cuda.stream(side):
+            call('dc_linear_bwd_weight', ptr(dy), ld, ptr(x), ldx, M, K, Nout, ptr(dw), K, ptr(ws_w), nb_w)
+        call('dc_linear_bwd_input', ptr(dy), ld, ptr(weight), ldw, M, K, Nout, ptr(dx), K, ptr(ws_x), nb_x)
+        cur.wait_stream(side)
+        return dx, dw
+    if want_dx:
+        call('dc_linear_bwd_input', ptr(dy), ld, ptr(weight), ldw, M, K, Nout, ptr(dx), K, ptr(ws_x), nb_x)
+    if want_dw:
+        call('dc_linear_bwd_weight', ptr(dy), ld, ptr(x), ldx, M, K, Nout, ptr(dw), K, ptr(ws_w), nb_w)
+    return dx, dw
 
 
 class _Linear(torch.autograd.Function):
@@ -602,15 +665,8 @@ class _Linear(torch.autograd.Function):
         weight, ldw = _mat(weight)
         dy, ld = _mat(dy, 'grad_output')
         M, K, Nout = x.size(0), x.size(1), weight.size(0)
-        dx = dw = db = None
-        if ctx.needs_input_grad[0]:
-            dx = torch.empty(M, K, dtype=_F32, device=dy.device)
-            ws, nb = _gemm_ws(M, K, Nout, dy.device)
-            call('dc_linear_bwd_input', ptr(dy), ld, ptr(weight), ldw, M, K, Nout, ptr(dx), K, ptr(ws), nb)
-        if ctx.needs_input_grad[1]:
-            dw = torch.empty(Nout, K, dtype=_F32, device=dy.device)
-            ws, nb = _gemm_ws(Nout, K, M, dy.device)
-            call('dc_linear_bwd_weight', ptr(dy), ld, ptr(x), ldx, M, K, Nout, ptr(dw), K, ptr(ws), nb)
+        db = None
+        dx, dw = _linear_backward_pair(dy, ld, weight, ldw, x, ldx, M, K, Nout, ctx.needs_input_grad[0], ctx.needs_input_grad[1])
         if ctx.has_bias and ctx.needs_input_grad[2]:
             db = torch.empty(Nout, dtype=_F32, device=dy.device)
             nb = query('dc_colreduce_ws_bytes', Nout)
@@ -624,33 +680,38 @@ def linear(x, weight, bias=None):
 
 
 class _ExpandVecWeight(torch.autograd.Function):
-    """[W1 | W2] -> [[W1, -W2], [W2, W1]] — folds I_J (operators.py:19-21) into the weights."""
+    """[W1 | W2] -> [[W1, -W2], [W2, W1]] — folds I_J (operators.py:19-21) into the weights.  `Kp` >= K is the width of the
+    (padded) operand it multiplies, `col_map` the operand column of every weight column."""
 
     @staticmethod
-    def forward(ctx, weight):
+    def forward(ctx, weight, Kp, col_map):
         weight = _f32(weight, 'weight').contiguous()
         Cout, K2 = weight.shape
-        out = torch.empty(2 * Cout, K2, dtype=_F32, device=weight.device)
-        call('dc_expand_vec_weight', ptr(weight), Cout, K2 // 2, ptr(out))
+        out = torch.empty(2 * Cout, 2 * Kp, dtype=_F32, device=weight.device)
+        call('dc_expand_vec_weight', ptr(weight), Cout, K2 // 2, Kp, ptr(col_map), ptr(out))
+        ctx.K, ctx.col_map = K2 // 2, col_map
         return out
 
     @staticmethod
     def backward(ctx, dwe):
         dwe = dwe.contiguous()
-        Cout, K2 = dwe.size(0) // 2, dwe.size(1)
-        dw = torch.empty(Cout, K2, dtype=_F32, device=dwe.device)
-        call('dc_fold_vec_weight_grad', ptr(dwe), Cout, K2 // 2, ptr(dw))
-        return dw
+        Cout, Kp, K = dwe.size(0) // 2, dwe.size(1) // 2, ctx.K
+        dw = torch.empty(Cout, 2 * K, dtype=_F32, device=dwe.device)
+        call('dc_fold_vec_weight_grad', ptr(dwe), Cout, K, Kp, ptr(ctx.col_map), ptr(dw))
+        return dw, None, None
 
 
 def vector_linear_with_rotation(v_cat, weight):
-    """Linear(I_J(v_cat)) (deltaconv.py:68) as one GEMM on the [N, 2K] view of the interleaved
-    field with the expanded weight; v_cat [2N,K], weight [Cout,2K] -> [2N,Cout]."""
-    rows, K = v_cat.shape
-    if weight.size(1) != 2 * K:
-        raise _lib.DeltaConvLibraryError(f"vector Linear: weight expects {weight.size(1)} inputs, I_J(v) has {2 * K}")
-    we = _ExpandVecWeight.apply(weight)
-    out = _Linear.apply(v_cat.contiguous().view(rows // 2, 2 * K), we, None)
+    """Linear(I_J(v_cat)) (deltaconv.py:68) as one GEMM on the [N, 2K] view of the interleaved field with the expanded weight;
+    v_cat [2N,Kp], weight [Cout,2K] -> [2N,Cout].  A `v_cat` from ops.vector_cat(pad=True) carries its column map
+    (`_dc_colmap`): its blocks start at multiples of 4 floats, the columns in between are zero."""
+    rows, Kp = v_cat.shape
+    K = weight.size(1) // 2
+    col_map = getattr(v_cat, '_dc_colmap', None)
+    if weight.size(1) != 2 * K or (Kp != K and (col_map is None or col_map.numel() != K)):
+        raise _lib.DeltaConvLibraryError(f"vector Linear: weight expects {weight.size(1)} inputs, I_J(v) has {2 * Kp}")
+    we = _ExpandVecWeight.apply(weight, Kp, col_map)
+    out = _Linear.apply(v_cat.contiguous().view(rows // 2, 2 * Kp), we, None)
     return out.view(rows, weight.size(0))
 
 
@@ -785,15 +846,7 @@ class _LinearBNAct(torch.autograd.Function):
         ws = workspace(nb, dev)
         call('dc_bn_act_bwd', ptr(y), C, ptr(dout), ldd, M, C, ptr(mean), ptr(invstd), ptr(gamma), ptr(beta), float(ctx.slope), 1,
              ptr(dgamma), ptr(dbeta), ptr(dy), C, ptr(ws), nb)
-        dx = dw = None
-        if ctx.needs_input_grad[0]:
-            dx = torch.empty(M, K, dtype=_F32, device=dev)
-            ws, nb = _gemm_ws(M, K, C, dev)
-            call('dc_linear_bwd_input', ptr(dy), C, ptr(weight), ldw, M, K, C, ptr(dx), K, ptr(ws), nb)
-        if ctx.needs_input_grad[1]:
-            dw = torch.empty(C, K, dtype=_F32, device=dev)
-            ws, nb = _gemm_ws(C, K, M, dev)
-            call('dc_linear_bwd_weight', ptr(dy), C, ptr(x), ldx, M, K, C, ptr(dw), K, ptr(ws), nb)
+        dx, dw = _linear_backward_pair(dy, C, weight, ldw, x, ldx, M, K, C, ctx.needs_input_grad[0], ctx.needs_input_grad[1])
         return (dx, dw, dgamma if gamma is not None else None, dbeta if beta is not None else None,
                 dout if ctx.has_add else None, None, None, None)
 
@@ -849,6 +902,8 @@ class _VecNonLin(torch.autograd.Function):
 
 
 def vec_nonlin(v, bias, bn):
+    if bn is None:
+        _f32(bias, 'VectorNonLin.bias')              # a parameter left on the CPU would hand the kernel a host address
     if bn is not None:
         return _VecNonLin.apply(v, bn.weight, bn.bias, None, bn)
     return _VecNonLin.apply(v, None, None, bias, None)
@@ -1089,15 +1144,7 @@ class _LinearBNActPool(torch.autograd.Function):
         ws = workspace(nb, dev)
         call('dc_bn_act_pool_bwd', ptr(y), C, M, C, ptr(cloud_ptr), ctx.B, ptr(arg), dmax, ld, dmean, ld,
              ptr(mean), ptr(invstd), ptr(gamma), ptr(beta), float(ctx.slope), ptr(dgamma), ptr(dbeta), ptr(dy), C, ptr(ws), nb)
-        dx = dw = None
-        if ctx.needs_input_grad[0]:
-            dx = torch.empty(M, K, dtype=_F32, device=dev)
-            ws, nb = _gemm_ws(M, K, C, dev)
-            call('dc_linear_bwd_input', ptr(dy), C, ptr(weight), ldw, M, K, C, ptr(dx), K, ptr(ws), nb)
-        if ctx.needs_input_grad[1]:
-            dw = torch.empty(C, K, dtype=_F32, device=dev)
-            ws, nb = _gemm_ws(C, K, M, dev)
-            call('dc_linear_bwd_weight', ptr(dy), C, ptr(x), ldx, M, K, C, ptr(dw), K, ptr(ws), nb)
+        dx, dw = _linear_backward_pair(dy, C, weight, ldw, x, ldx, M, K, C, ctx.needs_input_grad[0], ctx.needs_input_grad[1])
         return (dx, dw, dgamma if gamma is not None else None, dbeta if beta is not None else None) + (None,) * 5
 
 

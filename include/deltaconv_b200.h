@@ -285,9 +285,13 @@ int dc_linear_bwd_input(const float* dY, int64_t ld_dy, const float* W, int64_t 
                         float* dX, int64_t ld_dx, void* ws, size_t ws_bytes, void* stream);
 int dc_linear_bwd_weight(const float* dY, int64_t ld_dy, const float* X, int64_t ldx, int64_t M, int K, int Nout,
                          float* dW, int64_t ld_dw, void* ws, size_t ws_bytes, void* stream);
-/* I_J folded into the weights (operators.py:19-21, deltaconv.py:68): W [Cout,2K] -> [[W1,-W2],[W2,W1]] */
-int dc_expand_vec_weight(const float* W, int Cout, int K, float* W_expanded, void* stream);
-int dc_fold_vec_weight_grad(const float* dW_expanded, int Cout, int K, float* dW, void* stream);
+/* I_J folded into the weights (operators.py:19-21, deltaconv.py:68): W [Cout,2K] -> [[W1,-W2],[W2,W1]] as [2Cout, 2*K_padded].
+ * K_padded > K: the operand's column blocks are padded to multiples of 4 floats; col_map [K] (device, nullable = identity)
+ * gives the padded column of every source column, the remaining columns of W_expanded are zero. */
+int dc_expand_vec_weight(const float* W, int Cout, int K, int K_padded, const int32_t* col_map_or_null,
+                         float* W_expanded, void* stream);
+int dc_fold_vec_weight_grad(const float* dW_expanded, int Cout, int K, int K_padded, const int32_t* col_map_or_null,
+                            float* dW, void* stream);
 
 #ifdef __cplusplus
 }

@@ -6,7 +6,9 @@ Random inputs: the reference's tests seed the CPU generator (`torch.manual_seed(
 that sample only (the gauge-equivariance check of test_build_grad_div: the fp64 oracle itself differs between gauges by
 1e-2 on other samples of the same construction, tests/test_gpu_reference_properties.py).  torch.rand / randn / randint /
 randperm therefore keep drawing from the CPU generator, exactly the numbers of the reference's own runs, and the result is
-moved to the device."""
+moved to the device; in-place random fills of device tensors (module initialisers: uniform_, normal_) are drawn the same way,
+so the modules' initial weights are the reference run's too.  torch.FloatTensor([...]) — a CPU tensor whatever the default
+device — builds on the device."""
 import functools
 import os
 import sys
@@ -30,7 +32,48 @@ def _cpu_draw(fn):
     return draw
 
 
+def _cpu_fill(name):
+    original = getattr(torch.Tensor, name)
+
+    @functools.wraps(original)
+    def fill(self, *args, **kwargs):
+        if not self.is_cuda:
+            return original(self, *args, **kwargs)
+        with torch.no_grad():
+            drawn = original(torch.empty(self.shape, dtype=self.dtype, device='cpu'), *args, **kwargs)
+            self.copy_(drawn)
+        return self
+    return fill
+
+
+def _logging_allclose(original, path):
+    """torch.allclose with its outcome unchanged; every comparison's worst excess over its own tolerance is appended to `path`
+    (tests/test_gpu_reference_files.py reads it to report margins, and to judge the one knife-edge assertion of the suite)."""
+    @functools.wraps(original)
+    def allclose(a, b, rtol=1e-5, atol=1e-8, equal_nan=False):
+        ok = original(a, b, rtol=rtol, atol=atol, equal_nan=equal_nan)
+        try:
+            if a.is_floating_point() and b.is_floating_point() and a.numel():
+                import inspect
+                frame = inspect.stack()[1]
+                diff = (a - b).abs()
+                excess = float((diff - (atol + rtol * b.abs())).max())
+                with open(path, 'a') as f:
+                    f.write(f'{os.path.basename(frame.filename)}:{frame.lineno}\t{int(ok)}\tmax_diff={float(diff.max()):.3e}\t'
+                            f'excess={excess:.3e}\tatol={atol:g}\tscale={float(b.abs().max()):.3e}\n')
+        except Exception:
+            pass
+        return ok
+    return allclose
+
+
+if os.environ.get('DC_REFSHIM_LOG'):
+    torch.allclose = _logging_allclose(torch.allclose, os.environ['DC_REFSHIM_LOG'])
+
 if torch.cuda.is_available():
     torch.set_default_device('cuda')
     for _name in ('rand', 'randn', 'randint', 'randperm'):
         setattr(torch, _name, _cpu_draw(getattr(torch, _name)))
+    for _name in ('uniform_', 'normal_'):
+        setattr(torch.Tensor, _name, _cpu_fill(_name))
+    torch.FloatTensor = lambda data: torch.tensor(data, dtype=torch.float32)

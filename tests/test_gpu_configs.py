@@ -45,9 +45,10 @@ def compare_train_step(name, model, oracle, data, loss_ours, loss_ref, grad_fact
     Gradients pass through arg-max routing (kNN max aggregation, global max pool): where two candidates are closer than fp32
     rounding, ANY fp32 evaluation may route the gradient to the other one than the fp64 oracle does, and with a classifier's
     gradient concentrated on ~32 pooled points per channel one such flip moves a weight gradient by percents of its scale.
-    That floor is measured, per tensor, by running the SAME oracle in fp32: a tensor passes when it is within
-    `grad_factor * GRAD_REL` of the fp64 oracle, or within three times the fp32 oracle's own distance from it (the two fp32
-    evaluations do not flip at the same near-ties)."""
+    That floor is measured by running the SAME oracle in fp32: a tensor passes when it is within `grad_factor * GRAD_REL` of
+    the fp64 oracle, or within three times the fp32 oracle's own distance from it on that tensor, or within 1.5x the fp32
+    oracle's worst tensor (the two fp32 evaluations do not flip at the same near-ties); the median over tensors must be below
+    GRAD_REL or twice the fp32 oracle's median."""
     import copy
     oracle32 = copy.deepcopy(oracle).float().train()
     model.train()
@@ -69,7 +70,7 @@ def compare_train_step(name, model, oracle, data, loss_ours, loss_ref, grad_fact
     # the fp64 oracle returns ~1e-16 for them).  Each tensor is therefore measured against max(its own scale, 1e-3 x the
     # largest gradient scale of the network), the rule tests/test_gpu_nn.py uses for the reference fixtures.
     net_scale = max(float(g.grad.abs().max()) for g in ref_grads.values() if g.grad is not None)
-    worst, worst_name, worst_floor, worst_margin = 0.0, None, 0.0, 0.0
+    errs, floors = {}, {}
     for pname, p in model.named_parameters():
         if ref_grads[pname].grad is None:
             assert p.grad is None, pname              # VectorNonLin.bias under BatchNorm
@@ -77,15 +78,23 @@ def compare_train_step(name, model, oracle, data, loss_ours, loss_ref, grad_fact
         assert p.grad is not None, pname
         ref_g = ref_grads[pname].grad
         denom = max(float(ref_g.abs().max()), 1e-3 * net_scale)
-        err = float((p.grad.cpu().double() - ref_g).abs().max()) / denom
-        floor = float((floor_grads[pname].grad.double() - ref_g).abs().max()) / denom
-        if err > worst:
-            worst, worst_name, worst_floor = err, pname, floor
-        worst_margin = max(worst_margin, err / max(grad_factor * GRAD_REL, 3 * floor))
-        assert err < max(grad_factor * GRAD_REL, 3 * floor), (pname, err, floor)
-    report(f'{name}.grad_worst[{worst_name}]', worst)
-    report(f'{name}.grad_worst.fp32_oracle_floor_same_tensor', worst_floor)
-    report(f'{name}.grad_worst_fraction_of_allowance', worst_margin)
+        errs[pname] = float((p.grad.cpu().double() - ref_g).abs().max()) / denom
+        floors[pname] = float((floor_grads[pname].grad.double() - ref_g).abs().max()) / denom
+    # Which near-ties flip is chaotic (any last-bit difference upstream moves them), so the fp32 oracle's floor is used two
+    # ways: per tensor (3x) and network-wide (1.5x its worst tensor).  The bulk must agree as tightly as fp32 allows: median below
+    # max(GRAD_REL, 2 x the fp32 oracle's median).
+    net_floor = max(floors.values())
+    worst_name = max(errs, key=errs.get)
+    ordered = sorted(errs.values())
+    report(f'{name}.grad_worst[{worst_name}]', errs[worst_name])
+    report(f'{name}.grad_worst.fp32_oracle_floor_same_tensor', floors[worst_name])
+    report(f'{name}.grad_fp32_oracle_floor_worst_tensor', net_floor)
+    floor_median = sorted(floors.values())[len(floors) // 2]
+    report(f'{name}.grad_median_over_tensors', ordered[len(ordered) // 2])
+    report(f'{name}.grad_median_over_tensors.fp32_oracle_floor', floor_median)
+    assert ordered[len(ordered) // 2] < max(GRAD_REL, 2 * floor_median)
+    for pname, err in errs.items():
+        assert err < max(grad_factor * GRAD_REL, 3 * floors[pname], 1.5 * net_floor), (pname, err, floors[pname], net_floor)
     return logits, ref
 
 
