@@ -353,7 +353,7 @@ def run_cuda_arm(args):
             flat.zero()
             loss = workload_loss(model(data), data.y)
             loss.backward()
-            flat.all_reduce()
+            flat.all_reduce(defer_average=True)          # SUM over NCCL; FlatSGD folds 1 / world into its update kernel
             opt.step()
             return loss
     else:

@@ -70,8 +70,8 @@ _SIGNATURES = {
     'dc_pool_bwd': [_P, _I, _I, _I, _P, _P, _L, _P, _L, _P, _L, _P],
     'dc_bn_act_pool_fwd': [_P, _L, _P, _I, _I, _P, _P, _P, _P, _F, _P, _L, _P, _L, _P, _P],
     'dc_bn_act_pool_bwd': [_P, _L, _L, _I, _P, _I, _P, _P, _L, _P, _L, _P, _P, _P, _P, _F, _P, _P, _P, _L, _P, _Z, _P],
-    'dc_sgd_step': [_P, _P, _P, _L, _P, _F, _F, _P],
-    'dc_adam_step': [_P, _P, _P, _P, _L, _P, _P, _F, _F, _F, _F, _P],
+    'dc_sgd_step': [_P, _P, _P, _L, _P, _F, _F, _F, _P],
+    'dc_adam_step': [_P, _P, _P, _P, _L, _P, _P, _F, _F, _F, _F, _F, _P],
     'dc_add_rows': [_P, _L, _P, _L, _L, _I, _P, _L, _P],
     'dc_bcast_rows': [_P, _L, _P, _I, _I, _I, _P, _L, _P],
     'dc_set_gemm_mode': [_I],

@@ -259,24 +259,25 @@ __global__ void add_rows_kernel(const float* __restrict__ a, long long lda, cons
 }
 
 // ---- SGD with momentum and weight decay on flat buffers (torch.optim.SGD, dampening 0, no Nesterov) ----------------
-// g' = g + wd * p;  buf = mu * buf + g';  p -= lr * buf.   A zero-initialised buf makes the first step buf = g' as in torch.
-// lr is read from device memory so that a captured step follows learning-rate schedules.
+// g' = gs * g + wd * p;  buf = mu * buf + g';  p -= lr * buf.   A zero-initialised buf makes the first step buf = g' as in torch.
+// lr is read from device memory so that a captured step follows learning-rate schedules.  gs (grad_scale) is 1 / world size
+// after a SUM all-reduce: the averaging costs no pass of its own.
 __global__ void sgd_step_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ buf, long long n,
-                                const float* __restrict__ lr_ptr, float momentum, float weight_decay) {
+                                const float* __restrict__ lr_ptr, float momentum, float weight_decay, float gs) {
     const float lr = __ldg(lr_ptr);
     const long long n4 = n >> 2;
     for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < n4; t += (long long)gridDim.x * blockDim.x) {
         float4 pv = reinterpret_cast<float4*>(p)[t], bv = reinterpret_cast<float4*>(buf)[t];
         const float4 gv = ld_stream4(reinterpret_cast<const float4*>(g) + t);
-        bv.x = fmaf(momentum, bv.x, fmaf(weight_decay, pv.x, gv.x)); pv.x = fmaf(-lr, bv.x, pv.x);
-        bv.y = fmaf(momentum, bv.y, fmaf(weight_decay, pv.y, gv.y)); pv.y = fmaf(-lr, bv.y, pv.y);
-        bv.z = fmaf(momentum, bv.z, fmaf(weight_decay, pv.z, gv.z)); pv.z = fmaf(-lr, bv.z, pv.z);
-        bv.w = fmaf(momentum, bv.w, fmaf(weight_decay, pv.w, gv.w)); pv.w = fmaf(-lr, bv.w, pv.w);
+        bv.x = fmaf(momentum, bv.x, fmaf(weight_decay, pv.x, gs * gv.x)); pv.x = fmaf(-lr, bv.x, pv.x);
+        bv.y = fmaf(momentum, bv.y, fmaf(weight_decay, pv.y, gs * gv.y)); pv.y = fmaf(-lr, bv.y, pv.y);
+        bv.z = fmaf(momentum, bv.z, fmaf(weight_decay, pv.z, gs * gv.z)); pv.z = fmaf(-lr, bv.z, pv.z);
+        bv.w = fmaf(momentum, bv.w, fmaf(weight_decay, pv.w, gs * gv.w)); pv.w = fmaf(-lr, bv.w, pv.w);
         reinterpret_cast<float4*>(buf)[t] = bv;
         reinterpret_cast<float4*>(p)[t] = pv;
     }
     for (long long t = (n4 << 2) + blockIdx.x * (long long)blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x) {
-        const float b = fmaf(momentum, buf[t], fmaf(weight_decay, p[t], g[t]));
+        const float b = fmaf(momentum, buf[t], fmaf(weight_decay, p[t], gs * g[t]));
         buf[t] = b;
         p[t] = fmaf(-lr, b, p[t]);
     }
@@ -287,13 +288,13 @@ __global__ void sgd_step_kernel(float* __restrict__ p, const float* __restrict__
 // The step counter and the learning rate live in device memory (captured steps); adam_advance_kernel increments the counter.
 __global__ void adam_step_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
                                  long long n, const float* __restrict__ lr_ptr, const int* __restrict__ step_ptr,
-                                 float beta1, float beta2, float eps, float weight_decay) {
+                                 float beta1, float beta2, float eps, float weight_decay, float gs) {
     const float t = (float)(__ldg(step_ptr) + 1);
     const float bc1 = 1.f - powf(beta1, t), bc2_sqrt = sqrtf(1.f - powf(beta2, t));
     const float step_size = __ldg(lr_ptr) / bc1;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
         const float pi = p[i];
-        const float gi = fmaf(weight_decay, pi, g[i]);
+        const float gi = fmaf(weight_decay, pi, gs * g[i]);
         const float mi = fmaf(beta1, m[i], (1.f - beta1) * gi);
         const float vi = fmaf(beta2, v[i], (1.f - beta2) * gi * gi);
         m[i] = mi; v[i] = vi;
@@ -1112,20 +1113,21 @@ extern "C" int dc_pool_bwd(const int32_t* cloud_ptr, int B, int N, int C, const 
 }
 
 extern "C" int dc_sgd_step(float* params, const float* grads, float* momentum_buf, int64_t n, const float* lr_device,
-                           float momentum, float weight_decay, void* stream) {
+                           float momentum, float weight_decay, float grad_scale, void* stream) {
     DC_REQUIRE(lr_device != nullptr, "dc_sgd_step: the learning rate is read from device memory");
     DC_REQUIRE(all_aligned16(params, grads, momentum_buf), "dc_sgd_step: buffers must be 16-byte aligned");
     if (n <= 0) return DC_OK;
-    sgd_step_kernel<<<elementwise_grid((n + 3) / 4), 256, 0, (cudaStream_t)stream>>>(params, grads, momentum_buf, n, lr_device, momentum, weight_decay);
+    sgd_step_kernel<<<elementwise_grid((n + 3) / 4), 256, 0, (cudaStream_t)stream>>>(params, grads, momentum_buf, n, lr_device, momentum, weight_decay, grad_scale);
     return dc_check_launch("dc_sgd_step");
 }
 
 extern "C" int dc_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, const float* lr_device,
-                            int32_t* step_device, float beta1, float beta2, float eps, float weight_decay, void* stream) {
+                            int32_t* step_device, float beta1, float beta2, float eps, float weight_decay, float grad_scale,
+                            void* stream) {
     DC_REQUIRE(lr_device != nullptr && step_device != nullptr, "dc_adam_step: learning rate and step counter are read from device memory");
     if (n <= 0) return DC_OK;
     adam_step_kernel<<<elementwise_grid(n), 256, 0, (cudaStream_t)stream>>>(params, grads, exp_avg, exp_avg_sq, n, lr_device, step_device,
-                                                                           beta1, beta2, eps, weight_decay);
+                                                                           beta1, beta2, eps, weight_decay, grad_scale);
     adam_advance_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(step_device);
     return dc_check_launch_n("dc_adam_step", 2);
 }

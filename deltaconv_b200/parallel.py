@@ -29,11 +29,13 @@ class FlatGradients:
             raise ValueError("no trainable parameters")
         self.flat = None
         self.packed = False          # True between pack() and the next zero(): `flat` holds this step's gradients
+        self.pending_scale = 1.0     # factor the optimizer still has to apply to `flat` (1 / world after a SUM all-reduce)
 
     def zero(self):
         for p in self.params:
             p.grad = None
         self.packed = False
+        self.pending_scale = 1.0
 
     def _world(self, group):
         if not (dist.is_available() and dist.is_initialized()):
@@ -59,15 +61,20 @@ class FlatGradients:
         self.packed = True
         return self.flat
 
-    def all_reduce(self, group=None, average=True, sources=None):
-        """Sum (or mean) of all gradients over the ranks with one collective; no-op for a single process."""
+    def all_reduce(self, group=None, average=True, sources=None, defer_average=False):
+        """Sum (or mean) of all gradients over the ranks with one collective; no-op for a single process.
+        defer_average=True leaves the SUM in the buffer and records 1 / world in `pending_scale`: FlatSGD / FlatAdam fold it
+        into their update kernel (any other reader of `p.grad` sees the sum)."""
         world = self._world(group)
         if world == 1:
             return None
         flat = self.pack(sources)
         dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
         if average:
-            flat.div_(world)
+            if defer_average:
+                self.pending_scale = 1.0 / world
+            else:
+                flat.div_(world)
         return flat
 
     def nbytes(self):
@@ -148,7 +155,8 @@ class FlatSGD(torch.optim.Optimizer):
         self.sync_lr()
         group = self.param_groups[0]
         call('dc_sgd_step', self._p.data_ptr(), g.data_ptr(), self._buf.data_ptr(), self._p.numel(), self._lr.data_ptr(),
-             float(group['momentum']), float(group['weight_decay']))
+             float(group['momentum']), float(group['weight_decay']), float(self.flat.pending_scale))
+        self.flat.pending_scale = 1.0
         return loss
 
     def state_dict(self):
@@ -194,7 +202,9 @@ class FlatAdam(FlatSGD):
         self.sync_lr()
         group = self.param_groups[0]
         call('dc_adam_step', self._p.data_ptr(), g.data_ptr(), self._buf.data_ptr(), self._v.data_ptr(), self._p.numel(),
-             self._lr.data_ptr(), self._step.data_ptr(), group['betas'][0], group['betas'][1], group['eps'], group['weight_decay'])
+             self._lr.data_ptr(), self._step.data_ptr(), group['betas'][0], group['betas'][1], group['eps'], group['weight_decay'],
+             float(self.flat.pending_scale))
+        self.flat.pending_scale = 1.0
         return loss
 
     def state_dict(self):

@@ -105,23 +105,16 @@ class GraphedTrainStep(_StaticInputs):
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
         self.graph_fb = torch.cuda.CUDAGraph()
-        self.graph_opt = None
-        self._graph_grads = None
         self._stage = None
-        if self.distributed:
-            # the collective stays outside the graphs: fwd+bwd graph -> pack + NCCL all-reduce -> optimizer graph.
-            # The gradients a replay produces live in graph memory: keep the tensors so every step can pack them.
-            with torch.cuda.graph(self.graph_fb):
-                self.loss = self._forward_backward()
-            self._graph_grads = [p.grad for p in self.flat.params if p.grad is not None]
-            self.flat.all_reduce(sources=self._graph_grads)          # p.grad now are views of the (static) flat buffer
-            self.graph_opt = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(self.graph_opt, pool=self.graph_fb.pool()):
-                self.optimizer.step()
-        else:
-            with torch.cuda.graph(self.graph_fb):
-                self.loss = self._forward_backward()
-                self.optimizer.step()
+        from ..parallel import FlatSGD
+        self._fold = self.distributed and isinstance(self.optimizer, FlatSGD)      # FlatSGD / FlatAdam apply 1 / world themselves
+        # ONE graph per step, also with several ranks: forward, backward, gradient pack, NCCL all-reduce (capturable; the
+        # warm-up steps above already ran it eagerly on this communicator) and the optimizer.  `thread_local` capture mode:
+        # NCCL's watchdog thread makes CUDA calls of its own while this thread captures.
+        with torch.cuda.graph(self.graph_fb, capture_error_mode='thread_local' if self.distributed else 'global'):
+            self.loss = self._forward_backward()
+            self.flat.all_reduce(defer_average=self._fold)
+            self.optimizer.step()
         self._keep_workspaces()
 
     def _forward_backward(self):
@@ -135,7 +128,4 @@ class GraphedTrainStep(_StaticInputs):
         if sync_lr is not None:
             sync_lr()                    # a scheduler may have changed the learning rate: the captured kernel reads it from the device
         self.graph_fb.replay()
-        if self.graph_opt is not None:
-            self.flat.all_reduce(sources=self._graph_grads)
-            self.graph_opt.replay()
         return self.loss

@@ -243,11 +243,11 @@ int dc_bn_act_pool_bwd(const float* y, int64_t ldy, int64_t M, int C, const int3
 /* One SGD step (momentum, weight decay; dampening 0, no Nesterov — torch.optim.SGD as experiments/train_*.py configure it) on flat
  * parameter / gradient / momentum buffers of n floats: buf = momentum*buf + grad + weight_decay*p; p -= lr*buf.  lr is a device scalar. */
 int dc_sgd_step(float* params, const float* grads, float* momentum_buf, int64_t n, const float* lr_device,
-                float momentum, float weight_decay, void* stream);
+                float momentum, float weight_decay, float grad_scale, void* stream);
 /* One Adam step (torch.optim.Adam as experiments/train_shapeseg.py:82 configures it: L2 weight decay, no amsgrad) on flat buffers;
  * the step counter (int32, starts at 0, incremented by the call) and lr are device scalars. */
 int dc_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, const float* lr_device,
-                 int32_t* step_device, float beta1, float beta2, float eps, float weight_decay, void* stream);
+                 int32_t* step_device, float beta1, float beta2, float eps, float weight_decay, float grad_scale, void* stream);
 /* out = a + b on [M,C] column slices of wider row-major buffers: the sum of the two gradients of [div v | curl v], which feeds both
  * the scalar concatenation (deltaconv.py:57) and the Hodge Laplacian of the vector stream (deltaconv.py:66) */
 int dc_add_rows(const float* a, int64_t lda, const float* b, int64_t ldb, int64_t M, int C, float* out, int64_t ldo, void* stream);

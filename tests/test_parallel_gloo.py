@@ -57,6 +57,16 @@ def _worker(rank, world, port, out):
     assert not flat.packed                                          # a new step starts unpacked ...
     (((model(x[b:e]) - y[b:e]) ** 2).sum() / 8 * world).backward()
     assert flat.all_reduce().data_ptr() == address and flat.packed  # ... and packs into the same (stable) buffer
+    mean = flat.flat.clone()
+    # deferred averaging (what the captured step uses): the buffer keeps the SUM and the factor 1 / world is handed to the
+    # optimizer kernel through `pending_scale`; zero() resets it
+    flat.zero()
+    assert flat.pending_scale == 1.0
+    (((model(x[b:e]) - y[b:e]) ** 2).sum() / 8 * world).backward()
+    summed = flat.all_reduce(defer_average=True)
+    assert flat.pending_scale == 1.0 / world and torch.allclose(summed * flat.pending_scale, mean, atol=1e-7)
+    flat.zero()
+    assert flat.pending_scale == 1.0
     dist.destroy_process_group()
 
 
