@@ -105,16 +105,27 @@ class GraphedTrainStep(_StaticInputs):
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
         self.graph_fb = torch.cuda.CUDAGraph()
+        self.graph_opt = None
+        self._graph_grads = None
         self._stage = None
         from ..parallel import FlatSGD
         self._fold = self.distributed and isinstance(self.optimizer, FlatSGD)      # FlatSGD / FlatAdam apply 1 / world themselves
-        # ONE graph per step, also with several ranks: forward, backward, gradient pack, NCCL all-reduce (capturable; the
-        # warm-up steps above already ran it eagerly on this communicator) and the optimizer.  `thread_local` capture mode:
-        # NCCL's watchdog thread makes CUDA calls of its own while this thread captures.
-        with torch.cuda.graph(self.graph_fb, capture_error_mode='thread_local' if self.distributed else 'global'):
-            self.loss = self._forward_backward()
-            self.flat.all_reduce(defer_average=self._fold)
-            self.optimizer.step()
+        if self.distributed:
+            # The collective stays between two graphs: fwd+bwd graph -> pack + NCCL all-reduce (SUM) -> optimizer graph, which
+            # also applies 1 / world.  (Capturing the all-reduce into one graph with the rest hung on 2 GPUs in this
+            # environment — torch 2.11 / NCCL 2.28, capture_error_mode thread_local — and is not used.)
+            # The gradients a replay produces live in graph memory: keep the tensors so every step can pack them.
+            with torch.cuda.graph(self.graph_fb):
+                self.loss = self._forward_backward()
+            self._graph_grads = [p.grad for p in self.flat.params if p.grad is not None]
+            self.flat.all_reduce(sources=self._graph_grads, defer_average=self._fold)   # p.grad now are views of the (static) flat buffer
+            self.graph_opt = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.graph_opt, pool=self.graph_fb.pool()):
+                self.optimizer.step()
+        else:
+            with torch.cuda.graph(self.graph_fb):
+                self.loss = self._forward_backward()
+                self.optimizer.step()
         self._keep_workspaces()
 
     def _forward_backward(self):
@@ -128,4 +139,7 @@ class GraphedTrainStep(_StaticInputs):
         if sync_lr is not None:
             sync_lr()                    # a scheduler may have changed the learning rate: the captured kernel reads it from the device
         self.graph_fb.replay()
+        if self.graph_opt is not None:
+            self.flat.all_reduce(sources=self._graph_grads, defer_average=self._fold)
+            self.graph_opt.replay()
         return self.loss
