@@ -191,8 +191,11 @@ template <int OP> struct StagedTraits {
     static constexpr int m1 = (OP == OP_HODGE || OP == OP_DIVCURL_T) ? 1 : 0;
 };
 
-template <int OP>
-__global__ void __launch_bounds__(256) spmm_staged_kernel(SpArgs a, int CH, int lpp_log2) {
+// STAGE = false is the same cloud-major schedule WITHOUT the explicit copy: the CTA gathers straight from global memory and
+// relies on the SM's L1 (no shared memory is requested, so nearly all of the 256 KB is cache) to hold the cloud's rows of
+// this channel chunk — the k-fold re-reads then hit L1 instead of crossing to L2.  1024 threads per CTA in that mode.
+template <int OP, bool STAGE>
+__global__ void __launch_bounds__(STAGE ? 256 : 1024) spmm_staged_kernel(SpArgs a, int CH, int lpp_log2) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float* t0 = reinterpret_cast<float*>(smem_raw);
     const int b = blockIdx.y;
@@ -205,19 +208,19 @@ __global__ void __launch_bounds__(256) spmm_staged_kernel(SpArgs a, int CH, int 
     const bool has0 = a.in0 != nullptr, has1 = M1 > 0 && a.in1 != nullptr;
     // stage: rows [M*s, M*e) x channels [ch0, ch0+cw), float4 granularity, coalesced along channels
     const int q4 = cw >> 2;
-    if (has0)
+    if (STAGE && has0)
         for (int t = threadIdx.x; t < M0 * P * q4; t += blockDim.x) {
             const int r = t / q4, c4 = t - r * q4;
             *reinterpret_cast<float4*>(t0 + (size_t)r * CH + 4 * c4) =
                 __ldg(reinterpret_cast<const float4*>(a.in0 + ((size_t)M0 * s + r) * a.ld_in0 + ch0 + 4 * c4));
         }
-    if (has1)
+    if (STAGE && has1)
         for (int t = threadIdx.x; t < M1 * P * q4; t += blockDim.x) {
             const int r = t / q4, c4 = t - r * q4;
             *reinterpret_cast<float4*>(t1 + (size_t)r * CH + 4 * c4) =
                 __ldg(reinterpret_cast<const float4*>(a.in1 + ((size_t)M1 * s + r) * a.ld_in1 + ch0 + 4 * c4));
         }
-    __syncthreads();
+    if (STAGE) __syncthreads();
 
     typedef Vec<4> V;
     const int lpp = 1 << lpp_log2, lane = threadIdx.x & 31, sub = lane & (lpp - 1);
@@ -225,8 +228,20 @@ __global__ void __launch_bounds__(256) spmm_staged_kernel(SpArgs a, int CH, int 
     const int chl = sub * 4;                                // channel offset inside the chunk
     const bool ch_ok = chl < cw;
     const int ch = ch0 + chl;
-    auto ld0 = [&](int row) { V r; r.v = *reinterpret_cast<const float4*>(t0 + (size_t)row * CH + chl); return r; };
-    auto ld1 = [&](int row) { V r; r.v = *reinterpret_cast<const float4*>(t1 + (size_t)row * CH + chl); return r; };
+    const float* g0 = a.in0 ? a.in0 + (size_t)M0 * s * a.ld_in0 + ch : nullptr;     // the cloud's first row, this lane's channels
+    const float* g1 = (M1 > 0 && a.in1) ? a.in1 + (size_t)M1 * s * a.ld_in1 + ch : nullptr;
+    auto ld0 = [&](int row) {
+        V r;
+        if (STAGE) r.v = *reinterpret_cast<const float4*>(t0 + (size_t)row * CH + chl);
+        else r.v = __ldg(reinterpret_cast<const float4*>(g0 + (size_t)row * a.ld_in0));
+        return r;
+    };
+    auto ld1 = [&](int row) {
+        V r;
+        if (STAGE) r.v = *reinterpret_cast<const float4*>(t1 + (size_t)row * CH + chl);
+        else r.v = __ldg(reinterpret_cast<const float4*>(g1 + (size_t)row * a.ld_in1));
+        return r;
+    };
 
     for (int rbase = 0; rbase < P; rbase += groups) {
         const int rl = rbase + (threadIdx.x >> 5) * rows_per_warp + (lane >> lpp_log2);   // local row
@@ -338,7 +353,22 @@ int launch_spmm(const SpArgs& a, cudaStream_t st) {
                       a.ld_out0 % 4 == 0 && a.ld_out1 % 4 == 0 && a.ld_out2 % 4 == 0 && a.ld_cp_src % 4 == 0 && a.ld_cp_dst % 4 == 0 &&
                       aligned16(a.cp_src) && aligned16(a.cp_dst) && aligned16(a.in0) && aligned16(a.in1) &&
                       aligned16(a.in2) && aligned16(a.in3) && aligned16(a.out0) && aligned16(a.out1) && aligned16(a.out2);
-    if (vec4 && a.cloud_ptr != nullptr && a.max_cloud > 0 && g_spmm_staged) {
+    if (vec4 && a.cloud_ptr != nullptr && a.max_cloud > 0 && g_spmm_staged == 2) {
+        // cloud-major through L1: a CTA = (cloud, channel chunk); the chunk is as wide as keeps ~one CTA per SM busy and the
+        // cloud's rows of the chunk inside L1 (~200 KB)
+        constexpr int M0 = StagedTraits<OP>::m0, M1 = StagedTraits<OP>::m1;
+        const int rows = (M0 + ((M1 > 0 && a.in1) ? M1 : 0)) * a.max_cloud;
+        int CH = 128;
+        while (CH > 4 && (CH > a.C || (size_t)rows * CH * 4 > 200 * 1024)) CH >>= 1;
+        while (CH > 8 && (long long)a.B * ((a.C + CH - 1) / CH) < dc_sm_count() * 3 / 4) CH >>= 1;
+        int lpp_log2 = 0;
+        while ((1 << lpp_log2) < CH / 4) ++lpp_log2;
+        DC_CUDA(cudaFuncSetAttribute(spmm_staged_kernel<OP, false>, cudaFuncAttributePreferredSharedMemoryCarveout, 0));
+        dim3 grid(dc_ceil_div(a.C, CH), a.B);
+        spmm_staged_kernel<OP, false><<<grid, 1024, 0, st>>>(a, CH, lpp_log2);
+        return dc_check_launch("spmm/cloud-major");
+    }
+    if (vec4 && a.cloud_ptr != nullptr && a.max_cloud > 0 && g_spmm_staged == 1) {
         // shared-memory staged variant: pick the channel chunk so that the staged rows fit (<= ~200 KB)
         constexpr int M0 = StagedTraits<OP>::m0, M1 = StagedTraits<OP>::m1;
         const int rows = (M0 + ((M1 > 0 && a.in1) ? M1 : 0)) * a.max_cloud;
@@ -350,9 +380,9 @@ int launch_spmm(const SpArgs& a, cudaStream_t st) {
         if (smem <= 200 * 1024) {
             int lpp_log2 = 0;
             while ((1 << lpp_log2) < CH / 4) ++lpp_log2;
-            DC_CUDA(cudaFuncSetAttribute(spmm_staged_kernel<OP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            DC_CUDA(cudaFuncSetAttribute(spmm_staged_kernel<OP, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             dim3 grid(dc_ceil_div(a.C, CH), a.B);
-            spmm_staged_kernel<OP><<<grid, 256, smem, st>>>(a, CH, lpp_log2);
+            spmm_staged_kernel<OP, true><<<grid, 256, smem, st>>>(a, CH, lpp_log2);
             return dc_check_launch("spmm/staged");
         }
     }
@@ -549,5 +579,6 @@ extern "C" int dc_hodge_bwd(const int32_t* in_ptr, const int32_t* in_edge, const
     return launch_spmm<OP_HODGE_T>(a, (cudaStream_t)stream);
 }
 
-// tuning switch: 1 = stage a cloud's rows in shared memory when the cloud layout is known, 0 (default) = gather from L2
+// tuning switch: 0 (default) = row-major grid gathering from L2, 1 = a cloud's rows staged in shared memory, 2 = cloud-major grid
+// gathering through L1 (both need the cloud layout)
 extern "C" int dc_set_spmm_staged(int v) { g_spmm_staged = v; return DC_OK; }
