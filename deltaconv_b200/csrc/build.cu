@@ -70,7 +70,7 @@ __device__ __forceinline__ V3 gather_pos(const float* __restrict__ pos, const fl
 }
 
 // ---- pass A: m_i = mean_e ||p_j - p_i||  (grad_div_mls.py:233, :112 inner mean) --------------
-// One thread per point; the CTA's idx tile is loaded coalesced and transposed into shared memory (as in the fit), four
+// One thread per point; the CTA's idx tile is loaded coalesced and transposed into shared memory (as in the fit), eight
 // neighbour positions are in flight per thread.  (The first version spread a point over 8 lanes: 43 warp-instructions per
 // point and 91 us per 2^20 points, more than the fit itself.)
 constexpr int EDGE_T = 128;
@@ -97,16 +97,16 @@ edge_mean_kernel(const float* __restrict__ pos, const float4* __restrict__ posp,
     const V3 p = v3_load(pos + 3 * (size_t)i);
     float acc = 0.f;
 #pragma unroll 1
-    for (int e = 0; e < k; e += 4) {
-        V3 pj[4];
+    for (int e = 0; e < k; e += 8) {
+        V3 pj[8];
 #pragma unroll
-        for (int u = 0; u < 4; ++u)
+        for (int u = 0; u < 8; ++u)
             if (e + u < k) {
                 const int j = jdx[(e + u) * STRIDE];
                 pj[u] = gather_pos<PACKED>(pos, posp, ((unsigned)j >= (unsigned)N) ? 0 : j);
             }
 #pragma unroll
-        for (int u = 0; u < 4; ++u)
+        for (int u = 0; u < 8; ++u)
             if (e + u < k) {
                 const V3 d = pj[u] - p;
                 const float d2 = dot(d, d);
@@ -151,6 +151,7 @@ __global__ void __launch_bounds__(CLOUD_MEAN_T) cloud_mean_kernel(const float* _
 // shared-memory address is an immediate.  Entries are written WITHOUT the per-cloud normalisation; the per-cloud maxima go to
 // S (one atomicMax per warp: s_i >= 0, so its bit pattern orders like the value and the integer max is exact and order
 // independent, replacing scatter_max of grad_div_mls.py:259) and scale_kernel applies them.
+constexpr int FIT_BATCH = 8;       // gathers in flight per thread (ncu: the kernel waits on its gathers at 16 warps per SM; 4 -> 8 measured below)
 template <int T, int K, bool DEBUG, bool PACKED>
 __global__ void __launch_bounds__(T)
 fit_kernel(const float* __restrict__ pos, const float* __restrict__ normal, const float* __restrict__ xb,
@@ -193,18 +194,18 @@ fit_kernel(const float* __restrict__ pos, const float* __restrict__ normal, cons
         FitSums sums;
         fit_sums_zero(sums);
 #pragma unroll 1
-        for (int e = 0; e < k; e += 4) {
-            int j[4];
-            V3 pj[4];
+        for (int e = 0; e < k; e += FIT_BATCH) {
+            int j[FIT_BATCH];
+            V3 pj[FIT_BATCH];
 #pragma unroll
-            for (int u = 0; u < 4; ++u)
+            for (int u = 0; u < FIT_BATCH; ++u)
                 if (e + u < k) {
                     j[u] = jdx[(e + u) * STRIDE];
                     const int jj = ((unsigned)j[u] >= (unsigned)N) ? 0 : j[u];
                     pj[u] = gather_pos<PACKED>(pos, posp, jj);
                 }
 #pragma unroll
-            for (int u = 0; u < 4; ++u)
+            for (int u = 0; u < FIT_BATCH; ++u)
                 if (e + u < k) dat[(e + u) * STRIDE] = fit_slot_accumulate(pj[u], (unsigned)j[u] < (unsigned)N, p, n, ex, ey, nl2, sums);
         }
         float z1[6], z2[6], coef[6];
@@ -215,10 +216,10 @@ fit_kernel(const float* __restrict__ pos, const float* __restrict__ normal, cons
         float* dm_ = DEBUG && dbg_mapping ? dbg_mapping + (size_t)i * k * 4 : nullptr;
         float ax = 0.f, ay = 0.f;
 #pragma unroll 1
-        for (int e = 0; e < k; e += 4) {
-            V3 xj[4], yj[4];
+        for (int e = 0; e < k; e += FIT_BATCH) {
+            V3 xj[FIT_BATCH], yj[FIT_BATCH];
 #pragma unroll
-            for (int u = 0; u < 4; ++u)
+            for (int u = 0; u < FIT_BATCH; ++u)
                 if (e + u < k) {
                     const int j = jdx[(e + u) * STRIDE];
                     const int jj = ((unsigned)j >= (unsigned)N) ? 0 : j;
@@ -230,7 +231,7 @@ fit_kernel(const float* __restrict__ pos, const float* __restrict__ normal, cons
                     }
                 }
 #pragma unroll
-            for (int u = 0; u < 4; ++u)
+            for (int u = 0; u < FIT_BATCH; ++u)
                 if (e + u < k) {
                     const float4 out = fit_slot_entry(xj[u], yj[u], dat[(e + u) * STRIDE], n, ex, ey, z1, z2, coef, inv_wnorm,
                                                       dc_ ? dc_ + 2 * (e + u) : nullptr, dw_ ? dw_ + (e + u) : nullptr,

@@ -51,7 +51,13 @@ class DeltaNetBase(torch.nn.Module):
             normal = data.norm if perm is None else data.norm[perm]
             x_basis, y_basis = build_tangent_basis(normal)
         else:
-            edge_index_normal = knn_graph(pos, 10, batch, loop=True, flow='target_to_source', num_clouds=clouds, max_points=maxp)
+            # the reference builds a second graph with k = 10 (deltanet_base.py:63).  Neighbours are ordered by (d2, index), so
+            # the 10 nearest are exactly the first 10 slots of the k-nearest when k >= 10: no second search
+            graph = ops.graph_of(edge_index, pos.size(0))
+            if graph.k >= 10:
+                edge_index_normal = ops.EllGraph(graph.idx[:, :10].contiguous(), graph.cloud_ptr, graph.B, graph.max_cloud)
+            else:
+                edge_index_normal = knn_graph(pos, 10, batch, loop=True, flow='target_to_source', num_clouds=clouds, max_points=maxp)
             normal, x_basis, y_basis = estimate_basis(pos, edge_index_normal, orientation=pos)
         grad, div = build_grad_div(pos, normal, x_basis, y_basis, edge_index, batch,
                                    kernel_width=self.grad_kernel_width, regularizer=self.grad_regularizer)

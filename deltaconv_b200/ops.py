@@ -735,6 +735,18 @@ def _running_update(bn):
     return True, float(bn.momentum), (nbt.data_ptr() if counted else None)
 
 
+def _running_invstd(bn):
+    """1 / sqrt(running_var + eps) of a BatchNorm in evaluation mode, computed once per state of `running_var` (its in-place
+    version counter) instead of with two small launches per layer and forward.  A captured inference graph holds the tensor
+    that was current at capture: re-capture after loading new statistics."""
+    rv = bn.running_var
+    cached = getattr(bn, '_dc_invstd', None)
+    if cached is None or cached[0] != rv._version or cached[1] != bn.eps or cached[2].device != rv.device or cached[3] != rv.data_ptr():
+        cached = (rv._version, bn.eps, torch.rsqrt(rv + bn.eps), rv.data_ptr())
+        bn._dc_invstd = cached
+    return cached[2]
+
+
 def _bn_moments(bn, x, ldx, M, C, mode):
     """(mean, invstd) to normalise with: batch statistics in training mode (running stats are
     updated in place like torch.nn.BatchNorm1d), running statistics in eval mode."""
@@ -749,9 +761,7 @@ def _bn_moments(bn, x, ldx, M, C, mode):
         call('dc_bn_stats', x.data_ptr(), ldx, M, C, mode, float(bn.eps), float(momentum), ptr(mean), ptr(invstd),
              ptr(bn.running_mean) if update else None, ptr(bn.running_var) if update else None, nbt, ptr(ws), nb)
         return mean, invstd, True
-    mean = bn.running_mean.contiguous()
-    invstd = torch.rsqrt(bn.running_var + bn.eps)
-    return mean, invstd, False
+    return bn.running_mean.contiguous(), _running_invstd(bn), False
 
 
 class _BNAct(torch.autograd.Function):
@@ -1017,7 +1027,7 @@ class _CentralizedMax(torch.autograd.Function):
                  ptr(bn.running_var) if update else None, nbt, ptr(ws), nbytes)
         else:
             mean = bn.running_mean.contiguous()
-            invstd = torch.rsqrt(bn.running_var + bn.eps)
+            invstd = _running_invstd(bn)
         out = torch.empty(N, Cout, dtype=_F32, device=dev)
         arg = torch.empty(N, Cout, dtype=torch.uint8, device=dev)
         call('dc_central_fwd', ptr(graph.idx), N, k, Cin, Cout, ptr(x), ldx, ptr(weight), ptr(gamma), ptr(beta), ptr(mean), ptr(invstd),
@@ -1167,7 +1177,7 @@ def linear_bn_act_pool_inference(x, weight, bn, slope, batch, mode, size=None):
     ws, nb = _gemm_ws(M, C, K, dev)
     call('dc_linear_fwd', ptr(x), ldx, ptr(weight), ldw, None, M, K, C, ptr(y), C, ptr(ws), nb)
     mean = bn.running_mean.contiguous()
-    invstd = torch.rsqrt(bn.running_var + bn.eps)
+    invstd = _running_invstd(bn)
     want_max, want_mean = mode in ('max', 'maxmean'), mode in ('mean', 'maxmean')
     width = C * (2 if mode == 'maxmean' else 1)
     out = torch.empty(B, width, dtype=_F32, device=dev)

@@ -13,7 +13,7 @@ for r in rows[hdr + 1:]:
     if len(r) < 15:
         continue
     name = re.sub(r'\(anonymous namespace\)::|<unnamed>::', '', r[4]).split('(')[0].replace('void ', '')
-    if pat and not pat.search(name):
+    if (pat and not pat.search(name)) or 'spin_kernel' in name:
         continue
     per.setdefault((r[0], name), {})[r[12]] = float(r[14].replace(',', ''))
 agg = collections.OrderedDict()
