@@ -324,10 +324,15 @@ def run_cuda_arm(args):
         raise SystemExit('bench.py: no CUDA device — the CUDA arm has no CPU fallback (use --impl reference for the CPU arm)')
     torch.cuda.set_device(local)
     dev = torch.device('cuda', local)
+    nccl_log = None
     if world > 1:
-        # stdout carries exactly one JSON line (printed last): whatever NCCL logs (the caller's NCCL_DEBUG setting is kept)
-        # goes to stderr unless the caller chose a file
-        os.environ.setdefault('NCCL_DEBUG_FILE', '/dev/stderr')
+        # stdout carries exactly one JSON line (printed last).  The caller's NCCL_DEBUG setting is kept; unless the caller
+        # chose a file, every rank logs to a file of its own and copies it to stderr when it is done (NCCL opens its log file
+        # itself: N ranks opening /dev/stderr would each write from offset 0 of a redirected stderr, over one another).
+        if os.environ.get('NCCL_DEBUG') and not os.environ.get('NCCL_DEBUG_FILE'):
+            import tempfile
+            nccl_log = os.path.join(tempfile.gettempdir(), f'dc_bench_nccl.{os.getpid()}.rank{rank}.log')
+            os.environ['NCCL_DEBUG_FILE'] = nccl_log
         dist.init_process_group('nccl', device_id=dev)
     lib = _lib.load()
     if args.gemm_mode is not None:
@@ -473,9 +478,17 @@ def run_cuda_arm(args):
     if args.detail and rank == 0:
         open(args.detail, "w").write(prof.detail(args.steps, top=120) + "\n")
 
+    def flush_nccl_log():
+        if nccl_log and os.path.exists(nccl_log):
+            with open(nccl_log, errors='replace') as f:
+                sys.stderr.write(f.read())
+            sys.stderr.flush()
+            os.remove(nccl_log)
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
+            flush_nccl_log()
         return
 
     pk = peaks()
@@ -548,6 +561,7 @@ def run_cuda_arm(args):
                                        frac_of_peak=round(hbm_bytes / (hbm_ms / 1000) / 1e9 / pk['hbm'], 4) if hbm_ms else None))
     if world > 1:
         dist.destroy_process_group()
+        flush_nccl_log()
     print(json.dumps(line), flush=True)
 
 
