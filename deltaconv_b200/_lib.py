@@ -27,6 +27,7 @@ _SIGNATURES = {
     'dc_geodesic_fps_ws_bytes': [_I],
     'dc_geodesic_fps': [_P, _P, _I, _I, _I, _I, _P, _P, _P, _P, _P, _Z, _P],
     'dc_set_knn_grid_density': [_F],
+    'dc_set_knn_merge_min': [_I, _I],
     'dc_knn_grid': [_P, _P, _I, _I, _I, _P, _P, _P, _P, _Z, _P],
     'dc_ell_from_edge_index': [_P, _I, _I, _P, _P],
     'dc_edge_index_from_ell': [_P, _I, _I, _P, _P],
@@ -126,7 +127,12 @@ def exported_symbols():
 
 
 def stream_ptr():
-    return torch.cuda.current_stream().cuda_stream
+    """Raw handle of the current CUDA stream of the current device (the fast private accessor when torch has it: an eager
+    step makes ~200 library calls, each of which needs it)."""
+    try:
+        return torch._C._cuda_getCurrentRawStream(torch.cuda.current_device())
+    except AttributeError:
+        return torch.cuda.current_stream().cuda_stream
 
 
 def ptr(t):
@@ -167,8 +173,21 @@ def call(name, *args):
         raise DeltaConvLibraryError(f"{name} failed (code {rc}): {msg}")
 
 
+_query_cache = {}
+_UNCACHED_QUERIES = {'dc_knn_grid_ws_bytes', 'dc_get_gemm_mode', 'dc_launch_count'}      # depend on run-time tuning switches / state
+
+
 def query(name, *args):
-    return getattr(load(), name)(*args)
+    """Value of a pure size / limit query (`dc_*_ws_bytes`, ...), memoised: the answers depend on the arguments only."""
+    if name in _UNCACHED_QUERIES:
+        return getattr(load(), name)(*args)
+    key = (name,) + args
+    val = _query_cache.get(key)
+    if val is None:
+        val = getattr(load(), name)(*args)
+        if len(_query_cache) < 65536:
+            _query_cache[key] = val
+    return val
 
 
 def rows_ld(t):

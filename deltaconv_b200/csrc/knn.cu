@@ -21,7 +21,7 @@ template <int SLOTS, bool STAGED>
 __device__ __forceinline__ void scan(u64 (&keys)[SLOTS], u64& tau, int k, int lane, float qx, float qy, float qz,
                                      const float* __restrict__ sx, const float* __restrict__ sy,
                                      const float* __restrict__ sz, const float* __restrict__ gpos,
-                                     int base, int count) {
+                                     int base, int count, MergeMin mm) {
     for (int j0 = 0; j0 < count; j0 += 32) {
         int j = j0 + lane;
         u64 key = KEY_INF;
@@ -32,14 +32,14 @@ __device__ __forceinline__ void scan(u64 (&keys)[SLOTS], u64& tau, int k, int la
             float d2 = knn_dist2(qx, qy, qz, px, py, pz);
             key = ((u64)__float_as_uint(d2) << 32) | (unsigned)(base + j);
         }
-        list_offer<SLOTS>(keys, tau, k, lane, key);
+        list_offer<SLOTS>(keys, tau, k, lane, key, mm);
     }
 }
 
 template <int SLOTS>
 __global__ void __launch_bounds__(KNN_WARPS * 32)
 knn_kernel(const float* __restrict__ pos, const int* __restrict__ cloud_ptr, int B, int N, int k,
-           int* __restrict__ idx_out, long long* __restrict__ edge_out, float* __restrict__ d2_out) {
+           int* __restrict__ idx_out, long long* __restrict__ edge_out, float* __restrict__ d2_out, MergeMin mm) {
     __shared__ float sx[KNN_CHUNK], sy[KNN_CHUNK], sz[KNN_CHUNK];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int q_begin = blockIdx.x * KNN_TILE;
@@ -68,8 +68,8 @@ knn_kernel(const float* __restrict__ pos, const int* __restrict__ cloud_ptr, int
 #pragma unroll
             for (int t = 0; t < SLOTS; ++t) keys[t] = KEY_INF;
             u64 tau = KEY_INF;
-            if (staged) scan<SLOTS, true>(keys, tau, k, lane, qx, qy, qz, sx, sy, sz, nullptr, 0, P);
-            else scan<SLOTS, false>(keys, tau, k, lane, qx, qy, qz, nullptr, nullptr, nullptr, pos + 3 * (size_t)s, 0, P);
+            if (staged) scan<SLOTS, true>(keys, tau, k, lane, qx, qy, qz, sx, sy, sz, nullptr, 0, P, mm);
+            else scan<SLOTS, false>(keys, tau, k, lane, qx, qy, qz, nullptr, nullptr, nullptr, pos + 3 * (size_t)s, 0, P, mm);
 #pragma unroll
             for (int t = 0; t < SLOTS; ++t) {
                 int p = t * 32 + lane;
@@ -109,6 +109,15 @@ __global__ void edges_from_ell_kernel(const int* __restrict__ idx, long long E, 
 
 }  // namespace
 
+// tuning: survivors per round from which the bitonic merge replaces single insertions (one / two list slots per lane)
+static MergeMin g_merge_min = {12, 8};      // scripts/exp_knn_merge.py: two slots 2..33 -> 8 is best (k=40: 7.38 ms; 12: 7.50; 4: 8.51)
+MergeMin dc_knn_merge_min() { return g_merge_min; }
+extern "C" int dc_set_knn_merge_min(int one_slot, int two_slots) {
+    if (one_slot > 0) g_merge_min.one_slot = one_slot;
+    if (two_slots > 0) g_merge_min.two_slots = two_slots;
+    return DC_OK;
+}
+
 extern "C" int dc_cloud_ptr(const int64_t* batch, int N, int B, int32_t* cloud_ptr, void* stream) {
     DC_REQUIRE(N >= 0 && B >= 1, "dc_cloud_ptr: need N >= 0 and B >= 1 (got N=%d B=%d)", N, B);
     cloud_ptr_kernel<<<dc_ceil_div(N + 1, 256), 256, 0, (cudaStream_t)stream>>>((const long long*)batch, N, B, cloud_ptr);
@@ -123,9 +132,9 @@ extern "C" int dc_knn(const float* pos, const int32_t* cloud_ptr, int B, int N, 
     const int grid = dc_ceil_div(N, KNN_TILE);
     cudaStream_t st = (cudaStream_t)stream;
     long long* eo = (long long*)edge_index_or_null;
-    if (k <= 32) knn_kernel<1><<<grid, KNN_WARPS * 32, 0, st>>>(pos, cloud_ptr, B, N, k, idx, eo, d2_or_null);
-    else if (k <= 64) knn_kernel<2><<<grid, KNN_WARPS * 32, 0, st>>>(pos, cloud_ptr, B, N, k, idx, eo, d2_or_null);
-    else knn_kernel<4><<<grid, KNN_WARPS * 32, 0, st>>>(pos, cloud_ptr, B, N, k, idx, eo, d2_or_null);
+    if (k <= 32) knn_kernel<1><<<grid, KNN_WARPS * 32, 0, st>>>(pos, cloud_ptr, B, N, k, idx, eo, d2_or_null, dc_knn_merge_min());
+    else if (k <= 64) knn_kernel<2><<<grid, KNN_WARPS * 32, 0, st>>>(pos, cloud_ptr, B, N, k, idx, eo, d2_or_null, dc_knn_merge_min());
+    else knn_kernel<4><<<grid, KNN_WARPS * 32, 0, st>>>(pos, cloud_ptr, B, N, k, idx, eo, d2_or_null, dc_knn_merge_min());
     return dc_check_launch("dc_knn");
 }
 

@@ -8,6 +8,8 @@
 #include "geom_core.cuh"
 #include "knn_list.cuh"
 
+MergeMin dc_knn_merge_min();      // knn.cu
+
 namespace {
 
 constexpr int GRID_MAX_DIM = 1024;     // cells per axis
@@ -160,7 +162,7 @@ __global__ void grid_fill_kernel(const float* __restrict__ pos, const int* __res
 // Offer the sorted points [begin, end) to the list (all lanes take part in every round).
 template <int SLOTS>
 __device__ __forceinline__ void grid_scan_range(u64 (&keys)[SLOTS], u64& tau, int k, int lane, float qx, float qy, float qz,
-                                                const float4* __restrict__ sorted, int begin, int end) {
+                                                const float4* __restrict__ sorted, int begin, int end, MergeMin mm) {
     for (int j0 = begin; j0 < end; j0 += 32) {
         const int j = j0 + lane;
         u64 key = KEY_INF;
@@ -169,7 +171,7 @@ __device__ __forceinline__ void grid_scan_range(u64 (&keys)[SLOTS], u64& tau, in
             const float d2 = knn_dist2(qx, qy, qz, p.x, p.y, p.z);
             key = ((u64)__float_as_uint(d2) << 32) | (unsigned)__float_as_int(p.w);
         }
-        list_offer<SLOTS>(keys, tau, k, lane, key);
+        list_offer<SLOTS>(keys, tau, k, lane, key, mm);
     }
 }
 
@@ -177,7 +179,7 @@ __device__ __forceinline__ void grid_scan_range(u64 (&keys)[SLOTS], u64& tau, in
 template <int SLOTS>
 __global__ void __launch_bounds__(GRID_WARPS * 32)
 grid_query_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell_start, const int* __restrict__ cloud_ptr, int B, int N, int k,
-                  const GridCloud* __restrict__ clouds, int* __restrict__ idx_out, long long* __restrict__ edge_out, float* __restrict__ d2_out) {
+                  const GridCloud* __restrict__ clouds, int* __restrict__ idx_out, long long* __restrict__ edge_out, float* __restrict__ d2_out, MergeMin mm) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int j = blockIdx.x * GRID_WARPS + warp;                 // position of the query in the sorted array
     if (j >= N) return;
@@ -201,12 +203,12 @@ grid_query_kernel(const float4* __restrict__ sorted, const int* __restrict__ cel
                 const int row = g.cell_base + (z * g.gy + y) * g.gx;
                 if (R == 1 || abs(dz) == R || abs(dy) == R) {     // a whole row of the block: its cells are contiguous in memory
                     const int x0 = max(cx - R, 0), x1 = min(cx + R, g.gx - 1);
-                    grid_scan_range<SLOTS>(keys, tau, k, lane, qx, qy, qz, sorted, __ldg(cell_start + row + x0), __ldg(cell_start + row + x1 + 1));
+                    grid_scan_range<SLOTS>(keys, tau, k, lane, qx, qy, qz, sorted, __ldg(cell_start + row + x0), __ldg(cell_start + row + x1 + 1), mm);
                 } else {                                          // interior row of a later shell: only its two end cells are new
                     if (cx - R >= 0)
-                        grid_scan_range<SLOTS>(keys, tau, k, lane, qx, qy, qz, sorted, __ldg(cell_start + row + cx - R), __ldg(cell_start + row + cx - R + 1));
+                        grid_scan_range<SLOTS>(keys, tau, k, lane, qx, qy, qz, sorted, __ldg(cell_start + row + cx - R), __ldg(cell_start + row + cx - R + 1), mm);
                     if (cx + R <= g.gx - 1)
-                        grid_scan_range<SLOTS>(keys, tau, k, lane, qx, qy, qz, sorted, __ldg(cell_start + row + cx + R), __ldg(cell_start + row + cx + R + 1));
+                        grid_scan_range<SLOTS>(keys, tau, k, lane, qx, qy, qz, sorted, __ldg(cell_start + row + cx + R), __ldg(cell_start + row + cx + R + 1), mm);
                 }
             }
         }
@@ -323,8 +325,8 @@ extern "C" int dc_knn_grid(const float* pos, const int32_t* cloud_ptr, int B, in
     grid_fill_kernel<<<dc_ceil_div(N, 256), 256, 0, st>>>(pos, cloud_ptr, B, N, cell_of, cell_start, cursor, sorted);
     const int grid = dc_ceil_div(N, GRID_WARPS);
     long long* eo = (long long*)edge_index_or_null;
-    if (k <= 32) grid_query_kernel<1><<<grid, GRID_WARPS * 32, 0, st>>>(sorted, cell_start, cloud_ptr, B, N, k, clouds, idx, eo, d2_or_null);
-    else if (k <= 64) grid_query_kernel<2><<<grid, GRID_WARPS * 32, 0, st>>>(sorted, cell_start, cloud_ptr, B, N, k, clouds, idx, eo, d2_or_null);
-    else grid_query_kernel<4><<<grid, GRID_WARPS * 32, 0, st>>>(sorted, cell_start, cloud_ptr, B, N, k, clouds, idx, eo, d2_or_null);
+    if (k <= 32) grid_query_kernel<1><<<grid, GRID_WARPS * 32, 0, st>>>(sorted, cell_start, cloud_ptr, B, N, k, clouds, idx, eo, d2_or_null, dc_knn_merge_min());
+    else if (k <= 64) grid_query_kernel<2><<<grid, GRID_WARPS * 32, 0, st>>>(sorted, cell_start, cloud_ptr, B, N, k, clouds, idx, eo, d2_or_null, dc_knn_merge_min());
+    else grid_query_kernel<4><<<grid, GRID_WARPS * 32, 0, st>>>(sorted, cell_start, cloud_ptr, B, N, k, clouds, idx, eo, d2_or_null, dc_knn_merge_min());
     return dc_check_launch_n("dc_knn_grid", 7);
 }

@@ -4,6 +4,8 @@
 #pragma once
 #include "common.cuh"
 
+struct MergeMin { int one_slot, two_slots; };      // survivors per round from which a merge replaces insertions, per slot count
+
 namespace {
 
 typedef unsigned long long u64;
@@ -88,14 +90,16 @@ __device__ __forceinline__ void list_merge64(u64 (&keys)[2], u64 key, int lane) 
     keys[1] = hi;
 }
 
-constexpr int KNN_MERGE_MIN = 12;     // survivors in a round from which the merge is cheaper than single insertions (5 / 8 / 12 / 16 / 24 measured: 12 is best)
+// survivors in a round from which the merge is cheaper than single insertions.  One slot per lane: 5 / 8 / 12 / 16 / 24
+// measured, 12 is best.  Two slots per lane: an insertion costs about twice as much (two 64-bit registers shifted per
+// lane), the merge only 26 steps instead of 20 — the threshold is lower (dc_set_knn_merge_min tunes both at run time).
 
 
 // Offer one key per lane to the list (KEY_INF = no candidate); tau is the current k-th best.
 template <int SLOTS>
-__device__ __forceinline__ void list_offer(u64 (&keys)[SLOTS], u64& tau, int k, int lane, u64 key) {
+__device__ __forceinline__ void list_offer(u64 (&keys)[SLOTS], u64& tau, int k, int lane, u64 key, MergeMin mm) {
     unsigned mask = __ballot_sync(FULL, key < tau);
-    if (SLOTS <= 2 && __popc(mask) >= KNN_MERGE_MIN) {
+    if (SLOTS <= 2 && __popc(mask) >= (SLOTS == 1 ? mm.one_slot : mm.two_slots)) {
         if constexpr (SLOTS == 1) keys[0] = list_merge32(keys[0], key, lane);
         else if constexpr (SLOTS == 2) list_merge64(keys, key, lane);
         tau = list_get<SLOTS>(keys, k - 1);
