@@ -145,14 +145,24 @@ __global__ void __launch_bounds__(256) thin_dw_kernel(const float* __restrict__ 
     const int n_local = threadIdx.x & 63, g = threadIdx.x >> 6;
     const int n0 = blockIdx.y * 64;
     const int r_begin = blockIdx.x * rows_per_cta, r_end = min(M, r_begin + rows_per_cta);
+    const bool vec4 = (ld_dy & 3) == 0 && (N & 3) == 0 && (reinterpret_cast<uintptr_t>(dY) & 15u) == 0;
     float acc[KG];
 #pragma unroll
     for (int u = 0; u < KG; ++u) acc[u] = 0.f;
     for (int r0 = r_begin; r0 < r_end; r0 += THIN_ROWS) {
         __syncthreads();
-        for (int e = threadIdx.x; e < THIN_ROWS * 64; e += 256) {
-            const int m = e >> 6, c = e & 63;
-            dys[m][c] = (r0 + m < r_end && n0 + c < N) ? __ldg(dY + (long long)(r0 + m) * ld_dy + n0 + c) : 0.f;
+        if (vec4) {                 // 16-byte loads: 4 per thread and tile instead of 16
+            for (int e = threadIdx.x; e < THIN_ROWS * 16; e += 256) {
+                const int m = e >> 4, c = (e & 15) * 4;
+                float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (r0 + m < r_end && n0 + c < N) q = __ldg(reinterpret_cast<const float4*>(dY + (long long)(r0 + m) * ld_dy + n0 + c));
+                dys[m][c] = q.x; dys[m][c + 1] = q.y; dys[m][c + 2] = q.z; dys[m][c + 3] = q.w;
+            }
+        } else {
+            for (int e = threadIdx.x; e < THIN_ROWS * 64; e += 256) {
+                const int m = e >> 6, c = e & 63;
+                dys[m][c] = (r0 + m < r_end && n0 + c < N) ? __ldg(dY + (long long)(r0 + m) * ld_dy + n0 + c) : 0.f;
+            }
         }
         for (int e = threadIdx.x; e < THIN_ROWS * 4 * KG; e += 256) {
             const int m = e / (4 * KG), c = e - m * 4 * KG;
@@ -172,23 +182,29 @@ __global__ void __launch_bounds__(256) thin_dw_kernel(const float* __restrict__ 
             if (g * KG + u < K) partial[((size_t)blockIdx.x * N + n0 + n_local) * K + g * KG + u] = acc[u];
 }
 
-__global__ void thin_dw_reduce_kernel(const float* __restrict__ partial, int chunks, int NK, int K, float* __restrict__ dW, long long ld_dw) {
-    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+// one warp per output element: lanes take every 32nd partial (all of a lane's loads in flight), lane sums are combined by a
+// shuffle tree — fixed order, deterministic (a thread per output walking ~600 partials one after the other took ~30 us)
+__global__ void __launch_bounds__(256) thin_dw_reduce_kernel(const float* __restrict__ partial, int chunks, int NK, int K,
+                                                             float* __restrict__ dW, long long ld_dw) {
+    const int t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (t >= NK) return;
     float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-    int q = 0;
-    for (; q + 3 < chunks; q += 4) {          // four independent loads in flight, fixed order
-        s0 += partial[(size_t)q * NK + t]; s1 += partial[(size_t)(q + 1) * NK + t];
-        s2 += partial[(size_t)(q + 2) * NK + t]; s3 += partial[(size_t)(q + 3) * NK + t];
+    int q = lane;
+    for (; q + 96 < chunks; q += 128) {
+        s0 += partial[(size_t)q * NK + t]; s1 += partial[(size_t)(q + 32) * NK + t];
+        s2 += partial[(size_t)(q + 64) * NK + t]; s3 += partial[(size_t)(q + 96) * NK + t];
     }
-    for (; q < chunks; ++q) s0 += partial[(size_t)q * NK + t];
-    const int n = t / K, k = t - n * K;
-    dW[(long long)n * ld_dw + k] = (s0 + s1) + (s2 + s3);
+    for (; q < chunks; q += 32) s0 += partial[(size_t)q * NK + t];
+    const float s = warp_sum((s0 + s1) + (s2 + s3));
+    if (lane == 0) {
+        const int n = t / K, k = t - n * K;
+        dW[(long long)n * ld_dw + k] = s;
+    }
 }
 
 int thin_dw_chunks(long long M) {
     long long c = (M + 4 * THIN_ROWS - 1) / (4 * THIN_ROWS);       // at least four tiles per CTA
-    const long long cap = 2LL * dc_sm_count();
+    const long long cap = 6LL * dc_sm_count();                     // each CTA is one latency chain of tile loads: several per SM
     if (c > cap) c = cap;
     return (int)(c < 1 ? 1 : c);
 }
@@ -292,7 +308,7 @@ extern "C" int dc_linear_bwd_weight(const float* dY, int64_t ld_dy, const float*
             else if (K <= 8) thin_dw_kernel<2><<<grid, 256, 0, (cudaStream_t)stream>>>(dY, ld_dy, X, ldx, (int)M, K, Nout, rows_per_cta, (float*)ws);
             else if (K <= 12) thin_dw_kernel<3><<<grid, 256, 0, (cudaStream_t)stream>>>(dY, ld_dy, X, ldx, (int)M, K, Nout, rows_per_cta, (float*)ws);
             else thin_dw_kernel<4><<<grid, 256, 0, (cudaStream_t)stream>>>(dY, ld_dy, X, ldx, (int)M, K, Nout, rows_per_cta, (float*)ws);
-            thin_dw_reduce_kernel<<<dc_ceil_div(Nout * K, 256), 256, 0, (cudaStream_t)stream>>>((const float*)ws, chunks, Nout * K, K, dW, ld_dw);
+            thin_dw_reduce_kernel<<<dc_ceil_div((long long)Nout * K * 32, 256), 256, 0, (cudaStream_t)stream>>>((const float*)ws, chunks, Nout * K, K, dW, ld_dw);
             return dc_check_launch_n("dc_linear_bwd_weight/thin", 2);
         }
     }

@@ -772,6 +772,57 @@ __global__ void segmax_bwd_kernel(const float* __restrict__ dout, long long ldd,
     }
 }
 
+// float4 variants of the two kernels above (C % 4 == 0, 16-byte aligned rows): the [N*k, C] tensors of the generic centralized
+// layer are hundreds of MB (ShapeNet configuration: 983,040 edge rows x 64 channels), the scalar kernels spend their time on
+// 64-bit index arithmetic and 4-byte accesses.  Forward: a thread owns (point, 4 channels) and keeps 6 edge rows in flight.
+__global__ void __launch_bounds__(256) segmax_fwd_vec4_kernel(const float* __restrict__ in, int N, int k, int C4, const int* __restrict__ idx,
+                                                              float* __restrict__ out, long long ldo, unsigned char* __restrict__ arg) {
+    for (RowCol rc(C4); rc.r < N; rc.next()) {
+        const int i = (int)rc.r, c = rc.c * 4;
+        const float4* row = reinterpret_cast<const float4*>(in + ((size_t)i * k) * (4 * C4) + c);
+        float4 best = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+        uchar4 slot = make_uchar4(0, 0, 0, 0);
+        for (int e0 = 0; e0 < k; e0 += 6) {
+            float4 v[6];
+            bool ok[6];
+#pragma unroll
+            for (int u = 0; u < 6; ++u) {
+                ok[u] = e0 + u < k && !(idx && (unsigned)__ldg(idx + (size_t)i * k + e0 + u) >= (unsigned)N);
+                if (e0 + u < k) v[u] = ld_stream4(row + (size_t)(e0 + u) * C4);
+            }
+#pragma unroll
+            for (int u = 0; u < 6; ++u)
+                if (ok[u]) {
+                    const unsigned char e = (unsigned char)(e0 + u);
+                    if (v[u].x > best.x) { best.x = v[u].x; slot.x = e; }
+                    if (v[u].y > best.y) { best.y = v[u].y; slot.y = e; }
+                    if (v[u].z > best.z) { best.z = v[u].z; slot.z = e; }
+                    if (v[u].w > best.w) { best.w = v[u].w; slot.w = e; }
+                }
+        }
+        best.x = best.x == -INFINITY ? 0.f : best.x; best.y = best.y == -INFINITY ? 0.f : best.y;
+        best.z = best.z == -INFINITY ? 0.f : best.z; best.w = best.w == -INFINITY ? 0.f : best.w;
+        *reinterpret_cast<float4*>(out + (size_t)i * ldo + c) = best;
+        *reinterpret_cast<uchar4*>(arg + (size_t)i * (4 * C4) + c) = slot;
+    }
+}
+
+// Backward: a thread owns (point, 4 channels), reads arg and dOut once and streams the k rows of dIn (one element per row
+// and channel is non-zero).
+__global__ void __launch_bounds__(256) segmax_bwd_vec4_kernel(const float* __restrict__ dout, long long ldd, int N, int k, int C4,
+                                                              const unsigned char* __restrict__ arg, float* __restrict__ din) {
+    for (RowCol rc(C4); rc.r < N; rc.next()) {
+        const int i = (int)rc.r, c = rc.c * 4;
+        const uchar4 a = *reinterpret_cast<const uchar4*>(arg + (size_t)i * (4 * C4) + c);
+        const float4 d = __ldg(reinterpret_cast<const float4*>(dout + (size_t)i * ldd + c));
+        float4* row = reinterpret_cast<float4*>(din + ((size_t)i * k) * (4 * C4) + c);
+        for (int e = 0; e < k; ++e) {
+            const unsigned char ee = (unsigned char)e;
+            st_stream4(row + (size_t)e * C4, make_float4(a.x == ee ? d.x : 0.f, a.y == ee ? d.y : 0.f, a.z == ee ? d.z : 0.f, a.w == ee ? d.w : 0.f));
+        }
+    }
+}
+
 // ---- global pools (one CTA per (cloud, 32-channel block); rows of a cloud are contiguous) ------
 // out_max[b,c] = max_i x[i,c] (arg kept), out_mean[b,c] = mean_i x[i,c]
 // With BN the pooled quantity is leaky_relu(gamma * (x - mean) * invstd + beta): the activation of the embedding layer is
@@ -1037,13 +1088,19 @@ extern "C" int dc_segmax_fwd(const float* in, int N, int k, int C, const int32_t
                              uint8_t* arg, void* stream) {
     DC_REQUIRE(k <= 255, "dc_segmax_fwd: k must be <= 255");
     if (N <= 0 || C <= 0) return DC_OK;
-    segmax_fwd_kernel<<<elementwise_grid((long long)N * C), 256, 0, (cudaStream_t)stream>>>(in, N, k, C, idx_or_null, out, ldo, arg);
+    if (C % 4 == 0 && ldo % 4 == 0 && all_aligned16(in, out, arg))
+        segmax_fwd_vec4_kernel<<<elementwise_grid((long long)N * C / 4), 256, 0, (cudaStream_t)stream>>>(in, N, k, C / 4, idx_or_null, out, ldo, arg);
+    else
+        segmax_fwd_kernel<<<elementwise_grid((long long)N * C), 256, 0, (cudaStream_t)stream>>>(in, N, k, C, idx_or_null, out, ldo, arg);
     return dc_check_launch("dc_segmax_fwd");
 }
 
 extern "C" int dc_segmax_bwd(const float* dout, int64_t ldd, int N, int k, int C, const uint8_t* arg, float* din, void* stream) {
     if (N <= 0 || C <= 0) return DC_OK;
-    segmax_bwd_kernel<<<elementwise_grid((long long)N * k * C), 256, 0, (cudaStream_t)stream>>>(dout, ldd, N, k, C, arg, din);
+    if (C % 4 == 0 && ldd % 4 == 0 && all_aligned16(dout, din, arg))
+        segmax_bwd_vec4_kernel<<<elementwise_grid((long long)N * C / 4), 256, 0, (cudaStream_t)stream>>>(dout, ldd, N, k, C / 4, arg, din);
+    else
+        segmax_bwd_kernel<<<elementwise_grid((long long)N * k * C), 256, 0, (cudaStream_t)stream>>>(dout, ldd, N, k, C, arg, din);
     return dc_check_launch("dc_segmax_bwd");
 }
 
