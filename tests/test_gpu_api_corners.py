@@ -185,3 +185,20 @@ def test_flat_optimizer_state_loaded_before_the_first_step(kind):
     assert got == pytest.approx(want, rel=1e-6)
     for p, q in zip(net.parameters(), net2.parameters()):
         assert torch.allclose(p, q, rtol=1e-6, atol=1e-7)
+
+
+def test_morton_order_pretransform_is_a_permutation_inside_every_cloud():
+    """transforms.MortonOrder: clouds keep their place, per-point fields move together, and the classifier's logits are those
+    of the original batch up to fp32 summation order."""
+    D = dc()
+    data = D.utils.synthetic_batch(3, 0, config=8, sizes=[700, 300, 1024], num_classes=7).to(DEV)
+    ref = D.utils.Data(**data.__dict__)
+    out = D.transforms.MortonOrder()(D.utils.Data(**data.__dict__))
+    perm = out.morton_perm
+    assert torch.equal(torch.sort(perm).values, torch.arange(2024, device=DEV))
+    assert torch.equal(data.batch[perm], data.batch)                       # a permutation inside every cloud
+    assert torch.equal(out.pos, ref.pos[perm]) and torch.equal(out.norm, ref.norm[perm]) and torch.equal(out.y, ref.y)
+    model = D.utils.fill_deterministic(D.models.DeltaNetClassification(3, 7, conv_channels=[16, 32], num_neighbors=12), 4).to(DEV).eval()
+    with torch.no_grad():
+        a, b = model(ref), model(out)
+    assert rel_err(b.cpu(), a.cpu()) < 1e-4
