@@ -49,6 +49,13 @@ WORKLOADS = {
                   "k=20, 15 classes, convs [64,64,64,128], no normals (second kNN k=10 + estimated frames), sharded by cloud, "
                   "no collective (experiments/train_scanobjectnn.py:69-76)"),
         metric="DeltaNetClassification inference throughput (eval forward), clouds/s"),
+    'infer_depth2': dict(
+        tag='configs[4] (depth-2 reading)', kind='cls', training=False, clouds=32, points=2048, k=20, classes=15, convs=[64, 64, 64, 128],
+        normals=False, synth=5, smoothing=True, mlp_depth=2,
+        workload=("configs[4] read literally ('depth-2 vector MLPs'): the same ScanObjectNN-shape inference with the backbone built "
+                  "as DeltaNetBase(mlp_depth=2) under the classification head (DeltaNetClassification itself fixes depth 1, "
+                  "deltanet_classification.py:31); 32 clouds x 2048 pts per GPU, k=20, no normals"),
+        metric="DeltaNetClassification (depth-2 backbone) inference throughput (eval forward), clouds/s"),
 }
 WL = WORKLOADS['train']                 # set by main()
 
@@ -58,7 +65,11 @@ def make_model(pkg, wl):
     if wl['kind'] == 'seg':
         return pkg.DeltaNetSegmentation(3, wl['classes'], conv_channels=list(wl['convs']), mlp_depth=2, embedding_size=1024,
                                         categorical_vector=True, num_neighbors=wl['k'])
-    return pkg.DeltaNetClassification(3, wl['classes'], conv_channels=list(wl['convs']), num_neighbors=wl['k'])
+    model = pkg.DeltaNetClassification(3, wl['classes'], conv_channels=list(wl['convs']), num_neighbors=wl['k'])
+    if wl.get('mlp_depth', 1) != 1:                  # same head over a deeper backbone (deltanet_base.py:9,39)
+        base_cls = type(model.deltanet_base)
+        model.deltanet_base = base_cls(3, list(wl['convs']), wl['mlp_depth'], wl['k'], 1e-3, 1)
+    return model
 
 
 def make_batch(wl, rank=0, clouds=None):
@@ -117,10 +128,10 @@ class ClockSampler:
 
 
 # algorithmic work per entry point: name -> (args -> (bytes, flops)), family
-def _w_knn(a): N, k = a[3], a[4]; return N * (12 + 4 * k + (16 * k if a[6] else 0)), 0
-def _w_knn_grid(a): N, k = a[3], a[4]; return N * (12 + 4 * k + (16 * k if a[6] else 0)), 0
+def _w_knn(a): N, k = a[3], a[4]; return N * (12 + 4 * k + (16 * k if a[6] else 0) + (4 * k if a[7] else 0)), 0      # + edge_index, + d2
+def _w_knn_grid(a): N, k = a[3], a[4]; return N * (12 + 4 * k + (16 * k if a[6] else 0) + (4 * k if a[7] else 0)), 0
 def _w_basis(a): N, k = a[2], a[3]; return N * (48 + 4 * k), 0
-def _w_build(a): N, k = a[7], a[8]; return N * (48 + 20 * k), 0
+def _w_build(a): N, k = a[8], a[9]; return N * (48 + 20 * k), 0
 def _w_grad(a): N, k, C = a[2], a[3], a[4]; return N * (12 * k + 12 * C), 0
 def _w_grad_t(a): N, k, C = a[3], a[4], a[5]; return N * (12 * k + 12 * C), 0
 def _w_dcn(a): N, k, C = a[2], a[3], a[4]; return N * (12 * k + 20 * C + (8 * C if a[13] else 0)), 0     # + x copy-through
@@ -664,7 +675,7 @@ def main():
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-graph', action='store_true', help='time eager launches instead of CUDA-graph replays')
     ap.add_argument('--detail', default=None, help='write the per-call device-time table to this file')
-    ap.add_argument('--workload', default='train', choices=['train', 'seg', 'infer', 'fps'],
+    ap.add_argument('--workload', default='train', choices=['train', 'seg', 'infer', 'infer_depth2', 'fps'],
                     help="'train' (default, the contract line): configs[1] classifier training; 'seg': configs[2] part-segmentation "
                          "training; 'infer': configs[4] ScanObjectNN-shape inference; 'fps': the geodesic farthest-point sampling "
                          "pre-transform (1 GPU)")

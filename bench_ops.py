@@ -56,13 +56,15 @@ def main():
             data = D.transforms.MortonOrder()(data)
         N = B * P
         for k in args.k:
-            graph = ops.knn(data.pos, k, data.batch, num_clouds=B, want_edge_index=False)
+            graph = ops.knn(data.pos, k, data.batch, num_clouds=B, want_edge_index=False)      # writes idx and d2
             t_knn = time_ms(lambda: ops.knn(data.pos, k, data.batch, num_clouds=B, want_edge_index=False), flush, 3)
             xb, yb = ops.tangent_basis(data.norm)
             cp = graph.cloud_ptr
-            t_build = time_ms(lambda: ops.build_operators(data.pos, data.norm, xb, yb, graph, cp, B), flush)
-            G, Dv = ops.build_operators(data.pos, data.norm, xb, yb, graph, cp, B)
-            grad, div = ops.EllOperator('grad', graph, G, Dv), ops.EllOperator('div', graph, G, Dv)
+            # the build as the models call it (geometry.build_grad_div): mean edge lengths from the kNN distances that ride on
+            # the graph, per-cloud normalisation deferred to the operator applications
+            t_build = time_ms(lambda: ops.build_operators(data.pos, data.norm, xb, yb, graph, cp, B, deferred=True), flush)
+            G, Dv, scale = ops.build_operators(data.pos, data.norm, xb, yb, graph, cp, B, deferred=True)
+            grad, div = ops.EllOperator('grad', graph, G, Dv, scale), ops.EllOperator('div', graph, G, Dv, scale)
             graph.transpose()
             rec = dict(P=P, B=B, k=k,
                        knn_ms=round(t_knn, 4), knn_gbps=round(N * (12 + 4 * k) / t_knn / 1e6, 1),

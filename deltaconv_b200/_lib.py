@@ -37,18 +37,18 @@ _SIGNATURES = {
     'dc_estimate_basis': [_P, _P, _I, _I, _P, _P, _P, _P, _P],
     'dc_build_ws_bytes': [_I, _I],
     'dc_build_ws_min_bytes': [_I, _I],
-    'dc_build_grad_div': [_P, _P, _P, _P, _P, _P, _I, _I, _I, _F, _F, _F, _I, _I, _P, _P, _P, _P, _P, _P, _Z, _P],
+    'dc_build_grad_div': [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _F, _F, _F, _I, _I, _P, _P, _P, _P, _P, _P, _P, _Z, _P],
     'dc_set_build_chunk': [_I],
     'dc_build_static_max_points': [],
     'dc_build_static_max_clouds': [],
     'dc_build_grad_div_static': [_P, _P, _P, _P, _P, _P, _I, _I, _I, _F, _F, _F, _I, _I, _P, _P, _P],
     'dc_set_spmm_staged': [_I],
-    'dc_grad_fwd': [_P, _P, _I, _I, _I, _P, _L, _P, _L, _P, _I, _I, _P],
-    'dc_grad_bwd': [_P, _P, _P, _I, _I, _I, _P, _L, _P, _L, _P, _I, _I, _P],
-    'dc_divcurlnorm_fwd': [_P, _P, _I, _I, _I, _P, _L, _P, _L, _P, _L, _P, _L, _P, _L, _P, _L, _P, _I, _I, _P],
-    'dc_divcurlnorm_bwd': [_P, _P, _P, _I, _I, _I, _P, _L, _P, _L, _P, _L, _P, _L, _P, _L, _P, _I, _I, _P],
-    'dc_hodge_fwd': [_P, _P, _I, _I, _I, _P, _L, _P, _L, _P, _L, _P, _L, _P, _L, _P, _I, _I, _P],
-    'dc_hodge_bwd': [_P, _P, _P, _I, _I, _I, _P, _L, _P, _L, _P, _L, _P, _I, _I, _P],
+    'dc_grad_fwd': [_P, _P, _I, _I, _I, _P, _L, _P, _L, _P, _P, _I, _I, _P],
+    'dc_grad_bwd': [_P, _P, _P, _I, _I, _I, _P, _L, _P, _L, _P, _P, _I, _I, _P],
+    'dc_divcurlnorm_fwd': [_P, _P, _I, _I, _I, _P, _L, _P, _L, _P, _L, _P, _L, _P, _L, _P, _L, _P, _P, _I, _I, _P],
+    'dc_divcurlnorm_bwd': [_P, _P, _P, _I, _I, _I, _P, _L, _P, _L, _P, _L, _P, _L, _P, _L, _P, _P, _I, _I, _P],
+    'dc_hodge_fwd': [_P, _P, _I, _I, _I, _P, _L, _P, _L, _P, _L, _P, _L, _P, _L, _P, _P, _I, _I, _P],
+    'dc_hodge_bwd': [_P, _P, _P, _I, _I, _I, _P, _L, _P, _L, _P, _L, _P, _P, _I, _I, _P],
     'dc_gathermax_fwd': [_P, _I, _I, _I, _P, _L, _P, _L, _P, _P],
     'dc_gathermax_bwd': [_P, _P, _I, _I, _I, _P, _P, _L, _P, _L, _P],
     'dc_edge_diff_fwd': [_P, _I, _I, _I, _P, _L, _P, _P],
@@ -96,6 +96,7 @@ _RESTYPES = {'dc_launch_count': ctypes.c_longlong, 'dc_reset_launch_count': None
              'dc_gemm_ws_bytes': _Z, 'dc_central_ws_bytes': _Z, 'dc_knn_grid_ws_bytes': _Z, 'dc_geodesic_fps_ws_bytes': _Z}
 
 _lib = None
+ABI_VERSION = 2          # dc_abi_version() of the library these signatures describe
 
 
 class DeltaConvLibraryError(RuntimeError):
@@ -118,6 +119,9 @@ def load():
         fn = getattr(lib, name)          # AttributeError here = header/library mismatch
         fn.argtypes = argtypes
         fn.restype = _RESTYPES.get(name, _I)
+    if lib.dc_abi_version() != ABI_VERSION:
+        raise DeltaConvLibraryError(f"{LIB_PATH} has ABI version {lib.dc_abi_version()}, this package binds version {ABI_VERSION}: "
+                                    f"rebuild it (`python __graft_entry__.py build`)")
     _lib = lib
     return lib
 

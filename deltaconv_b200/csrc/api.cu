@@ -38,7 +38,7 @@ int dc_sm_count() {
 }
 
 extern "C" const char* dc_last_error(void) { return g_err; }
-extern "C" int dc_abi_version(void) { return 1; }
+extern "C" int dc_abi_version(void) { return 2; }      // 2: round-2 signature changes
 // kernels launched by this library since the last reset (bench.py reports it as gpu_launches)
 extern "C" long long dc_launch_count(void) { return g_launches.load(); }
 extern "C" void dc_reset_launch_count(void) { g_launches = 0; }

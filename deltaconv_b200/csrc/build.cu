@@ -116,6 +116,25 @@ edge_mean_kernel(const float* __restrict__ pos, const float4* __restrict__ posp,
     m[i] = acc / (float)k;
 }
 
+// The same from the squared distances the kNN search already has (dc_knn / dc_knn_grid d2 output): no gather at all, one
+// coalesced pass over [N,k] floats.  A padded slot (d2 = +inf) is measured against point 0 like the reference does.
+__global__ void edge_mean_from_d2_kernel(const float* __restrict__ d2, const float* __restrict__ pos, int N, int k, float* __restrict__ m) {
+    const int sub = threadIdx.x & 7;
+    const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 3;
+    float acc = 0.f;
+    if (i < N) {
+        for (int e = sub; e < k; e += 8) {
+            float q = __ldg(d2 + (size_t)i * k + e);
+            if (isinf(q)) { const V3 d = v3_load(pos) - v3_load(pos + 3 * (size_t)i); q = dot(d, d); }
+            acc += q > 0.f ? q * dc_rsqrt(q) : 0.f;
+        }
+    }
+    acc += __shfl_xor_sync(FULL, acc, 4);
+    acc += __shfl_xor_sync(FULL, acc, 2);
+    acc += __shfl_xor_sync(FULL, acc, 1);
+    if (i < N && sub == 0) m[i] = acc / (float)k;
+}
+
 // ---- per-cloud mean of m (scatter_mean, grad_div_mls.py:112); fixed-order tree => deterministic
 constexpr int CLOUD_MEAN_T = 1024;
 __global__ void __launch_bounds__(CLOUD_MEAN_T) cloud_mean_kernel(const float* __restrict__ m, const int* __restrict__ cloud_ptr, int B,
@@ -301,6 +320,12 @@ scale_kernel(V* __restrict__ G, V* __restrict__ D, const int* __restrict__ cloud
     }
 }
 
+// deferred normalisation: the factor of every point, for consumers that apply it to their result rows
+__global__ void point_scale_kernel(const int* __restrict__ cloud_ptr, int B, const unsigned* __restrict__ S, int N, float* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < N) out[i] = fit_scale(__uint_as_float(__ldg(S + cloud_of(cloud_ptr, B, i))));
+}
+
 size_t fit_smem_bytes(int T, int k) { return (size_t)k * (T + 1) * (sizeof(float4) + sizeof(int)); }
 
 struct FitArgs {
@@ -364,10 +389,12 @@ extern "C" size_t dc_build_ws_bytes(int N, int B) { return build_ws_min_bytes(N,
 extern "C" size_t dc_build_ws_min_bytes(int N, int B) { return build_ws_min_bytes(N, B); }
 
 extern "C" int dc_build_grad_div(const float* pos, const float* normal, const float* xb, const float* yb,
-                                 const int32_t* idx, const int32_t* cloud_ptr, int B, int N, int k,
+                                 const int32_t* idx, const float* d2_or_null, const int32_t* cloud_ptr, int B, int N, int k,
                                  float kernel_width, float lam, float lam_shape, int use_shape, int normalized,
-                                 float* G, float* D, float* dbg_coords, float* dbg_weights, float* dbg_mapping,
+                                 float* G, float* D, float* point_scale_or_null, float* dbg_coords, float* dbg_weights, float* dbg_mapping,
                                  void* ws, size_t ws_bytes, void* stream) {
+    DC_REQUIRE(normalized >= 0 && normalized <= 2, "dc_build_grad_div: normalized must be 0, 1 or 2 (deferred)");
+    DC_REQUIRE(normalized != 2 || point_scale_or_null != nullptr, "dc_build_grad_div: normalized = 2 (deferred) needs the point_scale output");
     DC_REQUIRE(k >= 1 && k <= 256, "dc_build_grad_div: k must be in [1,256] (got %d)", k);
     DC_REQUIRE(B >= 1, "dc_build_grad_div: B must be >= 1");
     DC_REQUIRE(ws_bytes >= build_ws_min_bytes(N, B), "dc_build_grad_div: workspace too small (%zu < %zu)", ws_bytes,
@@ -392,12 +419,12 @@ extern "C" int dc_build_grad_div(const float* pos, const float* normal, const fl
     }
     if (packed) {
         pack_kernel<<<dc_ceil_div(N, 256), 256, 0, st>>>(pos, xb, yb, N, posp, frm);
-        edge_mean_kernel<true><<<dc_ceil_div(N, EDGE_T), EDGE_T, edge_smem, st>>>(pos, posp, idx, N, k, m);
         rc = dc_check_launch_n("dc_build_grad_div/pack", 1);
         if (rc) return rc;
-    } else {
-        edge_mean_kernel<false><<<dc_ceil_div(N, EDGE_T), EDGE_T, edge_smem, st>>>(pos, nullptr, idx, N, k, m);
     }
+    if (d2_or_null) edge_mean_from_d2_kernel<<<dc_ceil_div((long long)N * 8, 256), 256, 0, st>>>(d2_or_null, pos, N, k, m);
+    else if (packed) edge_mean_kernel<true><<<dc_ceil_div(N, EDGE_T), EDGE_T, edge_smem, st>>>(pos, posp, idx, N, k, m);
+    else edge_mean_kernel<false><<<dc_ceil_div(N, EDGE_T), EDGE_T, edge_smem, st>>>(pos, nullptr, idx, N, k, m);
     cloud_mean_kernel<<<B, CLOUD_MEAN_T, 0, st>>>(m, cloud_ptr, B, abar, S);
     rc = dc_check_launch_n("dc_build_grad_div/mean", 2);
     if (rc) return rc;
@@ -411,14 +438,14 @@ extern "C" int dc_build_grad_div(const float* pos, const float* normal, const fl
     // short fit launch ends in a partially filled wave; so the default is one chunk.
     long long chunk = g_build_chunk_points > 0 ? g_build_chunk_points : N;
     chunk = (chunk + T - 1) / T * T;
-    if (!normalized || chunk > N) chunk = N;
+    if (normalized != 1 || chunk > N) chunk = N;
     for (long long n0 = 0; n0 < N; n0 += chunk) {
         const int n1 = (int)(n0 + chunk < N ? n0 + chunk : N);
         if (T == 128) rc = launch_fit<128>(a, (int)n0, n1, st);
         else if (T == 64) rc = launch_fit<64>(a, (int)n0, n1, st);
         else rc = launch_fit<32>(a, (int)n0, n1, st);
         if (rc) return rc;
-        if (normalized) {
+        if (normalized == 1) {
             const int tiles = dc_ceil_div(n1 - (int)n0, SCALE_PTS) + 1;
             const int cap = dc_sm_count() * 8;
             const int grid = tiles < cap ? tiles : cap;
@@ -428,6 +455,11 @@ extern "C" int dc_build_grad_div(const float* pos, const float* normal, const fl
             rc = dc_check_launch("dc_build_grad_div/scale");
             if (rc) return rc;
         }
+    }
+    if (normalized == 2) {
+        point_scale_kernel<<<dc_ceil_div(N, 256), 256, 0, st>>>(cloud_ptr, B, S, N, point_scale_or_null);
+        rc = dc_check_launch("dc_build_grad_div/point_scale");
+        if (rc) return rc;
     }
     return DC_OK;
 }
@@ -510,6 +542,7 @@ extern "C" int dc_build_grad_div_static(const float* pos, const float* normal, c
         }
         scratch = scratch_of_device[dev];
     }
-    return dc_build_grad_div(pos, normal, xb, yb, idx, cloud_ptr, B, N, k, kernel_width, lam, lam_shape, use_shape,
-                             normalized, G, D, nullptr, nullptr, nullptr, scratch, DC_STATIC_SCRATCH_BYTES, stream);
+    DC_REQUIRE(normalized == 0 || normalized == 1, "dc_build_grad_div_static: normalized must be 0 or 1");
+    return dc_build_grad_div(pos, normal, xb, yb, idx, nullptr, cloud_ptr, B, N, k, kernel_width, lam, lam_shape, use_shape,
+                             normalized, G, D, nullptr, nullptr, nullptr, nullptr, scratch, DC_STATIC_SCRATCH_BYTES, stream);
 }

@@ -42,6 +42,9 @@ struct SpArgs {
     float* out2; long long ld_out2;
     const float* cp_src; long long ld_cp_src;   // OP_DIVCURL: x [N,C], OP_HODGE: v [2N,C] — copied through into a column
     float* cp_dst; long long ld_cp_dst;         // slice of the concatenation buffer (saves a strided copy launch)
+    const float* row_scale;                       // nullable: per-point factor of the operator (deferred per-cloud normalisation of
+                                                  // build_grad_div, grad_div_mls.py:258-260).  All of a point's neighbours lie in its
+                                                  // cloud, so for every one of the six operations the factor of the RESULT row applies
     const int* cloud_ptr; int B; int max_cloud;   // staged variant: clouds and the size of the largest one (0 = unknown)
 };
 
@@ -81,6 +84,8 @@ __global__ void __launch_bounds__(256) spmm_kernel(SpArgs a, int lpp_log2) {
     const int r = row_ok ? (int)row_ll : 0;
     const int ch = (blockIdx.y * lpp + sub) * VEC;
     const bool ch_ok = ch < a.C;
+    // the row's normalisation factor, requested before the gather loop so that its latency is hidden behind it
+    const float sc = (a.row_scale && row_ok) ? __ldg(a.row_scale + r) : 1.f;
 
     int t_begin, t_end;
     if (OpTraits<OP>::transposed) { t_begin = row_ok ? __ldg(a.in_ptr + r) : 0; t_end = row_ok ? __ldg(a.in_ptr + r + 1) : 0; }
@@ -144,6 +149,10 @@ __global__ void __launch_bounds__(256) spmm_kernel(SpArgs a, int lpp_log2) {
         }
     }
     if (!row_ok || !ch_ok) return;
+    if (a.row_scale) {
+        acc0 = V::map2(acc0, acc0, [sc](float p, float) { return p * sc; });
+        acc1 = V::map2(acc1, acc1, [sc](float p, float) { return p * sc; });
+    }
     if (OP == OP_DIVCURL && a.cp_src) V::load(a.cp_src + (size_t)r * a.ld_cp_src + ch).store(a.cp_dst + (size_t)r * a.ld_cp_dst + ch);
     if (OP == OP_HODGE && a.cp_src) {
         V::load(a.cp_src + (size_t)(2 * r) * a.ld_cp_src + ch).store(a.cp_dst + (size_t)(2 * r) * a.ld_cp_dst + ch);
@@ -247,6 +256,7 @@ __global__ void __launch_bounds__(STAGE ? 256 : 1024) spmm_staged_kernel(SpArgs 
         const int rl = rbase + (threadIdx.x >> 5) * rows_per_warp + (lane >> lpp_log2);   // local row
         const bool row_ok = rl < P;
         const int r = s + (row_ok ? rl : 0);
+        const float sc = (a.row_scale && row_ok) ? __ldg(a.row_scale + r) : 1.f;
         int t_begin, len;
         if (OpTraits<OP>::transposed) { t_begin = row_ok ? __ldg(a.in_ptr + r) : 0; len = row_ok ? __ldg(a.in_ptr + r + 1) - t_begin : 0; }
         else { t_begin = 0; len = row_ok ? a.k : 0; }
@@ -306,6 +316,10 @@ __global__ void __launch_bounds__(STAGE ? 256 : 1024) spmm_staged_kernel(SpArgs 
             }
         }
         if (!row_ok || !ch_ok) continue;
+        if (a.row_scale) {
+            acc0 = V::map2(acc0, acc0, [sc](float p, float) { return p * sc; });
+            acc1 = V::map2(acc1, acc1, [sc](float p, float) { return p * sc; });
+        }
         if (OP == OP_DIVCURL && a.cp_src) V::load(a.cp_src + (size_t)r * a.ld_cp_src + ch).store(a.cp_dst + (size_t)r * a.ld_cp_dst + ch);
         if (OP == OP_HODGE && a.cp_src) {
             V::load(a.cp_src + (size_t)(2 * r) * a.ld_cp_src + ch).store(a.cp_dst + (size_t)(2 * r) * a.ld_cp_dst + ch);
@@ -511,71 +525,71 @@ extern "C" int dc_ell_transpose(const int32_t* idx, int N, int k, int32_t* in_pt
 }
 
 extern "C" int dc_grad_fwd(const int32_t* idx, const float* G, int N, int k, int C, const float* x, int64_t ldx,
-                           float* out, int64_t ldo, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream) {
+                           float* out, int64_t ldo, const float* row_scale_or_null, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream) {
     SpArgs a = {};
     SP_COMMON(a, N, k, C);
     a.idx = idx; a.coef = (const float2*)G; a.in0 = x; a.ld_in0 = ldx; a.out0 = out; a.ld_out0 = ldo;
-    a.cloud_ptr = cloud_ptr_or_null; a.B = B; a.max_cloud = max_cloud_points;
+    a.row_scale = row_scale_or_null; a.cloud_ptr = cloud_ptr_or_null; a.B = B; a.max_cloud = max_cloud_points;
     return launch_spmm<OP_GRAD>(a, (cudaStream_t)stream);
 }
 
 extern "C" int dc_grad_bwd(const int32_t* in_ptr, const int32_t* in_edge, const float* G, int N, int k, int C,
-                           const float* dV, int64_t ld_dv, float* dX, int64_t ld_dx, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream) {
+                           const float* dV, int64_t ld_dv, float* dX, int64_t ld_dx, const float* row_scale_or_null, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream) {
     SpArgs a = {};
     SP_COMMON(a, N, k, C);
     a.in_ptr = in_ptr; a.in_edge = in_edge; a.coef = (const float2*)G; a.in0 = dV; a.ld_in0 = ld_dv; a.out0 = dX; a.ld_out0 = ld_dx;
-    a.cloud_ptr = cloud_ptr_or_null; a.B = B; a.max_cloud = max_cloud_points;
+    a.row_scale = row_scale_or_null; a.cloud_ptr = cloud_ptr_or_null; a.B = B; a.max_cloud = max_cloud_points;
     return launch_spmm<OP_GRAD_T>(a, (cudaStream_t)stream);
 }
 
 extern "C" int dc_divcurlnorm_fwd(const int32_t* idx, const float* D, int N, int k, int C, const float* v, int64_t ldv,
                                   float* div_or_null, int64_t ld_div, float* curl_or_null, int64_t ld_curl,
                                   float* norm_or_null, int64_t ld_norm, const float* x_or_null, int64_t ldx, float* x_copy, int64_t ld_copy,
-                                  const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream) {
+                                  const float* row_scale_or_null, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream) {
     SpArgs a = {};
     SP_COMMON(a, N, k, C);
     DC_REQUIRE(x_or_null == nullptr || x_copy != nullptr, "dc_divcurlnorm_fwd: x given without a destination");
     a.cp_src = x_or_null; a.ld_cp_src = ldx; a.cp_dst = x_copy; a.ld_cp_dst = ld_copy;
     a.idx = idx; a.coef = (const float2*)D; a.in0 = v; a.ld_in0 = ldv;
     a.out0 = div_or_null; a.ld_out0 = ld_div; a.out1 = curl_or_null; a.ld_out1 = ld_curl; a.out2 = norm_or_null; a.ld_out2 = ld_norm;
-    a.cloud_ptr = cloud_ptr_or_null; a.B = B; a.max_cloud = max_cloud_points;
+    a.row_scale = row_scale_or_null; a.cloud_ptr = cloud_ptr_or_null; a.B = B; a.max_cloud = max_cloud_points;
     return launch_spmm<OP_DIVCURL>(a, (cudaStream_t)stream);
 }
 
 extern "C" int dc_divcurlnorm_bwd(const int32_t* in_ptr, const int32_t* in_edge, const float* D, int N, int k, int C,
                                   const float* d_div_or_null, int64_t ld_ddiv, const float* d_curl_or_null, int64_t ld_dcurl,
                                   const float* d_norm_or_null, int64_t ld_dnorm, const float* v, int64_t ldv,
-                                  float* dV, int64_t ld_dv, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream) {
+                                  float* dV, int64_t ld_dv, const float* row_scale_or_null, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream) {
     SpArgs a = {};
     SP_COMMON(a, N, k, C);
     a.in_ptr = in_ptr; a.in_edge = in_edge; a.coef = (const float2*)D;
     a.in0 = d_div_or_null; a.ld_in0 = ld_ddiv; a.in1 = d_curl_or_null; a.ld_in1 = ld_dcurl;
     a.in2 = d_norm_or_null; a.ld_in2 = ld_dnorm; a.in3 = v; a.ld_in3 = ldv;
     a.out0 = dV; a.ld_out0 = ld_dv;
-    a.cloud_ptr = cloud_ptr_or_null; a.B = B; a.max_cloud = max_cloud_points;
+    a.row_scale = row_scale_or_null; a.cloud_ptr = cloud_ptr_or_null; a.B = B; a.max_cloud = max_cloud_points;
     return launch_spmm<OP_DIVCURL_T>(a, (cudaStream_t)stream);
 }
 
 extern "C" int dc_hodge_fwd(const int32_t* idx, const float* G, int N, int k, int C, const float* div_v, int64_t ld_a,
                             const float* curl_v, int64_t ld_b, float* out, int64_t ldo, const float* v_or_null, int64_t ldv,
-                            float* v_copy, int64_t ld_copy, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream) {
+                            float* v_copy, int64_t ld_copy, const float* row_scale_or_null, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream) {
     SpArgs a = {};
     SP_COMMON(a, N, k, C);
     DC_REQUIRE(v_or_null == nullptr || v_copy != nullptr, "dc_hodge_fwd: v given without a destination");
     a.cp_src = v_or_null; a.ld_cp_src = ldv; a.cp_dst = v_copy; a.ld_cp_dst = ld_copy;
     a.idx = idx; a.coef = (const float2*)G; a.in0 = div_v; a.ld_in0 = ld_a; a.in1 = curl_v; a.ld_in1 = ld_b; a.out0 = out; a.ld_out0 = ldo;
-    a.cloud_ptr = cloud_ptr_or_null; a.B = B; a.max_cloud = max_cloud_points;
+    a.row_scale = row_scale_or_null; a.cloud_ptr = cloud_ptr_or_null; a.B = B; a.max_cloud = max_cloud_points;
     return launch_spmm<OP_HODGE>(a, (cudaStream_t)stream);
 }
 
 extern "C" int dc_hodge_bwd(const int32_t* in_ptr, const int32_t* in_edge, const float* G, int N, int k, int C,
                             const float* d_out, int64_t ld_do, float* d_div, int64_t ld_da, float* d_curl, int64_t ld_db,
-                            const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream) {
+                            const float* row_scale_or_null, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream) {
     SpArgs a = {};
     SP_COMMON(a, N, k, C);
     a.in_ptr = in_ptr; a.in_edge = in_edge; a.coef = (const float2*)G; a.in0 = d_out; a.ld_in0 = ld_do;
     a.out0 = d_div; a.ld_out0 = ld_da; a.out1 = d_curl; a.ld_out1 = ld_db;
-    a.cloud_ptr = cloud_ptr_or_null; a.B = B; a.max_cloud = max_cloud_points;
+    a.row_scale = row_scale_or_null; a.cloud_ptr = cloud_ptr_or_null; a.B = B; a.max_cloud = max_cloud_points;
     return launch_spmm<OP_HODGE_T>(a, (cudaStream_t)stream);
 }
 

@@ -46,9 +46,9 @@ def build_grad_div(pos, normal, x_basis, y_basis, edge_index, batch=None, kernel
     (grad_div_mls.py:197-277) as `EllOperator`s sharing one fixed-k ELL storage."""
     graph, cp, B = _prepare(pos, edge_index, batch)
     with torch.no_grad():
-        G, D = ops.build_operators(pos, normal, x_basis, y_basis, graph, cp, B, kernel_width, regularizer,
-                                   normalized, shape_regularizer)
-    return ops.EllOperator('grad', graph, G, D), ops.EllOperator('div', graph, G, D)
+        G, D, scale = ops.build_operators(pos, normal, x_basis, y_basis, graph, cp, B, kernel_width, regularizer,
+                                          normalized, shape_regularizer, deferred=True)
+    return ops.EllOperator('grad', graph, G, D, scale), ops.EllOperator('div', graph, G, D, scale)
 
 
 def operator_parts(pos, normal, x_basis, y_basis, edge_index, batch=None, kernel_width=1, regularizer=0.001,

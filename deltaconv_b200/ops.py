@@ -101,6 +101,7 @@ class EllGraph:
         self.cloud_ptr, self.B, self.max_cloud = cloud_ptr, num_clouds, int(max_cloud or 0)
         self._transpose = None
         self._edge_index = None
+        self.d2 = self.d2_of = None
 
     def clouds(self):
         """(cloud_ptr pointer or None, B, largest cloud) as the SpMM entry points take them."""
@@ -132,8 +133,9 @@ KNN_GRID_FROM = 1536      # points in the largest cloud from which the grid sear
 KNN_METHOD = 'auto'       # 'auto' | 'brute' | 'grid' (tests and benchmarks force one)
 
 
-def knn(pos, k, batch=None, num_clouds=None, want_edge_index=True, max_points=None):
-    """ELL kNN graph of `pos` [N,3] per cloud (self included, ascending (d2, index))."""
+def knn(pos, k, batch=None, num_clouds=None, want_edge_index=True, max_points=None, want_d2=True):
+    """ELL kNN graph of `pos` [N,3] per cloud (self included, ascending (d2, index)).  The squared distances ride along as
+    `graph.d2` [N,k] (+inf in padded slots): the operator build takes the mean edge lengths from them."""
     pos = _f32(pos, 'pos').contiguous()
     if pos.dim() != 2 or pos.size(1) != 3:
         raise _lib.DeltaConvLibraryError(f"knn: expected pos of shape [N,3], got {tuple(pos.shape)}")
@@ -141,14 +143,16 @@ def knn(pos, k, batch=None, num_clouds=None, want_edge_index=True, max_points=No
     cp, B, maxp = cloud_layout(batch, N, pos.device, num_clouds, max_points)
     idx = torch.empty(N, k, dtype=_I32, device=pos.device)
     ei = torch.empty(2, N * k, dtype=_I64, device=pos.device) if want_edge_index else None
+    d2 = torch.empty(N, k, dtype=_F32, device=pos.device) if want_d2 else None
     method = KNN_METHOD if KNN_METHOD != 'auto' else ('grid' if maxp > KNN_GRID_FROM else 'brute')
     if method == 'grid':                 # large clouds: uniform grid + ring search, same exact result (dc_knn_grid)
         nb = query('dc_knn_grid_ws_bytes', N, B)
         ws = workspace(nb, pos.device)
-        call('dc_knn_grid', ptr(pos), ptr(cp), B, N, k, ptr(idx), ptr(ei), None, ptr(ws), nb)
+        call('dc_knn_grid', ptr(pos), ptr(cp), B, N, k, ptr(idx), ptr(ei), ptr(d2), ptr(ws), nb)
     else:
-        call('dc_knn', ptr(pos), ptr(cp), B, N, k, ptr(idx), ptr(ei), None)
+        call('dc_knn', ptr(pos), ptr(cp), B, N, k, ptr(idx), ptr(ei), ptr(d2))
     graph = EllGraph(idx, cp, B, maxp)
+    graph.d2, graph.d2_of = d2, pos              # distances belong to these positions (build_operators checks the tensor)
     if ei is not None:
         ei._dc_graph = graph
         graph._edge_index = ei
@@ -269,7 +273,9 @@ def estimate_frames(pos, graph, orientation=None):
 
 
 def build_operators(pos, normal, xb, yb, graph, cloud_ptr, B, kernel_width=1.0, lam=1e-3, normalized=True,
-                    lam_shape=None, debug=False):
+                    lam_shape=None, debug=False, deferred=False):
+    """G, D [N,k,2] of dc_build_grad_div (normalised entries), or with deferred=True (G_raw, D_raw, point_scale [N] or None):
+    the entries before the per-cloud normalisation and the factor the operator applications multiply their rows with."""
     pos, normal, xb, yb = (_f32(t, n).contiguous() for t, n in ((pos, 'pos'), (normal, 'normal'), (xb, 'x_basis'), (yb, 'y_basis')))
     N, k = graph.N, graph.k
     dev = pos.device
@@ -279,12 +285,19 @@ def build_operators(pos, normal, xb, yb, graph, cloud_ptr, B, kernel_width=1.0, 
     if debug:
         dbg = [torch.empty(N, k, 2, dtype=_F32, device=dev), torch.empty(N, k, dtype=_F32, device=dev),
                torch.empty(N, k, 2, 2, dtype=_F32, device=dev)]
+    mode = (2 if deferred else 1) if normalized else 0
+    scale = torch.empty(N, dtype=_F32, device=dev) if mode == 2 else None
+    # the kNN's squared distances, if the graph was built on these very positions
+    d2 = graph.d2 if (graph.d2 is not None and graph.d2_of is not None and graph.d2_of.data_ptr() == pos.data_ptr()
+                      and graph.d2_of._version == pos._version) else None
     nbytes = query('dc_build_ws_bytes', N, B)
     ws = workspace(nbytes, dev)
-    call('dc_build_grad_div', ptr(pos), ptr(normal), ptr(xb), ptr(yb), ptr(graph.idx), ptr(cloud_ptr), B, N, k,
+    call('dc_build_grad_div', ptr(pos), ptr(normal), ptr(xb), ptr(yb), ptr(graph.idx), ptr(d2), ptr(cloud_ptr), B, N, k,
          float(kernel_width), float(lam), float(lam_shape if lam_shape is not None else 0.0),
-         int(lam_shape is not None), int(bool(normalized)), ptr(G), ptr(D), ptr(dbg[0]), ptr(dbg[1]), ptr(dbg[2]),
+         int(lam_shape is not None), mode, ptr(G), ptr(D), ptr(scale), ptr(dbg[0]), ptr(dbg[1]), ptr(dbg[2]),
          ptr(ws), nbytes)
+    if deferred:
+        return (G, D, scale, dbg) if debug else (G, D, scale)
     return (G, D, dbg) if debug else (G, D)
 
 
@@ -300,7 +313,7 @@ class _GradApply(torch.autograd.Function):
         if x.size(0) != g.N:
             raise _lib.DeltaConvLibraryError(f"grad @ x: x has {x.size(0)} rows, operator has {g.N} columns")
         out = torch.empty(2 * g.N, x.size(1), dtype=_F32, device=x.device)
-        call('dc_grad_fwd', ptr(g.idx), ptr(op.G), g.N, g.k, x.size(1), ptr(x), ldx, ptr(out), out.size(1), *g.clouds())
+        call('dc_grad_fwd', ptr(g.idx), ptr(op.G_raw), g.N, g.k, x.size(1), ptr(x), ldx, ptr(out), out.size(1), *op.tail())
         ctx.op = op
         return out
 
@@ -310,7 +323,7 @@ class _GradApply(torch.autograd.Function):
         dv, ld = _mat(dv, 'grad_output')
         in_ptr, in_edge = g.transpose()
         dx = torch.empty(g.N, dv.size(1), dtype=_F32, device=dv.device)
-        call('dc_grad_bwd', ptr(in_ptr), ptr(in_edge), ptr(op.G), g.N, g.k, dv.size(1), ptr(dv), ld, ptr(dx), dx.size(1), *g.clouds())
+        call('dc_grad_bwd', ptr(in_ptr), ptr(in_edge), ptr(op.G_raw), g.N, g.k, dv.size(1), ptr(dv), ld, ptr(dx), dx.size(1), *op.tail())
         return dx, None
 
 
@@ -323,7 +336,7 @@ class _DivApply(torch.autograd.Function):
             raise _lib.DeltaConvLibraryError(f"div @ v: v has {v.size(0)} rows, operator has {2 * g.N} columns")
         C = v.size(1)
         out = torch.empty(g.N, C, dtype=_F32, device=v.device)
-        call('dc_divcurlnorm_fwd', ptr(g.idx), ptr(op.D), g.N, g.k, C, ptr(v), ldv, ptr(out), C, None, 0, None, 0, None, 0, None, 0, *g.clouds())
+        call('dc_divcurlnorm_fwd', ptr(g.idx), ptr(op.D_raw), g.N, g.k, C, ptr(v), ldv, ptr(out), C, None, 0, None, 0, None, 0, None, 0, *op.tail())
         ctx.op = op
         return out
 
@@ -334,18 +347,43 @@ class _DivApply(torch.autograd.Function):
         in_ptr, in_edge = g.transpose()
         C = dd.size(1)
         dv = torch.empty(2 * g.N, C, dtype=_F32, device=dd.device)
-        call('dc_divcurlnorm_bwd', ptr(in_ptr), ptr(in_edge), ptr(op.D), g.N, g.k, C, ptr(dd), ld, None, 0, None, 0,
-             None, 0, ptr(dv), C, *g.clouds())
+        call('dc_divcurlnorm_bwd', ptr(in_ptr), ptr(in_edge), ptr(op.D_raw), g.N, g.k, C, ptr(dd), ld, None, 0, None, 0,
+             None, 0, ptr(dv), C, *op.tail())
         return dv, None
 
 
 class EllOperator:
     """What `build_grad_div` returns in place of a torch_sparse.SparseTensor: supports `.size(i)`,
     `.sizes()` and `@ dense` (differentiable w.r.t. the dense operand), like the reference's
-    operators are used (deltanet_base.py:78, deltaconv.py:57,66, operators.py:23-46)."""
+    operators are used (deltanet_base.py:78, deltaconv.py:57,66, operators.py:23-46).
 
-    def __init__(self, kind, graph, G, D):
-        self.kind, self.graph, self.G, self.D = kind, graph, G, D
+    Storage: the kernels read `G_raw` / `D_raw` [N,k,2] and, when `scale` [N] is given, multiply their result rows by it (the
+    per-cloud normalisation of grad_div_mls.py:258-260, deferred: dc_build_grad_div normalized = 2).  `G` / `D` are the
+    reference's entries (normalised), materialised on first access for inspection, `coo()` and `to_dense()`."""
+
+    def __init__(self, kind, graph, G, D, scale=None):
+        self.kind, self.graph, self.G_raw, self.D_raw, self.scale = kind, graph, G, D, scale
+        self._entries = None
+
+    def _normalised(self):
+        if self.scale is None:
+            return self.G_raw, self.D_raw
+        if self._entries is None:
+            f = self.scale[:, None, None]
+            self._entries = (self.G_raw * f, self.D_raw * f)
+        return self._entries
+
+    @property
+    def G(self):
+        return self._normalised()[0]
+
+    @property
+    def D(self):
+        return self._normalised()[1]
+
+    def tail(self):
+        """(row_scale pointer, cloud_ptr pointer, B, largest cloud): the trailing arguments of the operator applications."""
+        return (ptr(self.scale),) + self.graph.clouds()
 
     def size(self, dim):
         N = self.graph.N
@@ -403,9 +441,9 @@ class _ScalarCat(torch.autograd.Function):
         if v.size(0) != 2 * g.N or v.size(1) != C or x.size(0) != g.N:
             raise _lib.DeltaConvLibraryError(f"DeltaConv: x {tuple(x.shape)} / v {tuple(v.shape)} do not match N={g.N}")
         cat = torch.empty(g.N, 4 * C, dtype=_F32, device=x.device)
-        call('dc_divcurlnorm_fwd', ptr(g.idx), ptr(op.D), g.N, g.k, C, ptr(v), ldv,
+        call('dc_divcurlnorm_fwd', ptr(g.idx), ptr(op.D_raw), g.N, g.k, C, ptr(v), ldv,
              cat.data_ptr() + 4 * C, 4 * C, cat.data_ptr() + 8 * C, 4 * C, cat.data_ptr() + 12 * C, 4 * C,
-             ptr(x), ldx, cat.data_ptr(), 4 * C, *g.clouds())
+             ptr(x), ldx, cat.data_ptr(), 4 * C, *op.tail())
         dc = cat[:, C:3 * C]
         ctx.op, ctx.C = op, C
         ctx.save_for_backward(v)
@@ -426,8 +464,8 @@ class _ScalarCat(torch.autograd.Function):
             d_div, d_curl, ldt = dcat.data_ptr() + 4 * C, dcat.data_ptr() + 8 * C, ld
         in_ptr, in_edge = g.transpose()
         dv = torch.empty(2 * g.N, C, dtype=_F32, device=dcat.device)
-        call('dc_divcurlnorm_bwd', ptr(in_ptr), ptr(in_edge), ptr(op.D), g.N, g.k, C, d_div, ldt, d_curl, ldt,
-             dcat.data_ptr() + 12 * C, ld, ptr(v), ldv, ptr(dv), C, *g.clouds())
+        call('dc_divcurlnorm_bwd', ptr(in_ptr), ptr(in_edge), ptr(op.D_raw), g.N, g.k, C, d_div, ldt, d_curl, ldt,
+             dcat.data_ptr() + 12 * C, ld, ptr(v), ldv, ptr(dv), C, *op.tail())
         return dcat[:, :C], dv, None
 
 
@@ -464,9 +502,9 @@ class _VectorCat(torch.autograd.Function):
             cat = torch.empty(2 * g.N, W, dtype=_F32, device=v.device)
         else:
             cat = torch.zeros(2 * g.N, W, dtype=_F32, device=v.device)
-        call('dc_hodge_fwd', ptr(g.idx), ptr(op.G), g.N, g.k, Cin, ptr(dc), ld_dc, dc.data_ptr() + 4 * Cin, ld_dc,
-             cat.data_ptr() + 4 * c_h, W, ptr(v), ldv, cat.data_ptr(), W, *g.clouds())
-        call('dc_grad_fwd', ptr(g.idx), ptr(op.G), g.N, g.k, Cout, ptr(x_new), ldx, cat.data_ptr() + 4 * c_g, W, *g.clouds())
+        call('dc_hodge_fwd', ptr(g.idx), ptr(op.G_raw), g.N, g.k, Cin, ptr(dc), ld_dc, dc.data_ptr() + 4 * Cin, ld_dc,
+             cat.data_ptr() + 4 * c_h, W, ptr(v), ldv, cat.data_ptr(), W, *op.tail())
+        call('dc_grad_fwd', ptr(g.idx), ptr(op.G_raw), g.N, g.k, Cout, ptr(x_new), ldx, cat.data_ptr() + 4 * c_g, W, *op.tail())
         ctx.op, ctx.Cin, ctx.Cout, ctx.c_h, ctx.c_g = op, Cin, Cout, c_h, c_g
         if col_map is not None:
             cat._dc_colmap = col_map
@@ -478,10 +516,10 @@ class _VectorCat(torch.autograd.Function):
         dcat, ld = _mat(dcat.contiguous(), 'grad_output')
         in_ptr, in_edge = g.transpose()
         ddc = torch.empty(g.N, 2 * Cin, dtype=_F32, device=dcat.device)
-        call('dc_hodge_bwd', ptr(in_ptr), ptr(in_edge), ptr(op.G), g.N, g.k, Cin, dcat.data_ptr() + 4 * ctx.c_h, ld,
-             ptr(ddc), 2 * Cin, ddc.data_ptr() + 4 * Cin, 2 * Cin, *g.clouds())
+        call('dc_hodge_bwd', ptr(in_ptr), ptr(in_edge), ptr(op.G_raw), g.N, g.k, Cin, dcat.data_ptr() + 4 * ctx.c_h, ld,
+             ptr(ddc), 2 * Cin, ddc.data_ptr() + 4 * Cin, 2 * Cin, *op.tail())
         dx = torch.empty(g.N, Cout, dtype=_F32, device=dcat.device)
-        call('dc_grad_bwd', ptr(in_ptr), ptr(in_edge), ptr(op.G), g.N, g.k, Cout, dcat.data_ptr() + 4 * ctx.c_g, ld, ptr(dx), Cout, *g.clouds())
+        call('dc_grad_bwd', ptr(in_ptr), ptr(in_edge), ptr(op.G_raw), g.N, g.k, Cout, dcat.data_ptr() + 4 * ctx.c_g, ld, ptr(dx), Cout, *op.tail())
         return dcat[:, :Cin], ddc, dx, None, None
 
 
@@ -507,7 +545,7 @@ class _CurlApply(torch.autograd.Function):
         g = op.graph
         C = v.size(1)
         out = torch.empty(g.N, C, dtype=_F32, device=v.device)
-        call('dc_divcurlnorm_fwd', ptr(g.idx), ptr(op.D), g.N, g.k, C, ptr(v), ldv, None, 0, ptr(out), C, None, 0, None, 0, None, 0, *g.clouds())
+        call('dc_divcurlnorm_fwd', ptr(g.idx), ptr(op.D_raw), g.N, g.k, C, ptr(v), ldv, None, 0, ptr(out), C, None, 0, None, 0, None, 0, *op.tail())
         ctx.op = op
         return out
 
@@ -518,8 +556,8 @@ class _CurlApply(torch.autograd.Function):
         in_ptr, in_edge = g.transpose()
         C = dcurl.size(1)
         dv = torch.empty(2 * g.N, C, dtype=_F32, device=dcurl.device)
-        call('dc_divcurlnorm_bwd', ptr(in_ptr), ptr(in_edge), ptr(op.D), g.N, g.k, C, None, 0, ptr(dcurl), ld, None, 0,
-             None, 0, ptr(dv), C, *g.clouds())
+        call('dc_divcurlnorm_bwd', ptr(in_ptr), ptr(in_edge), ptr(op.D_raw), g.N, g.k, C, None, 0, ptr(dcurl), ld, None, 0,
+             None, 0, ptr(dv), C, *op.tail())
         return dv, None
 
 

@@ -100,14 +100,21 @@ int dc_estimate_basis(const float* pos, const int32_t* idx, int N, int k, const 
 /* build_grad_div(pos, normal, x_basis, y_basis, edge_index, batch, kernel_width, regularizer,
  * normalized, shape_regularizer) — grad_div_mls.py:197-277 with coords_projected (:72-97),
  * gaussian_weights (:100-116), weighted_least_squares (:119-152), fit_vector_mapping (:155-194).
- * Optional debug outputs expose those helpers' results: coords [N,k,2], weights [N,k], mapping [N,k,2,2]. */
+ * Optional debug outputs expose those helpers' results: coords [N,k,2], weights [N,k], mapping [N,k,2,2].
+ * d2_or_null [N,k]: the squared neighbour distances of dc_knn / dc_knn_grid (+inf in padded slots); given, the per-point mean
+ * edge length (:233, :112) is taken from them instead of gathering the neighbour positions again.
+ * normalized: 0 = no per-cloud normalisation (:258-260), 1 = G and D hold the normalised entries, 2 = deferred: G and D hold
+ * the entries BEFORE the normalisation and point_scale [N] the factor of every point's cloud (1 / S_b, or 1 where S_b <= 1e-5);
+ * the operator applications take it as `row_scale` and multiply their result rows (every neighbour of a point lies in its
+ * cloud, and D = g M is linear in g), which saves a read-modify-write pass over all 16 k bytes per point of entries. */
 size_t dc_build_ws_bytes(int N, int B);       /* recommended: includes 48 B per point of repacked gather records */
 size_t dc_build_ws_min_bytes(int N, int B);   /* accepted minimum (4 B per point + 8 B per cloud): slower scalar gathers */
 int dc_set_build_chunk(int points);    /* tuning: points per fit/normalise chunk, 0 = automatic; no reference counterpart */
 int dc_build_grad_div(const float* pos, const float* normal, const float* xb, const float* yb,
-                      const int32_t* idx, const int32_t* cloud_ptr, int B, int N, int k,
+                      const int32_t* idx, const float* d2_or_null, const int32_t* cloud_ptr, int B, int N, int k,
                       float kernel_width, float lam, float lam_shape, int use_shape, int normalized,
-                      float* G, float* D, float* dbg_coords, float* dbg_weights, float* dbg_mapping,
+                      float* G, float* D, float* point_scale_or_null,
+                      float* dbg_coords, float* dbg_weights, float* dbg_mapping,
                       void* ws, size_t ws_bytes, void* stream);
 
 /* Same build for callers that must not allocate device memory (a host whose memory is partitioned once
@@ -134,31 +141,31 @@ int dc_build_grad_div_static(const float* pos, const float* normal, const float*
 int dc_set_spmm_staged(int v);
 /* grad @ x — deltanet_base.py:78, deltaconv.py:66:  out[2i+a,:] = sum_e G[i,e,a] x[idx[i,e],:] */
 int dc_grad_fwd(const int32_t* idx, const float* G, int N, int k, int C, const float* x, int64_t ldx,
-                float* out, int64_t ldo, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream);
+                float* out, int64_t ldo, const float* row_scale_or_null, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream);
 /* its transpose (autograd of the above w.r.t. x): dX[j,:] = sum_{(i,e)->j} G[i,e,:] . dV[2i:2i+2,:] */
 int dc_grad_bwd(const int32_t* in_ptr, const int32_t* in_edge, const float* G, int N, int k, int C,
-                const float* dV, int64_t ld_dv, float* dX, int64_t ld_dx, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream);
+                const float* dV, int64_t ld_dv, float* dX, int64_t ld_dx, const float* row_scale_or_null, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream);
 
 /* [div @ v | curl(v, div) | norm(v)] in one pass — deltaconv.py:57, operators.py:4-7,23-27.  With x given, x [N,C] is also
  * copied to x_copy (the first column block of the same torch.cat) by the same threads. */
 int dc_divcurlnorm_fwd(const int32_t* idx, const float* D, int N, int k, int C, const float* v, int64_t ldv,
                        float* div_or_null, int64_t ld_div, float* curl_or_null, int64_t ld_curl,
                        float* norm_or_null, int64_t ld_norm, const float* x_or_null, int64_t ldx, float* x_copy, int64_t ld_copy,
-                       const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream);
+                       const float* row_scale_or_null, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream);
 int dc_divcurlnorm_bwd(const int32_t* in_ptr, const int32_t* in_edge, const float* D, int N, int k, int C,
                        const float* d_div_or_null, int64_t ld_ddiv, const float* d_curl_or_null, int64_t ld_dcurl,
                        const float* d_norm_or_null, int64_t ld_dnorm, const float* v, int64_t ldv,
-                       float* dV, int64_t ld_dv, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream);
+                       float* dV, int64_t ld_dv, const float* row_scale_or_null, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream);
 
 /* hodge_laplacian(v, grad, div) given div v and curl v — operators.py:35-46:
  * out = -(grad(div_v) + J grad(curl_v)), rows interleaved like every vector field.  With v given, v [2N,C] is also copied to
  * v_copy (the first column block of torch.cat([v, hodge, grad x]), deltaconv.py:66). */
 int dc_hodge_fwd(const int32_t* idx, const float* G, int N, int k, int C, const float* div_v, int64_t ld_a,
                  const float* curl_v, int64_t ld_b, float* out, int64_t ldo, const float* v_or_null, int64_t ldv,
-                 float* v_copy, int64_t ld_copy, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream);
+                 float* v_copy, int64_t ld_copy, const float* row_scale_or_null, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream);
 int dc_hodge_bwd(const int32_t* in_ptr, const int32_t* in_edge, const float* G, int N, int k, int C,
                  const float* d_out, int64_t ld_do, float* d_div, int64_t ld_da, float* d_curl, int64_t ld_db,
-                 const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream);
+                 const float* row_scale_or_null, const int32_t* cloud_ptr_or_null, int B, int max_cloud_points, void* stream);
 
 /* ---- scalar stream: kNN max aggregation ------------------------------------------------------ */
 

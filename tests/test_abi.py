@@ -45,7 +45,7 @@ def test_ctypes_table_matches_header():
 @pytest.mark.skipif(not os.path.exists(_lib.LIB_PATH), reason='library not built')
 def test_loader_and_version():
     lib = _lib.load()
-    assert lib.dc_abi_version() == 1
+    assert lib.dc_abi_version() == 2
     assert lib.dc_last_error() is not None
 
 

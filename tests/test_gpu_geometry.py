@@ -382,3 +382,40 @@ def test_grid_knn_is_bit_identical_to_brute_force(sizes, k):
         out[method] = (g.idx.clone(), g.edge_index().clone())
     assert torch.equal(out['brute'][0], out['grid'][0])
     assert torch.equal(out['brute'][1], out['grid'][1])
+
+
+def test_deferred_normalisation_and_knn_distances_give_the_same_operators():
+    """geometry.build_grad_div stores the entries before the per-cloud normalisation plus one factor per point (applied by
+    the operator kernels) and takes the mean edge lengths from the kNN's squared distances.  Against the plain build
+    (normalised entries written by the library, neighbour positions gathered again): same entries to fp32 rounding, same
+    operator applications forward and backward."""
+    from deltaconv_b200 import ops
+    d = synth(3, 0, cfg=11, sizes=[500, 130, 1024])
+    pos, nrm, batch = d.pos.to(DEV), d.norm.to(DEV), d.batch.to(DEV)
+    graph = ops.knn(pos, 16, batch, num_clouds=3)
+    assert graph.d2 is not None and torch.isfinite(graph.d2).all()
+    nb = graph.idx.long()
+    assert torch.allclose(graph.d2, (pos[nb] - pos[:, None]).pow(2).sum(-1), rtol=1e-5, atol=1e-7)
+    xb, yb = ops.tangent_basis(nrm)
+    plain_graph = ops.EllGraph(graph.idx, graph.cloud_ptr, graph.B, graph.max_cloud)          # no distances attached
+    G1, D1 = ops.build_operators(pos, nrm, xb, yb, plain_graph, graph.cloud_ptr, 3)
+    G2, D2, scale = ops.build_operators(pos, nrm, xb, yb, graph, graph.cloud_ptr, 3, deferred=True)
+    assert scale is not None and (scale > 0).all()
+    row = G1.abs().amax(dim=(1, 2), keepdim=True).clamp(min=1e-30)
+    assert ((G2 * scale[:, None, None] - G1).abs() / row).max() < 2e-6
+    row = D1.abs().amax(dim=(1, 2), keepdim=True).clamp(min=1e-30)
+    assert ((D2 * scale[:, None, None] - D1).abs() / row).max() < 2e-6
+    ops1 = (ops.EllOperator('grad', plain_graph, G1, D1), ops.EllOperator('div', plain_graph, G1, D1))
+    ops2 = (ops.EllOperator('grad', graph, G2, D2, scale), ops.EllOperator('div', graph, G2, D2, scale))
+    torch.manual_seed(2)
+    x0, v0 = torch.randn(pos.size(0), 8, device=DEV), torch.randn(2 * pos.size(0), 8, device=DEV)
+    outs = []
+    for grad, div in (ops1, ops2):
+        x, v = x0.clone().requires_grad_(True), v0.clone().requires_grad_(True)
+        cat, dcu = ops.scalar_cat(x, v, div)
+        vcat = ops.vector_cat(v, dcu, x, grad)
+        lap = dc().geometry.laplacian(x, grad, div)
+        (cat.sum() + (vcat * vcat).sum() + (lap * lap).sum()).backward()
+        outs.append((cat.detach(), vcat.detach(), lap.detach(), x.grad, v.grad))
+    for a, b in zip(*outs):
+        assert rel_err(b.cpu(), a.cpu()) < 5e-6

@@ -28,8 +28,10 @@ def _build(static, pos, normal, xb, yb, graph, normalized, lam, lam_shape):
     N, k, B = graph.N, graph.k, graph.B
     G = torch.full((N, k, 2), float('nan'), device=DEV)
     D_ = torch.full((N, k, 2), float('nan'), device=DEV)
-    common = (ptr(pos), ptr(normal), ptr(xb), ptr(yb), ptr(graph.idx), ptr(graph.cloud_ptr), B, N, k, 1.0, lam,
-              lam_shape if lam_shape is not None else 0.0, int(lam_shape is not None), int(normalized), ptr(G), ptr(D_))
+    head = (ptr(pos), ptr(normal), ptr(xb), ptr(yb), ptr(graph.idx))
+    tail = (ptr(graph.cloud_ptr), B, N, k, 1.0, lam, lam_shape if lam_shape is not None else 0.0, int(lam_shape is not None),
+            int(normalized), ptr(G), ptr(D_))
+    common = head + tail
     if static:
         torch.cuda.synchronize()
         # count allocation EVENTS (monotonic), not bytes in use: a garbage-collection pass may free unrelated
@@ -40,7 +42,7 @@ def _build(static, pos, normal, xb, yb, graph, normalized, lam, lam_shape):
     else:
         nbytes = query('dc_build_ws_bytes', N, B)
         ws = torch.empty(nbytes, dtype=torch.uint8, device=DEV)
-        call('dc_build_grad_div', *common, None, None, None, ptr(ws), nbytes)
+        call('dc_build_grad_div', *head, None, *tail, None, None, None, None, ptr(ws), nbytes)       # no kNN distances, no deferred scale
     return G, D_
 
 
