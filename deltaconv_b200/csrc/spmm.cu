@@ -71,7 +71,10 @@ template <int OP> struct OpTraits {
     static constexpr bool two_inputs = OP != OP_GRAD;
 };
 
-template <int OP, int VEC>
+// SCALED: multiply the result rows by a.row_scale (deferred per-cloud normalisation).  A template flag, not a run-time test:
+// the factor costs the light kernels a register allocation step (grad^T: 32 -> 40 registers = 64 -> 48 resident warps, +12 %
+// time), which the un-scaled instantiation must not pay; forcing the old allocation with launch bounds spills and is slower.
+template <int OP, int VEC, bool SCALED>
 __global__ void __launch_bounds__(256) spmm_kernel(SpArgs a, int lpp_log2) {
     typedef Vec<VEC> V;
     const int lpp = 1 << lpp_log2;
@@ -85,7 +88,7 @@ __global__ void __launch_bounds__(256) spmm_kernel(SpArgs a, int lpp_log2) {
     const int ch = (blockIdx.y * lpp + sub) * VEC;
     const bool ch_ok = ch < a.C;
     // the row's normalisation factor, requested before the gather loop so that its latency is hidden behind it
-    const float sc = (a.row_scale && row_ok) ? __ldg(a.row_scale + r) : 1.f;
+    const float sc = (SCALED && row_ok) ? __ldg(a.row_scale + r) : 1.f;
 
     int t_begin, t_end;
     if (OpTraits<OP>::transposed) { t_begin = row_ok ? __ldg(a.in_ptr + r) : 0; t_end = row_ok ? __ldg(a.in_ptr + r + 1) : 0; }
@@ -149,7 +152,7 @@ __global__ void __launch_bounds__(256) spmm_kernel(SpArgs a, int lpp_log2) {
         }
     }
     if (!row_ok || !ch_ok) return;
-    if (a.row_scale) {
+    if (SCALED) {
         acc0 = V::map2(acc0, acc0, [sc](float p, float) { return p * sc; });
         acc1 = V::map2(acc1, acc1, [sc](float p, float) { return p * sc; });
     }
@@ -407,8 +410,13 @@ int launch_spmm(const SpArgs& a, cudaStream_t st) {
     const int lpp = 1 << lpp_log2;
     const int rows_per_cta = 8 * (32 >> lpp_log2);
     dim3 grid(dc_ceil_div(a.N, rows_per_cta), dc_ceil_div(units, lpp));
-    if (vec4) spmm_kernel<OP, 4><<<grid, 256, 0, st>>>(a, lpp_log2);
-    else spmm_kernel<OP, 1><<<grid, 256, 0, st>>>(a, lpp_log2);
+    if (a.row_scale) {
+        if (vec4) spmm_kernel<OP, 4, true><<<grid, 256, 0, st>>>(a, lpp_log2);
+        else spmm_kernel<OP, 1, true><<<grid, 256, 0, st>>>(a, lpp_log2);
+    } else {
+        if (vec4) spmm_kernel<OP, 4, false><<<grid, 256, 0, st>>>(a, lpp_log2);
+        else spmm_kernel<OP, 1, false><<<grid, 256, 0, st>>>(a, lpp_log2);
+    }
     return dc_check_launch("spmm");
 }
 

@@ -273,9 +273,10 @@ def estimate_frames(pos, graph, orientation=None):
 
 
 def build_operators(pos, normal, xb, yb, graph, cloud_ptr, B, kernel_width=1.0, lam=1e-3, normalized=True,
-                    lam_shape=None, debug=False, deferred=False):
-    """G, D [N,k,2] of dc_build_grad_div (normalised entries), or with deferred=True (G_raw, D_raw, point_scale [N] or None):
-    the entries before the per-cloud normalisation and the factor the operator applications multiply their rows with."""
+                    lam_shape=None, debug=False, deferred=None):
+    """G, D [N,k,2] of dc_build_grad_div (normalised entries).  With `deferred` given (True / False) the return is
+    (G, D, point_scale): deferred=True leaves the entries un-normalised and returns the factor [N] the operator applications
+    multiply their rows with; deferred=False normalises in place and returns None as the factor."""
     pos, normal, xb, yb = (_f32(t, n).contiguous() for t, n in ((pos, 'pos'), (normal, 'normal'), (xb, 'x_basis'), (yb, 'y_basis')))
     N, k = graph.N, graph.k
     dev = pos.device
@@ -296,7 +297,7 @@ def build_operators(pos, normal, xb, yb, graph, cloud_ptr, B, kernel_width=1.0, 
          float(kernel_width), float(lam), float(lam_shape if lam_shape is not None else 0.0),
          int(lam_shape is not None), mode, ptr(G), ptr(D), ptr(scale), ptr(dbg[0]), ptr(dbg[1]), ptr(dbg[2]),
          ptr(ws), nbytes)
-    if deferred:
+    if deferred is not None:
         return (G, D, scale, dbg) if debug else (G, D, scale)
     return (G, D, dbg) if debug else (G, D)
 
