@@ -54,39 +54,71 @@ __global__ void bbox_kernel(const float* __restrict__ pos, const int* __restrict
     atomicMax(bbox + b * 6 + 3, x); atomicMax(bbox + b * 6 + 4, y); atomicMax(bbox + b * 6 + 5, z);
 }
 
-// One thread lays out all grids: cell size from the bounding volume and the point count (about two points per cell of
-// the bounding box; surface samples fill far fewer cells, so occupied cells hold a few tens of points), at most
-// 4 P + 64 cells per cloud so that the cell arrays have a fixed size.
-__global__ void grid_params_kernel(const int* __restrict__ cloud_ptr, int B, const int* __restrict__ bbox, GridCloud* __restrict__ clouds,
-                                   int* __restrict__ total_cells, float points_per_cell) {
-    if (blockIdx.x != 0 || threadIdx.x != 0) return;
-    int base = 0;
-    for (int b = 0; b < B; ++b) {
-        GridCloud g;
-        g.s = cloud_ptr[b]; g.e = cloud_ptr[b + 1];
-        const int P = g.e - g.s;
-        g.cell_base = base;
-        if (P <= 0) { g.ox = g.oy = g.oz = 0.f; g.h = 1.f; g.inv_h = 1.f; g.gx = g.gy = g.gz = 1; clouds[b] = g; base += 1; continue; }
-        const float x0 = ord2f(bbox[b * 6]), y0 = ord2f(bbox[b * 6 + 1]), z0 = ord2f(bbox[b * 6 + 2]);
-        const float ex = ord2f(bbox[b * 6 + 3]) - x0, ey = ord2f(bbox[b * 6 + 4]) - y0, ez = ord2f(bbox[b * 6 + 5]) - z0;
-        const float emax = fmaxf(ex, fmaxf(ey, ez));
-        // degenerate extents (planar or collinear clouds) count as one cell layer
-        const float floor_ext = fmaxf(emax * 1e-3f, 1e-30f);
-        const float vol = fmaxf(ex, floor_ext) * fmaxf(ey, floor_ext) * fmaxf(ez, floor_ext);
-        float h = cbrtf(vol / fmaxf((float)P / points_per_cell, 1.f));
-        h = fmaxf(h, emax / (float)(GRID_MAX_DIM - 1));
-        if (!(h > 0.f)) h = 1.f;                                    // all points coincide
-        const long long cap = 4LL * P + 64;
-        for (int it = 0; it < 64; ++it) {
-            g.gx = min(GRID_MAX_DIM, (int)(ex / h) + 1); g.gy = min(GRID_MAX_DIM, (int)(ey / h) + 1); g.gz = min(GRID_MAX_DIM, (int)(ez / h) + 1);
-            if ((long long)g.gx * g.gy * g.gz <= cap) break;
-            h *= 1.26f;
-        }
-        g.ox = x0; g.oy = y0; g.oz = z0; g.h = h; g.inv_h = 1.f / h;
-        clouds[b] = g;
-        base += g.gx * g.gy * g.gz;
+// Lays out all grids: cell size from the bounding volume and the point count, at most 4 P + 64 cells per cloud so that the
+// cell arrays have a fixed size.  One CTA: a thread per cloud computes that cloud's grid, then the cell counts are scanned over
+// the clouds (first cell id of every cloud).  (The first version was one thread walking all clouds: 21 us for 32 clouds.)
+constexpr int GPAR_T = 1024;
+__device__ __forceinline__ GridCloud grid_of_cloud(const int* __restrict__ cloud_ptr, const int* __restrict__ bbox, int b, float points_per_cell) {
+    GridCloud g;
+    g.s = cloud_ptr[b]; g.e = cloud_ptr[b + 1];
+    g.cell_base = 0;
+    const int P = g.e - g.s;
+    if (P <= 0) { g.ox = g.oy = g.oz = 0.f; g.h = 1.f; g.inv_h = 1.f; g.gx = g.gy = g.gz = 1; return g; }
+    const float x0 = ord2f(bbox[b * 6]), y0 = ord2f(bbox[b * 6 + 1]), z0 = ord2f(bbox[b * 6 + 2]);
+    const float ex = ord2f(bbox[b * 6 + 3]) - x0, ey = ord2f(bbox[b * 6 + 4]) - y0, ez = ord2f(bbox[b * 6 + 5]) - z0;
+    const float emax = fmaxf(ex, fmaxf(ey, ez));
+    // degenerate extents (planar or collinear clouds) count as one cell layer
+    const float floor_ext = fmaxf(emax * 1e-3f, 1e-30f);
+    const float vol = fmaxf(ex, floor_ext) * fmaxf(ey, floor_ext) * fmaxf(ez, floor_ext);
+    // points per bounding-box cell: given, or (points_per_cell <= 0) chosen from the cloud's size — measured optimum
+    // (scripts/tune_knn_small.py, k = 10 ... 40): ~6 for clouds of 1-4 K points (17-28 % faster than 2 at 2048 points),
+    // 3 around 16 K, 1.5 at 2^20 (a surface cloud fills only a shell of its box: the occupied cells hold several times this)
+    const float ppc = points_per_cell > 0.f ? points_per_cell : (P <= 6144 ? 6.f : (P <= 49152 ? 3.f : 1.5f));
+    float h = cbrtf(vol / fmaxf((float)P / ppc, 1.f));
+    h = fmaxf(h, emax / (float)(GRID_MAX_DIM - 1));
+    if (!(h > 0.f)) h = 1.f;                                    // all points coincide
+    const long long cap = 4LL * P + 64;
+    for (int it = 0; it < 64; ++it) {
+        g.gx = min(GRID_MAX_DIM, (int)(ex / h) + 1); g.gy = min(GRID_MAX_DIM, (int)(ey / h) + 1); g.gz = min(GRID_MAX_DIM, (int)(ez / h) + 1);
+        if ((long long)g.gx * g.gy * g.gz <= cap) break;
+        h *= 1.26f;
     }
-    *total_cells = base;
+    g.ox = x0; g.oy = y0; g.oz = z0; g.h = h; g.inv_h = 1.f / h;
+    return g;
+}
+
+__global__ void __launch_bounds__(GPAR_T) grid_params_kernel(const int* __restrict__ cloud_ptr, int B, const int* __restrict__ bbox,
+                                                             GridCloud* __restrict__ clouds, int* __restrict__ total_cells, float points_per_cell) {
+    __shared__ int warp_tot[32];
+    __shared__ int carry_s;
+    if (threadIdx.x == 0) carry_s = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int base = 0; base < B; base += GPAR_T) {
+        const int b = base + threadIdx.x;
+        GridCloud g;
+        int cells = 0;
+        if (b < B) { g = grid_of_cloud(cloud_ptr, bbox, b, points_per_cell); cells = g.gx * g.gy * g.gz; }
+        int x = cells;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(FULL, x, o); if (lane >= o) x += y; }
+        if (lane == 31) warp_tot[warp] = x;
+        __syncthreads();
+        if (warp == 0) {
+            int w = warp_tot[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(FULL, w, o); if (lane >= o) w += y; }
+            warp_tot[lane] = w;
+        }
+        __syncthreads();
+        const int carry = carry_s;
+        const int incl = x + (warp > 0 ? warp_tot[warp - 1] : 0);
+        if (b < B) { g.cell_base = carry + incl - cells; clouds[b] = g; }
+        __syncthreads();
+        if (threadIdx.x == GPAR_T - 1) carry_s = carry + incl;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *total_cells = carry_s;
 }
 
 __device__ __forceinline__ int cell_coord(float p, float o, float inv_h, int G) {
@@ -109,19 +141,22 @@ __global__ void grid_count_kernel(const float* __restrict__ pos, const int* __re
 }
 
 constexpr int GSCAN_T = 1024, GSCAN_V = 4;
-// exclusive scan (single CTA, 4096 elements per round), out[n] = total
-__global__ void __launch_bounds__(GSCAN_T) grid_scan_kernel(const int* __restrict__ cnt, const int* __restrict__ n_ptr, int* __restrict__ out) {
-    const int n = *n_ptr;                  // number of cells actually laid out (device-side)
+// exclusive scan of the cell counts, one CTA per cloud (4096 cells per round): the cells of cloud b are consecutive and its
+// points occupy sorted[s_b, e_b), so every cloud's scan starts at s_b and the clouds are independent.  out[total] = N.
+__global__ void __launch_bounds__(GSCAN_T) grid_scan_kernel(const int* __restrict__ cnt, const GridCloud* __restrict__ clouds, int B, int N,
+                                                            int* __restrict__ out) {
+    const GridCloud g = clouds[blockIdx.x];
+    const int first = g.cell_base, n = g.gx * g.gy * g.gz;
     __shared__ int warp_tot[32];
     __shared__ int carry_s;
-    if (threadIdx.x == 0) carry_s = 0;
+    if (threadIdx.x == 0) carry_s = g.s;
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int base = 0; base < n; base += GSCAN_T * GSCAN_V) {
         const int i0 = base + threadIdx.x * GSCAN_V;
         int v[GSCAN_V], sum = 0;
 #pragma unroll
-        for (int u = 0; u < GSCAN_V; ++u) { v[u] = (i0 + u < n) ? cnt[i0 + u] : 0; sum += v[u]; }
+        for (int u = 0; u < GSCAN_V; ++u) { v[u] = (i0 + u < n) ? cnt[first + i0 + u] : 0; sum += v[u]; }
         int x = sum;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(FULL, x, o); if (lane >= o) x += y; }
@@ -138,12 +173,12 @@ __global__ void __launch_bounds__(GSCAN_T) grid_scan_kernel(const int* __restric
         const int incl = x + (warp > 0 ? warp_tot[warp - 1] : 0);
         int run = carry + incl - sum;
 #pragma unroll
-        for (int u = 0; u < GSCAN_V; ++u) { if (i0 + u < n) out[i0 + u] = run; run += v[u]; }
+        for (int u = 0; u < GSCAN_V; ++u) { if (i0 + u < n) out[first + i0 + u] = run; run += v[u]; }
         __syncthreads();
         if (threadIdx.x == GSCAN_T - 1) carry_s = carry + incl;
         __syncthreads();
     }
-    if (threadIdx.x == 0) out[n] = carry_s;
+    if (blockIdx.x == B - 1 && threadIdx.x == 0) out[first + n] = N;
 }
 
 // points sorted by cell: (x, y, z, local index bits).  The order inside a cell is arbitrary (atomic cursor); the selection
@@ -154,7 +189,7 @@ __global__ void grid_fill_kernel(const float* __restrict__ pos, const int* __res
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= N) return;
     const int cell = cell_of[i];
-    const int slot = atomicAdd(cursor + cell, 1);
+    const int slot = atomicSub(cursor + cell, 1) - 1;           // `cursor` is the cell's count, counted down: no second zeroed array
     const int s = cloud_ptr[cloud_of(cloud_ptr, B, i)];
     sorted[cell_start[cell] + slot] = make_float4(pos[3 * (size_t)i], pos[3 * (size_t)i + 1], pos[3 * (size_t)i + 2], __int_as_float(i - s));
 }
@@ -243,7 +278,7 @@ grid_query_kernel(const float4* __restrict__ sorted, const int* __restrict__ cel
     }
 }
 
-float g_points_per_cell = 2.f;       // target occupancy of a bounding-box cell (dc_set_knn_grid_density)
+float g_points_per_cell = 0.f;       // target occupancy of a bounding-box cell (dc_set_knn_grid_density); 0 = by cloud size
 // 30-bit Morton code of a point inside its cloud's bounding box (10 bits per axis), cloud index above it: sorting by this key
 // orders every cloud along a space-filling curve without mixing clouds.
 __device__ __forceinline__ unsigned spread10(unsigned v) {
@@ -286,7 +321,7 @@ extern "C" int dc_morton_keys(const float* pos, const int32_t* cloud_ptr, int B,
 
 // tuning: points per bounding-box cell the grid aims at (default 2)
 extern "C" int dc_set_knn_grid_density(float points_per_cell) {
-    DC_REQUIRE(points_per_cell >= 0.25f && points_per_cell <= 64.f, "dc_set_knn_grid_density: out of range");
+    DC_REQUIRE(points_per_cell == 0.f || (points_per_cell >= 0.25f && points_per_cell <= 64.f), "dc_set_knn_grid_density: out of range (0 = automatic)");
     g_points_per_cell = points_per_cell;
     return DC_OK;
 }
@@ -316,13 +351,13 @@ extern "C" int dc_knn_grid(const float* pos, const int32_t* cloud_ptr, int B, in
     int* cursor = (int*)w; w += align256(((size_t)cap + 2) * 4);
     float4* sorted = (float4*)w;
     DC_CUDA(cudaMemsetAsync(cnt, 0, ((size_t)cap + 2) * 4, st));
-    DC_CUDA(cudaMemsetAsync(cursor, 0, ((size_t)cap + 2) * 4, st));
+    (void)cursor;
     bbox_init_kernel<<<dc_ceil_div(B * 6, 256), 256, 0, st>>>(bbox, B);
     bbox_kernel<<<dc_ceil_div(N, 256), 256, 0, st>>>(pos, cloud_ptr, B, N, bbox);
-    grid_params_kernel<<<1, 32, 0, st>>>(cloud_ptr, B, bbox, clouds, total, g_points_per_cell);
+    grid_params_kernel<<<1, GPAR_T, 0, st>>>(cloud_ptr, B, bbox, clouds, total, g_points_per_cell);
     grid_count_kernel<<<dc_ceil_div(N, 256), 256, 0, st>>>(pos, cloud_ptr, B, N, clouds, cell_of, cnt);
-    grid_scan_kernel<<<1, GSCAN_T, 0, st>>>(cnt, total, cell_start);
-    grid_fill_kernel<<<dc_ceil_div(N, 256), 256, 0, st>>>(pos, cloud_ptr, B, N, cell_of, cell_start, cursor, sorted);
+    grid_scan_kernel<<<B, GSCAN_T, 0, st>>>(cnt, clouds, B, N, cell_start);
+    grid_fill_kernel<<<dc_ceil_div(N, 256), 256, 0, st>>>(pos, cloud_ptr, B, N, cell_of, cell_start, cnt, sorted);
     const int grid = dc_ceil_div(N, GRID_WARPS);
     long long* eo = (long long*)edge_index_or_null;
     if (k <= 32) grid_query_kernel<1><<<grid, GRID_WARPS * 32, 0, st>>>(sorted, cell_start, cloud_ptr, B, N, k, clouds, idx, eo, d2_or_null, dc_knn_merge_min());

@@ -130,6 +130,7 @@ class EllGraph:
 
 
 KNN_GRID_FROM = 1536      # points in the largest cloud from which the grid search replaces the brute-force scan (measured crossover)
+KNN_GRID_FROM_K20 = 1000  # ... for k >= 20: with ~6 points per cell the grid already wins at 1024-point clouds (130 vs 145 us per 32 clouds at k = 20, 173 vs 265 at k = 40)
 KNN_METHOD = 'auto'       # 'auto' | 'brute' | 'grid' (tests and benchmarks force one)
 
 
@@ -144,7 +145,7 @@ def knn(pos, k, batch=None, num_clouds=None, want_edge_index=True, max_points=No
     idx = torch.empty(N, k, dtype=_I32, device=pos.device)
     ei = torch.empty(2, N * k, dtype=_I64, device=pos.device) if want_edge_index else None
     d2 = torch.empty(N, k, dtype=_F32, device=pos.device) if want_d2 else None
-    method = KNN_METHOD if KNN_METHOD != 'auto' else ('grid' if maxp > KNN_GRID_FROM else 'brute')
+    method = KNN_METHOD if KNN_METHOD != 'auto' else ('grid' if maxp > (KNN_GRID_FROM_K20 if k >= 20 else KNN_GRID_FROM) else 'brute')
     if method == 'grid':                 # large clouds: uniform grid + ring search, same exact result (dc_knn_grid)
         nb = query('dc_knn_grid_ws_bytes', N, B)
         ws = workspace(nb, pos.device)
