@@ -162,7 +162,7 @@ WORK = {
     'dc_grad_fwd': (_w_grad, 'spmm'), 'dc_grad_bwd': (_w_grad_t, 'spmm'),
     'dc_divcurlnorm_fwd': (_w_dcn, 'spmm'), 'dc_divcurlnorm_bwd': (_w_dcn_t, 'spmm'),
     'dc_hodge_fwd': (_w_hodge, 'spmm'), 'dc_hodge_bwd': (_w_hodge_t, 'spmm'),
-    'dc_gathermax_fwd': (_w_gmax, 'gathermax'), 'dc_gathermax_bwd': (_w_gmax_t, 'gathermax'),
+    'dc_gathermax_fwd': (_w_gmax, 'gathermax'), 'dc_gathermax_bwd': (_w_gmax_t, 'gathermax'), 'dc_gathermax_bn_fwd': (_w_gmax, 'gathermax'),
     'dc_bn_act_pool_fwd': (_w_bnpool, 'batchnorm'), 'dc_bn_act_pool_bwd': (_w_bnpool_t, 'batchnorm'),
     'dc_sgd_step': (_w_sgd, 'optimizer'), 'dc_pool_fwd': (_w_pool, 'pool'), 'dc_pool_bwd': (_w_pool, 'pool'), 'dc_bcast_rows': (_w_pool, 'pool'),
     'dc_bn_stats': (_w_stats, 'batchnorm'), 'dc_bn_act_fwd': (_w_bnf, 'batchnorm'), 'dc_bn_act_bwd': (_w_bnb, 'batchnorm'),

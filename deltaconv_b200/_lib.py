@@ -51,6 +51,7 @@ _SIGNATURES = {
     'dc_hodge_bwd': [_P, _P, _P, _I, _I, _I, _P, _L, _P, _L, _P, _L, _P, _P, _I, _I, _P],
     'dc_gathermax_fwd': [_P, _I, _I, _I, _P, _L, _P, _L, _P, _P],
     'dc_gathermax_bwd': [_P, _P, _I, _I, _I, _P, _P, _L, _P, _L, _P],
+    'dc_gathermax_bn_fwd': [_P, _I, _I, _I, _P, _L, _P, _P, _P, _P, _F, _P, _L, _P, _P],
     'dc_edge_diff_fwd': [_P, _I, _I, _I, _P, _L, _P, _P],
     'dc_edge_diff_bwd': [_P, _P, _I, _I, _I, _P, _P, _L, _P],
     'dc_segmax_fwd': [_P, _I, _I, _I, _P, _P, _L, _P, _P],

@@ -641,10 +641,20 @@ __global__ void gathermax_bwd_kernel(const int* __restrict__ in_ptr, const int* 
     }
 }
 
-// float4 variants: a group of LPP lanes owns one point and 4*LPP consecutive channels (like spmm_kernel)
+struct BnAct {
+    const float* mean; const float* invstd; const float* gamma; const float* beta; float slope;
+};
+
+// float4 variants: a group of LPP lanes owns one point and 4*LPP consecutive channels (like spmm_kernel).
+// BN = true: the gathered rows are PRE-activations y and the result is max_e act(bn(y[idx[i,e]])) without the activation ever
+// being written: z -> leaky_relu(gamma (z - mean) invstd + beta) is monotone per channel (increasing for gamma >= 0, decreasing
+// otherwise; invstd > 0, slope > 0), so the maximum of the activations is the activation of the per-channel maximum — or
+// minimum — of y.  The arg slot is that extreme's, and the value is computed from that very element: bitwise what a separate
+// BatchNorm + activation pass followed by the plain gather-max gives.
+template <bool BN>
 __global__ void __launch_bounds__(256) gathermax_fwd_vec4_kernel(const int* __restrict__ idx, int N, int k, int C, const float* __restrict__ y,
                                                                  long long ldy, float* __restrict__ out, long long ldo,
-                                                                 unsigned char* __restrict__ arg, int lpp_log2) {
+                                                                 unsigned char* __restrict__ arg, int lpp_log2, BnAct bn) {
     const int lpp = 1 << lpp_log2, lane = threadIdx.x & 31, sub = lane & (lpp - 1);
     const long long row_ll = ((long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * (32 >> lpp_log2) + (lane >> lpp_log2);
     const bool row_ok = row_ll < N;
@@ -653,6 +663,13 @@ __global__ void __launch_bounds__(256) gathermax_fwd_vec4_kernel(const int* __re
     const bool ch_ok = ch < C;
     float4 best = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
     uchar4 slot = make_uchar4(0, 0, 0, 0);
+    // sign of the channel's slope: invstd > 0, so it is the sign bit of gamma; one bit per channel in ONE register (the
+    // kernel hides its gather latency by occupancy: the other BatchNorm constants are loaded after the loop)
+    unsigned neg = 0u;
+    if (BN && ch_ok && bn.gamma) {
+        const float4 ga = __ldg(reinterpret_cast<const float4*>(bn.gamma + ch));
+        neg = (__float_as_uint(ga.x) >> 31) | ((__float_as_uint(ga.y) >> 31) << 1) | ((__float_as_uint(ga.z) >> 31) << 2) | ((__float_as_uint(ga.w) >> 31) << 3);
+    }
     for (int e0 = 0; e0 < k; e0 += lpp) {
         int my_j = -1;
         if (row_ok && e0 + sub < k) { my_j = __ldg(idx + (size_t)i * k + e0 + sub); if ((unsigned)my_j >= (unsigned)N) my_j = -1; }
@@ -661,7 +678,11 @@ __global__ void __launch_bounds__(256) gathermax_fwd_vec4_kernel(const int* __re
         for (int q = 0; q < cnt; ++q) {
             const int j = __shfl_sync(FULL, my_j, q, lpp);
             if (!row_ok || !ch_ok || j < 0) continue;
-            const float4 v = __ldg(reinterpret_cast<const float4*>(y + (size_t)j * ldy + ch));
+            float4 v = __ldg(reinterpret_cast<const float4*>(y + (size_t)j * ldy + ch));
+            if (BN) {            // flip the sign bit where gamma < 0: the order of (+-)y is the order of act(bn(y))
+                v.x = __uint_as_float(__float_as_uint(v.x) ^ ((neg & 1u) << 31)); v.y = __uint_as_float(__float_as_uint(v.y) ^ ((neg & 2u) << 30));
+                v.z = __uint_as_float(__float_as_uint(v.z) ^ ((neg & 4u) << 29)); v.w = __uint_as_float(__float_as_uint(v.w) ^ ((neg & 8u) << 28));
+            }
             const unsigned char e = (unsigned char)(e0 + q);
             if (v.x > best.x) { best.x = v.x; slot.x = e; }
             if (v.y > best.y) { best.y = v.y; slot.y = e; }
@@ -670,8 +691,25 @@ __global__ void __launch_bounds__(256) gathermax_fwd_vec4_kernel(const int* __re
         }
     }
     if (!row_ok || !ch_ok) return;
-    best.x = best.x == -INFINITY ? 0.f : best.x; best.y = best.y == -INFINITY ? 0.f : best.y;
-    best.z = best.z == -INFINITY ? 0.f : best.z; best.w = best.w == -INFINITY ? 0.f : best.w;
+    if (BN) {
+        const float4 mu = __ldg(reinterpret_cast<const float4*>(bn.mean + ch)), is = __ldg(reinterpret_cast<const float4*>(bn.invstd + ch));
+        const float4 ga = bn.gamma ? __ldg(reinterpret_cast<const float4*>(bn.gamma + ch)) : make_float4(1.f, 1.f, 1.f, 1.f);
+        const float4 be = bn.beta ? __ldg(reinterpret_cast<const float4*>(bn.beta + ch)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        const float b4[4] = {best.x, best.y, best.z, best.w}, m4[4] = {mu.x, mu.y, mu.z, mu.w};
+        const float i4[4] = {is.x, is.y, is.z, is.w}, g4[4] = {ga.x, ga.y, ga.z, ga.w}, e4[4] = {be.x, be.y, be.z, be.w};
+        float o4[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const float ysel = __uint_as_float(__float_as_uint(b4[u]) ^ (((neg >> u) & 1u) << 31));      // the selected y itself
+            float z = g4[u] * ((ysel - m4[u]) * i4[u]) + e4[u];                    // the expression of bn_act_fwd_kernel on it
+            z = z > 0.f ? z : bn.slope * z;
+            o4[u] = b4[u] == -INFINITY ? 0.f : z;                                  // empty group -> 0 (torch_scatter)
+        }
+        best = make_float4(o4[0], o4[1], o4[2], o4[3]);
+    } else {
+        best.x = best.x == -INFINITY ? 0.f : best.x; best.y = best.y == -INFINITY ? 0.f : best.y;
+        best.z = best.z == -INFINITY ? 0.f : best.z; best.w = best.w == -INFINITY ? 0.f : best.w;
+    }
     *reinterpret_cast<float4*>(out + (size_t)i * ldo + ch) = best;
     *reinterpret_cast<uchar4*>(arg + (size_t)i * C + ch) = slot;
 }
@@ -827,9 +865,6 @@ __global__ void __launch_bounds__(256) segmax_bwd_vec4_kernel(const float* __res
 // out_max[b,c] = max_i x[i,c] (arg kept), out_mean[b,c] = mean_i x[i,c]
 // With BN the pooled quantity is leaky_relu(gamma * (x - mean) * invstd + beta): the activation of the embedding layer is
 // applied while its pre-activation is read, so the [N,C] activation never exists in memory.
-struct BnAct {
-    const float* mean; const float* invstd; const float* gamma; const float* beta; float slope;
-};
 
 template <bool BN>
 __global__ void __launch_bounds__(256) pool_fwd_kernel(const float* __restrict__ x, long long ldx, const int* __restrict__ cloud_ptr,
@@ -1052,10 +1087,28 @@ extern "C" int dc_gathermax_fwd(const int32_t* idx, int N, int k, int C, const f
         int lpp_log2 = 0;
         while ((1 << lpp_log2) < C / 4 && lpp_log2 < 5) ++lpp_log2;
         dim3 grid(dc_ceil_div(N, 8 * (32 >> lpp_log2)), dc_ceil_div(C / 4, 1 << lpp_log2));
-        gathermax_fwd_vec4_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(idx, N, k, C, y, ldy, out, ldo, arg, lpp_log2);
+        gathermax_fwd_vec4_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(idx, N, k, C, y, ldy, out, ldo, arg, lpp_log2, BnAct());
     } else
         gathermax_fwd_kernel<<<dc_ceil_div((long long)N * 32, 256), 256, 0, (cudaStream_t)stream>>>(idx, N, k, C, y, ldy, out, ldo, arg);
     return dc_check_launch("dc_gathermax_fwd");
+}
+
+// max over the neighbours of leaky_relu(BatchNorm(y)) from the pre-activations y (deltaconv.py:54 with the last block of
+// s_mlp_max, mlp.py:9, folded in): the [N,C] activation is never written.  Needs the float4 layout (C % 4 == 0, 16-byte rows).
+extern "C" int dc_gathermax_bn_fwd(const int32_t* idx, int N, int k, int C, const float* y, int64_t ldy, const float* mean,
+                                   const float* invstd, const float* gamma_or_null, const float* beta_or_null, float slope,
+                                   float* out, int64_t ldo, uint8_t* arg, void* stream) {
+    DC_REQUIRE(k <= 255, "dc_gathermax_bn_fwd: k must be <= 255 (arg slots are stored as u8)");
+    DC_REQUIRE(slope > 0.f, "dc_gathermax_bn_fwd: the activation must be strictly increasing (LeakyReLU slope > 0)");
+    DC_REQUIRE(C % 4 == 0 && ldy % 4 == 0 && ldo % 4 == 0 && all_aligned16(y, out, mean, invstd, gamma_or_null, beta_or_null) &&
+               (reinterpret_cast<uintptr_t>(arg) & 3u) == 0, "dc_gathermax_bn_fwd: needs C %% 4 == 0 and 16-byte aligned rows");
+    if (N <= 0 || C <= 0) return DC_OK;
+    int lpp_log2 = 0;
+    while ((1 << lpp_log2) < C / 4 && lpp_log2 < 5) ++lpp_log2;
+    dim3 grid(dc_ceil_div(N, 8 * (32 >> lpp_log2)), dc_ceil_div(C / 4, 1 << lpp_log2));
+    BnAct bn = {mean, invstd, gamma_or_null, beta_or_null, slope};
+    gathermax_fwd_vec4_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(idx, N, k, C, y, ldy, out, ldo, arg, lpp_log2, bn);
+    return dc_check_launch("dc_gathermax_bn_fwd");
 }
 
 extern "C" int dc_gathermax_bwd(const int32_t* in_ptr, const int32_t* in_edge, int N, int k, int C, const uint8_t* arg,

@@ -49,7 +49,16 @@ class DeltaConv(torch.nn.Module):
             else:
                 x_max = ops.segment_max(self.s_mlp_max(ops.edge_diff(x, graph)), graph)
         else:
-            x_max = ops.gather_max(self.s_mlp_max(x), graph)
+            blocks = list(self.s_mlp_max)
+            tail = blocks[-1]
+            if ops.gathermax_fusable(tail[0], _slope_of(tail[2]), x):
+                h = x
+                for block in blocks[:-1]:
+                    h = block(h)
+                # Linear + BatchNorm statistics + (BatchNorm, activation, max over the neighbours) as one node
+                x_max = ops.linear_bn_act_gathermax(h, tail[0].weight, tail[1].bn, _slope_of(tail[2]), graph)
+            else:
+                x_max = ops.gather_max(self.s_mlp_max(x), graph)
         x_cat, div_curl = ops.scalar_cat(x, v, div)
         x = self.s_mlp(x_cat, x_max, x_slot)
 

@@ -991,6 +991,68 @@ def gather_max(y, graph):
     return _GatherMax.apply(y, graph)
 
 
+class _LinearBNActGatherMax(torch.autograd.Function):
+    """max over the neighbours of act(BatchNorm1d(x @ W.T)) (deltaconv.py:54 with the last block of s_mlp_max) as ONE node: the
+    GEMM writes the pre-activation, the statistics pass reads it, and the gather-max applies BatchNorm + LeakyReLU to the
+    per-channel extreme it selects (dc_gathermax_bn_fwd) — the [N,C] activation is neither written nor read.  Backward: the
+    plain gather-max backward gives the gradient of the activation, then the BatchNorm and Linear backward of _LinearBNAct."""
+
+    @staticmethod
+    def forward(ctx, x, weight, gamma, beta, bn, slope, graph):
+        x, ldx = _mat(x, 'input')
+        weight, ldw = _mat(weight, 'weight')
+        if x.size(1) != weight.size(1):
+            raise _lib.DeltaConvLibraryError(f"Linear: input has {x.size(1)} features, weight expects {weight.size(1)}")
+        M, K, C = x.size(0), x.size(1), weight.size(0)
+        if M != graph.N:
+            raise _lib.DeltaConvLibraryError(f"gather-max: {M} feature rows for a graph on {graph.N} points")
+        dev = x.device
+        y = torch.empty(M, C, dtype=_F32, device=dev)
+        ws, nb = _gemm_ws(M, C, K, dev)
+        call('dc_linear_fwd', ptr(x), ldx, ptr(weight), ldw, None, M, K, C, ptr(y), C, ptr(ws), nb)
+        mean, invstd, batch_stats = _bn_moments(bn, y, C, M, C, 0)
+        out = torch.empty(M, C, dtype=_F32, device=dev)
+        arg = torch.empty(M, C, dtype=torch.uint8, device=dev)
+        call('dc_gathermax_bn_fwd', ptr(graph.idx), M, graph.k, C, ptr(y), C, ptr(mean), ptr(invstd), ptr(gamma), ptr(beta),
+             float(slope), ptr(out), C, ptr(arg))
+        ctx.save_for_backward(x, weight, y, mean, invstd, gamma, beta, arg)
+        ctx.slope, ctx.batch_stats, ctx.graph = slope, batch_stats, graph
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        x, weight, y, mean, invstd, gamma, beta, arg = ctx.saved_tensors
+        g = ctx.graph
+        x, ldx = _mat(x)
+        weight, ldw = _mat(weight)
+        dout, ldd = _mat(dout, 'grad_output')
+        M, K, C = x.size(0), x.size(1), weight.size(0)
+        dev = x.device
+        in_ptr, in_edge = g.transpose()
+        da = torch.empty(M, C, dtype=_F32, device=dev)
+        call('dc_gathermax_bwd', ptr(in_ptr), ptr(in_edge), M, g.k, C, ptr(arg), ptr(dout), ldd, ptr(da), C)
+        dgamma = torch.empty(C, dtype=_F32, device=dev)
+        dbeta = torch.empty(C, dtype=_F32, device=dev)
+        dy = torch.empty(M, C, dtype=_F32, device=dev)
+        nb = query('dc_colreduce_ws_bytes', C)
+        ws = workspace(nb, dev)
+        call('dc_bn_act_bwd', ptr(y), C, ptr(da), C, M, C, ptr(mean), ptr(invstd), ptr(gamma), ptr(beta), float(ctx.slope),
+             int(ctx.batch_stats), ptr(dgamma), ptr(dbeta), ptr(dy), C, ptr(ws), nb)
+        dx, dw = _linear_backward_pair(dy, C, weight, ldw, x, ldx, M, K, C, ctx.needs_input_grad[0], ctx.needs_input_grad[1])
+        return (dx, dw, dgamma if gamma is not None else None, dbeta if beta is not None else None, None, None, None)
+
+
+def gathermax_fusable(lin, slope, x):
+    """The last block of s_mlp_max can run as the fused node: no Linear bias, a strictly increasing LeakyReLU-family activation
+    (slope > 0; ReLU's flat part would make the arg ambiguous but not the value — kept out for exact parity of the routing),
+    a channel count the float4 kernels take."""
+    return lin.bias is None and slope is not None and slope > 0 and lin.out_features % 4 == 0 and x.dim() == 2
+
+
+def linear_bn_act_gathermax(x, weight, bn, slope, graph):
+    return _LinearBNActGatherMax.apply(x, weight, bn.weight, bn.bias, bn, float(slope), graph)
+
+
 class _EdgeDiff(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, graph):

@@ -175,6 +175,12 @@ int dc_gathermax_fwd(const int32_t* idx, int N, int k, int C, const float* y, in
                      uint8_t* arg, void* stream);
 int dc_gathermax_bwd(const int32_t* in_ptr, const int32_t* in_edge, int N, int k, int C, const uint8_t* arg,
                      const float* dout, int64_t ldd, float* dy, int64_t ld_dy, void* stream);
+/* The same aggregation over leaky_relu(BatchNorm1d(y)) taken from the pre-activations y — scatter(reduce='max') of
+ * deltaconv.py:54 with the last block of s_mlp_max (mlp.py:9) folded in; the activation is monotone per channel, so the
+ * maximum is the activation of the per-channel max (gamma >= 0) or min (gamma < 0) of y.  Float4 layout only (C % 4 == 0). */
+int dc_gathermax_bn_fwd(const int32_t* idx, int N, int k, int C, const float* y, int64_t ldy, const float* mean,
+                        const float* invstd, const float* gamma_or_null, const float* beta_or_null, float slope,
+                        float* out, int64_t ldo, uint8_t* arg, void* stream);
 
 /* centralized first layer, deltaconv.py:50-52: edge features x[col]-x[row] ([N*k,C], dense) and the
  * max over the k rows of every point after the edge MLP. */

@@ -680,3 +680,39 @@ def test_transforms_run_on_a_device_batch():
     assert (out.norm.norm(dim=1) - 1).abs().max() < 1e-5
     net = no_dropout(D.utils.fill_deterministic(D.models.DeltaNetClassification(3, 10, conv_channels=[16, 32]), 5)).to(DEV).train()
     assert torch.isfinite(net(out)).all()
+
+
+@pytest.mark.parametrize('train', [True, False])
+def test_fused_gathermax_over_batchnorm_activation_matches_the_two_pass_form(train):
+    """ops.linear_bn_act_gathermax (the activation is never written: the gather-max applies BatchNorm + LeakyReLU to the
+    per-channel extreme of the pre-activations) against Linear -> BatchNorm -> LeakyReLU -> gather-max as separate kernels:
+    bitwise the same values, the same arg routing, the same gradients — including channels with a negative gamma, where the
+    maximum of the activation is the activation of the MINIMUM."""
+    D = dc()
+    from deltaconv_b200 import ops
+    torch.manual_seed(4)
+    d = D.utils.synthetic_batch(3, 0, config=12, sizes=[300, 700, 40])
+    graph = ops.knn(d.pos.to(DEV), 12, d.batch.to(DEV), num_clouds=3)
+    N, K, C = d.pos.size(0), 24, 32
+    lin = D.nn.Linear(K, C, bias=False).to(DEV)
+    bn = torch.nn.BatchNorm1d(C).to(DEV)
+    with torch.no_grad():
+        bn.weight.copy_(torch.randn(C))                   # about half of the channels get a negative gamma
+        bn.bias.copy_(0.3 * torch.randn(C))
+        bn.running_mean.copy_(0.2 * torch.randn(C)); bn.running_var.copy_(0.5 + torch.rand(C))
+    x0 = torch.randn(N, K, device=DEV)
+    g0 = torch.randn(N, C, device=DEV)
+    results = []
+    for fused in (False, True):
+        bn_i = copy.deepcopy(bn).train(train)
+        lin_i = copy.deepcopy(lin)
+        x = x0.clone().requires_grad_(True)
+        if fused:
+            out = ops.linear_bn_act_gathermax(x, lin_i.weight, bn_i, 0.2, graph)
+        else:
+            out = ops.gather_max(ops.bn_act(ops.linear(x, lin_i.weight), bn_i, 0.2), graph)
+        (out * g0).sum().backward()
+        results.append((out.detach(), x.grad, lin_i.weight.grad, bn_i.weight.grad, bn_i.bias.grad, bn_i.running_mean.clone()))
+    assert (bn.weight < 0).any() and (bn.weight > 0).any()
+    for a, b in zip(*results):
+        assert torch.equal(a, b)
