@@ -525,14 +525,24 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) tc_pair_gemm_kernel(const __gr
     const uint32_t b_base = base + PA_SLOTS * A_SLOT_BYTES;
     const uint32_t epi_base = b_base + PB_SLOTS * B_SLOT_BYTES;
     const uint32_t bar_base = epi_base + EPI_BYTES;
-    auto a_full = [&](int q) { return bar_base + 8u * q; };                                   // TMA bytes of the raw A tile
-    auto a_empty = [&](int q) { return bar_base + 8u * (PA_SLOTS + q); };                      // 4 local converter warps
-    auto b_full = [&](int sb) { return bar_base + 8u * (2 * PA_SLOTS + sb); };
-    auto ready = [&](int q) { return bar_base + 8u * (2 * PA_SLOTS + PB_SLOTS + q); };          // converters of both CTAs (rank 0's copy)
-    auto done = [&](int d) { return bar_base + 8u * (2 * PA_SLOTS + PB_SLOTS + PT_SLOTS + d); }; // MMA commit (multicast to both CTAs)
-    auto acc_full_bar = [&](int a) { return bar_base + 8u * (2 * PA_SLOTS + PB_SLOTS + PT_SLOTS + PD_SLOTS + a); };
-    auto acc_empty_bar = [&](int a) { return bar_base + 8u * (2 * PA_SLOTS + PB_SLOTS + PT_SLOTS + PD_SLOTS + 2 + a); };
-    const uint32_t tmem_slot = bar_base + 8u * (2 * PA_SLOTS + PB_SLOTS + PT_SLOTS + PD_SLOTS + 4);
+    // "Tile landed" barriers exist once per CONVERTER GROUP.  A parity wait is only meaningful on a barrier whose phases the
+    // waiter observes one after the other: the two groups take alternate k-blocks, and with an odd number of slots a slot's
+    // k-blocks alternate between the groups, so on a shared barrier a group would test phase n without ever having seen phase
+    // n-1 complete — and the test for parity n&1 also succeeds while phase n-1 is still in flight (a load that lands late, e.g.
+    // behind a TLB miss).  The group then consumed and RELEASED a slot whose load had not landed, the producer posted a second
+    // expect_tx on a barrier with no pending arrival left, and the kernel faulted (seen once per ~10^5 launches).  With a
+    // barrier per (group, slot) the k-blocks signalled on it (it = g mod 2, q mod SLOTS: every 2*SLOTS-th) all belong to one
+    // group, which waits for each of them in turn.
+    constexpr int NBAR = 3 * PA_SLOTS + 2 * PB_SLOTS + PT_SLOTS + PD_SLOTS + 4;
+    static_assert(PA_SLOTS % 2 == 1 && PB_SLOTS % 2 == 1 && PT_SLOTS == 2, "phase arithmetic below: odd slot counts, one tensor-memory slot per converter group");
+    auto a_full = [&](int grp, int q) { return bar_base + 8u * (grp * PA_SLOTS + q); };          // TMA bytes of the raw A tile
+    auto a_empty = [&](int q) { return bar_base + 8u * (2 * PA_SLOTS + q); };                    // 4 local converter warps
+    auto b_full = [&](int grp, int sb) { return bar_base + 8u * (3 * PA_SLOTS + grp * PB_SLOTS + sb); };
+    auto ready = [&](int q) { return bar_base + 8u * (3 * PA_SLOTS + 2 * PB_SLOTS + q); };        // converters of both CTAs (rank 0's copy)
+    auto done = [&](int d) { return bar_base + 8u * (3 * PA_SLOTS + 2 * PB_SLOTS + PT_SLOTS + d); }; // MMA commit (multicast to both CTAs)
+    auto acc_full_bar = [&](int a) { return bar_base + 8u * (3 * PA_SLOTS + 2 * PB_SLOTS + PT_SLOTS + PD_SLOTS + a); };
+    auto acc_empty_bar = [&](int a) { return bar_base + 8u * (3 * PA_SLOTS + 2 * PB_SLOTS + PT_SLOTS + PD_SLOTS + 2 + a); };
+    const uint32_t tmem_slot = bar_base + 8u * NBAR;
     volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(base_ptr + (tmem_slot - base));
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -548,8 +558,8 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) tc_pair_gemm_kernel(const __gr
 #define TC_TRACE(ev, it) do { if (trace && (it) < 256u) trace[(ev) * 256 + (it)] = clock64(); } while (0)
 
     if (threadIdx.x == 0) {
-        for (int q = 0; q < PA_SLOTS; ++q) { mbar_init(a_full(q), 1); mbar_init(a_empty(q), 4); }
-        for (int sb = 0; sb < PB_SLOTS; ++sb) mbar_init(b_full(sb), 1);
+        for (int q = 0; q < PA_SLOTS; ++q) { mbar_init(a_full(0, q), 1); mbar_init(a_full(1, q), 1); mbar_init(a_empty(q), 4); }
+        for (int sb = 0; sb < PB_SLOTS; ++sb) { mbar_init(b_full(0, sb), 1); mbar_init(b_full(1, sb), 1); }
         for (int q = 0; q < PT_SLOTS; ++q) mbar_init(ready(q), 8);
         for (int d = 0; d < PD_SLOTS; ++d) mbar_init(done(d), 1);
         for (int a = 0; a < 2; ++a) { mbar_init(acc_full_bar(a), 1); mbar_init(acc_empty_bar(a), 8); }
@@ -591,15 +601,16 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) tc_pair_gemm_kernel(const __gr
                 for (int kb = 0; kb < nkb; ++kb, ++it) {
                     const int q = it % PA_SLOTS;
                     const uint32_t ph = (it / PA_SLOTS) & 1;
+                    const uint32_t full = a_full((int)(it & 1u), q);      // the barrier of the converter group that takes this k-block
                     mbar_wait(a_empty(q), ph ^ 1u);
-                    mbar_expect_tx(a_full(q), A_SLOT_BYTES);
+                    mbar_expect_tx(full, A_SLOT_BYTES);
 #pragma unroll
                     for (int j = 0; j < PK; ++j) {
                         const int k0 = (kb_begin + kb * PK + j) * TC_BK;
-                        if (!A_MN) tma_load_2d(slot_a(q) + j * A_BYTES, &tmA, a_full(q), k0, m0);
+                        if (!A_MN) tma_load_2d(slot_a(q) + j * A_BYTES, &tmA, full, k0, m0);
                         else
 #pragma unroll
-                            for (int c = 0; c < TC_BM / 32; ++c) tma_load_2d(slot_a(q) + j * A_BYTES + c * CHUNK_BYTES, &tmA, a_full(q), m0 + 32 * c, k0);
+                            for (int c = 0; c < TC_BM / 32; ++c) tma_load_2d(slot_a(q) + j * A_BYTES + c * CHUNK_BYTES, &tmA, full, m0 + 32 * c, k0);
                     }
                 }
             }
@@ -619,14 +630,15 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) tc_pair_gemm_kernel(const __gr
                         const uint32_t prev = it - PB_SLOTS;
                         mbar_wait(done(prev % PD_SLOTS), (prev / PD_SLOTS) & 1);
                     }
-                    mbar_expect_tx(b_full(sb), PK * BH_BYTES);
+                    const uint32_t full = b_full((int)(it & 1u), sb);
+                    mbar_expect_tx(full, PK * BH_BYTES);
 #pragma unroll
                     for (int j = 0; j < PK; ++j) {
                         const int k0 = (kb_begin + kb * PK + j) * TC_BK;
-                        if (!B_MN) tma_load_2d(slot_b(sb) + j * BH_BYTES, &tmB, b_full(sb), k0, nb0);
+                        if (!B_MN) tma_load_2d(slot_b(sb) + j * BH_BYTES, &tmB, full, k0, nb0);
                         else
 #pragma unroll
-                            for (int c = 0; c < BH / 32; ++c) tma_load_2d(slot_b(sb) + j * BH_BYTES + c * CHUNK_BYTES, &tmB, b_full(sb), nb0 + 32 * c, k0);
+                            for (int c = 0; c < BH / 32; ++c) tma_load_2d(slot_b(sb) + j * BH_BYTES + c * CHUNK_BYTES, &tmB, full, nb0 + 32 * c, k0);
                     }
                 }
             }
@@ -692,8 +704,9 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) tc_pair_gemm_kernel(const __gr
             for (int kb = 0; kb < nkb; ++kb, ++it) {
                 if ((int)(it & 1u) != grp) continue;
                 const int qa = it % PA_SLOTS, q = it % PT_SLOTS, sb = it % PB_SLOTS;
-                const uint32_t aph = (it / PA_SLOTS) & 1, bph = (it / PB_SLOTS) & 1;
-                mbar_wait(a_full(qa), aph);
+                // barrier (grp, slot) is signalled for every (2 * SLOTS)-th k-block, all of them this group's
+                const uint32_t aph = (it / (2 * PA_SLOTS)) & 1, bph = (it / (2 * PB_SLOTS)) & 1;
+                mbar_wait(a_full(grp, qa), aph);
                 if ((warp & 3) == 2 && lane == 0) TC_TRACE(4, it);
                 const int row = (warp & 3) * 32 + lane;
                 if (it >= (uint32_t)PT_SLOTS) {                        // the MMAs that read this tensor-memory slot have completed
@@ -737,7 +750,7 @@ __global__ void __launch_bounds__(TCP_THREADS, 1) tc_pair_gemm_kernel(const __gr
                 __syncwarp();
                 if (lane == 0) mbar_arrive(a_empty(qa));
                 // B half: lo next to the raw tile (the MMA truncates the raw fp32 words to tf32 itself)
-                mbar_wait(b_full(sb), bph);
+                mbar_wait(b_full(grp, sb), bph);
                 if ((warp & 3) == 2 && lane == 0) TC_TRACE(6, it);
                 const float4* b_hi = reinterpret_cast<const float4*>(base_ptr + (slot_b(sb) - base));
                 float4* b_lo = reinterpret_cast<float4*>(base_ptr + (slot_b_lo(sb) - base));
@@ -941,7 +954,7 @@ int g_tc_pair = 1;          // 1: CTA pairs (cta_group::2) for the 3xTF32 produc
 
 template <int BN, bool A_MN, bool B_MN>
 int launch_tc_pair(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const TcArgs& g, int splits, cudaStream_t st) {
-    const size_t smem = (size_t)PA_SLOTS * PK * TC_BM * 128 + (size_t)PB_SLOTS * PK * BN * 128 + 32768 + 1024 + 8 * (2 * PA_SLOTS + PB_SLOTS + PT_SLOTS + PD_SLOTS + 4) + 16;
+    const size_t smem = (size_t)PA_SLOTS * PK * TC_BM * 128 + (size_t)PB_SLOTS * PK * BN * 128 + 32768 + 1024 + 8 * (3 * PA_SLOTS + 2 * PB_SLOTS + PT_SLOTS + PD_SLOTS + 4) + 16;
     auto kern = tc_pair_gemm_kernel<BN, A_MN, B_MN>;
     DC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const long long tiles_n = (g.N + BN - 1) / BN, tiles_m = (g.M + TC_BM - 1) / TC_BM;
