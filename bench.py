@@ -150,6 +150,10 @@ def _w_linb(a): M, K, N = a[4], a[5], a[6]; return 4 * (M * K + K * N + M * N), 
 def _w_ediff(a): N, k, C = a[1], a[2], a[3]; return N * (4 * k + 4 * C + 4 * k * C), 0
 def _w_segmax(a): N, k, C = a[1], a[2], a[3]; return N * C * (4 * k + 5), 0
 def _w_segmax_t(a): N, k, C = a[2], a[3], a[4]; return N * C * (4 * k + 5), 0
+def _w_segmax_bn(a): N, k, C = a[1], a[2], a[3]; return N * C * (4 * k + 5), 0                  # y [N*k,C] read, out + arg written
+def _w_segmax_bn_t(a): N, k, C = a[1], a[2], a[3]; return N * C * (8 * k + 5), 0               # y read, dy written
+def _w_cedge(a): N, k, Cout = a[1], a[2], a[4]; return N * (12 + 4 * k + 4 * k * Cout), 0      # coordinates + idx read, h [N*k,Cout] written
+def _w_cedge_t(a): N, k, Cout = a[1], a[2], a[4]; return N * (12 + 4 * k + 4 * k * Cout), 0    # dh read once
 def _w_pool(a): return 0, 0
 def _w_sgd(a): return a[3] * 20, 0                               # p, buf read and written, g read
 def _w_bnpool(a): return WL['clouds'] * WL['points'] * a[4] * 4, 0          # y read once, only [B,2C] written
@@ -170,6 +174,8 @@ WORK = {
     'dc_linear_fwd': (_w_lin, 'gemm'), 'dc_linear_bwd_input': (_w_linb, 'gemm'), 'dc_linear_bwd_weight': (_w_linb, 'gemm'),
     'dc_edge_diff_fwd': (_w_ediff, 'centralized'), 'dc_segmax_fwd': (_w_segmax, 'centralized'),
     'dc_segmax_bwd': (_w_segmax_t, 'centralized'),
+    'dc_segmax_bn_fwd': (_w_segmax_bn, 'centralized'), 'dc_segmax_bn_bwd': (_w_segmax_bn_t, 'centralized'),
+    'dc_central_edge_fwd': (_w_cedge, 'centralized'), 'dc_central_edge_bwd': (_w_cedge_t, 'centralized'),
 }
 KERNEL_OF = {'gemm': 'tc_pair_gemm_kernel / tc_gemm_kernel / sgemm_kernel (dc_linear_fwd / _bwd_input / _bwd_weight)', 'spmm': 'spmm_kernel (grad/div/curl/hodge and transposes)',
              'batchnorm': 'col_reduce/bn_act kernels', 'knn': 'knn_kernel', 'build_grad_div': 'fit_kernel (+ edge/cloud means)',

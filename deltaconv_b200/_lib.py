@@ -56,11 +56,15 @@ _SIGNATURES = {
     'dc_edge_diff_bwd': [_P, _P, _I, _I, _I, _P, _P, _L, _P],
     'dc_segmax_fwd': [_P, _I, _I, _I, _P, _P, _L, _P, _P],
     'dc_segmax_bwd': [_P, _L, _I, _I, _I, _P, _P, _P],
+    'dc_segmax_bn_fwd': [_P, _I, _I, _I, _P, _P, _P, _P, _P, _F, _P, _L, _P, _P],
+    'dc_segmax_bn_bwd': [_P, _I, _I, _I, _P, _P, _L, _P, _P, _P, _P, _F, _I, _P, _P, _P, _P, _Z, _P],
     'dc_central_max_cin': [],
     'dc_central_ws_bytes': [_I, _I, _I, _I],
     'dc_central_stats': [_P, _I, _I, _I, _I, _P, _L, _P, _F, _F, _P, _P, _P, _P, _P, _P, _P, _Z, _P],
     'dc_central_fwd': [_P, _I, _I, _I, _I, _P, _L, _P, _P, _P, _P, _P, _F, _P, _L, _P, _P],
     'dc_central_bwd': [_P, _P, _P, _I, _I, _I, _I, _P, _L, _P, _P, _P, _P, _P, _P, _F, _I, _P, _P, _L, _P, _P, _P, _P, _L, _P, _Z, _P],
+    'dc_central_edge_fwd': [_P, _I, _I, _I, _I, _P, _L, _P, _P, _P, _P, _P, _F, _P, _P],
+    'dc_central_edge_bwd': [_P, _I, _I, _I, _I, _P, _L, _P, _P, _P, _P, _P, _P, _F, _I, _P, _L, _P, _P, _P, _P, _Z, _P],
     'dc_colreduce_ws_bytes': [_I],
     'dc_bn_stats': [_P, _L, _L, _I, _I, _F, _F, _P, _P, _P, _P, _P, _P, _Z, _P],
     'dc_bn_act_fwd': [_P, _L, _L, _I, _P, _P, _P, _P, _F, _P, _L, _P, _L, _P],

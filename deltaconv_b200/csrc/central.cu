@@ -248,6 +248,108 @@ __global__ void __launch_bounds__(256) central_bwd_edge_kernel(const int* __rest
     }
 }
 
+// ---- deeper edge MLPs (s_mlp_max of depth >= 2: the ShapeNet configuration) --------------------------------
+// Only the FIRST block can be recomputed from the offsets; its activation h[e,c] = act(bn(w_c . d_e)) feeds a Linear over the
+// E rows and has to exist.  It is written once, straight from the point coordinates: the [E,Cin] offsets, the [E,Cout]
+// pre-activation, the statistics pass over it and the normalise pass (write, read, read + write of E x Cout floats) never
+// happen — the statistics are the moment formula above.
+__global__ void __launch_bounds__(256) central_edge_fwd_kernel(const int* __restrict__ idx, int N, int k, int Cin, int Cout,
+                                                               const float* __restrict__ x, long long ldx, const float* __restrict__ W,
+                                                               const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                               const float* __restrict__ mean, const float* __restrict__ invstd, float slope,
+                                                               float* __restrict__ out) {
+    const long long warp = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (warp >= N) return;
+    const int i = (int)warp;
+    float d[2][CIN_MAX];
+    load_offsets(idx, N, k, Cin, x, ldx, i, lane, d);
+    float* row = out + (size_t)i * k * Cout;
+    for (int c0 = 0; c0 < Cout; c0 += 32) {
+        const int c = c0 + lane;
+        const bool ok = c < Cout;
+        float w[CIN_MAX];
+#pragma unroll
+        for (int q = 0; q < CIN_MAX; ++q) w[q] = (ok && q < Cin) ? __ldg(W + (size_t)c * Cin + q) : 0.f;
+        const float mu = ok ? __ldg(mean + c) : 0.f, is = ok ? __ldg(invstd + c) : 0.f;
+        const float g = (ok && gamma) ? __ldg(gamma + c) : 1.f, b = (ok && beta) ? __ldg(beta + c) : 0.f;
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+            const int cnt = min(32, k - 32 * s);
+            for (int e = 0; e < cnt; ++e) {
+                float t = 0.f;
+#pragma unroll
+                for (int q = 0; q < CIN_MAX; ++q) t = fmaf(w[q], __shfl_sync(FULL, d[s][q], e), t);
+                float z = g * ((t - mu) * is) + b;
+                z = z > 0.f ? z : slope * z;
+                if (ok) __stcs(row + (size_t)(e + 32 * s) * Cout + c, z);       // 128 contiguous bytes per warp store
+            }
+        }
+    }
+}
+
+// Backward of that block from the DENSE gradient dh [E,Cout] of its activation: the same three sums as CentralBwdVal, taken
+// over all E edge rows in one pass (dh is read once; offsets and pre-activation are recomputed), and the same finalize.
+// Replaces the BatchNorm backward (two reads of y and dh, one write) and the weight-gradient product over E rows.
+template <int CIN>
+struct CentralCols { float w[4][CIN]; float mean[4], invstd[4], gamma[4], beta[4]; };
+
+template <int CIN>
+struct CentralDenseBwdVal {
+    const int* idx; int N, k, Cout;
+    const float* x; long long ldx; const float* W; const float* gamma; const float* beta; const float* mean; const float* invstd;
+    float slope; const float* dh; long long ldd;
+    __device__ __forceinline__ void offsets(long long r, float (&d)[CIN]) const {
+        const int i = (int)r / k;
+        int j = __ldg(idx + r);
+        if ((unsigned)j >= (unsigned)N) j = i;
+#pragma unroll
+        for (int q = 0; q < CIN; ++q) d[q] = __ldg(x + (size_t)j * ldx + q) - __ldg(x + (size_t)i * ldx + q);
+    }
+    __device__ void operator()(long long r, int c, float (&o)[2 + CIN]) const {
+        float d[CIN], t = 0.f;
+        offsets(r, d);
+#pragma unroll
+        for (int q = 0; q < CIN; ++q) t = fmaf(__ldg(W + (size_t)c * CIN + q), d[q], t);
+        const float xh = (t - __ldg(mean + c)) * __ldg(invstd + c);
+        const float g = gamma ? __ldg(gamma + c) : 1.f, b = beta ? __ldg(beta + c) : 0.f;
+        const float z = g * xh + b;
+        const float dz = __ldg(dh + r * ldd + c) * (z > 0.f ? 1.f : slope);
+        o[0] = dz; o[1] = dz * xh;
+#pragma unroll
+        for (int q = 0; q < CIN; ++q) o[2 + q] = dz * d[q];
+    }
+    __device__ CentralCols<CIN> columns(int c) const {
+        CentralCols<CIN> kc;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+#pragma unroll
+            for (int q = 0; q < CIN; ++q) kc.w[u][q] = __ldg(W + (size_t)(c + u) * CIN + q);
+            kc.mean[u] = __ldg(mean + c + u); kc.invstd[u] = __ldg(invstd + c + u);
+            kc.gamma[u] = gamma ? __ldg(gamma + c + u) : 1.f; kc.beta[u] = beta ? __ldg(beta + c + u) : 0.f;
+        }
+        return kc;
+    }
+    __device__ void quad(long long r, int c, const CentralCols<CIN>& kc, float (&o)[4][2 + CIN]) const {
+        float d[CIN];
+        offsets(r, d);
+        const float4 dv = __ldg(reinterpret_cast<const float4*>(dh + r * ldd + c));
+        const float dd[4] = {dv.x, dv.y, dv.z, dv.w};
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            float t = 0.f;
+#pragma unroll
+            for (int q = 0; q < CIN; ++q) t = fmaf(kc.w[u][q], d[q], t);
+            const float xh = (t - kc.mean[u]) * kc.invstd[u];
+            const float z = kc.gamma[u] * xh + kc.beta[u];
+            const float dz = dd[u] * (z > 0.f ? 1.f : slope);
+            o[u][0] = dz; o[u][1] = dz * xh;
+#pragma unroll
+            for (int q = 0; q < CIN; ++q) o[u][2 + q] = dz * d[q];
+        }
+    }
+};
+
 int moments_chunks(long long E) {
     long long g = (E + 255) / 256, cap = (long long)dc_sm_count() * 4;
     return (int)(g < cap ? (g < 1 ? 1 : g) : cap);
@@ -338,4 +440,46 @@ extern "C" int dc_central_bwd(const int32_t* idx, const int32_t* in_ptr_or_null,
         return dc_edge_diff_bwd(in_ptr_or_null, in_edge_or_null, N, k, Cin, g, dx_or_null, ld_dx, stream);
     }
     return dc_check_launch_n("dc_central_bwd", launches);
+}
+
+// First block of a deeper edge MLP: h[e, :] = act(bn(W (x_j - x_i))) for every edge slot, [N*k, Cout] row-major (the layout
+// dc_edge_diff_fwd + Linear + dc_bn_act_fwd would produce).  mean / invstd come from dc_central_stats (training) or the
+// running statistics (evaluation).
+extern "C" int dc_central_edge_fwd(const int32_t* idx, int N, int k, int Cin, int Cout, const float* x, int64_t ldx, const float* W,
+                                   const float* gamma_or_null, const float* beta_or_null, const float* mean, const float* invstd, float slope,
+                                   float* out, void* stream) {
+    DC_REQUIRE(Cin >= 1 && Cin <= CIN_MAX, "dc_central_edge_fwd: Cin must be in [1,%d]", CIN_MAX);
+    DC_REQUIRE(k >= 1 && k <= 64, "dc_central_edge_fwd: k must be in [1,64]");
+    if (N <= 0 || Cout <= 0) return DC_OK;
+    central_edge_fwd_kernel<<<dc_ceil_div((long long)N * 32, 256), 256, 0, (cudaStream_t)stream>>>(idx, N, k, Cin, Cout, x, ldx, W, gamma_or_null,
+                                                                                                    beta_or_null, mean, invstd, slope, out);
+    return dc_check_launch("dc_central_edge_fwd");
+}
+
+// Its backward from dh [N*k, Cout] (row pitch ldd): dW [Cout,Cin], dgamma, dbeta.  No gradient w.r.t. x (callers that need it
+// use the unfused sequence).  Workspace: dc_central_ws_bytes.
+extern "C" int dc_central_edge_bwd(const int32_t* idx, int N, int k, int Cin, int Cout, const float* x, int64_t ldx, const float* W,
+                                   const float* gamma_or_null, const float* beta_or_null, const float* mean, const float* invstd,
+                                   const double* moments, float slope, int training, const float* dh, int64_t ldd, float* dW, float* dgamma,
+                                   float* dbeta, void* ws, size_t ws_bytes, void* stream) {
+    DC_REQUIRE(Cin >= 1 && Cin <= CIN_MAX, "dc_central_edge_bwd: Cin must be in [1,%d]", CIN_MAX);
+    DC_REQUIRE(k >= 1 && k <= 64, "dc_central_edge_bwd: k must be in [1,64]");
+    DC_REQUIRE((long long)N * k < (1LL << 31), "dc_central_edge_bwd: more than 2^31 edge rows");
+    DC_REQUIRE(ws_bytes >= dc_central_ws_bytes(N, k, Cin, Cout), "dc_central_edge_bwd: workspace too small");
+    if (N <= 0 || Cout <= 0) return DC_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    double* partial = (double*)ws;
+    const long long E = (long long)N * k;
+    const bool vec4_ok = Cout % 4 == 0 && ldd % 4 == 0 && ((uintptr_t)dh & 15) == 0;
+#define DC_CENTRAL_CASE(CIN)                                                                                                      \
+    case CIN: {                                                                                                                   \
+        CentralDenseBwdVal<CIN> f = {idx, N, k, Cout, x, ldx, W, gamma_or_null, beta_or_null, mean, invstd, slope, dh, ldd};     \
+        const int chunks = col_reduce_launch<2 + CIN>(f, E, Cout, vec4_ok, partial, st);                                          \
+        central_bwd_finalize_kernel<CIN><<<dc_ceil_div(Cout, FIN_COLS), FIN_T, 0, st>>>(partial, chunks, Cout, W, gamma_or_null, mean, invstd,  \
+                                                                                 moments, training, dW, dgamma, dbeta);          \
+        break;                                                                                                                    \
+    }
+    switch (Cin) { DC_CENTRAL_CASE(1) DC_CENTRAL_CASE(2) DC_CENTRAL_CASE(3) DC_CENTRAL_CASE(4) }
+#undef DC_CENTRAL_CASE
+    return dc_check_launch_n("dc_central_edge_bwd", 2);
 }

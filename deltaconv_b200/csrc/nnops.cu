@@ -861,6 +861,137 @@ __global__ void __launch_bounds__(256) segmax_bwd_vec4_kernel(const float* __res
     }
 }
 
+// The last block of a deeper edge MLP fused with the max over the edges (the segment-max analogue of gathermax_fwd_vec4_kernel
+// <true>): `in` holds the PRE-activations y [N*k, C]; out[i,c] = max_e act(bn(y[i*k+e, c])) by selecting the per-channel extreme
+// of (+-)y — the activation [N*k, C] is neither written nor read back.  The value is computed from the selected element with the
+// expression of bn_act_fwd_kernel: bitwise what BatchNorm + activation followed by segmax_fwd_vec4_kernel gives.
+__global__ void __launch_bounds__(256) segmax_bn_fwd_vec4_kernel(const float* __restrict__ in, int N, int k, int C4, const int* __restrict__ idx,
+                                                                 float* __restrict__ out, long long ldo, unsigned char* __restrict__ arg, BnAct bn) {
+    for (RowCol rc(C4); rc.r < N; rc.next()) {
+        const int i = (int)rc.r, c = rc.c * 4;
+        const float4* row = reinterpret_cast<const float4*>(in + ((size_t)i * k) * (4 * C4) + c);
+        unsigned neg = 0u;
+        if (bn.gamma) {
+            const float4 ga = __ldg(reinterpret_cast<const float4*>(bn.gamma + c));
+            neg = (__float_as_uint(ga.x) >> 31) | ((__float_as_uint(ga.y) >> 31) << 1) | ((__float_as_uint(ga.z) >> 31) << 2) | ((__float_as_uint(ga.w) >> 31) << 3);
+        }
+        float4 best = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+        uchar4 slot = make_uchar4(0, 0, 0, 0);
+        for (int e0 = 0; e0 < k; e0 += 6) {
+            float4 v[6];
+            bool ok[6];
+#pragma unroll
+            for (int u = 0; u < 6; ++u) {
+                ok[u] = e0 + u < k && !(idx && (unsigned)__ldg(idx + (size_t)i * k + e0 + u) >= (unsigned)N);
+                if (e0 + u < k) v[u] = ld_stream4(row + (size_t)(e0 + u) * C4);
+            }
+#pragma unroll
+            for (int u = 0; u < 6; ++u)
+                if (ok[u]) {
+                    const unsigned char e = (unsigned char)(e0 + u);
+                    const float vx = __uint_as_float(__float_as_uint(v[u].x) ^ ((neg & 1u) << 31)), vy = __uint_as_float(__float_as_uint(v[u].y) ^ ((neg & 2u) << 30));
+                    const float vz = __uint_as_float(__float_as_uint(v[u].z) ^ ((neg & 4u) << 29)), vw = __uint_as_float(__float_as_uint(v[u].w) ^ ((neg & 8u) << 28));
+                    if (vx > best.x) { best.x = vx; slot.x = e; }
+                    if (vy > best.y) { best.y = vy; slot.y = e; }
+                    if (vz > best.z) { best.z = vz; slot.z = e; }
+                    if (vw > best.w) { best.w = vw; slot.w = e; }
+                }
+        }
+        const float4 mu = __ldg(reinterpret_cast<const float4*>(bn.mean + c)), is = __ldg(reinterpret_cast<const float4*>(bn.invstd + c));
+        const float4 ga = bn.gamma ? __ldg(reinterpret_cast<const float4*>(bn.gamma + c)) : make_float4(1.f, 1.f, 1.f, 1.f);
+        const float4 be = bn.beta ? __ldg(reinterpret_cast<const float4*>(bn.beta + c)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        const float b4[4] = {best.x, best.y, best.z, best.w}, m4[4] = {mu.x, mu.y, mu.z, mu.w};
+        const float i4[4] = {is.x, is.y, is.z, is.w}, g4[4] = {ga.x, ga.y, ga.z, ga.w}, e4[4] = {be.x, be.y, be.z, be.w};
+        float o4[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const float ysel = __uint_as_float(__float_as_uint(b4[u]) ^ (((neg >> u) & 1u) << 31));
+            float z = g4[u] * ((ysel - m4[u]) * i4[u]) + e4[u];
+            z = z > 0.f ? z : bn.slope * z;
+            o4[u] = b4[u] == -INFINITY ? 0.f : z;
+        }
+        *reinterpret_cast<float4*>(out + (size_t)i * ldo + c) = make_float4(o4[0], o4[1], o4[2], o4[3]);
+        *reinterpret_cast<uchar4*>(arg + (size_t)i * (4 * C4) + c) = slot;
+    }
+}
+
+// Backward of that node.  The gradient of the activation is non-zero only at the arg-max edge of each (point, channel), so the
+// two BatchNorm sums run over the N points (y is read at the selected rows only) ...
+struct SegBnBwdVal {
+    const float* y; int k, C; const unsigned char* arg; const float* dout; long long ldd;
+    const float* mean; const float* invstd; const float* gamma; const float* beta; float slope;
+    __device__ void operator()(long long r, int c, float (&o)[2]) const {
+        const int e = arg[(size_t)r * C + c];
+        const float xh = (__ldg(y + ((size_t)r * k + e) * C + c) - __ldg(mean + c)) * __ldg(invstd + c);
+        const float g = gamma ? __ldg(gamma + c) : 1.f, b = beta ? __ldg(beta + c) : 0.f;
+        const float z = g * xh + b;
+        const float dz = __ldg(dout + r * ldd + c) * (z > 0.f ? 1.f : slope);
+        o[0] = dz; o[1] = dz * xh;
+    }
+    __device__ BnColumns columns(int c) const { return bn_columns(mean, invstd, gamma, beta, c); }
+    __device__ void quad(long long r, int c, const BnColumns& kc, float (&o)[4][2]) const {
+        const uchar4 a = *reinterpret_cast<const uchar4*>(arg + (size_t)r * C + c);
+        const float4 dv = __ldg(reinterpret_cast<const float4*>(dout + r * ldd + c));
+        const float* base = y + (size_t)r * k * C + c;
+        const float yy[4] = {__ldg(base + (size_t)a.x * C), __ldg(base + (size_t)a.y * C + 1), __ldg(base + (size_t)a.z * C + 2),
+                             __ldg(base + (size_t)a.w * C + 3)};
+        const float dd[4] = {dv.x, dv.y, dv.z, dv.w};
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const float xh = (yy[u] - kc.mean[u]) * kc.invstd[u];
+            const float z = kc.gamma[u] * xh + kc.beta[u];
+            const float dz = dd[u] * (z > 0.f ? 1.f : slope);
+            o[u][0] = dz; o[u][1] = dz * xh;
+        }
+    }
+};
+
+// ... and the elementwise part streams y [N*k, C] once and writes dy once: a thread owns (point, 4 channels), the sparse
+// gradient of the activation (dout at the arg slot) is formed in registers.  M = N*k rows share the statistics.
+__global__ void __launch_bounds__(256) segmax_bn_bwd_vec4_kernel(const float* __restrict__ y, const float* __restrict__ dout, long long ldd,
+                                                                 int N, int k, int C4, const unsigned char* __restrict__ arg, BnAct bn,
+                                                                 const float* __restrict__ sum_dz, const float* __restrict__ sum_dz_xh,
+                                                                 int training, float* __restrict__ dy) {
+    const float invM = 1.f / ((float)N * (float)k);
+    for (RowCol rc(C4); rc.r < N; rc.next()) {
+        const int i = (int)rc.r, c = rc.c * 4;
+        const uchar4 a = *reinterpret_cast<const uchar4*>(arg + (size_t)i * (4 * C4) + c);
+        const float4 d = __ldg(reinterpret_cast<const float4*>(dout + (size_t)i * ldd + c));
+        const float4 mu = __ldg(reinterpret_cast<const float4*>(bn.mean + c)), is = __ldg(reinterpret_cast<const float4*>(bn.invstd + c));
+        const float4 g = bn.gamma ? __ldg(reinterpret_cast<const float4*>(bn.gamma + c)) : make_float4(1.f, 1.f, 1.f, 1.f);
+        const float4 b = bn.beta ? __ldg(reinterpret_cast<const float4*>(bn.beta + c)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        float4 s1 = make_float4(0.f, 0.f, 0.f, 0.f), s2 = s1;
+        if (training) {
+            s1 = __ldg(reinterpret_cast<const float4*>(sum_dz + c)); s2 = __ldg(reinterpret_cast<const float4*>(sum_dz_xh + c));
+            s1.x *= invM; s1.y *= invM; s1.z *= invM; s1.w *= invM; s2.x *= invM; s2.y *= invM; s2.z *= invM; s2.w *= invM;
+        }
+        const float slope = bn.slope;
+        auto one = [&](float yy, float dd, bool hit, float m, float i_, float gg, float bb, float a1, float a2) {
+            const float xh = (yy - m) * i_;
+            const float z = gg * xh + bb;
+            const float dz = hit ? dd * (z > 0.f ? 1.f : slope) : 0.f;
+            return gg * i_ * (dz - a1 - xh * a2);
+        };
+        const float4* yrow = reinterpret_cast<const float4*>(y + ((size_t)i * k) * (4 * C4) + c);
+        float4* drow = reinterpret_cast<float4*>(dy + ((size_t)i * k) * (4 * C4) + c);
+        for (int e0 = 0; e0 < k; e0 += 4) {
+            float4 v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (e0 + u < k) v[u] = ld_stream4(yrow + (size_t)(e0 + u) * C4);
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (e0 + u < k) {
+                    const unsigned char ee = (unsigned char)(e0 + u);
+                    float4 o;
+                    o.x = one(v[u].x, d.x, a.x == ee, mu.x, is.x, g.x, b.x, s1.x, s2.x); o.y = one(v[u].y, d.y, a.y == ee, mu.y, is.y, g.y, b.y, s1.y, s2.y);
+                    o.z = one(v[u].z, d.z, a.z == ee, mu.z, is.z, g.z, b.z, s1.z, s2.z); o.w = one(v[u].w, d.w, a.w == ee, mu.w, is.w, g.w, b.w, s1.w, s2.w);
+                    st_stream4(drow + (size_t)(e0 + u) * C4, o);
+                }
+        }
+    }
+}
+
 // ---- global pools (one CTA per (cloud, 32-channel block); rows of a cloud are contiguous) ------
 // out_max[b,c] = max_i x[i,c] (arg kept), out_mean[b,c] = mean_i x[i,c]
 // With BN the pooled quantity is leaky_relu(gamma * (x - mean) * invstd + beta): the activation of the embedding layer is
@@ -1155,6 +1286,43 @@ extern "C" int dc_segmax_bwd(const float* dout, int64_t ldd, int N, int k, int C
     else
         segmax_bwd_kernel<<<elementwise_grid((long long)N * k * C), 256, 0, (cudaStream_t)stream>>>(dout, ldd, N, k, C, arg, din);
     return dc_check_launch("dc_segmax_bwd");
+}
+
+// max over each point's k edge rows of leaky_relu(BatchNorm(y)) from the pre-activations y [N*k, C] (the last block of a
+// centralized s_mlp_max of depth >= 2, deltaconv.py:50-52): the activation is never written.  float4 layout only.
+extern "C" int dc_segmax_bn_fwd(const float* y, int N, int k, int C, const int32_t* idx_or_null, const float* mean, const float* invstd,
+                                const float* gamma_or_null, const float* beta_or_null, float slope, float* out, int64_t ldo, uint8_t* arg,
+                                void* stream) {
+    DC_REQUIRE(k >= 1 && k <= 255, "dc_segmax_bn_fwd: k must be in [1,255]");
+    DC_REQUIRE(slope > 0.f, "dc_segmax_bn_fwd: the activation must be strictly increasing (LeakyReLU slope > 0)");
+    DC_REQUIRE(C % 4 == 0 && ldo % 4 == 0 && all_aligned16(y, out, mean, invstd, gamma_or_null, beta_or_null) &&
+               (reinterpret_cast<uintptr_t>(arg) & 3u) == 0, "dc_segmax_bn_fwd: needs C %% 4 == 0 and 16-byte aligned rows");
+    if (N <= 0 || C <= 0) return DC_OK;
+    BnAct bn = {mean, invstd, gamma_or_null, beta_or_null, slope};
+    segmax_bn_fwd_vec4_kernel<<<elementwise_grid((long long)N * C / 4), 256, 0, (cudaStream_t)stream>>>(y, N, k, C / 4, idx_or_null, out, ldo, arg, bn);
+    return dc_check_launch("dc_segmax_bn_fwd");
+}
+
+// Backward of dc_segmax_bn_fwd: dout [N,C] (gradient of the max) -> dy [N*k, C] (gradient of the pre-activations), d_gamma,
+// d_beta.  training != 0: batch statistics over the N*k rows (the mean terms reach every row); 0: running statistics.
+// Workspace: dc_colreduce_ws_bytes(C).
+extern "C" int dc_segmax_bn_bwd(const float* y, int N, int k, int C, const uint8_t* arg, const float* dout, int64_t ldd, const float* mean,
+                                const float* invstd, const float* gamma_or_null, const float* beta_or_null, float slope, int training,
+                                float* d_gamma, float* d_beta, float* dy, void* ws, size_t ws_bytes, void* stream) {
+    DC_REQUIRE(k >= 1 && k <= 255, "dc_segmax_bn_bwd: k must be in [1,255]");
+    DC_REQUIRE(C % 4 == 0 && ldd % 4 == 0 && all_aligned16(y, dout, dy, mean, invstd, gamma_or_null, beta_or_null) &&
+               all_aligned16(d_gamma, d_beta) && (reinterpret_cast<uintptr_t>(arg) & 3u) == 0,
+               "dc_segmax_bn_bwd: needs C %% 4 == 0 and 16-byte aligned rows");
+    DC_REQUIRE(ws_bytes >= dc_colreduce_ws_bytes(C), "dc_segmax_bn_bwd: workspace too small");
+    if (N <= 0 || C <= 0) return DC_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    double* partial = (double*)ws;
+    SegBnBwdVal f = {y, k, C, arg, dout, ldd, mean, invstd, gamma_or_null, beta_or_null, slope};
+    const int chunks = col_reduce_launch<2>(f, (long long)N, C, true, partial, st);
+    sum2_finalize_kernel<<<dc_ceil_div(C, FIN_COLS), FIN_T, 0, st>>>(partial, chunks, C, d_beta, d_gamma);
+    BnAct bn = {mean, invstd, gamma_or_null, beta_or_null, slope};
+    segmax_bn_bwd_vec4_kernel<<<elementwise_grid((long long)N * C / 4), 256, 0, st>>>(y, dout, ldd, N, k, C / 4, arg, bn, d_beta, d_gamma, training, dy);
+    return dc_check_launch_n("dc_segmax_bn_bwd", 3);
 }
 
 extern "C" int dc_pool_fwd(const float* x, int64_t ldx, const int32_t* cloud_ptr, int B, int C, float* out_max_or_null,

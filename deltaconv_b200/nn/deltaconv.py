@@ -47,7 +47,7 @@ class DeltaConv(torch.nn.Module):
                 # edge MLP + BatchNorm over the E edge rows + max, without any per-edge tensor
                 x_max = ops.centralized_max(x, block[0].weight, block[1].bn, graph, slope)
             else:
-                x_max = ops.segment_max(self.s_mlp_max(ops.edge_diff(x, graph)), graph)
+                x_max = self._centralized_deep(x, graph)
         else:
             blocks = list(self.s_mlp_max)
             tail = blocks[-1]
@@ -70,6 +70,28 @@ class DeltaConv(torch.nn.Module):
             for block in list(self.v_mlp)[1:]:
                 v = block(v)
         return x, v
+
+    def _centralized_deep(self, x, graph):
+        """scatter_max(s_mlp_max(x_j - x_i)) for an edge MLP of depth >= 2 (deltaconv.py:50-52; train_shapenet.py builds depth 2).
+        The [N*k, C] tensors between the blocks have to exist, the ones around them do not: the first block's activation is
+        written straight from the coordinates with statistics from the offsets' moments (ops.central_edge_act), the last block's
+        BatchNorm + activation are folded into the max (ops.linear_bn_act_segmax).  Anything those nodes do not cover (a
+        Linear bias, another activation, wide inputs, a gradient w.r.t. x) takes the plain sequence."""
+        blocks = list(self.s_mlp_max)
+        head, tail = blocks[0], blocks[-1]
+        head_slope, tail_slope = _slope_of(head[2]), _slope_of(tail[2])
+        fuse_head = (len(blocks) >= 2 and head_slope is not None and head[0].bias is None and not x.requires_grad
+                     and ops.centralized_max_supported(x.size(1), graph.k))
+        fuse_tail = len(blocks) >= 2 and ops.segmax_fusable(tail[0], tail_slope)
+        if fuse_head:
+            h = ops.central_edge_act(x, head[0].weight, head[1].bn, graph, head_slope)
+        else:
+            h = head(ops.edge_diff(x, graph))
+        for block in blocks[1:-1] if fuse_tail else blocks[1:]:
+            h = block(h)
+        if fuse_tail:
+            return ops.linear_bn_act_segmax(h, tail[0].weight, tail[1].bn, tail_slope, graph)
+        return ops.segment_max(h, graph)
 
     def _forward_generic(self, x, v, grad, div, edge_index):
         """deltaconv.py:44-70 literally: gather, MLP, scatter-reduce; operators through `@`.  The Linear / BatchNorm /

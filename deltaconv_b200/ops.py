@@ -1169,6 +1169,123 @@ def centralized_max(x, weight, bn, graph, slope):
     return _CentralizedMax.apply(x, weight, bn.weight, bn.bias, bn, graph, float(slope))
 
 
+class _CentralEdgeAct(torch.autograd.Function):
+    """First block of a centralized edge MLP of depth >= 2 (deltaconv.py:50-52 with mlp_depth = 2, the ShapeNet configuration):
+    h [N*k, Cout] = act(BatchNorm(Linear(x_j - x_i))) written ONCE from the coordinates.  Statistics over the E edge rows from
+    the moments of the offsets (dc_central_stats); backward from the dense gradient of h in one pass over it
+    (dc_central_edge_bwd).  No gradient w.r.t. x: callers that need it take the unfused sequence."""
+
+    @staticmethod
+    def forward(ctx, x, weight, gamma, beta, bn, graph, slope):
+        x, ldx = _mat(x, 'x')
+        weight = _f32(weight, 'weight').contiguous()
+        N, k, Cin, Cout = graph.N, graph.k, x.size(1), weight.size(0)
+        dev = x.device
+        use_batch = bn.training or not bn.track_running_stats or bn.running_mean is None
+        moments = None
+        if use_batch:
+            nbytes = query('dc_central_ws_bytes', N, k, Cin, Cout)
+            ws = workspace(nbytes, dev)
+            moments = torch.empty(20, dtype=torch.float64, device=dev)
+            mean = torch.empty(Cout, dtype=_F32, device=dev)
+            invstd = torch.empty(Cout, dtype=_F32, device=dev)
+            update, momentum, nbt = _running_update(bn)
+            call('dc_central_stats', ptr(graph.idx), N, k, Cin, Cout, ptr(x), ldx, ptr(weight), float(bn.eps), float(momentum),
+                 ptr(moments), ptr(mean), ptr(invstd), ptr(bn.running_mean) if update else None,
+                 ptr(bn.running_var) if update else None, nbt, ptr(ws), nbytes)
+        else:
+            mean = bn.running_mean.contiguous()
+            invstd = _running_invstd(bn)
+        out = torch.empty(N * k, Cout, dtype=_F32, device=dev)
+        call('dc_central_edge_fwd', ptr(graph.idx), N, k, Cin, Cout, ptr(x), ldx, ptr(weight), ptr(gamma), ptr(beta), ptr(mean), ptr(invstd),
+             float(slope), ptr(out))
+        ctx.graph, ctx.slope, ctx.use_batch = graph, slope, use_batch
+        ctx.save_for_backward(x, weight, gamma, beta, mean, invstd, moments)
+        return out
+
+    @staticmethod
+    def backward(ctx, dh):
+        if ctx.needs_input_grad[0]:
+            raise _lib.DeltaConvLibraryError("central_edge_act: no gradient w.r.t. the point features on this path")
+        x, weight, gamma, beta, mean, invstd, moments = ctx.saved_tensors
+        g = ctx.graph
+        x, ldx = _mat(x)
+        dh, ldd = _mat(dh, 'grad_output')
+        N, k, Cin, Cout = g.N, g.k, x.size(1), weight.size(0)
+        dev = x.device
+        nbytes = query('dc_central_ws_bytes', N, k, Cin, Cout)
+        ws = workspace(nbytes, dev)
+        dW = torch.empty(Cout, Cin, dtype=_F32, device=dev)
+        dgamma = torch.empty(Cout, dtype=_F32, device=dev)
+        dbeta = torch.empty(Cout, dtype=_F32, device=dev)
+        call('dc_central_edge_bwd', ptr(g.idx), N, k, Cin, Cout, ptr(x), ldx, ptr(weight), ptr(gamma), ptr(beta), ptr(mean), ptr(invstd),
+             ptr(moments), float(ctx.slope), int(ctx.use_batch), ptr(dh), ldd, ptr(dW), ptr(dgamma), ptr(dbeta), ptr(ws), nbytes)
+        return (None, dW, dgamma if gamma is not None else None, dbeta if beta is not None else None, None, None, None)
+
+
+def central_edge_act(x, weight, bn, graph, slope):
+    return _CentralEdgeAct.apply(x, weight, bn.weight, bn.bias, bn, graph, float(slope))
+
+
+class _LinearBNActSegMax(torch.autograd.Function):
+    """max over each point's k edge rows of act(BatchNorm1d(h @ W.T)) — the LAST block of a centralized edge MLP and the
+    scatter-max of deltaconv.py:52 as one node: the GEMM writes the pre-activation [N*k, C], the statistics pass reads it, the
+    max applies BatchNorm + LeakyReLU to the extreme it selects (dc_segmax_bn_fwd).  Backward: the gradient of the activation
+    is non-zero at one edge per (point, channel), so the BatchNorm sums run over the points and the [N*k, C] gradient of the
+    pre-activation is written directly (dc_segmax_bn_bwd) — the dense gradient of the activation is never formed."""
+
+    @staticmethod
+    def forward(ctx, h, weight, gamma, beta, bn, slope, graph):
+        h, ldh = _mat(h, 'input')
+        weight, ldw = _mat(weight, 'weight')
+        if h.size(1) != weight.size(1):
+            raise _lib.DeltaConvLibraryError(f"Linear: input has {h.size(1)} features, weight expects {weight.size(1)}")
+        M, K, C = h.size(0), h.size(1), weight.size(0)
+        N, k = graph.N, graph.k
+        if M != N * k:
+            raise _lib.DeltaConvLibraryError(f"segment-max: {M} edge rows for a graph with {N} x {k} slots")
+        dev = h.device
+        y = torch.empty(M, C, dtype=_F32, device=dev)
+        ws, nb = _gemm_ws(M, C, K, dev)
+        call('dc_linear_fwd', ptr(h), ldh, ptr(weight), ldw, None, M, K, C, ptr(y), C, ptr(ws), nb)
+        mean, invstd, batch_stats = _bn_moments(bn, y, C, M, C, 0)
+        out = torch.empty(N, C, dtype=_F32, device=dev)
+        arg = torch.empty(N, C, dtype=torch.uint8, device=dev)
+        call('dc_segmax_bn_fwd', ptr(y), N, k, C, ptr(graph.idx), ptr(mean), ptr(invstd), ptr(gamma), ptr(beta), float(slope),
+             ptr(out), C, ptr(arg))
+        ctx.save_for_backward(h, weight, y, mean, invstd, gamma, beta, arg)
+        ctx.slope, ctx.batch_stats, ctx.graph = slope, batch_stats, graph
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        h, weight, y, mean, invstd, gamma, beta, arg = ctx.saved_tensors
+        g = ctx.graph
+        h, ldh = _mat(h)
+        weight, ldw = _mat(weight)
+        dout, ldd = _mat(dout, 'grad_output')
+        M, K, C = h.size(0), h.size(1), weight.size(0)
+        dev = h.device
+        dgamma = torch.empty(C, dtype=_F32, device=dev)
+        dbeta = torch.empty(C, dtype=_F32, device=dev)
+        dy = torch.empty(M, C, dtype=_F32, device=dev)
+        nb = query('dc_colreduce_ws_bytes', C)
+        ws = workspace(nb, dev)
+        call('dc_segmax_bn_bwd', ptr(y), g.N, g.k, C, ptr(arg), ptr(dout), ldd, ptr(mean), ptr(invstd), ptr(gamma), ptr(beta),
+             float(ctx.slope), int(ctx.batch_stats), ptr(dgamma), ptr(dbeta), ptr(dy), ptr(ws), nb)
+        dh, dw = _linear_backward_pair(dy, C, weight, ldw, h, ldh, M, K, C, ctx.needs_input_grad[0], ctx.needs_input_grad[1])
+        return (dh, dw, dgamma if gamma is not None else None, dbeta if beta is not None else None, None, None, None)
+
+
+def linear_bn_act_segmax(h, weight, bn, slope, graph):
+    return _LinearBNActSegMax.apply(h, weight, bn.weight, bn.bias, bn, float(slope), graph)
+
+
+def segmax_fusable(lin, slope):
+    """The last block of a centralized edge MLP can run as the fused node (same conditions as gathermax_fusable)."""
+    return lin.bias is None and slope is not None and slope > 0 and lin.out_features % 4 == 0
+
+
 class _Pool(torch.autograd.Function):
     """mode 'max' | 'mean' | 'maxmean' ([max | mean] side by side, deltanet_classification.py:46-49)."""
 

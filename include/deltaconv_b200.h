@@ -190,6 +190,17 @@ int dc_edge_diff_bwd(const int32_t* in_ptr, const int32_t* in_edge, int N, int k
 int dc_segmax_fwd(const float* in, int N, int k, int C, const int32_t* idx_or_null, float* out, int64_t ldo,
                   uint8_t* arg, void* stream);
 int dc_segmax_bwd(const float* dout, int64_t ldd, int N, int k, int C, const uint8_t* arg, float* din, void* stream);
+/* The last block of an edge MLP folded into the max (deltaconv.py:50-52 with depth >= 2): y [N*k,C] are the pre-activations of
+ * that block, out = max over each point's k rows of leaky_relu(BatchNorm1d(y)), selected through the per-channel extreme of y
+ * like dc_gathermax_bn_fwd; the activation is never written.  Backward: dout [N,C] -> dy [N*k,C], d_gamma, d_beta, with the
+ * BatchNorm sums taken over the arg-max rows only (training != 0: batch statistics over N*k rows).  Float4 layout only;
+ * workspace dc_colreduce_ws_bytes(C). */
+int dc_segmax_bn_fwd(const float* y, int N, int k, int C, const int32_t* idx_or_null, const float* mean, const float* invstd,
+                     const float* gamma_or_null, const float* beta_or_null, float slope, float* out, int64_t ldo, uint8_t* arg,
+                     void* stream);
+int dc_segmax_bn_bwd(const float* y, int N, int k, int C, const uint8_t* arg, const float* dout, int64_t ldd, const float* mean,
+                     const float* invstd, const float* gamma_or_null, const float* beta_or_null, float slope, int training,
+                     float* d_gamma, float* d_beta, float* dy, void* ws, size_t ws_bytes, void* stream);
 
 /* Fused form of the same three lines for Cin <= dc_central_max_cin() (4), k <= 64 and a depth-1 edge MLP:
  * scatter_max(LeakyReLU(BatchNorm(Linear(x[col]-x[row]))), row) without any [E,*] temporary.  dc_central_stats gives the
@@ -209,6 +220,17 @@ int dc_central_bwd(const int32_t* idx, const int32_t* in_ptr_or_null, const int3
                    const float* mean, const float* invstd, const double* moments, float slope, int training,
                    const uint8_t* arg, const float* dout, int64_t ldd, float* dW, float* dgamma, float* dbeta,
                    float* dx_or_null, int64_t ld_dx, void* ws, size_t ws_bytes, void* stream);
+/* Depth >= 2 edge MLPs (train_shapenet.py:79-89 builds DeltaNetSegmentation with mlp_depth = 2): the FIRST block's activation
+ * h [N*k,Cout] = LeakyReLU(BatchNorm(Linear(x[col]-x[row]))) written once from the coordinates (statistics from dc_central_stats,
+ * no [E,Cin] offsets, no pre-activation tensor), and its backward from the dense gradient dh [N*k,Cout] in one pass over dh
+ * (dW, dgamma, dbeta; no d/dx).  Same limits and workspace as dc_central_fwd / dc_central_bwd. */
+int dc_central_edge_fwd(const int32_t* idx, int N, int k, int Cin, int Cout, const float* x, int64_t ldx, const float* W,
+                        const float* gamma_or_null, const float* beta_or_null, const float* mean, const float* invstd, float slope,
+                        float* out, void* stream);
+int dc_central_edge_bwd(const int32_t* idx, int N, int k, int Cin, int Cout, const float* x, int64_t ldx, const float* W,
+                        const float* gamma_or_null, const float* beta_or_null, const float* mean, const float* invstd,
+                        const double* moments, float slope, int training, const float* dh, int64_t ldd, float* dW, float* dgamma,
+                        float* dbeta, void* ws, size_t ws_bytes, void* stream);
 
 /* ---- BatchNorm1d wrapper + LeakyReLU (nonlin.py:11-35, mlp.py:7-11) -------------------------- */
 

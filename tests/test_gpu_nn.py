@@ -716,3 +716,110 @@ def test_fused_gathermax_over_batchnorm_activation_matches_the_two_pass_form(tra
     assert (bn.weight < 0).any() and (bn.weight > 0).any()
     for a, b in zip(*results):
         assert torch.equal(a, b)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('train', [True, False])
+def test_fused_segmax_over_batchnorm_activation_matches_the_two_pass_form(train):
+    """ops.linear_bn_act_segmax (last block of a deep centralized edge MLP folded into the max over each point's k edge rows;
+    backward writes the gradient of the pre-activation directly, the BatchNorm sums run over the arg-max rows only) against
+    Linear -> BatchNorm -> LeakyReLU -> segment-max as separate kernels.  Values and routing are bitwise the same; the gradients
+    agree to rounding (the sums are formed over N rows instead of N*k rows with zeros: another summation tree)."""
+    D = dc()
+    from deltaconv_b200 import ops
+    torch.manual_seed(5)
+    k = 12
+    d = D.utils.synthetic_batch(3, 0, config=12, sizes=[300, 700, 8])          # the 8-point cloud has padded (invalid) slots
+    graph = ops.knn(d.pos.to(DEV), k, d.batch.to(DEV), num_clouds=3)
+    N, K, C = d.pos.size(0), 24, 32
+    lin = D.nn.Linear(K, C, bias=False).to(DEV)
+    bn = torch.nn.BatchNorm1d(C).to(DEV)
+    with torch.no_grad():
+        bn.weight.copy_(torch.randn(C))
+        bn.bias.copy_(0.3 * torch.randn(C))
+        bn.running_mean.copy_(0.2 * torch.randn(C)); bn.running_var.copy_(0.5 + torch.rand(C))
+    h0 = torch.randn(N * k, K, device=DEV)
+    g0 = torch.randn(N, C, device=DEV)
+    results = []
+    for fused in (False, True):
+        bn_i = copy.deepcopy(bn).train(train)
+        lin_i = copy.deepcopy(lin)
+        h = h0.clone().requires_grad_(True)
+        if fused:
+            out = ops.linear_bn_act_segmax(h, lin_i.weight, bn_i, 0.2, graph)
+        else:
+            out = ops.segment_max(ops.bn_act(ops.linear(h, lin_i.weight), bn_i, 0.2), graph)
+        (out * g0).sum().backward()
+        results.append((out.detach(), bn_i.running_mean.clone(), h.grad, lin_i.weight.grad, bn_i.weight.grad, bn_i.bias.grad))
+    assert (bn.weight < 0).any() and (bn.weight > 0).any()
+    assert torch.equal(results[0][0], results[1][0]) and torch.equal(results[0][1], results[1][1])
+    for name, a, b in zip(('dh', 'dW', 'dgamma', 'dbeta'), results[0][2:], results[1][2:]):
+        err = rel_err(b, a)
+        report(f'fused_segmax_bn.train{int(train)}.{name}_vs_two_pass', err)
+        assert err < 2e-5, (name, err)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('train', [True, False])
+@pytest.mark.parametrize('depth', [2, 3])
+def test_deep_centralized_edge_mlp_matches_the_plain_sequence_and_the_oracle(train, depth):
+    """DeltaConv(centralized=True, depth >= 2) — the ShapeNet configuration's first layer.  The scheduled form (first block
+    written from the coordinates with moment statistics, last block folded into the max) against the plain sequence
+    edge_diff -> MLP -> segment_max on the same parameters: output, running statistics and every parameter gradient; and the
+    output against the fp64 oracle's edge MLP."""
+    D = dc()
+    from deltaconv_b200 import ops
+    torch.manual_seed(6)
+    k = 10
+    d = D.utils.synthetic_batch(3, 0, config=12, sizes=[500, 260, 7])
+    pos = d.pos.to(DEV)
+    graph = ops.knn(pos, k, d.batch.to(DEV), num_clouds=3)
+    conv = D.nn.DeltaConv(3, 32, depth=depth, centralized=True).to(DEV)
+    with torch.no_grad():
+        for m in conv.s_mlp_max.modules():
+            if isinstance(m, torch.nn.BatchNorm1d):
+                m.weight.copy_(torch.randn_like(m.weight)); m.bias.copy_(0.3 * torch.randn_like(m.bias))
+                m.running_mean.copy_(0.1 * torch.randn_like(m.running_mean)); m.running_var.copy_(0.5 + torch.rand_like(m.running_var))
+    g0 = torch.randn(pos.size(0), 32, device=DEV)
+    results = []
+    for fused in (False, True):
+        c = copy.deepcopy(conv).train(train)
+        if fused:
+            out = c._centralized_deep(pos, graph)
+        else:
+            out = ops.segment_max(c.s_mlp_max(ops.edge_diff(pos, graph)), graph)
+        (out * g0).sum().backward()
+        params = dict(c.s_mlp_max.named_parameters())
+        stats = {n: b.clone() for n, b in c.s_mlp_max.named_buffers() if 'running' in n}
+        results.append((out.detach(), {n: p.grad for n, p in params.items()}, stats))
+    (out_a, grads_a, stats_a), (out_b, grads_b, stats_b) = results
+    err = rel_err(out_b, out_a)
+    report(f'deep_centralized.depth{depth}.train{int(train)}.out_vs_plain', err)
+    assert err < 1e-5, err
+    for n in stats_a:
+        assert rel_err(stats_b[n], stats_a[n]) < 1e-5, n
+    for n in grads_a:
+        assert grads_b[n] is not None, n
+        e = rel_err(grads_b[n], grads_a[n])
+        report(f'deep_centralized.depth{depth}.train{int(train)}.d{n}', e)
+        assert e < 2e-4, (n, e)            # arg-max ties / kinks between two fp32 evaluations of the first block
+    # fp64 restatement of deltaconv.py:50-52 (torch, CPU)
+    ref = copy.deepcopy(conv).train(train).cpu().double()
+    idx = graph.idx.cpu().long()
+    N = pos.size(0)
+    valid = (idx >= 0) & (idx < N)
+    nb = torch.where(valid, idx, torch.arange(N)[:, None].expand_as(idx))
+    p64 = pos.cpu().double()
+    t = (p64[nb] - p64[:, None, :]).reshape(N * k, 3)
+    for block in ref.s_mlp_max:
+        lin, bnw, act = block[0], block[1].bn, block[2]
+        t = t @ lin.weight.T
+        if train:
+            mu, var = t.mean(0), t.var(0, unbiased=False)
+        else:
+            mu, var = bnw.running_mean, bnw.running_var
+        t = torch.nn.functional.leaky_relu((t - mu) / torch.sqrt(var + bnw.eps) * bnw.weight + bnw.bias, act.negative_slope)
+    t = t.reshape(N, k, -1).masked_fill(~valid[:, :, None], float('-inf')).amax(1)
+    err = rel_err(out_b.cpu().double(), t)
+    report(f'deep_centralized.depth{depth}.train{int(train)}.out_vs_fp64', err)
+    assert err < 2e-5, err
