@@ -291,64 +291,72 @@ __global__ void __launch_bounds__(256) central_edge_fwd_kernel(const int* __rest
 // Backward of that block from the DENSE gradient dh [E,Cout] of its activation: the same three sums as CentralBwdVal, taken
 // over all E edge rows in one pass (dh is read once; offsets and pre-activation are recomputed), and the same finalize.
 // Replaces the BatchNorm backward (two reads of y and dh, one write) and the weight-gradient product over E rows.
+// A warp owns a point (its k offsets live in the lanes, as in the forward kernel), a lane owns a channel: every load of dh is
+// 128 contiguous bytes, six edge rows are in flight per warp, a point's k terms are summed in fp32 and the points of a warp in
+// fp64.  partial[block][v][c] has the layout of the column reductions (fixed grid and order: deterministic).
 template <int CIN>
-struct CentralCols { float w[4][CIN]; float mean[4], invstd[4], gamma[4], beta[4]; };
-
-template <int CIN>
-struct CentralDenseBwdVal {
-    const int* idx; int N, k, Cout;
-    const float* x; long long ldx; const float* W; const float* gamma; const float* beta; const float* mean; const float* invstd;
-    float slope; const float* dh; long long ldd;
-    __device__ __forceinline__ void offsets(long long r, float (&d)[CIN]) const {
-        const int i = (int)r / k;
-        int j = __ldg(idx + r);
-        if ((unsigned)j >= (unsigned)N) j = i;
+__global__ void __launch_bounds__(256) central_dense_bwd_kernel(const int* __restrict__ idx, int N, int k, int Cout, const float* __restrict__ x,
+                                                                long long ldx, const float* __restrict__ W, const float* __restrict__ gamma,
+                                                                const float* __restrict__ beta, const float* __restrict__ mean,
+                                                                const float* __restrict__ invstd, float slope, const float* __restrict__ dh,
+                                                                long long ldd, double* __restrict__ partial) {
+    constexpr int NV = 2 + CIN;
+    __shared__ double sh[8][NV][32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int first = blockIdx.x * 8 + warp, stride = gridDim.x * 8;
+    for (int c0 = 0; c0 < Cout; c0 += 32) {
+        const int c = c0 + lane;
+        const bool ok = c < Cout;
+        float w[CIN];
 #pragma unroll
-        for (int q = 0; q < CIN; ++q) d[q] = __ldg(x + (size_t)j * ldx + q) - __ldg(x + (size_t)i * ldx + q);
-    }
-    __device__ void operator()(long long r, int c, float (&o)[2 + CIN]) const {
-        float d[CIN], t = 0.f;
-        offsets(r, d);
+        for (int q = 0; q < CIN; ++q) w[q] = ok ? __ldg(W + (size_t)c * CIN + q) : 0.f;
+        const float mu = ok ? __ldg(mean + c) : 0.f, is = ok ? __ldg(invstd + c) : 0.f;
+        const float g = (ok && gamma) ? __ldg(gamma + c) : 1.f, b = (ok && beta) ? __ldg(beta + c) : 0.f;
+        double acc[NV];
 #pragma unroll
-        for (int q = 0; q < CIN; ++q) t = fmaf(__ldg(W + (size_t)c * CIN + q), d[q], t);
-        const float xh = (t - __ldg(mean + c)) * __ldg(invstd + c);
-        const float g = gamma ? __ldg(gamma + c) : 1.f, b = beta ? __ldg(beta + c) : 0.f;
-        const float z = g * xh + b;
-        const float dz = __ldg(dh + r * ldd + c) * (z > 0.f ? 1.f : slope);
-        o[0] = dz; o[1] = dz * xh;
+        for (int v = 0; v < NV; ++v) acc[v] = 0.0;
+        for (int i = first; i < N; i += stride) {
+            float d[2][CIN_MAX];
+            load_offsets(idx, N, k, CIN, x, ldx, i, lane, d);
+            const float* row = dh + (size_t)i * k * ldd + (ok ? c : 0);
+            float s[NV];
 #pragma unroll
-        for (int q = 0; q < CIN; ++q) o[2 + q] = dz * d[q];
-    }
-    __device__ CentralCols<CIN> columns(int c) const {
-        CentralCols<CIN> kc;
+            for (int v = 0; v < NV; ++v) s[v] = 0.f;
+            for (int e0 = 0; e0 < k; e0 += 6) {
+                float dv[6];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
+                for (int u = 0; u < 6; ++u) dv[u] = (ok && e0 + u < k) ? __ldcs(row + (size_t)(e0 + u) * ldd) : 0.f;
 #pragma unroll
-            for (int q = 0; q < CIN; ++q) kc.w[u][q] = __ldg(W + (size_t)(c + u) * CIN + q);
-            kc.mean[u] = __ldg(mean + c + u); kc.invstd[u] = __ldg(invstd + c + u);
-            kc.gamma[u] = gamma ? __ldg(gamma + c + u) : 1.f; kc.beta[u] = beta ? __ldg(beta + c + u) : 0.f;
+                for (int u = 0; u < 6; ++u) {
+                    const int e = e0 + u;
+                    if (e < k) {                                       // warp-uniform
+                        float de[CIN], t = 0.f;
+#pragma unroll
+                        for (int q = 0; q < CIN; ++q) { de[q] = __shfl_sync(FULL, e < 32 ? d[0][q] : d[1][q], e & 31); t = fmaf(w[q], de[q], t); }
+                        const float xh = (t - mu) * is;
+                        const float z = g * xh + b;
+                        const float dz = dv[u] * (z > 0.f ? 1.f : slope);
+                        s[0] += dz; s[1] = fmaf(dz, xh, s[1]);
+#pragma unroll
+                        for (int q = 0; q < CIN; ++q) s[2 + q] = fmaf(dz, de[q], s[2 + q]);
+                    }
+                }
+            }
+#pragma unroll
+            for (int v = 0; v < NV; ++v) acc[v] += (double)s[v];
         }
-        return kc;
-    }
-    __device__ void quad(long long r, int c, const CentralCols<CIN>& kc, float (&o)[4][2 + CIN]) const {
-        float d[CIN];
-        offsets(r, d);
-        const float4 dv = __ldg(reinterpret_cast<const float4*>(dh + r * ldd + c));
-        const float dd[4] = {dv.x, dv.y, dv.z, dv.w};
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            float t = 0.f;
+        for (int v = 0; v < NV; ++v) sh[warp][v][lane] = acc[v];
+        __syncthreads();
+        if (warp < NV && ok) {                                         // warp v adds the 8 warp sums of value v in a fixed order
+            double t = 0.0;
 #pragma unroll
-            for (int q = 0; q < CIN; ++q) t = fmaf(kc.w[u][q], d[q], t);
-            const float xh = (t - kc.mean[u]) * kc.invstd[u];
-            const float z = kc.gamma[u] * xh + kc.beta[u];
-            const float dz = dd[u] * (z > 0.f ? 1.f : slope);
-            o[u][0] = dz; o[u][1] = dz * xh;
-#pragma unroll
-            for (int q = 0; q < CIN; ++q) o[u][2 + q] = dz * d[q];
+            for (int q = 0; q < 8; ++q) t += sh[q][warp][lane];
+            partial[((size_t)blockIdx.x * NV + warp) * Cout + c] = t;
         }
+        __syncthreads();
     }
-};
+}
 
 int moments_chunks(long long E) {
     long long g = (E + 255) / 256, cap = (long long)dc_sm_count() * 4;
@@ -469,16 +477,15 @@ extern "C" int dc_central_edge_bwd(const int32_t* idx, int N, int k, int Cin, in
     if (N <= 0 || Cout <= 0) return DC_OK;
     cudaStream_t st = (cudaStream_t)stream;
     double* partial = (double*)ws;
-    const long long E = (long long)N * k;
-    const bool vec4_ok = Cout % 4 == 0 && ldd % 4 == 0 && ((uintptr_t)dh & 15) == 0;
+    int chunks = dc_ceil_div(N, 8);                            // a warp per point, 8 warps per CTA, up to 8 CTAs per SM
+    if (chunks > RED_MAX_CHUNKS) chunks = RED_MAX_CHUNKS;
 #define DC_CENTRAL_CASE(CIN)                                                                                                      \
-    case CIN: {                                                                                                                   \
-        CentralDenseBwdVal<CIN> f = {idx, N, k, Cout, x, ldx, W, gamma_or_null, beta_or_null, mean, invstd, slope, dh, ldd};     \
-        const int chunks = col_reduce_launch<2 + CIN>(f, E, Cout, vec4_ok, partial, st);                                          \
+    case CIN:                                                                                                                     \
+        central_dense_bwd_kernel<CIN><<<chunks, 256, 0, st>>>(idx, N, k, Cout, x, ldx, W, gamma_or_null, beta_or_null, mean, invstd, slope,  \
+                                                              dh, ldd, partial);                                                 \
         central_bwd_finalize_kernel<CIN><<<dc_ceil_div(Cout, FIN_COLS), FIN_T, 0, st>>>(partial, chunks, Cout, W, gamma_or_null, mean, invstd,  \
                                                                                  moments, training, dW, dgamma, dbeta);          \
-        break;                                                                                                                    \
-    }
+        break;
     switch (Cin) { DC_CENTRAL_CASE(1) DC_CENTRAL_CASE(2) DC_CENTRAL_CASE(3) DC_CENTRAL_CASE(4) }
 #undef DC_CENTRAL_CASE
     return dc_check_launch_n("dc_central_edge_bwd", 2);

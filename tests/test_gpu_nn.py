@@ -191,6 +191,8 @@ def test_gather_max_pool_broadcast_edge_ops():
     (bc * gb.to(DEV)).sum().backward()
     assert torch.equal(bc.detach().cpu(), s0[d.batch])
     assert rel_err(s.grad.cpu(), torch.zeros(3, 11).index_add(0, d.batch, gb)) < 1e-5
+    s4 = torch.randn(3, 24)                                 # the float4 kernel (C % 4 == 0)
+    assert torch.equal(dc().ops.broadcast_rows(s4.to(DEV), batch, N).cpu(), s4[d.batch])
 
 
 # ----------------------------------------------------------------------------------------------
