@@ -80,6 +80,7 @@ _SIGNATURES = {
     'dc_adam_step': [_P, _P, _P, _P, _L, _P, _P, _F, _F, _F, _F, _F, _P],
     'dc_add_rows': [_P, _L, _P, _L, _L, _I, _P, _L, _P],
     'dc_bcast_rows': [_P, _L, _P, _I, _I, _I, _P, _L, _P],
+    'dc_bcast_rows_add': [_P, _L, _P, _I, _I, _I, _P, _L, _P],
     'dc_set_gemm_mode': [_I],
     'dc_get_gemm_mode': [],
     'dc_set_gemm_no_ts': [_I],

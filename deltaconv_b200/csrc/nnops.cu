@@ -1085,6 +1085,27 @@ __global__ void __launch_bounds__(256) bcast_rows_vec4_kernel(const float* __res
     }
 }
 
+// out[i, :] += src[cloud(i), :] — the per-cloud part of a Linear whose input is [broadcast per-cloud features | per-point
+// features]: the product with the broadcast block is formed on the B cloud rows and added here.
+__global__ void __launch_bounds__(256) bcast_rows_add_vec4_kernel(const float* __restrict__ src, long long lds, const int* __restrict__ cloud_ptr,
+                                                                  int B, int N, int C4, float* __restrict__ out, long long ldo) {
+    for (RowCol rc(C4); rc.r < N; rc.next()) {
+        const int i = (int)rc.r, c = rc.c * 4;
+        const int b = cloud_of(cloud_ptr, B, i);
+        float4* o = reinterpret_cast<float4*>(out + (size_t)i * ldo + c);
+        const float4 a = *o, s = __ldg(reinterpret_cast<const float4*>(src + (size_t)b * lds + c));
+        *o = make_float4(a.x + s.x, a.y + s.y, a.z + s.z, a.w + s.w);
+    }
+}
+__global__ void bcast_rows_add_kernel(const float* __restrict__ src, long long lds, const int* __restrict__ cloud_ptr, int B, int N, int C,
+                                      float* __restrict__ out, long long ldo) {
+    const long long total = (long long)N * C;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+        int i = (int)(t / C), c = (int)(t - (long long)i * C);
+        out[(size_t)i * ldo + c] += __ldg(src + (size_t)cloud_of(cloud_ptr, B, i) * lds + c);
+    }
+}
+
 template <class... P>
 bool all_aligned16(P... ptrs) {
     const void* a[] = {(const void*)ptrs...};
@@ -1436,4 +1457,15 @@ extern "C" int dc_bcast_rows(const float* src, int64_t lds, const int32_t* cloud
     else
         bcast_rows_kernel<<<elementwise_grid((long long)N * C), 256, 0, (cudaStream_t)stream>>>(src, lds, cloud_ptr, B, N, C, out, ldo);
     return dc_check_launch("dc_bcast_rows");
+}
+
+// out[i, :] += src[cloud of i, :]   (out [N,C] with row pitch ldo, src [B,C] with row pitch lds)
+extern "C" int dc_bcast_rows_add(const float* src, int64_t lds, const int32_t* cloud_ptr, int B, int N, int C, float* out, int64_t ldo,
+                                 void* stream) {
+    if (N <= 0 || C <= 0) return DC_OK;
+    if (C % 4 == 0 && lds % 4 == 0 && ldo % 4 == 0 && all_aligned16(src, out))
+        bcast_rows_add_vec4_kernel<<<elementwise_grid((long long)N * C / 4), 256, 0, (cudaStream_t)stream>>>(src, lds, cloud_ptr, B, N, C / 4, out, ldo);
+    else
+        bcast_rows_add_kernel<<<elementwise_grid((long long)N * C), 256, 0, (cudaStream_t)stream>>>(src, lds, cloud_ptr, B, N, C, out, ldo);
+    return dc_check_launch("dc_bcast_rows_add");
 }

@@ -1443,6 +1443,87 @@ class _BcastRows(torch.autograd.Function):
         return dsrc * counts[:, None], None, None, None, None
 
 
+class _LinearBcastBNAct(torch.autograd.Function):
+    """act(BatchNorm1d([g[batch] | x] @ W.T)) — the first block of the segmentation head (deltanet_segmentation.py:61-66: the
+    pooled embedding and the category features are broadcast to every point and concatenated with the per-point features)
+    WITHOUT the broadcast: the product splits into x @ W_x.T over the N points plus (g @ W_g.T)[batch] over the B clouds, so
+    the [N, Kg] broadcast block is never written, never multiplied and never receives a gradient of its own (Kg = 1088 of the
+    1536 input columns in the ShapeNet configuration).  Weight layout as in the reference: columns [0,Kg) multiply g."""
+
+    @staticmethod
+    def forward(ctx, x, g, weight, gamma, beta, bn, slope, cloud_ptr, B):
+        x, ldx = _mat(x, 'input')
+        g, ldg = _mat(g, 'per-cloud input')
+        _f32(weight, 'weight')
+        N, Kx, Kg, C = x.size(0), x.size(1), g.size(1), weight.size(0)
+        if weight.dim() != 2 or weight.size(1) != Kg + Kx:
+            raise _lib.DeltaConvLibraryError(f"Linear: input has {Kg} + {Kx} features, weight expects {weight.size(-1)}")
+        if g.size(0) != B:
+            raise _lib.DeltaConvLibraryError(f"broadcast: {g.size(0)} per-cloud rows for {B} clouds")
+        weight = weight.contiguous()
+        Wg, ldw = _mat(weight[:, :Kg])
+        Wx, _ = _mat(weight[:, Kg:])
+        dev = x.device
+        yg = torch.empty(B, C, dtype=_F32, device=dev)
+        ws, nb = _gemm_ws(B, C, Kg, dev)
+        call('dc_linear_fwd', ptr(g), ldg, ptr(Wg), ldw, None, B, Kg, C, ptr(yg), C, ptr(ws), nb)
+        y = torch.empty(N, C, dtype=_F32, device=dev)
+        ws, nb = _gemm_ws(N, C, Kx, dev)
+        call('dc_linear_fwd', ptr(x), ldx, ptr(Wx), ldw, None, N, Kx, C, ptr(y), C, ptr(ws), nb)
+        call('dc_bcast_rows_add', ptr(yg), C, ptr(cloud_ptr), B, N, C, ptr(y), C)
+        mean, invstd, batch_stats = _bn_moments(bn, y, C, N, C, 0)
+        out = torch.empty(N, C, dtype=_F32, device=dev)
+        call('dc_bn_act_fwd', ptr(y), C, N, C, ptr(mean), ptr(invstd), ptr(gamma), ptr(beta), float(slope), None, 0, ptr(out), C)
+        ctx.save_for_backward(x, g, weight, y, mean, invstd, gamma, beta, cloud_ptr)
+        ctx.slope, ctx.batch_stats, ctx.B = slope, batch_stats, B
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        x, g, weight, y, mean, invstd, gamma, beta, cloud_ptr = ctx.saved_tensors
+        x, ldx = _mat(x)
+        g, ldg = _mat(g)
+        dout, ldd = _mat(dout, 'grad_output')
+        N, Kx, Kg, C, B = x.size(0), x.size(1), g.size(1), weight.size(0), ctx.B
+        Wg, ldw = _mat(weight[:, :Kg])
+        Wx, _ = _mat(weight[:, Kg:])
+        dev = x.device
+        dgamma = torch.empty(C, dtype=_F32, device=dev)
+        dbeta = torch.empty(C, dtype=_F32, device=dev)
+        dy = torch.empty(N, C, dtype=_F32, device=dev)
+        nb = query('dc_colreduce_ws_bytes', C)
+        ws = workspace(nb, dev)
+        call('dc_bn_act_bwd', ptr(y), C, ptr(dout), ldd, N, C, ptr(mean), ptr(invstd), ptr(gamma), ptr(beta), float(ctx.slope),
+             int(ctx.batch_stats), ptr(dgamma), ptr(dbeta), ptr(dy), C, ptr(ws), nb)
+        # gradient of the per-cloud rows: column sums of dy over each cloud (the mean pool's kernel, times the cloud sizes)
+        dyg = torch.empty(B, C, dtype=_F32, device=dev)
+        call('dc_pool_fwd', ptr(dy), C, ptr(cloud_ptr), B, C, None, 0, ptr(dyg), C, None)
+        dyg = dyg * (cloud_ptr[1:] - cloud_ptr[:-1]).to(_F32)[:, None]
+        want_x, want_g, want_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1], ctx.needs_input_grad[2]
+        dx = dg = dw = None
+        if want_w:
+            dw = torch.empty(C, Kg + Kx, dtype=_F32, device=dev)
+            ws_w, nb_w = _gemm_ws(C, Kx, N, dev)
+            call('dc_linear_bwd_weight', ptr(dy), C, ptr(x), ldx, N, Kx, C, ptr(dw[:, Kg:]), Kg + Kx, ptr(ws_w), nb_w)
+            ws_w, nb_w = _gemm_ws(C, Kg, B, dev)
+            call('dc_linear_bwd_weight', ptr(dyg), C, ptr(g), ldg, B, Kg, C, ptr(dw), Kg + Kx, ptr(ws_w), nb_w)
+        if want_x:
+            dx = torch.empty(N, Kx, dtype=_F32, device=dev)
+            ws_x, nb_x = _gemm_ws(N, Kx, C, dev)
+            call('dc_linear_bwd_input', ptr(dy), C, ptr(Wx), ldw, N, Kx, C, ptr(dx), Kx, ptr(ws_x), nb_x)
+        if want_g:
+            dg = torch.empty(B, Kg, dtype=_F32, device=dev)
+            ws_x, nb_x = _gemm_ws(B, Kg, C, dev)
+            call('dc_linear_bwd_input', ptr(dyg), C, ptr(Wg), ldw, B, Kg, C, ptr(dg), Kg, ptr(ws_x), nb_x)
+        return (dx, dg, dw, dgamma if gamma is not None else None, dbeta if beta is not None else None, None, None, None, None)
+
+
+def linear_bcast_bn_act(x, g, weight, bn, slope, batch, num_clouds=None):
+    """act(BatchNorm1d(cat([g[batch], x], 1) @ weight.T)) without forming g[batch]: x [N,Kx] per point, g [B,Kg] per cloud."""
+    cp, B = cloud_ptr_of(batch, x.size(0), x.device, num_clouds)
+    return _LinearBcastBNAct.apply(x, g, weight, bn.weight, bn.bias, bn, float(slope), cp, B)
+
+
 def broadcast_rows(src, batch, num_points, slot=None):
     cp, B = cloud_ptr_of(batch, num_points, src.device, src.size(0))
     return _BcastRows.apply(src, cp, B, num_points, slot)

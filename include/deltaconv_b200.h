@@ -291,6 +291,10 @@ int dc_add_rows(const float* a, int64_t lda, const float* b, int64_t ldb, int64_
 /* out[i,:] = src[cloud(i),:] — `global_max_pool(x, batch)[batch]`, deltanet_segmentation.py:61,64 */
 int dc_bcast_rows(const float* src, int64_t lds, const int32_t* cloud_ptr, int B, int N, int C, float* out, int64_t ldo,
                   void* stream);
+/* out[i,:] += src[cloud of i,:]: a Linear over [x_max[batch] | per-point features] (deltanet_segmentation.py:61-66) is the product
+ * with the per-point block plus the product of the B pooled rows with their weight columns, added here. */
+int dc_bcast_rows_add(const float* src, int64_t lds, const int32_t* cloud_ptr, int B, int N, int C, float* out, int64_t ldo,
+                      void* stream);
 
 /* ---- Linear (mlp.py:9,15; heads) ---------------------------------------------------------------- */
 /* Precision of the tensor-core (tcgen05) path behind dc_linear_*: 3 = 3xTF32 split, fp32-grade accuracy (default);

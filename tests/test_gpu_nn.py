@@ -825,3 +825,48 @@ def test_deep_centralized_edge_mlp_matches_the_plain_sequence_and_the_oracle(tra
     err = rel_err(out_b.cpu().double(), t)
     report(f'deep_centralized.depth{depth}.train{int(train)}.out_vs_fp64', err)
     assert err < 2e-5, err
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('train', [True, False])
+def test_segmentation_head_without_the_broadcast_matches_the_materialised_form(train):
+    """DeltaNetSegmentation computes the head's first Linear over [x_max[batch] | categorical[batch] | conv features] as a per-point
+    product plus a per-cloud product added per cloud (ops.linear_bcast_bn_act).  Against the materialised concatenation
+    (decompose_head = False) on the same parameters: logits and every parameter gradient."""
+    D = dc()
+    torch.manual_seed(8)
+    d = D.utils.synthetic_batch(3, 0, config=13, sizes=[400, 250, 350], per_point_labels=True, num_classes=50, categories=16)
+    data = d.to(DEV)
+    net = D.models.DeltaNetSegmentation(3, 50, conv_channels=[32, 64], mlp_depth=2, embedding_size=128, categorical_vector=True,
+                                        num_neighbors=12).to(DEV)
+    net = D.utils.fill_deterministic(net, 3).to(DEV)
+    results = []
+    for decompose in (False, True):
+        m = copy.deepcopy(net).train(train)
+        m.decompose_head = decompose
+        for mod in m.modules():
+            if isinstance(mod, torch.nn.Dropout):
+                mod.p = 0.0
+        out = m(data)
+        F.cross_entropy(out, data.y).backward()
+        results.append((out.detach(), {n: p.grad for n, p in m.named_parameters()}))
+    (out_a, ga), (out_b, gb) = results
+    err = report(f'seg_head_decomposed.train{int(train)}.logits', rel_err(out_b, out_a))
+    assert err < 2e-5, err
+    # Gradients: a tensor's error is taken relative to max(its own scale, 1e-3 of the network's largest gradient) — in training
+    # mode some are analytically zero (a shift of lin_global's output is removed by the head's BatchNorm) — and single arg-max /
+    # LeakyReLU-kink flips between two fp32 evaluations move a small tensor by up to a percent (DESIGN.md section 4): the bound
+    # is on the median over tensors, with a loose cap on each.
+    scale = max(float(g.abs().max()) for g in ga.values() if g is not None)
+    errs = {}
+    for n in ga:
+        if ga[n] is None:
+            assert gb[n] is None, n
+            continue
+        errs[n] = float((gb[n] - ga[n]).abs().max()) / max(float(ga[n].abs().max()), 1e-3 * scale)
+    ordered = sorted(errs.values())
+    median, worst = ordered[len(ordered) // 2], ordered[-1]
+    report(f'seg_head_decomposed.train{int(train)}.median_grad', median)
+    report(f'seg_head_decomposed.train{int(train)}.worst_grad', worst)
+    assert median < 1e-3, median
+    assert worst < 5e-2, max(errs, key=errs.get)
