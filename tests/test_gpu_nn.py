@@ -853,10 +853,13 @@ def test_segmentation_head_without_the_broadcast_matches_the_materialised_form(t
     (out_a, ga), (out_b, gb) = results
     err = report(f'seg_head_decomposed.train{int(train)}.logits', rel_err(out_b, out_a))
     assert err < 2e-5, err
-    # Gradients: a tensor's error is taken relative to max(its own scale, 1e-3 of the network's largest gradient) — in training
-    # mode some are analytically zero (a shift of lin_global's output is removed by the head's BatchNorm) — and single arg-max /
-    # LeakyReLU-kink flips between two fp32 evaluations move a small tensor by up to a percent: the bound
-    # is on the median over tensors, with a loose cap on each.
+    # Gradients.  The two forms agree to ~2e-6 in the head's first pre-activation, which is enough to put a handful of its
+    # ~640 K LeakyReLU inputs (three head blocks x 1000 points) on the other side of zero; ONE such flip changes the gradient of
+    # one point by O(1) of itself, i.e. every upstream tensor by ~1/N = 1e-3 here (measured on B200: training mode no flip,
+    # median 2.5e-6, worst 2.7e-5; evaluation mode one flip, median 1.6e-3, worst 9.9e-3).  A wrong block offset or a missing
+    # term shows as O(0.1 - 1): the bounds sit between.  A tensor's error is relative to max(its own scale, 1e-3 of the
+    # network's largest gradient) — in training mode some gradients are analytically zero (a shift of lin_global's output is
+    # removed by the head's BatchNorm).  Parity of the gradients with the fp64 oracle is test_gpu_configs.py's job.
     scale = max(float(g.abs().max()) for g in ga.values() if g is not None)
     errs = {}
     for n in ga:
@@ -868,5 +871,5 @@ def test_segmentation_head_without_the_broadcast_matches_the_materialised_form(t
     median, worst = ordered[len(ordered) // 2], ordered[-1]
     report(f'seg_head_decomposed.train{int(train)}.median_grad', median)
     report(f'seg_head_decomposed.train{int(train)}.worst_grad', worst)
-    assert median < 1e-3, median
-    assert worst < 5e-2, max(errs, key=errs.get)
+    assert median < 1e-2, median
+    assert worst < 1e-1, max(errs, key=errs.get)
