@@ -84,3 +84,22 @@ def test_last_block_folded_into_the_max():
     dy = (gamma.detach() * invstd.detach()) * (hit - S1 / E - xh3 * (S2 / E))
     assert torch.allclose(dy.reshape(E, -1), y.grad, atol=1e-10)
     assert torch.allclose(S2, gamma.grad, atol=1e-10) and torch.allclose(S1, beta.grad, atol=1e-10)
+
+
+def test_head_linear_without_the_broadcast():
+    """ops.linear_bcast_bn_act's algebra (deltanet_segmentation.py:61-66): cat([g[batch], x], 1) @ W.T = x @ W_x.T + (g @ W_g.T)[batch]
+    with W = [W_g | W_x]; the gradients of g and of W_g come from the per-cloud sums of dy."""
+    gen = torch.Generator().manual_seed(3)
+    N, B, Kg, Kx, C = 50, 3, 7, 4, 6
+    batch = torch.sort(torch.randint(0, B, (N,), generator=gen)).values
+    x = torch.randn(N, Kx, generator=gen, dtype=torch.float64, requires_grad=True)
+    g = torch.randn(B, Kg, generator=gen, dtype=torch.float64, requires_grad=True)
+    W = torch.randn(C, Kg + Kx, generator=gen, dtype=torch.float64, requires_grad=True)
+    y = torch.cat([g[batch], x], 1) @ W.T
+    dy = torch.randn(N, C, generator=gen, dtype=torch.float64)
+    y.backward(dy)
+    Wg, Wx = W.detach()[:, :Kg], W.detach()[:, Kg:]
+    assert torch.allclose(x.detach() @ Wx.T + (g.detach() @ Wg.T)[batch], y.detach(), atol=1e-12)
+    dyg = torch.zeros(B, C, dtype=torch.float64).index_add_(0, batch, dy)
+    assert torch.allclose(dy @ Wx, x.grad, atol=1e-12) and torch.allclose(dyg @ Wg, g.grad, atol=1e-12)
+    assert torch.allclose(torch.cat([dyg.T @ g.detach(), dy.T @ x.detach()], 1), W.grad, atol=1e-12)
