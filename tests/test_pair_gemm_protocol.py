@@ -53,3 +53,14 @@ def test_shared_barriers_reproduce_the_fault_seen_on_b200():
         except model.ProtocolViolation as exc:
             outcomes.add('fault' if 'no pending arrival' in str(exc) else 'stuck')
     assert {'clean', 'stale', 'fault'} <= outcomes, outcomes
+
+
+def test_slow_roles_do_not_break_it_either():
+    """Roles that are scheduled fifty times less often than the others (a converter group behind the rest, a lagging producer, a
+    slow epilogue): a parity wait is also wrong when the waiter is LATE by two phases — it would then block for ever."""
+    names = ['mma'] + [f'{r}{c}' for c in (0, 1) for r in ('a_prod', 'b_prod', 'epi')] + [f'conv{c}{g}' for c in (0, 1) for g in (0, 1)]
+    for s in range(800):
+        rng = random.Random(5000 + s)
+        weights = {n: rng.choice([1.0, 1.0, 1.0, 0.02]) for n in names}
+        m = model.PairGemmModel(rng.randint(1, 5), rng.randint(1, 7), False, rng, rng.choice([0.0, 0.05, 0.3]))
+        m.run(role_weights=weights)                              # raises ProtocolViolation on a stale read, a barrier fault or a deadlock

@@ -187,7 +187,9 @@ class PairGemmModel:
             self.acc_empty[acc].arrive()
 
     # -- scheduler ------------------------------------------------------------------------------------------
-    def run(self, max_ticks=2_000_000):
+    def run(self, max_ticks=2_000_000, role_weights=None):
+        """role_weights: name -> relative chance of being scheduled when runnable (default 1): slow roles stress the windows in
+        which a parity test is meaningful from the other side (a waiter that is LATE by two phases would block for ever)."""
         roles = {'mma': self.mma()}
         for c in range(2):
             roles[f'a_prod{c}'] = self.a_producer(c)
@@ -212,7 +214,10 @@ class PairGemmModel:
                     raise ProtocolViolation('deadlock: ' + ', '.join(f'{n}: {w[0].name}/{w[1]}' for n, w in waiting.items() if n in roles and w))
                 self.tick = min(e[0] for e in self.events) - 1
                 continue
-            name = self.rng.choice(runnable)
+            if role_weights:
+                name = self.rng.choices(runnable, weights=[role_weights.get(n, 1.0) for n in runnable])[0]
+            else:
+                name = self.rng.choice(runnable)
             try:
                 waiting[name] = next(roles[name])
             except StopIteration:
