@@ -319,7 +319,7 @@ extern "C" int dc_morton_keys(const float* pos, const int32_t* cloud_ptr, int B,
     return dc_check_launch_n("dc_morton_keys", 3);
 }
 
-// tuning: points per bounding-box cell the grid aims at (default 2)
+// tuning: points per bounding-box cell the grid aims at (0 = default: chosen per cloud from its size, grid_of_cloud)
 extern "C" int dc_set_knn_grid_density(float points_per_cell) {
     DC_REQUIRE(points_per_cell == 0.f || (points_per_cell >= 0.25f && points_per_cell <= 64.f), "dc_set_knn_grid_density: out of range (0 = automatic)");
     g_points_per_cell = points_per_cell;

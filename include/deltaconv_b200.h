@@ -47,11 +47,11 @@ int dc_knn(const float* pos, const int32_t* cloud_ptr, int B, int N, int k, int3
 
 /* The same graph for large clouds: a uniform grid per cloud (counting sort by cell) and a ring search per query instead of the
  * O(P^2) scan; exact, so bit-identical to dc_knn.  Worth it from a few thousand points per cloud (deltaconv_b200.ops.knn switches at
- * 1536).  Workspace from dc_knn_grid_ws_bytes(N, B); no host synchronisation. */
+ * 1536 points per cloud, at 1000 for k >= 20).  Workspace from dc_knn_grid_ws_bytes(N, B); no host synchronisation. */
 size_t dc_knn_grid_ws_bytes(int N, int B);
-int dc_set_knn_grid_density(float points_per_bounding_box_cell);
+int dc_set_knn_grid_density(float points_per_bounding_box_cell);   /* tuning knob; 0 (default) = by cloud size: 6 / 3 / 1.5 */
 /* tuning: survivors per round from which the top-k list merges instead of inserting (one / two list slots per lane; <= 0 keeps) */
-int dc_set_knn_merge_min(int one_slot, int two_slots);   /* tuning knob, default 2 */
+int dc_set_knn_merge_min(int one_slot, int two_slots);   /* tuning knob, defaults 12 and 8 */
 int dc_knn_grid(const float* pos, const int32_t* cloud_ptr, int B, int N, int k, int32_t* idx,
                 int64_t* edge_index_or_null, float* d2_or_null, void* ws, size_t ws_bytes, void* stream);
 
